@@ -1,0 +1,253 @@
+/*
+ * fitslam_cuda.h -- C ABI of the B200-native FIT-SLAM exploration hot path.
+ *
+ * This is the drop-in boundary.  Every entry point below
+ * replaces one public method of the reference's `frontier_exploration` C++
+ * classes; the header-only C++ classes under fit-slam_b200/cpp/ wrap these
+ * calls behind the reference's own signatures.  Plain pointers and sizes only:
+ * no STL, no torch types, no exceptions across the boundary.
+ *
+ * Reference paths are relative to /root/reference:
+ *   DEP/  = dev_ws/src/DEPRECATED/frontier_exploration/frontier_exploration/
+ *   ORBW/ = ORB-SLAM3-ROS2-Docker/orb_slam3_ros2_wrapper/
+ *
+ * Threading: one context = one CUDA stream.  Calls on one context are not
+ * re-entrant (the reference is single-threaded per behaviour-tree tick,
+ * DEP/src/ExplorationBT.cpp:166-197); different contexts are independent.
+ *
+ * There is NO CPU fallback: every compute entry point launches sm_100a kernels
+ * and returns FITSLAM_E_CUDA if the device is unavailable.
+ */
+#ifndef FITSLAM_CUDA_H_
+#define FITSLAM_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define FITSLAM_API
+#else
+#define FITSLAM_API __attribute__((visibility("default")))
+#endif
+
+#define FITSLAM_ABI_VERSION 1
+
+typedef struct fitslam_ctx fitslam_ctx;
+
+typedef enum fitslam_status {
+  FITSLAM_OK = 0,
+  FITSLAM_E_INVALID = 1,             /* bad argument / parameter out of the supported range     */
+  FITSLAM_E_CUDA = 2,                /* CUDA runtime error; text in fitslam_last_error()         */
+  FITSLAM_E_CAPACITY = 3,            /* caller buffer too small; required count written back     */
+  FITSLAM_E_NO_COSTMAP = 4,          /* compute call before fitslam_set_costmap                  */
+  FITSLAM_E_ROBOT_OUT_OF_BOUNDS = 5, /* DEP/src/FrontierSearch.cpp:28-32 (empty list + CRITICAL) */
+  FITSLAM_E_NO_FRONTIERS = 6,        /* DEP/src/FrontierCostsManager.cpp:55-59 (returns false)   */
+  FITSLAM_E_NO_POLYGON = 7,          /* DEP/src/FrontierCostsManager.cpp:61-65 (returns false)   */
+  FITSLAM_E_ARRIVAL_UTILITY = 8,     /* "ARRIVAL UTILITY ERROR! MORE THAN 1" :149 (throws)       */
+  FITSLAM_E_COST_OUT_OF_BOUNDS = 9,  /* "Cost out of bounds" :174 (throws)                       */
+  FITSLAM_E_NO_LOOKUP_TABLE = 10,    /* "Cannot load lookup table..." FisherInfoManager.cpp:238  */
+  FITSLAM_E_NO_MAP_POINTS = 11,      /* Fisher call before fitslam_set_map_points                */
+  FITSLAM_E_IO = 12
+} fitslam_status;
+
+/* ---- parameters (defaults = DEP/params/exploration_params.yaml:50-87) ---- */
+typedef struct fitslam_params {
+  /* frontierSearch/ (DEP/src/FrontierSearch.cpp:12-18) */
+  int32_t min_frontier_cluster_size; /* 1   */
+  int32_t max_frontier_cluster_size; /* 20 (supported: 1..63) */
+  double max_frontier_distance;      /* 50.0 m */
+  int32_t lethal_threshold;          /* 160 */
+  int32_t _pad0;
+  /* costCalculator/ (DEP/src/CostCalculator.cpp:7-9,19) */
+  double max_camera_depth; /* 2.0 m  */
+  double delta_theta;      /* 0.10 rad */
+  double camera_fov;       /* 1.04 rad */
+  double robot_radius;     /* 0.60 m (Costmap2DROS::getRobotRadius) */
+  double max_arrival_factor; /* 1.2  (DEP/src/CostCalculator.cpp:186) */
+  double min_arrival_factor; /* 0.70 (:188) */
+  /* frontierCostsManager/ (DEP/src/FrontierCostsManager.cpp:10-16) */
+  double alpha;  /* 0.25 */
+  double beta;   /* 1.0  */
+  double vx_max; /* 0.5  */
+  double wz_max; /* 0.5  */
+  /* FullPathOptimizer constants (DEP/include/.../FullPathOptimizer.hpp:13,16) */
+  int32_t num_frontiers_in_local_area; /* 5 */
+  int32_t _pad1;
+  double local_frontier_search_radius; /* 12.0 m */
+  /* Fisher information (DEP/include/.../FisherInfoManager.hpp:23-30, FisherInfoManager.cpp:41,89) */
+  float voxel_step;      /* step_max = 0.3f */
+  float crowd_exponent;  /* 0.8f */
+  double fisher_information_threshold; /* 550.0 */
+  /* lookup-table bounds (DEP/src/fisher_information/GenerateLookupMain.cpp:8) */
+  float lut_min_x, lut_max_x; /* 0, 21 */
+  float lut_min_y, lut_max_y; /* -+ 8.5*1.732 */
+  float lut_min_z, lut_max_z; /* -+ 8.5*1.732 */
+  /* pinhole intrinsics + image bounds (ORBW/params/gazebo_rgbd.yaml:10-13, ORBW/src/orb_slam3_interface.cpp:218-221) */
+  float fx, fy, cx, cy;       /* 432.496042035043 x2, 320, 240 */
+  float img_max_u, img_max_v; /* 640, 480 */
+  /* z of the candidate poses built from frontier goals (0.3) */
+  double candidate_pose_z;
+} fitslam_params;
+
+/* One frontier as produced by FrontierSearch::searchFrom (DEP/src/FrontierSearch.cpp:21-96,
+ * Frontier fields DEP/include/frontier_exploration/Frontier.hpp:39-136). */
+typedef struct fitslam_frontier {
+  double goal_x, goal_y;    /* goal point = centre of the median cell (FrontierSearch.cpp:161-165) */
+  uint32_t goal_mx, goal_my;/* the same cell in map coordinates */
+  int32_t size;             /* Frontier::getSize() */
+  uint32_t component;       /* ordinal of the 8-connected frontier component, in discovery order */
+  uint32_t chunk;           /* ordinal of this chunk inside its component */
+  uint32_t first_cell;      /* offset of this chunk's first cell in the every_frontier cell list */
+} fitslam_frontier;
+
+/* Output of FrontierCostCalculator::setArrivalInformationForFrontier (DEP/src/CostCalculator.cpp:23-121). */
+typedef struct fitslam_arrival {
+  int32_t information;    /* maxValue: best window sum of unknown cells (:93-102,112)        */
+  int32_t max_index;      /* maxIndex: first window attaining it                              */
+  double theta_s_star;    /* maxIndex*delta_theta + camera_fov/2 (:119); 0.0 on a failed ray  */
+  uint8_t achievable;     /* Frontier::isAchievable() after the call                          */
+  uint8_t footprint_in_lethal; /* isRobotFootprintInLethal (:77)                              */
+  uint8_t ray_failed;     /* getTracedCells returned false (:50-55)                           */
+  uint8_t _pad[5];
+} fitslam_arrival;
+
+/* A pose in the ROS map frame (geometry_msgs::msg::Pose). */
+typedef struct fitslam_pose {
+  double x, y, z;
+  double qx, qy, qz, qw;
+} fitslam_pose;
+
+/* Result of FullPathOptimizer::getFilteredFrontiersN (DEP/src/FullPathOptimizer.cpp:157-227).
+ * `sorted` (caller array, capacity >= F) receives the indices of the eligible frontiers in
+ * ascending path_length_m order.  local_frontiers = sorted[0 .. n_local),
+ * global_frontiers = sorted[global_begin .. global_begin + n_global). */
+typedef struct fitslam_selection {
+  uint32_t n_sorted;
+  uint32_t n_local;
+  uint32_t global_begin;
+  uint32_t n_global;
+  int32_t closest_global; /* frontier index of closest_global_frontier, -1 if none */
+  int32_t _pad;
+} fitslam_selection;
+
+/* Whole-cycle summary (fitslam_cycle). */
+typedef struct fitslam_cycle_result {
+  uint32_t n_frontiers;
+  uint32_t n_frontier_cells;
+  uint32_t n_components;
+  uint32_t n_candidates;   /* frontier x yaw-window candidates scored */
+  uint32_t n_fisher_poses; /* poses scored by the Fisher stage */
+  uint32_t bfs_levels;
+  uint32_t ambiguous_sorts;/* chunks whose median sort had two angles within 4 ulp */
+  uint32_t _pad;
+  fitslam_selection selection;
+  float stage_ms[8];       /* extract, arrival, distance, fisher, normalise+select, 3 spare */
+} fitslam_cycle_result;
+
+enum { FITSLAM_DIST_GIVEN = 0, FITSLAM_DIST_EUCLIDEAN = 1 };
+enum { FITSLAM_FISHER_OFF = 0, FITSLAM_FISHER_BEST_YAW = 1, FITSLAM_FISHER_ALL_YAWS = 2 };
+
+/* ------------------------------------------------------------------ lifecycle */
+FITSLAM_API int fitslam_abi_version(void);
+FITSLAM_API void fitslam_default_params(fitslam_params *p);
+FITSLAM_API fitslam_status fitslam_create(const fitslam_params *p, int device, fitslam_ctx **out);
+FITSLAM_API void fitslam_destroy(fitslam_ctx *ctx);
+FITSLAM_API const char *fitslam_last_error(const fitslam_ctx *ctx);
+FITSLAM_API const char *fitslam_status_string(fitslam_status s);
+/* Restrict the scoring stages to the frontiers f with f % nranks == rank (8e: candidate sharding).
+ * Records of the other frontiers are left untouched in the output buffers. */
+FITSLAM_API fitslam_status fitslam_set_shard(fitslam_ctx *ctx, int rank, int nranks);
+/* The CUDA stream all work of this context is enqueued on (a cudaStream_t). */
+FITSLAM_API void *fitslam_stream(fitslam_ctx *ctx);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+FITSLAM_API uint64_t fitslam_launch_count(const fitslam_ctx *ctx);
+
+/* ------------------------------------------------------------------ inputs */
+/* nav2_costmap_2d::Costmap2D snapshot (getCharMap/getSizeInCellsX/getResolution/getOriginX; T1).
+ * `data` may be a host or a device pointer (detected).  dirty_xywh = {x0,y0,w,h} restricts the
+ * upload to a sub-rectangle of an already-resident map of the same geometry (rapid mode), NULL = full. */
+FITSLAM_API fitslam_status fitslam_set_costmap(fitslam_ctx *ctx, const uint8_t *data, uint32_t size_x,
+                                               uint32_t size_y, double resolution, double origin_x,
+                                               double origin_y, const uint32_t *dirty_xywh);
+/* ORB-SLAM3 map points, ROS map frame, xyz float32 triples (slam_msgs/MapPoint.position; T7). */
+FITSLAM_API fitslam_status fitslam_set_map_points(fitslam_ctx *ctx, const float *xyz, uint64_t n_points);
+
+/* ------------------------------------------------------------------ frontier extraction */
+/* FrontierSearch::reset(); searchFrom(position); getAllFrontiers()
+ * (DEP/src/FrontierSearch.cpp:21-96,251-254; FrontierSearch.hpp:39-52).
+ * *n_frontiers in: capacity of `out`; out: number found.  every_cells (optional) receives the map index
+ * of every frontier cell in discovery order (getAllFrontiers); *n_cells in/out likewise.  */
+FITSLAM_API fitslam_status fitslam_search_frontiers(fitslam_ctx *ctx, double robot_x, double robot_y,
+                                                    fitslam_frontier *out, uint32_t *n_frontiers,
+                                                    uint32_t *every_cells, uint32_t *n_cells);
+FITSLAM_API fitslam_status fitslam_set_search_distance(fitslam_ctx *ctx, double max_frontier_distance);
+
+/* ------------------------------------------------------------------ arrival information */
+/* FrontierCostCalculator::setMaxArrivalInformation (DEP/src/CostCalculator.cpp:123-191). */
+FITSLAM_API fitslam_status fitslam_arrival_limits(fitslam_ctx *ctx, double *max_arrival_info_gt,
+                                                  double *min_arrival_info_gt, int32_t *max_value);
+/* setArrivalInformationForFrontier for a list of frontiers (DEP/src/CostCalculator.cpp:23-121).
+ * frontiers == NULL scores the list left on the device by the last fitslam_search_frontiers.
+ * info_along_ray (optional, F x n_rays uint16) and window_sums (optional, F x n_windows int32) expose
+ * the intermediate arrays `information_along_ray` / `result` of the reference for stage-wise parity. */
+FITSLAM_API fitslam_status fitslam_score_arrival(fitslam_ctx *ctx, const fitslam_frontier *frontiers,
+                                                 uint32_t n_frontiers, const double poly_xy_min_max[4],
+                                                 fitslam_arrival *out, uint16_t *info_along_ray,
+                                                 int32_t *window_sums);
+/* Ray fan geometry implied by the parameters: number of rays (theta loop :36), window k (:87), windows. */
+FITSLAM_API fitslam_status fitslam_ray_shape(const fitslam_ctx *ctx, uint32_t *n_rays, uint32_t *k,
+                                             uint32_t *n_windows, uint32_t *max_length);
+
+/* ------------------------------------------------------------------ Fisher information */
+/* FisherInformationManager::generateLookupTable / loadLookupTable
+ * (DEP/src/fisher_information/FisherInfoManager.cpp:117-262).  path may be NULL (memory only). */
+FITSLAM_API fitslam_status fitslam_fisher_generate_lookup(fitslam_ctx *ctx, const char *save_path);
+FITSLAM_API fitslam_status fitslam_fisher_load_lookup(fitslam_ctx *ctx, const char *path);
+/* Dense copy of the table: out[(ix*ny + iy)*nz + iz] (NaN = no entry); dims and index origin returned. */
+FITSLAM_API fitslam_status fitslam_fisher_lookup_dims(const fitslam_ctx *ctx, int32_t dims[3], int32_t origin[3]);
+FITSLAM_API fitslam_status fitslam_fisher_lookup_copy(fitslam_ctx *ctx, float *out, uint64_t capacity);
+/* FisherInformationManager::isPoseSafe for a batch of poses (FisherInfoManager.cpp:39-115) with the
+ * landmark service replaced by the resident map points culled as ORBW/src/orb_slam3_interface.cpp:188-317
+ * (exhaustive search) and transformed as ORBW/src/rgbd/rgbd-slam-node.cpp:414-429. */
+FITSLAM_API fitslam_status fitslam_score_fisher(fitslam_ctx *ctx, const fitslam_pose *poses, uint32_t n_poses,
+                                                float *information, uint8_t *safe, uint32_t *n_visible);
+
+/* ------------------------------------------------------------------ normalisation + selection */
+/* FrontierCostsManager::assignCosts U1 block (DEP/src/FrontierCostsManager.cpp:121-205) followed by
+ * FullPathOptimizer::getFilteredFrontiersN (DEP/src/FullPathOptimizer.cpp:157-227).
+ * arrival/achievable come from the last fitslam_score_arrival.  path_length_m / path_heading: one per
+ * frontier (inputs produced by the planner in the reference); blacklisted may be NULL. */
+FITSLAM_API fitslam_status fitslam_normalise_select(fitslam_ctx *ctx, const double *path_length_m,
+                                                    const double *path_heading, const uint8_t *blacklisted,
+                                                    uint32_t n_frontiers, double *weighted_cost,
+                                                    double *arrival_utility, double *distance_utility,
+                                                    uint8_t *achievable, uint32_t *sorted,
+                                                    fitslam_selection *sel);
+
+/* ------------------------------------------------------------------ one whole exploration cycle */
+/* searchFrom -> setArrivalInformationForFrontier -> setPlanForFrontierEuclidean -> (Fisher) -> U1 ->
+ * getFilteredFrontiersN, enqueued back to back on the context stream with a single host sync at the end.
+ * robot_yaw feeds path_heading (DEP/src/CostCalculator.cpp:467-477). */
+FITSLAM_API fitslam_status fitslam_cycle(fitslam_ctx *ctx, double robot_x, double robot_y, double robot_yaw,
+                                         const double poly_xy_min_max[4], int fisher_mode,
+                                         fitslam_cycle_result *result);
+/* Copy-out of the per-frontier records of the last cycle (any pointer may be NULL). */
+FITSLAM_API fitslam_status fitslam_cycle_fetch(fitslam_ctx *ctx, fitslam_frontier *frontiers,
+                                               fitslam_arrival *arrival, double *path_length_m,
+                                               double *path_heading, double *weighted_cost, float *fisher_info,
+                                               uint32_t *sorted, uint32_t capacity);
+
+/* ------------------------------------------------------------------ multi-GPU plumbing (8e) */
+/* Device address + byte size of the packed per-frontier score records of the last scoring call, laid out
+ * for an in-place all-gather (record f of rank r lives at index f).  16 bytes per frontier:
+ * {int32 information, int32 max_index, float fisher, uint32 flags}. */
+FITSLAM_API fitslam_status fitslam_score_records(fitslam_ctx *ctx, void **device_ptr, uint64_t *bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FITSLAM_CUDA_H_ */
