@@ -1,0 +1,142 @@
+// ctx.h -- internal state of one fitslam context (one CUDA stream, device-resident map + points).
+// Not part of the ABI; include/fitslam_cuda.h is.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/fitslam_cuda.h"
+
+namespace fitslam {
+
+// Device view of a nav2_costmap_2d::Costmap2D snapshot (T1).  Rows are stored with a pitch that is a
+// multiple of 16 bytes so the same buffer can back a TMA tensor map; map indices at the ABI are my*W+mx.
+struct MapView {
+  const uint8_t *data;
+  uint32_t W, H, pitch;
+  double res, ox, oy;
+};
+
+// Ray fan geometry (function of the parameters only; DEP/src/CostCalculator.cpp:28,36,42,87).
+struct RayShape {
+  uint32_t n_rays;     // iterations of `for (theta = 0; theta <= 2*pi; theta += delta_theta)`
+  uint32_t k;          // static_cast<int>(camera_fov / delta_theta)
+  uint32_t n_windows;  // n_rays - k + 1
+  uint32_t max_length; // (unsigned)(max_camera_depth / resolution)
+  uint32_t radius_cells; // ceil(robot_radius / resolution)
+  uint32_t half;       // half size of the staged window: max(max_length, radius_cells)
+};
+
+template <typename T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t cap = 0;  // elements
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = n + n / 4 + 64;
+    cudaError_t e = cudaMalloc((void **)&p, want * sizeof(T));
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct ScoreRecord {  // 16 bytes, the all-gather unit
+  int32_t information;
+  int32_t max_index;
+  float fisher;
+  uint32_t flags;  // bit0 achievable, bit1 footprint_in_lethal, bit2 ray_failed, bit3 fisher valid, bit4 fisher safe
+};
+
+}  // namespace fitslam
+
+struct fitslam_ctx {
+  fitslam_params prm;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+  int rank = 0, nranks = 1;
+
+  // ---- costmap
+  fitslam::DevBuf<uint8_t> map;
+  uint32_t W = 0, H = 0, pitch = 0;
+  double res = 0, ox = 0, oy = 0;
+  bool have_map = false;
+  CUtensorMap tmap;       // 2-D uint8 tensor map over `map`
+  bool have_tmap = false;
+  int use_tma = 1;        // FITSLAM_RAYCAST_TMA=0 switches to the direct-gather variant (ablation)
+
+  // ---- ray fan tables (host-built from parameters, uploaded)
+  fitslam::RayShape shape{};
+  fitslam::DevBuf<double> ray_dxdy;  // 2*n_rays doubles: depth*cos(theta_i), depth*sin(theta_i)
+  double shape_res = -1.0;
+  bool limits_set = false;
+  double max_arrival_info_gt = 0.0, min_arrival_info_gt = 0.0;
+  int32_t limits_max_value = 0;
+
+  // ---- frontier list resident on the device (last search / last upload)
+  fitslam::DevBuf<fitslam_frontier> frontiers;
+  uint32_t n_frontiers = 0;
+  fitslam::DevBuf<fitslam_arrival> arrival;
+  fitslam::DevBuf<uint16_t> info_ray;
+  fitslam::DevBuf<int32_t> win_sums;
+  fitslam::DevBuf<fitslam::ScoreRecord> records;
+
+  // ---- scratch
+  fitslam::DevBuf<uint8_t> scratch;
+  void *pinned = nullptr;
+  size_t pinned_cap = 0;
+
+  // opaque per-stage state (defined in the stage's .cu file)
+  struct FrontierState *fs = nullptr;
+  struct FisherState *fi = nullptr;
+  struct SelectState *sel = nullptr;
+};
+
+namespace fitslam {
+
+inline fitslam_status fail(fitslam_ctx *c, fitslam_status s, const std::string &msg) {
+  if (c) c->err = msg;
+  return s;
+}
+#define FS_CUDA(ctx, expr)                                                                         \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) {                                                                       \
+      return ::fitslam::fail((ctx), FITSLAM_E_CUDA,                                                \
+                             std::string(#expr) + ": " + cudaGetErrorString(_e));                  \
+    }                                                                                              \
+  } while (0)
+
+inline MapView map_view(const fitslam_ctx *c) {
+  MapView m;
+  m.data = c->map.p;
+  m.W = c->W;
+  m.H = c->H;
+  m.pitch = c->pitch;
+  m.res = c->res;
+  m.ox = c->ox;
+  m.oy = c->oy;
+  return m;
+}
+
+fitslam_status ensure_pinned(fitslam_ctx *c, size_t bytes);
+fitslam_status update_ray_shape(fitslam_ctx *c);
+
+// stage entry points (each .cu file)
+fitslam_status raycast_limits(fitslam_ctx *c);
+fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_frontiers, uint32_t n,
+                             const double poly[4], fitslam_arrival *d_out, uint16_t *d_info_ray,
+                             int32_t *d_win_sums, ScoreRecord *d_records);
+
+}  // namespace fitslam
