@@ -1,0 +1,274 @@
+"""ctypes view of include/fitslam_cuda.h (the C ABI of libfitslam_cuda.so).
+
+This is test/bench plumbing: the product is the shared library and the C++ classes in
+fit-slam_b200/cpp/.  There is no fallback: if the library is missing, import fails.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfitslam_cuda.so")
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("min_frontier_cluster_size", C.c_int32), ("max_frontier_cluster_size", C.c_int32),
+        ("max_frontier_distance", C.c_double), ("lethal_threshold", C.c_int32), ("_pad0", C.c_int32),
+        ("max_camera_depth", C.c_double), ("delta_theta", C.c_double), ("camera_fov", C.c_double),
+        ("robot_radius", C.c_double), ("max_arrival_factor", C.c_double), ("min_arrival_factor", C.c_double),
+        ("alpha", C.c_double), ("beta", C.c_double), ("vx_max", C.c_double), ("wz_max", C.c_double),
+        ("num_frontiers_in_local_area", C.c_int32), ("_pad1", C.c_int32),
+        ("local_frontier_search_radius", C.c_double),
+        ("voxel_step", C.c_float), ("crowd_exponent", C.c_float), ("fisher_information_threshold", C.c_double),
+        ("lut_min_x", C.c_float), ("lut_max_x", C.c_float), ("lut_min_y", C.c_float), ("lut_max_y", C.c_float),
+        ("lut_min_z", C.c_float), ("lut_max_z", C.c_float),
+        ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+        ("img_max_u", C.c_float), ("img_max_v", C.c_float), ("candidate_pose_z", C.c_double),
+    ]
+
+
+FRONTIER_DTYPE = np.dtype([("goal_x", "<f8"), ("goal_y", "<f8"), ("goal_mx", "<u4"), ("goal_my", "<u4"),
+                           ("size", "<i4"), ("component", "<u4"), ("chunk", "<u4"), ("first_cell", "<u4")])
+ARRIVAL_DTYPE = np.dtype([("information", "<i4"), ("max_index", "<i4"), ("theta_s_star", "<f8"),
+                          ("achievable", "u1"), ("footprint_in_lethal", "u1"), ("ray_failed", "u1"),
+                          ("_pad", "u1", (5,))])
+POSE_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("qx", "<f8"), ("qy", "<f8"), ("qz", "<f8"),
+                       ("qw", "<f8")])
+RECORD_DTYPE = np.dtype([("information", "<i4"), ("max_index", "<i4"), ("fisher", "<f4"), ("flags", "<u4")])
+assert FRONTIER_DTYPE.itemsize == 40 and ARRIVAL_DTYPE.itemsize == 24 and POSE_DTYPE.itemsize == 56
+
+
+class Selection(C.Structure):
+    _fields_ = [("n_sorted", C.c_uint32), ("n_local", C.c_uint32), ("global_begin", C.c_uint32),
+                ("n_global", C.c_uint32), ("closest_global", C.c_int32), ("_pad", C.c_int32)]
+
+
+class CycleResult(C.Structure):
+    _fields_ = [("n_frontiers", C.c_uint32), ("n_frontier_cells", C.c_uint32), ("n_components", C.c_uint32),
+                ("n_candidates", C.c_uint32), ("n_fisher_poses", C.c_uint32), ("bfs_levels", C.c_uint32),
+                ("ambiguous_sorts", C.c_uint32), ("_pad", C.c_uint32), ("selection", Selection),
+                ("stage_ms", C.c_float * 8)]
+
+
+OK, E_INVALID, E_CUDA, E_CAPACITY, E_NO_COSTMAP, E_ROBOT_OUT_OF_BOUNDS, E_NO_FRONTIERS, E_NO_POLYGON, \
+    E_ARRIVAL_UTILITY, E_COST_OUT_OF_BOUNDS, E_NO_LOOKUP_TABLE, E_NO_MAP_POINTS, E_IO = range(13)
+DIST_GIVEN, DIST_EUCLIDEAN = 0, 1
+FISHER_OFF, FISHER_BEST_YAW, FISHER_ALL_YAWS = 0, 1, 2
+
+_vp, _u32p, _dp = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_double)
+
+# name -> (restype, argtypes); every symbol include/fitslam_cuda.h declares
+PROTOTYPES = {
+    "fitslam_abi_version": (C.c_int, []),
+    "fitslam_default_params": (None, [C.POINTER(Params)]),
+    "fitslam_create": (C.c_int, [C.POINTER(Params), C.c_int, C.POINTER(_vp)]),
+    "fitslam_destroy": (None, [_vp]),
+    "fitslam_last_error": (C.c_char_p, [_vp]),
+    "fitslam_status_string": (C.c_char_p, [C.c_int]),
+    "fitslam_set_shard": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "fitslam_stream": (_vp, [_vp]),
+    "fitslam_launch_count": (C.c_uint64, [_vp]),
+    "fitslam_set_costmap": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, _vp]),
+    "fitslam_set_map_points": (C.c_int, [_vp, _vp, C.c_uint64]),
+    "fitslam_search_frontiers": (C.c_int, [_vp, C.c_double, C.c_double, _vp, _u32p, _vp, _u32p]),
+    "fitslam_set_search_distance": (C.c_int, [_vp, C.c_double]),
+    "fitslam_arrival_limits": (C.c_int, [_vp, _dp, _dp, C.POINTER(C.c_int32)]),
+    "fitslam_score_arrival": (C.c_int, [_vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp]),
+    "fitslam_ray_shape": (C.c_int, [_vp, _u32p, _u32p, _u32p, _u32p]),
+    "fitslam_fisher_generate_lookup": (C.c_int, [_vp, C.c_char_p]),
+    "fitslam_fisher_load_lookup": (C.c_int, [_vp, C.c_char_p]),
+    "fitslam_fisher_lookup_dims": (C.c_int, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "fitslam_fisher_lookup_copy": (C.c_int, [_vp, _vp, C.c_uint64]),
+    "fitslam_score_fisher": (C.c_int, [_vp, _vp, C.c_uint32, _vp, _vp, _vp]),
+    "fitslam_normalise_select": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp, _vp,
+                                           C.POINTER(Selection)]),
+    "fitslam_cycle": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, C.POINTER(CycleResult)]),
+    "fitslam_cycle_fetch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint32]),
+    "fitslam_score_records": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
+}
+
+
+def load_library(path=LIB_PATH):
+    if not os.path.exists(path):
+        raise ImportError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback for the exploration hot path)")
+    lib = C.CDLL(path)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+def default_params(lib=None):
+    lib = lib or load_library()
+    p = Params()
+    lib.fitslam_default_params(C.byref(p))
+    return p
+
+
+class FitslamError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"fitslam status {status}: {msg}")
+        self.status = status
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data
+    return int(a)  # raw (device) address
+
+
+class Context:
+    """One fitslam_ctx.  Thin: every method is one C-ABI call plus numpy buffer allocation."""
+
+    def __init__(self, params=None, device=0, lib=None):
+        self.lib = lib or load_library()
+        self.params = params or default_params(self.lib)
+        h = _vp()
+        st = self.lib.fitslam_create(C.byref(self.params), device, C.byref(h))
+        if st != OK:
+            raise FitslamError(st, "fitslam_create: " + self.lib.fitslam_status_string(st).decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.fitslam_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _check(self, st, allow=()):
+        if st != OK and st not in allow:
+            raise FitslamError(st, self.lib.fitslam_last_error(self.h).decode())
+        return st
+
+    @property
+    def stream(self):
+        return self.lib.fitslam_stream(self.h)
+
+    @property
+    def launch_count(self):
+        return int(self.lib.fitslam_launch_count(self.h))
+
+    def set_shard(self, rank, nranks):
+        self._check(self.lib.fitslam_set_shard(self.h, rank, nranks))
+
+    def set_costmap(self, data, res, ox, oy, dirty=None, shape=None):
+        """data: uint8 numpy array [H, W] (host) or a raw device address with shape=(H, W)."""
+        if isinstance(data, np.ndarray):
+            assert data.dtype == np.uint8 and data.ndim == 2
+            data = np.ascontiguousarray(data)
+            H, W = data.shape
+        else:
+            H, W = shape
+        d = None if dirty is None else np.asarray(dirty, dtype=np.uint32)
+        self._check(self.lib.fitslam_set_costmap(self.h, _ptr(data), W, H, res, ox, oy, _ptr(d)))
+        self.W, self.H = W, H
+
+    def set_map_points(self, xyz, n=None):
+        if isinstance(xyz, np.ndarray):
+            xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+            n = xyz.shape[0]
+        self._check(self.lib.fitslam_set_map_points(self.h, _ptr(xyz), n))
+
+    def ray_shape(self):
+        v = [C.c_uint32() for _ in range(4)]
+        self._check(self.lib.fitslam_ray_shape(self.h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)  # n_rays, k, n_windows, max_length
+
+    def arrival_limits(self):
+        a, b, m = C.c_double(), C.c_double(), C.c_int32()
+        self._check(self.lib.fitslam_arrival_limits(self.h, C.byref(a), C.byref(b), C.byref(m)))
+        return a.value, b.value, m.value
+
+    def set_search_distance(self, d):
+        self._check(self.lib.fitslam_set_search_distance(self.h, d))
+
+    def search_frontiers(self, rx, ry, capacity=1 << 16, cell_capacity=1 << 21, want_cells=True):
+        out = np.zeros(capacity, dtype=FRONTIER_DTYPE)
+        n = C.c_uint32(capacity)
+        cells = np.zeros(cell_capacity, dtype=np.uint32) if want_cells else None
+        nc = C.c_uint32(cell_capacity if want_cells else 0)
+        st = self._check(self.lib.fitslam_search_frontiers(self.h, rx, ry, _ptr(out), C.byref(n), _ptr(cells),
+                                                           C.byref(nc)), allow=(E_ROBOT_OUT_OF_BOUNDS,))
+        if st == E_ROBOT_OUT_OF_BOUNDS:
+            return st, out[:0], (cells[:0] if want_cells else None)
+        return st, out[:n.value], (cells[:nc.value] if want_cells else None)
+
+    def score_arrival(self, frontiers, poly, want_rays=False, want_windows=False, n=None):
+        """frontiers: FRONTIER_DTYPE array, or None to score the list resident from the last search."""
+        if frontiers is not None:
+            frontiers = np.ascontiguousarray(frontiers)
+            n = len(frontiers)
+        n_rays, k, n_win, _ = self.ray_shape()
+        out = np.zeros(n, dtype=ARRIVAL_DTYPE)
+        rays = np.zeros((n, n_rays), dtype=np.uint16) if want_rays else None
+        wins = np.zeros((n, n_win), dtype=np.int32) if want_windows else None
+        poly = None if poly is None else np.asarray(poly, dtype=np.float64)
+        self._check(self.lib.fitslam_score_arrival(self.h, _ptr(frontiers), n, _ptr(poly), _ptr(out), _ptr(rays),
+                                                   _ptr(wins)))
+        return out, rays, wins
+
+    def fisher_generate_lookup(self, path=None):
+        self._check(self.lib.fitslam_fisher_generate_lookup(self.h, path.encode() if path else None))
+
+    def fisher_load_lookup(self, path):
+        self._check(self.lib.fitslam_fisher_load_lookup(self.h, path.encode()))
+
+    def fisher_lookup(self):
+        dims, org = (C.c_int32 * 3)(), (C.c_int32 * 3)()
+        self._check(self.lib.fitslam_fisher_lookup_dims(self.h, dims, org))
+        out = np.zeros(tuple(dims), dtype=np.float32)
+        self._check(self.lib.fitslam_fisher_lookup_copy(self.h, _ptr(out), out.size))
+        return out, tuple(org)
+
+    def score_fisher(self, poses):
+        poses = np.ascontiguousarray(poses)
+        n = len(poses)
+        info = np.zeros(n, dtype=np.float32)
+        safe = np.zeros(n, dtype=np.uint8)
+        nvis = np.zeros(n, dtype=np.uint32)
+        self._check(self.lib.fitslam_score_fisher(self.h, _ptr(poses), n, _ptr(info), _ptr(safe), _ptr(nvis)))
+        return info, safe, nvis
+
+    def normalise_select(self, path_length_m, path_heading, blacklisted=None):
+        n = len(path_length_m)
+        pl = np.ascontiguousarray(path_length_m, dtype=np.float64)
+        ph = np.ascontiguousarray(path_heading, dtype=np.float64)
+        bl = None if blacklisted is None else np.ascontiguousarray(blacklisted, dtype=np.uint8)
+        wc, ua, ud = (np.zeros(n, dtype=np.float64) for _ in range(3))
+        ach = np.zeros(n, dtype=np.uint8)
+        srt = np.zeros(n, dtype=np.uint32)
+        sel = Selection()
+        st = self._check(self.lib.fitslam_normalise_select(self.h, _ptr(pl), _ptr(ph), _ptr(bl), n, _ptr(wc), _ptr(ua),
+                                                           _ptr(ud), _ptr(ach), _ptr(srt), C.byref(sel)),
+                         allow=(E_ARRIVAL_UTILITY, E_COST_OUT_OF_BOUNDS))
+        return st, wc, ua, ud, ach, srt[:sel.n_sorted], sel
+
+    def cycle(self, rx, ry, ryaw, poly, fisher_mode=FISHER_OFF):
+        res = CycleResult()
+        poly = np.asarray(poly, dtype=np.float64)
+        st = self._check(self.lib.fitslam_cycle(self.h, rx, ry, ryaw, _ptr(poly), fisher_mode, C.byref(res)),
+                         allow=(E_ROBOT_OUT_OF_BOUNDS, E_NO_FRONTIERS))
+        return st, res
+
+    def cycle_fetch(self, n):
+        fr = np.zeros(n, dtype=FRONTIER_DTYPE)
+        ar = np.zeros(n, dtype=ARRIVAL_DTYPE)
+        pl, ph, wc = (np.zeros(n, dtype=np.float64) for _ in range(3))
+        fi = np.zeros(n, dtype=np.float32)
+        srt = np.zeros(n, dtype=np.uint32)
+        self._check(self.lib.fitslam_cycle_fetch(self.h, _ptr(fr), _ptr(ar), _ptr(pl), _ptr(ph), _ptr(wc), _ptr(fi),
+                                                 _ptr(srt), n))
+        return dict(frontiers=fr, arrival=ar, path_length_m=pl, path_heading=ph, weighted_cost=wc, fisher=fi, sorted=srt)
+
+    def score_records(self):
+        p, b = _vp(), C.c_uint64()
+        self._check(self.lib.fitslam_score_records(self.h, C.byref(p), C.byref(b)))
+        return p.value, b.value

@@ -1,0 +1,345 @@
+// api.cu -- C ABI entry points: lifecycle, inputs, ray-fan tables, arrival-information calls.
+// The stage kernels live in raycast.cu / frontier.cu / fisher.cu / select.cu.
+#include "ctx.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+using namespace fitslam;
+
+static_assert(sizeof(fitslam_params) == 192, "ABI layout");
+static_assert(sizeof(fitslam_frontier) == 40 && sizeof(fitslam_arrival) == 24 && sizeof(fitslam_pose) == 56, "ABI layout");
+static_assert(sizeof(fitslam_selection) == 24 && sizeof(fitslam_cycle_result) == 88 && sizeof(ScoreRecord) == 16, "ABI layout");
+
+namespace fitslam {
+
+fitslam_status ensure_pinned(fitslam_ctx *c, size_t bytes) {
+  if (bytes <= c->pinned_cap) return FITSLAM_OK;
+  if (c->pinned) cudaFreeHost(c->pinned);
+  c->pinned = nullptr;
+  c->pinned_cap = 0;
+  size_t want = bytes + bytes / 2 + 4096;
+  FS_CUDA(c, cudaMallocHost(&c->pinned, want));
+  c->pinned_cap = want;
+  return FITSLAM_OK;
+}
+
+// Ray fan geometry and the per-ray end-point offsets.  The theta loop is the reference's own
+// (`for (double theta = 0; theta <= 2*M_PI; theta += DELTA_THETA)`, DEP/src/CostCalculator.cpp:36) and
+// cos/sin are evaluated once here on the host, because they are functions of the parameters only.
+fitslam_status update_ray_shape(fitslam_ctx *c) {
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  if (c->shape_res == c->res) return FITSLAM_OK;
+  const fitslam_params &p = c->prm;
+  if (!(p.delta_theta > 0.0) || !(p.camera_fov > 0.0) || !(p.max_camera_depth > 0.0))
+    return fail(c, FITSLAM_E_INVALID, "delta_theta, camera_fov and max_camera_depth must be positive");
+  std::vector<double> tab;
+  for (double theta = 0; theta <= (2 * M_PI); theta += p.delta_theta) {
+    tab.push_back(p.max_camera_depth * cos(theta));
+    tab.push_back(p.max_camera_depth * sin(theta));
+    if (tab.size() > 2 * 1024) return fail(c, FITSLAM_E_INVALID, "delta_theta gives more than 1024 rays");
+  }
+  RayShape s;
+  s.n_rays = (uint32_t)(tab.size() / 2);
+  const int k = static_cast<int>(p.camera_fov / p.delta_theta);  // :87
+  if (k < 1 || (uint32_t)k > s.n_rays) return fail(c, FITSLAM_E_INVALID, "camera_fov / delta_theta out of range");
+  s.k = (uint32_t)k;
+  s.n_windows = s.n_rays - s.k + 1;
+  s.max_length = (unsigned int)(p.max_camera_depth / c->res);  // :28
+  s.radius_cells = (uint32_t)std::ceil(p.robot_radius / c->res);  // :77
+  s.half = std::max(s.max_length, s.radius_cells);  // Bresenham takes at most max_length steps
+  if (2 * s.half + 1 > 256) return fail(c, FITSLAM_E_INVALID, "ray length exceeds the 127-cell staged window");
+  FS_CUDA(c, c->ray_dxdy.reserve(tab.size()));
+  FS_CUDA(c, cudaMemcpyAsync(c->ray_dxdy.p, tab.data(), tab.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->shape = s;
+  c->shape_res = c->res;
+  return FITSLAM_OK;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// 2-D uint8 tensor map over the resident costmap; box = the staged window of the raycast kernel.
+static void build_tensor_map(fitslam_ctx *c) {
+  c->have_tmap = false;
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc || !c->have_map || c->shape_res != c->res) return;
+  const uint32_t tile_h = 2 * c->shape.half + 1;
+  const uint32_t tile_w = (tile_h + 15u) & ~15u;
+  cuuint64_t dims[2] = {c->W, c->H};
+  cuuint64_t strides[1] = {c->pitch};
+  cuuint32_t box[2] = {tile_w, tile_h};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(&c->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *)c->map.p, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  c->have_tmap = (r == CUDA_SUCCESS);
+}
+
+}  // namespace fitslam
+
+extern "C" {
+
+int fitslam_abi_version(void) { return FITSLAM_ABI_VERSION; }
+
+void fitslam_default_params(fitslam_params *p) {
+  if (!p) return;
+  memset(p, 0, sizeof(*p));
+  p->min_frontier_cluster_size = 1;
+  p->max_frontier_cluster_size = 20;
+  p->max_frontier_distance = 50.0;
+  p->lethal_threshold = 160;
+  p->max_camera_depth = 2.0;
+  p->delta_theta = 0.10;
+  p->camera_fov = 1.04;
+  p->robot_radius = 0.60;
+  p->max_arrival_factor = 1.2;
+  p->min_arrival_factor = 0.70;
+  p->alpha = 0.25;
+  p->beta = 1.0;
+  p->vx_max = 0.5;
+  p->wz_max = 0.5;
+  p->num_frontiers_in_local_area = 5;
+  p->local_frontier_search_radius = 12.0;
+  p->voxel_step = 0.3f;
+  p->crowd_exponent = 0.8f;
+  p->fisher_information_threshold = 550.0;
+  p->lut_min_x = 0.0f;
+  p->lut_max_x = 21.0f;
+  p->lut_min_y = (float)(-8.5 * 1.732);  // GenerateLookupMain.cpp:8, double product narrowed at the call
+  p->lut_max_y = (float)(8.5 * 1.732);
+  p->lut_min_z = (float)(-8.5 * 1.732);  // GenerateLookupMain.cpp:8, double product narrowed at the call
+  p->lut_max_z = (float)(8.5 * 1.732);
+  p->fx = (float)432.496042035043;
+  p->fy = (float)432.496042035043;
+  p->cx = 320.0f;
+  p->cy = 240.0f;
+  p->img_max_u = 640.0f;
+  p->img_max_v = 480.0f;
+  p->candidate_pose_z = 0.3;
+}
+
+const char *fitslam_status_string(fitslam_status s) {
+  switch (s) {
+    case FITSLAM_OK: return "ok";
+    case FITSLAM_E_INVALID: return "invalid argument";
+    case FITSLAM_E_CUDA: return "CUDA error";
+    case FITSLAM_E_CAPACITY: return "output buffer too small";
+    case FITSLAM_E_NO_COSTMAP: return "no costmap set";
+    case FITSLAM_E_ROBOT_OUT_OF_BOUNDS: return "Robot out of costmap bounds, cannot search for frontiers";
+    case FITSLAM_E_NO_FRONTIERS: return "No frontiers found from frontier search.";
+    case FITSLAM_E_NO_POLYGON: return "Frontier cannot be selected, no polygon.";
+    case FITSLAM_E_ARRIVAL_UTILITY: return "ARRIVAL UTILITY ERROR! MORE THAN 1";
+    case FITSLAM_E_COST_OUT_OF_BOUNDS: return "Cost out of bounds";
+    case FITSLAM_E_NO_LOOKUP_TABLE: return "Cannot load lookup table. Please generate it first.";
+    case FITSLAM_E_NO_MAP_POINTS: return "no map points set";
+    case FITSLAM_E_IO: return "I/O error";
+  }
+  return "unknown status";
+}
+
+fitslam_status fitslam_create(const fitslam_params *p, int device, fitslam_ctx **out) {
+  if (!out) return FITSLAM_E_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    return FITSLAM_E_CUDA;  // no CPU fallback: the path needs a device
+  }
+  fitslam_ctx *c = new (std::nothrow) fitslam_ctx();
+  if (!c) return FITSLAM_E_INVALID;
+  if (p) c->prm = *p; else fitslam_default_params(&c->prm);
+  const fitslam_params &q = c->prm;
+  if (q.max_frontier_cluster_size < 1 || q.max_frontier_cluster_size > 63 || q.min_frontier_cluster_size < 0 ||
+      q.lethal_threshold < 1 || q.lethal_threshold > 254) {
+    delete c;
+    return FITSLAM_E_INVALID;
+  }
+  c->device = device;
+  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    delete c;
+    return FITSLAM_E_CUDA;
+  }
+  const char *e = getenv("FITSLAM_RAYCAST_TMA");
+  if (e && e[0] == '0') c->use_tma = 0;
+  *out = c;
+  return FITSLAM_OK;
+}
+
+void fitslam_destroy(fitslam_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  destroy_frontier_state(c);
+  destroy_fisher_state(c);
+  destroy_select_state(c);
+  c->map.release();
+  c->ray_dxdy.release();
+  c->frontiers.release();
+  c->arrival.release();
+  c->info_ray.release();
+  c->win_sums.release();
+  c->records.release();
+  c->scratch.release();
+  if (c->pinned) cudaFreeHost(c->pinned);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+const char *fitslam_last_error(const fitslam_ctx *c) { return c ? c->err.c_str() : "null context"; }
+
+fitslam_status fitslam_set_shard(fitslam_ctx *c, int rank, int nranks) {
+  if (!c || nranks < 1 || rank < 0 || rank >= nranks) return fail(c, FITSLAM_E_INVALID, "bad shard");
+  c->rank = rank;
+  c->nranks = nranks;
+  return FITSLAM_OK;
+}
+
+void *fitslam_stream(fitslam_ctx *c) { return c ? (void *)c->stream : nullptr; }
+uint64_t fitslam_launch_count(const fitslam_ctx *c) { return c ? c->launches : 0; }
+
+
+/* ------------------------------------------------------------------ inputs */
+static bool is_device_ptr(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+fitslam_status fitslam_set_costmap(fitslam_ctx *c, const uint8_t *data, uint32_t size_x, uint32_t size_y,
+                                   double resolution, double origin_x, double origin_y, const uint32_t *dirty) {
+  if (!c || !data || size_x == 0 || size_y == 0 || !(resolution > 0.0))
+    return fail(c, FITSLAM_E_INVALID, "set_costmap: bad argument");
+  if ((uint64_t)size_x * size_y >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "set_costmap: more than 2^31 cells");
+  cudaSetDevice(c->device);
+  const bool same_geom = c->have_map && c->W == size_x && c->H == size_y && c->res == resolution &&
+                         c->ox == origin_x && c->oy == origin_y;
+  const cudaMemcpyKind kind = is_device_ptr(data) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  if (dirty) {
+    if (!same_geom) return fail(c, FITSLAM_E_INVALID, "set_costmap: dirty rectangle needs a resident map of the same geometry");
+    const uint32_t x0 = dirty[0], y0 = dirty[1], w = dirty[2], h = dirty[3];
+    if (w == 0 || h == 0) return FITSLAM_OK;
+    if ((uint64_t)x0 + w > size_x || (uint64_t)y0 + h > size_y) return fail(c, FITSLAM_E_INVALID, "set_costmap: dirty rectangle outside the map");
+    FS_CUDA(c, cudaMemcpy2DAsync(c->map.p + (size_t)y0 * c->pitch + x0, c->pitch, data + (size_t)y0 * size_x + x0, size_x,
+                                 w, h, kind, c->stream));
+    FS_CUDA(c, cudaStreamSynchronize(c->stream));  // the caller may reuse `data` on return
+    return FITSLAM_OK;
+  }
+  const uint32_t pitch = (size_x + 15u) & ~15u;  // TMA needs 16-byte row strides
+  FS_CUDA(c, c->map.reserve((size_t)pitch * size_y + 256));
+  if (pitch != size_x) FS_CUDA(c, cudaMemsetAsync(c->map.p, 0, (size_t)pitch * size_y, c->stream));
+  FS_CUDA(c, cudaMemcpy2DAsync(c->map.p, pitch, data, size_x, size_x, size_y, kind, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->W = size_x;
+  c->H = size_y;
+  c->pitch = pitch;
+  c->res = resolution;
+  c->ox = origin_x;
+  c->oy = origin_y;
+  c->have_map = true;
+  if (!same_geom) {
+    c->shape_res = -1.0;
+    // arrival_info_limits_set_ lives as long as the FrontierCostCalculator; a new map geometry is a new calculator
+    c->limits_set = false;
+  }
+  fitslam_status st = update_ray_shape(c);
+  if (st != FITSLAM_OK) return st;
+  build_tensor_map(c);
+  return FITSLAM_OK;
+}
+
+/* ------------------------------------------------------------------ arrival information */
+fitslam_status fitslam_ray_shape(const fitslam_ctx *c, uint32_t *n_rays, uint32_t *k, uint32_t *n_windows,
+                                 uint32_t *max_length) {
+  if (!c || !c->have_map) return FITSLAM_E_NO_COSTMAP;
+  if (n_rays) *n_rays = c->shape.n_rays;
+  if (k) *k = c->shape.k;
+  if (n_windows) *n_windows = c->shape.n_windows;
+  if (max_length) *max_length = c->shape.max_length;
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_arrival_limits(fitslam_ctx *c, double *max_gt, double *min_gt, int32_t *max_value) {
+  if (!c) return FITSLAM_E_INVALID;
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  cudaSetDevice(c->device);
+  fitslam_status st = raycast_limits(c);
+  if (st != FITSLAM_OK) return st;
+  if (max_gt) *max_gt = c->max_arrival_info_gt;
+  if (min_gt) *min_gt = c->min_arrival_info_gt;
+  if (max_value) *max_value = c->limits_max_value;
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_score_arrival(fitslam_ctx *c, const fitslam_frontier *frontiers, uint32_t n,
+                                     const double poly[4], fitslam_arrival *out, uint16_t *info_along_ray,
+                                     int32_t *window_sums) {
+  if (!c) return FITSLAM_E_INVALID;
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  if (!poly) return fail(c, FITSLAM_E_NO_POLYGON, "Frontier cannot be selected, no polygon.");
+  cudaSetDevice(c->device);
+  if (frontiers) {
+    FS_CUDA(c, c->frontiers.reserve(n));
+    if (n) FS_CUDA(c, cudaMemcpyAsync(c->frontiers.p, frontiers, (size_t)n * sizeof(fitslam_frontier),
+                                      is_device_ptr(frontiers) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    c->n_frontiers = n;
+  } else {
+    n = c->n_frontiers;
+  }
+  if (n == 0) return fail(c, FITSLAM_E_NO_FRONTIERS, "No frontiers found from frontier search.");
+  fitslam_status st = raycast_limits(c);  // assignCosts: setMaxArrivalInformation() first (FrontierCostsManager.cpp:67)
+  if (st != FITSLAM_OK) return st;
+  const RayShape &s = c->shape;
+  FS_CUDA(c, c->arrival.reserve(n));
+  FS_CUDA(c, c->records.reserve(n));
+  if (info_along_ray) FS_CUDA(c, c->info_ray.reserve((size_t)n * s.n_rays));
+  if (window_sums) FS_CUDA(c, c->win_sums.reserve((size_t)n * s.n_windows));
+  if (c->nranks > 1) {  // records of the other shards stay zero until the caller merges them
+    FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)n * sizeof(fitslam_arrival), c->stream));
+    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)n * sizeof(ScoreRecord), c->stream));
+    if (info_along_ray) FS_CUDA(c, cudaMemsetAsync(c->info_ray.p, 0, (size_t)n * s.n_rays * 2, c->stream));
+    if (window_sums) FS_CUDA(c, cudaMemsetAsync(c->win_sums.p, 0, (size_t)n * s.n_windows * 4, c->stream));
+  }
+  st = raycast_score(c, c->frontiers.p, n, poly, c->arrival.p, info_along_ray ? c->info_ray.p : nullptr,
+                     window_sums ? c->win_sums.p : nullptr, c->records.p);
+  if (st != FITSLAM_OK) return st;
+  if (out) FS_CUDA(c, cudaMemcpyAsync(out, c->arrival.p, (size_t)n * sizeof(fitslam_arrival),
+                                      is_device_ptr(out) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+  if (info_along_ray) FS_CUDA(c, cudaMemcpyAsync(info_along_ray, c->info_ray.p, (size_t)n * s.n_rays * 2, cudaMemcpyDefault, c->stream));
+  if (window_sums) FS_CUDA(c, cudaMemcpyAsync(window_sums, c->win_sums.p, (size_t)n * s.n_windows * 4, cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_score_records(fitslam_ctx *c, void **device_ptr, uint64_t *bytes) {
+  if (!c || !device_ptr || !bytes) return fail(c, FITSLAM_E_INVALID, "score_records: null argument");
+  *device_ptr = c->records.p;
+  *bytes = (uint64_t)c->n_frontiers * sizeof(ScoreRecord);
+  return FITSLAM_OK;
+}
+
+}  // extern "C"

@@ -133,6 +133,10 @@ inline MapView map_view(const fitslam_ctx *c) {
 fitslam_status ensure_pinned(fitslam_ctx *c, size_t bytes);
 fitslam_status update_ray_shape(fitslam_ctx *c);
 
+void destroy_frontier_state(fitslam_ctx *c);
+void destroy_fisher_state(fitslam_ctx *c);
+void destroy_select_state(fitslam_ctx *c);
+
 // stage entry points (each .cu file)
 fitslam_status raycast_limits(fitslam_ctx *c);
 fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_frontiers, uint32_t n,
