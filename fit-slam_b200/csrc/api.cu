@@ -61,41 +61,6 @@ fitslam_status update_ray_shape(fitslam_ctx *c) {
   return FITSLAM_OK;
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_tiled_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
-    void *p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
-  }
-  return fn;
-}
-
-// 2-D uint8 tensor map over the resident costmap; box = the staged window of the raycast kernel.
-static void build_tensor_map(fitslam_ctx *c) {
-  c->have_tmap = false;
-  EncodeTiledFn enc = encode_tiled_fn();
-  if (!enc || !c->have_map || c->shape_res != c->res) return;
-  const uint32_t tile_h = 2 * c->shape.half + 1;
-  const uint32_t tile_w = (tile_h + 15u) & ~15u;
-  cuuint64_t dims[2] = {c->W, c->H};
-  cuuint64_t strides[1] = {c->pitch};
-  cuuint32_t box[2] = {tile_w, tile_h};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(&c->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *)c->map.p, dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  c->have_tmap = (r == CUDA_SUCCESS);
-}
-
 }  // namespace fitslam
 
 extern "C" {
@@ -268,7 +233,6 @@ fitslam_status fitslam_set_costmap(fitslam_ctx *c, const uint8_t *data, uint32_t
   }
   fitslam_status st = update_ray_shape(c);
   if (st != FITSLAM_OK) return st;
-  build_tensor_map(c);
   return FITSLAM_OK;
 }
 

@@ -2,7 +2,6 @@
 // Not part of the ABI; include/fitslam_cuda.h is.
 #pragma once
 #include <cuda_runtime.h>
-#include <cuda.h>
 #include <stdint.h>
 #include <string>
 #include <vector>
@@ -12,7 +11,7 @@
 namespace fitslam {
 
 // Device view of a nav2_costmap_2d::Costmap2D snapshot (T1).  Rows are stored with a pitch that is a
-// multiple of 16 bytes so the same buffer can back a TMA tensor map; map indices at the ABI are my*W+mx.
+// multiple of 16 bytes so every window row can be fetched with 16-byte aligned TMA bulk copies; map indices at the ABI are my*W+mx.
 struct MapView {
   const uint8_t *data;
   uint32_t W, H, pitch;
@@ -72,8 +71,6 @@ struct fitslam_ctx {
   uint32_t W = 0, H = 0, pitch = 0;
   double res = 0, ox = 0, oy = 0;
   bool have_map = false;
-  CUtensorMap tmap;       // 2-D uint8 tensor map over `map`
-  bool have_tmap = false;
   int use_tma = 1;        // FITSLAM_RAYCAST_TMA=0 switches to the direct-gather variant (ablation)
 
   // ---- ray fan tables (host-built from parameters, uploaded)

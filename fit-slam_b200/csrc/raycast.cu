@@ -6,8 +6,10 @@
 // and setMaxArrivalInformation (DEP/src/CostCalculator.cpp:123-191).
 //
 // Layout: one thread group (a whole number of warps) per frontier, one lane per ray.  The (2*half+1)^2 costmap
-// window around the goal cell is staged into shared memory with one TMA tile load per frontier
-// (cp.async.bulk.tensor.2d, out-of-bounds cells zero-filled), rays walk it with Bresenham out of shared memory,
+// window around the goal cell is staged into shared memory by the TMA engine, one 1-D bulk copy per window row
+// (cp.async.bulk.shared::cluster.global, SASS UBLKCP, completion on an mbarrier; the tensor-map form UTMALDG raises
+// "illegal instruction" on this pool's B200 boxes even through libcu++'s own wrapper), rays walk it
+// with Bresenham out of shared memory,
 // per-ray unknown-cell counts are prefix-summed with warp shuffles, the k-ray windows are differenced from the
 // prefix and the first-max argmax is a warp-shuffle reduction.  All outputs are integers (bit-exact); the only
 // floating point is the IEEE double arithmetic that locates the end cell of each ray (no FMA contraction:
@@ -39,12 +41,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase) {
         : "memory");
   }
 }
-__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tmap, int c0, int c1, uint64_t *bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-          smem_u32(dst)),
-      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
-      : "memory");
+// 1-D bulk copy global -> shared through the TMA engine; src/dst 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void tma_bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 
 struct RayParams {
@@ -113,7 +114,7 @@ __device__ __forceinline__ int trace_ray(int x0, int y0, int x1, int y1, int str
 
 template <bool USE_TMA>
 __global__ void __launch_bounds__(1024)
-raycast_kernel(const __grid_constant__ CUtensorMap tmap, const RayParams P, const fitslam_frontier *__restrict__ fr,
+raycast_kernel(const RayParams P, const fitslam_frontier *__restrict__ fr,
                fitslam_arrival *__restrict__ out, uint16_t *__restrict__ info_ray_out, int32_t *__restrict__ win_out,
                ScoreRecord *__restrict__ rec_out) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -124,7 +125,7 @@ raycast_kernel(const __grid_constant__ CUtensorMap tmap, const RayParams P, cons
   const uint32_t nwg = P.tpf >> 5;
   // shared layout: [fpb tiles][fpb mbarriers][fpb * (tpf prefix ints)][fpb * 32 warp scratch (int64)][fpb flags]
   uint8_t *tile = smem + (size_t)g * P.tile_stride;
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)P.fpb * P.tile_stride);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (USE_TMA ? (size_t)P.fpb * P.tile_stride : 0));
   int32_t *prefix_all = reinterpret_cast<int32_t *>(bars + P.fpb);
   int32_t *prefix = prefix_all + (size_t)g * (P.tpf + 1);
   long long *wscr_all = reinterpret_cast<long long *>(prefix_all + (size_t)P.fpb * (P.tpf + 1) + ((P.fpb * (P.tpf + 1)) & 1));
@@ -157,9 +158,17 @@ raycast_kernel(const __grid_constant__ CUtensorMap tmap, const RayParams P, cons
     }
   }
   __syncthreads();
-  if (USE_TMA && t == 0 && live && goal_ok) {
-    mbar_expect_tx(&bars[g], P.tile_w * P.tile_h);
-    tma_load_2d(tile, &tmap, (int)x0 - half, (int)y0 - half, &bars[g]);
+  // staged window: rows [wy0, wy0 + wrows) x columns [wx0, wx0 + tile_w) of the map, wx0 16-byte aligned and
+  // clamped into the pitched row so every bulk copy stays inside the allocation
+  int wx0 = 0, wy0 = 0, wrows = 0;
+  if (USE_TMA && live && goal_ok) {
+    wx0 = ((int)x0 - half) & ~15;
+    wx0 = max(0, min(wx0, (int)P.map.pitch - (int)P.tile_w));
+    wy0 = max(0, (int)y0 - half);
+    wrows = min((int)P.map.H - 1, (int)y0 + half) - wy0 + 1;
+    if (t == 0) mbar_expect_tx(&bars[g], (uint32_t)wrows * P.tile_w);
+    for (int r = (int)t; r < wrows; r += (int)P.tpf)
+      tma_bulk_load(tile + r * (int)P.tile_w, P.map.data + (size_t)(wy0 + r) * P.map.pitch + wx0, P.tile_w, &bars[g]);
   }
 
   // ---- ray end cell (DEP/src/CostCalculator.cpp:42-48), overlapped with the tile load
@@ -180,8 +189,8 @@ raycast_kernel(const __grid_constant__ CUtensorMap tmap, const RayParams P, cons
   if (has_ray && ray_ok) {
     if (USE_TMA) {
       const int stride = (int)P.tile_w;
-      count = trace_ray<false>((int)x0, (int)y0, (int)x1, (int)y1, stride, half * stride + half, P.max_length_d,
-                               [&](int off) { return (int)tile[off]; });
+      count = trace_ray<false>((int)x0, (int)y0, (int)x1, (int)y1, stride, ((int)y0 - wy0) * stride + ((int)x0 - wx0),
+                               P.max_length_d, [&](int off) { return (int)tile[off]; });
     } else {
       const uint8_t *__restrict__ m = P.map.data;
       const int stride = (int)P.map.pitch;
@@ -198,12 +207,12 @@ raycast_kernel(const __grid_constant__ CUtensorMap tmap, const RayParams P, cons
     for (int i = (int)t; i < side * side; i += (int)P.tpf) {
       const int dy = i / side - r, dx = i - (i / side) * side - r;
       if (dx * dx + dy * dy > r * r) continue;
+      const int x = (int)x0 + dx, y = (int)y0 + dy;
+      if (x < 0 || y < 0 || x >= (int)P.map.W || y >= (int)P.map.H) continue;
       int cost;
       if (USE_TMA) {
-        cost = tile[(half + dy) * (int)P.tile_w + (half + dx)];  // cells off the map were zero-filled
+        cost = tile[(y - wy0) * (int)P.tile_w + (x - wx0)];
       } else {
-        const long x = (long)x0 + dx, y = (long)y0 + dy;
-        if (x < 0 || y < 0 || x >= (long)P.map.W || y >= (long)P.map.H) continue;
         cost = __ldg(P.map.data + (size_t)y * P.map.pitch + x);
       }
       lethal |= (cost == 254);
@@ -331,7 +340,7 @@ static RayParams make_params(fitslam_ctx *c, const double poly[4], uint32_t n) {
   P.delta_theta = c->prm.delta_theta;
   P.half_fov = c->prm.camera_fov / 2;
   P.tile_h = 2 * c->shape.half + 1;
-  P.tile_w = (P.tile_h + 15u) & ~15u;
+  P.tile_w = (P.tile_h + 15u + 15u) & ~15u;  // + up to 15 columns of slack from aligning the row start down to 16 B
   P.tpf = (std::max(c->shape.n_rays, 32u) + 31u) & ~31u;
   P.tile_stride = (P.tile_w * P.tile_h + 127u) & ~127u;
   P.n = n;
@@ -373,7 +382,7 @@ fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_fr, uint3
                              fitslam_arrival *d_out, uint16_t *d_info_ray, int32_t *d_win, ScoreRecord *d_rec) {
   if (n == 0) return FITSLAM_OK;
   RayParams P = make_params(c, poly, n);
-  const bool tma = c->use_tma && c->have_tmap;
+  const bool tma = c->use_tma && c->pitch >= P.tile_w;
   // frontiers per block: fill ~256 threads, bounded by shared memory
   uint32_t fpb = std::max(1u, 256u / P.tpf);
   while (fpb > 1 && (size_t)fpb * P.tile_stride > 96 * 1024) --fpb;
@@ -385,10 +394,10 @@ fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_fr, uint3
   const uint32_t block = fpb * P.tpf;
   if (tma) {
     FS_CUDA(c, cudaFuncSetAttribute(raycast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    raycast_kernel<true><<<grid, block, smem, c->stream>>>(c->tmap, P, d_fr, d_out, d_info_ray, d_win, d_rec);
+    raycast_kernel<true><<<grid, block, smem, c->stream>>>(P, d_fr, d_out, d_info_ray, d_win, d_rec);
   } else {
     FS_CUDA(c, cudaFuncSetAttribute(raycast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    raycast_kernel<false><<<grid, block, smem, c->stream>>>(c->tmap, P, d_fr, d_out, d_info_ray, d_win, d_rec);
+    raycast_kernel<false><<<grid, block, smem, c->stream>>>(P, d_fr, d_out, d_info_ray, d_win, d_rec);
   }
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
