@@ -49,6 +49,11 @@ struct DevBuf {
   }
 };
 
+struct FrontierState;
+struct FisherState;
+struct SelectState;
+struct CycleState;
+
 struct ScoreRecord {  // 16 bytes, the all-gather unit
   int32_t information;
   int32_t max_index;
@@ -95,9 +100,10 @@ struct fitslam_ctx {
   size_t pinned_cap = 0;
 
   // opaque per-stage state (defined in the stage's .cu file)
-  struct FrontierState *fs = nullptr;
-  struct FisherState *fi = nullptr;
-  struct SelectState *sel = nullptr;
+  fitslam::FrontierState *fs = nullptr;
+  fitslam::FisherState *fi = nullptr;
+  fitslam::SelectState *sel = nullptr;
+  fitslam::CycleState *cy = nullptr;
 };
 
 namespace fitslam {

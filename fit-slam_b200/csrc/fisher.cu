@@ -1,0 +1,807 @@
+// fisher.cu -- stage F: Fisher information of the ORB-SLAM3 map points for a batch of candidate poses.
+//
+// Replaces FisherInformationManager::{generateLookupTable, loadLookupTable, getVoxelCoordinate,
+// getInformationFromLookup, isPoseSafe} (DEP/src/fisher_information/FisherInfoManager.cpp:39-324,
+// DEP/include/frontier_exploration/fisher_information/FisherInfoManager.hpp:23-123), the Fisher helpers
+// computeJacobianForPointLocal / computeFIM / computeInformationOfPointLocal (DEP/src/Helpers.cpp:397-449) and the
+// server side of the landmark service: ORBSLAM3Interface::mapPointsVisibleFromPose
+// (ORBW/src/orb_slam3_interface.cpp:188-317, exhaustive search), RgbdSlamNode::getMapPointsInViewServer
+// (ORBW/src/rgbd/rgbd-slam-node.cpp:406-429), se3ROSToORB (ORBW/src/type_conversion.cpp:74-100) and
+// Pinhole::project (ORB/src/CameraModels/Pinhole.cpp:43-49).
+//
+// Layout.  The lookup table is a dense float grid indexed by the integer voxel index round(x / step) per axis
+// (NaN = no entry).  The map points are bucketed once per map update into a uniform xy bin grid (counting sort,
+// float4 records).  One CTA scores one pose: it culls the bins around the pose against the frustum and the lookup
+// domain (conservative plane tests), runs the reference's per-point float arithmetic on the surviving points,
+// counts the points per camera-frame voxel in a shared-memory hash table (the crowding rank of
+// getInformationFromLookup is order-free per voxel: information * S(count), S a host-tabulated prefix sum of
+// exp(1 - j^0.8)) and reduces the voxel terms with warp shuffles.  Float arithmetic follows Eigen's evaluation
+// order (x0*y0 + (x1*y1 + x2*y2)); this file is compiled with -fmad=false so it rounds like the host.
+#include "ctx.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+namespace fitslam {
+
+static constexpr int CROWD_MAX = 512;       // exp(1 - j^0.8) underflows to 0 in float long before j = 512
+static constexpr int HASH_SLOTS = 4096;     // per-CTA voxel hash table
+static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding square of the lookup domain)
+static constexpr int FISHER_THREADS = 128;
+
+struct M3f { float m[3][3]; };
+struct V3f { float v[3]; };
+
+__host__ __device__ __forceinline__ float dot3(float a0, float b0, float a1, float b1, float a2, float b2) {
+  return a0 * b0 + (a1 * b1 + a2 * b2);
+}
+__host__ __device__ inline V3f mulv(const M3f &A, const V3f &x) {
+  V3f r;
+  for (int i = 0; i < 3; ++i) r.v[i] = dot3(A.m[i][0], x.v[0], A.m[i][1], x.v[1], A.m[i][2], x.v[2]);
+  return r;
+}
+__host__ __device__ inline M3f mulm(const M3f &A, const M3f &B) {
+  M3f r;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) r.m[i][j] = dot3(A.m[i][0], B.m[0][j], A.m[i][1], B.m[1][j], A.m[i][2], B.m[2][j]);
+  return r;
+}
+__host__ __device__ inline M3f transp(const M3f &A) {
+  M3f r;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) r.m[i][j] = A.m[j][i];
+  return r;
+}
+// Eigen::Quaternionf::toRotationMatrix
+__host__ __device__ inline M3f quat_to_matrix(float w, float x, float y, float z) {
+  M3f r;
+  const float tx = 2.0f * x, ty = 2.0f * y, tz = 2.0f * z;
+  const float twx = tx * w, twy = ty * w, twz = tz * w;
+  const float txx = tx * x, txy = ty * x, txz = tz * x;
+  const float tyy = ty * y, tyz = tz * y, tzz = tz * z;
+  r.m[0][0] = 1.0f - (tyy + tzz); r.m[0][1] = txy - twz;          r.m[0][2] = txz + twy;
+  r.m[1][0] = txy + twz;          r.m[1][1] = 1.0f - (txx + tzz); r.m[1][2] = tyz - twx;
+  r.m[2][0] = txz - twy;          r.m[2][1] = tyz + twx;          r.m[2][2] = 1.0f - (txx + tyy);
+  return r;
+}
+__host__ __device__ inline float cofac(const M3f &m, int i, int j) {
+  const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+  return m.m[i1][j1] * m.m[i2][j2] - m.m[i1][j2] * m.m[i2][j1];
+}
+// Eigen compute_inverse<Matrix3f>: cofactors, determinant from column 0, scaled by 1/det
+__host__ __device__ inline M3f inverse3(const M3f &m) {
+  const float c0 = cofac(m, 0, 0), c1 = cofac(m, 1, 0), c2 = cofac(m, 2, 0);
+  const float det = dot3(c0, m.m[0][0], c1, m.m[1][0], c2, m.m[2][0]);
+  const float invdet = 1.0f / det;
+  M3f r;
+  r.m[0][0] = c0 * invdet; r.m[0][1] = c1 * invdet; r.m[0][2] = c2 * invdet;
+  r.m[1][0] = cofac(m, 0, 1) * invdet; r.m[1][1] = cofac(m, 1, 1) * invdet; r.m[1][2] = cofac(m, 2, 1) * invdet;
+  r.m[2][0] = cofac(m, 0, 2) * invdet; r.m[2][1] = cofac(m, 1, 2) * invdet; r.m[2][2] = cofac(m, 2, 2) * invdet;
+  return r;
+}
+
+// computeInformationOfPointLocal(p, Q = I) = trace(J^T Q^-1 J), J = df_dpc * [-I | skew(p)]  (DEP/src/Helpers.cpp:397-449)
+__host__ __device__ inline float information_of_point_local(const V3f &p) {
+  const float n = sqrtf(dot3(p.v[0], p.v[0], p.v[1], p.v[1], p.v[2], p.v[2]));
+  const float a = 1 / n;
+  const float s = 1 / (n * n * n);
+  M3f df;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) df.m[i][j] = a * (i == j ? 1.0f : 0.0f) - (s * p.v[i]) * p.v[j];
+  float right[3][6];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) right[i][j] = (float)((-1.0) * (i == j ? 1.0f : 0.0f));
+  right[0][3] = 0;        right[0][4] = -p.v[2]; right[0][5] = p.v[1];
+  right[1][3] = p.v[2];   right[1][4] = 0;       right[1][5] = -p.v[0];
+  right[2][3] = -p.v[1];  right[2][4] = p.v[0];  right[2][5] = 0;
+  float J[3][6];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 6; ++j) J[i][j] = dot3(df.m[i][0], right[0][j], df.m[i][1], right[1][j], df.m[i][2], right[2][j]);
+  M3f Q;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) Q.m[i][j] = i == j ? 1.0f : 0.0f;
+  const M3f Qi = inverse3(Q);
+  float d[6];
+  for (int i = 0; i < 6; ++i) {
+    float q[3];
+    for (int k = 0; k < 3; ++k) q[k] = dot3(J[0][i], Qi.m[0][k], J[1][i], Qi.m[1][k], J[2][i], Qi.m[2][k]);
+    d[i] = dot3(q[0], J[0][i], q[1], J[1][i], q[2], J[2][i]);
+  }
+  return (d[0] + (d[1] + d[2])) + (d[3] + (d[4] + d[5]));
+}
+
+struct FisherState {
+  // lookup table: lut[((ix - org0) * dims1 + (iy - org1)) * dims2 + (iz - org2)], NaN = absent
+  DevBuf<float> lut;
+  int32_t dims[3] = {0, 0, 0}, org[3] = {0, 0, 0};
+  bool have_lut = false;
+  std::vector<int> axis[3];     // voxel indices per axis in generation order (file order of the .dat records)
+  DevBuf<int32_t> d_axis;
+  DevBuf<double> crowd;         // S[k] = sum_{j<=k} (float)exp(1 - pow(j, s)), k = 0..CROWD_MAX
+  // map points, bucketed
+  DevBuf<float4> pts;           // sorted by bin
+  DevBuf<float> raw;            // staging copy of the caller's xyz
+  DevBuf<uint32_t> bin_start;   // nbx*nby + 1
+  DevBuf<uint32_t> bin_cursor;
+  DevBuf<float> bbox;           // device reduction scratch: 6 ordered-int floats
+  uint64_t n_points = 0;
+  bool have_points = false;
+  float bx0 = 0, by0 = 0, bin_size = 3.0f, zmin = 0, zmax = 0;
+  int nbx = 0, nby = 0;
+  // per-call buffers
+  DevBuf<fitslam_pose> poses;
+  DevBuf<float> info;
+  DevBuf<uint8_t> safe;
+  DevBuf<uint32_t> nvis;
+};
+
+static FisherState *fstate(fitslam_ctx *c) {
+  if (!c->fi) c->fi = new FisherState();
+  return c->fi;
+}
+
+void destroy_fisher_state(fitslam_ctx *c) {
+  if (!c->fi) return;
+  FisherState *f = c->fi;
+  f->lut.release(); f->d_axis.release(); f->crowd.release(); f->pts.release(); f->raw.release();
+  f->bin_start.release(); f->bin_cursor.release(); f->bbox.release(); f->poses.release(); f->info.release();
+  f->safe.release(); f->nvis.release();
+  delete f;
+  c->fi = nullptr;
+}
+
+// ------------------------------------------------------------------------------------------------ lookup table
+// One thread per (ix, iy, iz) of the axis lists.  key = (float)(index * (double)step) is what getVoxelCoordinate
+// returns for every landmark that rounds to this index (FisherInfoManager.hpp:108-123).
+__global__ void lut_fill_kernel(const int32_t *__restrict__ ax, int n0, int n1, int n2, int o0, int o1, int o2, int d1, int d2,
+                                double step, float *__restrict__ lut) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long)n0 * n1 * n2) return;
+  const int a = (int)(i / ((long)n1 * n2)), b = (int)((i / n2) % n1), cc = (int)(i % n2);
+  const int ix = ax[a], iy = ax[n0 + b], iz = ax[n0 + n1 + cc];
+  V3f p;
+  p.v[0] = (float)((double)ix * step);
+  p.v[1] = (float)((double)iy * step);
+  p.v[2] = (float)((double)iz * step);
+  lut[((long)(ix - o0) * d1 + (iy - o1)) * d2 + (iz - o2)] = information_of_point_local(p);
+}
+__global__ void fill_nan_kernel(float *p, long n) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = __int_as_float(0x7fc00000);
+}
+// key (0,0,0) := max over the table (FisherInfoManager.cpp:190-197); one block
+__global__ void lut_max_kernel(float *lut, long n, long zero_index) {
+  __shared__ float sh[32];
+  float m = -3.402823466e+38f;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = lut[i];
+    if (v == v) m = fmaxf(m, v);
+  }
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (unsigned w = 1; w < blockDim.x / 32; ++w) m = fmaxf(m, sh[w]);
+    if (zero_index >= 0) lut[zero_index] = m;
+  }
+}
+
+// Voxel indices visited by one axis of the generateLookupTable loop nest (FisherInfoManager.cpp:130-150): float bounds
+// snapped with floor/ceil, a float counter advanced by step_max (the step_min branch is dead: subSampleVoxelUntil_m =
+// -1, so increment_value becomes step_max before the first inner iteration), index = round(counter * (1 / (double)step)).
+static void axis_indices(float lo, float hi, float step_max, std::vector<int> &out) {
+  out.clear();
+  lo = std::floor(lo * (1 / step_max)) * step_max;
+  hi = std::ceil(hi * (1 / step_max)) * step_max;
+  const double corrected_step = step_max;
+  for (float counter = lo; counter <= hi; counter += step_max) {
+    const int idx = (int)std::round(counter * (1 / corrected_step));
+    if (std::find(out.begin(), out.end(), idx) == out.end()) out.push_back(idx);
+    if (out.size() > 4096) break;
+  }
+}
+
+static fitslam_status upload_crowd_table(fitslam_ctx *c) {
+  FisherState *f = fstate(c);
+  std::vector<double> S(CROWD_MAX + 1, 0.0);
+  for (int j = 1; j <= CROWD_MAX; ++j) {
+    // getFactorFromNum (FisherInfoManager.hpp:102-106): float = std::exp(1 - std::pow(int, float))
+    const float factor = (float)std::exp(1 - std::pow((double)j, (double)c->prm.crowd_exponent));
+    S[j] = S[j - 1] + (double)factor;
+  }
+  FS_CUDA(c, f->crowd.reserve(S.size()));
+  FS_CUDA(c, cudaMemcpyAsync(f->crowd.p, S.data(), S.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}
+
+static fitslam_status alloc_lut(fitslam_ctx *c, const int lo[3], const int hi[3]) {
+  FisherState *f = fstate(c);
+  long n = 1;
+  for (int a = 0; a < 3; ++a) {
+    f->org[a] = std::min(lo[a], 0);  // key (0,0,0) is always an entry
+    f->dims[a] = std::max(hi[a], 0) - f->org[a] + 1;
+    n *= f->dims[a];
+  }
+  if (n <= 0 || n > (1l << 28)) return fail(c, FITSLAM_E_INVALID, "lookup table too large");
+  FS_CUDA(c, f->lut.reserve((size_t)n));
+  fill_nan_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(f->lut.p, n);
+  ++c->launches;
+  return FITSLAM_OK;
+}
+
+static long lut_size(const FisherState *f) { return (long)f->dims[0] * f->dims[1] * f->dims[2]; }
+
+}  // namespace fitslam
+
+using namespace fitslam;
+
+extern "C" {
+
+fitslam_status fitslam_fisher_generate_lookup(fitslam_ctx *c, const char *save_path) {
+  if (!c) return FITSLAM_E_INVALID;
+  cudaSetDevice(c->device);
+  FisherState *f = fstate(c);
+  const fitslam_params &p = c->prm;
+  if (!(p.voxel_step > 0.0f)) return fail(c, FITSLAM_E_INVALID, "voxel_step must be positive");
+  axis_indices(p.lut_min_x, p.lut_max_x, p.voxel_step, f->axis[0]);
+  axis_indices(p.lut_min_y, p.lut_max_y, p.voxel_step, f->axis[1]);
+  axis_indices(p.lut_min_z, p.lut_max_z, p.voxel_step, f->axis[2]);
+  int lo[3], hi[3];
+  std::vector<int32_t> flat;
+  for (int a = 0; a < 3; ++a) {
+    if (f->axis[a].empty()) return fail(c, FITSLAM_E_INVALID, "empty lookup-table axis");
+    lo[a] = *std::min_element(f->axis[a].begin(), f->axis[a].end());
+    hi[a] = *std::max_element(f->axis[a].begin(), f->axis[a].end());
+    flat.insert(flat.end(), f->axis[a].begin(), f->axis[a].end());
+  }
+  fitslam_status st = alloc_lut(c, lo, hi);
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, f->d_axis.reserve(flat.size()));
+  FS_CUDA(c, cudaMemcpyAsync(f->d_axis.p, flat.data(), flat.size() * 4, cudaMemcpyHostToDevice, c->stream));
+  const int n0 = (int)f->axis[0].size(), n1 = (int)f->axis[1].size(), n2 = (int)f->axis[2].size();
+  const long n = (long)n0 * n1 * n2;
+  lut_fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(f->d_axis.p, n0, n1, n2, f->org[0], f->org[1], f->org[2],
+                                                                     f->dims[1], f->dims[2], (double)p.voxel_step, f->lut.p);
+  const long zero = ((long)(0 - f->org[0]) * f->dims[1] + (0 - f->org[1])) * f->dims[2] + (0 - f->org[2]);
+  lut_max_kernel<<<1, 1024, 0, c->stream>>>(f->lut.p, lut_size(f), zero);
+  c->launches += 2;
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  f->have_lut = true;
+  st = upload_crowd_table(c);
+  if (st != FITSLAM_OK) return st;
+  if (save_path) {
+    // .dat layout (FisherInfoManager.cpp:185-186): {float key[3], float value} per entry, loop order, (0,0,0) last
+    std::vector<float> host((size_t)lut_size(f));
+    FS_CUDA(c, cudaMemcpy(host.data(), f->lut.p, host.size() * 4, cudaMemcpyDeviceToHost));
+    FILE *fp = fopen(save_path, "wb");
+    if (!fp) return fail(c, FITSLAM_E_IO, std::string("cannot open ") + save_path);
+    const double step = (double)p.voxel_step;
+    auto at = [&](int ix, int iy, int iz) {
+      return host[((size_t)(ix - f->org[0]) * f->dims[1] + (iy - f->org[1])) * f->dims[2] + (iz - f->org[2])];
+    };
+    for (int ix : f->axis[0])
+      for (int iy : f->axis[1])
+        for (int iz : f->axis[2]) {
+          if (ix == 0 && iy == 0 && iz == 0) continue;  // NaN at generation time: skipped, appended below
+          const float v = at(ix, iy, iz);
+          if (v != v) continue;
+          const float rec[4] = {(float)(ix * step), (float)(iy * step), (float)(iz * step), v};
+          fwrite(rec, sizeof(float), 4, fp);
+        }
+    const float last[4] = {0.0f, 0.0f, 0.0f, at(0, 0, 0)};
+    fwrite(last, sizeof(float), 4, fp);
+    fclose(fp);
+  }
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_fisher_load_lookup(fitslam_ctx *c, const char *path) {
+  if (!c || !path) return fail(c, FITSLAM_E_INVALID, "load_lookup: null argument");
+  cudaSetDevice(c->device);
+  FisherState *f = fstate(c);
+  FILE *fp = fopen(path, "rb");
+  if (!fp) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
+  std::vector<float> rec;
+  float r[4];
+  while (fread(r, sizeof(float), 4, fp) == 4) rec.insert(rec.end(), r, r + 4);
+  fclose(fp);
+  const size_t n = rec.size() / 4;
+  if (n == 0) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
+  const double inv = 1 / (double)c->prm.voxel_step;
+  int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+  std::vector<int> idx(3 * n);
+  for (size_t i = 0; i < n; ++i)
+    for (int a = 0; a < 3; ++a) {
+      const int v = (int)std::round((double)rec[4 * i + a] * inv);  // the key IS index * step: the same index comes back
+      idx[3 * i + a] = v;
+      lo[a] = std::min(lo[a], v);
+      hi[a] = std::max(hi[a], v);
+    }
+  fitslam_status st = alloc_lut(c, lo, hi);
+  if (st != FITSLAM_OK) return st;
+  std::vector<float> host((size_t)lut_size(f), std::numeric_limits<float>::quiet_NaN());
+  for (size_t i = 0; i < n; ++i)  // later records overwrite earlier ones, like unordered_map::operator[]
+    host[((size_t)(idx[3 * i] - f->org[0]) * f->dims[1] + (idx[3 * i + 1] - f->org[1])) * f->dims[2] + (idx[3 * i + 2] - f->org[2])] = rec[4 * i + 3];
+  FS_CUDA(c, cudaMemcpyAsync(f->lut.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (int a = 0; a < 3; ++a) f->axis[a].clear();
+  f->have_lut = true;
+  return upload_crowd_table(c);
+}
+
+fitslam_status fitslam_fisher_lookup_dims(const fitslam_ctx *c, int32_t dims[3], int32_t origin[3]) {
+  if (!c || !c->fi || !c->fi->have_lut) return FITSLAM_E_NO_LOOKUP_TABLE;
+  for (int a = 0; a < 3; ++a) {
+    if (dims) dims[a] = c->fi->dims[a];
+    if (origin) origin[a] = c->fi->org[a];
+  }
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_fisher_lookup_copy(fitslam_ctx *c, float *out, uint64_t capacity) {
+  if (!c || !out) return fail(c, FITSLAM_E_INVALID, "lookup_copy: null argument");
+  if (!c->fi || !c->fi->have_lut) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
+  const uint64_t n = (uint64_t)lut_size(c->fi);
+  if (capacity < n) return fail(c, FITSLAM_E_CAPACITY, "lookup_copy: buffer too small");
+  cudaSetDevice(c->device);
+  FS_CUDA(c, cudaMemcpyAsync(out, c->fi->lut.p, n * 4, cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}
+
+}  // extern "C"
+
+// ================================================================================================ map points
+namespace fitslam {
+
+__device__ __forceinline__ uint32_t f2ord(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+static inline float ord2f(uint32_t o) {
+  const uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+__device__ __forceinline__ bool finite3(float x, float y, float z) { return isfinite(x) && isfinite(y) && isfinite(z); }
+
+// ord[0..2] = min xyz, ord[3..5] = max xyz over the finite points
+__global__ void points_bbox_kernel(const float *__restrict__ xyz, uint64_t n, uint32_t *ord) {
+  uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0, 0, 0};
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    if (!finite3(x, y, z)) continue;
+    const uint32_t o[3] = {f2ord(x), f2ord(y), f2ord(z)};
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = min(lo[a], o[a]);
+      hi[a] = max(hi[a], o[a]);
+    }
+  }
+  for (int a = 0; a < 3; ++a) {
+    for (int s = 16; s > 0; s >>= 1) {
+      lo[a] = min(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], s));
+      hi[a] = max(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], s));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(&ord[a], lo[a]);
+      atomicMax(&ord[3 + a], hi[a]);
+    }
+  }
+}
+
+struct BinGrid {
+  float x0, y0, inv, size;
+  int nbx, nby;
+};
+__device__ __forceinline__ int bin_of(const BinGrid &g, float x, float y) {
+  int bx = (int)floorf((x - g.x0) * g.inv), by = (int)floorf((y - g.y0) * g.inv);
+  bx = max(0, min(g.nbx - 1, bx));
+  by = max(0, min(g.nby - 1, by));
+  return by * g.nbx + bx;
+}
+__global__ void points_count_kernel(const float *__restrict__ xyz, uint64_t n, BinGrid g, uint32_t *count) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    if (finite3(x, y, z)) atomicAdd(&count[bin_of(g, x, y)], 1u);
+  }
+}
+// exclusive scan of count[0..n) in place, count[n] = total; start[] = cursor[] copies.  One block.
+__global__ void bins_scan_kernel(uint32_t *count, uint32_t *cursor, uint32_t n) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < n; base += blockDim.x) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < n ? count[i] : 0;
+    uint32_t incl = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+      uint32_t w = lane < blockDim.x / 32 ? wsum[lane] : 0, wi = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+        if ((int)lane >= o) wi += t;
+      }
+      wsum[lane] = wi - w;
+    }
+    __syncthreads();
+    const uint32_t excl = carry + wsum[wid] + incl - v;
+    if (i < n) {
+      count[i] = excl;
+      cursor[i] = excl;
+    }
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry = excl + v;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) count[n] = carry;
+}
+__global__ void points_scatter_kernel(const float *__restrict__ xyz, uint64_t n, BinGrid g, uint32_t *cursor, float4 *out) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    if (!finite3(x, y, z)) continue;
+    const uint32_t pos = atomicAdd(&cursor[bin_of(g, x, y)], 1u);
+    out[pos] = make_float4(x, y, z, __uint_as_float((uint32_t)i));
+  }
+}
+
+// radius (map frame, metres) that contains the whole lookup domain seen from the pose origin, any orientation
+static double lut_reach(const fitslam_ctx *c) {
+  const FisherState *f = c->fi;
+  const double step = (double)c->prm.voxel_step;
+  double r2 = 0;
+  for (int a = 0; a < 3; ++a) {
+    const double lo = (f->org[a] - 0.5) * step, hi = (f->org[a] + f->dims[a] - 0.5) * step;
+    const double m = std::max(std::fabs(lo), std::fabs(hi));
+    r2 += m * m;
+  }
+  return std::sqrt(r2) + 0.1;
+}
+
+}  // namespace fitslam
+
+extern "C" fitslam_status fitslam_set_map_points(fitslam_ctx *c, const float *xyz, uint64_t n) {
+  if (!c || (!xyz && n)) return fail(c, FITSLAM_E_INVALID, "set_map_points: null argument");
+  if (n >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "set_map_points: more than 2^31 points");
+  cudaSetDevice(c->device);
+  FisherState *f = fstate(c);
+  f->have_points = false;
+  f->n_points = n;
+  FS_CUDA(c, f->raw.reserve(3 * n + 3));
+  FS_CUDA(c, f->pts.reserve(n + 1));
+  FS_CUDA(c, f->bbox.reserve(8));
+  if (n) FS_CUDA(c, cudaMemcpyAsync(f->raw.p, xyz, 3 * n * sizeof(float), cudaMemcpyDefault, c->stream));
+  const uint32_t init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0, 0, 0};
+  FS_CUDA(c, cudaMemcpyAsync(f->bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
+  const unsigned grid = (unsigned)std::min<uint64_t>(148 * 8, (n + 255) / 256 + 1);
+  points_bbox_kernel<<<grid, 256, 0, c->stream>>>(f->raw.p, n, reinterpret_cast<uint32_t *>(f->bbox.p));
+  ++c->launches;
+  uint32_t ord[6];
+  FS_CUDA(c, cudaMemcpyAsync(ord, f->bbox.p, sizeof(ord), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+  if (ord[0] <= ord[3])
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = ord2f(ord[a]);
+      hi[a] = ord2f(ord[3 + a]);
+    }
+  // bin size: >= 3 m, and large enough that (a) the grid has at most 2^20 bins, (b) a pose touches <= 30 x 30 bins
+  double bs = 3.0;
+  const double ex = (double)hi[0] - lo[0], ey = (double)hi[1] - lo[1];
+  while ((std::floor(ex / bs) + 1) * (std::floor(ey / bs) + 1) > (double)(1 << 20)) bs *= 2;
+  f->bin_size = (float)bs;
+  f->bx0 = lo[0];
+  f->by0 = lo[1];
+  f->zmin = lo[2];
+  f->zmax = hi[2];
+  f->nbx = (int)std::floor(ex / bs) + 1;
+  f->nby = (int)std::floor(ey / bs) + 1;
+  const uint32_t nb = (uint32_t)f->nbx * f->nby;
+  FS_CUDA(c, f->bin_start.reserve(nb + 1));
+  FS_CUDA(c, f->bin_cursor.reserve(nb + 1));
+  FS_CUDA(c, cudaMemsetAsync(f->bin_start.p, 0, (nb + 1) * 4, c->stream));
+  BinGrid g{f->bx0, f->by0, (float)(1.0 / bs), f->bin_size, f->nbx, f->nby};
+  points_count_kernel<<<grid, 256, 0, c->stream>>>(f->raw.p, n, g, f->bin_start.p);
+  bins_scan_kernel<<<1, 1024, 0, c->stream>>>(f->bin_start.p, f->bin_cursor.p, nb);
+  points_scatter_kernel<<<grid, 256, 0, c->stream>>>(f->raw.p, n, g, f->bin_cursor.p, f->pts.p);
+  c->launches += 3;
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  f->have_points = true;
+  return FITSLAM_OK;
+}
+
+// ================================================================================================ scoring
+namespace fitslam {
+
+struct FisherParams {
+  const float4 *pts;
+  const uint32_t *bin_start;
+  BinGrid grid;
+  float zmin, zmax;
+  const float *lut;
+  int dims[3], org[3];
+  const double *crowd;
+  double inv_step;      // 1 / (double)step_max, the factor getVoxelCoordinate multiplies by
+  double step;
+  double reach;         // lut_reach()
+  double threshold;
+  float fx, fy, cx, cy, max_u, max_v;
+  uint32_t n_poses;
+  int rank, nranks;
+};
+
+struct PoseFrame {      // per-CTA, built by thread 0
+  M3f Rcw;  V3f tcw;    // se3ROSToORB(poseToAffine(pose))
+  M3f Rinv; V3f tinv;   // inverse(poseToAffine(pose)): map -> pose frame
+  double plane[11][4];  // n.p + d >= -margin inside (map frame, unit normals): 5 frustum + 6 lookup-domain planes
+  float px, py;
+};
+
+__device__ void build_pose_frame(const fitslam_pose &pose, const FisherParams &P, PoseFrame &F) {
+  // poseToAffine (ORBW/src/type_conversion.cpp:141-153): doubles narrowed to float
+  V3f t;
+  t.v[0] = (float)pose.x; t.v[1] = (float)pose.y; t.v[2] = (float)pose.z;
+  const M3f R = quat_to_matrix((float)pose.qw, (float)pose.qx, (float)pose.qy, (float)pose.qz);
+  M3f ros2orb, orb2ros;
+  const float a[9] = {0, -1, 0, 0, 0, -1, 1, 0, 0}, b[9] = {0, 0, 1, -1, 0, 0, 0, -1, 0};
+  for (int i = 0; i < 9; ++i) { ros2orb.m[i / 3][i % 3] = a[i]; orb2ros.m[i / 3][i % 3] = b[i]; }
+  // se3ROSToORB (type_conversion.cpp:74-100)
+  const M3f Rtemp = mulm(ros2orb, R);
+  const V3f ttemp = mulv(ros2orb, t);
+  const M3f Rti = transp(Rtemp);
+  const V3f ti = mulv(Rti, ttemp);
+  V3f tneg; tneg.v[0] = -ti.v[0]; tneg.v[1] = -ti.v[1]; tneg.v[2] = -ti.v[2];
+  F.Rcw = mulm(ros2orb, Rti);
+  F.tcw = mulv(ros2orb, tneg);
+  // Eigen Affine3f::inverse(): linear().inverse(), translation = -linear_inv * t
+  F.Rinv = inverse3(R);
+  M3f neg;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) neg.m[i][j] = -F.Rinv.m[i][j];
+  F.tinv = mulv(neg, t);
+  F.px = t.v[0]; F.py = t.v[1];
+  // ---- conservative culling planes (double; only used to skip whole bins)
+  // camera coords = Rcw * Perm * p + tcw with Perm = ros2orb: column j of M = Rcw * Perm
+  double M[3][3];
+  for (int i = 0; i < 3; ++i) {
+    M[i][0] = F.Rcw.m[i][2]; M[i][1] = -(double)F.Rcw.m[i][0]; M[i][2] = -(double)F.Rcw.m[i][1];
+  }
+  const double cam[5][3] = {{0, 0, 1}, {P.fx, 0, P.cx}, {-(double)P.fx, 0, (double)P.max_u - P.cx},
+                            {0, P.fy, P.cy}, {0, -(double)P.fy, (double)P.max_v - P.cy}};
+  for (int k = 0; k < 5; ++k) {
+    const double nn = sqrt(cam[k][0] * cam[k][0] + cam[k][1] * cam[k][1] + cam[k][2] * cam[k][2]);
+    double d = 0;
+    for (int j = 0; j < 3; ++j) {
+      F.plane[k][j] = (cam[k][0] * M[0][j] + cam[k][1] * M[1][j] + cam[k][2] * M[2][j]) / nn;
+      d += cam[k][j] * (double)F.tcw.v[j];
+    }
+    F.plane[k][3] = d / nn;
+  }
+  for (int ax = 0; ax < 3; ++ax) {
+    const double lo = (P.org[ax] - 0.5) * P.step, hi = (P.org[ax] + P.dims[ax] - 0.5) * P.step;
+    for (int j = 0; j < 3; ++j) {
+      F.plane[5 + 2 * ax][j] = F.Rinv.m[ax][j];
+      F.plane[6 + 2 * ax][j] = -(double)F.Rinv.m[ax][j];
+    }
+    F.plane[5 + 2 * ax][3] = (double)F.tinv.v[ax] - lo;
+    F.plane[6 + 2 * ax][3] = hi - (double)F.tinv.v[ax];
+  }
+}
+
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+
+// voxel of one map point as seen from the pose: -1 if culled, outside the table or a NaN entry
+__device__ __forceinline__ int voxel_of_point(const float4 q, const PoseFrame &F, const FisherParams &P) {
+  V3f Pw; Pw.v[0] = -q.y; Pw.v[1] = -q.z; Pw.v[2] = q.x;  // ROS map axes -> ORB world axes
+  const V3f RP = mulv(F.Rcw, Pw);
+  const float Xc = RP.v[0] + F.tcw.v[0], Yc = RP.v[1] + F.tcw.v[1], Zc = RP.v[2] + F.tcw.v[2];
+  if (Zc < 0.0f) return -1;                       // orb_slam3_interface.cpp:286-289
+  const float u = P.fx * Xc / Zc + P.cx;          // Pinhole.cpp:43-49
+  const float v = P.fy * Yc / Zc + P.cy;
+  if (u < 0.0f || u > P.max_u) return -1;         // :295-300
+  if (v < 0.0f || v > P.max_v) return -1;
+  // rgbd-slam-node.cpp:419-425: vector3fORBToROS, then inverse(pose) * position
+  V3f pos; pos.v[0] = dot3(0.f, Pw.v[0], 0.f, Pw.v[1], 1.f, Pw.v[2]);
+  pos.v[1] = dot3(-1.f, Pw.v[0], 0.f, Pw.v[1], 0.f, Pw.v[2]);
+  pos.v[2] = dot3(0.f, Pw.v[0], -1.f, Pw.v[1], 0.f, Pw.v[2]);
+  const V3f lp = mulv(F.Rinv, pos);
+  int idx[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const float c = lp.v[a] + F.tinv.v[a];
+    const double r = round((double)c * P.inv_step);  // getVoxelCoordinate (FisherInfoManager.hpp:108-123)
+    if (!(r >= (double)P.org[a] && r < (double)(P.org[a] + P.dims[a]))) return -1;  // also rejects NaN
+    idx[a] = (int)r - P.org[a];
+  }
+  const int lin = (idx[0] * P.dims[1] + idx[1]) * P.dims[2] + idx[2];
+  const float val = __ldg(P.lut + lin);
+  return (val == val) ? lin : -1;
+}
+
+__global__ void __launch_bounds__(FISHER_THREADS)
+fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, float *__restrict__ info_out,
+              uint8_t *__restrict__ safe_out, uint32_t *__restrict__ nvis_out, ScoreRecord *__restrict__ rec_out,
+              uint32_t rec_stride) {
+  __shared__ PoseFrame F;
+  __shared__ uint32_t keys[HASH_SLOTS];
+  __shared__ uint32_t cnts[HASH_SLOTS];
+  __shared__ uint32_t s_used, s_overflow;
+  __shared__ double s_red[FISHER_THREADS / 32];
+  const uint64_t pi64 = (uint64_t)P.rank + (uint64_t)blockIdx.x * (uint64_t)P.nranks;
+  if (pi64 >= P.n_poses) return;
+  const uint32_t pi = (uint32_t)pi64;
+  if (threadIdx.x == 0) build_pose_frame(poses[pi], P, F);
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5, nw = FISHER_THREADS / 32;
+  // bins of the bounding square of the lookup domain around the pose
+  const BinGrid g = P.grid;
+  const int bx_lo = max(0, (int)floor(((double)F.px - P.reach - g.x0) * g.inv)), bx_hi = min(g.nbx - 1, (int)floor(((double)F.px + P.reach - g.x0) * g.inv));
+  const int by_lo = max(0, (int)floor(((double)F.py - P.reach - g.y0) * g.inv)), by_hi = min(g.nby - 1, (int)floor(((double)F.py + P.reach - g.y0) * g.inv));
+  const int sq_w = bx_hi - bx_lo + 1, sq_h = by_hi - by_lo + 1;
+  const int n_sq = (sq_w > 0 && sq_h > 0) ? sq_w * sq_h : 0;
+  const double margin = 0.05 + 1e-4 * (fabs((double)F.px) + fabs((double)F.py));
+
+  double total = 0.0;
+  uint32_t used = 0;
+  for (uint32_t npass = 1; npass <= 4096; npass <<= 1) {
+    total = 0.0;
+    if (threadIdx.x == 0) { s_used = 0; s_overflow = 0; }
+    for (uint32_t pass = 0; pass < npass; ++pass) {
+      for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) { keys[i] = 0; cnts[i] = 0; }
+      __syncthreads();
+      uint32_t my_used = 0;
+      for (int b0 = (int)wid * 32; b0 < n_sq; b0 += (int)nw * 32) {
+        const int b = b0 + (int)lane;
+        bool keep = false;
+        uint32_t start = 0, end = 0;
+        if (b < n_sq) {
+          const int bx = bx_lo + b % sq_w, by = by_lo + b / sq_w;
+          const uint32_t bi = (uint32_t)by * g.nbx + bx;
+          start = __ldg(P.bin_start + bi);
+          end = __ldg(P.bin_start + bi + 1);
+          if (end > start) {
+            // clamped edge bins also hold points outside their nominal square: open the box on that side
+            const double x0 = bx == 0 ? -1e30 : (double)g.x0 + bx * (double)g.size, x1 = bx == g.nbx - 1 ? 1e30 : (double)g.x0 + (bx + 1) * (double)g.size;
+            const double y0 = by == 0 ? -1e30 : (double)g.y0 + by * (double)g.size, y1 = by == g.nby - 1 ? 1e30 : (double)g.y0 + (by + 1) * (double)g.size;
+            keep = true;
+#pragma unroll 1
+            for (int k = 0; k < 11 && keep; ++k) {
+              const double nx = F.plane[k][0], ny = F.plane[k][1], nz = F.plane[k][2];
+              const double mx = fmax(nx * x0, nx * x1) + fmax(ny * y0, ny * y1) + fmax(nz * (double)P.zmin, nz * (double)P.zmax) + F.plane[k][3];
+              if (mx < -margin) keep = false;
+            }
+          }
+        }
+        uint32_t live = __ballot_sync(0xffffffffu, keep);
+        while (live) {
+          const int src = __ffs(live) - 1;
+          live &= live - 1;
+          const uint32_t s = __shfl_sync(0xffffffffu, start, src), e = __shfl_sync(0xffffffffu, end, src);
+          for (uint32_t i = s + lane; i < e; i += 32) {
+            const int vox = voxel_of_point(__ldg(P.pts + i), F, P);
+            if (vox < 0) continue;
+            const uint32_t h = mix32((uint32_t)vox);
+            if (npass > 1 && ((h >> 12) & (npass - 1)) != pass) continue;
+            ++my_used;
+            uint32_t slot = h & (HASH_SLOTS - 1);
+            bool done = false;
+            for (int probe = 0; probe < HASH_SLOTS; ++probe) {
+              const uint32_t prev = atomicCAS(&keys[slot], 0u, (uint32_t)vox + 1u);
+              if (prev == 0u || prev == (uint32_t)vox + 1u) { atomicAdd(&cnts[slot], 1u); done = true; break; }
+              slot = (slot + 1) & (HASH_SLOTS - 1);
+            }
+            if (!done) s_overflow = 1;
+          }
+        }
+      }
+      if (my_used) atomicAdd(&s_used, my_used);
+      __syncthreads();
+      if (s_overflow) break;
+      for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) {
+        const uint32_t k = keys[i];
+        if (k) total += (double)__ldg(P.lut + (k - 1)) * __ldg(P.crowd + min(cnts[i], (uint32_t)CROWD_MAX));
+      }
+      __syncthreads();
+    }
+    used = s_used;
+    const bool ovf = s_overflow != 0;
+    __syncthreads();
+    if (!ovf) break;
+  }
+  for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+  if (lane == 0) s_red[wid] = total;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (uint32_t w = 0; w < nw; ++w) t += s_red[w];
+    const float information = (float)t;
+    const bool is_safe = (double)information > P.threshold;  // FisherInfoManager.cpp:112-114
+    if (info_out) info_out[pi] = information;
+    if (safe_out) safe_out[pi] = is_safe ? 1 : 0;
+    if (nvis_out) nvis_out[pi] = used;
+    if (rec_out) {
+      ScoreRecord *r = rec_out + (size_t)pi * rec_stride;
+      r->fisher = information;
+      r->flags |= 8u | (is_safe ? 16u : 0u);
+    }
+  }
+}
+
+fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, float *d_info, uint8_t *d_safe,
+                                   uint32_t *d_nvis, ScoreRecord *d_rec, uint32_t rec_stride, bool shard) {
+  FisherState *f = c->fi;
+  if (!f || !f->have_lut) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
+  if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no map points set");
+  if (n == 0) return FITSLAM_OK;
+  FisherParams P;
+  memset(&P, 0, sizeof(P));
+  P.pts = f->pts.p;
+  P.bin_start = f->bin_start.p;
+  P.grid = BinGrid{f->bx0, f->by0, 1.0f / f->bin_size, f->bin_size, f->nbx, f->nby};
+  P.zmin = f->zmin;
+  P.zmax = f->zmax;
+  P.lut = f->lut.p;
+  for (int a = 0; a < 3; ++a) { P.dims[a] = f->dims[a]; P.org[a] = f->org[a]; }
+  P.crowd = f->crowd.p;
+  P.step = (double)c->prm.voxel_step;
+  P.inv_step = 1 / P.step;
+  P.reach = lut_reach(c);
+  P.threshold = c->prm.fisher_information_threshold;
+  P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
+  P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
+  P.n_poses = n;
+  P.rank = shard ? c->rank : 0;
+  P.nranks = shard ? c->nranks : 1;
+  const uint32_t n_local = (n > (uint32_t)P.rank) ? (n - P.rank + P.nranks - 1) / P.nranks : 0;
+  if (n_local == 0) return FITSLAM_OK;
+  fisher_kernel<<<n_local, FISHER_THREADS, 0, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, rec_stride);
+  ++c->launches;
+  FS_CUDA(c, cudaGetLastError());
+  return FITSLAM_OK;
+}
+
+}  // namespace fitslam
+
+extern "C" fitslam_status fitslam_score_fisher(fitslam_ctx *c, const fitslam_pose *poses, uint32_t n, float *information,
+                                               uint8_t *safe, uint32_t *n_visible) {
+  if (!c || (!poses && n)) return fail(c, FITSLAM_E_INVALID, "score_fisher: null argument");
+  cudaSetDevice(c->device);
+  FisherState *f = fstate(c);
+  if (!f->have_lut) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
+  if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no map points set");
+  if (n == 0) return FITSLAM_OK;
+  FS_CUDA(c, f->poses.reserve(n));
+  FS_CUDA(c, f->info.reserve(n));
+  FS_CUDA(c, f->safe.reserve(n));
+  FS_CUDA(c, f->nvis.reserve(n));
+  FS_CUDA(c, cudaMemcpyAsync(f->poses.p, poses, (size_t)n * sizeof(fitslam_pose), cudaMemcpyDefault, c->stream));
+  if (c->nranks > 1) {
+    FS_CUDA(c, cudaMemsetAsync(f->info.p, 0, (size_t)n * 4, c->stream));
+    FS_CUDA(c, cudaMemsetAsync(f->safe.p, 0, n, c->stream));
+    FS_CUDA(c, cudaMemsetAsync(f->nvis.p, 0, (size_t)n * 4, c->stream));
+  }
+  fitslam_status st = fisher_score_device(c, f->poses.p, n, f->info.p, f->safe.p, f->nvis.p, nullptr, 0, true);
+  if (st != FITSLAM_OK) return st;
+  if (information) FS_CUDA(c, cudaMemcpyAsync(information, f->info.p, (size_t)n * 4, cudaMemcpyDefault, c->stream));
+  if (safe) FS_CUDA(c, cudaMemcpyAsync(safe, f->safe.p, n, cudaMemcpyDefault, c->stream));
+  if (n_visible) FS_CUDA(c, cudaMemcpyAsync(n_visible, f->nvis.p, (size_t)n * 4, cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}

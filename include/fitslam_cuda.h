@@ -212,7 +212,9 @@ FITSLAM_API fitslam_status fitslam_fisher_lookup_dims(const fitslam_ctx *ctx, in
 FITSLAM_API fitslam_status fitslam_fisher_lookup_copy(fitslam_ctx *ctx, float *out, uint64_t capacity);
 /* FisherInformationManager::isPoseSafe for a batch of poses (FisherInfoManager.cpp:39-115) with the
  * landmark service replaced by the resident map points culled as ORBW/src/orb_slam3_interface.cpp:188-317
- * (exhaustive search) and transformed as ORBW/src/rgbd/rgbd-slam-node.cpp:414-429. */
+ * (exhaustive search) and transformed as ORBW/src/rgbd/rgbd-slam-node.cpp:414-429.
+ * n_visible[i] = landmarks in view of pose i that hit a lookup-table entry (the ones that contribute; the
+ * reference has no far plane, landmarks beyond the table domain return NaN and are skipped, :90-94). */
 FITSLAM_API fitslam_status fitslam_score_fisher(fitslam_ctx *ctx, const fitslam_pose *poses, uint32_t n_poses,
                                                 float *information, uint8_t *safe, uint32_t *n_visible);
 

@@ -177,10 +177,13 @@ class Oracle:
         info = np.zeros(n, dtype=np.float32)
         safe = np.zeros(n, dtype=np.uint8)
         nvis = np.zeros(n, dtype=np.uint32)
+        nused = np.zeros(n, dtype=np.uint32)
+        self.last_information_f64 = np.zeros(n, dtype=np.float64)
         st = self.lib.orc_fisher_poses(self.fisher, C.c_void_p(xyz.ctypes.data), C.c_uint64(len(xyz)),
                                        C.c_void_p(poses.ctypes.data), C.c_uint32(n), C.c_void_p(info.ctypes.data),
-                                       C.c_void_p(safe.ctypes.data), C.c_void_p(nvis.ctypes.data))
-        return st, info, safe, nvis
+                                       C.c_void_p(safe.ctypes.data), C.c_void_p(nvis.ctypes.data),
+                                       C.c_void_p(nused.ctypes.data), C.c_void_p(self.last_information_f64.ctypes.data))
+        return st, info, safe, nvis, nused
 
     def landmarks_in_view(self, xyz, pose, cap=1 << 20):
         xyz = np.ascontiguousarray(xyz, dtype=np.float32)

@@ -1007,6 +1007,8 @@ class FisherInformationManager {
   }
 
   // cpp:39-115
+  double total_information_f64_ = 0.0;  // stage dump: the same per-landmark float terms accumulated in double
+  uint32_t n_used_ = 0;  // stage dump: landmarks of the last query that hit a lookup-table entry
   bool isPoseSafe(const fitslam_pose &given_pose, const float *xyz, uint64_t P, float &information,
                   uint32_t &n_visible) {
     double fisher_information_threshold = prm.fisher_information_threshold;
@@ -1016,11 +1018,15 @@ class FisherInformationManager {
     n_visible = (uint32_t)map_points.size();
     float total_information = 0.0;
     occupied_voxel_count_ = 0;
+    n_used_ = 0;
+    total_information_f64_ = 0.0;
     for (const auto &mp : map_points) {
       // MapPoint.position is float64 on the wire, widened from the float the server computed
       double px = mp.v[0], py = mp.v[1], pz = mp.v[2];
       float info = getInformationFromLookup(px, py, pz, latest_version_);
       if (std::isnan(info)) continue;
+      ++n_used_;
+      total_information_f64_ += (double)info;
       total_information += info;
     }
     information = total_information;
@@ -1360,7 +1366,7 @@ float orc_crowd_factor(void *h, int num) {
 }
 
 int orc_fisher_poses(void *h, const float *xyz, uint64_t P, const fitslam_pose *poses, uint32_t n_poses,
-                     float *information, uint8_t *safe, uint32_t *n_visible) {
+                     float *information, uint8_t *safe, uint32_t *n_visible, uint32_t *n_used, double *information_f64) {
   auto *m = static_cast<FisherInformationManager *>(h);
   if (m->lookup_table_fi_.empty()) return FITSLAM_E_NO_LOOKUP_TABLE;
   for (uint32_t i = 0; i < n_poses; ++i) {
@@ -1370,6 +1376,8 @@ int orc_fisher_poses(void *h, const float *xyz, uint64_t P, const fitslam_pose *
     information[i] = info;
     if (safe) safe[i] = ok ? 1 : 0;
     if (n_visible) n_visible[i] = nv;
+    if (n_used) n_used[i] = m->n_used_;
+    if (information_f64) information_f64[i] = m->total_information_f64_;
   }
   return FITSLAM_OK;
 }
