@@ -1,0 +1,1060 @@
+// frontier.cu -- stage S: frontier extraction.
+//
+// Replaces FrontierSearch::searchFrom / buildNewFrontier / isNewFrontierCell / getAllFrontiers
+// (DEP/src/FrontierSearch.cpp:21-254), getCentroidOfCells + SortByMedianFunctor
+// (DEP/include/frontier_exploration/FrontierSearch.hpp:85-184) and nearestFreeCell (DEP/src/Helpers.cpp:285-330).
+//
+// The reference is two nested FIFO wavefronts; what it computes is ("stage S"):
+//   1. the static frontier mask M (isNewFrontierCell without the visited flag) and the traversable mask
+//      (cost < 254)                                                                             -> mask_kernel
+//   2. the 8-connected components of M                                                          -> union-find kernels
+//   3. which components are found, by which seed cell, and in which order: the first (dequeue rank of an
+//      expanded reachable cell, neighbour slot) that touches the component                      -> rank_bfs_kernel
+//   4. per found component, the cells in inner-wavefront order from the seed, cut into runs of
+//      max_frontier_cluster_size + 1                                                            -> replay_kernel
+//   5. per run, centroid / offset rule / libstdc++ std::sort by angle / median cell             -> chunk_kernel
+// Steps 1, 2 and 5 are order-free.  Steps 3 and 4 must reproduce FIFO order exactly, because the chunk boundaries
+// and therefore sizes and goal cells depend on it: they are level-synchronous passes in which a cell
+// decides locally whether it is the first in queue order to reach a neighbour (it reads the ranks of the neighbour's
+// other neighbours; no atomics, no sort) and an order-preserving block scan appends the winners to the queue.
+#include "ctx.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace fitslam {
+
+// `claim` encoding, one uint32 per map cell:
+//   0xFFFFFFFF            untouched
+//   0xFFFFFFFE            traversable cell visited by the outer wavefront but beyond the search radius (not enqueued)
+//   [0, 2^29)             traversable cell: its dequeue rank in the outer wavefront
+//   0x40000000 | r        frontier-mask cell: its position r in the inner wavefront of its component
+//   0x80000000 | key      frontier-mask cell: smallest (outer rank * 4 + slot) that touched it
+static constexpr uint32_t KEY_INF = 0xFFFFFFFFu;
+static constexpr uint32_t KEY_FAR = 0xFFFFFFFEu;
+static constexpr uint32_t INNER_BIT = 0x40000000u;
+static constexpr uint32_t TOUCH_BIT = 0x80000000u;
+static constexpr uint32_t MAX_RANK = (1u << 29) - 2;
+static constexpr int BFS_THREADS = 1024;
+static constexpr int REPLAY_THREADS = 128;
+static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
+
+struct Counters {
+  uint32_t n_mask;         // cells in the frontier mask
+  uint32_t n_comp;         // components touched by the search
+  uint32_t n_cells;        // cells of those components (every_frontier list)
+  uint32_t n_frontiers;    // runs with size > min_frontier_cluster_size
+  uint32_t bfs_levels;
+  uint32_t start_cell;
+  uint32_t overflow;       // bit0 mask list, bit1 bfs queue, bit2 component table
+  uint32_t ambiguous;      // chunk sorts with two angles within 4 ulp, or a comparator walk off the array
+  uint32_t expanded;       // reachable cells dequeued by the outer wavefront
+  uint32_t visited;        // queue entries + far cells (cleanup bound)
+  uint32_t pad[6];
+};
+
+struct SearchParams {
+  MapView map;
+  uint32_t wpr;            // mask words per row
+  uint32_t lethal;         // lethal_threshold
+  uint32_t robot_cell;     // getIndex(mx, my) of the robot
+  double robot_x, robot_y;
+  double dist_limit;       // max_frontier_distance + max_frontier_cluster_size * resolution * 1.414
+  int32_t min_size, max_size;
+  uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
+};
+
+struct FrontierState {
+  DevBuf<uint32_t> claim;     // per cell, see the encoding above; all KEY_INF between calls
+  DevBuf<uint32_t> slot;      // per cell: index into the mask-cell list (valid where the mask bit is set)
+  DevBuf<uint32_t> bits;      // frontier mask, wpr words per row
+  DevBuf<uint32_t> trav;      // traversable mask (cost < 254), same layout
+  DevBuf<uint32_t> mcell;     // mask-cell list (unordered)
+  DevBuf<uint32_t> parent;    // union-find over list indices
+  DevBuf<uint32_t> rkey;      // per root: min touch key of the component
+  DevBuf<uint32_t> rsize;     // per root: cell count
+  DevBuf<uint32_t> queue;     // outer wavefront, all levels back to back in dequeue order
+  DevBuf<uint32_t> ckey, cseed, csize;               // component table, unordered (append order)
+  DevBuf<uint32_t> oseed, osize, ocell0, ofront0;    // component table in discovery order + offsets
+  DevBuf<uint32_t> cells;     // every_frontier list, discovery order
+  DevBuf<double> centroids;   // per frontier: centroid after the offset rule (stage dump)
+  DevBuf<Counters> counters;
+  double search_distance = -1.0;  // < 0: use params.max_frontier_distance
+  uint64_t claim_cells = 0;   // cells for which claim is known to be all KEY_INF
+  uint32_t mask_cap = 0, queue_cap = 0, comp_cap = 0, cell_cap = 0, front_cap = 0;
+  Counters last{};
+};
+
+static FrontierState *fr_state(fitslam_ctx *c) {
+  if (!c->fs) c->fs = new FrontierState();
+  return c->fs;
+}
+
+void destroy_frontier_state(fitslam_ctx *c) {
+  if (!c->fs) return;
+  FrontierState *s = c->fs;
+  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->mcell.release();
+  s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
+  s->ckey.release(); s->cseed.release(); s->csize.release();
+  s->oseed.release(); s->osize.release(); s->ocell0.release(); s->ofront0.release();
+  s->cells.release(); s->centroids.release(); s->counters.release();
+  delete s;
+  c->fs = nullptr;
+}
+
+// ------------------------------------------------------------------------------------------------ helpers
+__device__ __forceinline__ bool get_bit(const uint32_t *__restrict__ bits, uint32_t wpr, uint32_t mx, uint32_t my) {
+  return (__ldg(bits + (size_t)my * wpr + (mx >> 5)) >> (mx & 31u)) & 1u;
+}
+__device__ __forceinline__ uint32_t ld_cg(const uint32_t *p) { return __ldcg(p); }
+
+// neighbour `s` of cell (mx, my) in the reference's order: -1, +1, -W, +W, -1-W, -1+W, +1-W, +1+W
+// (DEP/src/Helpers.cpp:185-255).  Returns false where the reference's bounds tests drop the neighbour.
+__device__ __forceinline__ bool nbr_of(uint32_t mx, uint32_t my, uint32_t W, uint32_t H, int s, uint32_t &nx, uint32_t &ny) {
+  const int dx = (s == 0 || s == 4 || s == 5) ? -1 : ((s == 1 || s == 6 || s == 7) ? 1 : 0);
+  const int dy = (s == 2 || s == 4 || s == 6) ? -1 : ((s == 3 || s == 5 || s == 7) ? 1 : 0);
+  const int x = (int)mx + dx, y = (int)my + dy;
+  if (x < 0 || y < 0 || x >= (int)W || y >= (int)H) return false;
+  nx = (uint32_t)x;
+  ny = (uint32_t)y;
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------------ K1: mask
+// isNewFrontierCell on the static map (DEP/src/FrontierSearch.cpp:218-249, predicates FrontierSearch.hpp:129-142):
+// cost == 255, no 4-neighbour with lethal_threshold <= cost < 255, at least one 4-neighbour with cost < lethal_threshold.
+// One thread per 32-cell mask word; rows are read as 16-byte vectors (pitch is a multiple of 16).
+__global__ void __launch_bounds__(256) mask_kernel(const SearchParams S, uint32_t *__restrict__ bits,
+                                                   uint32_t *__restrict__ trav, uint32_t *__restrict__ slot,
+                                                   uint32_t *__restrict__ mcell, Counters *__restrict__ cnt) {
+  const uint32_t W = S.map.W, H = S.map.H, pitch = S.map.pitch;
+  const uint64_t n_words = (uint64_t)S.wpr * H;
+  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t word = 0, tword = 0, my = 0, mx0 = 0;
+  if (gid < n_words) {
+    my = (uint32_t)(gid / S.wpr);
+    mx0 = (uint32_t)(gid - (uint64_t)my * S.wpr) * 32u;
+    const uint8_t *row = S.map.data + (size_t)my * pitch;
+    // centre row bytes mx0-1 .. mx0+32, up/down rows mx0 .. mx0+31 (the allocation is padded past the last row)
+    uint8_t c[34], u[32], d[32];
+    const bool full = mx0 + 32u <= pitch;
+    if (full) {
+      const uint4 *rc = reinterpret_cast<const uint4 *>(row + mx0);
+      uint4 a = __ldg(rc), b = __ldg(rc + 1);
+      memcpy(c + 1, &a, 16);
+      memcpy(c + 17, &b, 16);
+    } else {
+      for (int i = 0; i < 32; ++i) c[1 + i] = (mx0 + i < pitch) ? __ldg(row + mx0 + i) : 0;
+    }
+    c[0] = mx0 > 0 ? __ldg(row + mx0 - 1) : 0;
+    c[33] = (mx0 + 32u < W) ? __ldg(row + mx0 + 32) : 0;
+    const bool has_up = my > 0, has_dn = my + 1 < H;
+    if (full && has_up) {
+      const uint4 *r = reinterpret_cast<const uint4 *>(row - pitch + mx0);
+      uint4 a = __ldg(r), b = __ldg(r + 1);
+      memcpy(u, &a, 16);
+      memcpy(u + 16, &b, 16);
+    } else {
+      for (int i = 0; i < 32; ++i) u[i] = (has_up && mx0 + i < pitch) ? __ldg(row - pitch + mx0 + i) : 0;
+    }
+    if (full && has_dn) {
+      const uint4 *r = reinterpret_cast<const uint4 *>(row + pitch + mx0);
+      uint4 a = __ldg(r), b = __ldg(r + 1);
+      memcpy(d, &a, 16);
+      memcpy(d + 16, &b, 16);
+    } else {
+      for (int i = 0; i < 32; ++i) d[i] = (has_dn && mx0 + i < pitch) ? __ldg(row + pitch + mx0 + i) : 0;
+    }
+    const uint32_t thr = S.lethal;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const uint32_t mx = mx0 + i;
+      if (mx >= W) continue;
+      if (c[1 + i] < 254) tword |= 1u << i;  // map_[nbr] < LETHAL_OBSTACLE (FrontierSearch.cpp:67)
+      if (c[1 + i] != 255) continue;
+      bool fr = false, le = false;
+      if (mx > 0) { const uint32_t v = c[i]; fr |= v < thr; le |= (v >= thr && v != 255); }
+      if (mx + 1 < W) { const uint32_t v = c[2 + i]; fr |= v < thr; le |= (v >= thr && v != 255); }
+      if (has_up) { const uint32_t v = u[i]; fr |= v < thr; le |= (v >= thr && v != 255); }
+      if (has_dn) { const uint32_t v = d[i]; fr |= v < thr; le |= (v >= thr && v != 255); }
+      if (fr && !le) word |= 1u << i;
+    }
+    bits[gid] = word;
+    trav[gid] = tword;
+  }
+  // append the set cells to the list: one atomicAdd per warp
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t n = __popc(word);
+  uint32_t incl = n;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += v;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+  uint32_t base = 0;
+  if (total) {
+    if (lane == 31) base = atomicAdd(&cnt->n_mask, total);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    uint32_t pos = base + incl - n;
+    while (word) {
+      const int i = __ffs(word) - 1;
+      word &= word - 1;
+      const uint32_t cell = my * W + mx0 + i;
+      if (pos < S.mask_cap) {
+        mcell[pos] = cell;
+        slot[cell] = pos;
+      } else {
+        atomicOr(&cnt->overflow, 1u);
+      }
+      ++pos;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K2: union-find
+// 8-connected components of the frontier mask, over mask-list indices (lock-free min-root union).
+__device__ __forceinline__ uint32_t uf_find(uint32_t *parent, uint32_t i) {
+  uint32_t p = ld_cg(parent + i);
+  while (p != i) {
+    const uint32_t gp = ld_cg(parent + p);
+    if (gp != p) parent[i] = gp;  // path halving; racing writers only ever store an ancestor
+    i = p;
+    p = gp;
+  }
+  return i;
+}
+__device__ __forceinline__ void uf_union(uint32_t *parent, uint32_t a, uint32_t b) {
+  bool done;
+  do {
+    a = uf_find(parent, a);
+    b = uf_find(parent, b);
+    if (a < b) {
+      const uint32_t old = atomicMin(parent + b, a);
+      done = (old == b);
+      b = old;
+    } else if (b < a) {
+      const uint32_t old = atomicMin(parent + a, b);
+      done = (old == a);
+      a = old;
+    } else {
+      done = true;
+    }
+  } while (!done);
+}
+__global__ void uf_init_kernel(uint32_t *parent, uint32_t *rkey, uint32_t *rsize, const Counters *cnt, uint32_t cap) {
+  const uint32_t n = min(cnt->n_mask, cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    parent[i] = i;
+    rkey[i] = KEY_INF;
+    rsize[i] = 0;
+  }
+}
+// each mask cell links to its mask neighbours in the forward half of the 8-neighbourhood
+__global__ void uf_merge_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ slot,
+                                const uint32_t *__restrict__ mcell, uint32_t *parent, const Counters *cnt) {
+  if (cnt->overflow) return;  // slot[] is incomplete when the mask list overflowed; the host grows the list and reruns
+  const uint32_t n = min(cnt->n_mask, S.mask_cap);
+  const uint32_t W = S.map.W, H = S.map.H;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t c = mcell[i];
+    const uint32_t my = c / W, mx = c - my * W;
+    if (mx + 1 < W && get_bit(bits, S.wpr, mx + 1, my)) uf_union(parent, i, slot[c + 1]);
+    if (my + 1 < H) {
+      if (mx > 0 && get_bit(bits, S.wpr, mx - 1, my + 1)) uf_union(parent, i, slot[c + W - 1]);
+      if (get_bit(bits, S.wpr, mx, my + 1)) uf_union(parent, i, slot[c + W]);
+      if (mx + 1 < W && get_bit(bits, S.wpr, mx + 1, my + 1)) uf_union(parent, i, slot[c + W + 1]);
+    }
+  }
+}
+// flatten: parent[i] = root; rsize[root] = number of cells
+__global__ void uf_compress_kernel(uint32_t *parent, uint32_t *rsize, const Counters *cnt, uint32_t cap) {
+  const uint32_t n = min(cnt->n_mask, cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t r = uf_find(parent, i);
+    parent[i] = r;
+    atomicAdd(rsize + r, 1u);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K3: ranked wavefronts
+// Block-wide exclusive scan of small per-thread counts; returns this thread's offset, *total = sum.
+// warp_sums needs 33 words.  Ends with a barrier, so shared scratch can be reused right away.
+__device__ __forceinline__ uint32_t block_scan(uint32_t v, uint32_t *warp_sums, uint32_t *total) {
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  if (lane == 31) warp_sums[wid] = incl;
+  __syncthreads();
+  if (wid == 0) {
+    const uint32_t w = lane < nw ? warp_sums[lane] : 0;
+    uint32_t wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+      if ((int)lane >= o) wi += t;
+    }
+    warp_sums[lane] = wi - w;
+    if (lane == 31) warp_sums[32] = wi;
+  }
+  __syncthreads();
+  const uint32_t r = warp_sums[wid] + incl - v;
+  *total = warp_sums[32];
+  __syncthreads();
+  return r;
+}
+
+// nearestFreeCell (DEP/src/Helpers.cpp:285-330): 8-connected FIFO wavefront over every cell, stops at the first
+// dequeued cell with cost < lethal_threshold.  Rare path (the robot normally stands on free space), so it uses the
+// plain claim-with-atomicMin formulation: key = level base + queue position * 8 + slot.  Leaves claim[] clean.
+__device__ void nearest_free_cell(const SearchParams &S, uint32_t *claim, uint32_t *q0, uint32_t *q1, uint32_t start,
+                                  uint32_t *sh, Counters *cnt, uint32_t *found_cell) {
+  const uint32_t W = S.map.W, H = S.map.H;
+  uint32_t *warp_sums = sh;   // 33 words
+  uint32_t *s_min = sh + 40;
+  uint32_t n = 1, base = 1, levels = 0;
+  uint32_t *q = q0, *qn = q1;
+  if (threadIdx.x == 0) {
+    q[0] = start;
+    claim[start] = 0;
+  }
+  __syncthreads();
+  while (n > 0) {
+    if (threadIdx.x == 0) *s_min = KEY_INF;
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += BFS_THREADS) {
+      const uint32_t c = q[i];
+      const uint32_t my = c / W, mx = c - my * W;
+      if (S.map.data[(size_t)my * S.map.pitch + mx] < S.lethal) atomicMin(s_min, i);
+    }
+    __syncthreads();
+    if (*s_min != KEY_INF) {
+      if (threadIdx.x == 0) *found_cell = q[*s_min];
+      __syncthreads();
+      break;
+    }
+    const uint32_t total = n << 3;
+    for (uint32_t j = threadIdx.x; j < total; j += BFS_THREADS) {
+      const uint32_t c = q[j >> 3];
+      const uint32_t my = c / W, mx = c - my * W;
+      uint32_t nx, ny;
+      if (!nbr_of(mx, my, W, H, (int)(j & 7), nx, ny)) continue;
+      const uint32_t nb = ny * W + nx;
+      if (ld_cg(claim + nb) >= base) atomicMin(claim + nb, base + j);
+    }
+    __threadfence();
+    __syncthreads();
+    uint32_t n_next = 0;
+    for (uint32_t j0 = 0; j0 < total; j0 += BFS_THREADS) {
+      const uint32_t j = j0 + threadIdx.x;
+      bool push = false;
+      uint32_t nb = 0;
+      if (j < total) {
+        const uint32_t c = q[j >> 3];
+        const uint32_t my = c / W, mx = c - my * W;
+        uint32_t nx, ny;
+        if (nbr_of(mx, my, W, H, (int)(j & 7), nx, ny)) {
+          nb = ny * W + nx;
+          push = ld_cg(claim + nb) == base + j;
+        }
+      }
+      uint32_t tile_total;
+      const uint32_t off = block_scan(push ? 1u : 0u, warp_sums, &tile_total);
+      if (push) {
+        if (n_next + off < S.queue_cap / 2) qn[n_next + off] = nb;
+        else atomicOr(&cnt->overflow, 2u);
+      }
+      n_next += tile_total;
+    }
+    __threadfence();
+    __syncthreads();
+    base += total;
+    n = min(n_next, S.queue_cap / 2);
+    uint32_t *t = q; q = qn; qn = t;
+    ++levels;
+  }
+  // undo the claims (Chebyshev ball of radius levels + 1 around the start)
+  __syncthreads();
+  const uint32_t sy = start / W, sx = start - sy * W;
+  const int r = (int)levels + 1;
+  const long side = 2 * r + 1;
+  for (long i = threadIdx.x; i < side * side; i += BFS_THREADS) {
+    const int y = (int)sy - r + (int)(i / side), x = (int)sx - r + (int)(i % side);
+    if (x >= 0 && y >= 0 && x < (int)W && y < (int)H) claim[(size_t)y * W + x] = KEY_INF;
+  }
+  __threadfence();
+  __syncthreads();
+}
+
+// The outer wavefront of searchFrom (DEP/src/FrontierSearch.cpp:58-94), one CTA, levels in exact FIFO order.
+// A dequeued cell p with rank r looks at its 4 neighbours in the reference's order.  A traversable, unvisited neighbour c
+// is visited by p iff no other neighbour of c has a rank in [level base, r): those are exactly the cells dequeued
+// before p in this level that would have visited c first.  Winners are appended in (rank, slot) order by a block scan,
+// which is the order the reference pushes them.  Frontier-mask neighbours only record the smallest touching key.
+__global__ void __launch_bounds__(BFS_THREADS)
+rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ trav, uint32_t *claim,
+                uint32_t *queue, Counters *cnt) {
+  __shared__ uint32_t sh[48];
+  __shared__ uint32_t s_start;
+  if (cnt->overflow) return;
+  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
+  if (threadIdx.x == 0) s_start = S.robot_cell;  // falls back to pos when no cell qualifies (FrontierSearch.cpp:47-54)
+  __syncthreads();
+  if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+    nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh, cnt, &s_start);
+    __syncthreads();
+  }
+  const uint32_t start = s_start;
+  if (threadIdx.x == 0) {
+    cnt->start_cell = start;
+    queue[0] = start;
+    claim[start] = 0;
+  }
+  __syncthreads();
+  uint32_t base = 0, n = 1, levels = 0;
+  while (n > 0) {
+    const uint32_t next_base = base + n;
+    uint32_t n_next = 0;
+    for (uint32_t tile = 0; tile < n; tile += BFS_THREADS) {
+      const uint32_t i = tile + threadIdx.x;
+      uint32_t win[4];
+      uint32_t n_win = 0, far_mask = 0;
+      if (i < n) {
+        const uint32_t rank = base + i;
+        const uint32_t c = ld_cg(queue + rank);
+        const uint32_t my = c / W, mx = c - my * W;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          uint32_t nx, ny;
+          if (!nbr_of(mx, my, W, H, s, nx, ny)) continue;
+          const uint32_t nb = ny * W + nx;
+          if (get_bit(trav, S.wpr, nx, ny)) {
+            if (ld_cg(claim + nb) != KEY_INF) continue;  // visited_flag[nbr]
+            bool first = true;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              uint32_t ox, oy;
+              if (!nbr_of(nx, ny, W, H, t, ox, oy)) continue;
+              const uint32_t o = oy * W + ox;
+              if (o == c) continue;
+              const uint32_t r = ld_cg(claim + o);
+              if (r >= base && r < rank) first = false;
+            }
+            if (!first) continue;
+            // visited now; enqueued only inside the search radius (FrontierSearch.cpp:72-76)
+            const double wx = S.map.ox + (nx + 0.5) * S.map.res;
+            const double wy = S.map.oy + (ny + 0.5) * S.map.res;
+            const double ddx = S.robot_x - wx, ddy = S.robot_y - wy;
+            if (sqrt(ddx * ddx + ddy * ddy) < S.dist_limit) win[n_win++] = nb;
+            else far_mask |= 1u << s;
+          } else if (get_bit(bits, S.wpr, nx, ny)) {
+            atomicMin(claim + nb, TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
+          }
+        }
+      }
+      uint32_t tile_total;
+      const uint32_t off = block_scan(n_win, sh, &tile_total);
+      const uint32_t dst = next_base + n_next + off;
+      for (uint32_t k = 0; k < n_win; ++k) {
+        queue[dst + k] = win[k];
+        claim[win[k]] = dst + k;
+      }
+      if (far_mask) {
+        const uint32_t c = queue[base + i];
+        const uint32_t my = c / W, mx = c - my * W;
+        for (int s = 0; s < 4; ++s)
+          if (far_mask & (1u << s)) {
+            uint32_t nx, ny;
+            nbr_of(mx, my, W, H, s, nx, ny);
+            claim[ny * W + nx] = KEY_FAR;
+          }
+      }
+      n_next += tile_total;
+      __syncthreads();
+    }
+    base = next_base;
+    n = n_next;
+    ++levels;
+  }
+  if (threadIdx.x == 0) {
+    cnt->bfs_levels = levels;
+    cnt->expanded = base;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K4: found components
+// per component: smallest touching key (= the seed's key, FrontierSearch.cpp:78-81)
+__global__ void touch_reduce_kernel(const SearchParams S, const uint32_t *__restrict__ mcell, const uint32_t *__restrict__ parent,
+                                    const uint32_t *__restrict__ claim, uint32_t *rkey, const Counters *cnt) {
+  if (cnt->overflow) return;
+  const uint32_t n = min(cnt->n_mask, S.mask_cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t k = claim[mcell[i]];
+    if (k != KEY_INF) atomicMin(rkey + parent[i], k);
+  }
+}
+// the cell whose key equals its component's minimum is the seed: append {key, seed, size} to the component table
+__global__ void seed_collect_kernel(const SearchParams S, const uint32_t *__restrict__ mcell, const uint32_t *__restrict__ parent,
+                                    const uint32_t *__restrict__ claim, const uint32_t *__restrict__ rkey,
+                                    const uint32_t *__restrict__ rsize, uint32_t *ckey, uint32_t *cseed, uint32_t *csize,
+                                    Counters *cnt) {
+  if (cnt->overflow & 3u) return;
+  const uint32_t n = min(cnt->n_mask, S.mask_cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t c = mcell[i];
+    const uint32_t k = claim[c];
+    if (k == KEY_INF) continue;
+    const uint32_t r = parent[i];
+    if (rkey[r] != k) continue;
+    const uint32_t pos = atomicAdd(&cnt->n_comp, 1u);
+    if (pos < S.comp_cap) {
+      ckey[pos] = k;
+      cseed[pos] = c;
+      csize[pos] = rsize[r];
+    } else {
+      atomicOr(&cnt->overflow, 4u);
+    }
+  }
+}
+// discovery order = ascending seed key (keys are unique): rank by counting, scatter into the ordered table
+__global__ void __launch_bounds__(256)
+comp_order_kernel(const SearchParams S, const uint32_t *__restrict__ ckey, const uint32_t *__restrict__ cseed,
+                  const uint32_t *__restrict__ csize, uint32_t *oseed, uint32_t *osize, const Counters *cnt) {
+  __shared__ uint32_t sk[256];
+  const uint32_t n = min(cnt->n_comp, S.comp_cap);
+  for (uint32_t i0 = blockIdx.x * 256; i0 < n; i0 += gridDim.x * 256) {
+    const uint32_t i = i0 + threadIdx.x;
+    const uint32_t mine = i < n ? ckey[i] : 0;
+    uint32_t r = 0;
+    for (uint32_t base = 0; base < n; base += 256) {
+      sk[threadIdx.x] = base + threadIdx.x < n ? ckey[base + threadIdx.x] : KEY_INF;
+      __syncthreads();
+      if (i < n) {
+        const uint32_t m = min(256u, n - base);
+        for (uint32_t t = 0; t < m; ++t) r += sk[t] < mine ? 1u : 0u;
+      }
+      __syncthreads();
+    }
+    if (i < n) {
+      oseed[r] = cseed[i];
+      osize[r] = csize[i];
+    }
+  }
+}
+// exclusive scans over the ordered components: first cell / first frontier of each; totals into the counters.
+// run lengths (FrontierSearch.cpp:150-199): full runs of max+1 cells, then a remainder kept iff it is > min.
+__global__ void __launch_bounds__(1024)
+comp_scan_kernel(const SearchParams S, const uint32_t *__restrict__ osize, uint32_t *ocell0, uint32_t *ofront0, Counters *cnt) {
+  __shared__ uint32_t sh[40];
+  const uint32_t n = min(cnt->n_comp, S.comp_cap);
+  const uint32_t run = (uint32_t)S.max_size + 1u;
+  uint32_t cell_carry = 0, front_carry = 0;
+  for (uint32_t base = 0; base < n; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t sz = i < n ? osize[i] : 0;
+    const uint32_t rem = sz % run;
+    const uint32_t nf = i < n ? ((int)run > S.min_size ? sz / run : 0u) + ((int)rem > S.min_size ? 1u : 0u) : 0u;
+    uint32_t tc, tf;
+    const uint32_t oc = block_scan(sz, sh, &tc);
+    const uint32_t of = block_scan(nf, sh, &tf);
+    if (i < n) {
+      ocell0[i] = cell_carry + oc;
+      ofront0[i] = front_carry + of;
+    }
+    cell_carry += tc;
+    front_carry += tf;
+  }
+  if (threadIdx.x == 0) {
+    cnt->n_cells = cell_carry;
+    cnt->n_frontiers = front_carry;
+    if (cell_carry > S.cell_cap) atomicOr(&cnt->overflow, 8u);
+    if (front_carry > S.front_cap) atomicOr(&cnt->overflow, 16u);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K5: inner wavefronts
+// buildNewFrontier's FIFO, 8-connected wavefront over the frontier mask from the seed (DEP/src/FrontierSearch.cpp:123-189),
+// one CTA per found component, same first-in-queue-order rule as the outer wavefront.  The component's slice of the
+// every_frontier list IS the queue: level after level, in acceptance order.
+__global__ void __launch_bounds__(REPLAY_THREADS)
+replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t *claim, const uint32_t *__restrict__ oseed,
+              const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, uint32_t *cells, const Counters *cnt) {
+  __shared__ uint32_t sh[40];
+  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
+  if (cnt->overflow) return;
+  for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
+    uint32_t *out = cells + ocell0[comp];
+    const uint32_t seed = oseed[comp];
+    if (threadIdx.x == 0) {
+      out[0] = seed;
+      claim[seed] = INNER_BIT;
+    }
+    __syncthreads();
+    uint32_t base = 0, n = 1;
+    while (n > 0) {
+      const uint32_t next_base = base + n, items = n << 3;
+      uint32_t n_next = 0;
+      for (uint32_t tile = 0; tile < items; tile += REPLAY_THREADS) {
+        const uint32_t j = tile + threadIdx.x;
+        bool win = false;
+        uint32_t nb = 0;
+        if (j < items) {
+          const uint32_t rank = base + (j >> 3);
+          const uint32_t p = ld_cg(out + rank);
+          const uint32_t my = p / W, mx = p - my * W;
+          uint32_t nx, ny;
+          if (nbr_of(mx, my, W, H, (int)(j & 7u), nx, ny) && get_bit(bits, S.wpr, nx, ny)) {
+            nb = ny * W + nx;
+            if ((ld_cg(claim + nb) & 0xC0000000u) != INNER_BIT) {  // !frontier_flag[nbr]
+              win = true;
+#pragma unroll
+              for (int t = 0; t < 8; ++t) {
+                uint32_t ox, oy;
+                if (!nbr_of(nx, ny, W, H, t, ox, oy)) continue;
+                const uint32_t o = oy * W + ox;
+                if (o == p) continue;
+                const uint32_t r = ld_cg(claim + o);
+                if (r >= (INNER_BIT | base) && r < (INNER_BIT | rank)) win = false;
+              }
+            }
+          }
+        }
+        uint32_t tile_total;
+        const uint32_t off = block_scan(win ? 1u : 0u, sh, &tile_total);
+        if (win) {
+          const uint32_t dst = next_base + n_next + off;
+          out[dst] = nb;
+          claim[nb] = INNER_BIT | dst;
+        }
+        n_next += tile_total;
+        __syncthreads();
+      }
+      base = next_base;
+      n = n_next;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K6: runs -> frontiers
+// SortByMedianFunctor (FrontierSearch.hpp:156-184) on precomputed angles
+__device__ __forceinline__ bool median_less(double angle_a, double angle_b) {
+  if (0 <= angle_a && angle_a <= M_PI / 2 && 3 * M_PI / 2 <= angle_b && angle_b <= 2 * M_PI) return false;
+  if (0 <= angle_b && angle_b <= M_PI / 2 && 3 * M_PI / 2 <= angle_a && angle_a <= 2 * M_PI) return true;
+  return angle_a < angle_b;
+}
+
+struct SortCtx {
+  double *ang;     // angle of element k
+  uint8_t *idx;    // permutation being sorted
+  int n;
+  bool bad;        // an unguarded loop left [0, n): the comparator is not a strict weak order on this input
+};
+#define SLESS(a, b) median_less(sc.ang[sc.idx[a]], sc.ang[sc.idx[b]])
+__device__ __forceinline__ void s_swap(SortCtx &sc, int a, int b) { const uint8_t t = sc.idx[a]; sc.idx[a] = sc.idx[b]; sc.idx[b] = t; }
+
+// libstdc++ __unguarded_linear_insert / __insertion_sort (bits/stl_algo.h)
+__device__ void s_unguarded_linear_insert(SortCtx &sc, int last) {
+  const uint8_t val = sc.idx[last];
+  int next = last - 1;
+  while (next >= 0 && median_less(sc.ang[val], sc.ang[sc.idx[next]])) {
+    sc.idx[last] = sc.idx[next];
+    last = next;
+    --next;
+  }
+  if (next < 0 && last == 0) {
+    // the guarded form never gets here with a consistent comparator: position 0 is <= val by construction
+    sc.bad = true;
+  }
+  sc.idx[last] = val;
+}
+__device__ void s_insertion_sort(SortCtx &sc, int first, int last) {
+  if (first == last) return;
+  for (int i = first + 1; i != last; ++i) {
+    if (SLESS(i, first)) {
+      const uint8_t val = sc.idx[i];
+      for (int k = i; k > first; --k) sc.idx[k] = sc.idx[k - 1];
+      sc.idx[first] = val;
+    } else {
+      s_unguarded_linear_insert(sc, i);
+    }
+  }
+}
+// __move_median_to_first + __unguarded_partition
+__device__ int s_partition_pivot(SortCtx &sc, int first, int last) {
+  const int mid = first + (last - first) / 2;
+  const int a = first + 1, b = mid, c = last - 1, result = first;
+  if (SLESS(a, b)) {
+    if (SLESS(b, c)) s_swap(sc, result, b);
+    else if (SLESS(a, c)) s_swap(sc, result, c);
+    else s_swap(sc, result, a);
+  } else if (SLESS(a, c)) s_swap(sc, result, a);
+  else if (SLESS(b, c)) s_swap(sc, result, c);
+  else s_swap(sc, result, b);
+  int lo = first + 1, hi = last;
+  const int pivot = first;
+  while (true) {
+    while (lo < sc.n && SLESS(lo, pivot)) ++lo;
+    --hi;
+    while (hi >= 0 && SLESS(pivot, hi)) --hi;
+    if (lo >= sc.n || hi < 0) { sc.bad = true; return min(max(lo, first + 1), last); }
+    if (!(lo < hi)) return lo;
+    s_swap(sc, lo, hi);
+    ++lo;
+  }
+}
+// __adjust_heap / __make_heap / __sort_heap: the depth-limit fallback (__partial_sort(first, last, last))
+__device__ void s_adjust_heap(SortCtx &sc, int first, int hole, int len, uint8_t value) {
+  const int top = hole;
+  int child = hole;
+  while (child < (len - 1) / 2) {
+    child = 2 * (child + 1);
+    if (median_less(sc.ang[sc.idx[first + child]], sc.ang[sc.idx[first + child - 1]])) --child;
+    sc.idx[first + hole] = sc.idx[first + child];
+    hole = child;
+  }
+  if ((len & 1) == 0 && child == (len - 2) / 2) {
+    child = 2 * (child + 1);
+    sc.idx[first + hole] = sc.idx[first + child - 1];
+    hole = child - 1;
+  }
+  int parent = (hole - 1) / 2;  // __push_heap
+  while (hole > top && median_less(sc.ang[sc.idx[first + parent]], sc.ang[value])) {
+    sc.idx[first + hole] = sc.idx[first + parent];
+    hole = parent;
+    parent = (hole - 1) / 2;
+  }
+  sc.idx[first + hole] = value;
+}
+__device__ void s_heap_sort(SortCtx &sc, int first, int last) {
+  const int len = last - first;
+  if (len >= 2) {
+    int parent = (len - 2) / 2;
+    while (true) {
+      const uint8_t v = sc.idx[first + parent];
+      s_adjust_heap(sc, first, parent, len, v);
+      if (parent == 0) break;
+      --parent;
+    }
+  }
+  for (int l = last; l - first > 1;) {
+    --l;
+    const uint8_t v = sc.idx[l];
+    sc.idx[l] = sc.idx[first];
+    s_adjust_heap(sc, first, 0, l - first, v);
+  }
+}
+// std::sort: __introsort_loop (threshold 16, depth limit 2 * floor(log2 n)) + __final_insertion_sort
+__device__ void s_std_sort(SortCtx &sc) {
+  const int n = sc.n;
+  if (n < 2) return;
+  // the recursion `__introsort_loop(cut, last)` then `last = cut` is unrolled with an explicit stack of (first, last, depth)
+  int stk_first[16], stk_last[16], stk_depth[16];
+  int sp = 0;
+  stk_first[0] = 0; stk_last[0] = n; stk_depth[0] = 2 * (31 - __clz(n)); sp = 1;
+  while (sp > 0) {
+    --sp;
+    int first = stk_first[sp], last = stk_last[sp], depth = stk_depth[sp];
+    // the reference recurses on the RIGHT part first and loops on the left part; a stack pops in LIFO order, so
+    // process this range's loop and push right parts; order of independent sub-ranges does not affect the result
+    while (last - first > 16) {
+      if (depth == 0) {
+        s_heap_sort(sc, first, last);
+        break;
+      }
+      --depth;
+      const int cut = s_partition_pivot(sc, first, last);
+      if (sp < 16) { stk_first[sp] = cut; stk_last[sp] = last; stk_depth[sp] = depth; ++sp; }
+      else sc.bad = true;
+      last = cut;
+    }
+  }
+  if (n > 16) {
+    s_insertion_sort(sc, 0, 16);
+    for (int i = 16; i < n; ++i) s_unguarded_linear_insert(sc, i);
+  } else {
+    s_insertion_sort(sc, 0, n);
+  }
+}
+
+// One thread per kept run: getCentroidOfCells (FrontierSearch.hpp:85-126), std::sort with SortByMedianFunctor,
+// goal = sorted[size / 2] (FrontierSearch.cpp:161-165, 194-199).
+__global__ void __launch_bounds__(64)
+chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0,
+             const uint32_t *__restrict__ ofront0, const uint32_t *__restrict__ cells, fitslam_frontier *out,
+             double *centroids, Counters *cnt) {
+  if (cnt->overflow) return;
+  const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
+  const uint32_t n_front = cnt->n_frontiers;
+  const uint32_t run = (uint32_t)S.max_size + 1u;
+  const uint32_t W = S.map.W;
+  for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < n_front; f += gridDim.x * blockDim.x) {
+    // component of frontier f: last comp with ofront0[comp] <= f
+    uint32_t lo = 0, hi = n_comp;
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (ofront0[mid] <= f) lo = mid; else hi = mid;
+    }
+    const uint32_t comp = lo, j = f - ofront0[comp];
+    const uint32_t first_cell = ocell0[comp] + j * run;
+    const int n = (int)min(run, osize[comp] - j * run);
+    const uint32_t *cl = cells + first_cell;
+    double ang[MAX_CHUNK];
+    uint8_t idx[MAX_CHUNK];
+    double sumX = 0, sumY = 0;
+    for (int k = 0; k < n; ++k) {
+      const uint32_t c = cl[k];
+      const uint32_t my = c / W, mx = c - my * W;
+      sumX += S.map.ox + (mx + 0.5) * S.map.res;
+      sumY += S.map.oy + (my + 0.5) * S.map.res;
+    }
+    double centerX = sumX / (double)n, centerY = sumY / (double)n;
+    bool offset_centroid = false;
+    double varX = 0, varY = 0;
+    for (int k = 0; k < n; ++k) {
+      const uint32_t c = cl[k];
+      const uint32_t my = c / W, mx = c - my * W;
+      const double dx = (S.map.ox + (mx + 0.5) * S.map.res) - centerX, dy = (S.map.oy + (my + 0.5) * S.map.res) - centerY;
+      if (sqrt(dx * dx + dy * dy) < S.map.res * 3) offset_centroid = true;
+      varX += fabs(dx);
+      varY += fabs(dy);
+    }
+    const double distance_to_offset = S.map.res * 1.414 * 2;
+    if (varX > varY && offset_centroid) centerY -= distance_to_offset;
+    if (varX < varY && offset_centroid) centerX -= distance_to_offset;
+    for (int k = 0; k < n; ++k) {
+      const uint32_t c = cl[k];
+      const uint32_t my = c / W, mx = c - my * W;
+      double a = atan2((S.map.oy + (my + 0.5) * S.map.res) - centerY, (S.map.ox + (mx + 0.5) * S.map.res) - centerX);
+      if (a < 0) a = a + (2 * M_PI);
+      ang[k] = a;
+      idx[k] = (uint8_t)k;
+    }
+    SortCtx sc{ang, idx, n, false};
+    s_std_sort(sc);
+    bool ambiguous = sc.bad;
+    for (int k = 0; k + 1 < n; ++k) {
+      const long long a = __double_as_longlong(ang[idx[k]]), b = __double_as_longlong(ang[idx[k + 1]]);
+      if (a != b && llabs(a - b) <= 4) ambiguous = true;  // device atan2 is within 2 ulp of libm's
+    }
+    if (ambiguous) atomicAdd(&cnt->ambiguous, 1u);
+    const uint32_t g = cl[idx[n / 2]];
+    fitslam_frontier r;
+    r.goal_my = g / W;
+    r.goal_mx = g - r.goal_my * W;
+    r.goal_x = S.map.ox + (r.goal_mx + 0.5) * S.map.res;
+    r.goal_y = S.map.oy + (r.goal_my + 0.5) * S.map.res;
+    r.size = n;
+    r.component = comp;
+    r.chunk = j;
+    r.first_cell = first_cell;
+    out[f] = r;
+    if (centroids) {
+      centroids[2 * f] = centerX;
+      centroids[2 * f + 1] = centerY;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K7: clean claim[]
+// every cell the search wrote is a queue entry, one of its 4 neighbours, or a frontier-mask cell
+__global__ void cleanup_kernel(const SearchParams S, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ mcell,
+                               uint32_t *claim, const Counters *cnt) {
+  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t nq = cnt->expanded, nm = min(cnt->n_mask, S.mask_cap);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nq + nm; i += gridDim.x * blockDim.x) {
+    if (i < nq) {
+      const uint32_t c = queue[i];
+      const uint32_t my = c / W, mx = c - my * W;
+      claim[c] = KEY_INF;
+      if (mx > 0) claim[c - 1] = KEY_INF;
+      if (mx + 1 < W) claim[c + 1] = KEY_INF;
+      if (my > 0) claim[c - W] = KEY_INF;
+      if (my + 1 < H) claim[c + W] = KEY_INF;
+    } else {
+      claim[mcell[i - nq]] = KEY_INF;
+    }
+  }
+}
+
+}  // namespace fitslam
+
+// ================================================================================================ host side
+namespace fitslam {
+
+static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) {
+  const uint64_t N = (uint64_t)c->W * c->H;
+  if (N > MAX_RANK) return fail(c, FITSLAM_E_INVALID, "search_frontiers: more than 2^29 cells");
+  const uint32_t wpr = (c->W + 31u) / 32u;
+  FS_CUDA(c, s->bits.reserve((size_t)wpr * c->H));
+  FS_CUDA(c, s->trav.reserve((size_t)wpr * c->H));
+  FS_CUDA(c, s->slot.reserve(N));
+  FS_CUDA(c, s->queue.reserve(N + 8));
+  FS_CUDA(c, s->counters.reserve(1));
+  if (s->claim.cap < N || s->claim_cells != N) {
+    FS_CUDA(c, s->claim.reserve(N));
+    FS_CUDA(c, cudaMemsetAsync(s->claim.p, 0xFF, s->claim.cap * sizeof(uint32_t), c->stream));
+    s->claim_cells = N;
+  }
+  if (s->mask_cap == 0) {
+    s->mask_cap = (uint32_t)std::min<uint64_t>(N, std::max<uint64_t>(1u << 16, N / 32));
+    s->comp_cap = s->mask_cap / 4 + 1024;
+    s->cell_cap = s->mask_cap;
+    s->front_cap = s->mask_cap / 2 + 1024;
+  }
+  FS_CUDA(c, s->mcell.reserve(s->mask_cap));
+  FS_CUDA(c, s->parent.reserve(s->mask_cap));
+  FS_CUDA(c, s->rkey.reserve(s->mask_cap));
+  FS_CUDA(c, s->rsize.reserve(s->mask_cap));
+  FS_CUDA(c, s->ckey.reserve(s->comp_cap));
+  FS_CUDA(c, s->cseed.reserve(s->comp_cap));
+  FS_CUDA(c, s->csize.reserve(s->comp_cap));
+  FS_CUDA(c, s->oseed.reserve(s->comp_cap));
+  FS_CUDA(c, s->osize.reserve(s->comp_cap));
+  FS_CUDA(c, s->ocell0.reserve(s->comp_cap));
+  FS_CUDA(c, s->ofront0.reserve(s->comp_cap));
+  FS_CUDA(c, s->cells.reserve(s->cell_cap));
+  FS_CUDA(c, s->centroids.reserve(2 * (size_t)s->front_cap));
+  FS_CUDA(c, c->frontiers.reserve(s->front_cap));
+  return FITSLAM_OK;
+}
+
+// Enqueue one search on the context stream; counters land in *host_counters (pinned) after the stream drains.
+static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t robot_cell, double rx, double ry,
+                                     Counters *host_counters) {
+  SearchParams S;
+  memset(&S, 0, sizeof(S));
+  S.map = map_view(c);
+  S.wpr = (c->W + 31u) / 32u;
+  S.lethal = (uint32_t)c->prm.lethal_threshold;
+  S.robot_cell = robot_cell;
+  S.robot_x = rx;
+  S.robot_y = ry;
+  const double mfd = s->search_distance >= 0.0 ? s->search_distance : c->prm.max_frontier_distance;
+  S.dist_limit = mfd + (c->prm.max_frontier_cluster_size * c->res * 1.414);  // FrontierSearch.cpp:74
+  S.min_size = c->prm.min_frontier_cluster_size;
+  S.max_size = c->prm.max_frontier_cluster_size;
+  S.mask_cap = s->mask_cap;
+  S.queue_cap = (uint32_t)std::min<size_t>(s->queue.cap, 0xFFFFFFF0u);
+  S.comp_cap = s->comp_cap;
+  S.cell_cap = s->cell_cap;
+  S.front_cap = s->front_cap;
+  Counters *cnt = s->counters.p;
+  FS_CUDA(c, cudaMemsetAsync(cnt, 0, sizeof(Counters), c->stream));
+  const uint64_t n_words = (uint64_t)S.wpr * c->H;
+  const unsigned wide = 148 * 8;
+  mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->slot.p, s->mcell.p, cnt);
+  uf_init_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rkey.p, s->rsize.p, cnt, S.mask_cap);
+  uf_merge_kernel<<<wide, 256, 0, c->stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
+  uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, cnt, S.mask_cap);
+  rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);
+  touch_reduce_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, cnt);
+  seed_collect_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->ckey.p,
+                                                    s->cseed.p, s->csize.p, cnt);
+  comp_order_kernel<<<148 * 2, 256, 0, c->stream>>>(S, s->ckey.p, s->cseed.p, s->csize.p, s->oseed.p, s->osize.p, cnt);
+  comp_scan_kernel<<<1, 1024, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, cnt);
+  replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
+                                                            s->cells.p, cnt);
+  chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
+                                               s->centroids.p, cnt);
+  cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
+  c->launches += 12;
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaMemcpyAsync(host_counters, cnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+  return FITSLAM_OK;
+}
+
+// FrontierSearch::searchFrom on the device; the frontier list stays resident in c->frontiers (c->n_frontiers entries).
+fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  if (c->prm.max_frontier_cluster_size + 1 > MAX_CHUNK || c->prm.max_frontier_cluster_size + 1 <= c->prm.min_frontier_cluster_size)
+    return fail(c, FITSLAM_E_INVALID, "search_frontiers: need min_frontier_cluster_size < max_frontier_cluster_size + 1 <= 64");
+  FrontierState *s = fr_state(c);
+  // Costmap2D::worldToMap (FrontierSearch.cpp:28-32)
+  c->n_frontiers = 0;
+  if (rx < c->ox || ry < c->oy) return fail(c, FITSLAM_E_ROBOT_OUT_OF_BOUNDS, "Robot out of costmap bounds, cannot search for frontiers");
+  const unsigned int mx = static_cast<unsigned int>((rx - c->ox) / c->res), my = static_cast<unsigned int>((ry - c->oy) / c->res);
+  if (!(mx < c->W && my < c->H)) return fail(c, FITSLAM_E_ROBOT_OUT_OF_BOUNDS, "Robot out of costmap bounds, cannot search for frontiers");
+  fitslam_status st = ensure_pinned(c, sizeof(Counters));
+  if (st != FITSLAM_OK) return st;
+  for (int attempt = 0; attempt < 8; ++attempt) {
+    st = ensure_frontier_buffers(c, s);
+    if (st != FITSLAM_OK) return st;
+    Counters *hc = reinterpret_cast<Counters *>(c->pinned);
+    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc);
+    if (st != FITSLAM_OK) return st;
+    FS_CUDA(c, cudaStreamSynchronize(c->stream));
+    s->last = *hc;
+    if (!hc->overflow) {
+      c->n_frontiers = hc->n_frontiers;
+      return FITSLAM_OK;
+    }
+    // a list was too small: grow to what this run counted (plus slack) and search again
+    if (hc->overflow & 1u) s->mask_cap = hc->n_mask + hc->n_mask / 8 + 1024;
+    if (hc->overflow & 4u) s->comp_cap = hc->n_comp + hc->n_comp / 8 + 1024;
+    if (hc->overflow & 8u) s->cell_cap = hc->n_cells + hc->n_cells / 8 + 1024;
+    if (hc->overflow & 16u) s->front_cap = hc->n_frontiers + hc->n_frontiers / 8 + 1024;
+    s->cell_cap = std::max(s->cell_cap, s->mask_cap);
+    if (hc->overflow & 2u) return fail(c, FITSLAM_E_INVALID, "search_frontiers: wavefront queue overflow");
+  }
+  return fail(c, FITSLAM_E_INVALID, "search_frontiers: buffers still too small after 8 attempts");
+}
+
+const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_t *n_comp, uint32_t *levels, uint32_t *ambiguous) {
+  FrontierState *s = fr_state(c);
+  if (n_cells) *n_cells = s->last.n_cells;
+  if (n_comp) *n_comp = s->last.n_comp;
+  if (levels) *levels = s->last.bfs_levels;
+  if (ambiguous) *ambiguous = s->last.ambiguous;
+  return s->cells.p;
+}
+
+}  // namespace fitslam
+
+using namespace fitslam;
+
+extern "C" {
+
+fitslam_status fitslam_set_search_distance(fitslam_ctx *c, double max_frontier_distance) {
+  if (!c || !(max_frontier_distance >= 0.0)) return fail(c, FITSLAM_E_INVALID, "set_search_distance: bad argument");
+  fr_state(c)->search_distance = max_frontier_distance;  // incrementSearchDistance / resetSearchDistance (FrontierSearch.hpp:39-52)
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_search_frontiers(fitslam_ctx *c, double robot_x, double robot_y, fitslam_frontier *out,
+                                        uint32_t *n_frontiers, uint32_t *every_cells, uint32_t *n_cells) {
+  if (!c || !n_frontiers) return fail(c, FITSLAM_E_INVALID, "search_frontiers: null argument");
+  cudaSetDevice(c->device);
+  const uint32_t cap = *n_frontiers;
+  const uint32_t ccap = n_cells ? *n_cells : 0;
+  *n_frontiers = 0;
+  if (n_cells) *n_cells = 0;
+  fitslam_status st = frontier_search_device(c, robot_x, robot_y);
+  if (st != FITSLAM_OK) return st;
+  FrontierState *s = c->fs;
+  const uint32_t F = s->last.n_frontiers, NC = s->last.n_cells;
+  *n_frontiers = F;
+  if (n_cells) *n_cells = NC;
+  st = FITSLAM_OK;
+  if (out) {
+    if (F > cap) st = fail(c, FITSLAM_E_CAPACITY, "search_frontiers: frontier buffer too small");
+    const uint32_t m = std::min(F, cap);
+    if (m) FS_CUDA(c, cudaMemcpyAsync(out, c->frontiers.p, (size_t)m * sizeof(fitslam_frontier), cudaMemcpyDefault, c->stream));
+  }
+  if (every_cells) {
+    if (NC > ccap) st = fail(c, FITSLAM_E_CAPACITY, "search_frontiers: cell buffer too small");
+    const uint32_t m = std::min(NC, ccap);
+    if (m) FS_CUDA(c, cudaMemcpyAsync(every_cells, s->cells.p, (size_t)m * 4, cudaMemcpyDefault, c->stream));
+  }
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return st;
+}
+
+}  // extern "C"

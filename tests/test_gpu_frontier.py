@@ -1,0 +1,104 @@
+"""Stage S parity: FrontierSearch::searchFrom on the GPU vs the oracle.  Everything is integer or exact-grid data,
+so the bar is bit-exact: frontier list (goal cell, goal point, size, component, chunk, offsets) in discovery order
+and the every_frontier cell list in acceptance order."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(capi, oracle, a, meta, rx, ry, ov=None, expect_frontiers=True):
+    params = capi.default_params()
+    for k, v in (ov or {}).items():
+        setattr(params, k, v)
+        setattr(oracle.params, k, v)
+    wst, wfr, wcells, wseeds, wcent = oracle.search_frontiers(a, meta, rx, ry, capacity=1 << 18, cell_capacity=1 << 23)
+    ctx = capi.Context(params)
+    try:
+        ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        for _ in range(2):  # twice: the second run must find the claim array clean
+            st, fr, cells = ctx.search_frontiers(rx, ry, capacity=1 << 18, cell_capacity=1 << 23)
+            assert st == wst
+            assert len(cells) == len(wcells)
+            np.testing.assert_array_equal(cells, wcells)
+            assert len(fr) == len(wfr)
+            for f in ("goal_mx", "goal_my", "size", "component", "chunk", "first_cell"):
+                np.testing.assert_array_equal(fr[f], wfr[f], err_msg=f)
+            np.testing.assert_array_equal(fr["goal_x"].view(np.uint64), wfr["goal_x"].view(np.uint64))
+            np.testing.assert_array_equal(fr["goal_y"].view(np.uint64), wfr["goal_y"].view(np.uint64))
+        if expect_frontiers:
+            assert len(fr) > 0
+        return fr, cells
+    finally:
+        ctx.close()
+
+
+@pytest.mark.parametrize("name", ["C1", "C3", "C2"])
+def test_search_matches_oracle_on_config(capi, oracle, synth, name):
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], ov)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_search_inflated_maps_small_radius(capi, oracle, synth, seed):
+    # inflation ring (costs 1..253: traversable < 254 but lethal >= 160), search radius smaller than the explored
+    # region (cells beyond it are visited but not expanded), odd map width (pitch != W, partial mask words)
+    a, meta = synth.make_costmap(1001, 777, seed=seed, n_disc=14, r_lo=25, r_hi=70, n_holes=30, inflation=5)
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], dict(max_frontier_distance=6.0 + seed))
+
+
+def test_search_cluster_size_parameters(capi, oracle, synth):
+    a, meta = synth.make_costmap(800, 800, seed=5, n_disc=10, r_lo=30, r_hi=80, n_holes=20)
+    for mn, mx in ((1, 20), (3, 7), (0, 40), (5, 62)):
+        _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"],
+                 dict(min_frontier_cluster_size=mn, max_frontier_cluster_size=mx))
+
+
+def test_search_strip_and_map_border(capi, oracle):
+    # the 60-cell strip of tests/test_oracle_micro.py, and a frontier running along the map border
+    W, H = 80, 9
+    a = np.full((H, W), 254, np.uint8)
+    a[3, 10:70] = 0
+    a[4, 10:70] = 255
+    a[5, 10:70] = 255
+    a[4, 9] = a[4, 70] = 255
+    meta = dict(res=0.05, ox=0.0, oy=0.0)
+    fr, cells = _compare(capi, oracle, a, meta, (10 + 0.5) * 0.05, (3 + 0.5) * 0.05)
+    assert sorted(fr["size"].tolist(), reverse=True) == [21, 21, 18]
+    b = np.full((40, 50), 255, np.uint8)
+    b[1:39, 1:49] = 0          # free interior, unknown ring on the border rows/columns
+    b[10:12, 20:30] = 254
+    _compare(capi, oracle, b, dict(res=0.1, ox=-2.5, oy=-2.0), 0.0, 0.0)
+
+
+def test_search_robot_on_lethal_or_unknown_cell(capi, oracle, synth):
+    a, meta = synth.make_costmap(600, 600, seed=11, n_disc=8, r_lo=30, r_hi=70, n_holes=10)
+    cx, cy = 300, 300
+    a[cy - 4:cy + 5, cx - 4:cx + 5] = 254   # nearestFreeCell has to walk out of a lethal block
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"])
+    a[cy - 4:cy + 5, cx - 4:cx + 5] = 255
+    a[cy + 3, cx - 2] = 200                  # a non-free (>= lethal_threshold) traversable cell is not "free"
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"])
+
+
+def test_search_out_of_bounds_and_empty(capi, oracle):
+    a = np.zeros((64, 64), np.uint8)
+    meta = dict(res=0.05, ox=0.0, oy=0.0)
+    ctx = capi.Context()
+    ctx.set_costmap(a, 0.05, 0.0, 0.0)
+    st, fr, cells = ctx.search_frontiers(-1.0, 1.0)
+    assert st == capi.E_ROBOT_OUT_OF_BOUNDS and len(fr) == 0
+    st, fr, cells = ctx.search_frontiers(1.0, 64 * 0.05 + 0.01)
+    assert st == capi.E_ROBOT_OUT_OF_BOUNDS
+    ctx.close()
+    _compare(capi, oracle, a, meta, 1.0, 1.0, expect_frontiers=False)  # fully known map: no frontier at all
+
+
+def test_search_random_noise_maps(capi, oracle):
+    # adversarial: salt-and-pepper maps make many tiny components and many same-level ties in the wavefront
+    rng = np.random.default_rng(4)
+    for W, H in ((97, 61), (256, 200)):
+        a = rng.choice(np.array([0, 255, 254, 100, 200], np.uint8), size=(H, W), p=[0.55, 0.3, 0.05, 0.05, 0.05])
+        a[H // 2, W // 2] = 0
+        meta = dict(res=0.05, ox=-1.0, oy=2.0)
+        _compare(capi, oracle, a, meta, meta["ox"] + (W // 2 + 0.5) * 0.05, meta["oy"] + (H // 2 + 0.5) * 0.05)
