@@ -268,11 +268,16 @@ __global__ void uf_merge_kernel(const SearchParams S, const uint32_t *__restrict
     }
   }
 }
-// flatten: parent[i] = root; rsize[root] = number of cells
+// flatten: parent[i] = root; rsize[root] = number of cells.  The walk is read-only: a path-halving store from a
+// thread passing through i could land after i's own "parent[i] = root" and leave a non-root there.
 __global__ void uf_compress_kernel(uint32_t *parent, uint32_t *rsize, const Counters *cnt, uint32_t cap) {
   const uint32_t n = min(cnt->n_mask, cap);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t r = uf_find(parent, i);
+    uint32_t r = i, p = ld_cg(parent + r);
+    while (p != r) {  // every value ever stored in parent[x] is an ancestor of x, so this ends at the root
+      r = p;
+      p = ld_cg(parent + r);
+    }
     parent[i] = r;
     atomicAdd(rsize + r, 1u);
   }
