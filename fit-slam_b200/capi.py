@@ -85,6 +85,8 @@ PROTOTYPES = {
     "fitslam_normalise_select": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp, _vp,
                                            C.POINTER(Selection)]),
     "fitslam_cycle": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, C.POINTER(CycleResult)]),
+    "fitslam_cycle_begin": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, _u32p]),
+    "fitslam_cycle_end": (C.c_int, [_vp, C.POINTER(CycleResult)]),
     "fitslam_cycle_fetch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint32]),
     "fitslam_score_records": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
 }
@@ -258,6 +260,18 @@ class Context:
                          allow=(E_ROBOT_OUT_OF_BOUNDS, E_NO_FRONTIERS))
         return st, res
 
+    def cycle_begin(self, rx, ry, ryaw, poly, fisher_mode=FISHER_OFF):
+        n = C.c_uint32()
+        poly = np.asarray(poly, dtype=np.float64)
+        st = self._check(self.lib.fitslam_cycle_begin(self.h, rx, ry, ryaw, _ptr(poly), fisher_mode, C.byref(n)),
+                         allow=(E_ROBOT_OUT_OF_BOUNDS, E_NO_FRONTIERS))
+        return st, n.value
+
+    def cycle_end(self):
+        res = CycleResult()
+        self._check(self.lib.fitslam_cycle_end(self.h, C.byref(res)))
+        return res
+
     def cycle_fetch(self, n):
         fr = np.zeros(n, dtype=FRONTIER_DTYPE)
         ar = np.zeros(n, dtype=ARRIVAL_DTYPE)
@@ -267,6 +281,15 @@ class Context:
         self._check(self.lib.fitslam_cycle_fetch(self.h, _ptr(fr), _ptr(ar), _ptr(pl), _ptr(ph), _ptr(wc), _ptr(fi),
                                                  _ptr(srt), n))
         return dict(frontiers=fr, arrival=ar, path_length_m=pl, path_heading=ph, weighted_cost=wc, fisher=fi, sorted=srt)
+
+    def records_tensor(self):
+        """Zero-copy torch view (int32, [nranks * B, 4]) of the device score records, for the NCCL all-gather."""
+        import torch
+        ptr, nbytes = self.score_records()
+
+        class _Dev:
+            __cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+        return torch.as_tensor(_Dev(), device="cuda").view(-1, 4)
 
     def score_records(self):
         p, b = _vp(), C.c_uint64()

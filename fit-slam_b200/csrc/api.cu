@@ -159,6 +159,7 @@ void fitslam_destroy(fitslam_ctx *c) {
   destroy_frontier_state(c);
   destroy_fisher_state(c);
   destroy_select_state(c);
+  destroy_cycle_state(c);
   c->map.release();
   c->ray_dxdy.release();
   c->frontiers.release();
@@ -279,12 +280,13 @@ fitslam_status fitslam_score_arrival(fitslam_ctx *c, const fitslam_frontier *fro
   if (st != FITSLAM_OK) return st;
   const RayShape &s = c->shape;
   FS_CUDA(c, c->arrival.reserve(n));
-  FS_CUDA(c, c->records.reserve(n));
+  const size_t n_rec = (size_t)shard_block(c, n) * c->nranks;  // nranks equal blocks (in-place all-gather layout)
+  FS_CUDA(c, c->records.reserve(n_rec));
   if (info_along_ray) FS_CUDA(c, c->info_ray.reserve((size_t)n * s.n_rays));
   if (window_sums) FS_CUDA(c, c->win_sums.reserve((size_t)n * s.n_windows));
   if (c->nranks > 1) {  // records of the other shards stay zero until the caller merges them
     FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)n * sizeof(fitslam_arrival), c->stream));
-    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)n * sizeof(ScoreRecord), c->stream));
+    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, n_rec * sizeof(ScoreRecord), c->stream));
     if (info_along_ray) FS_CUDA(c, cudaMemsetAsync(c->info_ray.p, 0, (size_t)n * s.n_rays * 2, c->stream));
     if (window_sums) FS_CUDA(c, cudaMemsetAsync(c->win_sums.p, 0, (size_t)n * s.n_windows * 4, c->stream));
   }
@@ -302,7 +304,7 @@ fitslam_status fitslam_score_arrival(fitslam_ctx *c, const fitslam_frontier *fro
 fitslam_status fitslam_score_records(fitslam_ctx *c, void **device_ptr, uint64_t *bytes) {
   if (!c || !device_ptr || !bytes) return fail(c, FITSLAM_E_INVALID, "score_records: null argument");
   *device_ptr = c->records.p;
-  *bytes = (uint64_t)c->n_frontiers * sizeof(ScoreRecord);
+  *bytes = (uint64_t)shard_block(c, c->n_frontiers) * c->nranks * sizeof(ScoreRecord);  // nranks equal blocks
   return FITSLAM_OK;
 }
 

@@ -69,6 +69,7 @@ struct fitslam_ctx {
   cudaStream_t stream = nullptr;
   std::string err;
   uint64_t launches = 0;
+  float last_bfs_ms = 0;  // device time of the outer wavefront kernel in the last search
   int rank = 0, nranks = 1;
 
   // ---- costmap
@@ -134,13 +135,50 @@ inline MapView map_view(const fitslam_ctx *c) {
 }
 
 fitslam_status ensure_pinned(fitslam_ctx *c, size_t bytes);
+// candidate sharding: rank r owns the contiguous block [r * B, min(n, (r + 1) * B)), B = ceil(n / nranks),
+// so the per-frontier score records of all ranks concatenate into one in-place all-gather buffer of nranks * B records
+inline uint32_t shard_block(const fitslam_ctx *c, uint32_t n) { return (n + (uint32_t)c->nranks - 1) / (uint32_t)c->nranks; }
+inline void shard_range(const fitslam_ctx *c, uint32_t n, uint32_t *first, uint32_t *count) {
+  const uint32_t B = shard_block(c, n);
+  const uint64_t lo = (uint64_t)c->rank * B;
+  *first = (uint32_t)(lo < n ? lo : n);
+  *count = lo < n ? (uint32_t)((lo + B < n ? lo + B : n) - lo) : 0u;
+}
 fitslam_status update_ray_shape(fitslam_ctx *c);
 
 void destroy_frontier_state(fitslam_ctx *c);
 void destroy_fisher_state(fitslam_ctx *c);
 void destroy_select_state(fitslam_ctx *c);
+void destroy_cycle_state(fitslam_ctx *c);
+
+// ---- stage N state (select.cu), shared with cycle.cu
+struct SelectMeta {
+  double min_len, max_len, min_info;
+  uint32_t n_eligible;     // achievable && !blacklisted
+  uint32_t n_local_range;  // ... && path_length_m <= LOCAL_FRONTIER_SEARCH_RADIUS
+  uint32_t err_key;        // 2 * index + (0: arrival utility > 1, 1: cost out of bounds); 0xffffffff = none
+  uint32_t pad;
+  fitslam_selection sel;
+};
+struct SelectState {
+  DevBuf<double> len, head, wc, ua, ud;
+  DevBuf<uint8_t> bl, ach;
+  DevBuf<uint32_t> sorted;
+  DevBuf<SelectMeta> meta;
+};
+SelectState *sstate(fitslam_ctx *c);
 
 // stage entry points (each .cu file)
+fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry);
+const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_t *n_comp, uint32_t *levels, uint32_t *ambiguous);
+fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, uint32_t first, uint32_t count,
+                                   float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
+                                   const fitslam_arrival *d_arrival, uint32_t poses_per_frontier);
+bool fisher_ready(const fitslam_ctx *c);
+fitslam_status plan_euclidean_device(fitslam_ctx *c, uint32_t n, const fitslam_frontier *d_fr, const fitslam_arrival *d_arr,
+                                     double rx, double ry, double ryaw);
+fitslam_status select_device(fitslam_ctx *c, uint32_t n, const fitslam_arrival *d_arr, const uint8_t *d_ach,
+                             const uint8_t *d_bl, const double *d_len, const double *d_head);
 fitslam_status raycast_limits(fitslam_ctx *c);
 fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_frontiers, uint32_t n,
                              const double poly[4], fitslam_arrival *d_out, uint16_t *d_info_ray,

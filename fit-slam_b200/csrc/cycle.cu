@@ -1,0 +1,294 @@
+// cycle.cu -- one whole exploration cycle, enqueued back to back on the context stream.
+//
+// The order is the behaviour tree's (FS2/fit_slam2/xml/active_slam_exploration.xml:5-47, DEP/src/ExplorationBT.cpp:166-637):
+//   SearchForFrontiers  -> FrontierSearch::searchFrom                      (frontier.cu)
+//   ProcessFrontierCosts -> setArrivalInformationForFrontier per frontier  (raycast.cu)
+//                         -> setPlanForFrontierEuclidean                   (select.cu)
+//                         -> U1 utility block                              (select.cu)
+//   OptimizeFullPath     -> getFilteredFrontiersN                          (select.cu)
+//   EvaluateFisherInformation -> isPoseSafe, here for every candidate pose (fisher.cu)
+// fitslam_cycle_begin runs everything that shards across GPUs (extraction is replicated, arrival and Fisher are
+// scored for this rank's block of frontiers) and leaves 16-byte score records laid out for an in-place all-gather;
+// fitslam_cycle_end unpacks the merged records and runs the global steps (plan, normalise, select).
+#include "ctx.h"
+
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace fitslam {
+
+struct CycleState {
+  DevBuf<fitslam_pose> poses;
+  DevBuf<float> fisher;        // per pose
+  DevBuf<uint8_t> fisher_safe;
+  DevBuf<uint32_t> fisher_nvis;
+  DevBuf<double> yaw_q;        // per yaw window: qz, qw of orientationAroundZAxis(window * delta_theta + fov / 2)
+  uint32_t yaw_windows = 0;
+  double yaw_dt = 0, yaw_fov = 0;
+  cudaEvent_t ev[8] = {};
+  bool have_events = false;
+  // state carried from cycle_begin to cycle_end
+  bool open = false;
+  double rx = 0, ry = 0, ryaw = 0;
+  int fisher_mode = 0;
+  uint32_t n_poses = 0;
+  fitslam_cycle_result res{};
+};
+
+static CycleState *cstate(fitslam_ctx *c) {
+  if (!c->cy) c->cy = new CycleState();
+  return c->cy;
+}
+
+void destroy_cycle_state(fitslam_ctx *c) {
+  if (!c->cy) return;
+  CycleState *s = c->cy;
+  s->poses.release(); s->fisher.release(); s->fisher_safe.release(); s->fisher_nvis.release(); s->yaw_q.release();
+  if (s->have_events)
+    for (auto &e : s->ev) cudaEventDestroy(e);
+  delete s;
+  c->cy = nullptr;
+}
+
+// Candidate poses at the frontier goals: position = goal point, z = candidate_pose_z, yaw = window *
+// delta_theta + fov / 2 for every window (ppf = n_windows) or for the best window only (ppf = 1), i.e. what
+// setGoalOrientation produces (DEP/src/Frontier.cpp:50-56).  A frontier whose ray fan failed has orientation 0.
+__global__ void make_poses_kernel(const fitslam_frontier *__restrict__ fr, const fitslam_arrival *__restrict__ arr,
+                                  const double *__restrict__ yaw_q, uint32_t first_f, uint32_t count_f, uint32_t ppf,
+                                  double z, fitslam_pose *poses) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count_f * ppf) return;
+  const uint32_t f = first_f + i / ppf, w = i % ppf;
+  const uint32_t win = ppf == 1 ? (uint32_t)arr[f].max_index : w;
+  fitslam_pose p;
+  p.x = fr[f].goal_x;
+  p.y = fr[f].goal_y;
+  p.z = z;
+  p.qx = 0.0;
+  p.qy = 0.0;
+  if (ppf == 1 && arr[f].ray_failed) {
+    p.qz = 0.0;
+    p.qw = 1.0;
+  } else {
+    p.qz = yaw_q[2 * win];
+    p.qw = yaw_q[2 * win + 1];
+  }
+  poses[(size_t)f * ppf + w] = p;
+}
+
+// merged 16-byte records -> fitslam_arrival (the part of the record that other ranks scored)
+__global__ void unpack_records_kernel(const ScoreRecord *__restrict__ rec, fitslam_arrival *arr, uint32_t n, double dt,
+                                      double half_fov) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const ScoreRecord r = rec[i];
+  fitslam_arrival a;
+  memset(&a, 0, sizeof(a));
+  a.information = r.information;
+  a.max_index = r.max_index;
+  a.achievable = r.flags & 1u;
+  a.footprint_in_lethal = (r.flags >> 1) & 1u;
+  a.ray_failed = (r.flags >> 2) & 1u;
+  a.theta_s_star = a.ray_failed ? 0.0 : ((double)r.max_index * dt) + half_fov;
+  arr[i] = a;
+}
+
+__global__ void gather_fisher_kernel(const ScoreRecord *__restrict__ rec, float *out, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = rec[i].fisher;
+}
+
+static fitslam_status ensure_yaw_table(fitslam_ctx *c, CycleState *s) {
+  const uint32_t nw = c->shape.n_windows;
+  if (s->yaw_windows == nw && s->yaw_dt == c->prm.delta_theta && s->yaw_fov == c->prm.camera_fov) return FITSLAM_OK;
+  std::vector<double> q(2 * (size_t)nw);
+  for (uint32_t w = 0; w < nw; ++w) {
+    const double theta = (w * c->prm.delta_theta) + (c->prm.camera_fov / 2);  // DEP/src/CostCalculator.cpp:119
+    // tf2::Quaternion::setRPY(0, 0, theta) (nav2_util::geometry_utils::orientationAroundZAxis)
+    const double halfYaw = theta * 0.5, cosYaw = cos(halfYaw), sinYaw = sin(halfYaw);
+    const double cosPitch = cos(0.0), sinPitch = sin(0.0), cosRoll = cos(0.0), sinRoll = sin(0.0);
+    q[2 * w] = cosRoll * cosPitch * sinYaw - sinRoll * sinPitch * cosYaw;
+    q[2 * w + 1] = cosRoll * cosPitch * cosYaw + sinRoll * sinPitch * sinYaw;
+  }
+  FS_CUDA(c, s->yaw_q.reserve(q.size()));
+  FS_CUDA(c, cudaMemcpyAsync(s->yaw_q.p, q.data(), q.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  s->yaw_windows = nw;
+  s->yaw_dt = c->prm.delta_theta;
+  s->yaw_fov = c->prm.camera_fov;
+  return FITSLAM_OK;
+}
+
+}  // namespace fitslam
+
+using namespace fitslam;
+
+extern "C" {
+
+fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double ryaw, const double poly[4], int fisher_mode,
+                                   uint32_t *n_frontiers) {
+  if (!c) return FITSLAM_E_INVALID;
+  if (n_frontiers) *n_frontiers = 0;
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  if (!poly) return fail(c, FITSLAM_E_NO_POLYGON, "Frontier cannot be selected, no polygon.");
+  if (fisher_mode < FITSLAM_FISHER_OFF || fisher_mode > FITSLAM_FISHER_ALL_YAWS) return fail(c, FITSLAM_E_INVALID, "cycle: bad fisher_mode");
+  cudaSetDevice(c->device);
+  CycleState *s = cstate(c);
+  s->open = false;
+  if (!s->have_events) {
+    for (auto &e : s->ev) FS_CUDA(c, cudaEventCreate(&e));
+    s->have_events = true;
+  }
+  if (fisher_mode != FITSLAM_FISHER_OFF && !fisher_ready(c))
+    return fail(c, c->fi ? FITSLAM_E_NO_MAP_POINTS : FITSLAM_E_NO_LOOKUP_TABLE, "cycle: Fisher stage needs a lookup table and map points");
+  memset(&s->res, 0, sizeof(s->res));
+  s->res.selection.closest_global = -1;
+  fitslam_status st = raycast_limits(c);  // once per calculator (DEP/src/CostCalculator.cpp:125-129)
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, cudaEventRecord(s->ev[0], c->stream));
+  st = frontier_search_device(c, rx, ry);  // one host sync inside: the list sizes decide the next launches
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, cudaEventRecord(s->ev[1], c->stream));
+  const uint32_t F = c->n_frontiers;
+  uint32_t n_cells = 0, n_comp = 0, levels = 0, ambiguous = 0;
+  frontier_cells_device(c, &n_cells, &n_comp, &levels, &ambiguous);
+  s->res.n_frontiers = F;
+  s->res.n_frontier_cells = n_cells;
+  s->res.n_components = n_comp;
+  s->res.bfs_levels = levels;
+  s->res.ambiguous_sorts = ambiguous;
+  if (n_frontiers) *n_frontiers = F;
+  if (F == 0) return fail(c, FITSLAM_E_NO_FRONTIERS, "No frontiers found from frontier search.");
+  // ---- arrival information for this rank's block of frontiers
+  const uint32_t B = shard_block(c, F);
+  FS_CUDA(c, c->arrival.reserve(F));
+  FS_CUDA(c, c->records.reserve((size_t)B * c->nranks));
+  if (c->nranks > 1) {
+    FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)F * sizeof(fitslam_arrival), c->stream));
+    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)B * c->nranks * sizeof(ScoreRecord), c->stream));
+  }
+  st = raycast_score(c, c->frontiers.p, F, poly, c->arrival.p, nullptr, nullptr, c->records.p);
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, cudaEventRecord(s->ev[2], c->stream));
+  s->res.n_candidates = F * c->shape.n_windows;
+  // ---- Fisher information of the candidate poses of the same block
+  s->n_poses = 0;
+  if (fisher_mode != FITSLAM_FISHER_OFF) {
+    st = ensure_yaw_table(c, s);
+    if (st != FITSLAM_OK) return st;
+    const uint32_t ppf = fisher_mode == FITSLAM_FISHER_ALL_YAWS ? c->shape.n_windows : 1u;
+    const uint64_t n_poses = (uint64_t)F * ppf;
+    if (n_poses >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "cycle: too many candidate poses");
+    uint32_t first_f = 0, count_f = F;
+    shard_range(c, F, &first_f, &count_f);
+    FS_CUDA(c, s->poses.reserve(n_poses));
+    FS_CUDA(c, s->fisher.reserve(n_poses));
+    FS_CUDA(c, s->fisher_safe.reserve(n_poses));
+    FS_CUDA(c, s->fisher_nvis.reserve(n_poses));
+    if (c->nranks > 1) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, n_poses * sizeof(float), c->stream));
+    if (count_f) {
+      const uint32_t np = count_f * ppf;
+      make_poses_kernel<<<(np + 255) / 256, 256, 0, c->stream>>>(c->frontiers.p, c->arrival.p, s->yaw_q.p, first_f, count_f, ppf,
+                                                                c->prm.candidate_pose_z, s->poses.p);
+      ++c->launches;
+      st = fisher_score_device(c, s->poses.p, (uint32_t)n_poses, first_f * ppf, np, s->fisher.p, s->fisher_safe.p,
+                               s->fisher_nvis.p, c->records.p, c->arrival.p, ppf);
+      if (st != FITSLAM_OK) return st;
+    }
+    s->n_poses = (uint32_t)n_poses;
+    s->res.n_fisher_poses = (uint32_t)n_poses;
+  }
+  FS_CUDA(c, cudaEventRecord(s->ev[3], c->stream));
+  FS_CUDA(c, cudaGetLastError());
+  s->rx = rx; s->ry = ry; s->ryaw = ryaw;
+  s->fisher_mode = fisher_mode;
+  s->open = true;
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_cycle_end(fitslam_ctx *c, fitslam_cycle_result *result) {
+  if (!c) return FITSLAM_E_INVALID;
+  CycleState *s = cstate(c);
+  if (!s->open) return fail(c, FITSLAM_E_INVALID, "cycle_end without a successful cycle_begin");
+  s->open = false;
+  cudaSetDevice(c->device);
+  const uint32_t F = c->n_frontiers;
+  FS_CUDA(c, cudaEventRecord(s->ev[4], c->stream));
+  if (c->nranks > 1) {  // the caller has all-gathered the records: rebuild every frontier's arrival fields from them
+    unpack_records_kernel<<<(F + 255) / 256, 256, 0, c->stream>>>(c->records.p, c->arrival.p, F, c->prm.delta_theta,
+                                                                  c->prm.camera_fov / 2);
+    ++c->launches;
+  }
+  fitslam_status st = plan_euclidean_device(c, F, c->frontiers.p, c->arrival.p, s->rx, s->ry, s->ryaw);
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, cudaEventRecord(s->ev[5], c->stream));
+  SelectState *ss = sstate(c);
+  st = select_device(c, F, c->arrival.p, ss->ach.p, nullptr, ss->len.p, ss->head.p);
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, cudaEventRecord(s->ev[6], c->stream));
+  st = ensure_pinned(c, sizeof(SelectMeta));
+  if (st != FITSLAM_OK) return st;
+  SelectMeta *m = reinterpret_cast<SelectMeta *>(c->pinned);
+  FS_CUDA(c, cudaMemcpyAsync(m, ss->meta.p, sizeof(SelectMeta), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  s->res.selection = m->sel;
+  float ms = 0;
+  const int pairs[7][2] = {{0, 1}, {1, 2}, {4, 5}, {2, 3}, {5, 6}, {0, 3}, {4, 6}};
+  for (int i = 0; i < 7; ++i) {
+    FS_CUDA(c, cudaEventElapsedTime(&ms, s->ev[pairs[i][0]], s->ev[pairs[i][1]]));
+    s->res.stage_ms[i] = ms;  // extract, arrival, distance, fisher, normalise+select, begin total, end total
+  }
+  s->res.stage_ms[7] = c->last_bfs_ms;  // the outer wavefront kernel alone (inside stage 0)
+  if (result) *result = s->res;
+  if (m->err_key != 0xffffffffu) {
+    const bool arrival = (m->err_key & 1u) == 0;
+    return fail(c, arrival ? FITSLAM_E_ARRIVAL_UTILITY : FITSLAM_E_COST_OUT_OF_BOUNDS,
+                std::string(arrival ? "ARRIVAL UTILITY ERROR! MORE THAN 1" : "Cost out of bounds") + " (frontier " +
+                    std::to_string(m->err_key >> 1) + ")");
+  }
+  return FITSLAM_OK;
+}
+
+fitslam_status fitslam_cycle(fitslam_ctx *c, double rx, double ry, double ryaw, const double poly[4], int fisher_mode,
+                             fitslam_cycle_result *result) {
+  uint32_t F = 0;
+  fitslam_status st = fitslam_cycle_begin(c, rx, ry, ryaw, poly, fisher_mode, &F);
+  if (st != FITSLAM_OK) {
+    if (result && c && c->cy) *result = c->cy->res;
+    return st;
+  }
+  return fitslam_cycle_end(c, result);
+}
+
+fitslam_status fitslam_cycle_fetch(fitslam_ctx *c, fitslam_frontier *frontiers, fitslam_arrival *arrival, double *path_length_m,
+                                   double *path_heading, double *weighted_cost, float *fisher_info, uint32_t *sorted,
+                                   uint32_t capacity) {
+  if (!c || !c->cy) return fail(c, FITSLAM_E_INVALID, "cycle_fetch before fitslam_cycle");
+  cudaSetDevice(c->device);
+  CycleState *s = c->cy;
+  SelectState *ss = sstate(c);
+  const uint32_t F = c->n_frontiers;
+  if (capacity < F) return fail(c, FITSLAM_E_CAPACITY, "cycle_fetch: buffers too small");
+  if (F == 0) return FITSLAM_OK;
+  if (frontiers) FS_CUDA(c, cudaMemcpyAsync(frontiers, c->frontiers.p, (size_t)F * sizeof(fitslam_frontier), cudaMemcpyDefault, c->stream));
+  if (arrival) FS_CUDA(c, cudaMemcpyAsync(arrival, c->arrival.p, (size_t)F * sizeof(fitslam_arrival), cudaMemcpyDefault, c->stream));
+  if (path_length_m) FS_CUDA(c, cudaMemcpyAsync(path_length_m, ss->len.p, (size_t)F * 8, cudaMemcpyDefault, c->stream));
+  if (path_heading) FS_CUDA(c, cudaMemcpyAsync(path_heading, ss->head.p, (size_t)F * 8, cudaMemcpyDefault, c->stream));
+  if (weighted_cost) FS_CUDA(c, cudaMemcpyAsync(weighted_cost, ss->wc.p, (size_t)F * 8, cudaMemcpyDefault, c->stream));
+  if (fisher_info) {  // Fisher information of each frontier's best-yaw pose, from the (merged) records; 0 when the stage was off
+    FS_CUDA(c, s->fisher.reserve(F));
+    float *tmp = nullptr;
+    FS_CUDA(c, cudaMallocAsync((void **)&tmp, (size_t)F * 4, c->stream));
+    gather_fisher_kernel<<<(F + 255) / 256, 256, 0, c->stream>>>(c->records.p, tmp, F);
+    ++c->launches;
+    FS_CUDA(c, cudaMemcpyAsync(fisher_info, tmp, (size_t)F * 4, cudaMemcpyDefault, c->stream));
+    FS_CUDA(c, cudaFreeAsync(tmp, c->stream));
+  }
+  if (sorted && s->res.selection.n_sorted)
+    FS_CUDA(c, cudaMemcpyAsync(sorted, ss->sorted.p, (size_t)s->res.selection.n_sorted * 4, cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}
+
+}  // extern "C"

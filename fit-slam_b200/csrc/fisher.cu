@@ -541,7 +541,8 @@ struct FisherParams {
   double threshold;
   float fx, fy, cx, cy, max_u, max_v;
   uint32_t n_poses;
-  int rank, nranks;
+  uint32_t first;       // this launch scores poses [first, first + gridDim.x)
+  uint32_t poses_per_frontier;  // record f = pose / poses_per_frontier (cycle mode)
 };
 
 struct PoseFrame {      // per-CTA, built by thread 0
@@ -638,15 +639,14 @@ __device__ __forceinline__ int voxel_of_point(const float4 q, const PoseFrame &F
 __global__ void __launch_bounds__(FISHER_THREADS)
 fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, float *__restrict__ info_out,
               uint8_t *__restrict__ safe_out, uint32_t *__restrict__ nvis_out, ScoreRecord *__restrict__ rec_out,
-              uint32_t rec_stride) {
+              const fitslam_arrival *__restrict__ arrival) {
   __shared__ PoseFrame F;
   __shared__ uint32_t keys[HASH_SLOTS];
   __shared__ uint32_t cnts[HASH_SLOTS];
   __shared__ uint32_t s_used, s_overflow;
   __shared__ double s_red[FISHER_THREADS / 32];
-  const uint64_t pi64 = (uint64_t)P.rank + (uint64_t)blockIdx.x * (uint64_t)P.nranks;
-  if (pi64 >= P.n_poses) return;
-  const uint32_t pi = (uint32_t)pi64;
+  const uint32_t pi = P.first + blockIdx.x;
+  if (pi >= P.n_poses) return;
   if (threadIdx.x == 0) build_pose_frame(poses[pi], P, F);
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5, nw = FISHER_THREADS / 32;
@@ -736,20 +736,26 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
     if (info_out) info_out[pi] = information;
     if (safe_out) safe_out[pi] = is_safe ? 1 : 0;
     if (nvis_out) nvis_out[pi] = used;
-    if (rec_out) {
-      ScoreRecord *r = rec_out + (size_t)pi * rec_stride;
-      r->fisher = information;
-      r->flags |= 8u | (is_safe ? 16u : 0u);
+    if (rec_out) {  // the frontier's record carries the Fisher information of its best-yaw pose
+      const uint32_t f = pi / P.poses_per_frontier, w = pi - f * P.poses_per_frontier;
+      if (P.poses_per_frontier == 1 || (int32_t)w == arrival[f].max_index) {
+        rec_out[f].fisher = information;
+        rec_out[f].flags |= 8u | (is_safe ? 16u : 0u);
+      }
     }
   }
 }
 
-fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, float *d_info, uint8_t *d_safe,
-                                   uint32_t *d_nvis, ScoreRecord *d_rec, uint32_t rec_stride, bool shard) {
+bool fisher_ready(const fitslam_ctx *c) { return c->fi && c->fi->have_lut && c->fi->have_points; }
+
+// Scores poses [first, first + count) of the n resident poses.
+fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, uint32_t first, uint32_t count,
+                                   float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
+                                   const fitslam_arrival *d_arrival, uint32_t poses_per_frontier) {
   FisherState *f = c->fi;
   if (!f || !f->have_lut) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
   if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no map points set");
-  if (n == 0) return FITSLAM_OK;
+  if (n == 0 || count == 0) return FITSLAM_OK;
   FisherParams P;
   memset(&P, 0, sizeof(P));
   P.pts = f->pts.p;
@@ -767,11 +773,9 @@ fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, 
   P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
   P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
   P.n_poses = n;
-  P.rank = shard ? c->rank : 0;
-  P.nranks = shard ? c->nranks : 1;
-  const uint32_t n_local = (n > (uint32_t)P.rank) ? (n - P.rank + P.nranks - 1) / P.nranks : 0;
-  if (n_local == 0) return FITSLAM_OK;
-  fisher_kernel<<<n_local, FISHER_THREADS, 0, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, rec_stride);
+  P.first = first;
+  P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
+  fisher_kernel<<<count, FISHER_THREADS, 0, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, d_arrival);
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
   return FITSLAM_OK;
@@ -797,7 +801,9 @@ extern "C" fitslam_status fitslam_score_fisher(fitslam_ctx *c, const fitslam_pos
     FS_CUDA(c, cudaMemsetAsync(f->safe.p, 0, n, c->stream));
     FS_CUDA(c, cudaMemsetAsync(f->nvis.p, 0, (size_t)n * 4, c->stream));
   }
-  fitslam_status st = fisher_score_device(c, f->poses.p, n, f->info.p, f->safe.p, f->nvis.p, nullptr, 0, true);
+  uint32_t first = 0, count = n;
+  shard_range(c, n, &first, &count);
+  fitslam_status st = fisher_score_device(c, f->poses.p, n, first, count, f->info.p, f->safe.p, f->nvis.p, nullptr, nullptr, 1);
   if (st != FITSLAM_OK) return st;
   if (information) FS_CUDA(c, cudaMemcpyAsync(information, f->info.p, (size_t)n * 4, cudaMemcpyDefault, c->stream));
   if (safe) FS_CUDA(c, cudaMemcpyAsync(safe, f->safe.p, n, cudaMemcpyDefault, c->stream));

@@ -84,6 +84,9 @@ struct FrontierState {
   uint64_t claim_cells = 0;   // cells for which claim is known to be all KEY_INF
   uint32_t mask_cap = 0, queue_cap = 0, comp_cap = 0, cell_cap = 0, front_cap = 0;
   Counters last{};
+  cudaEvent_t ev_bfs[3] = {};  // around rank_bfs_kernel and replay_kernel (bench roofline of the dominant kernel)
+  bool have_ev = false;
+  float bfs_ms = 0, replay_ms = 0;
 };
 
 static FrontierState *fr_state(fitslam_ctx *c) {
@@ -97,6 +100,8 @@ void destroy_frontier_state(fitslam_ctx *c) {
   s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->mcell.release();
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
+  if (s->have_ev)
+    for (auto &e : s->ev_bfs) cudaEventDestroy(e);
   s->oseed.release(); s->osize.release(); s->ocell0.release(); s->ofront0.release();
   s->cells.release(); s->centroids.release(); s->counters.release();
   delete s;
@@ -959,7 +964,13 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   uf_init_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rkey.p, s->rsize.p, cnt, S.mask_cap);
   uf_merge_kernel<<<wide, 256, 0, c->stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
   uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, cnt, S.mask_cap);
+  if (!s->have_ev) {
+    for (auto &e : s->ev_bfs) FS_CUDA(c, cudaEventCreate(&e));
+    s->have_ev = true;
+  }
+  FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
   rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);
+  FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
   touch_reduce_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, cnt);
   seed_collect_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->ckey.p,
                                                     s->cseed.p, s->csize.p, cnt);
@@ -967,6 +978,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   comp_scan_kernel<<<1, 1024, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, cnt);
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
                                                             s->cells.p, cnt);
+  FS_CUDA(c, cudaEventRecord(s->ev_bfs[2], c->stream));
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
                                                s->centroids.p, cnt);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
@@ -997,6 +1009,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
     if (st != FITSLAM_OK) return st;
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
     s->last = *hc;
+    cudaEventElapsedTime(&s->bfs_ms, s->ev_bfs[0], s->ev_bfs[1]);
     if (!hc->overflow) {
       c->n_frontiers = hc->n_frontiers;
       return FITSLAM_OK;
@@ -1018,6 +1031,7 @@ const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_
   if (n_comp) *n_comp = s->last.n_comp;
   if (levels) *levels = s->last.bfs_levels;
   if (ambiguous) *ambiguous = s->last.ambiguous;
+  c->last_bfs_ms = s->bfs_ms;
   return s->cells.p;
 }
 

@@ -13,6 +13,9 @@ void destroy_fisher_state(fitslam_ctx *) {}
 #ifndef HAVE_SELECT
 void destroy_select_state(fitslam_ctx *) {}
 #endif
+#ifndef HAVE_CYCLE
+void destroy_cycle_state(fitslam_ctx *) {}
+#endif
 }
 extern "C" {
 #ifndef HAVE_FRONTIER
@@ -32,6 +35,8 @@ fitslam_status fitslam_normalise_select(fitslam_ctx *c, const double *, const do
 #endif
 #ifndef HAVE_CYCLE
 fitslam_status fitslam_cycle(fitslam_ctx *c, double, double, double, const double *, int, fitslam_cycle_result *) { NOT_IMPL(c); }
+fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double, double, double, const double *, int, uint32_t *) { NOT_IMPL(c); }
+fitslam_status fitslam_cycle_end(fitslam_ctx *c, fitslam_cycle_result *) { NOT_IMPL(c); }
 fitslam_status fitslam_cycle_fetch(fitslam_ctx *c, fitslam_frontier *, fitslam_arrival *, double *, double *, double *, float *, uint32_t *, uint32_t) { NOT_IMPL(c); }
 #endif
 }

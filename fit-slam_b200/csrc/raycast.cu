@@ -62,7 +62,7 @@ struct RayParams {
   uint32_t fpb;             // frontiers per block
   uint32_t tile_stride;     // bytes between the windows of two frontiers (multiple of 128)
   uint32_t n;               // frontiers in the list
-  int rank, nranks;         // shard: frontier f is scored iff f % nranks == rank
+  uint32_t first, count;    // shard: this launch scores frontiers [first, first + count)
 };
 
 // Costmap2D::worldToMap (nav2_costmap_2d, ROS 2 Humble)
@@ -133,10 +133,9 @@ raycast_kernel(const RayParams P, const fitslam_frontier *__restrict__ fr,
   int32_t *flags_all = reinterpret_cast<int32_t *>(wscr_all + (size_t)P.fpb * 32);
   int32_t *gflag = flags_all + g * 2;  // [0] any ray failed, [1] footprint in lethal
 
-  const uint64_t slot = (uint64_t)blockIdx.x * P.fpb + g;
-  const uint64_t f64 = (uint64_t)P.rank + slot * (uint64_t)P.nranks;
-  const bool live = f64 < P.n;
-  const uint32_t f = live ? (uint32_t)f64 : 0u;
+  const uint32_t slot = blockIdx.x * P.fpb + g;
+  const bool live = slot < P.count;
+  const uint32_t f = live ? P.first + slot : 0u;
 
   double sx = 0.0, sy = 0.0;
   int fsize = 0;
@@ -344,8 +343,7 @@ static RayParams make_params(fitslam_ctx *c, const double poly[4], uint32_t n) {
   P.tpf = (std::max(c->shape.n_rays, 32u) + 31u) & ~31u;
   P.tile_stride = (P.tile_w * P.tile_h + 127u) & ~127u;
   P.n = n;
-  P.rank = c->rank;
-  P.nranks = c->nranks;
+  shard_range(c, n, &P.first, &P.count);
   return P;
 }
 
@@ -388,7 +386,7 @@ fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_fr, uint3
   while (fpb > 1 && (size_t)fpb * P.tile_stride > 96 * 1024) --fpb;
   P.fpb = fpb;
   const size_t smem = smem_bytes(P, tma);
-  const uint32_t n_local = (n > (uint32_t)c->rank) ? (n - c->rank + c->nranks - 1) / c->nranks : 0;
+  const uint32_t n_local = P.count;
   if (n_local == 0) return FITSLAM_OK;
   const uint32_t grid = (n_local + fpb - 1) / fpb;
   const uint32_t block = fpb * P.tpf;

@@ -17,22 +17,6 @@
 
 namespace fitslam {
 
-struct SelectMeta {
-  double min_len, max_len, min_info;
-  uint32_t n_eligible;   // achievable && !blacklisted
-  uint32_t n_local_range;  // ... && path_length_m <= LOCAL_FRONTIER_SEARCH_RADIUS
-  uint32_t err_key;      // 2 * index + (0: arrival utility > 1, 1: cost out of bounds); 0xffffffff = none
-  uint32_t pad;
-  fitslam_selection sel;
-};
-
-struct SelectState {
-  DevBuf<double> len, head, wc, ua, ud;
-  DevBuf<uint8_t> bl, ach;
-  DevBuf<uint32_t> sorted;
-  DevBuf<SelectMeta> meta;
-};
-
 SelectState *sstate(fitslam_ctx *c) {
   if (!c->sel) c->sel = new SelectState();
   return c->sel;

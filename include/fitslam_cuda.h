@@ -145,7 +145,7 @@ typedef struct fitslam_cycle_result {
   uint32_t ambiguous_sorts;/* chunks whose median sort had two angles within 4 ulp */
   uint32_t _pad;
   fitslam_selection selection;
-  float stage_ms[8];       /* extract, arrival, distance, fisher, normalise+select, 3 spare */
+  float stage_ms[8];       /* extract, arrival, distance, fisher, normalise+select, cycle_begin total, cycle_end total, outer-wavefront kernel alone */
 } fitslam_cycle_result;
 
 enum { FITSLAM_DIST_GIVEN = 0, FITSLAM_DIST_EUCLIDEAN = 1 };
@@ -158,8 +158,8 @@ FITSLAM_API fitslam_status fitslam_create(const fitslam_params *p, int device, f
 FITSLAM_API void fitslam_destroy(fitslam_ctx *ctx);
 FITSLAM_API const char *fitslam_last_error(const fitslam_ctx *ctx);
 FITSLAM_API const char *fitslam_status_string(fitslam_status s);
-/* Restrict the scoring stages to the frontiers f with f % nranks == rank (8e: candidate sharding).
- * Records of the other frontiers are left untouched in the output buffers. */
+/* Restrict the scoring stages to this rank's contiguous block of frontiers, [rank * B, min(F, (rank + 1) * B)) with
+ * B = ceil(F / nranks) (8e: candidate sharding).  Records of the other frontiers are left zero in the output buffers. */
 FITSLAM_API fitslam_status fitslam_set_shard(fitslam_ctx *ctx, int rank, int nranks);
 /* The CUDA stream all work of this context is enqueued on (a cudaStream_t). */
 FITSLAM_API void *fitslam_stream(fitslam_ctx *ctx);
@@ -237,6 +237,14 @@ FITSLAM_API fitslam_status fitslam_normalise_select(fitslam_ctx *ctx, const doub
 FITSLAM_API fitslam_status fitslam_cycle(fitslam_ctx *ctx, double robot_x, double robot_y, double robot_yaw,
                                          const double poly_xy_min_max[4], int fisher_mode,
                                          fitslam_cycle_result *result);
+/* The same cycle in two halves, for candidate sharding across GPUs (8e).  cycle_begin: searchFrom (replicated on
+ * every rank), then arrival information and Fisher information for this rank's block of frontiers
+ * (fitslam_set_shard); the 16-byte score records are left on the device (fitslam_score_records) laid out for an
+ * in-place all-gather.  The caller all-gathers them (NCCL), then cycle_end unpacks the merged records and runs the
+ * global steps: setPlanForFrontierEuclidean, U1, getFilteredFrontiersN.  With one rank, cycle == begin + end. */
+FITSLAM_API fitslam_status fitslam_cycle_begin(fitslam_ctx *ctx, double robot_x, double robot_y, double robot_yaw,
+                                               const double poly_xy_min_max[4], int fisher_mode, uint32_t *n_frontiers);
+FITSLAM_API fitslam_status fitslam_cycle_end(fitslam_ctx *ctx, fitslam_cycle_result *result);
 /* Copy-out of the per-frontier records of the last cycle (any pointer may be NULL). */
 FITSLAM_API fitslam_status fitslam_cycle_fetch(fitslam_ctx *ctx, fitslam_frontier *frontiers,
                                                fitslam_arrival *arrival, double *path_length_m,
@@ -245,8 +253,10 @@ FITSLAM_API fitslam_status fitslam_cycle_fetch(fitslam_ctx *ctx, fitslam_frontie
 
 /* ------------------------------------------------------------------ multi-GPU plumbing (8e) */
 /* Device address + byte size of the packed per-frontier score records of the last scoring call, laid out
- * for an in-place all-gather (record f of rank r lives at index f).  16 bytes per frontier:
- * {int32 information, int32 max_index, float fisher, uint32 flags}. */
+ * for an in-place all-gather: nranks equal blocks of B = ceil(F / nranks) records, rank r's frontiers
+ * [r * B, (r + 1) * B) in block r, so record f lives at index f.  16 bytes per frontier:
+ * {int32 information, int32 max_index, float fisher, uint32 flags (bit0 achievable, bit1 footprint in lethal,
+ * bit2 ray failed, bit3 fisher valid, bit4 fisher safe)}. */
 FITSLAM_API fitslam_status fitslam_score_records(fitslam_ctx *ctx, void **device_ptr, uint64_t *bytes);
 
 #ifdef __cplusplus

@@ -1,0 +1,132 @@
+"""Whole-cycle parity: fitslam_cycle (search -> arrival -> euclidean plan -> Fisher -> U1 -> selection) against the same
+chain on the oracle, and the sharded begin / all-gather / end form against the single-GPU result."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_chain(oracle, synth, a, meta, pts, ryaw, fisher):
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"], capacity=1 << 18,
+                                                         cell_capacity=1 << 23)
+    arr, _, _ = oracle.score_arrival(a, meta, fr, meta["poly"])
+    ach, pl, ph = oracle.plan_euclidean(meta["robot_x"], meta["robot_y"], ryaw, fr, arr["achievable"])
+    max_gt = oracle.arrival_limits(a, meta)[0]
+    st, wc, ua, ud, err = oracle.normalise(arr, ach, pl, ph, None, max_gt)
+    assert st == 0
+    srt, sel = oracle.select(ach, pl)
+    finfo = None
+    if fisher:
+        oracle.fisher_generate()
+        theta = arr["theta_s_star"]
+        poses = synth.frontier_poses(fr, theta, oracle.params.candidate_pose_z)
+        q = np.array([oracle.orientation_around_z(t) for t in theta])
+        poses["qx"], poses["qy"], poses["qz"], poses["qw"] = q.T
+        st, finfo, fsafe, fvis, fused = oracle.fisher_poses(pts, poses)
+    return dict(fr=fr, arr=arr, ach=ach, pl=pl, ph=ph, wc=wc, srt=srt, sel=sel, fisher=finfo, n_cells=len(cells),
+                n_comp=len(seeds))
+
+
+def _check_against(capi, got, res, want, fisher):
+    F = len(want["fr"])
+    assert res.n_frontiers == F and res.n_frontier_cells == want["n_cells"] and res.n_components == want["n_comp"]
+    for f in ("goal_mx", "goal_my", "size", "component", "chunk", "first_cell"):
+        np.testing.assert_array_equal(got["frontiers"][f], want["fr"][f], err_msg=f)
+    for f in ("information", "max_index", "achievable", "footprint_in_lethal", "ray_failed"):
+        np.testing.assert_array_equal(got["arrival"][f], want["arr"][f], err_msg=f)
+    np.testing.assert_array_equal(got["arrival"]["theta_s_star"].view(np.uint64), want["arr"]["theta_s_star"].view(np.uint64))
+    np.testing.assert_array_equal(got["path_length_m"].view(np.uint64), want["pl"].view(np.uint64))  # sqrt: exact
+    # path_heading goes through atan2: device libm is within 2 ulp of glibc's, the U1 block adds a few roundings
+    ok = want["ach"].astype(bool)
+    np.testing.assert_allclose(got["path_heading"][ok], want["ph"][ok], rtol=1e-14, atol=1e-15)
+    np.testing.assert_allclose(got["weighted_cost"], want["wc"], rtol=1e-13)
+    sel, wsel = res.selection, want["sel"]
+    for f in ("n_sorted", "n_local", "global_begin", "n_global", "closest_global"):
+        assert getattr(sel, f) == getattr(wsel, f), f
+    np.testing.assert_array_equal(got["sorted"][:sel.n_sorted], want["srt"])
+    if fisher:
+        w = want["fisher"]
+        assert np.all(np.abs(got["fisher"] - w) <= 1e-4 * np.abs(w) + 1e-6)
+    # ambiguous_sorts counts runs in which two cells' angles are within 4 ulp (device atan2 vs glibc could order them
+    # differently); it is a diagnostic, the goal cells above are what must match
+    assert res.ambiguous_sorts <= max(8, res.n_frontiers // 100)
+
+
+@pytest.mark.parametrize("name,fisher", [("C1", 0), ("C1", 1), ("C3", 0), ("C2", 1)])
+def test_cycle_matches_oracle_chain(capi, oracle, synth, name, fisher):
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    synth.apply_overrides(oracle.params, ov)
+    ryaw = 0.7
+    want = _oracle_chain(oracle, synth, a, meta, pts, ryaw, fisher)
+    ctx = capi.Context(oracle.params)
+    ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+    if fisher:
+        ctx.fisher_generate_lookup()
+        ctx.set_map_points(pts)
+    for _ in range(2):
+        st, res = ctx.cycle(meta["robot_x"], meta["robot_y"], ryaw, meta["poly"], fisher)
+        assert st == 0
+        got = ctx.cycle_fetch(res.n_frontiers)
+        _check_against(capi, got, res, want, fisher)
+    assert sum(res.stage_ms[:5]) > 0
+    ctx.close()
+
+
+def test_cycle_all_yaws_record_is_best_yaw(capi, oracle, synth):
+    a, meta, pts, ov = synth.make_config("C1")  # BASELINE shape: 64 rays, 8 yaw windows
+    synth.apply_overrides(oracle.params, ov)
+    ctx = capi.Context(oracle.params)
+    ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+    ctx.fisher_generate_lookup()
+    ctx.set_map_points(pts)
+    st, r1 = ctx.cycle(meta["robot_x"], meta["robot_y"], 0.0, meta["poly"], capi.FISHER_BEST_YAW)
+    best = ctx.cycle_fetch(r1.n_frontiers)["fisher"].copy()
+    st, r2 = ctx.cycle(meta["robot_x"], meta["robot_y"], 0.0, meta["poly"], capi.FISHER_ALL_YAWS)
+    allyaw = ctx.cycle_fetch(r2.n_frontiers)["fisher"]
+    assert r2.n_fisher_poses == r2.n_frontiers * ctx.ray_shape()[2] and r1.n_fisher_poses == r1.n_frontiers
+    ok = ctx.cycle_fetch(r2.n_frontiers)["arrival"]["ray_failed"] == 0
+    np.testing.assert_array_equal(best[ok], allyaw[ok])
+    ctx.close()
+
+
+@pytest.mark.parametrize("nranks", [2, 3])
+def test_sharded_cycle_equals_single(capi, oracle, synth, nranks):
+    """N ranks emulated in one process on one GPU: each context scores its block, the records are merged the way the
+    NCCL all-gather does (block r from rank r), then every rank finishes and must match the single-context cycle."""
+    import torch
+    a, meta, pts, ov = synth.make_config("C1")
+    synth.apply_overrides(oracle.params, ov)
+    args = (meta["robot_x"], meta["robot_y"], 0.3, meta["poly"], capi.FISHER_BEST_YAW)
+
+    def make(rank, n):
+        c = capi.Context(oracle.params)
+        c.set_shard(rank, n)
+        c.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        c.fisher_generate_lookup()
+        c.set_map_points(pts)
+        return c
+    one = make(0, 1)
+    st, res = one.cycle(*args)
+    want = one.cycle_fetch(res.n_frontiers)
+    ranks = [make(r, nranks) for r in range(nranks)]
+    for c in ranks:
+        st, F = c.cycle_begin(*args)
+        assert st == 0 and F == res.n_frontiers
+    torch.cuda.synchronize()
+    recs = [c.records_tensor() for c in ranks]
+    B = recs[0].shape[0] // nranks
+    merged = torch.cat([recs[r][r * B:(r + 1) * B] for r in range(nranks)])
+    for r, c in enumerate(ranks):
+        own = np.zeros(recs[r].shape[0], bool)
+        own[r * B:(r + 1) * B] = True
+        assert not recs[r][torch.from_numpy(~own).cuda()].any()  # nothing scored outside the rank's block
+        recs[r].copy_(merged)
+    torch.cuda.synchronize()
+    for c in ranks:
+        r2 = c.cycle_end()
+        got = c.cycle_fetch(r2.n_frontiers)
+        for k in ("arrival", "path_length_m", "path_heading", "weighted_cost", "fisher", "sorted"):
+            assert got[k].tobytes() == want[k].tobytes(), k
+        assert bytes(r2.selection) == bytes(res.selection)
+    for c in ranks + [one]:
+        c.close()
