@@ -660,7 +660,11 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
 
   double total = 0.0;
   uint32_t used = 0;
-  for (uint32_t npass = 1; npass <= 4096; npass <<= 1) {
+  // Attempt 1 inserts every contributing landmark into one table.  If the table fills up (more occupied voxels than
+  // slots), the rest of the attempt only counts; the count then sizes a multi-pass run in which pass p owns the voxels
+  // whose hash falls in partition p, so that every pass fits with a load factor <= 1/2.
+  volatile uint32_t *v_overflow = &s_overflow;
+  for (uint32_t npass = 1; npass <= 65536;) {
     total = 0.0;
     if (threadIdx.x == 0) { s_used = 0; s_overflow = 0; }
     for (uint32_t pass = 0; pass < npass; ++pass) {
@@ -700,30 +704,39 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
             const uint32_t h = mix32((uint32_t)vox);
             if (npass > 1 && ((h >> 12) & (npass - 1)) != pass) continue;
             ++my_used;
+            if (*v_overflow) continue;  // this attempt is lost: keep counting only
             uint32_t slot = h & (HASH_SLOTS - 1);
             bool done = false;
-            for (int probe = 0; probe < HASH_SLOTS; ++probe) {
+            for (int probe = 0; probe < 256; ++probe) {
               const uint32_t prev = atomicCAS(&keys[slot], 0u, (uint32_t)vox + 1u);
               if (prev == 0u || prev == (uint32_t)vox + 1u) { atomicAdd(&cnts[slot], 1u); done = true; break; }
               slot = (slot + 1) & (HASH_SLOTS - 1);
             }
-            if (!done) s_overflow = 1;
+            if (!done) *v_overflow = 1;
           }
         }
       }
       if (my_used) atomicAdd(&s_used, my_used);
       __syncthreads();
-      if (s_overflow) break;
-      for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) {
-        const uint32_t k = keys[i];
-        if (k) total += (double)__ldg(P.lut + (k - 1)) * __ldg(P.crowd + min(cnts[i], (uint32_t)CROWD_MAX));
-      }
+      if (s_overflow && npass > 1) break;  // npass == 1: finish the (only) pass so that s_used is the full count
+      if (!s_overflow)
+        for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) {
+          const uint32_t k = keys[i];
+          if (k) total += (double)__ldg(P.lut + (k - 1)) * __ldg(P.crowd + min(cnts[i], (uint32_t)CROWD_MAX));
+        }
       __syncthreads();
     }
     used = s_used;
     const bool ovf = s_overflow != 0;
     __syncthreads();
     if (!ovf) break;
+    if (npass == 1) {  // size the partitioning from the exact count: <= HASH_SLOTS / 2 landmarks per pass on average
+      uint32_t want = 2;
+      while ((uint64_t)want * (HASH_SLOTS / 2) < used) want <<= 1;
+      npass = want;
+    } else {
+      npass <<= 1;  // skewed partitions: halve them again
+    }
   }
   for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
   if (lane == 0) s_red[wid] = total;

@@ -427,7 +427,14 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
     claim[start] = 0;
   }
   __syncthreads();
-  uint32_t base = 0, n = 1, levels = 0;
+  // The current level's cells are mirrored in shared memory (first SQ entries), so that the common narrow level costs
+  // two global round trips (neighbour bits + claims, then the claims of the neighbours' neighbours) instead of three.
+  constexpr uint32_t SQ = 2048;
+  __shared__ uint32_t sq[2][SQ];
+  if (threadIdx.x == 0) sq[0][0] = start;
+  __syncthreads();
+  uint32_t base = 0, n = 1, levels = 0, cur = 0;
+  const int dxs[4] = {-1, 1, 0, 0}, dys[4] = {0, 0, -1, 1};
   while (n > 0) {
     const uint32_t next_base = base + n;
     uint32_t n_next = 0;
@@ -435,61 +442,81 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
       const uint32_t i = tile + threadIdx.x;
       uint32_t win[4];
       uint32_t n_win = 0, far_mask = 0;
+      uint32_t c = 0, mx = 0, my = 0;
       if (i < n) {
         const uint32_t rank = base + i;
-        const uint32_t c = ld_cg(queue + rank);
-        const uint32_t my = c / W, mx = c - my * W;
+        c = i < SQ ? sq[cur][i] : ld_cg(queue + rank);
+        my = c / W;
+        mx = c - my * W;
+        // ---- batch 1: the four neighbours' class bits and claims, all loads independent
+        uint32_t nb[4], cl[4];
+        bool ok[4], tr[4], mk[4];
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
-          uint32_t nx, ny;
-          if (!nbr_of(mx, my, W, H, s, nx, ny)) continue;
-          const uint32_t nb = ny * W + nx;
-          if (get_bit(trav, S.wpr, nx, ny)) {
-            if (ld_cg(claim + nb) != KEY_INF) continue;  // visited_flag[nbr]
+          const int x = (int)mx + dxs[s], y = (int)my + dys[s];
+          ok[s] = x >= 0 && y >= 0 && x < (int)W && y < (int)H;
+          nb[s] = ok[s] ? (uint32_t)y * W + (uint32_t)x : c;
+        }
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const uint32_t ny = nb[s] / W, nx = nb[s] - ny * W;
+          tr[s] = get_bit(trav, S.wpr, nx, ny);
+          mk[s] = get_bit(bits, S.wpr, nx, ny);
+          cl[s] = ld_cg(claim + nb[s]);
+        }
+        // ---- batch 2: ranks of each candidate's other neighbours (own cell included: its rank is never < rank)
+        uint32_t gr[4][4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const bool cand = ok[s] && tr[s] && cl[s] == KEY_INF;
+          const uint32_t ny = nb[s] / W, nx = nb[s] - ny * W;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int x = (int)nx + dxs[t], y = (int)ny + dys[t];
+            const bool in = cand && x >= 0 && y >= 0 && x < (int)W && y < (int)H;
+            gr[s][t] = in ? ld_cg(claim + (uint32_t)y * W + (uint32_t)x) : KEY_INF;
+          }
+        }
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          if (!ok[s]) continue;
+          if (tr[s]) {
+            if (cl[s] != KEY_INF) continue;  // visited_flag[nbr]
             bool first = true;
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-              uint32_t ox, oy;
-              if (!nbr_of(nx, ny, W, H, t, ox, oy)) continue;
-              const uint32_t o = oy * W + ox;
-              if (o == c) continue;
-              const uint32_t r = ld_cg(claim + o);
-              if (r >= base && r < rank) first = false;
-            }
+            for (int t = 0; t < 4; ++t)
+              if (gr[s][t] >= base && gr[s][t] < rank) first = false;
             if (!first) continue;
             // visited now; enqueued only inside the search radius (FrontierSearch.cpp:72-76)
+            const uint32_t ny = nb[s] / W, nx = nb[s] - ny * W;
             const double wx = S.map.ox + (nx + 0.5) * S.map.res;
             const double wy = S.map.oy + (ny + 0.5) * S.map.res;
             const double ddx = S.robot_x - wx, ddy = S.robot_y - wy;
-            if (sqrt(ddx * ddx + ddy * ddy) < S.dist_limit) win[n_win++] = nb;
+            if (sqrt(ddx * ddx + ddy * ddy) < S.dist_limit) win[n_win++] = nb[s];
             else far_mask |= 1u << s;
-          } else if (get_bit(bits, S.wpr, nx, ny)) {
-            atomicMin(claim + nb, TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
+          } else if (mk[s]) {
+            atomicMin(claim + nb[s], TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
           }
         }
       }
       uint32_t tile_total;
       const uint32_t off = block_scan(n_win, sh, &tile_total);
-      const uint32_t dst = next_base + n_next + off;
+      const uint32_t pos = n_next + off;
       for (uint32_t k = 0; k < n_win; ++k) {
-        queue[dst + k] = win[k];
-        claim[win[k]] = dst + k;
+        queue[next_base + pos + k] = win[k];
+        if (pos + k < SQ) sq[cur ^ 1][pos + k] = win[k];
+        claim[win[k]] = next_base + pos + k;
       }
       if (far_mask) {
-        const uint32_t c = queue[base + i];
-        const uint32_t my = c / W, mx = c - my * W;
         for (int s = 0; s < 4; ++s)
-          if (far_mask & (1u << s)) {
-            uint32_t nx, ny;
-            nbr_of(mx, my, W, H, s, nx, ny);
-            claim[ny * W + nx] = KEY_FAR;
-          }
+          if (far_mask & (1u << s)) claim[(uint32_t)((int)my + dys[s]) * W + (uint32_t)((int)mx + dxs[s])] = KEY_FAR;
       }
       n_next += tile_total;
       __syncthreads();
     }
     base = next_base;
     n = n_next;
+    cur ^= 1;
     ++levels;
   }
   if (threadIdx.x == 0) {
