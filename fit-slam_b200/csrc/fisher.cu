@@ -29,9 +29,11 @@
 namespace fitslam {
 
 static constexpr int CROWD_MAX = 512;       // exp(1 - j^0.8) underflows to 0 in float long before j = 512
-static constexpr int HASH_SLOTS = 4096;     // per-CTA voxel hash table
+static constexpr int HASH_SLOTS = 16384;    // per-CTA voxel hash table: one packed word per slot (64 KB of dynamic shared memory)
+static constexpr int CNT_BITS = 10;         // low bits of a slot: landmarks in the voxel, saturating (>= CROWD_MAX is enough)
+static constexpr uint32_t CNT_MASK = (1u << CNT_BITS) - 1u;
 static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding square of the lookup domain)
-static constexpr int FISHER_THREADS = 128;
+static constexpr int FISHER_THREADS = 256;
 
 struct M3f { float m[3][3]; };
 struct V3f { float v[3]; };
@@ -119,6 +121,7 @@ struct FisherState {
   DevBuf<float> lut;
   int32_t dims[3] = {0, 0, 0}, org[3] = {0, 0, 0};
   bool have_lut = false;
+  bool lut_dense = false;       // no NaN inside dims (true for a generated table)
   std::vector<int> axis[3];     // voxel indices per axis in generation order (file order of the .dat records)
   DevBuf<int32_t> d_axis;
   DevBuf<double> crowd;         // S[k] = sum_{j<=k} (float)exp(1 - pow(j, s)), k = 0..CROWD_MAX
@@ -227,7 +230,7 @@ static fitslam_status alloc_lut(fitslam_ctx *c, const int lo[3], const int hi[3]
     f->dims[a] = std::max(hi[a], 0) - f->org[a] + 1;
     n *= f->dims[a];
   }
-  if (n <= 0 || n > (1l << 28)) return fail(c, FITSLAM_E_INVALID, "lookup table too large");
+  if (n <= 0 || n >= (1l << (32 - CNT_BITS)) - 1) return fail(c, FITSLAM_E_INVALID, "lookup table too large (voxel index must fit 22 bits)");
   FS_CUDA(c, f->lut.reserve((size_t)n));
   fill_nan_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(f->lut.p, n);
   ++c->launches;
@@ -273,6 +276,13 @@ fitslam_status fitslam_fisher_generate_lookup(fitslam_ctx *c, const char *save_p
   FS_CUDA(c, cudaGetLastError());
   FS_CUDA(c, cudaStreamSynchronize(c->stream));
   f->have_lut = true;
+  {  // dense iff the table has no hole: one host pass over a copy (once per table)
+    std::vector<float> chk((size_t)lut_size(f));
+    FS_CUDA(c, cudaMemcpy(chk.data(), f->lut.p, chk.size() * 4, cudaMemcpyDeviceToHost));
+    f->lut_dense = true;
+    for (float v : chk)
+      if (v != v) { f->lut_dense = false; break; }
+  }
   st = upload_crowd_table(c);
   if (st != FITSLAM_OK) return st;
   if (save_path) {
@@ -331,6 +341,9 @@ fitslam_status fitslam_fisher_load_lookup(fitslam_ctx *c, const char *path) {
   FS_CUDA(c, cudaMemcpyAsync(f->lut.p, host.data(), host.size() * 4, cudaMemcpyHostToDevice, c->stream));
   FS_CUDA(c, cudaStreamSynchronize(c->stream));
   for (int a = 0; a < 3; ++a) f->axis[a].clear();
+  f->lut_dense = true;
+  for (float v : host)
+    if (v != v) { f->lut_dense = false; break; }
   f->have_lut = true;
   return upload_crowd_table(c);
 }
@@ -543,6 +556,7 @@ struct FisherParams {
   uint32_t n_poses;
   uint32_t first;       // this launch scores poses [first, first + gridDim.x)
   uint32_t poses_per_frontier;  // record f = pose / poses_per_frontier (cycle mode)
+  int lut_dense;        // every voxel inside dims has an entry: the visibility test needs no table read
 };
 
 struct PoseFrame {      // per-CTA, built by thread 0
@@ -632,6 +646,7 @@ __device__ __forceinline__ int voxel_of_point(const float4 q, const PoseFrame &F
     idx[a] = (int)r - P.org[a];
   }
   const int lin = (idx[0] * P.dims[1] + idx[1]) * P.dims[2] + idx[2];
+  if (P.lut_dense) return lin;
   const float val = __ldg(P.lut + lin);
   return (val == val) ? lin : -1;
 }
@@ -641,8 +656,7 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
               uint8_t *__restrict__ safe_out, uint32_t *__restrict__ nvis_out, ScoreRecord *__restrict__ rec_out,
               const fitslam_arrival *__restrict__ arrival) {
   __shared__ PoseFrame F;
-  __shared__ uint32_t keys[HASH_SLOTS];
-  __shared__ uint32_t cnts[HASH_SLOTS];
+  extern __shared__ uint32_t tab[];  // HASH_SLOTS packed slots: (voxel + 1) << CNT_BITS | count, 0 = empty
   __shared__ uint32_t s_used, s_overflow;
   __shared__ double s_red[FISHER_THREADS / 32];
   const uint32_t pi = P.first + blockIdx.x;
@@ -668,7 +682,7 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
     total = 0.0;
     if (threadIdx.x == 0) { s_used = 0; s_overflow = 0; }
     for (uint32_t pass = 0; pass < npass; ++pass) {
-      for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) { keys[i] = 0; cnts[i] = 0; }
+      for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) tab[i] = 0;
       __syncthreads();
       uint32_t my_used = 0;
       for (int b0 = (int)wid * 32; b0 < n_sq; b0 += (int)nw * 32) {
@@ -708,8 +722,14 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
             uint32_t slot = h & (HASH_SLOTS - 1);
             bool done = false;
             for (int probe = 0; probe < 256; ++probe) {
-              const uint32_t prev = atomicCAS(&keys[slot], 0u, (uint32_t)vox + 1u);
-              if (prev == 0u || prev == (uint32_t)vox + 1u) { atomicAdd(&cnts[slot], 1u); done = true; break; }
+              const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
+              const uint32_t prev = atomicCAS(&tab[slot], 0u, key | 1u);
+              if (prev == 0u) { done = true; break; }
+              if ((prev & ~CNT_MASK) == key) {
+                if ((prev & CNT_MASK) < CNT_MASK - 256u) atomicAdd(&tab[slot], 1u);  // saturates far above CROWD_MAX
+                done = true;
+                break;
+              }
               slot = (slot + 1) & (HASH_SLOTS - 1);
             }
             if (!done) *v_overflow = 1;
@@ -721,8 +741,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
       if (s_overflow && npass > 1) break;  // npass == 1: finish the (only) pass so that s_used is the full count
       if (!s_overflow)
         for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) {
-          const uint32_t k = keys[i];
-          if (k) total += (double)__ldg(P.lut + (k - 1)) * __ldg(P.crowd + min(cnts[i], (uint32_t)CROWD_MAX));
+          const uint32_t w = tab[i];
+          if (w) total += (double)__ldg(P.lut + ((w >> CNT_BITS) - 1u)) * __ldg(P.crowd + min(w & CNT_MASK, (uint32_t)CROWD_MAX));
         }
       __syncthreads();
     }
@@ -788,7 +808,13 @@ fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, 
   P.n_poses = n;
   P.first = first;
   P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
-  fisher_kernel<<<count, FISHER_THREADS, 0, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, d_arrival);
+  P.lut_dense = f->lut_dense ? 1 : 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FS_CUDA(c, cudaFuncSetAttribute(fisher_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HASH_SLOTS * 4));
+    attr_set = true;
+  }
+  fisher_kernel<<<count, FISHER_THREADS, HASH_SLOTS * 4, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, d_arrival);
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
   return FITSLAM_OK;
