@@ -21,6 +21,7 @@
 
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace fitslam {
@@ -39,6 +40,15 @@ static constexpr uint32_t MAX_RANK = (1u << 29) - 2;
 static constexpr int BFS_THREADS = 1024;
 static constexpr int REPLAY_THREADS = 128;
 static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
+// shared-memory wavefronts (the default path; the global-memory kernels below them are the fallback for levels or
+// components that do not fit)
+static constexpr uint32_t OW_SLOTS = 8192;   // outer wavefront: hash slots per level table (three tables + one key array)
+static constexpr uint32_t OW_QCAP = 4096;    // outer wavefront: widest level the shared-memory path holds (load factor 1/2)
+static constexpr uint32_t OW_SMEM = (4 * OW_SLOTS + 2 * OW_QCAP) * 4;
+static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
+static constexpr uint32_t IW_SLOTS = 8192;
+static constexpr uint32_t IW_SMEM = (2 * IW_SLOTS + IW_CELLS) * 4;
+static constexpr uint32_t HKEY_EMPTY = 0xFFFFFFFFu;
 
 struct Counters {
   uint32_t n_mask;         // cells in the frontier mask
@@ -51,7 +61,9 @@ struct Counters {
   uint32_t ambiguous;      // chunk sorts with two angles within 4 ulp, or a comparator walk off the array
   uint32_t expanded;       // reachable cells dequeued by the outer wavefront
   uint32_t visited;        // queue entries + far cells (cleanup bound)
-  uint32_t pad[6];
+  uint32_t dirty_queue;    // entries of queue[] whose claim words (and their 4 neighbours') the cleanup must reset
+  uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rerun with the global-memory kernel
+  uint32_t pad[4];
 };
 
 struct SearchParams {
@@ -61,8 +73,10 @@ struct SearchParams {
   uint32_t robot_cell;     // getIndex(mx, my) of the robot
   double robot_x, robot_y;
   double dist_limit;       // max_frontier_distance + max_frontier_cluster_size * resolution * 1.414
+  int64_t near_cells_sq;   // (|dx| + 1)^2 + (|dy| + 1)^2 < near_cells_sq (in cells, from the robot cell) => surely inside dist_limit
   int32_t min_size, max_size;
   uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
+  uint32_t use_smem;       // 1: shared-memory wavefronts first, global-memory kernels only for what does not fit
 };
 
 struct FrontierState {
@@ -70,6 +84,7 @@ struct FrontierState {
   DevBuf<uint32_t> slot;      // per cell: index into the mask-cell list (valid where the mask bit is set)
   DevBuf<uint32_t> bits;      // frontier mask, wpr words per row
   DevBuf<uint32_t> trav;      // traversable mask (cost < 254), same layout
+  DevBuf<uint2> tm;           // {trav word, frontier-mask word} interleaved: one 8-byte load classifies a neighbour
   DevBuf<uint32_t> mcell;     // mask-cell list (unordered)
   DevBuf<uint32_t> parent;    // union-find over list indices
   DevBuf<uint32_t> rkey;      // per root: min touch key of the component
@@ -86,6 +101,8 @@ struct FrontierState {
   Counters last{};
   cudaEvent_t ev_bfs[3] = {};  // around rank_bfs_kernel and replay_kernel (bench roofline of the dominant kernel)
   bool have_ev = false;
+  bool attr_set = false;
+  int force_global = -1;      // FITSLAM_WAVEFRONT=global selects the global-memory wavefront kernels (ablation / fallback test)
   float bfs_ms = 0, replay_ms = 0;
 };
 
@@ -97,7 +114,7 @@ static FrontierState *fr_state(fitslam_ctx *c) {
 void destroy_frontier_state(fitslam_ctx *c) {
   if (!c->fs) return;
   FrontierState *s = c->fs;
-  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->mcell.release();
+  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->mcell.release();
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
   if (s->have_ev)
@@ -131,8 +148,9 @@ __device__ __forceinline__ bool nbr_of(uint32_t mx, uint32_t my, uint32_t W, uin
 // cost == 255, no 4-neighbour with lethal_threshold <= cost < 255, at least one 4-neighbour with cost < lethal_threshold.
 // One thread per 32-cell mask word; rows are read as 16-byte vectors (pitch is a multiple of 16).
 __global__ void __launch_bounds__(256) mask_kernel(const SearchParams S, uint32_t *__restrict__ bits,
-                                                   uint32_t *__restrict__ trav, uint32_t *__restrict__ slot,
-                                                   uint32_t *__restrict__ mcell, Counters *__restrict__ cnt) {
+                                                   uint32_t *__restrict__ trav, uint2 *__restrict__ tm,
+                                                   uint32_t *__restrict__ slot, uint32_t *__restrict__ mcell,
+                                                   Counters *__restrict__ cnt) {
   const uint32_t W = S.map.W, H = S.map.H, pitch = S.map.pitch;
   const uint64_t n_words = (uint64_t)S.wpr * H;
   const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -187,6 +205,7 @@ __global__ void __launch_bounds__(256) mask_kernel(const SearchParams S, uint32_
     }
     bits[gid] = word;
     trav[gid] = tword;
+    tm[gid] = make_uint2(tword, word);
   }
   // append the set cells to the list: one atomicAdd per warp
   const uint32_t lane = threadIdx.x & 31u;
@@ -412,6 +431,7 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   __shared__ uint32_t sh[48];
   __shared__ uint32_t s_start;
   if (cnt->overflow) return;
+  if (S.use_smem && !cnt->ow_fallback) return;  // the shared-memory wavefront finished the search
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
   if (threadIdx.x == 0) s_start = S.robot_cell;  // falls back to pos when no cell qualifies (FrontierSearch.cpp:47-54)
@@ -522,6 +542,155 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   if (threadIdx.x == 0) {
     cnt->bfs_levels = levels;
     cnt->expanded = base;
+    cnt->dirty_queue = base;
+  }
+}
+
+// ---- shared-memory wavefronts ------------------------------------------------------------------------------------
+// Multiplicative hash of a cell index into a table of 2^bits slots.
+__device__ __forceinline__ uint32_t hslot(uint32_t cell, uint32_t bits) { return (cell * 0x9E3779B1u) >> (32u - bits); }
+
+// The outer wavefront with all of its dynamic state in shared memory (the default path).
+//   * The 4-connected grid is bipartite, so every neighbour of a level-d cell is on level d-1 or d+1: "visited" is
+//     "member of level d-1", a lookup in that level's hash table.  Three tables rotate (d-1: lookups, d: idle, d+1: being
+//     built); no per-cell state is kept in global memory, and a cell beyond the search radius needs none at all (testing it
+//     again gives the same answer).
+//   * Who visits an unvisited cell first: every dequeued cell bids (queue position * 4 + slot) into the level-(d+1) table
+//     with atomicMin; after a barrier the bidder that still owns the minimum is the one the reference's FIFO order would
+//     have let through.  Winners are appended in (position, slot) order by a block scan.
+//   * The level's cells live in a shared-memory queue; the read-only class bits come through L1 (one 8-byte load per
+//     neighbour).  The only global writes are the first-touch keys of frontier-mask cells.
+// A level wider than OW_QCAP (or a table that fills up) sets ow_fallback and the global-memory kernel above reruns the search.
+__global__ void __launch_bounds__(BFS_THREADS, 1)
+rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, Counters *cnt) {
+  extern __shared__ uint32_t ow_sh[];
+  uint32_t *tabs = ow_sh;                    // 3 x OW_SLOTS cell keys
+  uint32_t *val = ow_sh + 3 * OW_SLOTS;      // bids for the table under construction
+  uint32_t *sq = val + OW_SLOTS;             // 2 x OW_QCAP: this level's and the next level's cells
+  __shared__ uint32_t sh[48];
+  __shared__ uint32_t s_start, s_abort;
+  if (cnt->overflow) return;
+  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
+  if (threadIdx.x == 0) { s_start = S.robot_cell; s_abort = 0; }
+  __syncthreads();
+  if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+    nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh, cnt, &s_start);
+    __syncthreads();
+  }
+  const uint32_t start = s_start;
+  for (uint32_t i = threadIdx.x; i < 3 * OW_SLOTS; i += BFS_THREADS) tabs[i] = HKEY_EMPTY;
+  for (uint32_t i = threadIdx.x; i < OW_SLOTS; i += BFS_THREADS) val[i] = KEY_INF;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    cnt->start_cell = start;
+    sq[0] = start;
+    tabs[hslot(start, 13)] = start;  // level 0 lives in table 0
+  }
+  __syncthreads();
+  constexpr uint32_t NONE = 0xFFFFFFFFu, SMASK = OW_SLOTS - 1;
+  static_assert(OW_SLOTS == (1u << 13), "hslot(., 13) assumes 8192 slots");
+  uint32_t base = 0, n = 1, levels = 0, cur = 0;
+  uint32_t t_prev = 2, t_cur = 0, t_next = 1;
+  const int dxs[4] = {-1, 1, 0, 0}, dys[4] = {0, 0, -1, 1};
+  while (n > 0) {
+    const volatile uint32_t *kprev = tabs + t_prev * OW_SLOTS;
+    uint32_t *knext = tabs + t_next * OW_SLOTS;
+    const uint32_t *q = sq + cur * OW_QCAP;
+    uint32_t *qn = sq + (cur ^ 1u) * OW_QCAP;
+    uint32_t n_next = 0;
+    for (uint32_t tile = 0; tile < n; tile += BFS_THREADS) {
+      const uint32_t i = tile + threadIdx.x;
+      uint32_t cslot[4] = {NONE, NONE, NONE, NONE};
+      uint32_t mx = 0, my = 0;
+      if (i < n) {
+        const uint32_t c = q[i];
+        const uint32_t rank = base + i;
+        my = c / W;
+        mx = c - my * W;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const int x = (int)mx + dxs[s], y = (int)my + dys[s];
+          if (x < 0 || y < 0 || x >= (int)W || y >= (int)H) continue;
+          const uint2 w = __ldg(tm + (size_t)y * S.wpr + ((uint32_t)x >> 5));
+          const uint32_t bit = 1u << ((uint32_t)x & 31u);
+          const uint32_t nb = (uint32_t)y * W + (uint32_t)x;
+          if (w.x & bit) {
+            // visited_flag[nbr] <=> nbr is on level d-1
+            uint32_t h = hslot(nb, 13);
+            bool seen = false;
+            while (true) {
+              const uint32_t k = kprev[h];
+              if (k == nb) { seen = true; break; }
+              if (k == HKEY_EMPTY) break;
+              h = (h + 1u) & SMASK;
+            }
+            if (seen) continue;
+            // enqueued only inside the search radius (FrontierSearch.cpp:72-76); exact test only near the rim
+            const int64_t adx = (int64_t)abs(x - (int)rx) + 1, ady = (int64_t)abs(y - (int)ry) + 1;
+            if (adx * adx + ady * ady >= S.near_cells_sq) {
+              const double wx = S.map.ox + ((uint32_t)x + 0.5) * S.map.res;
+              const double wy = S.map.oy + ((uint32_t)y + 0.5) * S.map.res;
+              const double ddx = S.robot_x - wx, ddy = S.robot_y - wy;
+              if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) continue;
+            }
+            // bid for the cell in the level d+1 table
+            h = hslot(nb, 13);
+            uint32_t probes = 0;
+            while (true) {
+              uint32_t k = ((volatile uint32_t *)knext)[h];
+              if (k == HKEY_EMPTY) {
+                k = atomicCAS(&knext[h], HKEY_EMPTY, nb);
+                if (k == HKEY_EMPTY) k = nb;
+              }
+              if (k == nb) break;
+              h = (h + 1u) & SMASK;
+              if (++probes >= OW_SLOTS) { s_abort = 1; break; }
+            }
+            if (probes < OW_SLOTS) {
+              atomicMin(&val[h], i * 4u + (uint32_t)s);
+              cslot[s] = h;
+            }
+          } else if (w.y & bit) {
+            atomicMin(claim + nb, TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
+          }
+        }
+      }
+      __syncthreads();
+      uint32_t win[4];
+      uint32_t n_win = 0;
+#pragma unroll
+      for (int s = 0; s < 4; ++s)
+        if (cslot[s] != NONE && ((volatile uint32_t *)val)[cslot[s]] == i * 4u + (uint32_t)s)
+          win[n_win++] = (uint32_t)((int)my + dys[s]) * W + (uint32_t)((int)mx + dxs[s]);
+      uint32_t tile_total;
+      const uint32_t off = block_scan(n_win, sh, &tile_total);
+      const uint32_t pos = n_next + off;
+      for (uint32_t k = 0; k < n_win; ++k)
+        if (pos + k < OW_QCAP) qn[pos + k] = win[k];
+      n_next += tile_total;
+    }
+    if (n_next > OW_QCAP || s_abort) {  // uniform: n_next is a block-wide total, s_abort was written before the last barriers
+      if (threadIdx.x == 0) cnt->ow_fallback = 1;
+      return;
+    }
+    // the level d-1 table is dead: it becomes the table built during the next level, with fresh bids
+    {
+      uint4 *a = reinterpret_cast<uint4 *>(tabs + t_prev * OW_SLOTS), *b = reinterpret_cast<uint4 *>(val);
+      const uint4 e = make_uint4(HKEY_EMPTY, HKEY_EMPTY, HKEY_EMPTY, HKEY_EMPTY);
+      for (uint32_t i = threadIdx.x; i < OW_SLOTS / 4; i += BFS_THREADS) { a[i] = e; b[i] = e; }
+    }
+    __syncthreads();
+    const uint32_t t = t_prev; t_prev = t_cur; t_cur = t_next; t_next = t;
+    base += n;
+    n = n_next;
+    cur ^= 1u;
+    ++levels;
+  }
+  if (threadIdx.x == 0) {
+    cnt->bfs_levels = levels;
+    cnt->expanded = base;
+    cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
   }
 }
 
@@ -627,6 +796,7 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
   const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
   if (cnt->overflow) return;
   for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
+    if (S.use_smem && osize[comp] <= IW_CELLS) continue;  // replay_smem_kernel took it
     uint32_t *out = cells + ocell0[comp];
     const uint32_t seed = oseed[comp];
     if (threadIdx.x == 0) {
@@ -671,6 +841,98 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
           claim[nb] = INNER_BIT | dst;
         }
         n_next += tile_total;
+        __syncthreads();
+      }
+      base = next_base;
+      n = n_next;
+    }
+    __syncthreads();
+  }
+}
+
+
+// The inner wavefront of one component out of shared memory (components of at most IW_CELLS cells; one CTA each).
+// One hash table holds every cell the wavefront has accepted, with the bid that won it: rank(parent) * 8 + slot.  Bids
+// grow from level to level, so "frontier_flag[nbr]" is "the entry's bid is below base * 8", and within a level the
+// smallest bid wins, as in the outer wavefront.  The component's cells are mirrored in shared memory in queue order.
+__global__ void __launch_bounds__(REPLAY_THREADS)
+replay_smem_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ oseed,
+                   const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, uint32_t *cells, const Counters *cnt) {
+  extern __shared__ uint32_t iw_sh[];
+  uint32_t *keys = iw_sh, *val = iw_sh + IW_SLOTS, *mir = iw_sh + 2 * IW_SLOTS;
+  __shared__ uint32_t wsum[REPLAY_THREADS / 32];
+  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
+  if (cnt->overflow) return;
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
+    const uint32_t size = osize[comp];
+    if (size > IW_CELLS) continue;  // replay_kernel takes it
+    uint32_t lg = 5;
+    while ((1u << lg) < 2u * size) ++lg;  // <= 13
+    const uint32_t slots = 1u << lg, smask = slots - 1u;
+    for (uint32_t i = threadIdx.x; i < slots; i += REPLAY_THREADS) { keys[i] = HKEY_EMPTY; val[i] = KEY_INF; }
+    __syncthreads();
+    uint32_t *out = cells + ocell0[comp];
+    if (threadIdx.x == 0) {
+      const uint32_t seed = oseed[comp];
+      out[0] = seed;
+      mir[0] = seed;
+      const uint32_t h = hslot(seed, lg);
+      keys[h] = seed;
+      val[h] = 0;
+    }
+    __syncthreads();
+    uint32_t base = 0, n = 1;
+    while (n > 0) {
+      const uint32_t next_base = base + n, items = n << 3;
+      uint32_t n_next = 0;
+      for (uint32_t tile = 0; tile < items; tile += REPLAY_THREADS) {
+        const uint32_t j = tile + threadIdx.x;
+        bool cand = false;
+        uint32_t nb = 0, h = 0, mykey = 0;
+        if (j < items) {
+          const uint32_t rank = base + (j >> 3);
+          const uint32_t p = mir[rank];
+          const uint32_t my = p / W, mx = p - my * W;
+          uint32_t nx, ny;
+          if (nbr_of(mx, my, W, H, (int)(j & 7u), nx, ny) && get_bit(bits, S.wpr, nx, ny)) {
+            nb = ny * W + nx;
+            mykey = rank * 8u + (j & 7u);
+            h = hslot(nb, lg);
+            while (true) {
+              uint32_t k = ((volatile uint32_t *)keys)[h];
+              if (k == HKEY_EMPTY) {
+                k = atomicCAS(&keys[h], HKEY_EMPTY, nb);
+                if (k == HKEY_EMPTY) k = nb;
+              }
+              if (k == nb) break;
+              h = (h + 1u) & smask;
+            }
+            if (((volatile uint32_t *)val)[h] >= base * 8u) {  // !frontier_flag[nbr]
+              atomicMin(&val[h], mykey);
+              cand = true;
+            }
+          }
+        }
+        __syncthreads();
+        const bool win = cand && ((volatile uint32_t *)val)[h] == mykey;
+        const uint32_t bal = __ballot_sync(0xffffffffu, win);
+        if (lane == 0) wsum[wid] = __popc(bal);
+        __syncthreads();
+        uint32_t off = __popc(bal & ((1u << lane) - 1u)), total = 0;
+#pragma unroll
+        for (uint32_t w = 0; w < REPLAY_THREADS / 32; ++w) {
+          const uint32_t t = wsum[w];
+          if (w < wid) off += t;
+          total += t;
+        }
+        if (win) {
+          const uint32_t dst = next_base + n_next + off;
+          out[dst] = nb;
+          mir[dst] = nb;
+        }
+        n_next += total;
         __syncthreads();
       }
       base = next_base;
@@ -905,7 +1167,7 @@ chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uin
 __global__ void cleanup_kernel(const SearchParams S, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ mcell,
                                uint32_t *claim, const Counters *cnt) {
   const uint32_t W = S.map.W, H = S.map.H;
-  const uint32_t nq = cnt->expanded, nm = min(cnt->n_mask, S.mask_cap);
+  const uint32_t nq = cnt->dirty_queue, nm = min(cnt->n_mask, S.mask_cap);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nq + nm; i += gridDim.x * blockDim.x) {
     if (i < nq) {
       const uint32_t c = queue[i];
@@ -932,6 +1194,7 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   const uint32_t wpr = (c->W + 31u) / 32u;
   FS_CUDA(c, s->bits.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->trav.reserve((size_t)wpr * c->H));
+  FS_CUDA(c, s->tm.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->slot.reserve(N));
   FS_CUDA(c, s->queue.reserve(N + 8));
   FS_CUDA(c, s->counters.reserve(1));
@@ -976,6 +1239,20 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   S.robot_y = ry;
   const double mfd = s->search_distance >= 0.0 ? s->search_distance : c->prm.max_frontier_distance;
   S.dist_limit = mfd + (c->prm.max_frontier_cluster_size * c->res * 1.414);  // FrontierSearch.cpp:74
+  {
+    const double L = S.dist_limit / c->res;
+    S.near_cells_sq = L > 4.0 ? (int64_t)(L * L * (1.0 - 1e-6)) - 2 : 0;
+  }
+  if (s->force_global < 0) {
+    const char *e = getenv("FITSLAM_WAVEFRONT");
+    s->force_global = (e && !strcmp(e, "global")) ? 1 : 0;
+  }
+  S.use_smem = s->force_global ? 0u : 1u;
+  if (!s->attr_set) {
+    FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
+    FS_CUDA(c, cudaFuncSetAttribute(replay_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)IW_SMEM));
+    s->attr_set = true;
+  }
   S.min_size = c->prm.min_frontier_cluster_size;
   S.max_size = c->prm.max_frontier_cluster_size;
   S.mask_cap = s->mask_cap;
@@ -987,7 +1264,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   FS_CUDA(c, cudaMemsetAsync(cnt, 0, sizeof(Counters), c->stream));
   const uint64_t n_words = (uint64_t)S.wpr * c->H;
   const unsigned wide = 148 * 8;
-  mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->slot.p, s->mcell.p, cnt);
+  mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
   uf_init_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rkey.p, s->rsize.p, cnt, S.mask_cap);
   uf_merge_kernel<<<wide, 256, 0, c->stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
   uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, cnt, S.mask_cap);
@@ -996,15 +1273,23 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     s->have_ev = true;
   }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
-  rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);
+  if (S.use_smem) {
+    rank_bfs_smem_kernel<<<1, BFS_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, cnt);
+    ++c->launches;
+  }
+  rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
   touch_reduce_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, cnt);
   seed_collect_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->ckey.p,
                                                     s->cseed.p, s->csize.p, cnt);
   comp_order_kernel<<<148 * 2, 256, 0, c->stream>>>(S, s->ckey.p, s->cseed.p, s->csize.p, s->oseed.p, s->osize.p, cnt);
   comp_scan_kernel<<<1, 1024, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, cnt);
+  if (S.use_smem) {
+    replay_smem_kernel<<<148 * 2, REPLAY_THREADS, IW_SMEM, c->stream>>>(S, s->bits.p, s->oseed.p, s->osize.p, s->ocell0.p, s->cells.p, cnt);
+    ++c->launches;
+  }
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
-                                                            s->cells.p, cnt);
+                                                            s->cells.p, cnt);  // components above IW_CELLS cells
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[2], c->stream));
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
                                                s->centroids.p, cnt);

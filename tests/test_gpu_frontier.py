@@ -102,3 +102,24 @@ def test_search_random_noise_maps(capi, oracle):
         a[H // 2, W // 2] = 0
         meta = dict(res=0.05, ox=-1.0, oy=2.0)
         _compare(capi, oracle, a, meta, meta["ox"] + (W // 2 + 0.5) * 0.05, meta["oy"] + (H // 2 + 0.5) * 0.05)
+
+
+@pytest.mark.parametrize("name", ["C1", "C3"])
+def test_search_global_memory_wavefronts(capi, oracle, synth, name, monkeypatch):
+    # FITSLAM_WAVEFRONT=global selects the global-memory wavefront kernels (the fallback for levels wider than the
+    # shared-memory queue and for components above 4096 cells); both paths must give the oracle's lists
+    monkeypatch.setenv("FITSLAM_WAVEFRONT", "global")
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], ov)
+
+
+def test_search_wide_levels_fall_back(capi, oracle):
+    # an open 3000 x 3000 map: the diamond wavefront grows past 4096 cells per level, so the shared-memory outer
+    # wavefront hands over to the global-memory kernel mid-search; one huge ring component (> 4096 cells) likewise.
+    # (resolution 1/16 m keeps every cell centre an exact double: the two-branch chunks of a straight frontier then give
+    # exact angle ties instead of ulp-level atan2 noise, which is a libm property and not what this test is about)
+    W = H = 3000
+    a = np.full((H, W), 255, np.uint8)
+    a[200:2800, 200:2800] = 0
+    meta = dict(res=0.0625, ox=-93.75, oy=-93.75)
+    _compare(capi, oracle, a, meta, 0.0, 0.0, dict(max_frontier_distance=250.0))
