@@ -42,12 +42,13 @@ static constexpr int REPLAY_THREADS = 128;
 static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
 // shared-memory wavefronts (the default path; the global-memory kernels below them are the fallback for levels or
 // components that do not fit)
-static constexpr uint32_t OW_SLOTS = 8192;   // outer wavefront: hash slots per level table (three tables + one key array)
+static constexpr uint32_t OW_SLOTS = 8192;   // outer wavefront: slots of the per-level bid table (cell, bid, directions)
 static constexpr uint32_t OW_QCAP = 4096;    // outer wavefront: widest level the shared-memory path holds (load factor 1/2)
-static constexpr uint32_t OW_SMEM = (4 * OW_SLOTS + 2 * OW_QCAP) * 4;
+static constexpr uint32_t OW_SMEM = (3 * OW_SLOTS + 2 * OW_QCAP) * 4 + 2 * OW_QCAP;
 static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
-static constexpr uint32_t IW_SLOTS = 8192;
-static constexpr uint32_t IW_SMEM = (2 * IW_SLOTS + IW_CELLS) * 4;
+static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells (many warps per SM), <= IW_CELLS cells (two per SM)
+static constexpr uint32_t IW_BITS_SMALL = 1024, IW_BITS_LARGE = 8192;  // words of the component's mask window held in shared memory
+static constexpr uint32_t iw_smem(uint32_t cells, uint32_t bit_words) { return (2 * 2 * cells + cells + bit_words) * 4; }
 static constexpr uint32_t HKEY_EMPTY = 0xFFFFFFFFu;
 
 struct Counters {
@@ -89,6 +90,8 @@ struct FrontierState {
   DevBuf<uint32_t> parent;    // union-find over list indices
   DevBuf<uint32_t> rkey;      // per root: min touch key of the component
   DevBuf<uint32_t> rsize;     // per root: cell count
+  DevBuf<uint32_t> rbox;      // per root: bounding box of the component (4 words: min x, min y, max x, max y)
+  DevBuf<uint32_t> cbox, obox;  // the same per found component, append order / discovery order
   DevBuf<uint32_t> queue;     // outer wavefront, all levels back to back in dequeue order
   DevBuf<uint32_t> ckey, cseed, csize;               // component table, unordered (append order)
   DevBuf<uint32_t> oseed, osize, ocell0, ofront0;    // component table in discovery order + offsets
@@ -116,6 +119,7 @@ void destroy_frontier_state(fitslam_ctx *c) {
   FrontierState *s = c->fs;
   s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->mcell.release();
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
+  s->rbox.release(); s->cbox.release(); s->obox.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
   if (s->have_ev)
     for (auto &e : s->ev_bfs) cudaEventDestroy(e);
@@ -267,12 +271,13 @@ __device__ __forceinline__ void uf_union(uint32_t *parent, uint32_t a, uint32_t 
     }
   } while (!done);
 }
-__global__ void uf_init_kernel(uint32_t *parent, uint32_t *rkey, uint32_t *rsize, const Counters *cnt, uint32_t cap) {
+__global__ void uf_init_kernel(uint32_t *parent, uint32_t *rkey, uint32_t *rsize, uint32_t *rbox, const Counters *cnt, uint32_t cap) {
   const uint32_t n = min(cnt->n_mask, cap);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     parent[i] = i;
     rkey[i] = KEY_INF;
     rsize[i] = 0;
+    reinterpret_cast<uint4 *>(rbox)[i] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
   }
 }
 // each mask cell links to its mask neighbours in the forward half of the 8-neighbourhood
@@ -294,7 +299,8 @@ __global__ void uf_merge_kernel(const SearchParams S, const uint32_t *__restrict
 }
 // flatten: parent[i] = root; rsize[root] = number of cells.  The walk is read-only: a path-halving store from a
 // thread passing through i could land after i's own "parent[i] = root" and leave a non-root there.
-__global__ void uf_compress_kernel(uint32_t *parent, uint32_t *rsize, const Counters *cnt, uint32_t cap) {
+__global__ void uf_compress_kernel(uint32_t *parent, uint32_t *rsize, uint32_t *rbox, const uint32_t *__restrict__ mcell, uint32_t W,
+                                   const Counters *cnt, uint32_t cap) {
   const uint32_t n = min(cnt->n_mask, cap);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     uint32_t r = i, p = ld_cg(parent + r);
@@ -304,6 +310,11 @@ __global__ void uf_compress_kernel(uint32_t *parent, uint32_t *rsize, const Coun
     }
     parent[i] = r;
     atomicAdd(rsize + r, 1u);
+    const uint32_t c = mcell[i], my = c / W, mx = c - my * W;
+    atomicMin(rbox + 4 * r, mx);
+    atomicMin(rbox + 4 * r + 1, my);
+    atomicMax(rbox + 4 * r + 2, mx);
+    atomicMax(rbox + 4 * r + 3, my);
   }
 }
 
@@ -551,137 +562,233 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
 __device__ __forceinline__ uint32_t hslot(uint32_t cell, uint32_t bits) { return (cell * 0x9E3779B1u) >> (32u - bits); }
 
 // The outer wavefront with all of its dynamic state in shared memory (the default path).
-//   * The 4-connected grid is bipartite, so every neighbour of a level-d cell is on level d-1 or d+1: "visited" is
-//     "member of level d-1", a lookup in that level's hash table.  Three tables rotate (d-1: lookups, d: idle, d+1: being
-//     built); no per-cell state is kept in global memory, and a cell beyond the search radius needs none at all (testing it
-//     again gives the same answer).
-//   * Who visits an unvisited cell first: every dequeued cell bids (queue position * 4 + slot) into the level-(d+1) table
-//     with atomicMin; after a barrier the bidder that still owns the minimum is the one the reference's FIFO order would
-//     have let through.  Winners are appended in (position, slot) order by a block scan.
-//   * The level's cells live in a shared-memory queue; the read-only class bits come through L1 (one 8-byte load per
-//     neighbour).  The only global writes are the first-touch keys of frontier-mask cells.
+//   * Who visits an unvisited cell first: every dequeued cell bids (queue position * 4 + slot) for each traversable
+//     neighbour it may visit into a per-level hash table with atomicMin; after a barrier the bidder that still owns the
+//     minimum is the one the reference's FIFO order would have let through.  Winners are appended in bid order by a block
+//     scan, which is the order the reference pushes them.
+//   * No visited array: the 4-connected grid is bipartite, so a neighbour of a level-d cell is on level d-1 or d+1.
+//     EVERY level-(d-1) neighbour of a cell bids for it, so the directions the bids came from (OR-ed into the table entry
+//     and carried with the queue entry) are exactly the cell's visited neighbours; every other traversable neighbour is
+//     unvisited.  A cell beyond the search radius needs no state at all (testing it again gives the same answer).
+//   * The level's cells (packed y << 16 | x) live in a shared-memory queue; the read-only class bits come through L1
+//     (three 8-byte loads per cell).  The only global writes are the first-touch keys of frontier-mask cells.
 // A level wider than OW_QCAP (or a table that fills up) sets ow_fallback and the global-memory kernel above reruns the search.
+struct OwShared {
+  uint32_t *keys, *val, *dmask;   // OW_SLOTS each: cell, smallest bid, directions the bids came from
+  uint32_t *q[2];                 // OW_QCAP each
+  uint8_t *qm[2];                 // OW_QCAP each: visited-neighbour directions of the queue entry
+  uint32_t *wsum;                 // 2 x 32 warp totals (alternating, so the scan needs one barrier)
+};
+
+template <int K>
+__device__ __forceinline__ uint32_t ow_level(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, const OwShared &sh,
+                                            uint32_t cur, uint32_t base, uint32_t n, uint32_t rx, uint32_t ry, uint32_t level,
+                                            uint32_t *s_abort) {
+  constexpr uint32_t SMASK = OW_SLOTS - 1;
+  constexpr uint32_t NOSLOT = 0xFFFFu;
+  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t *q = sh.q[cur];
+  const uint8_t *qm = sh.qm[cur];
+  uint32_t *qn = sh.q[cur ^ 1u];
+  uint8_t *qnm = sh.qm[cur ^ 1u];
+  uint32_t bslot[K][4];
+  uint32_t cxy[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const uint32_t pos = threadIdx.x * K + k;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) bslot[k][s] = NOSLOT;
+    cxy[k] = 0;
+    if (pos >= n) continue;
+    const uint32_t c = q[pos];
+    const uint32_t seen = qm[pos];
+    cxy[k] = c;
+    const uint32_t mx = c & 0xFFFFu, my = c >> 16;
+    const uint32_t rank = base + pos;
+    const uint32_t wx = mx >> 5, bx = mx & 31u;
+    // class words: {traversable, frontier mask} of the rows above / at / below, plus the side words at a word edge
+    const uint2 *row = tm + (size_t)my * S.wpr + wx;
+    const uint2 wc = __ldg(row);
+    const uint2 wu = my > 0 ? __ldg(row - S.wpr) : make_uint2(0, 0);
+    const uint2 wd = my + 1 < H ? __ldg(row + S.wpr) : make_uint2(0, 0);
+    uint32_t tr = 0, mk = 0;  // bit s: neighbour s is traversable / a frontier-mask cell
+    if (mx > 0) {
+      const uint2 w = bx ? wc : __ldg(row - 1);
+      const uint32_t b = (bx + 31u) & 31u;
+      tr |= ((w.x >> b) & 1u) << 0;
+      mk |= ((w.y >> b) & 1u) << 0;
+    }
+    if (mx + 1 < W) {
+      const uint2 w = bx != 31u ? wc : __ldg(row + 1);
+      const uint32_t b = (bx + 1u) & 31u;
+      tr |= ((w.x >> b) & 1u) << 1;
+      mk |= ((w.y >> b) & 1u) << 1;
+    }
+    tr |= ((wu.x >> bx) & 1u) << 2;
+    mk |= ((wu.y >> bx) & 1u) << 2;
+    tr |= ((wd.x >> bx) & 1u) << 3;
+    mk |= ((wd.y >> bx) & 1u) << 3;
+    tr &= ~seen;  // visited_flag[nbr]: the neighbours on level d-1
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const int dx = s == 0 ? -1 : (s == 1 ? 1 : 0), dy = s == 2 ? -1 : (s == 3 ? 1 : 0);
+      const uint32_t x = mx + dx, y = my + dy;
+      if ((tr >> s) & 1u) {
+        // enqueued only inside the search radius (FrontierSearch.cpp:72-76); the exact test runs only near the rim
+        const int64_t adx = (int64_t)abs((int)x - (int)rx) + 1, ady = (int64_t)abs((int)y - (int)ry) + 1;
+        if (adx * adx + ady * ady >= S.near_cells_sq) {
+          const double wx_ = S.map.ox + (x + 0.5) * S.map.res;
+          const double wy_ = S.map.oy + (y + 0.5) * S.map.res;
+          const double ddx = S.robot_x - wx_, ddy = S.robot_y - wy_;
+          if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) continue;
+        }
+        const uint32_t nb = (y << 16) | x;
+        uint32_t h = hslot(nb, 13);
+        uint32_t probes = 0;
+        while (true) {
+          uint32_t kk = ((volatile uint32_t *)sh.keys)[h];
+          if (kk == HKEY_EMPTY) {
+            kk = atomicCAS(&sh.keys[h], HKEY_EMPTY, nb);
+            if (kk == HKEY_EMPTY) kk = nb;
+          }
+          if (kk == nb) break;
+          h = (h + 1u) & SMASK;
+          if (++probes >= OW_SLOTS) break;
+        }
+        if (probes >= OW_SLOTS) {
+          *s_abort = 1;
+        } else {
+          atomicMin(&sh.val[h], pos * 4u + (uint32_t)s);
+          atomicOr(&sh.dmask[h], 1u << (s ^ 1));  // seen from nb, this cell lies in the opposite direction
+          bslot[k][s] = h;
+        }
+      } else if ((mk >> s) & 1u) {
+        atomicMin(claim + (size_t)y * W + x, TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
+      }
+    }
+  }
+  __syncthreads();
+  // winners: the bids that are still the minimum of their entry
+  uint32_t wins = 0, wmask = 0, n_win = 0;  // wins: bit (4k+s); wmask: 4 direction bits per winner, in order
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const uint32_t h = bslot[k][s];
+      if (h == NOSLOT) continue;
+      const uint32_t pos = threadIdx.x * K + k;
+      if (((volatile uint32_t *)sh.val)[h] == pos * 4u + (uint32_t)s) {
+        wins |= 1u << (4 * k + s);
+        if (K <= 2) wmask |= (((volatile uint32_t *)sh.dmask)[h] & 15u) << (4 * n_win);
+        ++n_win;
+      }
+    }
+  uint64_t wmask_hi = 0;  // K == 4: up to 16 winners need 64 bits
+  if (K > 2) {
+    uint32_t j = 0;
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+#pragma unroll
+      for (int s = 0; s < 4; ++s)
+        if (wins & (1u << (4 * k + s))) {
+          wmask_hi |= (uint64_t)(((volatile uint32_t *)sh.dmask)[bslot[k][s]] & 15u) << (4 * j);
+          ++j;
+        }
+  }
+  // block-wide exclusive scan of n_win: one barrier (warp totals alternate between two buffers)
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  uint32_t incl = n_win;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  uint32_t *ws = sh.wsum + (level & 1u) * 32u;
+  if (lane == 31) ws[wid] = incl;
+  __syncthreads();
+  uint32_t wv = ws[lane], wi = wv;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+    if ((int)lane >= o) wi += t;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, wi, 31);
+  const uint32_t wbase = __shfl_sync(0xffffffffu, wi - wv, wid);
+  uint32_t dst = wbase + incl - n_win;
+  // append the winners; every bidder puts its table entry back to empty
+  uint32_t j = 0;
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const uint32_t h = bslot[k][s];
+      if (h == NOSLOT) continue;
+      if (wins & (1u << (4 * k + s))) {
+        const int dx = s == 0 ? -1 : (s == 1 ? 1 : 0), dy = s == 2 ? -1 : (s == 3 ? 1 : 0);
+        const uint32_t mx = cxy[k] & 0xFFFFu, my = cxy[k] >> 16;
+        if (dst < OW_QCAP) {
+          qn[dst] = ((my + dy) << 16) | (mx + dx);
+          qnm[dst] = (uint8_t)(K <= 2 ? (wmask >> (4 * j)) & 15u : (uint32_t)(wmask_hi >> (4 * j)) & 15u);
+        }
+        ++dst;
+        ++j;
+      }
+      sh.keys[h] = HKEY_EMPTY;
+      sh.val[h] = KEY_INF;
+      sh.dmask[h] = 0;
+    }
+  __syncthreads();
+  return total;
+}
+
 __global__ void __launch_bounds__(BFS_THREADS, 1)
 rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, Counters *cnt) {
   extern __shared__ uint32_t ow_sh[];
-  uint32_t *tabs = ow_sh;                    // 3 x OW_SLOTS cell keys
-  uint32_t *val = ow_sh + 3 * OW_SLOTS;      // bids for the table under construction
-  uint32_t *sq = val + OW_SLOTS;             // 2 x OW_QCAP: this level's and the next level's cells
-  __shared__ uint32_t sh[48];
+  __shared__ uint32_t sh48[48];
   __shared__ uint32_t s_start, s_abort;
+  __shared__ uint32_t s_wsum[64];
+  OwShared sh;
+  sh.keys = ow_sh;
+  sh.val = ow_sh + OW_SLOTS;
+  sh.dmask = ow_sh + 2 * OW_SLOTS;
+  sh.q[0] = ow_sh + 3 * OW_SLOTS;
+  sh.q[1] = sh.q[0] + OW_QCAP;
+  sh.qm[0] = reinterpret_cast<uint8_t *>(sh.q[1] + OW_QCAP);
+  sh.qm[1] = sh.qm[0] + OW_QCAP;
+  sh.wsum = s_wsum;
   if (cnt->overflow) return;
-  const uint32_t W = S.map.W, H = S.map.H;
+  const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
   if (threadIdx.x == 0) { s_start = S.robot_cell; s_abort = 0; }
   __syncthreads();
   if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
-    nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh, cnt, &s_start);
+    nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
     __syncthreads();
   }
   const uint32_t start = s_start;
-  for (uint32_t i = threadIdx.x; i < 3 * OW_SLOTS; i += BFS_THREADS) tabs[i] = HKEY_EMPTY;
-  for (uint32_t i = threadIdx.x; i < OW_SLOTS; i += BFS_THREADS) val[i] = KEY_INF;
-  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < OW_SLOTS; i += BFS_THREADS) {
+    sh.keys[i] = HKEY_EMPTY;
+    sh.val[i] = KEY_INF;
+    sh.dmask[i] = 0;
+  }
   if (threadIdx.x == 0) {
     cnt->start_cell = start;
-    sq[0] = start;
-    tabs[hslot(start, 13)] = start;  // level 0 lives in table 0
+    const uint32_t sy = start / W, sx = start - sy * W;
+    sh.q[0][0] = (sy << 16) | sx;
+    sh.qm[0][0] = 0;
   }
   __syncthreads();
-  constexpr uint32_t NONE = 0xFFFFFFFFu, SMASK = OW_SLOTS - 1;
   static_assert(OW_SLOTS == (1u << 13), "hslot(., 13) assumes 8192 slots");
   uint32_t base = 0, n = 1, levels = 0, cur = 0;
-  uint32_t t_prev = 2, t_cur = 0, t_next = 1;
-  const int dxs[4] = {-1, 1, 0, 0}, dys[4] = {0, 0, -1, 1};
   while (n > 0) {
-    const volatile uint32_t *kprev = tabs + t_prev * OW_SLOTS;
-    uint32_t *knext = tabs + t_next * OW_SLOTS;
-    const uint32_t *q = sq + cur * OW_QCAP;
-    uint32_t *qn = sq + (cur ^ 1u) * OW_QCAP;
-    uint32_t n_next = 0;
-    for (uint32_t tile = 0; tile < n; tile += BFS_THREADS) {
-      const uint32_t i = tile + threadIdx.x;
-      uint32_t cslot[4] = {NONE, NONE, NONE, NONE};
-      uint32_t mx = 0, my = 0;
-      if (i < n) {
-        const uint32_t c = q[i];
-        const uint32_t rank = base + i;
-        my = c / W;
-        mx = c - my * W;
-#pragma unroll
-        for (int s = 0; s < 4; ++s) {
-          const int x = (int)mx + dxs[s], y = (int)my + dys[s];
-          if (x < 0 || y < 0 || x >= (int)W || y >= (int)H) continue;
-          const uint2 w = __ldg(tm + (size_t)y * S.wpr + ((uint32_t)x >> 5));
-          const uint32_t bit = 1u << ((uint32_t)x & 31u);
-          const uint32_t nb = (uint32_t)y * W + (uint32_t)x;
-          if (w.x & bit) {
-            // visited_flag[nbr] <=> nbr is on level d-1
-            uint32_t h = hslot(nb, 13);
-            bool seen = false;
-            while (true) {
-              const uint32_t k = kprev[h];
-              if (k == nb) { seen = true; break; }
-              if (k == HKEY_EMPTY) break;
-              h = (h + 1u) & SMASK;
-            }
-            if (seen) continue;
-            // enqueued only inside the search radius (FrontierSearch.cpp:72-76); exact test only near the rim
-            const int64_t adx = (int64_t)abs(x - (int)rx) + 1, ady = (int64_t)abs(y - (int)ry) + 1;
-            if (adx * adx + ady * ady >= S.near_cells_sq) {
-              const double wx = S.map.ox + ((uint32_t)x + 0.5) * S.map.res;
-              const double wy = S.map.oy + ((uint32_t)y + 0.5) * S.map.res;
-              const double ddx = S.robot_x - wx, ddy = S.robot_y - wy;
-              if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) continue;
-            }
-            // bid for the cell in the level d+1 table
-            h = hslot(nb, 13);
-            uint32_t probes = 0;
-            while (true) {
-              uint32_t k = ((volatile uint32_t *)knext)[h];
-              if (k == HKEY_EMPTY) {
-                k = atomicCAS(&knext[h], HKEY_EMPTY, nb);
-                if (k == HKEY_EMPTY) k = nb;
-              }
-              if (k == nb) break;
-              h = (h + 1u) & SMASK;
-              if (++probes >= OW_SLOTS) { s_abort = 1; break; }
-            }
-            if (probes < OW_SLOTS) {
-              atomicMin(&val[h], i * 4u + (uint32_t)s);
-              cslot[s] = h;
-            }
-          } else if (w.y & bit) {
-            atomicMin(claim + nb, TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
-          }
-        }
-      }
-      __syncthreads();
-      uint32_t win[4];
-      uint32_t n_win = 0;
-#pragma unroll
-      for (int s = 0; s < 4; ++s)
-        if (cslot[s] != NONE && ((volatile uint32_t *)val)[cslot[s]] == i * 4u + (uint32_t)s)
-          win[n_win++] = (uint32_t)((int)my + dys[s]) * W + (uint32_t)((int)mx + dxs[s]);
-      uint32_t tile_total;
-      const uint32_t off = block_scan(n_win, sh, &tile_total);
-      const uint32_t pos = n_next + off;
-      for (uint32_t k = 0; k < n_win; ++k)
-        if (pos + k < OW_QCAP) qn[pos + k] = win[k];
-      n_next += tile_total;
-    }
-    if (n_next > OW_QCAP || s_abort) {  // uniform: n_next is a block-wide total, s_abort was written before the last barriers
+    uint32_t n_next;
+    if (n <= BFS_THREADS) n_next = ow_level<1>(S, tm, claim, sh, cur, base, n, rx, ry, levels, &s_abort);
+    else if (n <= 2 * BFS_THREADS) n_next = ow_level<2>(S, tm, claim, sh, cur, base, n, rx, ry, levels, &s_abort);
+    else n_next = ow_level<4>(S, tm, claim, sh, cur, base, n, rx, ry, levels, &s_abort);
+    if (n_next > OW_QCAP || s_abort) {  // uniform: a block-wide total, and a flag written before the level's last barriers
       if (threadIdx.x == 0) cnt->ow_fallback = 1;
       return;
     }
-    // the level d-1 table is dead: it becomes the table built during the next level, with fresh bids
-    {
-      uint4 *a = reinterpret_cast<uint4 *>(tabs + t_prev * OW_SLOTS), *b = reinterpret_cast<uint4 *>(val);
-      const uint4 e = make_uint4(HKEY_EMPTY, HKEY_EMPTY, HKEY_EMPTY, HKEY_EMPTY);
-      for (uint32_t i = threadIdx.x; i < OW_SLOTS / 4; i += BFS_THREADS) { a[i] = e; b[i] = e; }
-    }
-    __syncthreads();
-    const uint32_t t = t_prev; t_prev = t_cur; t_cur = t_next; t_next = t;
     base += n;
     n = n_next;
     cur ^= 1u;
@@ -708,8 +815,8 @@ __global__ void touch_reduce_kernel(const SearchParams S, const uint32_t *__rest
 // the cell whose key equals its component's minimum is the seed: append {key, seed, size} to the component table
 __global__ void seed_collect_kernel(const SearchParams S, const uint32_t *__restrict__ mcell, const uint32_t *__restrict__ parent,
                                     const uint32_t *__restrict__ claim, const uint32_t *__restrict__ rkey,
-                                    const uint32_t *__restrict__ rsize, uint32_t *ckey, uint32_t *cseed, uint32_t *csize,
-                                    Counters *cnt) {
+                                    const uint32_t *__restrict__ rsize, const uint32_t *__restrict__ rbox, uint32_t *ckey,
+                                    uint32_t *cseed, uint32_t *csize, uint32_t *cbox, Counters *cnt) {
   if (cnt->overflow & 3u) return;
   const uint32_t n = min(cnt->n_mask, S.mask_cap);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -723,6 +830,7 @@ __global__ void seed_collect_kernel(const SearchParams S, const uint32_t *__rest
       ckey[pos] = k;
       cseed[pos] = c;
       csize[pos] = rsize[r];
+      reinterpret_cast<uint4 *>(cbox)[pos] = reinterpret_cast<const uint4 *>(rbox)[r];
     } else {
       atomicOr(&cnt->overflow, 4u);
     }
@@ -731,7 +839,8 @@ __global__ void seed_collect_kernel(const SearchParams S, const uint32_t *__rest
 // discovery order = ascending seed key (keys are unique): rank by counting, scatter into the ordered table
 __global__ void __launch_bounds__(256)
 comp_order_kernel(const SearchParams S, const uint32_t *__restrict__ ckey, const uint32_t *__restrict__ cseed,
-                  const uint32_t *__restrict__ csize, uint32_t *oseed, uint32_t *osize, const Counters *cnt) {
+                  const uint32_t *__restrict__ csize, const uint32_t *__restrict__ cbox, uint32_t *oseed, uint32_t *osize,
+                  uint32_t *obox, const Counters *cnt) {
   __shared__ uint32_t sk[256];
   const uint32_t n = min(cnt->n_comp, S.comp_cap);
   for (uint32_t i0 = blockIdx.x * 256; i0 < n; i0 += gridDim.x * 256) {
@@ -750,6 +859,7 @@ comp_order_kernel(const SearchParams S, const uint32_t *__restrict__ ckey, const
     if (i < n) {
       oseed[r] = cseed[i];
       osize[r] = csize[i];
+      reinterpret_cast<uint4 *>(obox)[r] = reinterpret_cast<const uint4 *>(cbox)[i];
     }
   }
 }
@@ -796,7 +906,7 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
   const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
   if (cnt->overflow) return;
   for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
-    if (S.use_smem && osize[comp] <= IW_CELLS) continue;  // replay_smem_kernel took it
+    if (S.use_smem && osize[comp] <= IW_CELLS) continue;  // replay_warp_kernel took it
     uint32_t *out = cells + ocell0[comp];
     const uint32_t seed = oseed[comp];
     if (threadIdx.x == 0) {
@@ -851,94 +961,106 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
 }
 
 
-// The inner wavefront of one component out of shared memory (components of at most IW_CELLS cells; one CTA each).
+// The inner wavefront of one component out of shared memory: one WARP per component (components of at most
+// `max_cells` cells; the launch is repeated per size class so that small components pack many warps per SM).
 // One hash table holds every cell the wavefront has accepted, with the bid that won it: rank(parent) * 8 + slot.  Bids
 // grow from level to level, so "frontier_flag[nbr]" is "the entry's bid is below base * 8", and within a level the
-// smallest bid wins, as in the outer wavefront.  The component's cells are mirrored in shared memory in queue order.
-__global__ void __launch_bounds__(REPLAY_THREADS)
-replay_smem_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ oseed,
-                   const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, uint32_t *cells, const Counters *cnt) {
+// smallest bid wins, as in the outer wavefront.  The component's cells (packed y << 16 | x) are mirrored in shared
+// memory in queue order, and the frontier-mask bits of the component's bounding box (+1 cell) are staged in shared
+// memory when they fit, so a level costs a handful of shared-memory round trips and two __syncwarp.
+__global__ void __launch_bounds__(32)
+replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ oseed,
+                   const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, const uint32_t *__restrict__ obox,
+                   uint32_t *cells, const Counters *cnt, uint32_t min_cells, uint32_t max_cells, uint32_t bit_words) {
   extern __shared__ uint32_t iw_sh[];
-  uint32_t *keys = iw_sh, *val = iw_sh + IW_SLOTS, *mir = iw_sh + 2 * IW_SLOTS;
-  __shared__ uint32_t wsum[REPLAY_THREADS / 32];
+  uint32_t *keys = iw_sh, *val = iw_sh + 2 * max_cells, *mir = iw_sh + 4 * max_cells, *bw = iw_sh + 5 * max_cells;
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
   if (cnt->overflow) return;
-  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  const uint32_t lane = threadIdx.x;
   for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
     const uint32_t size = osize[comp];
-    if (size > IW_CELLS) continue;  // replay_kernel takes it
+    if (size < min_cells || size > max_cells) continue;
     uint32_t lg = 5;
-    while ((1u << lg) < 2u * size) ++lg;  // <= 13
+    while ((1u << lg) < 2u * size) ++lg;
     const uint32_t slots = 1u << lg, smask = slots - 1u;
-    for (uint32_t i = threadIdx.x; i < slots; i += REPLAY_THREADS) { keys[i] = HKEY_EMPTY; val[i] = KEY_INF; }
-    __syncthreads();
+    for (uint32_t i = lane; i < slots; i += 32) { keys[i] = HKEY_EMPTY; val[i] = KEY_INF; }
+    // mask window: rows y0-1 .. y1+1, words of columns x0-1 .. x1+1 (clamped to the map)
+    const uint4 box = reinterpret_cast<const uint4 *>(obox)[comp];
+    const uint32_t wy0 = box.y > 0 ? box.y - 1 : 0, wy1 = min(box.w + 1, H - 1);
+    const uint32_t wx0 = (box.x > 0 ? box.x - 1 : 0) >> 5, wx1 = min(box.z + 1, W - 1) >> 5;
+    const uint32_t ww = wx1 - wx0 + 1, wh = wy1 - wy0 + 1;
+    const bool staged = (uint64_t)ww * wh <= bit_words;
+    if (staged)
+      for (uint32_t i = lane; i < ww * wh; i += 32) {
+        const uint32_t r = i / ww, cw = i - r * ww;
+        bw[i] = __ldg(bits + (size_t)(wy0 + r) * S.wpr + wx0 + cw);
+      }
     uint32_t *out = cells + ocell0[comp];
-    if (threadIdx.x == 0) {
+    if (lane == 0) {
       const uint32_t seed = oseed[comp];
+      const uint32_t sy = seed / W, sx = seed - sy * W;
+      const uint32_t pk = (sy << 16) | sx;
       out[0] = seed;
-      mir[0] = seed;
-      const uint32_t h = hslot(seed, lg);
-      keys[h] = seed;
+      mir[0] = pk;
+      const uint32_t h = hslot(pk, lg);
+      keys[h] = pk;
       val[h] = 0;
     }
-    __syncthreads();
+    __syncwarp();
     uint32_t base = 0, n = 1;
     while (n > 0) {
       const uint32_t next_base = base + n, items = n << 3;
       uint32_t n_next = 0;
-      for (uint32_t tile = 0; tile < items; tile += REPLAY_THREADS) {
-        const uint32_t j = tile + threadIdx.x;
+      for (uint32_t tile = 0; tile < items; tile += 32) {
+        const uint32_t j = tile + lane;
         bool cand = false;
         uint32_t nb = 0, h = 0, mykey = 0;
         if (j < items) {
-          const uint32_t rank = base + (j >> 3);
+          const uint32_t rank = base + (j >> 3), s = j & 7u;
           const uint32_t p = mir[rank];
-          const uint32_t my = p / W, mx = p - my * W;
-          uint32_t nx, ny;
-          if (nbr_of(mx, my, W, H, (int)(j & 7u), nx, ny) && get_bit(bits, S.wpr, nx, ny)) {
-            nb = ny * W + nx;
-            mykey = rank * 8u + (j & 7u);
-            h = hslot(nb, lg);
-            while (true) {
-              uint32_t k = ((volatile uint32_t *)keys)[h];
-              if (k == HKEY_EMPTY) {
-                k = atomicCAS(&keys[h], HKEY_EMPTY, nb);
-                if (k == HKEY_EMPTY) k = nb;
+          // neighbour s in the reference's order: -1, +1, -W, +W, -1-W, -1+W, +1-W, +1+W (DEP/src/Helpers.cpp:185-255)
+          const int ddx = (s == 0 || s == 4 || s == 5) ? -1 : ((s == 1 || s == 6 || s == 7) ? 1 : 0);
+          const int ddy = (s == 2 || s == 4 || s == 6) ? -1 : ((s == 3 || s == 5 || s == 7) ? 1 : 0);
+          const int x = (int)(p & 0xFFFFu) + ddx, y = (int)(p >> 16) + ddy;
+          if (x >= 0 && y >= 0 && x < (int)W && y < (int)H) {
+            const uint32_t word = staged ? bw[((uint32_t)y - wy0) * ww + (((uint32_t)x >> 5) - wx0)]
+                                         : __ldg(bits + (size_t)y * S.wpr + ((uint32_t)x >> 5));
+            if ((word >> ((uint32_t)x & 31u)) & 1u) {
+              nb = ((uint32_t)y << 16) | (uint32_t)x;
+              mykey = rank * 8u + s;
+              h = hslot(nb, lg);
+              while (true) {
+                uint32_t k = ((volatile uint32_t *)keys)[h];
+                if (k == HKEY_EMPTY) {
+                  k = atomicCAS(&keys[h], HKEY_EMPTY, nb);
+                  if (k == HKEY_EMPTY) k = nb;
+                }
+                if (k == nb) break;
+                h = (h + 1u) & smask;
               }
-              if (k == nb) break;
-              h = (h + 1u) & smask;
-            }
-            if (((volatile uint32_t *)val)[h] >= base * 8u) {  // !frontier_flag[nbr]
-              atomicMin(&val[h], mykey);
-              cand = true;
+              if (((volatile uint32_t *)val)[h] >= base * 8u) {  // !frontier_flag[nbr]
+                atomicMin(&val[h], mykey);
+                cand = true;
+              }
             }
           }
         }
-        __syncthreads();
+        __syncwarp();
         const bool win = cand && ((volatile uint32_t *)val)[h] == mykey;
         const uint32_t bal = __ballot_sync(0xffffffffu, win);
-        if (lane == 0) wsum[wid] = __popc(bal);
-        __syncthreads();
-        uint32_t off = __popc(bal & ((1u << lane) - 1u)), total = 0;
-#pragma unroll
-        for (uint32_t w = 0; w < REPLAY_THREADS / 32; ++w) {
-          const uint32_t t = wsum[w];
-          if (w < wid) off += t;
-          total += t;
-        }
         if (win) {
-          const uint32_t dst = next_base + n_next + off;
-          out[dst] = nb;
+          const uint32_t dst = next_base + n_next + __popc(bal & ((1u << lane) - 1u));
+          out[dst] = (nb >> 16) * W + (nb & 0xFFFFu);
           mir[dst] = nb;
         }
-        n_next += total;
-        __syncthreads();
+        n_next += __popc(bal);
+        __syncwarp();
       }
       base = next_base;
       n = n_next;
     }
-    __syncthreads();
+    __syncwarp();
   }
 }
 
@@ -1213,6 +1335,9 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   FS_CUDA(c, s->parent.reserve(s->mask_cap));
   FS_CUDA(c, s->rkey.reserve(s->mask_cap));
   FS_CUDA(c, s->rsize.reserve(s->mask_cap));
+  FS_CUDA(c, s->rbox.reserve(4 * (size_t)s->mask_cap));
+  FS_CUDA(c, s->cbox.reserve(4 * (size_t)s->comp_cap));
+  FS_CUDA(c, s->obox.reserve(4 * (size_t)s->comp_cap));
   FS_CUDA(c, s->ckey.reserve(s->comp_cap));
   FS_CUDA(c, s->cseed.reserve(s->comp_cap));
   FS_CUDA(c, s->csize.reserve(s->comp_cap));
@@ -1247,10 +1372,10 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     const char *e = getenv("FITSLAM_WAVEFRONT");
     s->force_global = (e && !strcmp(e, "global")) ? 1 : 0;
   }
-  S.use_smem = s->force_global ? 0u : 1u;
+  S.use_smem = (s->force_global || c->W > 65535u || c->H > 65535u) ? 0u : 1u;  // queue entries pack y << 16 | x
   if (!s->attr_set) {
     FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
-    FS_CUDA(c, cudaFuncSetAttribute(replay_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)IW_SMEM));
+    FS_CUDA(c, cudaFuncSetAttribute(replay_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iw_smem(IW_CELLS, IW_BITS_LARGE)));
     s->attr_set = true;
   }
   S.min_size = c->prm.min_frontier_cluster_size;
@@ -1265,9 +1390,9 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   const uint64_t n_words = (uint64_t)S.wpr * c->H;
   const unsigned wide = 148 * 8;
   mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
-  uf_init_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rkey.p, s->rsize.p, cnt, S.mask_cap);
+  uf_init_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rkey.p, s->rsize.p, s->rbox.p, cnt, S.mask_cap);
   uf_merge_kernel<<<wide, 256, 0, c->stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
-  uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, cnt, S.mask_cap);
+  uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, s->rbox.p, s->mcell.p, c->W, cnt, S.mask_cap);
   if (!s->have_ev) {
     for (auto &e : s->ev_bfs) FS_CUDA(c, cudaEventCreate(&e));
     s->have_ev = true;
@@ -1280,13 +1405,18 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
   touch_reduce_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, cnt);
-  seed_collect_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->ckey.p,
-                                                    s->cseed.p, s->csize.p, cnt);
-  comp_order_kernel<<<148 * 2, 256, 0, c->stream>>>(S, s->ckey.p, s->cseed.p, s->csize.p, s->oseed.p, s->osize.p, cnt);
+  seed_collect_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->rbox.p,
+                                                    s->ckey.p, s->cseed.p, s->csize.p, s->cbox.p, cnt);
+  comp_order_kernel<<<148 * 2, 256, 0, c->stream>>>(S, s->ckey.p, s->cseed.p, s->csize.p, s->cbox.p, s->oseed.p, s->osize.p,
+                                                     s->obox.p, cnt);
   comp_scan_kernel<<<1, 1024, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, cnt);
   if (S.use_smem) {
-    replay_smem_kernel<<<148 * 2, REPLAY_THREADS, IW_SMEM, c->stream>>>(S, s->bits.p, s->oseed.p, s->osize.p, s->ocell0.p, s->cells.p, cnt);
-    ++c->launches;
+    // large components first (two warps per SM, the long poles), then the small ones on the remaining shared memory
+    replay_warp_kernel<<<148 * 2, 32, iw_smem(IW_CELLS, IW_BITS_LARGE), c->stream>>>(
+        S, s->bits.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, IW_SMALL + 1, IW_CELLS, IW_BITS_LARGE);
+    replay_warp_kernel<<<148 * 16, 32, iw_smem(IW_SMALL, IW_BITS_SMALL), c->stream>>>(
+        S, s->bits.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL);
+    c->launches += 2;
   }
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
                                                             s->cells.p, cnt);  // components above IW_CELLS cells
