@@ -34,6 +34,8 @@ static constexpr int CNT_BITS = 10;         // low bits of a slot: landmarks in 
 static constexpr uint32_t CNT_MASK = (1u << CNT_BITS) - 1u;
 static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding square of the lookup domain)
 static constexpr int FISHER_THREADS = 256;
+static constexpr int CHUNK_PTS = 64;         // points per unit of work
+static constexpr int MAX_CHUNKS = 1536;      // 12 KB of static shared memory
 
 struct M3f { float m[3][3]; };
 struct V3f { float v[3]; };
@@ -549,6 +551,7 @@ struct FisherParams {
   int dims[3], org[3];
   const double *crowd;
   double inv_step;      // 1 / (double)step_max, the factor getVoxelCoordinate multiplies by
+  float inv_step_f;     // the same in float: prefilter of the rounding, see voxel_of_point
   double step;
   double reach;         // lut_reach()
   double threshold;
@@ -632,18 +635,30 @@ __device__ __forceinline__ int voxel_of_point(const float4 q, const PoseFrame &F
   const float v = P.fy * Yc / Zc + P.cy;
   if (u < 0.0f || u > P.max_u) return -1;         // :295-300
   if (v < 0.0f || v > P.max_v) return -1;
-  // rgbd-slam-node.cpp:419-425: vector3fORBToROS, then inverse(pose) * position
-  V3f pos; pos.v[0] = dot3(0.f, Pw.v[0], 0.f, Pw.v[1], 1.f, Pw.v[2]);
-  pos.v[1] = dot3(-1.f, Pw.v[0], 0.f, Pw.v[1], 0.f, Pw.v[2]);
-  pos.v[2] = dot3(0.f, Pw.v[0], -1.f, Pw.v[1], 0.f, Pw.v[2]);
+  // rgbd-slam-node.cpp:419-425: vector3fORBToROS, then inverse(pose) * position.  vector3fORBToROS multiplies by a signed
+  // permutation matrix, 0*a + (0*b + 1*c): for finite inputs that is the original ROS triple again (up to the sign of a
+  // zero, which cannot change a voxel index)
+  V3f pos; pos.v[0] = q.x; pos.v[1] = q.y; pos.v[2] = q.z;
   const V3f lp = mulv(F.Rinv, pos);
   int idx[3];
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     const float c = lp.v[a] + F.tinv.v[a];
-    const double r = round((double)c * P.inv_step);  // getVoxelCoordinate (FisherInfoManager.hpp:108-123)
-    if (!(r >= (double)P.org[a] && r < (double)(P.org[a] + P.dims[a]))) return -1;  // also rejects NaN
-    idx[a] = (int)r - P.org[a];
+    // getVoxelCoordinate (FisherInfoManager.hpp:108-123): round((double)c * (1 / (double)step)).  The float product is
+    // within 1.3e-4 of the double one while |c / step| < 1000, so away from a half-integer both round to the same index;
+    // only the remaining cases take the double path.
+    const float rf = c * P.inv_step_f;
+    const float ri = rintf(rf);
+    int r;
+    if (fabsf(rf - ri) < 0.49f && fabsf(rf) < 1000.0f) {
+      r = (int)ri;
+    } else {
+      const double rd = round((double)c * P.inv_step);
+      if (!(rd >= -2147483000.0 && rd <= 2147483000.0)) return -1;  // also rejects NaN
+      r = (int)rd;
+    }
+    if (r < P.org[a] || r >= P.org[a] + P.dims[a]) return -1;
+    idx[a] = r - P.org[a];
   }
   const int lin = (idx[0] * P.dims[1] + idx[1]) * P.dims[2] + idx[2];
   if (P.lut_dense) return lin;
@@ -657,7 +672,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
               const fitslam_arrival *__restrict__ arrival) {
   __shared__ PoseFrame F;
   extern __shared__ uint32_t tab[];  // HASH_SLOTS packed slots: (voxel + 1) << CNT_BITS | count, 0 = empty
-  __shared__ uint32_t s_used, s_overflow;
+  __shared__ uint32_t s_used, s_overflow, s_nchunk, s_next, s_chunk_ovf;
+  __shared__ uint2 s_chunk[MAX_CHUNKS];  // [first, last) point ranges of the bins that survive the cull
   __shared__ double s_red[FISHER_THREADS / 32];
   const uint32_t pi = P.first + blockIdx.x;
   if (pi >= P.n_poses) return;
@@ -672,6 +688,57 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   const int n_sq = (sq_w > 0 && sq_h > 0) ? sq_w * sq_h : 0;
   const double margin = 0.05 + 1e-4 * (fabs((double)F.px) + fabs((double)F.py));
 
+  // ---- cull the bins once, and cut the surviving ones into chunks of at most CHUNK_PTS points: the chunk list is
+  // the unit of work the warps pull from a shared counter, so a warp that met empty or culled bins takes more chunks
+  // (a static bins-per-warp split left half of the warps waiting at the barrier)
+  for (uint32_t chunk_pts = CHUNK_PTS;; chunk_pts <<= 1) {  // a very dense cloud overflows the list: coarser chunks then
+  if (threadIdx.x == 0) { s_nchunk = 0; s_chunk_ovf = 0; }
+  __syncthreads();
+  for (int b0 = (int)wid * 32; b0 < n_sq; b0 += (int)nw * 32) {
+    const int b = b0 + (int)lane;
+    uint32_t start = 0, end = 0;
+    bool keep = false;
+    if (b < n_sq) {
+      const int bx = bx_lo + b % sq_w, by = by_lo + b / sq_w;
+      const uint32_t bi = (uint32_t)by * g.nbx + bx;
+      start = __ldg(P.bin_start + bi);
+      end = __ldg(P.bin_start + bi + 1);
+      if (end > start) {
+        // clamped edge bins also hold points outside their nominal square: open the box on that side
+        const double x0 = bx == 0 ? -1e30 : (double)g.x0 + bx * (double)g.size, x1 = bx == g.nbx - 1 ? 1e30 : (double)g.x0 + (bx + 1) * (double)g.size;
+        const double y0 = by == 0 ? -1e30 : (double)g.y0 + by * (double)g.size, y1 = by == g.nby - 1 ? 1e30 : (double)g.y0 + (by + 1) * (double)g.size;
+        keep = true;
+#pragma unroll 1
+        for (int k = 0; k < 11 && keep; ++k) {
+          const double nx = F.plane[k][0], ny = F.plane[k][1], nz = F.plane[k][2];
+          const double mx = fmax(nx * x0, nx * x1) + fmax(ny * y0, ny * y1) + fmax(nz * (double)P.zmin, nz * (double)P.zmax) + F.plane[k][3];
+          if (mx < -margin) keep = false;
+        }
+      }
+    }
+    const uint32_t nch = keep ? (end - start + chunk_pts - 1) / chunk_pts : 0u;
+    uint32_t incl = nch;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t base = 0;
+    if (lane == 31 && tot) base = atomicAdd(&s_nchunk, tot);
+    base = __shfl_sync(0xffffffffu, base, 31) + incl - nch;
+    for (uint32_t k = 0; k < nch; ++k) {
+      if (base + k < MAX_CHUNKS) s_chunk[base + k] = make_uint2(start + k * chunk_pts, min(end, start + (k + 1) * chunk_pts));
+      else s_chunk_ovf = 1;
+    }
+  }
+  __syncthreads();
+  const bool again = s_chunk_ovf != 0 && chunk_pts < (1u << 30);
+  __syncthreads();
+  if (!again) break;
+  }
+  const uint32_t n_chunk = min(s_nchunk, (uint32_t)MAX_CHUNKS);
+
   double total = 0.0;
   uint32_t used = 0;
   // Attempt 1 inserts every contributing landmark into one table.  If the table fills up (more occupied voxels than
@@ -683,57 +750,36 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
     if (threadIdx.x == 0) { s_used = 0; s_overflow = 0; }
     for (uint32_t pass = 0; pass < npass; ++pass) {
       for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) tab[i] = 0;
+      if (threadIdx.x == 0) s_next = 0;
       __syncthreads();
       uint32_t my_used = 0;
-      for (int b0 = (int)wid * 32; b0 < n_sq; b0 += (int)nw * 32) {
-        const int b = b0 + (int)lane;
-        bool keep = false;
-        uint32_t start = 0, end = 0;
-        if (b < n_sq) {
-          const int bx = bx_lo + b % sq_w, by = by_lo + b / sq_w;
-          const uint32_t bi = (uint32_t)by * g.nbx + bx;
-          start = __ldg(P.bin_start + bi);
-          end = __ldg(P.bin_start + bi + 1);
-          if (end > start) {
-            // clamped edge bins also hold points outside their nominal square: open the box on that side
-            const double x0 = bx == 0 ? -1e30 : (double)g.x0 + bx * (double)g.size, x1 = bx == g.nbx - 1 ? 1e30 : (double)g.x0 + (bx + 1) * (double)g.size;
-            const double y0 = by == 0 ? -1e30 : (double)g.y0 + by * (double)g.size, y1 = by == g.nby - 1 ? 1e30 : (double)g.y0 + (by + 1) * (double)g.size;
-            keep = true;
-#pragma unroll 1
-            for (int k = 0; k < 11 && keep; ++k) {
-              const double nx = F.plane[k][0], ny = F.plane[k][1], nz = F.plane[k][2];
-              const double mx = fmax(nx * x0, nx * x1) + fmax(ny * y0, ny * y1) + fmax(nz * (double)P.zmin, nz * (double)P.zmax) + F.plane[k][3];
-              if (mx < -margin) keep = false;
+      while (true) {
+        uint32_t ci = 0;
+        if (lane == 0) ci = atomicAdd(&s_next, 1u);
+        ci = __shfl_sync(0xffffffffu, ci, 0);
+        if (ci >= n_chunk) break;
+        const uint2 ch = s_chunk[ci];
+        for (uint32_t i = ch.x + lane; i < ch.y; i += 32) {
+          const int vox = voxel_of_point(__ldg(P.pts + i), F, P);
+          if (vox < 0) continue;
+          const uint32_t h = mix32((uint32_t)vox);
+          if (npass > 1 && ((h >> 12) & (npass - 1)) != pass) continue;
+          ++my_used;
+          if (*v_overflow) continue;  // this attempt is lost: keep counting only
+          uint32_t slot = h & (HASH_SLOTS - 1);
+          bool done = false;
+          const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
+          for (int probe = 0; probe < 256; ++probe) {
+            const uint32_t prev = atomicCAS(&tab[slot], 0u, key | 1u);
+            if (prev == 0u) { done = true; break; }
+            if ((prev & ~CNT_MASK) == key) {
+              if ((prev & CNT_MASK) < CNT_MASK - 256u) atomicAdd(&tab[slot], 1u);  // saturates far above CROWD_MAX
+              done = true;
+              break;
             }
+            slot = (slot + 1) & (HASH_SLOTS - 1);
           }
-        }
-        uint32_t live = __ballot_sync(0xffffffffu, keep);
-        while (live) {
-          const int src = __ffs(live) - 1;
-          live &= live - 1;
-          const uint32_t s = __shfl_sync(0xffffffffu, start, src), e = __shfl_sync(0xffffffffu, end, src);
-          for (uint32_t i = s + lane; i < e; i += 32) {
-            const int vox = voxel_of_point(__ldg(P.pts + i), F, P);
-            if (vox < 0) continue;
-            const uint32_t h = mix32((uint32_t)vox);
-            if (npass > 1 && ((h >> 12) & (npass - 1)) != pass) continue;
-            ++my_used;
-            if (*v_overflow) continue;  // this attempt is lost: keep counting only
-            uint32_t slot = h & (HASH_SLOTS - 1);
-            bool done = false;
-            for (int probe = 0; probe < 256; ++probe) {
-              const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
-              const uint32_t prev = atomicCAS(&tab[slot], 0u, key | 1u);
-              if (prev == 0u) { done = true; break; }
-              if ((prev & ~CNT_MASK) == key) {
-                if ((prev & CNT_MASK) < CNT_MASK - 256u) atomicAdd(&tab[slot], 1u);  // saturates far above CROWD_MAX
-                done = true;
-                break;
-              }
-              slot = (slot + 1) & (HASH_SLOTS - 1);
-            }
-            if (!done) *v_overflow = 1;
-          }
+          if (!done) *v_overflow = 1;
         }
       }
       if (my_used) atomicAdd(&s_used, my_used);
@@ -801,6 +847,7 @@ fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, 
   P.crowd = f->crowd.p;
   P.step = (double)c->prm.voxel_step;
   P.inv_step = 1 / P.step;
+  P.inv_step_f = (float)P.inv_step;
   P.reach = lut_reach(c);
   P.threshold = c->prm.fisher_information_threshold;
   P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
