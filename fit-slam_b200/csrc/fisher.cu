@@ -20,6 +20,7 @@
 #include "ctx.h"
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -35,7 +36,7 @@ static constexpr uint32_t CNT_MASK = (1u << CNT_BITS) - 1u;
 static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding square of the lookup domain)
 static constexpr int FISHER_THREADS = 256;
 static constexpr int CHUNK_PTS = 64;         // points per unit of work
-static constexpr int MAX_CHUNKS = 1536;      // 12 KB of static shared memory
+static constexpr int MAX_CHUNKS = 768;       // 6 KB of static shared memory (three CTAs per SM with the 64 KB table)
 
 struct M3f { float m[3][3]; };
 struct V3f { float v[3]; };
@@ -625,45 +626,68 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
   return x;
 }
 
-// voxel of one map point as seen from the pose: -1 if culled, outside the table or a NaN entry
-__device__ __forceinline__ int voxel_of_point(const float4 q, const PoseFrame &F, const FisherParams &P) {
+// ORBSLAM3Interface::mapPointsVisibleFromPose for one map point: in front of the camera and inside the image
+// (orb_slam3_interface.cpp:286-300, Pinhole.cpp:43-49)
+__device__ __forceinline__ bool point_visible(const float4 q, const PoseFrame &F, const FisherParams &P) {
   V3f Pw; Pw.v[0] = -q.y; Pw.v[1] = -q.z; Pw.v[2] = q.x;  // ROS map axes -> ORB world axes
   const V3f RP = mulv(F.Rcw, Pw);
   const float Xc = RP.v[0] + F.tcw.v[0], Yc = RP.v[1] + F.tcw.v[1], Zc = RP.v[2] + F.tcw.v[2];
-  if (Zc < 0.0f) return -1;                       // orb_slam3_interface.cpp:286-289
-  const float u = P.fx * Xc / Zc + P.cx;          // Pinhole.cpp:43-49
+  if (Zc < 0.0f) return false;
+  const float u = P.fx * Xc / Zc + P.cx;
   const float v = P.fy * Yc / Zc + P.cy;
-  if (u < 0.0f || u > P.max_u) return -1;         // :295-300
-  if (v < 0.0f || v > P.max_v) return -1;
+  return !(u < 0.0f || u > P.max_u) && !(v < 0.0f || v > P.max_v);
+}
+
+// voxel of a visible map point in the pose frame: -1 if outside the table or a NaN entry
+__device__ __forceinline__ int voxel_of_visible_point(const float4 q, const PoseFrame &F, const FisherParams &P) {
   // rgbd-slam-node.cpp:419-425: vector3fORBToROS, then inverse(pose) * position.  vector3fORBToROS multiplies by a signed
   // permutation matrix, 0*a + (0*b + 1*c): for finite inputs that is the original ROS triple again (up to the sign of a
   // zero, which cannot change a voxel index)
   V3f pos; pos.v[0] = q.x; pos.v[1] = q.y; pos.v[2] = q.z;
   const V3f lp = mulv(F.Rinv, pos);
   int idx[3];
+  bool ok = true;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
     const float c = lp.v[a] + F.tinv.v[a];
     // getVoxelCoordinate (FisherInfoManager.hpp:108-123): round((double)c * (1 / (double)step)).  The float product is
-    // within 1.3e-4 of the double one while |c / step| < 1000, so away from a half-integer both round to the same index;
-    // only the remaining cases take the double path.
+    // within 2^-23 |c / step| < 6.2e-5 of the double one while |c / step| < 512, so farther than 1e-4 from a
+    // half-integer both round to the same index; only the remaining cases (2 in 10^4) take the double path.
     const float rf = c * P.inv_step_f;
     const float ri = rintf(rf);
     int r;
-    if (fabsf(rf - ri) < 0.49f && fabsf(rf) < 1000.0f) {
+    if (fabsf(rf - ri) < 0.4999f && fabsf(rf) < 512.0f) {
       r = (int)ri;
     } else {
       const double rd = round((double)c * P.inv_step);
-      if (!(rd >= -2147483000.0 && rd <= 2147483000.0)) return -1;  // also rejects NaN
-      r = (int)rd;
+      r = (rd >= -2147483000.0 && rd <= 2147483000.0) ? (int)rd : INT_MIN;  // also rejects NaN
     }
-    if (r < P.org[a] || r >= P.org[a] + P.dims[a]) return -1;
+    ok = ok && r >= P.org[a] && r < P.org[a] + P.dims[a];
     idx[a] = r - P.org[a];
   }
+  if (!ok) return -1;
   const int lin = (idx[0] * P.dims[1] + idx[1]) * P.dims[2] + idx[2];
   if (P.lut_dense) return lin;
   const float val = __ldg(P.lut + lin);
   return (val == val) ? lin : -1;
+}
+
+// count one landmark in its voxel: packed slot (voxel + 1) << CNT_BITS | count; plain loads walk the probe sequence and
+// only the claiming / counting step is an atomic (shared-memory atomics cost 2-4 cycles per LANE on this part)
+__device__ __forceinline__ bool table_count(uint32_t *tab, uint32_t h, int vox) {
+  uint32_t slot = h & (HASH_SLOTS - 1);
+  const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
+  for (int probe = 0; probe < 256; ++probe) {
+    uint32_t prev = ((volatile uint32_t *)tab)[slot];
+    if (prev == 0u) prev = atomicCAS(&tab[slot], 0u, key | 1u);
+    if (prev == 0u) return true;
+    if ((prev & ~CNT_MASK) == key) {
+      if ((prev & CNT_MASK) < CNT_MASK - 256u) atomicAdd(&tab[slot], 1u);  // saturates far above CROWD_MAX
+      return true;
+    }
+    slot = (slot + 1) & (HASH_SLOTS - 1);
+  }
+  return false;
 }
 
 __global__ void __launch_bounds__(FISHER_THREADS)
@@ -674,6 +698,7 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   extern __shared__ uint32_t tab[];  // HASH_SLOTS packed slots: (voxel + 1) << CNT_BITS | count, 0 = empty
   __shared__ uint32_t s_used, s_overflow, s_nchunk, s_next, s_chunk_ovf;
   __shared__ uint2 s_chunk[MAX_CHUNKS];  // [first, last) point ranges of the bins that survive the cull
+  __shared__ uint32_t s_wq[FISHER_THREADS / 32][64];  // per warp: indices of visible points waiting for the voxel step
   __shared__ double s_red[FISHER_THREADS / 32];
   const uint32_t pi = P.first + blockIdx.x;
   if (pi >= P.n_poses) return;
@@ -753,34 +778,43 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
       if (threadIdx.x == 0) s_next = 0;
       __syncthreads();
       uint32_t my_used = 0;
+      // Two steps per point, with a compaction in between: the visibility test runs on every point of the chunk, the
+      // indices of the visible ones (about 4 in 10) queue up per warp, and the voxel + table step runs on full warps.
+      uint32_t *wq = s_wq[wid];
+      uint32_t n_q = 0;
       while (true) {
         uint32_t ci = 0;
         if (lane == 0) ci = atomicAdd(&s_next, 1u);
         ci = __shfl_sync(0xffffffffu, ci, 0);
-        if (ci >= n_chunk) break;
-        const uint2 ch = s_chunk[ci];
-        for (uint32_t i = ch.x + lane; i < ch.y; i += 32) {
-          const int vox = voxel_of_point(__ldg(P.pts + i), F, P);
-          if (vox < 0) continue;
-          const uint32_t h = mix32((uint32_t)vox);
-          if (npass > 1 && ((h >> 12) & (npass - 1)) != pass) continue;
-          ++my_used;
-          if (*v_overflow) continue;  // this attempt is lost: keep counting only
-          uint32_t slot = h & (HASH_SLOTS - 1);
-          bool done = false;
-          const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
-          for (int probe = 0; probe < 256; ++probe) {
-            const uint32_t prev = atomicCAS(&tab[slot], 0u, key | 1u);
-            if (prev == 0u) { done = true; break; }
-            if ((prev & ~CNT_MASK) == key) {
-              if ((prev & CNT_MASK) < CNT_MASK - 256u) atomicAdd(&tab[slot], 1u);  // saturates far above CROWD_MAX
-              done = true;
-              break;
+        const bool last = ci >= n_chunk;
+        const uint2 ch = last ? make_uint2(0, 0) : s_chunk[ci];
+        for (uint32_t i0 = ch.x; i0 < ch.y || (last && n_q > 0); i0 += 32) {
+          const uint32_t i = i0 + lane;
+          const bool vis = i < ch.y && point_visible(__ldg(P.pts + i), F, P);
+          const uint32_t bal = __ballot_sync(0xffffffffu, vis);
+          if (vis) wq[n_q + __popc(bal & ((1u << lane) - 1u))] = i;
+          n_q += __popc(bal);
+          __syncwarp();
+          if (n_q >= 32 || (last && n_q > 0)) {
+            const uint32_t take = min(n_q, 32u);
+            int vox = -1;
+            if (lane < take) vox = voxel_of_visible_point(__ldg(P.pts + wq[lane]), F, P);
+            const uint32_t rest = n_q - take;
+            const uint32_t moved = lane < rest ? wq[32 + lane] : 0u;
+            __syncwarp();
+            if (lane < rest) wq[lane] = moved;
+            n_q = rest;
+            __syncwarp();
+            if (vox >= 0) {
+              const uint32_t h = mix32((uint32_t)vox);
+              if (npass == 1 || ((h >> 12) & (npass - 1)) == pass) {
+                ++my_used;
+                if (!*v_overflow && !table_count(tab, h, vox)) *v_overflow = 1;  // a lost attempt keeps counting only
+              }
             }
-            slot = (slot + 1) & (HASH_SLOTS - 1);
           }
-          if (!done) *v_overflow = 1;
         }
+        if (last) break;
       }
       if (my_used) atomicAdd(&s_used, my_used);
       __syncthreads();
