@@ -125,6 +125,7 @@ def run_gpu(args):
     import torch
     import torch.distributed as dist
     pkg, capi, synth = load()
+    shard = importlib.import_module("fitslam_b200.shard")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -159,9 +160,8 @@ def run_gpu(args):
             st, F = ctx.cycle_begin(rx, ry, ryaw, poly, mode)
             assert st == 0, st
             rec = ctx.records_tensor()
-            B = rec.shape[0] // world
             with torch.cuda.stream(stream):  # NCCL orders itself after the scoring kernels of this stream
-                dist.all_gather_into_tensor(rec, rec[rank * B:(rank + 1) * B])
+                shard.allgather_records_(rec, rank, world)
             res = ctx.cycle_end()
         last["res"] = res
         return res
