@@ -3,7 +3,7 @@
  *
  * This is the drop-in boundary.  Every entry point below
  * replaces one public method of the reference's `frontier_exploration` C++
- * classes; the header-only C++ classes under fit-slam_b200/cpp/ wrap these
+ * classes; the header-only C++ classes under fit-slam_b200/cpp/frontier_exploration_cuda.hpp wrap these
  * calls behind the reference's own signatures.  Plain pointers and sizes only:
  * no STL, no torch types, no exceptions across the boundary.
  *
