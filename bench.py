@@ -233,12 +233,18 @@ def run_gpu(args):
     ab = algorithmic_bytes(W, H, F, n_rays, max_len, len(pts))
     stage_names = ["extract", "arrival", "distance", "fisher", "normalise_select", "begin_total", "end_total", "outer_wavefront_kernel"]
     stage_ms = {n: float(v) for n, v in zip(stage_names, stages)}
-    # the outer wavefront kernel (rank_bfs_kernel) dominates the cycle; its algorithmic traffic is the searched map
+    # the outer wavefront kernel (rank_bfs_smem_kernel) dominates the cycle; its algorithmic traffic is the searched map.
+    # `traffic`: dram__bytes_read.sum + dram__bytes_write.sum of that kernel from the committed ncu --set full capture
     dom_ms = stage_ms["outer_wavefront_kernel"]
-    roof = {"bound": "hbm", "kernel": "rank_bfs_kernel (inside stage extract)", "achieved": ab["extract"] / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None,
-            "peak": peak, "unit": "GB/s", "peak_source": "measured" if peaks else "fallback", "traffic": None,
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json"))).get("rank_bfs_smem_kernel")
+    except Exception:
+        pass
+    roof = {"bound": "hbm", "kernel": "rank_bfs_smem_kernel (inside stage extract)", "achieved": ab["extract"] / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None,
+            "peak": peak, "unit": "GB/s", "peak_source": "measured" if peaks else "fallback", "traffic": traffic,
             "algorithmic_bytes_per_launch": ab["extract"], "kernel_ms": dom_ms,
-            "note": "latency-bound level-synchronous wavefront (one CTA): see DESIGN.md; per-stage fractions below",
+            "note": "latency-bound level-synchronous wavefront (one CTA, 2205 dependent levels): see DESIGN.md; per-stage fractions below",
             "stages": {n: {"ms": stage_ms[n], "algorithmic_bytes": ab[k2], "gbs": ab[k2] / (stage_ms[n] * 1e-3) / 1e9 if stage_ms[n] > 0 else None}
                        for n, k2 in (("extract", "extract"), ("arrival", "arrival"), ("fisher", "fisher"), ("normalise_select", "select"))}}
     roof["frac"] = roof["achieved"] / peak if roof["achieved"] else None

@@ -19,8 +19,10 @@
 // other neighbours; no atomics, no sort) and an order-preserving block scan appends the winners to the queue.
 #include "ctx.h"
 
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -38,13 +40,13 @@ static constexpr uint32_t INNER_BIT = 0x40000000u;
 static constexpr uint32_t TOUCH_BIT = 0x80000000u;
 static constexpr uint32_t MAX_RANK = (1u << 29) - 2;
 static constexpr int BFS_THREADS = 1024;
+static constexpr int OW_THREADS = 1024;      // shared-memory outer wavefront: two threads per queue position, 512 positions per pass
 static constexpr int REPLAY_THREADS = 128;
 static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
 // shared-memory wavefronts (the default path; the global-memory kernels below them are the fallback for levels or
 // components that do not fit)
-static constexpr uint32_t OW_SLOTS = 8192;   // outer wavefront: slots of the per-level bid table (cell, bid, directions)
-static constexpr uint32_t OW_QCAP = 4096;    // outer wavefront: widest level the shared-memory path holds (load factor 1/2)
-static constexpr uint32_t OW_SMEM = (3 * OW_SLOTS + 2 * OW_QCAP) * 4 + 2 * OW_QCAP;
+static constexpr uint32_t OW_QCAP = 8192;    // outer wavefront: widest level the shared-memory queue holds (80 KB; the rest of the SM's 256 KB stays L1)
+static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 4 + 2 * OW_QCAP;
 static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
 static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells (many warps per SM), <= IW_CELLS cells (two per SM)
 static constexpr uint32_t IW_BITS_SMALL = 1024, IW_BITS_LARGE = 8192;  // words of the component's mask window held in shared memory
@@ -63,8 +65,10 @@ struct Counters {
   uint32_t expanded;       // reachable cells dequeued by the outer wavefront
   uint32_t visited;        // queue entries + far cells (cleanup bound)
   uint32_t dirty_queue;    // entries of queue[] whose claim words (and their 4 neighbours') the cleanup must reset
-  uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rerun with the global-memory kernel
-  uint32_t pad[4];
+  uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rank_bfs_kernel resumes there
+  uint32_t resume_base, resume_n, resume_levels;
+  uint32_t pad[1];
+  unsigned long long prof[8];  // FITSLAM_PROF: cycles of warp 0 per phase of the outer wavefront
 };
 
 struct SearchParams {
@@ -78,6 +82,7 @@ struct SearchParams {
   int32_t min_size, max_size;
   uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
   uint32_t use_smem;       // 1: shared-memory wavefronts first, global-memory kernels only for what does not fit
+  uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
 };
 
 struct FrontierState {
@@ -209,7 +214,7 @@ __global__ void __launch_bounds__(256) mask_kernel(const SearchParams S, uint32_
     }
     bits[gid] = word;
     trav[gid] = tword;
-    tm[gid] = make_uint2(tword, word);
+    tm[((size_t)(my >> 3) * S.wpr + (mx0 >> 5)) * 8u + (my & 7u)] = make_uint2(tword, word);  // tm_index layout
   }
   // append the set cells to the list: one atomicAdd per warp
   const uint32_t lane = threadIdx.x & 31u;
@@ -367,7 +372,7 @@ __device__ void nearest_free_cell(const SearchParams &S, uint32_t *claim, uint32
   while (n > 0) {
     if (threadIdx.x == 0) *s_min = KEY_INF;
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < n; i += BFS_THREADS) {
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
       const uint32_t c = q[i];
       const uint32_t my = c / W, mx = c - my * W;
       if (S.map.data[(size_t)my * S.map.pitch + mx] < S.lethal) atomicMin(s_min, i);
@@ -379,7 +384,7 @@ __device__ void nearest_free_cell(const SearchParams &S, uint32_t *claim, uint32
       break;
     }
     const uint32_t total = n << 3;
-    for (uint32_t j = threadIdx.x; j < total; j += BFS_THREADS) {
+    for (uint32_t j = threadIdx.x; j < total; j += blockDim.x) {
       const uint32_t c = q[j >> 3];
       const uint32_t my = c / W, mx = c - my * W;
       uint32_t nx, ny;
@@ -390,7 +395,7 @@ __device__ void nearest_free_cell(const SearchParams &S, uint32_t *claim, uint32
     __threadfence();
     __syncthreads();
     uint32_t n_next = 0;
-    for (uint32_t j0 = 0; j0 < total; j0 += BFS_THREADS) {
+    for (uint32_t j0 = 0; j0 < total; j0 += blockDim.x) {
       const uint32_t j = j0 + threadIdx.x;
       bool push = false;
       uint32_t nb = 0;
@@ -423,7 +428,7 @@ __device__ void nearest_free_cell(const SearchParams &S, uint32_t *claim, uint32
   const uint32_t sy = start / W, sx = start - sy * W;
   const int r = (int)levels + 1;
   const long side = 2 * r + 1;
-  for (long i = threadIdx.x; i < side * side; i += BFS_THREADS) {
+  for (long i = threadIdx.x; i < side * side; i += blockDim.x) {
     const int y = (int)sy - r + (int)(i / side), x = (int)sx - r + (int)(i % side);
     if (x >= 0 && y >= 0 && x < (int)W && y < (int)H) claim[(size_t)y * W + x] = KEY_INF;
   }
@@ -443,28 +448,35 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   __shared__ uint32_t s_start;
   if (cnt->overflow) return;
   if (S.use_smem && !cnt->ow_fallback) return;  // the shared-memory wavefront finished the search
+  const bool resume = S.use_smem != 0;
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
   if (threadIdx.x == 0) s_start = S.robot_cell;  // falls back to pos when no cell qualifies (FrontierSearch.cpp:47-54)
   __syncthreads();
-  if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+  if (!resume && S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
     nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh, cnt, &s_start);
     __syncthreads();
   }
-  const uint32_t start = s_start;
-  if (threadIdx.x == 0) {
-    cnt->start_cell = start;
-    queue[0] = start;
-    claim[start] = 0;
-  }
-  __syncthreads();
   // The current level's cells are mirrored in shared memory (first SQ entries), so that the common narrow level costs
   // two global round trips (neighbour bits + claims, then the claims of the neighbours' neighbours) instead of three.
   constexpr uint32_t SQ = 2048;
   __shared__ uint32_t sq[2][SQ];
-  if (threadIdx.x == 0) sq[0][0] = start;
-  __syncthreads();
   uint32_t base = 0, n = 1, levels = 0, cur = 0;
+  if (resume) {  // take over from rank_bfs_smem_kernel: queue[] and claim[] are complete up to the level that did not fit
+    base = cnt->resume_base;
+    n = cnt->resume_n;
+    levels = cnt->resume_levels;
+    for (uint32_t i = threadIdx.x; i < min(n, SQ); i += BFS_THREADS) sq[0][i] = ld_cg(queue + base + i);
+  } else {
+    const uint32_t start = s_start;
+    if (threadIdx.x == 0) {
+      cnt->start_cell = start;
+      queue[0] = start;
+      claim[start] = 0;
+      sq[0][0] = start;
+    }
+  }
+  __syncthreads();
   const int dxs[4] = {-1, 1, 0, 0}, dys[4] = {0, 0, -1, 1};
   while (n > 0) {
     const uint32_t next_base = base + n;
@@ -561,152 +573,137 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
 // Multiplicative hash of a cell index into a table of 2^bits slots.
 __device__ __forceinline__ uint32_t hslot(uint32_t cell, uint32_t bits) { return (cell * 0x9E3779B1u) >> (32u - bits); }
 
-// The outer wavefront with all of its dynamic state in shared memory (the default path).
-//   * Who visits an unvisited cell first: every dequeued cell bids (queue position * 4 + slot) for each traversable
-//     neighbour it may visit into a per-level hash table with atomicMin; after a barrier the bidder that still owns the
-//     minimum is the one the reference's FIFO order would have let through.  Winners are appended in bid order by a block
-//     scan, which is the order the reference pushes them.
-//   * No visited array: the 4-connected grid is bipartite, so a neighbour of a level-d cell is on level d-1 or d+1.
-//     EVERY level-(d-1) neighbour of a cell bids for it, so the directions the bids came from (OR-ed into the table entry
-//     and carried with the queue entry) are exactly the cell's visited neighbours; every other traversable neighbour is
-//     unvisited.  A cell beyond the search radius needs no state at all (testing it again gives the same answer).
-//   * The level's cells (packed y << 16 | x) live in a shared-memory queue; the read-only class bits come through L1
-//     (three 8-byte loads per cell).  The only global writes are the first-touch keys of frontier-mask cells.
-// A level wider than OW_QCAP (or a table that fills up) sets ow_fallback and the global-memory kernel above reruns the search.
-struct OwShared {
-  uint32_t *keys, *val, *dmask;   // OW_SLOTS each: cell, smallest bid, directions the bids came from
-  uint32_t *q[2];                 // OW_QCAP each
-  uint8_t *qm[2];                 // OW_QCAP each: visited-neighbour directions of the queue entry
-  uint32_t *wsum;                 // 2 x 32 warp totals (alternating, so the scan needs one barrier)
+// class words {traversable, frontier mask} of 32 cells: rows are interleaved in groups of 8 so that the three rows a
+// cell needs share a 64-byte chunk, and the ring of a wavefront level stays inside L1 from one level to the next
+__host__ __device__ __forceinline__ size_t tm_index(uint32_t wx, uint32_t y, uint32_t wpr) {
+  return ((size_t)(y >> 3) * wpr + wx) * 8u + (y & 7u);
+}
+
+// The outer wavefront, default path.  Same decision rule as rank_bfs_kernel above (a dequeued cell p visits a
+// traversable, unvisited neighbour c iff no other neighbour of c was dequeued before p in this level), with the work
+// per level cut to what that rule needs:
+//   * the level's cells (packed y << 16 | x) live in a shared-memory queue, with the directions of their visited
+//     neighbours next to them.  The 4-connected grid is bipartite, so a neighbour of a level-d cell is on level d-1 or d+1;
+//     the level-(d-1) neighbours of a cell are exactly the cells that competed for it, which its winner saw while
+//     deciding.  So "visited_flag[nbr]" is a 4-bit mask carried with the queue entry: no visited array, no load.
+//   * the read-only class bits come through L1, three 8-byte loads per cell (rows above / at / below, tm_index layout).
+//   * only the ranks of a candidate's three other neighbours are read from global memory (claim[], L2): about four 4-byte
+//     loads per dequeued cell, all independent, against 28 for the kernel above.  A shared-memory bid table with atomicMin
+//     was tried first and lost: shared-memory atomics retire at about 2 cycles per LANE on this part, so three atomics
+//     per bid cost more than the L2 round trip they avoided (profiles/README.md, v4/v5).
+//   * a cell beyond the search radius needs no state at all (testing it again gives the same answer).
+//   * two threads share a queue position (one per axis), so the dependent instruction chain of a level, which is what
+//     bounds it (clock64 breakdown in profiles/README.md), is half as long, thread order is still bid order, and the
+//     winner counts are 0..2 per thread: the block scan is two ballots per warp.
+// Two barriers per pass.  A level wider than ow_qcap sets ow_fallback and rank_bfs_kernel resumes the search from the
+// global queue at that level.
+struct OwQueues {
+  uint32_t *q0, *q1;
+  uint8_t *qm0, *qm1;
 };
 
-template <int K>
-__device__ __forceinline__ uint32_t ow_level(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, const OwShared &sh,
-                                            uint32_t cur, uint32_t base, uint32_t n, uint32_t rx, uint32_t ry, uint32_t level,
-                                            uint32_t *s_abort) {
-  constexpr uint32_t SMASK = OW_SLOTS - 1;
-  constexpr uint32_t NOSLOT = 0xFFFFu;
+template <bool INTERIOR>
+__device__ __forceinline__ uint32_t ow_rank(const uint32_t *claim, uint32_t W, uint32_t H, int x, int y, bool want) {
+  if (!want) return KEY_INF;
+  if (!INTERIOR && (x < 0 || y < 0 || x >= (int)W || y >= (int)H)) return KEY_INF;
+  return ld_cg(claim + (size_t)y * W + x);
+}
+
+// one pass over up to OW_THREADS / 2 queue positions starting at `tile`: thread 2i + h takes cell i's neighbours
+// {left, right} (h = 0) or {up, down} (h = 1), so thread order is bid order
+__device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue,
+                                           const OwQueues &Q, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
+                                           uint32_t rx, uint32_t ry, uint32_t *ws, unsigned long long *prof) {
   const uint32_t W = S.map.W, H = S.map.H;
-  const uint32_t *q = sh.q[cur];
-  const uint8_t *qm = sh.qm[cur];
-  uint32_t *qn = sh.q[cur ^ 1u];
-  uint8_t *qnm = sh.qm[cur ^ 1u];
-  uint32_t bslot[K][4];
-  uint32_t cxy[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    const uint32_t pos = threadIdx.x * K + k;
-#pragma unroll
-    for (int s = 0; s < 4; ++s) bslot[k][s] = NOSLOT;
-    cxy[k] = 0;
-    if (pos >= n) continue;
-    const uint32_t c = q[pos];
-    const uint32_t seen = qm[pos];
-    cxy[k] = c;
-    const uint32_t mx = c & 0xFFFFu, my = c >> 16;
-    const uint32_t rank = base + pos;
-    const uint32_t wx = mx >> 5, bx = mx & 31u;
-    // class words: {traversable, frontier mask} of the rows above / at / below, plus the side words at a word edge
-    const uint2 *row = tm + (size_t)my * S.wpr + wx;
-    const uint2 wc = __ldg(row);
-    const uint2 wu = my > 0 ? __ldg(row - S.wpr) : make_uint2(0, 0);
-    const uint2 wd = my + 1 < H ? __ldg(row + S.wpr) : make_uint2(0, 0);
-    uint32_t tr = 0, mk = 0;  // bit s: neighbour s is traversable / a frontier-mask cell
-    if (mx > 0) {
-      const uint2 w = bx ? wc : __ldg(row - 1);
-      const uint32_t b = (bx + 31u) & 31u;
-      tr |= ((w.x >> b) & 1u) << 0;
-      mk |= ((w.y >> b) & 1u) << 0;
-    }
-    if (mx + 1 < W) {
-      const uint2 w = bx != 31u ? wc : __ldg(row + 1);
-      const uint32_t b = (bx + 1u) & 31u;
-      tr |= ((w.x >> b) & 1u) << 1;
-      mk |= ((w.y >> b) & 1u) << 1;
-    }
-    tr |= ((wu.x >> bx) & 1u) << 2;
-    mk |= ((wu.y >> bx) & 1u) << 2;
-    tr |= ((wd.x >> bx) & 1u) << 3;
-    mk |= ((wd.y >> bx) & 1u) << 3;
-    tr &= ~seen;  // visited_flag[nbr]: the neighbours on level d-1
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      const int dx = s == 0 ? -1 : (s == 1 ? 1 : 0), dy = s == 2 ? -1 : (s == 3 ? 1 : 0);
-      const uint32_t x = mx + dx, y = my + dy;
-      if ((tr >> s) & 1u) {
-        // enqueued only inside the search radius (FrontierSearch.cpp:72-76); the exact test runs only near the rim
-        const int64_t adx = (int64_t)abs((int)x - (int)rx) + 1, ady = (int64_t)abs((int)y - (int)ry) + 1;
-        if (adx * adx + ady * ady >= S.near_cells_sq) {
-          const double wx_ = S.map.ox + (x + 0.5) * S.map.res;
-          const double wy_ = S.map.oy + (y + 0.5) * S.map.res;
-          const double ddx = S.robot_x - wx_, ddy = S.robot_y - wy_;
-          if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) continue;
-        }
-        const uint32_t nb = (y << 16) | x;
-        uint32_t h = hslot(nb, 13);
-        uint32_t probes = 0;
-        while (true) {
-          uint32_t kk = ((volatile uint32_t *)sh.keys)[h];
-          if (kk == HKEY_EMPTY) {
-            kk = atomicCAS(&sh.keys[h], HKEY_EMPTY, nb);
-            if (kk == HKEY_EMPTY) kk = nb;
-          }
-          if (kk == nb) break;
-          h = (h + 1u) & SMASK;
-          if (++probes >= OW_SLOTS) break;
-        }
-        if (probes >= OW_SLOTS) {
-          *s_abort = 1;
-        } else {
-          atomicMin(&sh.val[h], pos * 4u + (uint32_t)s);
-          atomicOr(&sh.dmask[h], 1u << (s ^ 1));  // seen from nb, this cell lies in the opposite direction
-          bslot[k][s] = h;
-        }
-      } else if ((mk >> s) & 1u) {
-        atomicMin(claim + (size_t)y * W + x, TOUCH_BIT | (rank * 4u + (uint32_t)s));  // isNewFrontierCell branch: first touch
-      }
-    }
-  }
-  __syncthreads();
-  // winners: the bids that are still the minimum of their entry
-  uint32_t wins = 0, wmask = 0, n_win = 0;  // wins: bit (4k+s); wmask: 4 direction bits per winner, in order
-#pragma unroll
-  for (int k = 0; k < K; ++k)
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      const uint32_t h = bslot[k][s];
-      if (h == NOSLOT) continue;
-      const uint32_t pos = threadIdx.x * K + k;
-      if (((volatile uint32_t *)sh.val)[h] == pos * 4u + (uint32_t)s) {
-        wins |= 1u << (4 * k + s);
-        if (K <= 2) wmask |= (((volatile uint32_t *)sh.dmask)[h] & 15u) << (4 * n_win);
-        ++n_win;
-      }
-    }
-  uint64_t wmask_hi = 0;  // K == 4: up to 16 winners need 64 bits
-  if (K > 2) {
-    uint32_t j = 0;
-#pragma unroll
-    for (int k = 0; k < K; ++k)
-#pragma unroll
-      for (int s = 0; s < 4; ++s)
-        if (wins & (1u << (4 * k + s))) {
-          wmask_hi |= (uint64_t)(((volatile uint32_t *)sh.dmask)[bslot[k][s]] & 15u) << (4 * j);
-          ++j;
-        }
-  }
-  // block-wide exclusive scan of n_win: one barrier (warp totals alternate between two buffers)
+  const uint32_t next_base = base + n;
+  const long long c0 = clock64();
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-  uint32_t incl = n_win;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-    if ((int)lane >= o) incl += t;
+  const uint32_t pos = tile + (threadIdx.x >> 1), h = threadIdx.x & 1u;
+  const bool on = pos < n;
+  const uint32_t cell = on ? Q.q0[pos] : 0u;
+  const uint32_t seen = on ? (uint32_t)Q.qm0[pos] : 15u;
+  const int mx = (int)(cell & 0xFFFFu), my = (int)(cell >> 16);
+  const uint32_t rank = base + pos;
+  // the two neighbours of this thread: a = slot 2h, b = slot 2h + 1
+  const int ax = h ? mx : mx - 1, ay = h ? my - 1 : my, bx = h ? mx : mx + 1, by = h ? my + 1 : my;
+  const bool a_in = on && ax >= 0 && ay >= 0, b_in = on && bx < (int)W && by < (int)H;
+  const uint2 z = make_uint2(0, 0);
+  const uint2 wa = a_in ? __ldg(tm + tm_index((uint32_t)ax >> 5, (uint32_t)ay, S.wpr)) : z;
+  const uint2 wb = b_in ? __ldg(tm + tm_index((uint32_t)bx >> 5, (uint32_t)by, S.wpr)) : z;
+  bool a_tr = ((wa.x >> (ax & 31)) & 1u) && !((seen >> (2 * h)) & 1u);      // traversable and not on level d-1
+  bool b_tr = ((wb.x >> (bx & 31)) & 1u) && !((seen >> (2 * h + 1)) & 1u);
+  const bool a_mk = (wa.y >> (ax & 31)) & 1u, b_mk = (wb.y >> (bx & 31)) & 1u;
+  // enqueued only inside the search radius (FrontierSearch.cpp:72-76); the exact test runs only near the rim
+  {
+    const int64_t dxa = (int64_t)abs(ax - (int)rx) + 1, dya = (int64_t)abs(ay - (int)ry) + 1;
+    const int64_t dxb = (int64_t)abs(bx - (int)rx) + 1, dyb = (int64_t)abs(by - (int)ry) + 1;
+    if (a_tr && dxa * dxa + dya * dya >= S.near_cells_sq) {
+      const double ddx = S.robot_x - (S.map.ox + (ax + 0.5) * S.map.res), ddy = S.robot_y - (S.map.oy + (ay + 0.5) * S.map.res);
+      if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) a_tr = false;
+    }
+    if (b_tr && dxb * dxb + dyb * dyb >= S.near_cells_sq) {
+      const double ddx = S.robot_x - (S.map.ox + (bx + 0.5) * S.map.res), ddy = S.robot_y - (S.map.oy + (by + 0.5) * S.map.res);
+      if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) b_tr = false;
+    }
   }
-  uint32_t *ws = sh.wsum + (level & 1u) * 32u;
-  if (lane == 31) ws[wid] = incl;
+  const long long c1 = clock64();
+  // ranks of each candidate's three other neighbours (front, and the two sides), all loads independent.
+  // directions: 0 = -x, 1 = +x, 2 = -y, 3 = +y; seen from the candidate, this cell lies in direction (slot ^ 1)
+  const int fx = h ? 0 : 1, fy = h ? 1 : 0;  // unit step of this thread's axis
+  const int px = h ? 1 : 0, py = h ? 0 : 1;  // the perpendicular axis
+  uint32_t ra[3], rb[3];
+  const bool interior = mx >= 2 && my >= 2 && mx + 2 < (int)W && my + 2 < (int)H;
+  if (interior) {
+    ra[0] = ow_rank<true>(claim, W, H, ax - fx, ay - fy, a_tr);
+    ra[1] = ow_rank<true>(claim, W, H, ax - px, ay - py, a_tr);
+    ra[2] = ow_rank<true>(claim, W, H, ax + px, ay + py, a_tr);
+    rb[0] = ow_rank<true>(claim, W, H, bx + fx, by + fy, b_tr);
+    rb[1] = ow_rank<true>(claim, W, H, bx - px, by - py, b_tr);
+    rb[2] = ow_rank<true>(claim, W, H, bx + px, by + py, b_tr);
+  } else {
+    ra[0] = ow_rank<false>(claim, W, H, ax - fx, ay - fy, a_tr);
+    ra[1] = ow_rank<false>(claim, W, H, ax - px, ay - py, a_tr);
+    ra[2] = ow_rank<false>(claim, W, H, ax + px, ay + py, a_tr);
+    rb[0] = ow_rank<false>(claim, W, H, bx + fx, by + fy, b_tr);
+    rb[1] = ow_rank<false>(claim, W, H, bx - px, by - py, b_tr);
+    rb[2] = ow_rank<false>(claim, W, H, bx + px, by + py, b_tr);
+  }
+  // direction bits, seen from the candidate: front of a = slot 2h (further along -axis), of b = slot 2h + 1;
+  // the sides are the two slots of the other axis (minus first)
+  const uint32_t side_lo = 1u << (2 * (h ^ 1u)), side_hi = 2u << (2 * (h ^ 1u));
+  bool a_win = a_tr, b_win = b_tr;
+  uint32_t a_dm = 1u << (2 * h + 1), b_dm = 1u << (2 * h);  // this cell, seen from a / from b
+  {
+    const uint32_t dbit[3] = {1u << (2 * h), side_lo, side_hi};
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      if (ra[j] >= base && ra[j] < next_base) {  // a level-d neighbour of the candidate: it competes for it
+        a_dm |= dbit[j];
+        if (ra[j] < rank) a_win = false;          // dequeued before this cell: it visited the candidate first
+      }
+  }
+  {
+    const uint32_t dbit[3] = {1u << (2 * h + 1), side_lo, side_hi};
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      if (rb[j] >= base && rb[j] < next_base) {
+        b_dm |= dbit[j];
+        if (rb[j] < rank) b_win = false;
+      }
+  }
+  // frontier-mask neighbours record the first touch (isNewFrontierCell branch)
+  if (a_in && !((wa.x >> (ax & 31)) & 1u) && a_mk) atomicMin(claim + (size_t)ay * W + ax, TOUCH_BIT | (rank * 4u + 2u * h));
+  if (b_in && !((wb.x >> (bx & 31)) & 1u) && b_mk) atomicMin(claim + (size_t)by * W + bx, TOUCH_BIT | (rank * 4u + 2u * h + 1u));
+  const long long c2 = clock64();
+  // block-wide exclusive scan of the winner counts (0..2 per thread): two ballots per warp, one barrier
+  const uint32_t n_win = (a_win ? 1u : 0u) + (b_win ? 1u : 0u);
+  const uint32_t b0 = __ballot_sync(0xffffffffu, n_win & 1u), b1 = __ballot_sync(0xffffffffu, n_win >> 1);
+  const uint32_t lt = (1u << lane) - 1u;
+  const uint32_t excl = __popc(b0 & lt) + 2u * __popc(b1 & lt);
+  if (lane == 0) ws[wid] = __popc(b0) + 2u * __popc(b1);
   __syncthreads();
-  uint32_t wv = ws[lane], wi = wv;
+  const uint32_t wv = lane < OW_THREADS / 32 ? ws[lane] : 0u;
+  uint32_t wi = wv;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
@@ -714,90 +711,111 @@ __device__ __forceinline__ uint32_t ow_level(const SearchParams &S, const uint2 
   }
   const uint32_t total = __shfl_sync(0xffffffffu, wi, 31);
   const uint32_t wbase = __shfl_sync(0xffffffffu, wi - wv, wid);
-  uint32_t dst = wbase + incl - n_win;
-  // append the winners; every bidder puts its table entry back to empty
-  uint32_t j = 0;
-#pragma unroll
-  for (int k = 0; k < K; ++k)
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-      const uint32_t h = bslot[k][s];
-      if (h == NOSLOT) continue;
-      if (wins & (1u << (4 * k + s))) {
-        const int dx = s == 0 ? -1 : (s == 1 ? 1 : 0), dy = s == 2 ? -1 : (s == 3 ? 1 : 0);
-        const uint32_t mx = cxy[k] & 0xFFFFu, my = cxy[k] >> 16;
-        if (dst < OW_QCAP) {
-          qn[dst] = ((my + dy) << 16) | (mx + dx);
-          qnm[dst] = (uint8_t)(K <= 2 ? (wmask >> (4 * j)) & 15u : (uint32_t)(wmask_hi >> (4 * j)) & 15u);
-        }
-        ++dst;
-        ++j;
-      }
-      sh.keys[h] = HKEY_EMPTY;
-      sh.val[h] = KEY_INF;
-      sh.dmask[h] = 0;
+  uint32_t dst = n_next + wbase + excl;
+  const long long c3 = clock64();
+  // append the winners in (position, slot) order
+  if (a_win) {
+    const uint32_t lin = (uint32_t)ay * W + (uint32_t)ax;
+    queue[next_base + dst] = lin;
+    claim[lin] = next_base + dst;
+    if (dst < S.ow_qcap) {
+      Q.q1[dst] = ((uint32_t)ay << 16) | (uint32_t)ax;
+      Q.qm1[dst] = (uint8_t)a_dm;
     }
-  __syncthreads();
+    ++dst;
+  }
+  if (b_win) {
+    const uint32_t lin = (uint32_t)by * W + (uint32_t)bx;
+    queue[next_base + dst] = lin;
+    claim[lin] = next_base + dst;
+    if (dst < S.ow_qcap) {
+      Q.q1[dst] = ((uint32_t)by << 16) | (uint32_t)bx;
+      Q.qm1[dst] = (uint8_t)b_dm;
+    }
+  }
+  if (threadIdx.x == 0) {
+    const long long c4 = clock64();
+    prof[0] += c1 - c0; prof[1] += c2 - c1; prof[2] += c3 - c2; prof[3] += c4 - c3; prof[4] += 1;
+  }
   return total;
 }
 
-__global__ void __launch_bounds__(BFS_THREADS, 1)
+__global__ void __launch_bounds__(OW_THREADS, 1)
 rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, Counters *cnt) {
   extern __shared__ uint32_t ow_sh[];
   __shared__ uint32_t sh48[48];
-  __shared__ uint32_t s_start, s_abort;
+  __shared__ uint32_t s_start;
   __shared__ uint32_t s_wsum[64];
-  OwShared sh;
-  sh.keys = ow_sh;
-  sh.val = ow_sh + OW_SLOTS;
-  sh.dmask = ow_sh + 2 * OW_SLOTS;
-  sh.q[0] = ow_sh + 3 * OW_SLOTS;
-  sh.q[1] = sh.q[0] + OW_QCAP;
-  sh.qm[0] = reinterpret_cast<uint8_t *>(sh.q[1] + OW_QCAP);
-  sh.qm[1] = sh.qm[0] + OW_QCAP;
-  sh.wsum = s_wsum;
+  __shared__ unsigned long long s_prof[8];
+  if (threadIdx.x < 8) s_prof[threadIdx.x] = 0;
+  const long long k0 = clock64();
+  OwQueues Q;
+  Q.q0 = ow_sh;
+  Q.q1 = ow_sh + OW_QCAP;
+  Q.qm0 = reinterpret_cast<uint8_t *>(ow_sh + 2 * OW_QCAP);
+  Q.qm1 = Q.qm0 + OW_QCAP;
   if (cnt->overflow) return;
   const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
-  if (threadIdx.x == 0) { s_start = S.robot_cell; s_abort = 0; }
+  if (threadIdx.x == 0) s_start = S.robot_cell;
   __syncthreads();
   if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
     nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
     __syncthreads();
   }
   const uint32_t start = s_start;
-  for (uint32_t i = threadIdx.x; i < OW_SLOTS; i += BFS_THREADS) {
-    sh.keys[i] = HKEY_EMPTY;
-    sh.val[i] = KEY_INF;
-    sh.dmask[i] = 0;
-  }
   if (threadIdx.x == 0) {
     cnt->start_cell = start;
     const uint32_t sy = start / W, sx = start - sy * W;
-    sh.q[0][0] = (sy << 16) | sx;
-    sh.qm[0][0] = 0;
+    Q.q0[0] = (sy << 16) | sx;
+    Q.qm0[0] = 0;
+    queue[0] = start;
+    claim[start] = 0;
   }
   __syncthreads();
-  static_assert(OW_SLOTS == (1u << 13), "hslot(., 13) assumes 8192 slots");
-  uint32_t base = 0, n = 1, levels = 0, cur = 0;
+  uint32_t base = 0, n = 1, levels = 0, scans = 0;
   while (n > 0) {
-    uint32_t n_next;
-    if (n <= BFS_THREADS) n_next = ow_level<1>(S, tm, claim, sh, cur, base, n, rx, ry, levels, &s_abort);
-    else if (n <= 2 * BFS_THREADS) n_next = ow_level<2>(S, tm, claim, sh, cur, base, n, rx, ry, levels, &s_abort);
-    else n_next = ow_level<4>(S, tm, claim, sh, cur, base, n, rx, ry, levels, &s_abort);
-    if (n_next > OW_QCAP || s_abort) {  // uniform: a block-wide total, and a flag written before the level's last barriers
-      if (threadIdx.x == 0) cnt->ow_fallback = 1;
-      return;
+    uint32_t n_next = 0;
+    for (uint32_t tile = 0; tile < n;) {
+      uint32_t *ws = s_wsum + (scans & 1u) * 32u;
+      ++scans;
+      n_next += ow_pass(S, tm, claim, queue, Q, tile, n, base, n_next, rx, ry, ws, s_prof);
+      tile += OW_THREADS / 2;
     }
+    __syncthreads();
     base += n;
     n = n_next;
-    cur ^= 1u;
     ++levels;
+    if (n > S.ow_qcap) {  // uniform (a block-wide total): rank_bfs_kernel resumes from the global queue at this level
+      if (threadIdx.x == 0) {
+        cnt->ow_fallback = 1;
+        cnt->resume_base = base;
+        cnt->resume_n = n;
+        cnt->resume_levels = levels;
+      }
+      return;
+    }
+    uint32_t *tq = Q.q0; Q.q0 = Q.q1; Q.q1 = tq;
+    uint8_t *tb = Q.qm0; Q.qm0 = Q.qm1; Q.qm1 = tb;
   }
   if (threadIdx.x == 0) {
     cnt->bfs_levels = levels;
     cnt->expanded = base;
-    cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
+    cnt->dirty_queue = base;  // claim[] holds the rank of every dequeued cell
+    for (int i = 0; i < 5; ++i) cnt->prof[i] = s_prof[i];
+    cnt->prof[5] = clock64() - k0;
+  }
+}
+
+
+// Pulls the claim words of the search disc's bounding box into L2 ahead of the outer wavefront (one prefetch per
+// 128-byte line, all SMs): the wavefront then reads ranks at L2 latency instead of taking a DRAM miss per level.
+__global__ void claim_warm_kernel(const uint32_t *claim, uint32_t W, uint32_t x0, uint32_t y0, uint32_t lines_per_row, uint32_t rows) {
+  const uint64_t n = (uint64_t)lines_per_row * rows;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = (uint32_t)(i / lines_per_row), l = (uint32_t)(i - (uint64_t)r * lines_per_row);
+    const uint32_t *p = claim + (size_t)(y0 + r) * W + x0 + l * 32u;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
   }
 }
 
@@ -1015,44 +1033,48 @@ replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, cons
       for (uint32_t tile = 0; tile < items; tile += 32) {
         const uint32_t j = tile + lane;
         bool cand = false;
-        uint32_t nb = 0, h = 0, mykey = 0;
+        uint32_t nb = 0xFFFFFF00u + lane;  // distinct dummies: lanes without a candidate match nobody
         if (j < items) {
           const uint32_t rank = base + (j >> 3), s = j & 7u;
           const uint32_t p = mir[rank];
           // neighbour s in the reference's order: -1, +1, -W, +W, -1-W, -1+W, +1-W, +1+W (DEP/src/Helpers.cpp:185-255)
-          const int ddx = (s == 0 || s == 4 || s == 5) ? -1 : ((s == 1 || s == 6 || s == 7) ? 1 : 0);
-          const int ddy = (s == 2 || s == 4 || s == 6) ? -1 : ((s == 3 || s == 5 || s == 7) ? 1 : 0);
+          const int ddx = (int)((0xA058u >> (2 * s)) & 3u) - 1, ddy = (int)((0x8885u >> (2 * s)) & 3u) - 1;
           const int x = (int)(p & 0xFFFFu) + ddx, y = (int)(p >> 16) + ddy;
           if (x >= 0 && y >= 0 && x < (int)W && y < (int)H) {
             const uint32_t word = staged ? bw[((uint32_t)y - wy0) * ww + (((uint32_t)x >> 5) - wx0)]
                                          : __ldg(bits + (size_t)y * S.wpr + ((uint32_t)x >> 5));
             if ((word >> ((uint32_t)x & 31u)) & 1u) {
-              nb = ((uint32_t)y << 16) | (uint32_t)x;
-              mykey = rank * 8u + s;
-              h = hslot(nb, lg);
+              const uint32_t c = ((uint32_t)y << 16) | (uint32_t)x;
+              // frontier_flag[nbr]: the table holds every cell accepted so far (plain loads: only winners write it,
+              // and they did so before this tile started)
+              uint32_t h = hslot(c, lg);
+              bool seen = false;
               while (true) {
-                uint32_t k = ((volatile uint32_t *)keys)[h];
-                if (k == HKEY_EMPTY) {
-                  k = atomicCAS(&keys[h], HKEY_EMPTY, nb);
-                  if (k == HKEY_EMPTY) k = nb;
-                }
-                if (k == nb) break;
+                const uint32_t k = ((volatile uint32_t *)keys)[h];
+                if (k == c) { seen = true; break; }
+                if (k == HKEY_EMPTY) break;
                 h = (h + 1u) & smask;
               }
-              if (((volatile uint32_t *)val)[h] >= base * 8u) {  // !frontier_flag[nbr]
-                atomicMin(&val[h], mykey);
-                cand = true;
-              }
+              if (!seen) { cand = true; nb = c; }
             }
           }
         }
-        __syncwarp();
-        const bool win = cand && ((volatile uint32_t *)val)[h] == mykey;
+        // several lanes may reach the same cell in this tile: the lowest lane is the smallest (rank, slot), it wins
+        const uint32_t peers = __match_any_sync(0xffffffffu, nb);
+        const bool win = cand && (uint32_t)(__ffs(peers) - 1) == lane;
         const uint32_t bal = __ballot_sync(0xffffffffu, win);
         if (win) {
           const uint32_t dst = next_base + n_next + __popc(bal & ((1u << lane) - 1u));
-          out[dst] = (nb >> 16) * W + (nb & 0xFFFFu);
+          const uint32_t x = nb & 0xFFFFu, y = nb >> 16;
+          out[dst] = y * W + x;
           mir[dst] = nb;
+          uint32_t h = hslot(nb, lg);
+          while (atomicCAS(&keys[h], HKEY_EMPTY, nb) != HKEY_EMPTY) h = (h + 1u) & smask;  // winners are distinct cells
+          if (!staged) {  // the rows this cell's neighbours live in: in L1 by the time it is dequeued
+            const uint32_t wx = x >> 5;
+            if (y > 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(bits + (size_t)(y - 1) * S.wpr + wx));
+            if (y + 1 < H) asm volatile("prefetch.global.L1 [%0];" ::"l"(bits + (size_t)(y + 1) * S.wpr + wx));
+          }
         }
         n_next += __popc(bal);
         __syncwarp();
@@ -1316,7 +1338,7 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   const uint32_t wpr = (c->W + 31u) / 32u;
   FS_CUDA(c, s->bits.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->trav.reserve((size_t)wpr * c->H));
-  FS_CUDA(c, s->tm.reserve((size_t)wpr * c->H));
+  FS_CUDA(c, s->tm.reserve((size_t)wpr * ((c->H + 7u) / 8u) * 8u));
   FS_CUDA(c, s->slot.reserve(N));
   FS_CUDA(c, s->queue.reserve(N + 8));
   FS_CUDA(c, s->counters.reserve(1));
@@ -1372,6 +1394,11 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     const char *e = getenv("FITSLAM_WAVEFRONT");
     s->force_global = (e && !strcmp(e, "global")) ? 1 : 0;
   }
+  {
+    const char *e = getenv("FITSLAM_OW_QCAP");
+    const long v = e ? atol(e) : (long)OW_QCAP;
+    S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
+  }
   S.use_smem = (s->force_global || c->W > 65535u || c->H > 65535u) ? 0u : 1u;  // queue entries pack y << 16 | x
   if (!s->attr_set) {
     FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
@@ -1399,7 +1426,15 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
   if (S.use_smem) {
-    rank_bfs_smem_kernel<<<1, BFS_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, cnt);
+    // bounding box of the search disc, in cells (clipped to the map)
+    const uint32_t rcx = robot_cell % c->W, rcy = robot_cell / c->W;
+    const uint32_t rad = (uint32_t)std::min<double>(S.dist_limit / c->res + 3.0, 1e9);
+    const uint32_t bx0 = (rcx > rad ? rcx - rad : 0u) & ~31u, bx1 = std::min<uint64_t>((uint64_t)rcx + rad, c->W - 1);
+    const uint32_t by0 = rcy > rad ? rcy - rad : 0u, by1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1);
+    const uint32_t lpr = (bx1 - bx0) / 32u + 1u, rows = by1 - by0 + 1u;
+    claim_warm_kernel<<<wide, 256, 0, c->stream>>>(s->claim.p, c->W, bx0, by0, lpr, rows);
+    ++c->launches;
+    rank_bfs_smem_kernel<<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, cnt);
     ++c->launches;
   }
   rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once
@@ -1451,6 +1486,9 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
     if (st != FITSLAM_OK) return st;
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
     s->last = *hc;
+    if (getenv("FITSLAM_PROF"))
+      fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
+              hc->expanded, hc->prof[4], hc->prof[0], hc->prof[1], hc->prof[2], hc->prof[3], hc->prof[5]);
     cudaEventElapsedTime(&s->bfs_ms, s->ev_bfs[0], s->ev_bfs[1]);
     if (!hc->overflow) {
       c->n_frontiers = hc->n_frontiers;

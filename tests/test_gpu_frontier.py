@@ -113,9 +113,11 @@ def test_search_global_memory_wavefronts(capi, oracle, synth, name, monkeypatch)
     _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], ov)
 
 
-def test_search_wide_levels_fall_back(capi, oracle):
-    # an open 3000 x 3000 map: the diamond wavefront grows past 4096 cells per level, so the shared-memory outer
-    # wavefront hands over to the global-memory kernel mid-search; one huge ring component (> 4096 cells) likewise.
+def test_search_wide_levels_fall_back(capi, oracle, monkeypatch):
+    # an open 3000 x 3000 map: the diamond wavefront grows past the (here lowered) shared-memory queue capacity, so the
+    # shared-memory outer wavefront hands over to the global-memory kernel mid-search, which resumes from the global
+    # queue; one huge ring component (> 4096 cells) goes to the global-memory replay likewise.
+    monkeypatch.setenv("FITSLAM_OW_QCAP", "3000")
     # (resolution 1/16 m keeps every cell centre an exact double: the two-branch chunks of a straight frontier then give
     # exact angle ties instead of ulp-level atan2 noise, which is a libm property and not what this test is about)
     W = H = 3000
