@@ -40,6 +40,7 @@ static constexpr uint32_t INNER_BIT = 0x40000000u;
 static constexpr uint32_t TOUCH_BIT = 0x80000000u;
 static constexpr uint32_t MAX_RANK = (1u << 29) - 2;
 static constexpr int BFS_THREADS = 1024;
+static constexpr bool OW_PREFETCH = false;
 static constexpr int OW_THREADS = 1024;      // shared-memory outer wavefront: two threads per queue position, 512 positions per pass
 static constexpr int REPLAY_THREADS = 128;
 static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
@@ -82,6 +83,7 @@ struct SearchParams {
   int32_t min_size, max_size;
   uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
   uint32_t use_smem;       // 1: shared-memory wavefronts first, global-memory kernels only for what does not fit
+  uint32_t rk_tiles_x;     // 8 x 8 tiles per row of the rank array
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
 };
 
@@ -91,6 +93,7 @@ struct FrontierState {
   DevBuf<uint32_t> bits;      // frontier mask, wpr words per row
   DevBuf<uint32_t> trav;      // traversable mask (cost < 254), same layout
   DevBuf<uint2> tm;           // {trav word, frontier-mask word} interleaved: one 8-byte load classifies a neighbour
+  DevBuf<uint32_t> rk;        // outer wavefront ranks, rk_index layout; the search disc's tiles are reset before every search
   DevBuf<uint32_t> mcell;     // mask-cell list (unordered)
   DevBuf<uint32_t> parent;    // union-find over list indices
   DevBuf<uint32_t> rkey;      // per root: min touch key of the component
@@ -122,7 +125,7 @@ static FrontierState *fr_state(fitslam_ctx *c) {
 void destroy_frontier_state(fitslam_ctx *c) {
   if (!c->fs) return;
   FrontierState *s = c->fs;
-  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->mcell.release();
+  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->rk.release(); s->mcell.release();
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
   s->rbox.release(); s->cbox.release(); s->obox.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
@@ -448,7 +451,7 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   __shared__ uint32_t s_start;
   if (cnt->overflow) return;
   if (S.use_smem && !cnt->ow_fallback) return;  // the shared-memory wavefront finished the search
-  const bool resume = S.use_smem != 0;
+  const bool resume = false;  // (kept for a queue hand-over; the shared-memory wavefront restarts the search instead)
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
   if (threadIdx.x == 0) s_start = S.robot_cell;  // falls back to pos when no cell qualifies (FrontierSearch.cpp:47-54)
@@ -578,6 +581,11 @@ __device__ __forceinline__ uint32_t hslot(uint32_t cell, uint32_t bits) { return
 __host__ __device__ __forceinline__ size_t tm_index(uint32_t wx, uint32_t y, uint32_t wpr) {
   return ((size_t)(y >> 3) * wpr + wx) * 8u + (y & 7u);
 }
+// dequeue ranks of the outer wavefront, one word per cell in 8 x 8 tiles (two 128-byte lines per tile): the ranks a
+// level reads lie within 3 cells of the cells it dequeues, so they share a handful of lines that sit in L1
+__host__ __device__ __forceinline__ size_t rk_index(uint32_t x, uint32_t y, uint32_t tiles_x) {
+  return ((size_t)(y >> 3) * tiles_x + (x >> 3)) * 64u + ((y & 7u) << 3) + (x & 7u);
+}
 
 // The outer wavefront, default path.  Same decision rule as rank_bfs_kernel above (a dequeued cell p visits a
 // traversable, unvisited neighbour c iff no other neighbour of c was dequeued before p in this level), with the work
@@ -602,16 +610,42 @@ struct OwQueues {
   uint8_t *qm0, *qm1;
 };
 
+// rank of a cell.  Plain (L1-cached) loads: this kernel is one CTA, every rank it reads was stored by the same CTA
+// before an earlier barrier, so the SM's own write-through L1 is coherent for it.
 template <bool INTERIOR>
-__device__ __forceinline__ uint32_t ow_rank(const uint32_t *claim, uint32_t W, uint32_t H, int x, int y, bool want) {
+__device__ __forceinline__ uint32_t ow_rank(const uint32_t *rk, uint32_t tiles_x, uint32_t W, uint32_t H, int x, int y, bool want) {
   if (!want) return KEY_INF;
   if (!INTERIOR && (x < 0 || y < 0 || x >= (int)W || y >= (int)H)) return KEY_INF;
-  return ld_cg(claim + (size_t)y * W + x);
+  return rk[rk_index((uint32_t)x, (uint32_t)y, tiles_x)];
+}
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+// a winner joins the next level: rank, queue entry, and prefetches of what the next level will read around it (the
+// class words of its three rows and the rank lines within 3 cells), so that those loads hit L1 one level later
+__device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *rk, const OwQueues &Q,
+                                          uint32_t x, uint32_t y, uint32_t dm, uint32_t dst, uint32_t next_base) {
+  rk[rk_index(x, y, S.rk_tiles_x)] = next_base + dst;
+  if (dst < S.ow_qcap) {
+    Q.q1[dst] = (y << 16) | x;
+    Q.qm1[dst] = (uint8_t)dm;
+  }
+  if (OW_PREFETCH) {  // measured: eight prefetches per winner cost more issue time in the append phase than they save (README)
+    const uint32_t W = S.map.W, H = S.map.H;
+    const uint32_t y0 = y >= 3 ? y - 3 : 0, y1 = min(y + 3, H - 1), x0 = x >= 3 ? x - 3 : 0, x1 = min(x + 3, W - 1);
+    prefetch_l1(rk + rk_index(x0, y0, S.rk_tiles_x));
+    prefetch_l1(rk + rk_index(x1, y0, S.rk_tiles_x));
+    prefetch_l1(rk + rk_index(x0, y, S.rk_tiles_x));
+    prefetch_l1(rk + rk_index(x1, y, S.rk_tiles_x));
+    prefetch_l1(rk + rk_index(x0, y1, S.rk_tiles_x));
+    prefetch_l1(rk + rk_index(x1, y1, S.rk_tiles_x));
+    prefetch_l1(tm + tm_index(x >> 5, y > 0 ? y - 1 : 0, S.wpr));
+    prefetch_l1(tm + tm_index(x >> 5, min(y + 1, H - 1), S.wpr));
+  }
 }
 
 // one pass over up to OW_THREADS / 2 queue positions starting at `tile`: thread 2i + h takes cell i's neighbours
 // {left, right} (h = 0) or {up, down} (h = 1), so thread order is bid order
-__device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue,
+__device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *rk,
                                            const OwQueues &Q, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
                                            uint32_t rx, uint32_t ry, uint32_t *ws, unsigned long long *prof) {
   const uint32_t W = S.map.W, H = S.map.H;
@@ -654,19 +688,19 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   uint32_t ra[3], rb[3];
   const bool interior = mx >= 2 && my >= 2 && mx + 2 < (int)W && my + 2 < (int)H;
   if (interior) {
-    ra[0] = ow_rank<true>(claim, W, H, ax - fx, ay - fy, a_tr);
-    ra[1] = ow_rank<true>(claim, W, H, ax - px, ay - py, a_tr);
-    ra[2] = ow_rank<true>(claim, W, H, ax + px, ay + py, a_tr);
-    rb[0] = ow_rank<true>(claim, W, H, bx + fx, by + fy, b_tr);
-    rb[1] = ow_rank<true>(claim, W, H, bx - px, by - py, b_tr);
-    rb[2] = ow_rank<true>(claim, W, H, bx + px, by + py, b_tr);
+    ra[0] = ow_rank<true>(rk, S.rk_tiles_x, W, H, ax - fx, ay - fy, a_tr);
+    ra[1] = ow_rank<true>(rk, S.rk_tiles_x, W, H, ax - px, ay - py, a_tr);
+    ra[2] = ow_rank<true>(rk, S.rk_tiles_x, W, H, ax + px, ay + py, a_tr);
+    rb[0] = ow_rank<true>(rk, S.rk_tiles_x, W, H, bx + fx, by + fy, b_tr);
+    rb[1] = ow_rank<true>(rk, S.rk_tiles_x, W, H, bx - px, by - py, b_tr);
+    rb[2] = ow_rank<true>(rk, S.rk_tiles_x, W, H, bx + px, by + py, b_tr);
   } else {
-    ra[0] = ow_rank<false>(claim, W, H, ax - fx, ay - fy, a_tr);
-    ra[1] = ow_rank<false>(claim, W, H, ax - px, ay - py, a_tr);
-    ra[2] = ow_rank<false>(claim, W, H, ax + px, ay + py, a_tr);
-    rb[0] = ow_rank<false>(claim, W, H, bx + fx, by + fy, b_tr);
-    rb[1] = ow_rank<false>(claim, W, H, bx - px, by - py, b_tr);
-    rb[2] = ow_rank<false>(claim, W, H, bx + px, by + py, b_tr);
+    ra[0] = ow_rank<false>(rk, S.rk_tiles_x, W, H, ax - fx, ay - fy, a_tr);
+    ra[1] = ow_rank<false>(rk, S.rk_tiles_x, W, H, ax - px, ay - py, a_tr);
+    ra[2] = ow_rank<false>(rk, S.rk_tiles_x, W, H, ax + px, ay + py, a_tr);
+    rb[0] = ow_rank<false>(rk, S.rk_tiles_x, W, H, bx + fx, by + fy, b_tr);
+    rb[1] = ow_rank<false>(rk, S.rk_tiles_x, W, H, bx - px, by - py, b_tr);
+    rb[2] = ow_rank<false>(rk, S.rk_tiles_x, W, H, bx + px, by + py, b_tr);
   }
   // direction bits, seen from the candidate: front of a = slot 2h (further along -axis), of b = slot 2h + 1;
   // the sides are the two slots of the other axis (minus first)
@@ -715,24 +749,10 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   const long long c3 = clock64();
   // append the winners in (position, slot) order
   if (a_win) {
-    const uint32_t lin = (uint32_t)ay * W + (uint32_t)ax;
-    queue[next_base + dst] = lin;
-    claim[lin] = next_base + dst;
-    if (dst < S.ow_qcap) {
-      Q.q1[dst] = ((uint32_t)ay << 16) | (uint32_t)ax;
-      Q.qm1[dst] = (uint8_t)a_dm;
-    }
+    ow_append(S, tm, rk, Q, (uint32_t)ax, (uint32_t)ay, a_dm, dst, next_base);
     ++dst;
   }
-  if (b_win) {
-    const uint32_t lin = (uint32_t)by * W + (uint32_t)bx;
-    queue[next_base + dst] = lin;
-    claim[lin] = next_base + dst;
-    if (dst < S.ow_qcap) {
-      Q.q1[dst] = ((uint32_t)by << 16) | (uint32_t)bx;
-      Q.qm1[dst] = (uint8_t)b_dm;
-    }
-  }
+  if (b_win) ow_append(S, tm, rk, Q, (uint32_t)bx, (uint32_t)by, b_dm, dst, next_base);
   if (threadIdx.x == 0) {
     const long long c4 = clock64();
     prof[0] += c1 - c0; prof[1] += c2 - c1; prof[2] += c3 - c2; prof[3] += c4 - c3; prof[4] += 1;
@@ -741,7 +761,8 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
 }
 
 __global__ void __launch_bounds__(OW_THREADS, 1)
-rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, Counters *cnt) {
+rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, uint32_t *rk,
+                     Counters *cnt) {
   extern __shared__ uint32_t ow_sh[];
   __shared__ uint32_t sh48[48];
   __shared__ uint32_t s_start;
@@ -769,8 +790,7 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     const uint32_t sy = start / W, sx = start - sy * W;
     Q.q0[0] = (sy << 16) | sx;
     Q.qm0[0] = 0;
-    queue[0] = start;
-    claim[start] = 0;
+    rk[rk_index(sx, sy, S.rk_tiles_x)] = 0;
   }
   __syncthreads();
   uint32_t base = 0, n = 1, levels = 0, scans = 0;
@@ -779,20 +799,15 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     for (uint32_t tile = 0; tile < n;) {
       uint32_t *ws = s_wsum + (scans & 1u) * 32u;
       ++scans;
-      n_next += ow_pass(S, tm, claim, queue, Q, tile, n, base, n_next, rx, ry, ws, s_prof);
+      n_next += ow_pass(S, tm, claim, rk, Q, tile, n, base, n_next, rx, ry, ws, s_prof);
       tile += OW_THREADS / 2;
     }
     __syncthreads();
     base += n;
     n = n_next;
     ++levels;
-    if (n > S.ow_qcap) {  // uniform (a block-wide total): rank_bfs_kernel resumes from the global queue at this level
-      if (threadIdx.x == 0) {
-        cnt->ow_fallback = 1;
-        cnt->resume_base = base;
-        cnt->resume_n = n;
-        cnt->resume_levels = levels;
-      }
+    if (n > S.ow_qcap) {  // uniform (a block-wide total): rank_bfs_kernel reruns the search (claim[] holds touch keys only,
+      if (threadIdx.x == 0) cnt->ow_fallback = 1;  // and it would write the same ones)
       return;
     }
     uint32_t *tq = Q.q0; Q.q0 = Q.q1; Q.q1 = tq;
@@ -801,21 +816,22 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
   if (threadIdx.x == 0) {
     cnt->bfs_levels = levels;
     cnt->expanded = base;
-    cnt->dirty_queue = base;  // claim[] holds the rank of every dequeued cell
+    cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
     for (int i = 0; i < 5; ++i) cnt->prof[i] = s_prof[i];
     cnt->prof[5] = clock64() - k0;
   }
 }
 
 
-// Pulls the claim words of the search disc's bounding box into L2 ahead of the outer wavefront (one prefetch per
-// 128-byte line, all SMs): the wavefront then reads ranks at L2 latency instead of taking a DRAM miss per level.
-__global__ void claim_warm_kernel(const uint32_t *claim, uint32_t W, uint32_t x0, uint32_t y0, uint32_t lines_per_row, uint32_t rows) {
-  const uint64_t n = (uint64_t)lines_per_row * rows;
+// Resets the rank tiles of the search disc's bounding box to "not dequeued" before the outer wavefront (16-byte stores,
+// all SMs; it also leaves those lines in L2).  The wavefront never leaves the box: cells are enqueued only inside the disc.
+__global__ void rk_reset_kernel(uint32_t *rk, uint32_t tiles_x, uint32_t tx0, uint32_t ty0, uint32_t ntx, uint32_t nty) {
+  const uint64_t n = (uint64_t)ntx * nty * 16u;  // uint4 stores per tile: 64 words
+  const uint4 e = make_uint4(KEY_INF, KEY_INF, KEY_INF, KEY_INF);
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-    const uint32_t r = (uint32_t)(i / lines_per_row), l = (uint32_t)(i - (uint64_t)r * lines_per_row);
-    const uint32_t *p = claim + (size_t)(y0 + r) * W + x0 + l * 32u;
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    const uint64_t t = i >> 4;
+    const uint32_t r = (uint32_t)(t / ntx), cx = (uint32_t)(t - (uint64_t)r * ntx);
+    reinterpret_cast<uint4 *>(rk + ((size_t)(ty0 + r) * tiles_x + tx0 + cx) * 64u)[i & 15u] = e;
   }
 }
 
@@ -1339,6 +1355,7 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   FS_CUDA(c, s->bits.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->trav.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->tm.reserve((size_t)wpr * ((c->H + 7u) / 8u) * 8u));
+  FS_CUDA(c, s->rk.reserve((size_t)((c->W + 7u) / 8u) * ((c->H + 7u) / 8u) * 64u));
   FS_CUDA(c, s->slot.reserve(N));
   FS_CUDA(c, s->queue.reserve(N + 8));
   FS_CUDA(c, s->counters.reserve(1));
@@ -1399,6 +1416,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     const long v = e ? atol(e) : (long)OW_QCAP;
     S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
   }
+  S.rk_tiles_x = (c->W + 7u) / 8u;
   S.use_smem = (s->force_global || c->W > 65535u || c->H > 65535u) ? 0u : 1u;  // queue entries pack y << 16 | x
   if (!s->attr_set) {
     FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
@@ -1426,15 +1444,14 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
   if (S.use_smem) {
-    // bounding box of the search disc, in cells (clipped to the map)
+    // bounding box of the search disc (+ the 3-cell prefetch halo), in 8 x 8 tiles, clipped to the map
     const uint32_t rcx = robot_cell % c->W, rcy = robot_cell / c->W;
-    const uint32_t rad = (uint32_t)std::min<double>(S.dist_limit / c->res + 3.0, 1e9);
-    const uint32_t bx0 = (rcx > rad ? rcx - rad : 0u) & ~31u, bx1 = std::min<uint64_t>((uint64_t)rcx + rad, c->W - 1);
-    const uint32_t by0 = rcy > rad ? rcy - rad : 0u, by1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1);
-    const uint32_t lpr = (bx1 - bx0) / 32u + 1u, rows = by1 - by0 + 1u;
-    claim_warm_kernel<<<wide, 256, 0, c->stream>>>(s->claim.p, c->W, bx0, by0, lpr, rows);
+    const uint32_t rad = (uint32_t)std::min<double>(S.dist_limit / c->res + 8.0, 1e9);
+    const uint32_t tx0 = (rcx > rad ? rcx - rad : 0u) >> 3, tx1 = (uint32_t)std::min<uint64_t>((uint64_t)rcx + rad, c->W - 1) >> 3;
+    const uint32_t ty0 = (rcy > rad ? rcy - rad : 0u) >> 3, ty1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1) >> 3;
+    rk_reset_kernel<<<wide, 256, 0, c->stream>>>(s->rk.p, S.rk_tiles_x, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
     ++c->launches;
-    rank_bfs_smem_kernel<<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, cnt);
+    rank_bfs_smem_kernel<<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt);
     ++c->launches;
   }
   rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once
