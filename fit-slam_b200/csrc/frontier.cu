@@ -1003,7 +1003,7 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
 // memory in queue order, and the frontier-mask bits of the component's bounding box (+1 cell) are staged in shared
 // memory when they fit, so a level costs a handful of shared-memory round trips and two __syncwarp.
 __global__ void __launch_bounds__(32)
-replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint32_t *__restrict__ oseed,
+replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint2 *__restrict__ tm, const uint32_t *__restrict__ oseed,
                    const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, const uint32_t *__restrict__ obox,
                    uint32_t *cells, const Counters *cnt, uint32_t min_cells, uint32_t max_cells, uint32_t bit_words) {
   extern __shared__ uint32_t iw_sh[];
@@ -1057,8 +1057,10 @@ replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, cons
           const int ddx = (int)((0xA058u >> (2 * s)) & 3u) - 1, ddy = (int)((0x8885u >> (2 * s)) & 3u) - 1;
           const int x = (int)(p & 0xFFFFu) + ddx, y = (int)(p >> 16) + ddy;
           if (x >= 0 && y >= 0 && x < (int)W && y < (int)H) {
+            // not staged (a long thin component with a large bounding box): the tiled class words, whose 128-byte lines
+            // hold 8 rows, so a wavefront creeping along the component misses L1 once in several levels, not every level
             const uint32_t word = staged ? bw[((uint32_t)y - wy0) * ww + (((uint32_t)x >> 5) - wx0)]
-                                         : __ldg(bits + (size_t)y * S.wpr + ((uint32_t)x >> 5));
+                                         : __ldg(tm + tm_index((uint32_t)x >> 5, (uint32_t)y, S.wpr)).y;
             if ((word >> ((uint32_t)x & 31u)) & 1u) {
               const uint32_t c = ((uint32_t)y << 16) | (uint32_t)x;
               // frontier_flag[nbr]: the table holds every cell accepted so far (plain loads: only winners write it,
@@ -1086,11 +1088,6 @@ replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, cons
           mir[dst] = nb;
           uint32_t h = hslot(nb, lg);
           while (atomicCAS(&keys[h], HKEY_EMPTY, nb) != HKEY_EMPTY) h = (h + 1u) & smask;  // winners are distinct cells
-          if (!staged) {  // the rows this cell's neighbours live in: in L1 by the time it is dequeued
-            const uint32_t wx = x >> 5;
-            if (y > 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(bits + (size_t)(y - 1) * S.wpr + wx));
-            if (y + 1 < H) asm volatile("prefetch.global.L1 [%0];" ::"l"(bits + (size_t)(y + 1) * S.wpr + wx));
-          }
         }
         n_next += __popc(bal);
         __syncwarp();
@@ -1465,9 +1462,9 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   if (S.use_smem) {
     // large components first (two warps per SM, the long poles), then the small ones on the remaining shared memory
     replay_warp_kernel<<<148 * 2, 32, iw_smem(IW_CELLS, IW_BITS_LARGE), c->stream>>>(
-        S, s->bits.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, IW_SMALL + 1, IW_CELLS, IW_BITS_LARGE);
+        S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, IW_SMALL + 1, IW_CELLS, IW_BITS_LARGE);
     replay_warp_kernel<<<148 * 16, 32, iw_smem(IW_SMALL, IW_BITS_SMALL), c->stream>>>(
-        S, s->bits.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL);
+        S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL);
     c->launches += 2;
   }
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
