@@ -27,7 +27,7 @@ def _disc(a, cx, cy, r, value, only=None):
 
 
 def make_costmap(W, H, seed, n_disc, r_lo=30, r_hi=120, spread=None, n_rooms=0, n_holes=0, hole_r=(5, 25), n_walls=None, wall_len=(8, 50),
-                 porous=0.0, inflation=0, res=0.05):
+                 porous=0.0, inflation=0, res=0.05, grid_radius=0, grid_step=110):
     """Explored region = a random-walk chain of sensor discs (so it is one reachable component) plus rooms;
     thin lethal wall segments inside; optional porous lethal cells on the free/unknown edge (fragmenting the
     frontier into small clusters, config C3) and an inflation ring.  Returns (map[H,W] uint8, meta dict)."""
@@ -39,6 +39,19 @@ def make_costmap(W, H, seed, n_disc, r_lo=30, r_hi=120, spread=None, n_rooms=0, 
     lo_y, hi_y = max(MARGIN + r_hi, cy0 - spread), min(H - MARGIN - r_hi - 1, cy0 + spread)
     centres = [(cx0, cy0, (r_lo + r_hi) // 2)]
     _disc(a, cx0, cy0, centres[0][2], 0)
+    if grid_radius:
+        # a jittered grid of overlapping discs inside a circle (config C4: a large explored area around the robot);
+        # n_disc is ignored, neighbouring discs overlap (r_lo + r_lo > grid_step), so the region is one component
+        g = int(grid_radius // grid_step)
+        for gy in range(-g, g + 1):
+            for gx in range(-g, g + 1):
+                if (gx or gy) and gx * gx + gy * gy <= g * g:
+                    cx = int(min(hi_x, max(lo_x, cx0 + gx * grid_step + rng.integers(-8, 9))))
+                    cy = int(min(hi_y, max(lo_y, cy0 + gy * grid_step + rng.integers(-8, 9))))
+                    r = int(rng.integers(r_lo, r_hi + 1))
+                    _disc(a, cx, cy, r, 0)
+                    centres.append((cx, cy, r))
+        n_disc = 1
     for _ in range(n_disc - 1):
         # grow mostly from recent discs so the chain spreads out instead of piling up at the centre
         lo = max(0, len(centres) - 8) if rng.random() < 0.7 else 0
@@ -153,8 +166,8 @@ CONFIGS = {
     "C2": dict(W=4096, H=4096, n_disc=450, r_lo=30, r_hi=120, n_holes=1000, P=200_000, R=64, Y=16, max_frontier_distance=150.0),
     "C3": dict(W=2048, H=2048, n_disc=300, r_lo=25, r_hi=60, n_holes=1500, hole_r=(2, 6), n_walls=0, porous=0.3, P=50_000, R=64, Y=16,
                max_frontier_distance=80.0),
-    "C4": dict(W=16384, H=16384, n_disc=1500, r_lo=30, r_hi=120, P=1_000_000, R=64, Y=32,
-               max_frontier_distance=600.0),
+    "C4": dict(W=16384, H=16384, n_disc=1, r_lo=60, r_hi=120, grid_radius=2600, n_holes=9000, hole_r=(4, 14), n_walls=600, P=1_000_000,
+               R=64, Y=32, max_frontier_distance=150.0),
 }
 
 

@@ -1,0 +1,123 @@
+"""BASELINE.json's big and incremental configurations on the GPU, checked through size-independent properties where the
+oracle would take minutes:
+  * C4 (16384^2 map, 1M map points, ~20k frontiers x 32 yaw windows): a second cycle on the same context gives the same
+    bits (scratch state is clean between cycles), the union of 4 candidate shards equals the unsharded records, every goal
+    cell is an unknown cell next to known space, sizes obey the cluster bounds, the every_frontier list has no duplicates;
+    a sample of the frontiers is scored by the oracle (arrival information, bit-exact);
+  * C5 (rapid mode): a random walk reveals discs on a C1-size map; each step uploads only the dirty rectangle, and the
+    cycle must equal a cycle on a fresh context with the full map, and the oracle every 8th step."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REC_FIELDS = ("information", "max_index", "achievable", "footprint_in_lethal", "ray_failed")
+
+
+def _fetch(ctx, capi, meta, mode):
+    st, res = ctx.cycle(meta["robot_x"], meta["robot_y"], 0.3, meta["poly"], mode)
+    assert st == 0
+    return res, ctx.cycle_fetch(res.n_frontiers)
+
+
+def test_c4_full_size_properties(capi, oracle, synth):
+    a, meta, pts, ov = synth.make_config("C4")
+    params = synth.apply_overrides(capi.default_params(), ov)
+    synth.apply_overrides(oracle.params, ov)
+    H, W = a.shape
+    ctx = capi.Context(params)
+    try:
+        ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        ctx.fisher_generate_lookup()
+        ctx.set_map_points(pts)
+        res1, out1 = _fetch(ctx, capi, meta, capi.FISHER_ALL_YAWS)
+        res2, out2 = _fetch(ctx, capi, meta, capi.FISHER_ALL_YAWS)
+        F = res1.n_frontiers
+        n_rays, k, n_win, max_len = ctx.ray_shape()
+        assert F > 5000 and n_win == 32 and res1.n_candidates == F * n_win == res1.n_fisher_poses
+        print(f"C4: {F} frontiers, {res1.n_components} components, {res1.bfs_levels} levels, stage_ms {[round(v, 3) for v in res1.stage_ms]}")
+        # idempotence: the second cycle is bit-identical
+        assert res2.n_frontiers == F
+        for key in out1:
+            assert out1[key].tobytes() == out2[key].tobytes(), key
+        fr = out1["frontiers"]
+        # every goal is an unknown cell with a known, non-lethal 4-neighbour (isNewFrontierCell), sizes within bounds
+        gx, gy = fr["goal_mx"].astype(np.int64), fr["goal_my"].astype(np.int64)
+        assert np.all(a[gy, gx] == 255)
+        nb = np.stack([a[gy, gx - 1], a[gy, gx + 1], a[gy - 1, gx], a[gy + 1, gx]])
+        assert np.all((nb < params.lethal_threshold).any(axis=0))
+        assert fr["size"].min() > params.min_frontier_cluster_size and fr["size"].max() <= params.max_frontier_cluster_size + 1
+        st, fr2, cells = ctx.search_frontiers(meta["robot_x"], meta["robot_y"], capacity=1 << 17, cell_capacity=1 << 23)
+        assert len(cells) == res1.n_frontier_cells and len(np.unique(cells)) == len(cells)
+        assert fr2.tobytes() == fr.tobytes()
+        # shards: the union of 4 blocks equals the unsharded arrival records and Fisher information
+        B = (F + 3) // 4
+        merged_arr = np.zeros(F, dtype=out1["arrival"].dtype)
+        merged_f = np.zeros(F, np.float32)
+        for r in range(4):
+            ctx.set_shard(r, 4)
+            st, Fr = ctx.cycle_begin(meta["robot_x"], meta["robot_y"], 0.3, meta["poly"], capi.FISHER_ALL_YAWS)
+            assert st == 0 and Fr == F
+            import torch
+            torch.cuda.synchronize()  # cycle_begin leaves the scoring kernels in flight on the context stream
+            rec = ctx.records_tensor().cpu().numpy()
+            lo, hi = r * B, min(F, (r + 1) * B)
+            merged_arr["information"][lo:hi] = rec[lo:hi, 0]
+            merged_arr["max_index"][lo:hi] = rec[lo:hi, 1]
+            merged_f[lo:hi] = rec[lo:hi, 2].view(np.float32)
+            ctx.cycle_end()
+        ctx.set_shard(0, 1)
+        np.testing.assert_array_equal(merged_arr["information"], out1["arrival"]["information"])
+        np.testing.assert_array_equal(merged_arr["max_index"], out1["arrival"]["max_index"])
+        np.testing.assert_array_equal(merged_f.view(np.uint32), out1["fisher"].view(np.uint32))
+        # a sample of the frontiers through the oracle: arrival information bit-exact
+        pick = np.linspace(0, F - 1, 400).astype(np.int64)
+        arr, _, _ = oracle.score_arrival(a, meta, fr[pick], meta["poly"])
+        for key in REC_FIELDS:
+            np.testing.assert_array_equal(out1["arrival"][key][pick], arr[key], err_msg=key)
+    finally:
+        ctx.close()
+
+
+def test_c5_rapid_mode_dirty_rectangles(capi, oracle, synth):
+    a, meta = synth.make_costmap(1000, 1000, seed=55, n_disc=10, r_lo=30, r_hi=80, n_holes=15)
+    rng = np.random.default_rng(55)
+    H, W = a.shape
+    pts = synth.make_points(5000, synth.explored_bbox(a, meta), 55)
+    ctx = capi.Context()
+    try:
+        ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        ctx.fisher_generate_lookup()
+        ctx.set_map_points(pts)
+        cx = int((meta["robot_x"] - meta["ox"]) / meta["res"])
+        cy = int((meta["robot_y"] - meta["oy"]) / meta["res"])
+        for step in range(24):
+            cx = int(np.clip(cx + rng.integers(-4, 5), 100, W - 100))  # 0.2 m steps
+            cy = int(np.clip(cy + rng.integers(-4, 5), 100, H - 100))
+            rect = synth.reveal_step(a, meta, cx, cy, rng)
+            rx, ry = meta["ox"] + (cx + 0.5) * meta["res"], meta["oy"] + (cy + 0.5) * meta["res"]
+            ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"], dirty=rect)
+            st, res = ctx.cycle(rx, ry, 0.3, meta["poly"], capi.FISHER_BEST_YAW)
+            assert st == 0
+            got = ctx.cycle_fetch(res.n_frontiers)
+            if step % 4 == 0:  # a fresh context with the whole map gives the same bits
+                ref = capi.Context()
+                ref.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+                ref.fisher_generate_lookup()
+                ref.set_map_points(pts)
+                st2, res2 = ref.cycle(rx, ry, 0.3, meta["poly"], capi.FISHER_BEST_YAW)
+                want = ref.cycle_fetch(res2.n_frontiers)
+                ref.close()
+                assert st2 == 0 and res2.n_frontiers == res.n_frontiers
+                for key in got:
+                    assert got[key].tobytes() == want[key].tobytes(), (step, key)
+            if step % 8 == 0:  # and the oracle agrees
+                sto, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, rx, ry)
+                assert len(fr) == res.n_frontiers
+                for key in ("goal_mx", "goal_my", "size", "component", "chunk", "first_cell"):
+                    np.testing.assert_array_equal(got["frontiers"][key], fr[key], err_msg=key)
+                arr, _, _ = oracle.score_arrival(a, meta, fr, meta["poly"])
+                for key in REC_FIELDS:
+                    np.testing.assert_array_equal(got["arrival"][key], arr[key], err_msg=key)
+    finally:
+        ctx.close()
