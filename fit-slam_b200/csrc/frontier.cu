@@ -79,6 +79,7 @@ struct SearchParams {
   uint32_t robot_cell;     // getIndex(mx, my) of the robot
   double robot_x, robot_y;
   double dist_limit;       // max_frontier_distance + max_frontier_cluster_size * resolution * 1.414
+  uint32_t near_cells_sq32;  // the same clamped to 32 bits (shared-memory path)
   int64_t near_cells_sq;   // (|dx| + 1)^2 + (|dy| + 1)^2 < near_cells_sq (in cells, from the robot cell) => surely inside dist_limit
   int32_t min_size, max_size;
   uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
@@ -583,8 +584,8 @@ __host__ __device__ __forceinline__ size_t tm_index(uint32_t wx, uint32_t y, uin
 }
 // dequeue ranks of the outer wavefront, one word per cell in 8 x 8 tiles (two 128-byte lines per tile): the ranks a
 // level reads lie within 3 cells of the cells it dequeues, so they share a handful of lines that sit in L1
-__host__ __device__ __forceinline__ size_t rk_index(uint32_t x, uint32_t y, uint32_t tiles_x) {
-  return ((size_t)(y >> 3) * tiles_x + (x >> 3)) * 64u + ((y & 7u) << 3) + (x & 7u);
+__host__ __device__ __forceinline__ uint32_t rk_index(uint32_t x, uint32_t y, uint32_t tiles_x) {
+  return ((y >> 3) * tiles_x + (x >> 3)) * 64u + ((y & 7u) << 3) + (x & 7u);  // < 2^29 + rounding: the map has < 2^29 cells
 }
 
 // The outer wavefront, default path.  Same decision rule as rank_bfs_kernel above (a dequeued cell p visits a
@@ -653,13 +654,20 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   const long long c0 = clock64();
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
   const uint32_t pos = tile + (threadIdx.x >> 1), h = threadIdx.x & 1u;
+  int ax = 0, ay = 0, bx = 0, by = 0;
+  bool a_win = false, b_win = false;
+  uint32_t a_dm = 0, b_dm = 0;
+  long long c1 = c0;
+  // a warp whose 16 positions all lie beyond the level skips straight to the scan (narrow levels leave most warps idle,
+  // and idle warps would otherwise spend issue slots the busy ones need: the pass is issue-bound)
+  if (tile + (wid << 4) < n) {
   const bool on = pos < n;
   const uint32_t cell = on ? Q.q0[pos] : 0u;
   const uint32_t seen = on ? (uint32_t)Q.qm0[pos] : 15u;
   const int mx = (int)(cell & 0xFFFFu), my = (int)(cell >> 16);
   const uint32_t rank = base + pos;
   // the two neighbours of this thread: a = slot 2h, b = slot 2h + 1
-  const int ax = h ? mx : mx - 1, ay = h ? my - 1 : my, bx = h ? mx : mx + 1, by = h ? my + 1 : my;
+  ax = h ? mx : mx - 1; ay = h ? my - 1 : my; bx = h ? mx : mx + 1; by = h ? my + 1 : my;
   const bool a_in = on && ax >= 0 && ay >= 0, b_in = on && bx < (int)W && by < (int)H;
   const uint2 z = make_uint2(0, 0);
   const uint2 wa = a_in ? __ldg(tm + tm_index((uint32_t)ax >> 5, (uint32_t)ay, S.wpr)) : z;
@@ -669,18 +677,19 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   const bool a_mk = (wa.y >> (ax & 31)) & 1u, b_mk = (wb.y >> (bx & 31)) & 1u;
   // enqueued only inside the search radius (FrontierSearch.cpp:72-76); the exact test runs only near the rim
   {
-    const int64_t dxa = (int64_t)abs(ax - (int)rx) + 1, dya = (int64_t)abs(ay - (int)ry) + 1;
-    const int64_t dxb = (int64_t)abs(bx - (int)rx) + 1, dyb = (int64_t)abs(by - (int)ry) + 1;
-    if (a_tr && dxa * dxa + dya * dya >= S.near_cells_sq) {
+    // (|dx| + 1)^2 + (|dy| + 1)^2 fits 32 bits: the shared-memory path requires W, H <= 32768
+    const uint32_t dxa = (uint32_t)abs(ax - (int)rx) + 1u, dya = (uint32_t)abs(ay - (int)ry) + 1u;
+    const uint32_t dxb = (uint32_t)abs(bx - (int)rx) + 1u, dyb = (uint32_t)abs(by - (int)ry) + 1u;
+    if (a_tr && dxa * dxa + dya * dya >= S.near_cells_sq32) {
       const double ddx = S.robot_x - (S.map.ox + (ax + 0.5) * S.map.res), ddy = S.robot_y - (S.map.oy + (ay + 0.5) * S.map.res);
       if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) a_tr = false;
     }
-    if (b_tr && dxb * dxb + dyb * dyb >= S.near_cells_sq) {
+    if (b_tr && dxb * dxb + dyb * dyb >= S.near_cells_sq32) {
       const double ddx = S.robot_x - (S.map.ox + (bx + 0.5) * S.map.res), ddy = S.robot_y - (S.map.oy + (by + 0.5) * S.map.res);
       if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) b_tr = false;
     }
   }
-  const long long c1 = clock64();
+  c1 = clock64();
   // ranks of each candidate's three other neighbours (front, and the two sides), all loads independent.
   // directions: 0 = -x, 1 = +x, 2 = -y, 3 = +y; seen from the candidate, this cell lies in direction (slot ^ 1)
   const int fx = h ? 0 : 1, fy = h ? 1 : 0;  // unit step of this thread's axis
@@ -705,8 +714,8 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   // direction bits, seen from the candidate: front of a = slot 2h (further along -axis), of b = slot 2h + 1;
   // the sides are the two slots of the other axis (minus first)
   const uint32_t side_lo = 1u << (2 * (h ^ 1u)), side_hi = 2u << (2 * (h ^ 1u));
-  bool a_win = a_tr, b_win = b_tr;
-  uint32_t a_dm = 1u << (2 * h + 1), b_dm = 1u << (2 * h);  // this cell, seen from a / from b
+  a_win = a_tr; b_win = b_tr;
+  a_dm = 1u << (2 * h + 1); b_dm = 1u << (2 * h);  // this cell, seen from a / from b
   {
     const uint32_t dbit[3] = {1u << (2 * h), side_lo, side_hi};
 #pragma unroll
@@ -728,6 +737,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   // frontier-mask neighbours record the first touch (isNewFrontierCell branch)
   if (a_in && !((wa.x >> (ax & 31)) & 1u) && a_mk) atomicMin(claim + (size_t)ay * W + ax, TOUCH_BIT | (rank * 4u + 2u * h));
   if (b_in && !((wb.x >> (bx & 31)) & 1u) && b_mk) atomicMin(claim + (size_t)by * W + bx, TOUCH_BIT | (rank * 4u + 2u * h + 1u));
+  }
   const long long c2 = clock64();
   // block-wide exclusive scan of the winner counts (0..2 per thread): two ballots per warp, one barrier
   const uint32_t n_win = (a_win ? 1u : 0u) + (b_win ? 1u : 0u);
@@ -1403,6 +1413,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   {
     const double L = S.dist_limit / c->res;
     S.near_cells_sq = L > 4.0 ? (int64_t)(L * L * (1.0 - 1e-6)) - 2 : 0;
+    S.near_cells_sq32 = (uint32_t)std::min<int64_t>(S.near_cells_sq, 0x7FFFFFFF);
   }
   if (s->force_global < 0) {
     const char *e = getenv("FITSLAM_WAVEFRONT");
@@ -1414,7 +1425,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
   }
   S.rk_tiles_x = (c->W + 7u) / 8u;
-  S.use_smem = (s->force_global || c->W > 65535u || c->H > 65535u) ? 0u : 1u;  // queue entries pack y << 16 | x
+  S.use_smem = (s->force_global || c->W > 32768u || c->H > 32768u) ? 0u : 1u;  // queue entries pack y << 16 | x; 32-bit radius prefilter
   if (!s->attr_set) {
     FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
     FS_CUDA(c, cudaFuncSetAttribute(replay_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iw_smem(IW_CELLS, IW_BITS_LARGE)));
