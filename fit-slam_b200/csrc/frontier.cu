@@ -85,6 +85,7 @@ struct SearchParams {
   uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
   uint32_t use_smem;       // 1: shared-memory wavefronts first, global-memory kernels only for what does not fit
   uint32_t rk_tiles_x;     // 8 x 8 tiles per row of the rank array
+  uint32_t ow_wide;        // 1: levels wider than ow_qcap spill to the global queue (maps up to 16384 cells a side)
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
 };
 
@@ -451,7 +452,7 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   __shared__ uint32_t sh[48];
   __shared__ uint32_t s_start;
   if (cnt->overflow) return;
-  if (S.use_smem && !cnt->ow_fallback) return;  // the shared-memory wavefront finished the search
+  if (S.use_smem && cnt->ow_fallback != 1u) return;  // a shared-memory wavefront finished the search
   const bool resume = false;  // (kept for a queue hand-over; the shared-memory wavefront restarts the search instead)
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
@@ -607,6 +608,10 @@ __host__ __device__ __forceinline__ uint32_t rk_index(uint32_t x, uint32_t y, ui
 // Two barriers per pass.  A level wider than ow_qcap sets ow_fallback and rank_bfs_kernel resumes the search from the
 // global queue at that level.
 struct OwQueues {
+  // g0 / g1: the same queues in global memory, entries (mask << 28 | y << 14 | x), used while a level is wider than the
+  // shared-memory queue (maps up to 16384 cells a side): read when n > ow_qcap, written when the next level could be
+  uint32_t *g0, *g1;
+  bool from_global, to_global;
   uint32_t *q0, *q1;
   uint8_t *qm0, *qm1;
 };
@@ -623,6 +628,7 @@ __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefe
 
 // a winner joins the next level: rank, queue entry, and prefetches of what the next level will read around it (the
 // class words of its three rows and the rank lines within 3 cells), so that those loads hit L1 one level later
+template <bool WIDE>
 __device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *rk, const OwQueues &Q,
                                           uint32_t x, uint32_t y, uint32_t dm, uint32_t dst, uint32_t next_base) {
   rk[rk_index(x, y, S.rk_tiles_x)] = next_base + dst;
@@ -630,6 +636,7 @@ __device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__
     Q.q1[dst] = (y << 16) | x;
     Q.qm1[dst] = (uint8_t)dm;
   }
+  if (WIDE && Q.to_global) Q.g1[dst] = (dm << 28) | (y << 14) | x;
   if (OW_PREFETCH) {  // measured: eight prefetches per winner cost more issue time in the append phase than they save (README)
     const uint32_t W = S.map.W, H = S.map.H;
     const uint32_t y0 = y >= 3 ? y - 3 : 0, y1 = min(y + 3, H - 1), x0 = x >= 3 ? x - 3 : 0, x1 = min(x + 3, W - 1);
@@ -645,7 +652,9 @@ __device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__
 }
 
 // one pass over up to OW_THREADS / 2 queue positions starting at `tile`: thread 2i + h takes cell i's neighbours
-// {left, right} (h = 0) or {up, down} (h = 1), so thread order is bid order
+// {left, right} (h = 0) or {up, down} (h = 1), so thread order is bid order.  WIDE: the level or its successor may not fit
+// the shared-memory queue (a separate instantiation keeps the common narrow pass free of those branches)
+template <bool WIDE>
 __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *rk,
                                            const OwQueues &Q, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
                                            uint32_t rx, uint32_t ry, uint32_t *ws, unsigned long long *prof) {
@@ -662,8 +671,17 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   // and idle warps would otherwise spend issue slots the busy ones need: the pass is issue-bound)
   if (tile + (wid << 4) < n) {
   const bool on = pos < n;
-  const uint32_t cell = on ? Q.q0[pos] : 0u;
-  const uint32_t seen = on ? (uint32_t)Q.qm0[pos] : 15u;
+  uint32_t cell = 0u, seen = 15u;
+  if (on) {
+    if (WIDE && Q.from_global) {
+      const uint32_t e = ld_cg(Q.g0 + pos);
+      cell = ((e >> 14) & 0x3FFFu) << 16 | (e & 0x3FFFu);
+      seen = e >> 28;
+    } else {
+      cell = Q.q0[pos];
+      seen = Q.qm0[pos];
+    }
+  }
   const int mx = (int)(cell & 0xFFFFu), my = (int)(cell >> 16);
   const uint32_t rank = base + pos;
   // the two neighbours of this thread: a = slot 2h, b = slot 2h + 1
@@ -759,10 +777,10 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   const long long c3 = clock64();
   // append the winners in (position, slot) order
   if (a_win) {
-    ow_append(S, tm, rk, Q, (uint32_t)ax, (uint32_t)ay, a_dm, dst, next_base);
+    ow_append<WIDE>(S, tm, rk, Q, (uint32_t)ax, (uint32_t)ay, a_dm, dst, next_base);
     ++dst;
   }
-  if (b_win) ow_append(S, tm, rk, Q, (uint32_t)bx, (uint32_t)by, b_dm, dst, next_base);
+  if (b_win) ow_append<WIDE>(S, tm, rk, Q, (uint32_t)bx, (uint32_t)by, b_dm, dst, next_base);
   if (threadIdx.x == 0) {
     const long long c4 = clock64();
     prof[0] += c1 - c0; prof[1] += c2 - c1; prof[2] += c3 - c2; prof[3] += c4 - c3; prof[4] += 1;
@@ -770,6 +788,11 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   return total;
 }
 
+// WIDE = false: every level fits the shared-memory queue; a level that does not ends the kernel with ow_fallback = 2 (the
+// WIDE = true instantiation, launched right after, redoes the search with the global-memory queue spill; ranks already
+// written are the ones it will write again) or 1 (maps above 16384 cells a side: rank_bfs_kernel).  Two kernels rather
+// than one: carrying both pass bodies made the common narrow pass 7 % slower.
+template <bool WIDE>
 __global__ void __launch_bounds__(OW_THREADS, 1)
 rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, uint32_t *rk,
                      Counters *cnt) {
@@ -785,7 +808,12 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
   Q.q1 = ow_sh + OW_QCAP;
   Q.qm0 = reinterpret_cast<uint8_t *>(ow_sh + 2 * OW_QCAP);
   Q.qm1 = Q.qm0 + OW_QCAP;
+  Q.g0 = queue;
+  Q.g1 = queue + S.queue_cap / 2;
+  Q.from_global = false;
+  Q.to_global = false;
   if (cnt->overflow) return;
+  if (WIDE && cnt->ow_fallback != 2u) return;
   const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
   if (threadIdx.x == 0) s_start = S.robot_cell;
@@ -809,19 +837,22 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     for (uint32_t tile = 0; tile < n;) {
       uint32_t *ws = s_wsum + (scans & 1u) * 32u;
       ++scans;
-      n_next += ow_pass(S, tm, claim, rk, Q, tile, n, base, n_next, rx, ry, ws, s_prof);
+      n_next += ow_pass<WIDE>(S, tm, claim, rk, Q, tile, n, base, n_next, rx, ry, ws, s_prof);
       tile += OW_THREADS / 2;
     }
     __syncthreads();
     base += n;
     n = n_next;
     ++levels;
-    if (n > S.ow_qcap) {  // uniform (a block-wide total): rank_bfs_kernel reruns the search (claim[] holds touch keys only,
-      if (threadIdx.x == 0) cnt->ow_fallback = 1;  // and it would write the same ones)
+    if (n > S.ow_qcap && !WIDE) {  // uniform (a block-wide total): the next kernel reruns the search (claim[] holds touch
+      if (threadIdx.x == 0) cnt->ow_fallback = S.ow_wide ? 2u : 1u;  // keys only, and it would write the same ones)
       return;
     }
     uint32_t *tq = Q.q0; Q.q0 = Q.q1; Q.q1 = tq;
     uint8_t *tb = Q.qm0; Q.qm0 = Q.qm1; Q.qm1 = tb;
+    tq = Q.g0; Q.g0 = Q.g1; Q.g1 = tq;
+    Q.from_global = n > S.ow_qcap;                     // this level did not fit the shared queue: read it from global memory
+    Q.to_global = S.ow_wide && 3u * n + 4u > S.ow_qcap;  // a level has at most 3 children per cell: the next one may not fit
   }
   if (threadIdx.x == 0) {
     cnt->bfs_levels = levels;
@@ -1087,9 +1118,21 @@ replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, cons
             }
           }
         }
-        // several lanes may reach the same cell in this tile: the lowest lane is the smallest (rank, slot), it wins
-        const uint32_t peers = __match_any_sync(0xffffffffu, nb);
-        const bool win = cand && (uint32_t)(__ffs(peers) - 1) == lane;
+        // several lanes may reach the same cell in this tile; the lowest lane is the smallest (rank, slot) and wins.  The
+        // 8 lanes of one dequeued cell reach 8 different cells, so a lane loses exactly when its cell is also a neighbour
+        // of one of the (at most 3) cells dequeued by lower lanes of this tile: three shuffles instead of a MATCH, which
+        // the profile showed to be a third of the level time
+        bool win = cand;
+        {
+          const uint32_t pme = (j < items) ? mir[base + (j >> 3)] : 0xFFFFFFFFu;
+          const int nx = (int)(nb & 0xFFFFu), ny = (int)(nb >> 16);
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            const uint32_t pk = __shfl_sync(0xffffffffu, pme, 8 * k);
+            const int dx = nx - (int)(pk & 0xFFFFu), dy = ny - (int)(pk >> 16);
+            if ((int)(lane >> 3) > k && pk != 0xFFFFFFFFu && dx >= -1 && dx <= 1 && dy >= -1 && dy <= 1) win = false;
+          }
+        }
         const uint32_t bal = __ballot_sync(0xffffffffu, win);
         if (win) {
           const uint32_t dst = next_base + n_next + __popc(bal & ((1u << lane) - 1u));
@@ -1425,9 +1468,11 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
   }
   S.rk_tiles_x = (c->W + 7u) / 8u;
+  S.ow_wide = (c->W <= 16384u && c->H <= 16384u && !getenv("FITSLAM_OW_NOWIDE")) ? 1u : 0u;
   S.use_smem = (s->force_global || c->W > 32768u || c->H > 32768u) ? 0u : 1u;  // queue entries pack y << 16 | x; 32-bit radius prefilter
   if (!s->attr_set) {
-    FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
+    FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
+    FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
     FS_CUDA(c, cudaFuncSetAttribute(replay_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iw_smem(IW_CELLS, IW_BITS_LARGE)));
     s->attr_set = true;
   }
@@ -1459,7 +1504,9 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     const uint32_t ty0 = (rcy > rad ? rcy - rad : 0u) >> 3, ty1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1) >> 3;
     rk_reset_kernel<<<wide, 256, 0, c->stream>>>(s->rk.p, S.rk_tiles_x, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
     ++c->launches;
-    rank_bfs_smem_kernel<<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt);
+    rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt);
+    rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt);  // returns at once unless a level was too wide
+    ++c->launches;
     ++c->launches;
   }
   rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once

@@ -113,11 +113,15 @@ def test_search_global_memory_wavefronts(capi, oracle, synth, name, monkeypatch)
     _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], ov)
 
 
-def test_search_wide_levels_fall_back(capi, oracle, monkeypatch):
+@pytest.mark.parametrize("wide", [True, False])
+def test_search_wide_levels_fall_back(capi, oracle, monkeypatch, wide):
     # an open 3000 x 3000 map: the diamond wavefront grows past the (here lowered) shared-memory queue capacity, so the
     # shared-memory outer wavefront hands over to the global-memory kernel mid-search, which resumes from the global
     # queue; one huge ring component (> 4096 cells) goes to the global-memory replay likewise.
+    # wide=True: levels above the capacity spill to the global-memory queue inside the same kernel instead
     monkeypatch.setenv("FITSLAM_OW_QCAP", "3000")
+    if not wide:
+        monkeypatch.setenv("FITSLAM_OW_NOWIDE", "1")
     # (resolution 1/16 m keeps every cell centre an exact double: the two-branch chunks of a straight frontier then give
     # exact angle ties instead of ulp-level atan2 noise, which is a libm property and not what this test is about)
     W = H = 3000
