@@ -34,9 +34,21 @@ static constexpr int HASH_SLOTS = 16384;    // per-CTA voxel hash table: one pac
 static constexpr int CNT_BITS = 10;         // low bits of a slot: landmarks in the voxel, saturating (>= CROWD_MAX is enough)
 static constexpr uint32_t CNT_MASK = (1u << CNT_BITS) - 1u;
 static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding square of the lookup domain)
-static constexpr int FISHER_THREADS = 256;
-static constexpr int CHUNK_PTS = 64;         // points per unit of work
-static constexpr int MAX_CHUNKS = 768;       // 6 KB of static shared memory (three CTAs per SM with the 64 KB table)
+// 768 threads x 2 CTAs per SM = 48 warps (40 registers; the only spills are in thread 0's build_pose_frame).  The point
+// loop is latency-bound (one L2 load and one shared-memory CAS chain per iteration), so warps in flight are what pays:
+// measured on C2, 256 x 3: 6.5 ms, 512 x 2: 5.4 ms, 1024 x 1: 6.4 ms, 768 x 2: 5.1 ms, 1024 x 2 (32 registers): 5.1 ms.
+#ifndef FS_FISHER_THREADS
+#define FS_FISHER_THREADS 768
+#endif
+#ifndef FS_FISHER_MINB
+#define FS_FISHER_MINB 2
+#endif
+static constexpr int FISHER_THREADS = FS_FISHER_THREADS;
+#ifndef FS_CHUNK_PTS
+#define FS_CHUNK_PTS 64
+#endif
+static constexpr int CHUNK_PTS = FS_CHUNK_PTS;  // points per unit of work
+static constexpr int MAX_CHUNKS = 768 * 64 / CHUNK_PTS;  // 6 KB of static shared memory at 64 points per chunk
 
 struct M3f { float m[3][3]; };
 struct V3f { float v[3]; };
@@ -593,31 +605,35 @@ __device__ void build_pose_frame(const fitslam_pose &pose, const FisherParams &P
     for (int j = 0; j < 3; ++j) neg.m[i][j] = -F.Rinv.m[i][j];
   F.tinv = mulv(neg, t);
   F.px = t.v[0]; F.py = t.v[1];
-  // ---- conservative culling planes (double; only used to skip whole bins)
-  // camera coords = Rcw * Perm * p + tcw with Perm = ros2orb: column j of M = Rcw * Perm
-  double M[3][3];
-  for (int i = 0; i < 3; ++i) {
-    M[i][0] = F.Rcw.m[i][2]; M[i][1] = -(double)F.Rcw.m[i][0]; M[i][2] = -(double)F.Rcw.m[i][1];
-  }
-  const double cam[5][3] = {{0, 0, 1}, {P.fx, 0, P.cx}, {-(double)P.fx, 0, (double)P.max_u - P.cx},
-                            {0, P.fy, P.cy}, {0, -(double)P.fy, (double)P.max_v - P.cy}};
-  for (int k = 0; k < 5; ++k) {
-    const double nn = sqrt(cam[k][0] * cam[k][0] + cam[k][1] * cam[k][1] + cam[k][2] * cam[k][2]);
+}
+
+// ---- conservative culling planes (double; only used to skip whole bins): plane k of 11, one thread each
+__device__ void build_pose_plane(const FisherParams &P, PoseFrame &F, int k) {
+  if (k < 5) {
+    // camera coords = Rcw * Perm * p + tcw with Perm = ros2orb: column j of M = Rcw * Perm
+    double M[3][3];
+    for (int i = 0; i < 3; ++i) {
+      M[i][0] = F.Rcw.m[i][2]; M[i][1] = -(double)F.Rcw.m[i][0]; M[i][2] = -(double)F.Rcw.m[i][1];
+    }
+    double cam[3];
+    if (k == 0) { cam[0] = 0; cam[1] = 0; cam[2] = 1; }
+    else if (k == 1) { cam[0] = P.fx; cam[1] = 0; cam[2] = P.cx; }
+    else if (k == 2) { cam[0] = -(double)P.fx; cam[1] = 0; cam[2] = (double)P.max_u - P.cx; }
+    else if (k == 3) { cam[0] = 0; cam[1] = P.fy; cam[2] = P.cy; }
+    else { cam[0] = 0; cam[1] = -(double)P.fy; cam[2] = (double)P.max_v - P.cy; }
+    const double nn = sqrt(cam[0] * cam[0] + cam[1] * cam[1] + cam[2] * cam[2]);
     double d = 0;
     for (int j = 0; j < 3; ++j) {
-      F.plane[k][j] = (cam[k][0] * M[0][j] + cam[k][1] * M[1][j] + cam[k][2] * M[2][j]) / nn;
-      d += cam[k][j] * (double)F.tcw.v[j];
+      F.plane[k][j] = (cam[0] * M[0][j] + cam[1] * M[1][j] + cam[2] * M[2][j]) / nn;
+      d += cam[j] * (double)F.tcw.v[j];
     }
     F.plane[k][3] = d / nn;
-  }
-  for (int ax = 0; ax < 3; ++ax) {
+  } else {
+    const int ax = (k - 5) >> 1;
+    const bool upper = (k - 5) & 1;
     const double lo = (P.org[ax] - 0.5) * P.step, hi = (P.org[ax] + P.dims[ax] - 0.5) * P.step;
-    for (int j = 0; j < 3; ++j) {
-      F.plane[5 + 2 * ax][j] = F.Rinv.m[ax][j];
-      F.plane[6 + 2 * ax][j] = -(double)F.Rinv.m[ax][j];
-    }
-    F.plane[5 + 2 * ax][3] = (double)F.tinv.v[ax] - lo;
-    F.plane[6 + 2 * ax][3] = hi - (double)F.tinv.v[ax];
+    for (int j = 0; j < 3; ++j) F.plane[k][j] = upper ? -(double)F.Rinv.m[ax][j] : (double)F.Rinv.m[ax][j];
+    F.plane[k][3] = upper ? hi - (double)F.tinv.v[ax] : (double)F.tinv.v[ax] - lo;
   }
 }
 
@@ -673,24 +689,26 @@ __device__ __forceinline__ int voxel_of_visible_point(const float4 q, const Pose
 }
 
 // count one landmark in its voxel: packed slot (voxel + 1) << CNT_BITS | count; plain loads walk the probe sequence and
-// only the claiming / counting step is an atomic (shared-memory atomics cost 2-4 cycles per LANE on this part)
-__device__ __forceinline__ bool table_count(uint32_t *tab, uint32_t h, int vox) {
+// only the claiming / counting step is an atomic (shared-memory atomics cost 2-4 cycles per LANE on this part).
+// Returns the landmark's rank in its voxel (1 = it claimed the slot), or 0 if the table is full.
+__device__ __forceinline__ uint32_t table_count(uint32_t *tab, uint32_t h, int vox) {
   uint32_t slot = h & (HASH_SLOTS - 1);
   const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
   for (int probe = 0; probe < 256; ++probe) {
     uint32_t prev = ((volatile uint32_t *)tab)[slot];
     if (prev == 0u) prev = atomicCAS(&tab[slot], 0u, key | 1u);
-    if (prev == 0u) return true;
+    if (prev == 0u) return 1u;
     if ((prev & ~CNT_MASK) == key) {
-      if ((prev & CNT_MASK) < CNT_MASK - 256u) atomicAdd(&tab[slot], 1u);  // saturates far above CROWD_MAX
-      return true;
+      // saturates far above CROWD_MAX: ranks beyond it carry a zero crowding factor anyway
+      if ((prev & CNT_MASK) >= CNT_MASK - 256u) return CROWD_MAX + 1u;
+      return min((atomicAdd(&tab[slot], 1u) & CNT_MASK) + 1u, (uint32_t)CROWD_MAX + 1u);
     }
     slot = (slot + 1) & (HASH_SLOTS - 1);
   }
-  return false;
+  return 0u;
 }
 
-__global__ void __launch_bounds__(FISHER_THREADS)
+__global__ void __launch_bounds__(FISHER_THREADS, FS_FISHER_MINB)
 fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, float *__restrict__ info_out,
               uint8_t *__restrict__ safe_out, uint32_t *__restrict__ nvis_out, ScoreRecord *__restrict__ rec_out,
               const fitslam_arrival *__restrict__ arrival) {
@@ -703,6 +721,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   const uint32_t pi = P.first + blockIdx.x;
   if (pi >= P.n_poses) return;
   if (threadIdx.x == 0) build_pose_frame(poses[pi], P, F);
+  __syncthreads();
+  if (threadIdx.x < 11) build_pose_plane(P, F, (int)threadIdx.x);
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5, nw = FISHER_THREADS / 32;
   // bins of the bounding square of the lookup domain around the pose
@@ -809,7 +829,15 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
               const uint32_t h = mix32((uint32_t)vox);
               if (npass == 1 || ((h >> 12) & (npass - 1)) == pass) {
                 ++my_used;
-                if (!*v_overflow && !table_count(tab, h, vox)) *v_overflow = 1;  // a lost attempt keeps counting only
+                if (!*v_overflow) {  // a lost attempt keeps counting only
+                  // information(voxel) * exp(1 - k^0.8) for the k-th landmark of the voxel, added by whoever counted it:
+                  // the table load is in flight during the probe, and no pass over the table is needed afterwards
+                  const float inf_v = __ldg(P.lut + vox);
+                  const uint32_t k = table_count(tab, h, vox);
+                  if (k == 0u) *v_overflow = 1;
+                  else if (k == 1u) total += (double)inf_v;
+                  else if (k <= (uint32_t)CROWD_MAX) total += (double)inf_v * (__ldg(P.crowd + k) - __ldg(P.crowd + k - 1u));
+                }
               }
             }
           }
@@ -819,11 +847,6 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
       if (my_used) atomicAdd(&s_used, my_used);
       __syncthreads();
       if (s_overflow && npass > 1) break;  // npass == 1: finish the (only) pass so that s_used is the full count
-      if (!s_overflow)
-        for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) {
-          const uint32_t w = tab[i];
-          if (w) total += (double)__ldg(P.lut + ((w >> CNT_BITS) - 1u)) * __ldg(P.crowd + min(w & CNT_MASK, (uint32_t)CROWD_MAX));
-        }
       __syncthreads();
     }
     used = s_used;
