@@ -40,7 +40,6 @@ static constexpr uint32_t INNER_BIT = 0x40000000u;
 static constexpr uint32_t TOUCH_BIT = 0x80000000u;
 static constexpr uint32_t MAX_RANK = (1u << 29) - 2;
 static constexpr int BFS_THREADS = 1024;
-static constexpr bool OW_PREFETCH = false;
 static constexpr int OW_THREADS = 1024;      // shared-memory outer wavefront: two threads per queue position, 512 positions per pass
 static constexpr int REPLAY_THREADS = 128;
 static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
@@ -48,6 +47,11 @@ static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
 // components that do not fit)
 static constexpr uint32_t OW_QCAP = 8192;    // outer wavefront: widest level the shared-memory queue holds (80 KB; the rest of the SM's 256 KB stays L1)
 static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 4 + 2 * OW_QCAP;
+// The outer wavefront runs as up to OW_PARTS launches of ow_part_levels levels each (the last one runs to the end).  After
+// part k the components it touched have their final seed (later touches carry larger keys), so their inner wavefronts
+// replay on a second stream while part k + 1 runs: the long thin components that bound the replay time are usually
+// touched long before the outer wavefront ends.
+static constexpr int OW_PARTS = 16;          // levels per part: search radius in cells / OW_PARTS (SearchParams::ow_part_levels)
 static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
 static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells (many warps per SM), <= IW_CELLS cells (two per SM)
 static constexpr uint32_t IW_BITS_SMALL = 1024, IW_BITS_LARGE = 8192;  // words of the component's mask window held in shared memory
@@ -68,7 +72,12 @@ struct Counters {
   uint32_t dirty_queue;    // entries of queue[] whose claim words (and their 4 neighbours') the cleanup must reset
   uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rank_bfs_kernel resumes there
   uint32_t resume_base, resume_n, resume_levels;
-  uint32_t pad[1];
+  uint32_t ow_done;        // the shared-memory outer wavefront ran out of cells (later parts return at once)
+  uint32_t sv_base, sv_n, sv_levels;   // state handed from one part of the outer wavefront to the next (queue[] holds the level)
+  uint32_t part_end[OW_PARTS];         // cells dequeued when part k ended: touch keys below 4 * part_end[k] are final after it
+  uint32_t comp_done;                  // components ordered and scanned so far
+  uint32_t coll_c0[OW_PARTS], coll_c1[OW_PARTS];  // components [c0, c1) of collection k (the one after the last part: OW_PARTS - 1)
+  uint32_t cell_carry, front_carry;    // running totals of comp_scan_kernel across collections
   unsigned long long prof[8];  // FITSLAM_PROF: cycles of warp 0 per phase of the outer wavefront
 };
 
@@ -87,6 +96,7 @@ struct SearchParams {
   uint32_t rk_tiles_x;     // 8 x 8 tiles per row of the rank array
   uint32_t ow_wide;        // 1: levels wider than ow_qcap spill to the global queue (maps up to 16384 cells a side)
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
+  uint32_t ow_part_levels; // levels per launch of the shared-memory outer wavefront
 };
 
 struct FrontierState {
@@ -112,7 +122,11 @@ struct FrontierState {
   uint64_t claim_cells = 0;   // cells for which claim is known to be all KEY_INF
   uint32_t mask_cap = 0, queue_cap = 0, comp_cap = 0, cell_cap = 0, front_cap = 0;
   Counters last{};
-  cudaEvent_t ev_bfs[3] = {};  // around rank_bfs_kernel and replay_kernel (bench roofline of the dominant kernel)
+  cudaEvent_t ev_bfs[5] = {};  // outer wavefront: [0] start, [1] last part done, [3] second stream joined, [4] fallback kernels done; [2] replay done
+  cudaEvent_t ev_part[OW_PARTS] = {}, ev_coll[OW_PARTS] = {};  // part k of the outer wavefront done; tables of collection k done
+  cudaEvent_t ev_join = nullptr, ev_join3 = nullptr;           // second / third stream drained
+  cudaStream_t stream2 = nullptr, stream3 = nullptr;  // collections that overlap the outer wavefront; their large inner wavefronts
+  uint32_t ow_parts = OW_PARTS;    // FITSLAM_OW_PARTS=1: one launch, no overlap (ablation)
   bool have_ev = false;
   bool attr_set = false;
   int force_global = -1;      // FITSLAM_WAVEFRONT=global selects the global-memory wavefront kernels (ablation / fallback test)
@@ -131,8 +145,15 @@ void destroy_frontier_state(fitslam_ctx *c) {
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
   s->rbox.release(); s->cbox.release(); s->obox.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
-  if (s->have_ev)
+  if (s->have_ev) {
     for (auto &e : s->ev_bfs) cudaEventDestroy(e);
+    for (auto &e : s->ev_part) cudaEventDestroy(e);
+    for (auto &e : s->ev_coll) cudaEventDestroy(e);
+    cudaEventDestroy(s->ev_join);
+    cudaEventDestroy(s->ev_join3);
+    cudaStreamDestroy(s->stream2);
+    cudaStreamDestroy(s->stream3);
+  }
   s->oseed.release(); s->osize.release(); s->ocell0.release(); s->ofront0.release();
   s->cells.release(); s->centroids.release(); s->counters.release();
   delete s;
@@ -626,8 +647,8 @@ __device__ __forceinline__ uint32_t ow_rank(const uint32_t *rk, uint32_t tiles_x
 }
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
-// a winner joins the next level: rank, queue entry, and prefetches of what the next level will read around it (the
-// class words of its three rows and the rank lines within 3 cells), so that those loads hit L1 one level later
+// a winner joins the next level: rank and queue entry.  (Prefetching what the next level will read around it was tried
+// twice, eight lines per winner and one line per winner that crosses into a new line: both made the kernel slower.)
 template <bool WIDE>
 __device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *rk, const OwQueues &Q,
                                           uint32_t x, uint32_t y, uint32_t dm, uint32_t dst, uint32_t next_base) {
@@ -637,18 +658,6 @@ __device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__
     Q.qm1[dst] = (uint8_t)dm;
   }
   if (WIDE && Q.to_global) Q.g1[dst] = (dm << 28) | (y << 14) | x;
-  if (OW_PREFETCH) {  // measured: eight prefetches per winner cost more issue time in the append phase than they save (README)
-    const uint32_t W = S.map.W, H = S.map.H;
-    const uint32_t y0 = y >= 3 ? y - 3 : 0, y1 = min(y + 3, H - 1), x0 = x >= 3 ? x - 3 : 0, x1 = min(x + 3, W - 1);
-    prefetch_l1(rk + rk_index(x0, y0, S.rk_tiles_x));
-    prefetch_l1(rk + rk_index(x1, y0, S.rk_tiles_x));
-    prefetch_l1(rk + rk_index(x0, y, S.rk_tiles_x));
-    prefetch_l1(rk + rk_index(x1, y, S.rk_tiles_x));
-    prefetch_l1(rk + rk_index(x0, y1, S.rk_tiles_x));
-    prefetch_l1(rk + rk_index(x1, y1, S.rk_tiles_x));
-    prefetch_l1(tm + tm_index(x >> 5, y > 0 ? y - 1 : 0, S.wpr));
-    prefetch_l1(tm + tm_index(x >> 5, min(y + 1, H - 1), S.wpr));
-  }
 }
 
 // one pass over up to OW_THREADS / 2 queue positions starting at `tile`: thread 2i + h takes cell i's neighbours
@@ -795,7 +804,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
 template <bool WIDE>
 __global__ void __launch_bounds__(OW_THREADS, 1)
 rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, uint32_t *rk,
-                     Counters *cnt) {
+                     Counters *cnt, uint32_t part, uint32_t n_parts) {
   extern __shared__ uint32_t ow_sh[];
   __shared__ uint32_t sh48[48];
   __shared__ uint32_t s_start;
@@ -814,24 +823,39 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
   Q.to_global = false;
   if (cnt->overflow) return;
   if (WIDE && cnt->ow_fallback != 2u) return;
+  if (!WIDE && (cnt->ow_done || cnt->ow_fallback)) {  // finished, or handed over to the kernels behind this one
+    if (threadIdx.x == 0 && part > 0) cnt->part_end[part] = cnt->part_end[part - 1];
+    return;
+  }
   const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
-  if (threadIdx.x == 0) s_start = S.robot_cell;
-  __syncthreads();
-  if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
-    nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
-    __syncthreads();
-  }
-  const uint32_t start = s_start;
-  if (threadIdx.x == 0) {
-    cnt->start_cell = start;
-    const uint32_t sy = start / W, sx = start - sy * W;
-    Q.q0[0] = (sy << 16) | sx;
-    Q.qm0[0] = 0;
-    rk[rk_index(sx, sy, S.rk_tiles_x)] = 0;
-  }
-  __syncthreads();
   uint32_t base = 0, n = 1, levels = 0, scans = 0;
+  if (WIDE || part == 0) {
+    if (threadIdx.x == 0) s_start = S.robot_cell;
+    __syncthreads();
+    if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+      nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
+      __syncthreads();
+    }
+    const uint32_t start = s_start;
+    if (threadIdx.x == 0) {
+      cnt->start_cell = start;
+      const uint32_t sy = start / W, sx = start - sy * W;
+      Q.q0[0] = (sy << 16) | sx;
+      Q.qm0[0] = 0;
+      rk[rk_index(sx, sy, S.rk_tiles_x)] = 0;
+    }
+  } else {  // the level the previous part stopped at: cells in queue[0, n), their direction masks in the upper half
+    base = cnt->sv_base;
+    n = cnt->sv_n;
+    levels = cnt->sv_levels;
+    for (uint32_t i = threadIdx.x; i < n; i += OW_THREADS) {
+      Q.q0[i] = ld_cg(queue + i);
+      Q.qm0[i] = (uint8_t)ld_cg(queue + S.queue_cap / 2 + i);
+    }
+  }
+  __syncthreads();
+  const uint32_t stop_level = (!WIDE && part + 1 < n_parts) ? (part + 1) * S.ow_part_levels : 0xFFFFFFFFu;
   while (n > 0) {
     uint32_t n_next = 0;
     for (uint32_t tile = 0; tile < n;) {
@@ -845,7 +869,10 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     n = n_next;
     ++levels;
     if (n > S.ow_qcap && !WIDE) {  // uniform (a block-wide total): the next kernel reruns the search (claim[] holds touch
-      if (threadIdx.x == 0) cnt->ow_fallback = S.ow_wide ? 2u : 1u;  // keys only, and it would write the same ones)
+      if (threadIdx.x == 0) {      // keys only, and it would write the same ones)
+        cnt->ow_fallback = S.ow_wide ? 2u : 1u;
+        cnt->part_end[part] = base;  // every level below `base` ranks is complete: those touches stand
+      }
       return;
     }
     uint32_t *tq = Q.q0; Q.q0 = Q.q1; Q.q1 = tq;
@@ -853,13 +880,32 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     tq = Q.g0; Q.g0 = Q.g1; Q.g1 = tq;
     Q.from_global = n > S.ow_qcap;                     // this level did not fit the shared queue: read it from global memory
     Q.to_global = S.ow_wide && 3u * n + 4u > S.ow_qcap;  // a level has at most 3 children per cell: the next one may not fit
+    if (levels >= stop_level && n > 0) {  // hand the level to the next part
+      for (uint32_t i = threadIdx.x; i < n; i += OW_THREADS) {
+        queue[i] = Q.q0[i];
+        queue[S.queue_cap / 2 + i] = Q.qm0[i];
+      }
+      if (threadIdx.x == 0) {
+        cnt->sv_base = base;
+        cnt->sv_n = n;
+        cnt->sv_levels = levels;
+        cnt->part_end[part] = base;
+        for (int i = 0; i < 5; ++i) cnt->prof[i] += s_prof[i];
+        cnt->prof[5] += clock64() - k0;
+      }
+      return;
+    }
   }
   if (threadIdx.x == 0) {
     cnt->bfs_levels = levels;
     cnt->expanded = base;
     cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
-    for (int i = 0; i < 5; ++i) cnt->prof[i] = s_prof[i];
-    cnt->prof[5] = clock64() - k0;
+    if (!WIDE) {
+      cnt->ow_done = 1u;
+      cnt->part_end[part] = base;
+    }
+    for (int i = 0; i < 5; ++i) cnt->prof[i] += s_prof[i];
+    cnt->prof[5] += clock64() - k0;
   }
 }
 
@@ -877,52 +923,64 @@ __global__ void rk_reset_kernel(uint32_t *rk, uint32_t tiles_x, uint32_t tx0, ui
 }
 
 // ------------------------------------------------------------------------------------------------ K4: found components
+// Collections.  The kernels of this section run once after each part of the outer wavefront (`part` = its index, on the
+// second stream, while the next part runs) and once more after the last one (`part` = -1, everything that is left).
+// A collection after part k only looks at touch keys below 4 * part_end[k]: those were written before part k ended, and a
+// component with such a key has its final minimum (keys grow with the dequeue rank).  Keys at or above the bound may be
+// half-written by the part running concurrently and are left for the next collection.
+__device__ __forceinline__ uint32_t collect_bound(const Counters *cnt, int part) {
+  return part < 0 ? KEY_INF : (TOUCH_BIT | (cnt->part_end[part] << 2));
+}
 // per component: smallest touching key (= the seed's key, FrontierSearch.cpp:78-81)
 __global__ void touch_reduce_kernel(const SearchParams S, const uint32_t *__restrict__ mcell, const uint32_t *__restrict__ parent,
-                                    const uint32_t *__restrict__ claim, uint32_t *rkey, const Counters *cnt) {
+                                    const uint32_t *claim, uint32_t *rkey, const Counters *cnt, int part) {
   if (cnt->overflow) return;
-  const uint32_t n = min(cnt->n_mask, S.mask_cap);
+  const uint32_t n = min(cnt->n_mask, S.mask_cap), bound = collect_bound(cnt, part);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t k = claim[mcell[i]];
-    if (k != KEY_INF) atomicMin(rkey + parent[i], k);
+    const uint32_t k = ld_cg(claim + mcell[i]);
+    if (k < bound && k < ld_cg(rkey + parent[i])) atomicMin(rkey + parent[i], k);
   }
 }
-// the cell whose key equals its component's minimum is the seed: append {key, seed, size} to the component table
+// the cell whose key equals its component's minimum is the seed: append {key, seed, size} to the component table (once:
+// the top bit of the root's size marks a component as collected)
 __global__ void seed_collect_kernel(const SearchParams S, const uint32_t *__restrict__ mcell, const uint32_t *__restrict__ parent,
-                                    const uint32_t *__restrict__ claim, const uint32_t *__restrict__ rkey,
-                                    const uint32_t *__restrict__ rsize, const uint32_t *__restrict__ rbox, uint32_t *ckey,
-                                    uint32_t *cseed, uint32_t *csize, uint32_t *cbox, Counters *cnt) {
+                                    const uint32_t *claim, const uint32_t *rkey, uint32_t *rsize, const uint32_t *__restrict__ rbox,
+                                    uint32_t *ckey, uint32_t *cseed, uint32_t *csize, uint32_t *cbox, Counters *cnt, int part) {
   if (cnt->overflow & 3u) return;
-  const uint32_t n = min(cnt->n_mask, S.mask_cap);
+  const uint32_t n = min(cnt->n_mask, S.mask_cap), bound = collect_bound(cnt, part);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const uint32_t c = mcell[i];
-    const uint32_t k = claim[c];
-    if (k == KEY_INF) continue;
+    const uint32_t k = ld_cg(claim + c);
+    if (k >= bound) continue;
     const uint32_t r = parent[i];
-    if (rkey[r] != k) continue;
+    if (ld_cg(rkey + r) != k) continue;
+    const uint32_t sz = rsize[r];  // keys are unique: only this thread matches the component
+    if (sz & 0x80000000u) continue;
+    rsize[r] = sz | 0x80000000u;
     const uint32_t pos = atomicAdd(&cnt->n_comp, 1u);
     if (pos < S.comp_cap) {
       ckey[pos] = k;
       cseed[pos] = c;
-      csize[pos] = rsize[r];
+      csize[pos] = sz;
       reinterpret_cast<uint4 *>(cbox)[pos] = reinterpret_cast<const uint4 *>(rbox)[r];
     } else {
       atomicOr(&cnt->overflow, 4u);
     }
   }
 }
-// discovery order = ascending seed key (keys are unique): rank by counting, scatter into the ordered table
+// discovery order = ascending seed key (keys are unique): rank by counting, scatter into the ordered table.  A collection
+// orders its own components [comp_done, n_comp): every earlier collection's keys are smaller.
 __global__ void __launch_bounds__(256)
 comp_order_kernel(const SearchParams S, const uint32_t *__restrict__ ckey, const uint32_t *__restrict__ cseed,
                   const uint32_t *__restrict__ csize, const uint32_t *__restrict__ cbox, uint32_t *oseed, uint32_t *osize,
                   uint32_t *obox, const Counters *cnt) {
   __shared__ uint32_t sk[256];
-  const uint32_t n = min(cnt->n_comp, S.comp_cap);
-  for (uint32_t i0 = blockIdx.x * 256; i0 < n; i0 += gridDim.x * 256) {
+  const uint32_t n = min(cnt->n_comp, S.comp_cap), c0 = min(cnt->comp_done, n);
+  for (uint32_t i0 = c0 + blockIdx.x * 256; i0 < n; i0 += gridDim.x * 256) {
     const uint32_t i = i0 + threadIdx.x;
     const uint32_t mine = i < n ? ckey[i] : 0;
-    uint32_t r = 0;
-    for (uint32_t base = 0; base < n; base += 256) {
+    uint32_t r = c0;
+    for (uint32_t base = c0; base < n; base += 256) {
       sk[threadIdx.x] = base + threadIdx.x < n ? ckey[base + threadIdx.x] : KEY_INF;
       __syncthreads();
       if (i < n) {
@@ -941,12 +999,13 @@ comp_order_kernel(const SearchParams S, const uint32_t *__restrict__ ckey, const
 // exclusive scans over the ordered components: first cell / first frontier of each; totals into the counters.
 // run lengths (FrontierSearch.cpp:150-199): full runs of max+1 cells, then a remainder kept iff it is > min.
 __global__ void __launch_bounds__(1024)
-comp_scan_kernel(const SearchParams S, const uint32_t *__restrict__ osize, uint32_t *ocell0, uint32_t *ofront0, Counters *cnt) {
+comp_scan_kernel(const SearchParams S, const uint32_t *__restrict__ osize, uint32_t *ocell0, uint32_t *ofront0, Counters *cnt, int coll) {
   __shared__ uint32_t sh[40];
-  const uint32_t n = min(cnt->n_comp, S.comp_cap);
+  const uint32_t n = min(cnt->n_comp, S.comp_cap), c0 = min(cnt->comp_done, n);
   const uint32_t run = (uint32_t)S.max_size + 1u;
-  uint32_t cell_carry = 0, front_carry = 0;
-  for (uint32_t base = 0; base < n; base += 1024) {
+  uint32_t cell_carry = cnt->cell_carry, front_carry = cnt->front_carry;
+  __syncthreads();  // every thread has read the counters thread 0 rewrites below
+  for (uint32_t base = c0; base < n; base += 1024) {
     const uint32_t i = base + threadIdx.x;
     const uint32_t sz = i < n ? osize[i] : 0;
     const uint32_t rem = sz % run;
@@ -962,6 +1021,11 @@ comp_scan_kernel(const SearchParams S, const uint32_t *__restrict__ osize, uint3
     front_carry += tf;
   }
   if (threadIdx.x == 0) {
+    cnt->coll_c0[coll] = c0;
+    cnt->coll_c1[coll] = n;
+    cnt->comp_done = n;
+    cnt->cell_carry = cell_carry;
+    cnt->front_carry = front_carry;
     cnt->n_cells = cell_carry;
     cnt->n_frontiers = front_carry;
     if (cell_carry > S.cell_cap) atomicOr(&cnt->overflow, 8u);
@@ -1046,14 +1110,14 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
 __global__ void __launch_bounds__(32)
 replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const uint2 *__restrict__ tm, const uint32_t *__restrict__ oseed,
                    const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, const uint32_t *__restrict__ obox,
-                   uint32_t *cells, const Counters *cnt, uint32_t min_cells, uint32_t max_cells, uint32_t bit_words) {
+                   uint32_t *cells, const Counters *cnt, uint32_t min_cells, uint32_t max_cells, uint32_t bit_words, int coll) {
   extern __shared__ uint32_t iw_sh[];
   uint32_t *keys = iw_sh, *val = iw_sh + 2 * max_cells, *mir = iw_sh + 4 * max_cells, *bw = iw_sh + 5 * max_cells;
   const uint32_t W = S.map.W, H = S.map.H;
-  const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
+  const uint32_t n_comp = min(cnt->coll_c1[coll], S.comp_cap);  // this collection's components
   if (cnt->overflow) return;
   const uint32_t lane = threadIdx.x;
-  for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
+  for (uint32_t comp = cnt->coll_c0[coll] + blockIdx.x; comp < n_comp; comp += gridDim.x) {
     const uint32_t size = osize[comp];
     if (size < min_cells || size > max_cells) continue;
     uint32_t lg = 5;
@@ -1468,6 +1532,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
   }
   S.rk_tiles_x = (c->W + 7u) / 8u;
+  S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
   S.ow_wide = (c->W <= 16384u && c->H <= 16384u && !getenv("FITSLAM_OW_NOWIDE")) ? 1u : 0u;
   S.use_smem = (s->force_global || c->W > 32768u || c->H > 32768u) ? 0u : 1u;  // queue entries pack y << 16 | x; 32-bit radius prefilter
   if (!s->attr_set) {
@@ -1493,45 +1558,87 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, s->rbox.p, s->mcell.p, c->W, cnt, S.mask_cap);
   if (!s->have_ev) {
     for (auto &e : s->ev_bfs) FS_CUDA(c, cudaEventCreate(&e));
+    for (auto &e : s->ev_part) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : s->ev_coll) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+    FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_join3, cudaEventDisableTiming));
+    FS_CUDA(c, cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+    FS_CUDA(c, cudaStreamCreateWithFlags(&s->stream3, cudaStreamNonBlocking));
+    if (const char *e = getenv("FITSLAM_OW_PARTS")) s->ow_parts = (uint32_t)std::min<long>(std::max<long>(atol(e), 1), OW_PARTS);
     s->have_ev = true;
   }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
+  // one collection: seeds of the components whose keys are final, their discovery order and offsets on stream `st`, their
+  // inner wavefronts behind them; the large size class (the long poles: one warp walks a thin component level by level
+  // for milliseconds) goes to `st_large`, so that the collections queued behind it are not held up
+  auto collect = [&](cudaStream_t st, cudaStream_t st_large, int part) -> cudaError_t {
+    const int coll = part < 0 ? OW_PARTS - 1 : part;
+    touch_reduce_kernel<<<wide, 256, 0, st>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, cnt, part);
+    seed_collect_kernel<<<wide, 256, 0, st>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->rbox.p, s->ckey.p,
+                                              s->cseed.p, s->csize.p, s->cbox.p, cnt, part);
+    comp_order_kernel<<<148 * 2, 256, 0, st>>>(S, s->ckey.p, s->cseed.p, s->csize.p, s->cbox.p, s->oseed.p, s->osize.p, s->obox.p, cnt);
+    comp_scan_kernel<<<1, 1024, 0, st>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, cnt, coll);
+    c->launches += 4;
+    if (S.use_smem) {
+      if (st_large != st) {
+        cudaError_t e = cudaEventRecord(s->ev_coll[coll], st);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(st_large, s->ev_coll[coll], 0);
+        if (e != cudaSuccess) return e;
+      }
+      replay_warp_kernel<<<148 * 2, 32, iw_smem(IW_CELLS, IW_BITS_LARGE), st_large>>>(
+          S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, IW_SMALL + 1, IW_CELLS, IW_BITS_LARGE, coll);
+      replay_warp_kernel<<<148 * 16, 32, iw_smem(IW_SMALL, IW_BITS_SMALL), st>>>(
+          S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL, coll);
+      c->launches += 2;
+    }
+    return cudaSuccess;
+  };
   if (S.use_smem) {
-    // bounding box of the search disc (+ the 3-cell prefetch halo), in 8 x 8 tiles, clipped to the map
+    // bounding box of the search disc (+ a halo), in 8 x 8 tiles, clipped to the map
     const uint32_t rcx = robot_cell % c->W, rcy = robot_cell / c->W;
     const uint32_t rad = (uint32_t)std::min<double>(S.dist_limit / c->res + 8.0, 1e9);
     const uint32_t tx0 = (rcx > rad ? rcx - rad : 0u) >> 3, tx1 = (uint32_t)std::min<uint64_t>((uint64_t)rcx + rad, c->W - 1) >> 3;
     const uint32_t ty0 = (rcy > rad ? rcy - rad : 0u) >> 3, ty1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1) >> 3;
     rk_reset_kernel<<<wide, 256, 0, c->stream>>>(s->rk.p, S.rk_tiles_x, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
     ++c->launches;
-    rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt);
-    rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt);  // returns at once unless a level was too wide
+    // the search in parts on the context stream; after each part but the last, a collection on the second stream
+    const uint32_t n_parts = s->ow_parts;
+    for (uint32_t part = 0; part < n_parts; ++part) {
+      rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, part, n_parts);
+      ++c->launches;
+      if (part + 1 < n_parts) {
+        FS_CUDA(c, cudaEventRecord(s->ev_part[part], c->stream));
+        FS_CUDA(c, cudaStreamWaitEvent(s->stream2, s->ev_part[part], 0));
+        FS_CUDA(c, collect(s->stream2, s->stream3, (int)part));
+      }
+    }
+    FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
+    if (n_parts > 1) {  // the kernels below rewrite or rescan what the collections' table kernels read
+      FS_CUDA(c, cudaEventRecord(s->ev_join, s->stream2));
+      FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join, 0));
+    }
+    FS_CUDA(c, cudaEventRecord(s->ev_bfs[3], c->stream));
+    rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, 0, 1);  // returns at once unless a level was too wide
     ++c->launches;
-    ++c->launches;
+  }
+  else {
+    FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
+    FS_CUDA(c, cudaEventRecord(s->ev_bfs[3], c->stream));
   }
   rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once
-  FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
-  touch_reduce_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, cnt);
-  seed_collect_kernel<<<wide, 256, 0, c->stream>>>(S, s->mcell.p, s->parent.p, s->claim.p, s->rkey.p, s->rsize.p, s->rbox.p,
-                                                    s->ckey.p, s->cseed.p, s->csize.p, s->cbox.p, cnt);
-  comp_order_kernel<<<148 * 2, 256, 0, c->stream>>>(S, s->ckey.p, s->cseed.p, s->csize.p, s->cbox.p, s->oseed.p, s->osize.p,
-                                                     s->obox.p, cnt);
-  comp_scan_kernel<<<1, 1024, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, cnt);
-  if (S.use_smem) {
-    // large components first (two warps per SM, the long poles), then the small ones on the remaining shared memory
-    replay_warp_kernel<<<148 * 2, 32, iw_smem(IW_CELLS, IW_BITS_LARGE), c->stream>>>(
-        S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, IW_SMALL + 1, IW_CELLS, IW_BITS_LARGE);
-    replay_warp_kernel<<<148 * 16, 32, iw_smem(IW_SMALL, IW_BITS_SMALL), c->stream>>>(
-        S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL);
-    c->launches += 2;
-  }
+  FS_CUDA(c, cudaEventRecord(s->ev_bfs[4], c->stream));
+  FS_CUDA(c, collect(c->stream, c->stream, -1));
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
                                                             s->cells.p, cnt);  // components above IW_CELLS cells
+  if (S.use_smem && s->ow_parts > 1) {  // the large inner wavefronts still running on the third stream
+    FS_CUDA(c, cudaEventRecord(s->ev_join3, s->stream3));
+    FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join3, 0));
+  }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[2], c->stream));
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
                                                s->centroids.p, cnt);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
-  c->launches += 12;
+  c->launches += 8;  // mask, union-find x 3, global-memory wavefront, legacy replay, chunk, cleanup
   FS_CUDA(c, cudaGetLastError());
   FS_CUDA(c, cudaMemcpyAsync(host_counters, cnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
   return FITSLAM_OK;
@@ -1561,7 +1668,12 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
     if (getenv("FITSLAM_PROF"))
       fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
               hc->expanded, hc->prof[4], hc->prof[0], hc->prof[1], hc->prof[2], hc->prof[3], hc->prof[5]);
-    cudaEventElapsedTime(&s->bfs_ms, s->ev_bfs[0], s->ev_bfs[1]);
+    {  // the wavefront kernels alone: the parts, and the fallback kernels behind the join with the second stream
+      float a = 0, b = 0;
+      cudaEventElapsedTime(&a, s->ev_bfs[0], s->ev_bfs[1]);
+      cudaEventElapsedTime(&b, s->ev_bfs[3], s->ev_bfs[4]);
+      s->bfs_ms = a + b;
+    }
     if (!hc->overflow) {
       c->n_frontiers = hc->n_frontiers;
       return FITSLAM_OK;
