@@ -78,6 +78,7 @@ struct fitslam_ctx {
   double res = 0, ox = 0, oy = 0;
   bool have_map = false;
   int use_tma = 1;        // FITSLAM_RAYCAST_TMA=0 switches to the direct-gather variant (ablation)
+  size_t ray_smem_attr = 0;  // dynamic shared memory the raycast kernels are opted in for
 
   // ---- ray fan tables (host-built from parameters, uploaded)
   fitslam::RayShape shape{};
@@ -168,8 +169,40 @@ struct SelectState {
 };
 SelectState *sstate(fitslam_ctx *c);
 
+// A slice of the resident frontier list for one scoring launch: frontiers first + [0, count) whose tag matches.  With
+// `range` set, first / count come from device memory at kernel run time ({first, end}, count clamped to `cap`): that is
+// how frontiers are scored while the search that produces them is still running, without a host round trip.
+struct ScoreSlice {
+  const uint32_t *range = nullptr;
+  uint32_t first = 0, count = 0, cap = 0xFFFFFFFFu;
+  const uint8_t *tags = nullptr;  // per frontier: which launch scores it (nullptr: no filter)
+  uint32_t tag = 0;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slot, uint32_t &f) {
+  uint32_t first = s.first, count = s.count;
+  if (s.range) {
+    first = s.range[0];
+    const uint32_t end = s.range[1];
+    count = end > first ? min(end - first, s.cap) : 0u;
+  }
+  if (slot >= count) return false;
+  f = first + slot;
+  return !s.tags || s.tags[f] == s.tag;
+}
+#endif
+static constexpr uint32_t TAG_FINAL = 255;     // frontier produced after the search ended: scored by the host-sized launches
+static constexpr uint32_t EARLY_SLICE_CAP = 512;  // frontiers one early launch covers; what exceeds it is left to the final pass
+// called by the frontier search once per finished batch of frontiers, on a side stream (cycle.cu scores them there)
+struct EarlyHook {
+  fitslam_status (*fn)(fitslam_ctx *c, cudaStream_t stream, const ScoreSlice &slice, void *user);
+  void *user;
+};
+
 // stage entry points (each .cu file)
-fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry);
+fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, const EarlyHook *hook = nullptr);
+uint32_t frontier_capacity(fitslam_ctx *c);          // frontiers the resident list can hold (0 on failure)
+const uint8_t *frontier_tags_device(fitslam_ctx *c);  // per frontier of the last search: TAG_FINAL or the early launch that scored it
 const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_t *n_comp, uint32_t *levels, uint32_t *ambiguous);
 fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, uint32_t first, uint32_t count,
                                    float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
@@ -183,5 +216,10 @@ fitslam_status raycast_limits(fitslam_ctx *c);
 fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_frontiers, uint32_t n,
                              const double poly[4], fitslam_arrival *d_out, uint16_t *d_info_ray,
                              int32_t *d_win_sums, ScoreRecord *d_records);
+fitslam_status raycast_score_slice(fitslam_ctx *c, cudaStream_t stream, const fitslam_frontier *d_frontiers, const double poly[4],
+                                   fitslam_arrival *d_out, ScoreRecord *d_records, const ScoreSlice &slice);
+fitslam_status fisher_score_slice(fitslam_ctx *c, cudaStream_t stream, const fitslam_pose *d_poses, uint32_t poses_per_frontier,
+                                  const ScoreSlice &slice, float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
+                                  const fitslam_arrival *d_arrival);
 
 }  // namespace fitslam

@@ -21,6 +21,7 @@ namespace fitslam {
 struct CycleState {
   DevBuf<fitslam_pose> poses;
   DevBuf<float> fisher;        // per pose
+  DevBuf<float> fisher_best;   // per frontier: Fisher information of its best-yaw pose (cycle_fetch)
   DevBuf<uint8_t> fisher_safe;
   DevBuf<uint32_t> fisher_nvis;
   DevBuf<double> yaw_q;        // per yaw window: qz, qw of orientationAroundZAxis(window * delta_theta + fov / 2)
@@ -44,7 +45,7 @@ static CycleState *cstate(fitslam_ctx *c) {
 void destroy_cycle_state(fitslam_ctx *c) {
   if (!c->cy) return;
   CycleState *s = c->cy;
-  s->poses.release(); s->fisher.release(); s->fisher_safe.release(); s->fisher_nvis.release(); s->yaw_q.release();
+  s->poses.release(); s->fisher.release(); s->fisher_best.release(); s->fisher_safe.release(); s->fisher_nvis.release(); s->yaw_q.release();
   if (s->have_events)
     for (auto &e : s->ev) cudaEventDestroy(e);
   delete s;
@@ -55,11 +56,12 @@ void destroy_cycle_state(fitslam_ctx *c) {
 // delta_theta + fov / 2 for every window (ppf = n_windows) or for the best window only (ppf = 1), i.e. what
 // setGoalOrientation produces (DEP/src/Frontier.cpp:50-56).  A frontier whose ray fan failed has orientation 0.
 __global__ void make_poses_kernel(const fitslam_frontier *__restrict__ fr, const fitslam_arrival *__restrict__ arr,
-                                  const double *__restrict__ yaw_q, uint32_t first_f, uint32_t count_f, uint32_t ppf,
-                                  double z, fitslam_pose *poses) {
+                                  const double *__restrict__ yaw_q, const ScoreSlice slice, uint32_t ppf, double z,
+                                  fitslam_pose *poses) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= count_f * ppf) return;
-  const uint32_t f = first_f + i / ppf, w = i % ppf;
+  const uint32_t slot = i / ppf, w = i - slot * ppf;
+  uint32_t f = 0;
+  if (!slice_frontier(slice, slot, f)) return;
   const uint32_t win = ppf == 1 ? (uint32_t)arr[f].max_index : w;
   fitslam_pose p;
   p.x = fr[f].goal_x;
@@ -75,6 +77,29 @@ __global__ void make_poses_kernel(const fitslam_frontier *__restrict__ fr, const
     p.qw = yaw_q[2 * win + 1];
   }
   poses[(size_t)f * ppf + w] = p;
+}
+
+// Arrival information, candidate poses and Fisher information for one slice of the resident frontier list, on `stream`.
+// The cycle calls it for the rank's block of frontiers; the frontier search calls it (through the hook) for every batch
+// of frontiers that is final while the outer wavefront is still running.
+struct ScoreCfg {
+  CycleState *s;
+  double poly[4];
+  uint32_t ppf;  // 0: no Fisher stage
+};
+static fitslam_status score_slice(fitslam_ctx *c, cudaStream_t stream, const ScoreSlice &sl, void *user) {
+  const ScoreCfg *cfg = static_cast<const ScoreCfg *>(user);
+  CycleState *s = cfg->s;
+  fitslam_status st = raycast_score_slice(c, stream, c->frontiers.p, cfg->poly, c->arrival.p, c->records.p, sl);
+  if (st != FITSLAM_OK || cfg->ppf == 0) return st;
+  const uint64_t slots = sl.range ? sl.cap : sl.count;
+  if (slots == 0) return FITSLAM_OK;
+  const uint64_t np = slots * cfg->ppf;
+  make_poses_kernel<<<(unsigned)((np + 255) / 256), 256, 0, stream>>>(c->frontiers.p, c->arrival.p, s->yaw_q.p, sl, cfg->ppf,
+                                                                       c->prm.candidate_pose_z, s->poses.p);
+  ++c->launches;
+  return fisher_score_slice(c, stream, s->poses.p, cfg->ppf, sl, s->fisher.p, s->fisher_safe.p, s->fisher_nvis.p, c->records.p,
+                            c->arrival.p);
 }
 
 // merged 16-byte records -> fitslam_arrival (the part of the record that other ranks scored)
@@ -146,8 +171,34 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->res.selection.closest_global = -1;
   fitslam_status st = raycast_limits(c);  // once per calculator (DEP/src/CostCalculator.cpp:125-129)
   if (st != FITSLAM_OK) return st;
+  const uint32_t ppf = fisher_mode == FITSLAM_FISHER_OFF ? 0u : (fisher_mode == FITSLAM_FISHER_ALL_YAWS ? c->shape.n_windows : 1u);
+  if (ppf) {
+    st = ensure_yaw_table(c, s);
+    if (st != FITSLAM_OK) return st;
+  }
+  ScoreCfg cfg;
+  cfg.s = s;
+  for (int i = 0; i < 4; ++i) cfg.poly[i] = poly[i];
+  cfg.ppf = ppf;
+  // Unsharded, the frontiers are scored as the search produces them: buffers for as many frontiers as the search can
+  // return are laid out first, and the search calls score_slice on its side streams.  Sharded (one rank of several), a
+  // rank's block of frontiers is only known when the search has ended, so everything is scored after it.
+  EarlyHook hook{score_slice, &cfg};
+  const bool early = c->nranks == 1 && !getenv("FITSLAM_NO_EARLY_SCORING");
+  if (early) {
+    const uint32_t cap = frontier_capacity(c);
+    if (cap == 0) return fail(c, FITSLAM_E_CUDA, "cycle: frontier buffers");
+    FS_CUDA(c, c->arrival.reserve(cap));
+    FS_CUDA(c, c->records.reserve(cap));
+    if (ppf) {
+      FS_CUDA(c, s->poses.reserve((size_t)cap * ppf));
+      FS_CUDA(c, s->fisher.reserve((size_t)cap * ppf));
+      FS_CUDA(c, s->fisher_safe.reserve((size_t)cap * ppf));
+      FS_CUDA(c, s->fisher_nvis.reserve((size_t)cap * ppf));
+    }
+  }
   FS_CUDA(c, cudaEventRecord(s->ev[0], c->stream));
-  st = frontier_search_device(c, rx, ry);  // one host sync inside: the list sizes decide the next launches
+  st = frontier_search_device(c, rx, ry, early ? &hook : nullptr);  // one host sync inside: the list sizes decide the next launches
   if (st != FITSLAM_OK) return st;
   FS_CUDA(c, cudaEventRecord(s->ev[1], c->stream));
   const uint32_t F = c->n_frontiers;
@@ -160,42 +211,44 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->res.ambiguous_sorts = ambiguous;
   if (n_frontiers) *n_frontiers = F;
   if (F == 0) return fail(c, FITSLAM_E_NO_FRONTIERS, "No frontiers found from frontier search.");
-  // ---- arrival information for this rank's block of frontiers
+  // ---- arrival and Fisher information for this rank's block of frontiers: the ones not scored during the search
   const uint32_t B = shard_block(c, F);
+  const uint64_t n_poses = (uint64_t)F * ppf;
+  if (n_poses >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "cycle: too many candidate poses");
   FS_CUDA(c, c->arrival.reserve(F));
   FS_CUDA(c, c->records.reserve((size_t)B * c->nranks));
-  if (c->nranks > 1) {
-    FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)F * sizeof(fitslam_arrival), c->stream));
-    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)B * c->nranks * sizeof(ScoreRecord), c->stream));
-  }
-  st = raycast_score(c, c->frontiers.p, F, poly, c->arrival.p, nullptr, nullptr, c->records.p);
-  if (st != FITSLAM_OK) return st;
-  FS_CUDA(c, cudaEventRecord(s->ev[2], c->stream));
-  s->res.n_candidates = F * c->shape.n_windows;
-  // ---- Fisher information of the candidate poses of the same block
-  s->n_poses = 0;
-  if (fisher_mode != FITSLAM_FISHER_OFF) {
-    st = ensure_yaw_table(c, s);
-    if (st != FITSLAM_OK) return st;
-    const uint32_t ppf = fisher_mode == FITSLAM_FISHER_ALL_YAWS ? c->shape.n_windows : 1u;
-    const uint64_t n_poses = (uint64_t)F * ppf;
-    if (n_poses >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "cycle: too many candidate poses");
-    uint32_t first_f = 0, count_f = F;
-    shard_range(c, F, &first_f, &count_f);
+  if (ppf) {
     FS_CUDA(c, s->poses.reserve(n_poses));
     FS_CUDA(c, s->fisher.reserve(n_poses));
     FS_CUDA(c, s->fisher_safe.reserve(n_poses));
     FS_CUDA(c, s->fisher_nvis.reserve(n_poses));
-    if (c->nranks > 1) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, n_poses * sizeof(float), c->stream));
-    if (count_f) {
-      const uint32_t np = count_f * ppf;
-      make_poses_kernel<<<(np + 255) / 256, 256, 0, c->stream>>>(c->frontiers.p, c->arrival.p, s->yaw_q.p, first_f, count_f, ppf,
-                                                                c->prm.candidate_pose_z, s->poses.p);
-      ++c->launches;
-      st = fisher_score_device(c, s->poses.p, (uint32_t)n_poses, first_f * ppf, np, s->fisher.p, s->fisher_safe.p,
-                               s->fisher_nvis.p, c->records.p, c->arrival.p, ppf);
-      if (st != FITSLAM_OK) return st;
-    }
+  }
+  if (c->nranks > 1) {
+    FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)F * sizeof(fitslam_arrival), c->stream));
+    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)B * c->nranks * sizeof(ScoreRecord), c->stream));
+    if (ppf) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, n_poses * sizeof(float), c->stream));
+  }
+  ScoreSlice rest;
+  shard_range(c, F, &rest.first, &rest.count);
+  rest.tags = frontier_tags_device(c);
+  rest.tag = TAG_FINAL;
+  // two launches so that the stage times keep their meaning: arrival, then poses + Fisher
+  ScoreCfg arrival_only = cfg;
+  arrival_only.ppf = 0;
+  st = score_slice(c, c->stream, rest, &arrival_only);
+  if (st != FITSLAM_OK) return st;
+  FS_CUDA(c, cudaEventRecord(s->ev[2], c->stream));
+  s->res.n_candidates = F * c->shape.n_windows;
+  s->n_poses = 0;
+  if (ppf && rest.count) {
+    make_poses_kernel<<<(unsigned)(((uint64_t)rest.count * ppf + 255) / 256), 256, 0, c->stream>>>(
+        c->frontiers.p, c->arrival.p, s->yaw_q.p, rest, ppf, c->prm.candidate_pose_z, s->poses.p);
+    ++c->launches;
+    st = fisher_score_slice(c, c->stream, s->poses.p, ppf, rest, s->fisher.p, s->fisher_safe.p, s->fisher_nvis.p, c->records.p,
+                            c->arrival.p);
+    if (st != FITSLAM_OK) return st;
+  }
+  if (ppf) {
     s->n_poses = (uint32_t)n_poses;
     s->res.n_fisher_poses = (uint32_t)n_poses;
   }
@@ -277,13 +330,10 @@ fitslam_status fitslam_cycle_fetch(fitslam_ctx *c, fitslam_frontier *frontiers, 
   if (path_heading) FS_CUDA(c, cudaMemcpyAsync(path_heading, ss->head.p, (size_t)F * 8, cudaMemcpyDefault, c->stream));
   if (weighted_cost) FS_CUDA(c, cudaMemcpyAsync(weighted_cost, ss->wc.p, (size_t)F * 8, cudaMemcpyDefault, c->stream));
   if (fisher_info) {  // Fisher information of each frontier's best-yaw pose, from the (merged) records; 0 when the stage was off
-    FS_CUDA(c, s->fisher.reserve(F));
-    float *tmp = nullptr;
-    FS_CUDA(c, cudaMallocAsync((void **)&tmp, (size_t)F * 4, c->stream));
-    gather_fisher_kernel<<<(F + 255) / 256, 256, 0, c->stream>>>(c->records.p, tmp, F);
+    FS_CUDA(c, s->fisher_best.reserve(F));
+    gather_fisher_kernel<<<(F + 255) / 256, 256, 0, c->stream>>>(c->records.p, s->fisher_best.p, F);
     ++c->launches;
-    FS_CUDA(c, cudaMemcpyAsync(fisher_info, tmp, (size_t)F * 4, cudaMemcpyDefault, c->stream));
-    FS_CUDA(c, cudaFreeAsync(tmp, c->stream));
+    FS_CUDA(c, cudaMemcpyAsync(fisher_info, s->fisher_best.p, (size_t)F * 4, cudaMemcpyDefault, c->stream));
   }
   if (sorted && s->res.selection.n_sorted)
     FS_CUDA(c, cudaMemcpyAsync(sorted, ss->sorted.p, (size_t)s->res.selection.n_sorted * 4, cudaMemcpyDefault, c->stream));

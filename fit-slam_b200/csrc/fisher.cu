@@ -573,6 +573,8 @@ struct FisherParams {
   uint32_t first;       // this launch scores poses [first, first + gridDim.x)
   uint32_t poses_per_frontier;  // record f = pose / poses_per_frontier (cycle mode)
   int lut_dense;        // every voxel inside dims has an entry: the visibility test needs no table read
+  int use_slice;        // poses are frontier * poses_per_frontier + window for the frontiers of `slice` (cycle.cu)
+  ScoreSlice slice;
 };
 
 struct PoseFrame {      // per-CTA, built by thread 0
@@ -718,8 +720,16 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   __shared__ uint2 s_chunk[MAX_CHUNKS];  // [first, last) point ranges of the bins that survive the cull
   __shared__ uint32_t s_wq[FISHER_THREADS / 32][64];  // per warp: indices of visible points waiting for the voxel step
   __shared__ double s_red[FISHER_THREADS / 32];
-  const uint32_t pi = P.first + blockIdx.x;
-  if (pi >= P.n_poses) return;
+  uint32_t pi;
+  if (P.use_slice) {
+    const uint32_t slot = blockIdx.x / P.poses_per_frontier;
+    uint32_t f = 0;
+    if (!slice_frontier(P.slice, slot, f)) return;
+    pi = f * P.poses_per_frontier + (blockIdx.x - slot * P.poses_per_frontier);
+  } else {
+    pi = P.first + blockIdx.x;
+    if (pi >= P.n_poses) return;
+  }
   if (threadIdx.x == 0) build_pose_frame(poses[pi], P, F);
   __syncthreads();
   if (threadIdx.x < 11) build_pose_plane(P, F, (int)threadIdx.x);
@@ -884,15 +894,10 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
 
 bool fisher_ready(const fitslam_ctx *c) { return c->fi && c->fi->have_lut && c->fi->have_points; }
 
-// Scores poses [first, first + count) of the n resident poses.
-fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, uint32_t first, uint32_t count,
-                                   float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
-                                   const fitslam_arrival *d_arrival, uint32_t poses_per_frontier) {
+static fitslam_status fisher_params(fitslam_ctx *c, FisherParams &P) {
   FisherState *f = c->fi;
   if (!f || !f->have_lut) return fail(c, FITSLAM_E_NO_LOOKUP_TABLE, "Cannot load lookup table. Please generate it first.");
   if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no map points set");
-  if (n == 0 || count == 0) return FITSLAM_OK;
-  FisherParams P;
   memset(&P, 0, sizeof(P));
   P.pts = f->pts.p;
   P.bin_start = f->bin_start.p;
@@ -909,16 +914,47 @@ fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, 
   P.threshold = c->prm.fisher_information_threshold;
   P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
   P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
-  P.n_poses = n;
-  P.first = first;
-  P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
   P.lut_dense = f->lut_dense ? 1 : 0;
   static bool attr_set = false;
   if (!attr_set) {
     FS_CUDA(c, cudaFuncSetAttribute(fisher_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HASH_SLOTS * 4));
     attr_set = true;
   }
+  return FITSLAM_OK;
+}
+
+// Scores poses [first, first + count) of the n resident poses.
+fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, uint32_t first, uint32_t count,
+                                   float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
+                                   const fitslam_arrival *d_arrival, uint32_t poses_per_frontier) {
+  FisherParams P;
+  const fitslam_status st = fisher_params(c, P);
+  if (st != FITSLAM_OK) return st;
+  if (n == 0 || count == 0) return FITSLAM_OK;
+  P.n_poses = n;
+  P.first = first;
+  P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
   fisher_kernel<<<count, FISHER_THREADS, HASH_SLOTS * 4, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, d_arrival);
+  ++c->launches;
+  FS_CUDA(c, cudaGetLastError());
+  return FITSLAM_OK;
+}
+
+// Scores the candidate poses (frontier * poses_per_frontier + window) of the frontiers of a slice; CTAs of slots outside
+// the slice, or of frontiers another launch scores, return at once.
+fitslam_status fisher_score_slice(fitslam_ctx *c, cudaStream_t stream, const fitslam_pose *d_poses, uint32_t poses_per_frontier,
+                                  const ScoreSlice &slice, float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
+                                  const fitslam_arrival *d_arrival) {
+  FisherParams P;
+  const fitslam_status st = fisher_params(c, P);
+  if (st != FITSLAM_OK) return st;
+  const uint64_t slots = slice.range ? slice.cap : slice.count;
+  if (slots == 0) return FITSLAM_OK;
+  P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
+  P.use_slice = 1;
+  P.slice = slice;
+  fisher_kernel<<<(unsigned)(slots * P.poses_per_frontier), FISHER_THREADS, HASH_SLOTS * 4, stream>>>(P, d_poses, d_info, d_safe, d_nvis,
+                                                                                                     d_rec, d_arrival);
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
   return FITSLAM_OK;

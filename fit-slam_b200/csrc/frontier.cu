@@ -47,10 +47,11 @@ static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
 // components that do not fit)
 static constexpr uint32_t OW_QCAP = 8192;    // outer wavefront: widest level the shared-memory queue holds (80 KB; the rest of the SM's 256 KB stays L1)
 static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 4 + 2 * OW_QCAP;
-// The outer wavefront runs as up to OW_PARTS launches of ow_part_levels levels each (the last one runs to the end).  After
-// part k the components it touched have their final seed (later touches carry larger keys), so their inner wavefronts
-// replay on a second stream while part k + 1 runs: the long thin components that bound the replay time are usually
-// touched long before the outer wavefront ends.
+// The outer wavefront publishes its progress every ow_part_levels levels (OW_PARTS - 1 times at most; the last part runs
+// to the end).  After part k the components it touched have their final seed (later touches carry larger keys), so
+// their inner wavefronts replay on side streams, behind a one-thread kernel that polls the flag, while the wavefront
+// goes on: the long thin components that bound the replay time are usually touched long before it ends.  (Separate
+// launches per part were tried first: once the side streams fill the other SMs, the next part waits for a whole SM.)
 static constexpr int OW_PARTS = 16;          // levels per part: search radius in cells / OW_PARTS (SearchParams::ow_part_levels)
 static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
 static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells (many warps per SM), <= IW_CELLS cells (two per SM)
@@ -73,11 +74,13 @@ struct Counters {
   uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rank_bfs_kernel resumes there
   uint32_t resume_base, resume_n, resume_levels;
   uint32_t ow_done;        // the shared-memory outer wavefront ran out of cells (later parts return at once)
-  uint32_t sv_base, sv_n, sv_levels;   // state handed from one part of the outer wavefront to the next (queue[] holds the level)
+  uint32_t part_flag[OW_PARTS];        // part k of the outer wavefront is complete (published by the kernel, polled by wait_part_kernel)
   uint32_t part_end[OW_PARTS];         // cells dequeued when part k ended: touch keys below 4 * part_end[k] are final after it
   uint32_t comp_done;                  // components ordered and scanned so far
   uint32_t coll_c0[OW_PARTS], coll_c1[OW_PARTS];  // components [c0, c1) of collection k (the one after the last part: OW_PARTS - 1)
+  uint32_t coll_fr[OW_PARTS][2];       // frontiers [first, end) of collection k
   uint32_t cell_carry, front_carry;    // running totals of comp_scan_kernel across collections
+  uint32_t pad[1];
   unsigned long long prof[8];  // FITSLAM_PROF: cycles of warp 0 per phase of the outer wavefront
 };
 
@@ -117,6 +120,7 @@ struct FrontierState {
   DevBuf<uint32_t> oseed, osize, ocell0, ofront0;    // component table in discovery order + offsets
   DevBuf<uint32_t> cells;     // every_frontier list, discovery order
   DevBuf<double> centroids;   // per frontier: centroid after the offset rule (stage dump)
+  DevBuf<uint8_t> ftag;       // per frontier: 0 = not built yet, else the launch that scores it (ctx.h: TAG_FINAL, early tags)
   DevBuf<Counters> counters;
   double search_distance = -1.0;  // < 0: use params.max_frontier_distance
   uint64_t claim_cells = 0;   // cells for which claim is known to be all KEY_INF
@@ -125,7 +129,9 @@ struct FrontierState {
   cudaEvent_t ev_bfs[5] = {};  // outer wavefront: [0] start, [1] last part done, [3] second stream joined, [4] fallback kernels done; [2] replay done
   cudaEvent_t ev_part[OW_PARTS] = {}, ev_coll[OW_PARTS] = {};  // part k of the outer wavefront done; tables of collection k done
   cudaEvent_t ev_join = nullptr, ev_join3 = nullptr;           // second / third stream drained
+  cudaEvent_t ev_chunk[OW_PARTS][2] = {}, ev_score[2] = {};    // frontiers of collection k, size class c built; scoring streams drained
   cudaStream_t stream2 = nullptr, stream3 = nullptr;  // collections that overlap the outer wavefront; their large inner wavefronts
+  cudaStream_t score_stream[2] = {};  // low priority: early scoring of the frontiers of either size class (cycle.cu's hook)
   uint32_t ow_parts = OW_PARTS;    // FITSLAM_OW_PARTS=1: one launch, no overlap (ablation)
   bool have_ev = false;
   bool attr_set = false;
@@ -151,11 +157,15 @@ void destroy_frontier_state(fitslam_ctx *c) {
     for (auto &e : s->ev_coll) cudaEventDestroy(e);
     cudaEventDestroy(s->ev_join);
     cudaEventDestroy(s->ev_join3);
+    for (auto &row : s->ev_chunk)
+      for (auto &e : row) cudaEventDestroy(e);
+    for (auto &e : s->ev_score) cudaEventDestroy(e);
     cudaStreamDestroy(s->stream2);
     cudaStreamDestroy(s->stream3);
+    for (auto &st : s->score_stream) cudaStreamDestroy(st);
   }
   s->oseed.release(); s->osize.release(); s->ocell0.release(); s->ofront0.release();
-  s->cells.release(); s->centroids.release(); s->counters.release();
+  s->cells.release(); s->centroids.release(); s->ftag.release(); s->counters.release();
   delete s;
   c->fs = nullptr;
 }
@@ -804,7 +814,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
 template <bool WIDE>
 __global__ void __launch_bounds__(OW_THREADS, 1)
 rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, uint32_t *rk,
-                     Counters *cnt, uint32_t part, uint32_t n_parts) {
+                     Counters *cnt, uint32_t n_parts) {
   extern __shared__ uint32_t ow_sh[];
   __shared__ uint32_t sh48[48];
   __shared__ uint32_t s_start;
@@ -821,41 +831,34 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
   Q.g1 = queue + S.queue_cap / 2;
   Q.from_global = false;
   Q.to_global = false;
-  if (cnt->overflow) return;
+  // parts [from, n_parts - 1) are complete with `end` cells dequeued: every touch key below 4 * end is in memory (the
+  // atomics of all threads precede the barrier before this call; the fence orders them before the flags)
+  auto publish = [&](uint32_t from, uint32_t end) {
+    if (WIDE || threadIdx.x != 0) return;
+    for (uint32_t k = from; k + 1 < n_parts; ++k) cnt->part_end[k] = end;
+    __threadfence();
+    for (uint32_t k = from; k + 1 < n_parts; ++k) atomicExch(&cnt->part_flag[k], 1u);
+  };
+  if (cnt->overflow) { publish(0, 0); return; }
   if (WIDE && cnt->ow_fallback != 2u) return;
-  if (!WIDE && (cnt->ow_done || cnt->ow_fallback)) {  // finished, or handed over to the kernels behind this one
-    if (threadIdx.x == 0 && part > 0) cnt->part_end[part] = cnt->part_end[part - 1];
-    return;
-  }
   const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
-  uint32_t base = 0, n = 1, levels = 0, scans = 0;
-  if (WIDE || part == 0) {
-    if (threadIdx.x == 0) s_start = S.robot_cell;
+  uint32_t base = 0, n = 1, levels = 0, scans = 0, part = 0;
+  if (threadIdx.x == 0) s_start = S.robot_cell;
+  __syncthreads();
+  if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+    nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
     __syncthreads();
-    if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
-      nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
-      __syncthreads();
-    }
-    const uint32_t start = s_start;
-    if (threadIdx.x == 0) {
-      cnt->start_cell = start;
-      const uint32_t sy = start / W, sx = start - sy * W;
-      Q.q0[0] = (sy << 16) | sx;
-      Q.qm0[0] = 0;
-      rk[rk_index(sx, sy, S.rk_tiles_x)] = 0;
-    }
-  } else {  // the level the previous part stopped at: cells in queue[0, n), their direction masks in the upper half
-    base = cnt->sv_base;
-    n = cnt->sv_n;
-    levels = cnt->sv_levels;
-    for (uint32_t i = threadIdx.x; i < n; i += OW_THREADS) {
-      Q.q0[i] = ld_cg(queue + i);
-      Q.qm0[i] = (uint8_t)ld_cg(queue + S.queue_cap / 2 + i);
-    }
+  }
+  const uint32_t start = s_start;
+  if (threadIdx.x == 0) {
+    cnt->start_cell = start;
+    const uint32_t sy = start / W, sx = start - sy * W;
+    Q.q0[0] = (sy << 16) | sx;
+    Q.qm0[0] = 0;
+    rk[rk_index(sx, sy, S.rk_tiles_x)] = 0;
   }
   __syncthreads();
-  const uint32_t stop_level = (!WIDE && part + 1 < n_parts) ? (part + 1) * S.ow_part_levels : 0xFFFFFFFFu;
   while (n > 0) {
     uint32_t n_next = 0;
     for (uint32_t tile = 0; tile < n;) {
@@ -869,10 +872,8 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     n = n_next;
     ++levels;
     if (n > S.ow_qcap && !WIDE) {  // uniform (a block-wide total): the next kernel reruns the search (claim[] holds touch
-      if (threadIdx.x == 0) {      // keys only, and it would write the same ones)
-        cnt->ow_fallback = S.ow_wide ? 2u : 1u;
-        cnt->part_end[part] = base;  // every level below `base` ranks is complete: those touches stand
-      }
+      if (threadIdx.x == 0) cnt->ow_fallback = S.ow_wide ? 2u : 1u;  // keys only, and it would write the same ones)
+      publish(part, base);  // every level below `base` ranks is complete: those touches stand
       return;
     }
     uint32_t *tq = Q.q0; Q.q0 = Q.q1; Q.q1 = tq;
@@ -880,35 +881,38 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     tq = Q.g0; Q.g0 = Q.g1; Q.g1 = tq;
     Q.from_global = n > S.ow_qcap;                     // this level did not fit the shared queue: read it from global memory
     Q.to_global = S.ow_wide && 3u * n + 4u > S.ow_qcap;  // a level has at most 3 children per cell: the next one may not fit
-    if (levels >= stop_level && n > 0) {  // hand the level to the next part
-      for (uint32_t i = threadIdx.x; i < n; i += OW_THREADS) {
-        queue[i] = Q.q0[i];
-        queue[S.queue_cap / 2 + i] = Q.qm0[i];
-      }
+    if (!WIDE && part + 1 < n_parts && levels >= (part + 1) * S.ow_part_levels) {
       if (threadIdx.x == 0) {
-        cnt->sv_base = base;
-        cnt->sv_n = n;
-        cnt->sv_levels = levels;
         cnt->part_end[part] = base;
-        for (int i = 0; i < 5; ++i) cnt->prof[i] += s_prof[i];
-        cnt->prof[5] += clock64() - k0;
+        __threadfence();
+        atomicExch(&cnt->part_flag[part], 1u);
       }
-      return;
+      ++part;
     }
   }
+  publish(part, base);
   if (threadIdx.x == 0) {
     cnt->bfs_levels = levels;
     cnt->expanded = base;
     cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
-    if (!WIDE) {
-      cnt->ow_done = 1u;
-      cnt->part_end[part] = base;
-    }
-    for (int i = 0; i < 5; ++i) cnt->prof[i] += s_prof[i];
-    cnt->prof[5] += clock64() - k0;
+    for (int i = 0; i < 5; ++i) cnt->prof[i] = s_prof[i];
+    cnt->prof[5] = clock64() - k0;
   }
 }
 
+// One thread on a side stream: returns when part `part` of the outer wavefront has been published, so that the kernels
+// queued behind it see its touch keys.  Gives up (and flags the search as failed) if that never happens.
+__global__ void wait_part_kernel(Counters *cnt, uint32_t part) {
+  const long long t0 = clock64();
+  while (atomicAdd(&cnt->part_flag[part], 0u) == 0u) {
+    __nanosleep(500);
+    if (clock64() - t0 > (60ll << 30)) {  // ~30 s: the wavefront kernel never ran
+      atomicOr(&cnt->overflow, 32u);
+      break;
+    }
+  }
+  __threadfence();
+}
 
 // Resets the rank tiles of the search disc's bounding box to "not dequeued" before the outer wavefront (16-byte stores,
 // all SMs; it also leaves those lines in L2).  The wavefront never leaves the box: cells are enqueued only inside the disc.
@@ -1023,6 +1027,8 @@ comp_scan_kernel(const SearchParams S, const uint32_t *__restrict__ osize, uint3
   if (threadIdx.x == 0) {
     cnt->coll_c0[coll] = c0;
     cnt->coll_c1[coll] = n;
+    cnt->coll_fr[coll][0] = cnt->front_carry;
+    cnt->coll_fr[coll][1] = front_carry;
     cnt->comp_done = n;
     cnt->cell_carry = cell_carry;
     cnt->front_carry = front_carry;
@@ -1362,20 +1368,27 @@ __device__ void s_std_sort(SortCtx &sc) {
 __global__ void __launch_bounds__(64)
 chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0,
              const uint32_t *__restrict__ ofront0, const uint32_t *__restrict__ cells, fitslam_frontier *out,
-             double *centroids, Counters *cnt) {
+             double *centroids, uint8_t *ftag, Counters *cnt, int coll, uint32_t min_cells, uint32_t max_cells, uint32_t tag) {
+  // coll >= 0: the frontiers of collection `coll` whose component is in the size class [min_cells, max_cells] (its inner
+  // wavefronts have just been replayed on this stream), at most EARLY_SLICE_CAP of them; they get `tag`, and the launch
+  // that scores them follows on the same stream.  coll < 0, after the search: every frontier not built yet, TAG_FINAL.
   if (cnt->overflow) return;
-  const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
-  const uint32_t n_front = cnt->n_frontiers;
+  const uint32_t c_lo = coll < 0 ? 0u : cnt->coll_c0[coll], c_hi = coll < 0 ? min(cnt->n_comp, S.comp_cap) : min(cnt->coll_c1[coll], S.comp_cap);
+  const uint32_t f_lo = coll < 0 ? 0u : cnt->coll_fr[coll][0];
+  const uint32_t f_hi = coll < 0 ? cnt->n_frontiers : min(cnt->coll_fr[coll][1], f_lo + EARLY_SLICE_CAP);
+  if (f_hi > S.front_cap) return;
   const uint32_t run = (uint32_t)S.max_size + 1u;
   const uint32_t W = S.map.W;
-  for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < n_front; f += gridDim.x * blockDim.x) {
+  for (uint32_t f = f_lo + blockIdx.x * blockDim.x + threadIdx.x; f < f_hi; f += gridDim.x * blockDim.x) {
+    if (coll < 0 && ftag[f] != 0) continue;
     // component of frontier f: last comp with ofront0[comp] <= f
-    uint32_t lo = 0, hi = n_comp;
+    uint32_t lo = c_lo, hi = c_hi;
     while (hi - lo > 1) {
       const uint32_t mid = (lo + hi) >> 1;
       if (ofront0[mid] <= f) lo = mid; else hi = mid;
     }
     const uint32_t comp = lo, j = f - ofront0[comp];
+    if (coll >= 0 && (osize[comp] < min_cells || osize[comp] > max_cells)) continue;
     const uint32_t first_cell = ocell0[comp] + j * run;
     const int n = (int)min(run, osize[comp] - j * run);
     const uint32_t *cl = cells + first_cell;
@@ -1429,6 +1442,7 @@ chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uin
     r.chunk = j;
     r.first_cell = first_cell;
     out[f] = r;
+    ftag[f] = (uint8_t)tag;
     if (centroids) {
       centroids[2 * f] = centerX;
       centroids[2 * f + 1] = centerY;
@@ -1500,13 +1514,14 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   FS_CUDA(c, s->ofront0.reserve(s->comp_cap));
   FS_CUDA(c, s->cells.reserve(s->cell_cap));
   FS_CUDA(c, s->centroids.reserve(2 * (size_t)s->front_cap));
+  FS_CUDA(c, s->ftag.reserve(s->front_cap));
   FS_CUDA(c, c->frontiers.reserve(s->front_cap));
   return FITSLAM_OK;
 }
 
 // Enqueue one search on the context stream; counters land in *host_counters (pinned) after the stream drains.
 static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t robot_cell, double rx, double ry,
-                                     Counters *host_counters) {
+                                     Counters *host_counters, const EarlyHook *hook) {
   SearchParams S;
   memset(&S, 0, sizeof(S));
   S.map = map_view(c);
@@ -1550,6 +1565,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   S.front_cap = s->front_cap;
   Counters *cnt = s->counters.p;
   FS_CUDA(c, cudaMemsetAsync(cnt, 0, sizeof(Counters), c->stream));
+  FS_CUDA(c, cudaMemsetAsync(s->ftag.p, 0, s->front_cap, c->stream));
   const uint64_t n_words = (uint64_t)S.wpr * c->H;
   const unsigned wide = 148 * 8;
   mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
@@ -1562,8 +1578,16 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     for (auto &e : s->ev_coll) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
     FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_join3, cudaEventDisableTiming));
-    FS_CUDA(c, cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
-    FS_CUDA(c, cudaStreamCreateWithFlags(&s->stream3, cudaStreamNonBlocking));
+    for (auto &row : s->ev_chunk)
+      for (auto &e : row) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : s->ev_score) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    // the collections are short kernels on the critical path of their components; the scoring launches they feed are
+    // long and fill every SM, so they run at the lowest priority and the collections take the slots that free up first
+    int prio_lo = 0, prio_hi = 0;
+    FS_CUDA(c, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    FS_CUDA(c, cudaStreamCreateWithPriority(&s->stream2, cudaStreamNonBlocking, prio_hi));
+    FS_CUDA(c, cudaStreamCreateWithPriority(&s->stream3, cudaStreamNonBlocking, prio_hi));
+    for (auto &st : s->score_stream) FS_CUDA(c, cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, prio_lo));
     if (const char *e = getenv("FITSLAM_OW_PARTS")) s->ow_parts = (uint32_t)std::min<long>(std::max<long>(atol(e), 1), OW_PARTS);
     s->have_ev = true;
   }
@@ -1590,6 +1614,28 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
       replay_warp_kernel<<<148 * 16, 32, iw_smem(IW_SMALL, IW_BITS_SMALL), st>>>(
           S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL, coll);
       c->launches += 2;
+      if (part >= 0 && hook) {
+        // the frontiers of the components just replayed are final: build them and hand them to the scorer, per size class
+        // on the stream that replayed it (frontier.cu knows nothing about scoring: cycle.cu's hook launches it)
+        const uint32_t *range = &cnt->coll_fr[coll][0];
+        cudaStream_t sts[2] = {st, st_large};
+        const uint32_t lo[2] = {0u, IW_SMALL + 1u}, hi[2] = {IW_SMALL, IW_CELLS};
+        for (int cls = 0; cls < 2; ++cls) {
+          const uint32_t tag = 1u + 2u * (uint32_t)coll + (uint32_t)cls;
+          chunk_kernel<<<148 * 2, 64, 0, sts[cls]>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
+                                                     s->centroids.p, s->ftag.p, cnt, coll, lo[cls], hi[cls], tag);
+          ++c->launches;
+          ScoreSlice sl;
+          sl.range = range;
+          sl.cap = EARLY_SLICE_CAP;
+          sl.tags = s->ftag.p;
+          sl.tag = tag;
+          cudaError_t e = cudaEventRecord(s->ev_chunk[coll][cls], sts[cls]);
+          if (e == cudaSuccess) e = cudaStreamWaitEvent(s->score_stream[cls], s->ev_chunk[coll][cls], 0);
+          if (e != cudaSuccess) return e;
+          if (hook->fn(c, s->score_stream[cls], sl, hook->user) != FITSLAM_OK) return cudaErrorUnknown;
+        }
+      }
     }
     return cudaSuccess;
   };
@@ -1601,16 +1647,19 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     const uint32_t ty0 = (rcy > rad ? rcy - rad : 0u) >> 3, ty1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1) >> 3;
     rk_reset_kernel<<<wide, 256, 0, c->stream>>>(s->rk.p, S.rk_tiles_x, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
     ++c->launches;
-    // the search in parts on the context stream; after each part but the last, a collection on the second stream
+    // the search on the context stream; behind each published part but the last, a collection on the second stream
     const uint32_t n_parts = s->ow_parts;
-    for (uint32_t part = 0; part < n_parts; ++part) {
-      rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, part, n_parts);
+    if (n_parts > 1) {  // the side stream starts behind the counters reset and the union-find
+      FS_CUDA(c, cudaEventRecord(s->ev_part[0], c->stream));
+      FS_CUDA(c, cudaStreamWaitEvent(s->stream2, s->ev_part[0], 0));
+    }
+    rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
+    ++c->launches;
+    FS_CUDA(c, cudaGetLastError());  // (the kernels below poll flags only this one sets)
+    for (uint32_t part = 0; part + 1 < n_parts; ++part) {
+      wait_part_kernel<<<1, 1, 0, s->stream2>>>(cnt, part);
       ++c->launches;
-      if (part + 1 < n_parts) {
-        FS_CUDA(c, cudaEventRecord(s->ev_part[part], c->stream));
-        FS_CUDA(c, cudaStreamWaitEvent(s->stream2, s->ev_part[part], 0));
-        FS_CUDA(c, collect(s->stream2, s->stream3, (int)part));
-      }
+      FS_CUDA(c, collect(s->stream2, s->stream3, (int)part));
     }
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
     if (n_parts > 1) {  // the kernels below rewrite or rescan what the collections' table kernels read
@@ -1618,7 +1667,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
       FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join, 0));
     }
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[3], c->stream));
-    rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, 0, 1);  // returns at once unless a level was too wide
+    rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, 1);  // returns at once unless a level was too wide
     ++c->launches;
   }
   else {
@@ -1636,16 +1685,28 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[2], c->stream));
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
-                                               s->centroids.p, cnt);
+                                               s->centroids.p, s->ftag.p, cnt, -1, 0, 0xFFFFFFFFu, TAG_FINAL);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
   c->launches += 8;  // mask, union-find x 3, global-memory wavefront, legacy replay, chunk, cleanup
+  if (S.use_smem && s->ow_parts > 1 && hook)
+    for (int cls = 0; cls < 2; ++cls) {  // scores of the early batches: complete when the search is
+      FS_CUDA(c, cudaEventRecord(s->ev_score[cls], s->score_stream[cls]));
+      FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_score[cls], 0));
+    }
   FS_CUDA(c, cudaGetLastError());
   FS_CUDA(c, cudaMemcpyAsync(host_counters, cnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
   return FITSLAM_OK;
 }
 
 // FrontierSearch::searchFrom on the device; the frontier list stays resident in c->frontiers (c->n_frontiers entries).
-fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
+uint32_t frontier_capacity(fitslam_ctx *c) {
+  if (!c->have_map) return 0;
+  FrontierState *s = fr_state(c);
+  return ensure_frontier_buffers(c, s) == FITSLAM_OK ? s->front_cap : 0u;
+}
+const uint8_t *frontier_tags_device(fitslam_ctx *c) { return fr_state(c)->ftag.p; }
+
+fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, const EarlyHook *hook) {
   if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
   if (c->prm.max_frontier_cluster_size + 1 > MAX_CHUNK || c->prm.max_frontier_cluster_size + 1 <= c->prm.min_frontier_cluster_size)
     return fail(c, FITSLAM_E_INVALID, "search_frontiers: need min_frontier_cluster_size < max_frontier_cluster_size + 1 <= 64");
@@ -1661,7 +1722,8 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
     st = ensure_frontier_buffers(c, s);
     if (st != FITSLAM_OK) return st;
     Counters *hc = reinterpret_cast<Counters *>(c->pinned);
-    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc);
+    // (a repeated attempt has grown the lists: the caller sized its buffers for the first one, so no early scoring then)
+    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, attempt == 0 ? hook : nullptr);
     if (st != FITSLAM_OK) return st;
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
     s->last = *hc;
@@ -1685,6 +1747,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry) {
     if (hc->overflow & 16u) s->front_cap = hc->n_frontiers + hc->n_frontiers / 8 + 1024;
     s->cell_cap = std::max(s->cell_cap, s->mask_cap);
     if (hc->overflow & 2u) return fail(c, FITSLAM_E_INVALID, "search_frontiers: wavefront queue overflow");
+    if (hc->overflow & 32u) return fail(c, FITSLAM_E_CUDA, "search_frontiers: the outer wavefront never published its progress");
   }
   return fail(c, FITSLAM_E_INVALID, "search_frontiers: buffers still too small after 8 attempts");
 }

@@ -62,7 +62,7 @@ struct RayParams {
   uint32_t fpb;             // frontiers per block
   uint32_t tile_stride;     // bytes between the windows of two frontiers (multiple of 128)
   uint32_t n;               // frontiers in the list
-  uint32_t first, count;    // shard: this launch scores frontiers [first, first + count)
+  ScoreSlice slice;         // this launch scores the frontiers of the slice (a rank's shard, or a batch scored early)
 };
 
 // Costmap2D::worldToMap (nav2_costmap_2d, ROS 2 Humble)
@@ -134,8 +134,8 @@ raycast_kernel(const RayParams P, const fitslam_frontier *__restrict__ fr,
   int32_t *gflag = flags_all + g * 2;  // [0] any ray failed, [1] footprint in lethal
 
   const uint32_t slot = blockIdx.x * P.fpb + g;
-  const bool live = slot < P.count;
-  const uint32_t f = live ? P.first + slot : 0u;
+  uint32_t f = 0u;
+  const bool live = slice_frontier(P.slice, slot, f);
 
   double sx = 0.0, sy = 0.0;
   int fsize = 0;
@@ -343,7 +343,7 @@ static RayParams make_params(fitslam_ctx *c, const double poly[4], uint32_t n) {
   P.tpf = (std::max(c->shape.n_rays, 32u) + 31u) & ~31u;
   P.tile_stride = (P.tile_w * P.tile_h + 127u) & ~127u;
   P.n = n;
-  shard_range(c, n, &P.first, &P.count);
+  shard_range(c, n, &P.slice.first, &P.slice.count);
   return P;
 }
 
@@ -376,30 +376,42 @@ fitslam_status raycast_limits(fitslam_ctx *c) {
   return FITSLAM_OK;
 }
 
-fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_fr, uint32_t n, const double poly[4],
-                             fitslam_arrival *d_out, uint16_t *d_info_ray, int32_t *d_win, ScoreRecord *d_rec) {
-  if (n == 0) return FITSLAM_OK;
-  RayParams P = make_params(c, poly, n);
+static fitslam_status raycast_launch(fitslam_ctx *c, cudaStream_t stream, RayParams &P, uint32_t slots, const fitslam_frontier *d_fr,
+                                     fitslam_arrival *d_out, uint16_t *d_info_ray, int32_t *d_win, ScoreRecord *d_rec) {
   const bool tma = c->use_tma && c->pitch >= P.tile_w;
   // frontiers per block: fill ~256 threads, bounded by shared memory
   uint32_t fpb = std::max(1u, 256u / P.tpf);
   while (fpb > 1 && (size_t)fpb * P.tile_stride > 96 * 1024) --fpb;
   P.fpb = fpb;
   const size_t smem = smem_bytes(P, tma);
-  const uint32_t n_local = P.count;
-  if (n_local == 0) return FITSLAM_OK;
-  const uint32_t grid = (n_local + fpb - 1) / fpb;
+  if (slots == 0) return FITSLAM_OK;
+  const uint32_t grid = (slots + fpb - 1) / fpb;
   const uint32_t block = fpb * P.tpf;
-  if (tma) {
+  if (c->ray_smem_attr < smem) {  // (set before the early launches run concurrently: the value only grows)
     FS_CUDA(c, cudaFuncSetAttribute(raycast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    raycast_kernel<true><<<grid, block, smem, c->stream>>>(P, d_fr, d_out, d_info_ray, d_win, d_rec);
-  } else {
     FS_CUDA(c, cudaFuncSetAttribute(raycast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    raycast_kernel<false><<<grid, block, smem, c->stream>>>(P, d_fr, d_out, d_info_ray, d_win, d_rec);
+    c->ray_smem_attr = smem;
   }
+  if (tma) raycast_kernel<true><<<grid, block, smem, stream>>>(P, d_fr, d_out, d_info_ray, d_win, d_rec);
+  else raycast_kernel<false><<<grid, block, smem, stream>>>(P, d_fr, d_out, d_info_ray, d_win, d_rec);
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
   return FITSLAM_OK;
+}
+
+fitslam_status raycast_score(fitslam_ctx *c, const fitslam_frontier *d_fr, uint32_t n, const double poly[4],
+                             fitslam_arrival *d_out, uint16_t *d_info_ray, int32_t *d_win, ScoreRecord *d_rec) {
+  if (n == 0) return FITSLAM_OK;
+  RayParams P = make_params(c, poly, n);
+  return raycast_launch(c, c->stream, P, P.slice.count, d_fr, d_out, d_info_ray, d_win, d_rec);
+}
+
+// the same for a slice of the resident list (cycle.cu: batches scored while the search runs, then the rest)
+fitslam_status raycast_score_slice(fitslam_ctx *c, cudaStream_t stream, const fitslam_frontier *d_fr, const double poly[4],
+                                   fitslam_arrival *d_out, ScoreRecord *d_rec, const ScoreSlice &slice) {
+  RayParams P = make_params(c, poly, 0);
+  P.slice = slice;
+  return raycast_launch(c, stream, P, slice.range ? slice.cap : slice.count, d_fr, d_out, nullptr, nullptr, d_rec);
 }
 
 }  // namespace fitslam
