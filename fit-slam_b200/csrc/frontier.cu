@@ -52,6 +52,7 @@ static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 4 + 2 * OW_QCAP;
 // their inner wavefronts replay on side streams, behind a one-thread kernel that polls the flag, while the wavefront
 // goes on: the long thin components that bound the replay time are usually touched long before it ends.  (Separate
 // launches per part were tried first: once the side streams fill the other SMs, the next part waits for a whole SM.)
+static constexpr int OW_LARGE_STREAMS = 4;
 static constexpr int OW_PARTS = 16;          // levels per part: search radius in cells / OW_PARTS (SearchParams::ow_part_levels)
 static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
 static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells (many warps per SM), <= IW_CELLS cells (two per SM)
@@ -128,10 +129,12 @@ struct FrontierState {
   Counters last{};
   cudaEvent_t ev_bfs[5] = {};  // outer wavefront: [0] start, [1] last part done, [3] second stream joined, [4] fallback kernels done; [2] replay done
   cudaEvent_t ev_part[OW_PARTS] = {}, ev_coll[OW_PARTS] = {};  // part k of the outer wavefront done; tables of collection k done
-  cudaEvent_t ev_join = nullptr, ev_join3 = nullptr;           // second / third stream drained
-  cudaEvent_t ev_chunk[OW_PARTS][2] = {}, ev_score[2] = {};    // frontiers of collection k, size class c built; scoring streams drained
-  cudaStream_t stream2 = nullptr, stream3 = nullptr;  // collections that overlap the outer wavefront; their large inner wavefronts
-  cudaStream_t score_stream[2] = {};  // low priority: early scoring of the frontiers of either size class (cycle.cu's hook)
+  cudaEvent_t ev_join = nullptr, ev_join_large[OW_LARGE_STREAMS] = {};  // side streams drained
+  cudaEvent_t ev_chunk[OW_PARTS][2] = {}, ev_score[1 + OW_LARGE_STREAMS] = {};  // frontiers of collection k, size class c built; scoring streams drained
+  cudaStream_t stream2 = nullptr;     // collections that overlap the outer wavefront: tables, small inner wavefronts
+  cudaStream_t stream_large[OW_LARGE_STREAMS] = {};  // their large inner wavefronts, collection k on stream k % OW_LARGE_STREAMS: one
+                                      // warp walks a thin component for up to milliseconds, and must not hold up the next collection
+  cudaStream_t score_stream[1 + OW_LARGE_STREAMS] = {};  // low priority: early scoring (cycle.cu's hook), [0] small class, [1 + i] behind stream_large[i]
   uint32_t ow_parts = OW_PARTS;    // FITSLAM_OW_PARTS=1: one launch, no overlap (ablation)
   bool have_ev = false;
   bool attr_set = false;
@@ -156,12 +159,12 @@ void destroy_frontier_state(fitslam_ctx *c) {
     for (auto &e : s->ev_part) cudaEventDestroy(e);
     for (auto &e : s->ev_coll) cudaEventDestroy(e);
     cudaEventDestroy(s->ev_join);
-    cudaEventDestroy(s->ev_join3);
+    for (auto &e : s->ev_join_large) cudaEventDestroy(e);
     for (auto &row : s->ev_chunk)
       for (auto &e : row) cudaEventDestroy(e);
     for (auto &e : s->ev_score) cudaEventDestroy(e);
     cudaStreamDestroy(s->stream2);
-    cudaStreamDestroy(s->stream3);
+    for (auto &st : s->stream_large) cudaStreamDestroy(st);
     for (auto &st : s->score_stream) cudaStreamDestroy(st);
   }
   s->oseed.release(); s->osize.release(); s->ocell0.release(); s->ofront0.release();
@@ -1577,7 +1580,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     for (auto &e : s->ev_part) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : s->ev_coll) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
-    FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_join3, cudaEventDisableTiming));
+    for (auto &e : s->ev_join_large) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &row : s->ev_chunk)
       for (auto &e : row) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : s->ev_score) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1586,7 +1589,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     int prio_lo = 0, prio_hi = 0;
     FS_CUDA(c, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     FS_CUDA(c, cudaStreamCreateWithPriority(&s->stream2, cudaStreamNonBlocking, prio_hi));
-    FS_CUDA(c, cudaStreamCreateWithPriority(&s->stream3, cudaStreamNonBlocking, prio_hi));
+    for (auto &st : s->stream_large) FS_CUDA(c, cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, prio_hi));
     for (auto &st : s->score_stream) FS_CUDA(c, cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, prio_lo));
     if (const char *e = getenv("FITSLAM_OW_PARTS")) s->ow_parts = (uint32_t)std::min<long>(std::max<long>(atol(e), 1), OW_PARTS);
     s->have_ev = true;
@@ -1631,9 +1634,10 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
           sl.tags = s->ftag.p;
           sl.tag = tag;
           cudaError_t e = cudaEventRecord(s->ev_chunk[coll][cls], sts[cls]);
-          if (e == cudaSuccess) e = cudaStreamWaitEvent(s->score_stream[cls], s->ev_chunk[coll][cls], 0);
+          cudaStream_t sc = s->score_stream[cls == 0 ? 0 : 1 + coll % OW_LARGE_STREAMS];
+          if (e == cudaSuccess) e = cudaStreamWaitEvent(sc, s->ev_chunk[coll][cls], 0);
           if (e != cudaSuccess) return e;
-          if (hook->fn(c, s->score_stream[cls], sl, hook->user) != FITSLAM_OK) return cudaErrorUnknown;
+          if (hook->fn(c, sc, sl, hook->user) != FITSLAM_OK) return cudaErrorUnknown;
         }
       }
     }
@@ -1659,7 +1663,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     for (uint32_t part = 0; part + 1 < n_parts; ++part) {
       wait_part_kernel<<<1, 1, 0, s->stream2>>>(cnt, part);
       ++c->launches;
-      FS_CUDA(c, collect(s->stream2, s->stream3, (int)part));
+      FS_CUDA(c, collect(s->stream2, s->stream_large[part % OW_LARGE_STREAMS], (int)part));
     }
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
     if (n_parts > 1) {  // the kernels below rewrite or rescan what the collections' table kernels read
@@ -1679,19 +1683,20 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   FS_CUDA(c, collect(c->stream, c->stream, -1));
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
                                                             s->cells.p, cnt);  // components above IW_CELLS cells
-  if (S.use_smem && s->ow_parts > 1) {  // the large inner wavefronts still running on the third stream
-    FS_CUDA(c, cudaEventRecord(s->ev_join3, s->stream3));
-    FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join3, 0));
-  }
+  if (S.use_smem && s->ow_parts > 1)  // the large inner wavefronts still running on their streams
+    for (int i = 0; i < OW_LARGE_STREAMS; ++i) {
+      FS_CUDA(c, cudaEventRecord(s->ev_join_large[i], s->stream_large[i]));
+      FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join_large[i], 0));
+    }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[2], c->stream));
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
                                                s->centroids.p, s->ftag.p, cnt, -1, 0, 0xFFFFFFFFu, TAG_FINAL);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
   c->launches += 8;  // mask, union-find x 3, global-memory wavefront, legacy replay, chunk, cleanup
   if (S.use_smem && s->ow_parts > 1 && hook)
-    for (int cls = 0; cls < 2; ++cls) {  // scores of the early batches: complete when the search is
-      FS_CUDA(c, cudaEventRecord(s->ev_score[cls], s->score_stream[cls]));
-      FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_score[cls], 0));
+    for (int i = 0; i < 1 + OW_LARGE_STREAMS; ++i) {  // scores of the early batches: complete when the search is
+      FS_CUDA(c, cudaEventRecord(s->ev_score[i], s->score_stream[i]));
+      FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_score[i], 0));
     }
   FS_CUDA(c, cudaGetLastError());
   FS_CUDA(c, cudaMemcpyAsync(host_counters, cnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
@@ -1730,6 +1735,11 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
     if (getenv("FITSLAM_PROF"))
       fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
               hc->expanded, hc->prof[4], hc->prof[0], hc->prof[1], hc->prof[2], hc->prof[3], hc->prof[5]);
+    if (getenv("FITSLAM_PROF")) {
+      fprintf(stderr, "collections (cells dequeued | frontiers):");
+      for (int k = 0; k < OW_PARTS; ++k) fprintf(stderr, " %u|%u", hc->part_end[k], hc->coll_fr[k][1] - hc->coll_fr[k][0]);
+      fprintf(stderr, "\n");
+    }
     {  // the wavefront kernels alone: the parts, and the fallback kernels behind the join with the second stream
       float a = 0, b = 0;
       cudaEventElapsedTime(&a, s->ev_bfs[0], s->ev_bfs[1]);
