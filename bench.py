@@ -244,7 +244,9 @@ def run_gpu(args):
     roof = {"bound": "hbm", "kernel": "rank_bfs_smem_kernel (inside stage extract)", "achieved": ab["extract"] / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None,
             "peak": peak, "unit": "GB/s", "peak_source": "measured" if peaks else "fallback", "traffic": traffic,
             "algorithmic_bytes_per_launch": ab["extract"], "kernel_ms": dom_ms,
-            "note": "latency-bound level-synchronous wavefront (one CTA, 2205 dependent levels): see DESIGN.md; per-stage fractions below",
+            "note": "latency-bound level-synchronous wavefront (one CTA, 2205 dependent levels): see DESIGN.md; per-stage fractions below. "
+                    "On one GPU the arrival + Fisher scoring of finished frontier batches runs on side streams while this kernel runs, so "
+                    "stages arrival / fisher only hold the batch scored after the search (FITSLAM_NO_EARLY_SCORING=1 separates them)",
             "stages": {n: {"ms": stage_ms[n], "algorithmic_bytes": ab[k2], "gbs": ab[k2] / (stage_ms[n] * 1e-3) / 1e9 if stage_ms[n] > 0 else None}
                        for n, k2 in (("extract", "extract"), ("arrival", "arrival"), ("fisher", "fisher"), ("normalise_select", "select"))}}
     roof["frac"] = roof["achieved"] / peak if roof["achieved"] else None
