@@ -161,7 +161,7 @@ def run_gpu(args):
             assert st == 0, st
             rec = ctx.records_tensor()
             with torch.cuda.stream(stream):  # NCCL orders itself after the scoring kernels of this stream
-                shard.allgather_records_(rec, rank, world)
+                shard.allreduce_records_(rec, world)
             res = ctx.cycle_end()
         last["res"] = res
         return res
@@ -259,7 +259,7 @@ def run_gpu(args):
         "config": {"workload": wl.describe(F, n_rays, n_win, max_len),
                    "stages": ["extract", "arrival", "fisher(all yaws)", "plan", "normalise", "select"],
                    "l2": "flushed between steps (256 MiB memset)",
-                   "sharding": (f"frontier blocks of ceil(F/{world}) per rank, extraction replicated, NCCL all-gather of 16 B records"
+                   "sharding": (f"frontier f scored by rank f % {world}, extraction replicated, NCCL all-reduce (integer sum into zeroed rows) of the 16 B records"
                                 if world > 1 else "none"),
                    "components": int(res.n_components), "frontier_cells": int(res.n_frontier_cells),
                    "wavefront_levels": int(res.bfs_levels)},

@@ -282,6 +282,7 @@ fitslam_status fitslam_score_arrival(fitslam_ctx *c, const fitslam_frontier *fro
   FS_CUDA(c, c->arrival.reserve(n));
   const size_t n_rec = (size_t)shard_block(c, n) * c->nranks;  // nranks equal blocks (in-place all-gather layout)
   FS_CUDA(c, c->records.reserve(n_rec));
+  c->records_rows = n_rec;
   if (info_along_ray) FS_CUDA(c, c->info_ray.reserve((size_t)n * s.n_rays));
   if (window_sums) FS_CUDA(c, c->win_sums.reserve((size_t)n * s.n_windows));
   if (c->nranks > 1) {  // records of the other shards stay zero until the caller merges them
@@ -304,7 +305,7 @@ fitslam_status fitslam_score_arrival(fitslam_ctx *c, const fitslam_frontier *fro
 fitslam_status fitslam_score_records(fitslam_ctx *c, void **device_ptr, uint64_t *bytes) {
   if (!c || !device_ptr || !bytes) return fail(c, FITSLAM_E_INVALID, "score_records: null argument");
   *device_ptr = c->records.p;
-  *bytes = (uint64_t)shard_block(c, c->n_frontiers) * c->nranks * sizeof(ScoreRecord);  // nranks equal blocks
+  *bytes = c->records_rows * sizeof(ScoreRecord);  // cycle: one row per frontier; score_arrival: nranks equal blocks
   return FITSLAM_OK;
 }
 

@@ -95,6 +95,7 @@ struct fitslam_ctx {
   fitslam::DevBuf<uint16_t> info_ray;
   fitslam::DevBuf<int32_t> win_sums;
   fitslam::DevBuf<fitslam::ScoreRecord> records;
+  uint64_t records_rows = 0;  // rows of `records` the last scoring call laid out (fitslam_score_records)
 
   // ---- scratch
   fitslam::DevBuf<uint8_t> scratch;
@@ -136,8 +137,12 @@ inline MapView map_view(const fitslam_ctx *c) {
 }
 
 fitslam_status ensure_pinned(fitslam_ctx *c, size_t bytes);
-// candidate sharding: rank r owns the contiguous block [r * B, min(n, (r + 1) * B)), B = ceil(n / nranks),
-// so the per-frontier score records of all ranks concatenate into one in-place all-gather buffer of nranks * B records
+// candidate sharding.  In the cycle, rank r owns the frontiers f with f % nranks == r: ownership is then known
+// the moment a frontier exists, so a rank can score its share while the search is still running; every rank writes its
+// 16-byte records into a zeroed buffer of one record per frontier, and an all-reduce (integer sum: one owner, zeros
+// elsewhere) merges them.  The stand-alone scoring calls (fitslam_score_arrival / _fisher on a caller's list) use
+// contiguous blocks instead: rank r owns [r * B, min(n, (r + 1) * B)), B = ceil(n / nranks), and their records
+// concatenate into an in-place all-gather buffer of nranks * B records
 inline uint32_t shard_block(const fitslam_ctx *c, uint32_t n) { return (n + (uint32_t)c->nranks - 1) / (uint32_t)c->nranks; }
 inline void shard_range(const fitslam_ctx *c, uint32_t n, uint32_t *first, uint32_t *count) {
   const uint32_t B = shard_block(c, n);
@@ -177,6 +182,7 @@ struct ScoreSlice {
   uint32_t first = 0, count = 0, cap = 0xFFFFFFFFu;
   const uint8_t *tags = nullptr;  // per frontier: which launch scores it (nullptr: no filter)
   uint32_t tag = 0;
+  uint32_t mod = 1, rem = 0;      // only frontiers f with f % mod == rem (the cycle's sharding: rank `rem` of `mod`)
 };
 #ifdef __CUDACC__
 __device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slot, uint32_t &f) {
@@ -188,6 +194,7 @@ __device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slo
   }
   if (slot >= count) return false;
   f = first + slot;
+  if (s.mod > 1u && f % s.mod != s.rem) return false;
   return !s.tags || s.tags[f] == s.tag;
 }
 #endif

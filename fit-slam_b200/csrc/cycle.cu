@@ -87,9 +87,12 @@ struct ScoreCfg {
   double poly[4];
   uint32_t ppf;  // 0: no Fisher stage
 };
-static fitslam_status score_slice(fitslam_ctx *c, cudaStream_t stream, const ScoreSlice &sl, void *user) {
+static fitslam_status score_slice(fitslam_ctx *c, cudaStream_t stream, const ScoreSlice &sl_in, void *user) {
   const ScoreCfg *cfg = static_cast<const ScoreCfg *>(user);
   CycleState *s = cfg->s;
+  ScoreSlice sl = sl_in;  // this rank's share of the slice
+  sl.mod = (uint32_t)c->nranks;
+  sl.rem = (uint32_t)c->rank;
   fitslam_status st = raycast_score_slice(c, stream, c->frontiers.p, cfg->poly, c->arrival.p, c->records.p, sl);
   if (st != FITSLAM_OK || cfg->ppf == 0) return st;
   const uint64_t slots = sl.range ? sl.cap : sl.count;
@@ -180,13 +183,14 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   cfg.s = s;
   for (int i = 0; i < 4; ++i) cfg.poly[i] = poly[i];
   cfg.ppf = ppf;
-  // Unsharded, the frontiers are scored as the search produces them: buffers for as many frontiers as the search can
-  // return are laid out first, and the search calls score_slice on its side streams.  Sharded (one rank of several), a
-  // rank's block of frontiers is only known when the search has ended, so everything is scored after it.
+  // The frontiers are scored as the search produces them: buffers for as many frontiers as the search can return are laid
+  // out first, and the search calls score_slice on its side streams.  With several ranks each scores the frontiers f with
+  // f % nranks == rank into zeroed buffers (the caller's all-reduce merges the records).
   EarlyHook hook{score_slice, &cfg};
-  const bool early = c->nranks == 1 && !getenv("FITSLAM_NO_EARLY_SCORING");
+  const bool early = !getenv("FITSLAM_NO_EARLY_SCORING");
+  uint32_t cap = 0;
   if (early) {
-    const uint32_t cap = frontier_capacity(c);
+    cap = frontier_capacity(c);
     if (cap == 0) return fail(c, FITSLAM_E_CUDA, "cycle: frontier buffers");
     FS_CUDA(c, c->arrival.reserve(cap));
     FS_CUDA(c, c->records.reserve(cap));
@@ -195,6 +199,11 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
       FS_CUDA(c, s->fisher.reserve((size_t)cap * ppf));
       FS_CUDA(c, s->fisher_safe.reserve((size_t)cap * ppf));
       FS_CUDA(c, s->fisher_nvis.reserve((size_t)cap * ppf));
+    }
+    if (c->nranks > 1) {  // what the other ranks score stays zero
+      FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)cap * sizeof(fitslam_arrival), c->stream));
+      FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)cap * sizeof(ScoreRecord), c->stream));
+      if (ppf) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, (size_t)cap * ppf * sizeof(float), c->stream));
     }
   }
   FS_CUDA(c, cudaEventRecord(s->ev[0], c->stream));
@@ -211,25 +220,31 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->res.ambiguous_sorts = ambiguous;
   if (n_frontiers) *n_frontiers = F;
   if (F == 0) return fail(c, FITSLAM_E_NO_FRONTIERS, "No frontiers found from frontier search.");
-  // ---- arrival and Fisher information for this rank's block of frontiers: the ones not scored during the search
-  const uint32_t B = shard_block(c, F);
+  // ---- arrival and Fisher information for this rank's share of the frontiers: the ones not scored during the search
   const uint64_t n_poses = (uint64_t)F * ppf;
   if (n_poses >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "cycle: too many candidate poses");
-  FS_CUDA(c, c->arrival.reserve(F));
-  FS_CUDA(c, c->records.reserve((size_t)B * c->nranks));
-  if (ppf) {
-    FS_CUDA(c, s->poses.reserve(n_poses));
-    FS_CUDA(c, s->fisher.reserve(n_poses));
-    FS_CUDA(c, s->fisher_safe.reserve(n_poses));
-    FS_CUDA(c, s->fisher_nvis.reserve(n_poses));
+  const bool scored_early = early && F <= cap;  // (a search that had to grow its lists was repeated without the hook)
+  if (!scored_early) {
+    FS_CUDA(c, c->arrival.reserve(F));
+    FS_CUDA(c, c->records.reserve(F));
+    if (ppf) {
+      FS_CUDA(c, s->poses.reserve(n_poses));
+      FS_CUDA(c, s->fisher.reserve(n_poses));
+      FS_CUDA(c, s->fisher_safe.reserve(n_poses));
+      FS_CUDA(c, s->fisher_nvis.reserve(n_poses));
+    }
+    if (c->nranks > 1) {
+      FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)F * sizeof(fitslam_arrival), c->stream));
+      FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)F * sizeof(ScoreRecord), c->stream));
+      if (ppf) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, n_poses * sizeof(float), c->stream));
+    }
   }
-  if (c->nranks > 1) {
-    FS_CUDA(c, cudaMemsetAsync(c->arrival.p, 0, (size_t)F * sizeof(fitslam_arrival), c->stream));
-    FS_CUDA(c, cudaMemsetAsync(c->records.p, 0, (size_t)B * c->nranks * sizeof(ScoreRecord), c->stream));
-    if (ppf) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, n_poses * sizeof(float), c->stream));
-  }
+  c->records_rows = F;
   ScoreSlice rest;
-  shard_range(c, F, &rest.first, &rest.count);
+  rest.first = 0;
+  rest.count = F;
+  rest.mod = (uint32_t)c->nranks;
+  rest.rem = (uint32_t)c->rank;
   rest.tags = frontier_tags_device(c);
   rest.tag = TAG_FINAL;
   // two launches so that the stage times keep their meaning: arrival, then poses + Fisher

@@ -238,10 +238,11 @@ FITSLAM_API fitslam_status fitslam_cycle(fitslam_ctx *ctx, double robot_x, doubl
                                          const double poly_xy_min_max[4], int fisher_mode,
                                          fitslam_cycle_result *result);
 /* The same cycle in two halves, for candidate sharding across GPUs (8e).  cycle_begin: searchFrom (replicated on
- * every rank), then arrival information and Fisher information for this rank's block of frontiers
- * (fitslam_set_shard); the 16-byte score records are left on the device (fitslam_score_records) laid out for an
- * in-place all-gather.  The caller all-gathers them (NCCL), then cycle_end unpacks the merged records and runs the
- * global steps: setPlanForFrontierEuclidean, U1, getFilteredFrontiersN.  With one rank, cycle == begin + end. */
+ * every rank), with arrival information and Fisher information for this rank's share of the frontiers (frontier f
+ * belongs to rank f % nranks, fitslam_set_shard) scored while the search runs; the 16-byte score records are left on the
+ * device (fitslam_score_records): one row per frontier, zero where another rank scores.  The caller sums them over the
+ * ranks as int32 (NCCL all-reduce), then cycle_end unpacks the merged records and runs the global steps:
+ * setPlanForFrontierEuclidean, U1, getFilteredFrontiersN.  With one rank, cycle == begin + end. */
 FITSLAM_API fitslam_status fitslam_cycle_begin(fitslam_ctx *ctx, double robot_x, double robot_y, double robot_yaw,
                                                const double poly_xy_min_max[4], int fisher_mode, uint32_t *n_frontiers);
 FITSLAM_API fitslam_status fitslam_cycle_end(fitslam_ctx *ctx, fitslam_cycle_result *result);

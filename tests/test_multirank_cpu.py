@@ -1,5 +1,6 @@
 """The N > 1 path on CPU: world_size-2 `gloo` processes exercise the host-side sharding (fit-slam_b200/shard.py, the
-mirror of shard_block / shard_range in csrc/ctx.h) and the one collective of the path, the in-place all-gather of the
+mirror of shard_block / shard_range in csrc/ctx.h) and the collectives of the path: the integer all-reduce of the cycle's
+zero-padded record rows (frontier f on rank f % world) and, for the stand-alone scoring calls, the in-place all-gather of the
 16-byte score records.  Each rank scores ITS block of frontiers -- here with the CPU oracle standing in
 for the kernels, which is what a checker is for -- and after the all-gather every rank must hold exactly the records a
 single rank computes for the whole list."""
@@ -58,6 +59,18 @@ def _worker(rank, world, port, out_dir):
         got = t.numpy().reshape(-1).view(shard.RECORD_DTYPE)
         assert np.array_equal(got, want), "merged records differ from the single-rank records"
         np.save(os.path.join(out_dir, f"rec{rank}.npy"), t.numpy())
+        # the cycle's sharding: frontier f on rank f % world, zero-padded rows, merged by an integer all-reduce
+        own = np.array([shard.owner(f, world) == rank for f in range(F)])
+        rec2 = np.zeros(F, shard.RECORD_DTYPE)
+        arr_own, _, _ = orc.score_arrival(a, meta, fr[own], poly)
+        fisher = (np.arange(F, dtype=np.float32) * -0.37 + 1.25)[own]  # any bit patterns: they must survive the sum
+        rec2[own] = shard.pack_records(arr_own, fisher=fisher)
+        t2 = torch.from_numpy(rec2.view(np.int32).reshape(-1, 4))
+        shard.allreduce_records_(t2, world)
+        want2 = shard.pack_records(arr_all, fisher=np.arange(F, dtype=np.float32) * -0.37 + 1.25)
+        got2 = t2.numpy().reshape(-1).view(shard.RECORD_DTYPE)
+        assert got2.tobytes() == want2.tobytes(), "all-reduced records differ from the single-rank records"
+        np.save(os.path.join(out_dir, f"red{rank}.npy"), t2.numpy())
     finally:
         dist.destroy_process_group()
 
@@ -88,3 +101,6 @@ def test_two_rank_allgather_of_score_records(tmp_path):
     r0 = np.load(tmp_path / "rec0.npy")
     r1 = np.load(tmp_path / "rec1.npy")
     assert np.array_equal(r0, r1) and r0.any()
+    d0 = np.load(tmp_path / "red0.npy")
+    d1 = np.load(tmp_path / "red1.npy")
+    assert np.array_equal(d0, d1) and d0.any()
