@@ -1572,9 +1572,6 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   const uint64_t n_words = (uint64_t)S.wpr * c->H;
   const unsigned wide = 148 * 8;
   mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
-  uf_init_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rkey.p, s->rsize.p, s->rbox.p, cnt, S.mask_cap);
-  uf_merge_kernel<<<wide, 256, 0, c->stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
-  uf_compress_kernel<<<wide, 256, 0, c->stream>>>(s->parent.p, s->rsize.p, s->rbox.p, s->mcell.p, c->W, cnt, S.mask_cap);
   if (!s->have_ev) {
     for (auto &e : s->ev_bfs) FS_CUDA(c, cudaEventCreate(&e));
     for (auto &e : s->ev_part) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1594,6 +1591,16 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     if (const char *e = getenv("FITSLAM_OW_PARTS")) s->ow_parts = (uint32_t)std::min<long>(std::max<long>(atol(e), 1), OW_PARTS);
     s->have_ev = true;
   }
+  // the union-find feeds the collections, not the outer wavefront: when collections run on the side stream, so does it
+  const bool side = S.use_smem && s->ow_parts > 1;
+  cudaStream_t uf_stream = side ? s->stream2 : c->stream;
+  if (side) {  // the side stream starts behind the counters reset and the mask
+    FS_CUDA(c, cudaEventRecord(s->ev_part[0], c->stream));
+    FS_CUDA(c, cudaStreamWaitEvent(s->stream2, s->ev_part[0], 0));
+  }
+  uf_init_kernel<<<wide, 256, 0, uf_stream>>>(s->parent.p, s->rkey.p, s->rsize.p, s->rbox.p, cnt, S.mask_cap);
+  uf_merge_kernel<<<wide, 256, 0, uf_stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
+  uf_compress_kernel<<<wide, 256, 0, uf_stream>>>(s->parent.p, s->rsize.p, s->rbox.p, s->mcell.p, c->W, cnt, S.mask_cap);
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
   // one collection: seeds of the components whose keys are final, their discovery order and offsets on stream `st`, their
   // inner wavefronts behind them; the large size class (the long poles: one warp walks a thin component level by level
@@ -1653,10 +1660,6 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     ++c->launches;
     // the search on the context stream; behind each published part but the last, a collection on the second stream
     const uint32_t n_parts = s->ow_parts;
-    if (n_parts > 1) {  // the side stream starts behind the counters reset and the union-find
-      FS_CUDA(c, cudaEventRecord(s->ev_part[0], c->stream));
-      FS_CUDA(c, cudaStreamWaitEvent(s->stream2, s->ev_part[0], 0));
-    }
     rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
     ++c->launches;
     FS_CUDA(c, cudaGetLastError());  // (the kernels below poll flags only this one sets)
