@@ -786,15 +786,11 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   const uint32_t excl = __popc(b0 & lt) + 2u * __popc(b1 & lt);
   if (lane == 0) ws[wid] = __popc(b0) + 2u * __popc(b1);
   __syncthreads();
+  // every warp needs the block total and the sum of the warps before it: two warp reductions (REDUX) over the 32 warp
+  // totals instead of a shuffle scan
   const uint32_t wv = lane < OW_THREADS / 32 ? ws[lane] : 0u;
-  uint32_t wi = wv;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-    if ((int)lane >= o) wi += t;
-  }
-  const uint32_t total = __shfl_sync(0xffffffffu, wi, 31);
-  const uint32_t wbase = __shfl_sync(0xffffffffu, wi - wv, wid);
+  const uint32_t total = __reduce_add_sync(0xffffffffu, wv);
+  const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
   uint32_t dst = n_next + wbase + excl;
   const long long c3 = clock64();
   // append the winners in (position, slot) order
