@@ -123,6 +123,15 @@ const char *fitslam_status_string(fitslam_status s) {
   return "unknown status";
 }
 
+// The context stream carries the critical path of a cycle; the launches that score finished batches of frontiers beside
+// it run on lowest-priority streams (frontier.cu), so it takes the highest priority the device offers.
+static cudaError_t create_context_stream(cudaStream_t *st) {
+  int lo = 0, hi = 0;
+  cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  if (e != cudaSuccess) return e;
+  return cudaStreamCreateWithPriority(st, cudaStreamNonBlocking, hi);
+}
+
 fitslam_status fitslam_create(const fitslam_params *p, int device, fitslam_ctx **out) {
   if (!out) return FITSLAM_E_INVALID;
   *out = nullptr;
@@ -141,7 +150,7 @@ fitslam_status fitslam_create(const fitslam_params *p, int device, fitslam_ctx *
     return FITSLAM_E_INVALID;
   }
   c->device = device;
-  if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+  if (cudaSetDevice(device) != cudaSuccess || create_context_stream(&c->stream) != cudaSuccess) {
     cudaGetLastError();
     delete c;
     return FITSLAM_E_CUDA;

@@ -185,6 +185,11 @@ struct ScoreSlice {
   uint32_t mod = 1, rem = 0;      // only frontiers f with f % mod == rem (the cycle's sharding: rank `rem` of `mod`)
 };
 #ifdef __CUDACC__
+__device__ __forceinline__ uint32_t slice_slots(const ScoreSlice &s) {  // slots of the slice (owned or not, any tag)
+  if (!s.range) return s.count;
+  const uint32_t first = s.range[0], end = s.range[1];
+  return end > first ? min(end - first, s.cap) : 0u;
+}
 __device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slot, uint32_t &f) {
   uint32_t first = s.first, count = s.count;
   if (s.range) {

@@ -127,7 +127,7 @@ struct FrontierState {
   uint64_t claim_cells = 0;   // cells for which claim is known to be all KEY_INF
   uint32_t mask_cap = 0, queue_cap = 0, comp_cap = 0, cell_cap = 0, front_cap = 0;
   Counters last{};
-  cudaEvent_t ev_bfs[5] = {};  // outer wavefront: [0] start, [1] last part done, [3] second stream joined, [4] fallback kernels done; [2] replay done
+  cudaEvent_t ev_bfs[7] = {};  // outer wavefront: [0] start, [1] last part done, [3] second stream joined, [4] fallback kernels done; [2] replay done
   cudaEvent_t ev_part[OW_PARTS] = {}, ev_coll[OW_PARTS] = {};  // part k of the outer wavefront done; tables of collection k done
   cudaEvent_t ev_join = nullptr, ev_join_large[OW_LARGE_STREAMS] = {};  // side streams drained
   cudaEvent_t ev_chunk[OW_PARTS][2] = {}, ev_score[1 + OW_LARGE_STREAMS] = {};  // frontiers of collection k, size class c built; scoring streams drained
@@ -1520,7 +1520,7 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
 
 // Enqueue one search on the context stream; counters land in *host_counters (pinned) after the stream drains.
 static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t robot_cell, double rx, double ry,
-                                     Counters *host_counters, const EarlyHook *hook) {
+                                     Counters *host_counters, const EarlyHook *hook, int phase) {
   SearchParams S;
   memset(&S, 0, sizeof(S));
   S.map = map_view(c);
@@ -1563,11 +1563,18 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   S.cell_cap = s->cell_cap;
   S.front_cap = s->front_cap;
   Counters *cnt = s->counters.p;
-  FS_CUDA(c, cudaMemsetAsync(cnt, 0, sizeof(Counters), c->stream));
-  FS_CUDA(c, cudaMemsetAsync(s->ftag.p, 0, s->front_cap, c->stream));
+  // phase 0: the search.  phase 1 (only after the host has seen ow_fallback in the counters of phase 0: a level too wide
+  // for the shared-memory queue): the kernels that redo the wavefront with global-memory queues, then a collection of what
+  // they found.  They used to follow the shared-memory kernel unconditionally and return at once; but each is one CTA of
+  // 1024 threads that needs a whole free SM, and waited up to 0.5 ms for one while the scoring launches filled them all.
   const uint64_t n_words = (uint64_t)S.wpr * c->H;
   const unsigned wide = 148 * 8;
-  mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
+  if (phase == 0) {
+    FS_CUDA(c, cudaMemsetAsync(cnt, 0, sizeof(Counters), c->stream));
+    FS_CUDA(c, cudaMemsetAsync(s->ftag.p, 0, s->front_cap, c->stream));
+    mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
+    c->launches += 1;
+  }
   if (!s->have_ev) {
     for (auto &e : s->ev_bfs) FS_CUDA(c, cudaEventCreate(&e));
     for (auto &e : s->ev_part) FS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1588,15 +1595,18 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     s->have_ev = true;
   }
   // the union-find feeds the collections, not the outer wavefront: when collections run on the side stream, so does it
-  const bool side = S.use_smem && s->ow_parts > 1;
+  const bool side = S.use_smem && s->ow_parts > 1 && phase == 0;
   cudaStream_t uf_stream = side ? s->stream2 : c->stream;
   if (side) {  // the side stream starts behind the counters reset and the mask
     FS_CUDA(c, cudaEventRecord(s->ev_part[0], c->stream));
     FS_CUDA(c, cudaStreamWaitEvent(s->stream2, s->ev_part[0], 0));
   }
-  uf_init_kernel<<<wide, 256, 0, uf_stream>>>(s->parent.p, s->rkey.p, s->rsize.p, s->rbox.p, cnt, S.mask_cap);
-  uf_merge_kernel<<<wide, 256, 0, uf_stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
-  uf_compress_kernel<<<wide, 256, 0, uf_stream>>>(s->parent.p, s->rsize.p, s->rbox.p, s->mcell.p, c->W, cnt, S.mask_cap);
+  if (phase == 0) {
+    uf_init_kernel<<<wide, 256, 0, uf_stream>>>(s->parent.p, s->rkey.p, s->rsize.p, s->rbox.p, cnt, S.mask_cap);
+    uf_merge_kernel<<<wide, 256, 0, uf_stream>>>(S, s->bits.p, s->slot.p, s->mcell.p, s->parent.p, cnt);
+    uf_compress_kernel<<<wide, 256, 0, uf_stream>>>(s->parent.p, s->rsize.p, s->rbox.p, s->mcell.p, c->W, cnt, S.mask_cap);
+    c->launches += 3;
+  }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[0], c->stream));
   // one collection: seeds of the components whose keys are final, their discovery order and offsets on stream `st`, their
   // inner wavefronts behind them; the large size class (the long poles: one warp walks a thin component level by level
@@ -1646,7 +1656,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     }
     return cudaSuccess;
   };
-  if (S.use_smem) {
+  if (S.use_smem && phase == 0) {
     // bounding box of the search disc (+ a halo), in 8 x 8 tiles, clipped to the map
     const uint32_t rcx = robot_cell % c->W, rcy = robot_cell / c->W;
     const uint32_t rad = (uint32_t)std::min<double>(S.dist_limit / c->res + 8.0, 1e9);
@@ -1670,19 +1680,22 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
       FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join, 0));
     }
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[3], c->stream));
-    rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, 1);  // returns at once unless a level was too wide
-    ++c->launches;
-  }
-  else {
+  } else {
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[3], c->stream));
+    if (S.use_smem) {  // phase 1, ow_fallback == 2: the search again, wide levels spilled to a global-memory queue
+      rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, 1);
+      ++c->launches;
+    }
+    // the global-memory wavefront: the whole search when the shared-memory path is off, else only for ow_fallback == 1
+    rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);
+    ++c->launches;
   }
-  rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);  // fallback: returns at once
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[4], c->stream));
   FS_CUDA(c, collect(c->stream, c->stream, -1));
   replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
                                                             s->cells.p, cnt);  // components above IW_CELLS cells
-  if (S.use_smem && s->ow_parts > 1)  // the large inner wavefronts still running on their streams
+  if (side)  // the large inner wavefronts still running on their streams: the frontiers not built yet may be theirs
     for (int i = 0; i < OW_LARGE_STREAMS; ++i) {
       FS_CUDA(c, cudaEventRecord(s->ev_join_large[i], s->stream_large[i]));
       FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_join_large[i], 0));
@@ -1691,13 +1704,15 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
                                                s->centroids.p, s->ftag.p, cnt, -1, 0, 0xFFFFFFFFu, TAG_FINAL);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
-  c->launches += 8;  // mask, union-find x 3, global-memory wavefront, legacy replay, chunk, cleanup
-  if (S.use_smem && s->ow_parts > 1 && hook)
+  c->launches += 3;  // legacy replay, chunk, cleanup
+  FS_CUDA(c, cudaEventRecord(s->ev_bfs[5], c->stream));
+  if (side && hook)
     for (int i = 0; i < 1 + OW_LARGE_STREAMS; ++i) {  // scores of the early batches: complete when the search is
       FS_CUDA(c, cudaEventRecord(s->ev_score[i], s->score_stream[i]));
       FS_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_score[i], 0));
     }
   FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaEventRecord(s->ev_bfs[6], c->stream));
   FS_CUDA(c, cudaMemcpyAsync(host_counters, cnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
   return FITSLAM_OK;
 }
@@ -1727,14 +1742,25 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
     if (st != FITSLAM_OK) return st;
     Counters *hc = reinterpret_cast<Counters *>(c->pinned);
     // (a repeated attempt has grown the lists: the caller sized its buffers for the first one, so no early scoring then)
-    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, attempt == 0 ? hook : nullptr);
+    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, attempt == 0 ? hook : nullptr, 0);
     if (st != FITSLAM_OK) return st;
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (hc->ow_fallback && !hc->overflow) {  // a level too wide for the shared-memory queue: redo the wavefront, collect the rest
+      st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, nullptr, 1);
+      if (st != FITSLAM_OK) return st;
+      FS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
     s->last = *hc;
     if (getenv("FITSLAM_PROF"))
       fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
               hc->expanded, hc->prof[4], hc->prof[0], hc->prof[1], hc->prof[2], hc->prof[3], hc->prof[5]);
     if (getenv("FITSLAM_PROF")) {
+      float t[6] = {0, 0, 0, 0, 0, 0};
+      const int seq[7] = {0, 1, 3, 4, 2, 5, 6};
+      for (int i = 0; i < 6; ++i) cudaEventElapsedTime(&t[i], s->ev_bfs[seq[i]], s->ev_bfs[seq[i + 1]]);
+      fprintf(stderr, "context stream, ms: outer wavefront %.3f | wait for the collections %.3f | fallback kernels %.3f | last collection + "
+                      "large inner wavefronts %.3f | frontiers of the rest, cleanup %.3f | wait for the early scoring %.3f\n",
+              t[0], t[1], t[2], t[3], t[4], t[5]);
       fprintf(stderr, "collections (cells dequeued | frontiers):");
       for (int k = 0; k < OW_PARTS; ++k) fprintf(stderr, " %u|%u", hc->part_end[k], hc->coll_fr[k][1] - hc->coll_fr[k][0]);
       fprintf(stderr, "\n");
