@@ -718,7 +718,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   extern __shared__ uint32_t tab[];  // HASH_SLOTS packed slots: (voxel + 1) << CNT_BITS | count, 0 = empty
   __shared__ uint32_t s_used, s_overflow, s_nchunk, s_next, s_chunk_ovf;
   __shared__ uint2 s_chunk[MAX_CHUNKS];  // [first, last) point ranges of the bins that survive the cull
-  __shared__ uint32_t s_wq[FISHER_THREADS / 32][64];  // per warp: indices of visible points waiting for the voxel step
+  __shared__ float s_wq[FISHER_THREADS / 32][3][64];  // per warp: coordinates of visible points waiting for the voxel step
+                                                       // (kept here instead of their indices: no second load per point)
   __shared__ double s_red[FISHER_THREADS / 32];
   uint32_t pi;
   if (P.use_slice) {
@@ -810,7 +811,7 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
       uint32_t my_used = 0;
       // Two steps per point, with a compaction in between: the visibility test runs on every point of the chunk, the
       // indices of the visible ones (about 4 in 10) queue up per warp, and the voxel + table step runs on full warps.
-      uint32_t *wq = s_wq[wid];
+      float (*wq)[64] = s_wq[wid];
       uint32_t n_q = 0;
       while (true) {
         uint32_t ci = 0;
@@ -820,19 +821,25 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
         const uint2 ch = last ? make_uint2(0, 0) : s_chunk[ci];
         for (uint32_t i0 = ch.x; i0 < ch.y || (last && n_q > 0); i0 += 32) {
           const uint32_t i = i0 + lane;
-          const bool vis = i < ch.y && point_visible(__ldg(P.pts + i), F, P);
+          float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (i < ch.y) q = __ldg(P.pts + i);
+          const bool vis = i < ch.y && point_visible(q, F, P);
           const uint32_t bal = __ballot_sync(0xffffffffu, vis);
-          if (vis) wq[n_q + __popc(bal & ((1u << lane) - 1u))] = i;
+          if (vis) {
+            const uint32_t at = n_q + __popc(bal & ((1u << lane) - 1u));
+            wq[0][at] = q.x; wq[1][at] = q.y; wq[2][at] = q.z;
+          }
           n_q += __popc(bal);
           __syncwarp();
           if (n_q >= 32 || (last && n_q > 0)) {
             const uint32_t take = min(n_q, 32u);
             int vox = -1;
-            if (lane < take) vox = voxel_of_visible_point(__ldg(P.pts + wq[lane]), F, P);
+            if (lane < take) vox = voxel_of_visible_point(make_float4(wq[0][lane], wq[1][lane], wq[2][lane], 0.f), F, P);
             const uint32_t rest = n_q - take;
-            const uint32_t moved = lane < rest ? wq[32 + lane] : 0u;
+            float m0 = 0.f, m1 = 0.f, m2 = 0.f;
+            if (lane < rest) { m0 = wq[0][32 + lane]; m1 = wq[1][32 + lane]; m2 = wq[2][32 + lane]; }
             __syncwarp();
-            if (lane < rest) wq[lane] = moved;
+            if (lane < rest) { wq[0][lane] = m0; wq[1][lane] = m1; wq[2][lane] = m2; }
             n_q = rest;
             __syncwarp();
             if (vox >= 0) {
