@@ -74,7 +74,7 @@ struct Counters {
   uint32_t dirty_queue;    // entries of queue[] whose claim words (and their 4 neighbours') the cleanup must reset
   uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rank_bfs_kernel resumes there
   uint32_t resume_base, resume_n, resume_levels;
-  uint32_t ow_done;        // the shared-memory outer wavefront ran out of cells (later parts return at once)
+  uint32_t widest_level;   // cells in the widest level of the shared-memory outer wavefront
   uint32_t part_flag[OW_PARTS];        // part k of the outer wavefront is complete (published by the kernel, polled by wait_part_kernel)
   uint32_t part_end[OW_PARTS];         // cells dequeued when part k ended: touch keys below 4 * part_end[k] are final after it
   uint32_t comp_done;                  // components ordered and scanned so far
@@ -101,6 +101,7 @@ struct SearchParams {
   uint32_t ow_wide;        // 1: levels wider than ow_qcap spill to the global queue (maps up to 16384 cells a side)
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
   uint32_t ow_part_levels; // levels per launch of the shared-memory outer wavefront
+  uint32_t early_cap;      // frontiers one early scoring launch covers (what exceeds it waits for the launches after the search)
 };
 
 struct FrontierState {
@@ -139,6 +140,7 @@ struct FrontierState {
   bool have_ev = false;
   bool attr_set = false;
   int force_global = -1;      // FITSLAM_WAVEFRONT=global selects the global-memory wavefront kernels (ablation / fallback test)
+  bool prefer_wide = false;   // the last search met a level wider than the shared-memory queue: start with the spill instantiation
   float bfs_ms = 0, replay_ms = 0;
 };
 
@@ -807,9 +809,9 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
 }
 
 // WIDE = false: every level fits the shared-memory queue; a level that does not ends the kernel with ow_fallback = 2 (the
-// WIDE = true instantiation, launched right after, redoes the search with the global-memory queue spill; ranks already
-// written are the ones it will write again) or 1 (maps above 16384 cells a side: rank_bfs_kernel).  Two kernels rather
-// than one: carrying both pass bodies made the common narrow pass 7 % slower.
+// host repeats the search with the WIDE = true instantiation, which spills such levels to a global-memory queue, and
+// starts with that one from then on while the map keeps producing them) or 1 (maps above 16384 cells a side:
+// rank_bfs_kernel).  Two kernels rather than one: carrying both pass bodies made the common narrow pass 7 % slower.
 template <bool WIDE>
 __global__ void __launch_bounds__(OW_THREADS, 1)
 rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, uint32_t *rk,
@@ -833,16 +835,15 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
   // parts [from, n_parts - 1) are complete with `end` cells dequeued: every touch key below 4 * end is in memory (the
   // atomics of all threads precede the barrier before this call; the fence orders them before the flags)
   auto publish = [&](uint32_t from, uint32_t end) {
-    if (WIDE || threadIdx.x != 0) return;
+    if (threadIdx.x != 0) return;
     for (uint32_t k = from; k + 1 < n_parts; ++k) cnt->part_end[k] = end;
     __threadfence();
     for (uint32_t k = from; k + 1 < n_parts; ++k) atomicExch(&cnt->part_flag[k], 1u);
   };
   if (cnt->overflow) { publish(0, 0); return; }
-  if (WIDE && cnt->ow_fallback != 2u) return;
   const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
-  uint32_t base = 0, n = 1, levels = 0, scans = 0, part = 0;
+  uint32_t base = 0, n = 1, levels = 0, scans = 0, part = 0, widest = 1;
   if (threadIdx.x == 0) s_start = S.robot_cell;
   __syncthreads();
   if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
@@ -870,6 +871,7 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     base += n;
     n = n_next;
     ++levels;
+    widest = max(widest, n);
     if (n > S.ow_qcap && !WIDE) {  // uniform (a block-wide total): the next kernel reruns the search (claim[] holds touch
       if (threadIdx.x == 0) cnt->ow_fallback = S.ow_wide ? 2u : 1u;  // keys only, and it would write the same ones)
       publish(part, base);  // every level below `base` ranks is complete: those touches stand
@@ -880,7 +882,7 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     tq = Q.g0; Q.g0 = Q.g1; Q.g1 = tq;
     Q.from_global = n > S.ow_qcap;                     // this level did not fit the shared queue: read it from global memory
     Q.to_global = S.ow_wide && 3u * n + 4u > S.ow_qcap;  // a level has at most 3 children per cell: the next one may not fit
-    if (!WIDE && part + 1 < n_parts && levels >= (part + 1) * S.ow_part_levels) {
+    if (part + 1 < n_parts && levels >= (part + 1) * S.ow_part_levels) {
       if (threadIdx.x == 0) {
         cnt->part_end[part] = base;
         __threadfence();
@@ -894,6 +896,7 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     cnt->bfs_levels = levels;
     cnt->expanded = base;
     cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
+    cnt->widest_level = widest;
     for (int i = 0; i < 5; ++i) cnt->prof[i] = s_prof[i];
     cnt->prof[5] = clock64() - k0;
   }
@@ -1374,7 +1377,7 @@ chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uin
   if (cnt->overflow) return;
   const uint32_t c_lo = coll < 0 ? 0u : cnt->coll_c0[coll], c_hi = coll < 0 ? min(cnt->n_comp, S.comp_cap) : min(cnt->coll_c1[coll], S.comp_cap);
   const uint32_t f_lo = coll < 0 ? 0u : cnt->coll_fr[coll][0];
-  const uint32_t f_hi = coll < 0 ? cnt->n_frontiers : min(cnt->coll_fr[coll][1], f_lo + EARLY_SLICE_CAP);
+  const uint32_t f_hi = coll < 0 ? cnt->n_frontiers : min(cnt->coll_fr[coll][1], f_lo + S.early_cap);
   if (f_hi > S.front_cap) return;
   const uint32_t run = (uint32_t)S.max_size + 1u;
   const uint32_t W = S.map.W;
@@ -1546,6 +1549,8 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
   }
   S.rk_tiles_x = (c->W + 7u) / 8u;
+  // a batch is about 1/12 of the frontiers; the launches are sized for a quarter of the last search's count
+  S.early_cap = std::min<uint32_t>(std::max<uint32_t>(EARLY_SLICE_CAP, s->last.n_frontiers / 4u), 8192u);
   S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
   S.ow_wide = (c->W <= 16384u && c->H <= 16384u && !getenv("FITSLAM_OW_NOWIDE")) ? 1u : 0u;
   S.use_smem = (s->force_global || c->W > 32768u || c->H > 32768u) ? 0u : 1u;  // queue entries pack y << 16 | x; 32-bit radius prefilter
@@ -1563,10 +1568,11 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   S.cell_cap = s->cell_cap;
   S.front_cap = s->front_cap;
   Counters *cnt = s->counters.p;
-  // phase 0: the search.  phase 1 (only after the host has seen ow_fallback in the counters of phase 0: a level too wide
-  // for the shared-memory queue): the kernels that redo the wavefront with global-memory queues, then a collection of what
-  // they found.  They used to follow the shared-memory kernel unconditionally and return at once; but each is one CTA of
-  // 1024 threads that needs a whole free SM, and waited up to 0.5 ms for one while the scoring launches filled them all.
+  // phase 0: the search.  phase 1 (only after the host has seen ow_fallback == 1 in the counters of phase 0: a level too
+  // wide for the shared-memory queue on a map too large for the spill instantiation): the global-memory wavefront redoes
+  // the search, then a collection of what it found.  The fallback kernels used to follow the shared-memory kernel
+  // unconditionally and return at once; but each is one CTA of 1024 threads that needs a whole free SM, and waited up to
+  // 0.5 ms for one while the scoring launches filled them all.
   const uint64_t n_words = (uint64_t)S.wpr * c->H;
   const unsigned wide = 148 * 8;
   if (phase == 0) {
@@ -1643,7 +1649,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
           ++c->launches;
           ScoreSlice sl;
           sl.range = range;
-          sl.cap = EARLY_SLICE_CAP;
+          sl.cap = S.early_cap;
           sl.tags = s->ftag.p;
           sl.tag = tag;
           cudaError_t e = cudaEventRecord(s->ev_chunk[coll][cls], sts[cls]);
@@ -1666,7 +1672,10 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     ++c->launches;
     // the search on the context stream; behind each published part but the last, a collection on the second stream
     const uint32_t n_parts = s->ow_parts;
-    rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
+    if (s->prefer_wide && S.ow_wide)
+      rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
+    else
+      rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
     ++c->launches;
     FS_CUDA(c, cudaGetLastError());  // (the kernels below poll flags only this one sets)
     for (uint32_t part = 0; part + 1 < n_parts; ++part) {
@@ -1683,11 +1692,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   } else {
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[3], c->stream));
-    if (S.use_smem) {  // phase 1, ow_fallback == 2: the search again, wide levels spilled to a global-memory queue
-      rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, 1);
-      ++c->launches;
-    }
-    // the global-memory wavefront: the whole search when the shared-memory path is off, else only for ow_fallback == 1
+    // the global-memory wavefront: the whole search when the shared-memory path is off, else (phase 1) for ow_fallback == 1
     rank_bfs_kernel<<<1, BFS_THREADS, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->claim.p, s->queue.p, cnt);
     ++c->launches;
   }
@@ -1717,6 +1722,13 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   return FITSLAM_OK;
 }
 
+// widest level the shared-memory queue holds (FITSLAM_OW_QCAP lowers it in tests)
+static uint32_t hc_qcap(const FrontierState *) {
+  const char *e = getenv("FITSLAM_OW_QCAP");
+  const long v = e ? atol(e) : (long)OW_QCAP;
+  return (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
+}
+
 // FrontierSearch::searchFrom on the device; the frontier list stays resident in c->frontiers (c->n_frontiers entries).
 uint32_t frontier_capacity(fitslam_ctx *c) {
   if (!c->have_map) return 0;
@@ -1737,19 +1749,25 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
   if (!(mx < c->W && my < c->H)) return fail(c, FITSLAM_E_ROBOT_OUT_OF_BOUNDS, "Robot out of costmap bounds, cannot search for frontiers");
   fitslam_status st = ensure_pinned(c, sizeof(Counters));
   if (st != FITSLAM_OK) return st;
-  for (int attempt = 0; attempt < 8; ++attempt) {
+  bool grown = false;
+  for (int attempt = 0; attempt < 10; ++attempt) {
     st = ensure_frontier_buffers(c, s);
     if (st != FITSLAM_OK) return st;
     Counters *hc = reinterpret_cast<Counters *>(c->pinned);
-    // (a repeated attempt has grown the lists: the caller sized its buffers for the first one, so no early scoring then)
-    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, attempt == 0 ? hook : nullptr, 0);
+    // (once the lists have grown, the caller's buffers, sized for the first attempt, may be too small: no early scoring then)
+    st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, grown ? nullptr : hook, 0);
     if (st != FITSLAM_OK) return st;
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (hc->ow_fallback && !hc->overflow) {  // a level too wide for the shared-memory queue: redo the wavefront, collect the rest
+    if (hc->ow_fallback == 2u && !hc->overflow && !s->prefer_wide) {
+      s->prefer_wide = true;  // a level too wide for the shared-memory queue: again, with the instantiation that spills
+      continue;
+    }
+    if (hc->ow_fallback == 1u && !hc->overflow) {  // ... on a map too large for it: the global-memory wavefront, then the rest
       st = enqueue_search(c, s, my * c->W + mx, rx, ry, hc, nullptr, 1);
       if (st != FITSLAM_OK) return st;
       FS_CUDA(c, cudaStreamSynchronize(c->stream));
     }
+    if (s->prefer_wide && !hc->overflow && hc->widest_level <= hc_qcap(s)) s->prefer_wide = false;  // narrow levels again
     s->last = *hc;
     if (getenv("FITSLAM_PROF"))
       fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
@@ -1776,6 +1794,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
       return FITSLAM_OK;
     }
     // a list was too small: grow to what this run counted (plus slack) and search again
+    grown = true;
     if (hc->overflow & 1u) s->mask_cap = hc->n_mask + hc->n_mask / 8 + 1024;
     if (hc->overflow & 4u) s->comp_cap = hc->n_comp + hc->n_comp / 8 + 1024;
     if (hc->overflow & 8u) s->cell_cap = hc->n_cells + hc->n_cells / 8 + 1024;
@@ -1784,7 +1803,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
     if (hc->overflow & 2u) return fail(c, FITSLAM_E_INVALID, "search_frontiers: wavefront queue overflow");
     if (hc->overflow & 32u) return fail(c, FITSLAM_E_CUDA, "search_frontiers: the outer wavefront never published its progress");
   }
-  return fail(c, FITSLAM_E_INVALID, "search_frontiers: buffers still too small after 8 attempts");
+  return fail(c, FITSLAM_E_INVALID, "search_frontiers: buffers still too small after repeated attempts");
 }
 
 const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_t *n_comp, uint32_t *levels, uint32_t *ambiguous) {

@@ -35,7 +35,8 @@ def test_c4_full_size_properties(capi, oracle, synth):
         F = res1.n_frontiers
         n_rays, k, n_win, max_len = ctx.ray_shape()
         assert F > 5000 and n_win == 32 and res1.n_candidates == F * n_win == res1.n_fisher_poses
-        print(f"C4: {F} frontiers, {res1.n_components} components, {res1.bfs_levels} levels, stage_ms {[round(v, 3) for v in res1.stage_ms]}")
+        print(f"C4: {F} frontiers, {res1.n_components} components, {res1.bfs_levels} levels, stage_ms first cycle {[round(v, 3) for v in res1.stage_ms]}, "
+              f"second cycle {[round(v, 3) for v in res2.stage_ms]}")
         # idempotence: the second cycle is bit-identical
         assert res2.n_frontiers == F
         for key in out1:
