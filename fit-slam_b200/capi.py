@@ -74,6 +74,7 @@ PROTOTYPES = {
     "fitslam_set_map_points": (C.c_int, [_vp, _vp, C.c_uint64]),
     "fitslam_search_frontiers": (C.c_int, [_vp, C.c_double, C.c_double, _vp, _u32p, _vp, _u32p]),
     "fitslam_set_search_distance": (C.c_int, [_vp, C.c_double]),
+    "fitslam_roadmap_connectable": (C.c_int, [_vp, _vp, C.c_uint32, C.c_double, _vp, _vp]),
     "fitslam_arrival_limits": (C.c_int, [_vp, _dp, _dp, C.POINTER(C.c_int32)]),
     "fitslam_score_arrival": (C.c_int, [_vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp]),
     "fitslam_ray_shape": (C.c_int, [_vp, _u32p, _u32p, _u32p, _u32p]),
@@ -183,6 +184,15 @@ class Context:
         v = [C.c_uint32() for _ in range(4)]
         self._check(self.lib.fitslam_ray_shape(self.h, *[C.byref(x) for x in v]))
         return tuple(x.value for x in v)  # n_rays, k, n_windows, max_length
+
+    def roadmap_connectable(self, segments, radius, want_unknown=True):
+        """FrontierRoadMap::isConnectable for n node pairs (n x 4 doubles, world frame) on the resident costmap."""
+        seg = np.ascontiguousarray(segments, np.float64).reshape(-1, 4)
+        n = len(seg)
+        ok = np.zeros(n, np.uint8)
+        unk = np.zeros(n, np.int32) if want_unknown else None
+        self._check(self.lib.fitslam_roadmap_connectable(self.h, _ptr(seg), n, radius, _ptr(ok), _ptr(unk) if want_unknown else None))
+        return ok, unk
 
     def arrival_limits(self):
         a, b, m = C.c_double(), C.c_double(), C.c_int32()

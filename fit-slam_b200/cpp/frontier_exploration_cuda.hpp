@@ -331,6 +331,39 @@ private:
   float step_max = 0.3f;
 };
 
+// ---- FrontierRoadMap, the edge test only (RE/include/roadmap_explorer/planners/FrontierRoadmap.hpp:173-188) -------------
+// isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-694) decides the roadmap's edges: one traced ray per node pair.
+// The node store, A* and publishing stay with the caller; the batch form scores every candidate pair of a node in one launch.
+class FrontierRoadMap {
+public:
+  FrontierRoadMap(CudaContextPtr ctx, double radius_to_decide_edges) : ctx_(ctx), RADIUS_TO_DECIDE_EDGES(radius_to_decide_edges) {
+    max_connection_length_ = RADIUS_TO_DECIDE_EDGES * 1.5;  // FrontierRoadmap.cpp:32
+  }
+  bool isConnectable(const FrontierPtr &f1, const FrontierPtr &f2) {
+    const double seg[4] = {f1->getGoalPoint().x, f1->getGoalPoint().y, f2->getGoalPoint().x, f2->getGoalPoint().y};
+    uint8_t ok = 0;
+    ctx_->check(fitslam_roadmap_connectable(ctx_->get(), seg, 1, RADIUS_TO_DECIDE_EDGES, &ok, nullptr), "fitslam_roadmap_connectable");
+    return ok != 0;
+  }
+  // f against every node of `others` (populateNodes' inner loop, FrontierRoadmap.cpp:316-345): one launch
+  std::vector<uint8_t> areConnectable(const FrontierPtr &f, const std::vector<FrontierPtr> &others) {
+    std::vector<double> seg(4 * others.size());
+    for (size_t i = 0; i < others.size(); ++i) {
+      seg[4 * i] = f->getGoalPoint().x; seg[4 * i + 1] = f->getGoalPoint().y;
+      seg[4 * i + 2] = others[i]->getGoalPoint().x; seg[4 * i + 3] = others[i]->getGoalPoint().y;
+    }
+    std::vector<uint8_t> ok(others.size(), 0);
+    if (!others.empty())
+      ctx_->check(fitslam_roadmap_connectable(ctx_->get(), seg.data(), (uint32_t)others.size(), RADIUS_TO_DECIDE_EDGES, ok.data(), nullptr),
+                  "fitslam_roadmap_connectable");
+    return ok;
+  }
+private:
+  CudaContextPtr ctx_;
+  double max_connection_length_;
+  double RADIUS_TO_DECIDE_EDGES;
+};
+
 }  // namespace frontier_exploration
 
 namespace roadmap_explorer {  // the maintained package uses the same classes under this namespace (RE/include/roadmap_explorer/)
@@ -340,5 +373,6 @@ using frontier_exploration::FisherInformationManager;
 using frontier_exploration::Frontier;
 using frontier_exploration::FrontierCostCalculator;
 using frontier_exploration::FrontierPtr;
+using frontier_exploration::FrontierRoadMap;
 using frontier_exploration::FrontierSearch;
 }  // namespace roadmap_explorer

@@ -97,6 +97,10 @@ struct fitslam_ctx {
   fitslam::DevBuf<fitslam::ScoreRecord> records;
   uint64_t records_rows = 0;  // rows of `records` the last scoring call laid out (fitslam_score_records)
 
+  // ---- roadmap edge batches (fitslam_roadmap_connectable)
+  fitslam::DevBuf<double> edge_seg;
+  fitslam::DevBuf<int32_t> edge_out;
+
   // ---- scratch
   fitslam::DevBuf<uint8_t> scratch;
   void *pinned = nullptr;

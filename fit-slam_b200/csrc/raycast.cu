@@ -415,3 +415,87 @@ fitslam_status raycast_score_slice(fitslam_ctx *c, cudaStream_t stream, const fi
 }
 
 }  // namespace fitslam
+
+// ================================================================================================ roadmap edges
+namespace fitslam {
+
+// FrontierRoadMap::isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-694): one thread per node pair walks the
+// Bresenham line of getTracedCells (RE/src/Helpers.cpp:30-91, bresenham2D :7-28) over the costmap.  The cells of a
+// Bresenham line are distinct, so RayTracedCells' duplicate check (Helpers.hpp:41-46) never fires and the walk needs
+// no list: obstacle = any cost in 253..254 (hasHitObstacle), unknown = count of 255 (getNumUnknown).
+__global__ void connectable_kernel(const MapView M, const double *__restrict__ seg, uint32_t n, double max_length_d,
+                                   double unknown_limit, uint8_t *__restrict__ ok_out, int32_t *__restrict__ unk_out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double sx = seg[4 * i], sy = seg[4 * i + 1], wx = seg[4 * i + 2], wy = seg[4 * i + 3];
+  uint32_t x0, y0, x1, y1;
+  if (!world_to_map(M, wx, wy, x1, y1) || !world_to_map(M, sx, sy, x0, y0)) {  // "Not world to map": not connectable
+    ok_out[i] = 0;
+    if (unk_out) unk_out[i] = -1;
+    return;
+  }
+  const int dx = (int)(x1 - x0), dy = (int)(y1 - y0);
+  // std::hypot(int, int): the integer sum of squares is exact in double, and its IEEE square root is the correctly
+  // rounded hypotenuse
+  const double dist = sqrt((double)((long long)dx * dx + (long long)dy * dy));
+  const uint32_t abs_dx = (uint32_t)abs(dx), abs_dy = (uint32_t)abs(dy);
+  const long long step_x = dx > 0 ? 1 : -1, step_y = (dy > 0 ? 1 : -1) * (long long)M.pitch;  // sign(0) = -1 (Helpers.hpp:92-95)
+  const double scale = (dist == 0.0) ? 1.0 : fmin(1.0, max_length_d / dist);
+  const bool x_major = abs_dx >= abs_dy;
+  const uint32_t abs_da = x_major ? abs_dx : abs_dy, abs_db = x_major ? abs_dy : abs_dx;
+  const long long off_a = x_major ? step_x : step_y, off_b = x_major ? step_y : step_x;
+  const uint32_t end = min((uint32_t)(scale * abs_da), abs_da);
+  int error_b = (int)(abs_da / 2);
+  long long off = (long long)y0 * M.pitch + x0;
+  bool hit = false;
+  int unknown = 0;
+  for (uint32_t k = 0; k <= end; ++k) {  // `end` steps, then the final at(offset)
+    const uint32_t cost = M.data[off];
+    hit |= cost >= 253u && cost <= 254u;
+    unknown += cost == 255u ? 1 : 0;
+    off += off_a;
+    error_b += (int)abs_db;
+    if ((uint32_t)error_b >= abs_da) {
+      off += off_b;
+      error_b -= (int)abs_da;
+    }
+  }
+  ok_out[i] = (!hit && !((double)unknown > unknown_limit)) ? 1 : 0;
+  if (unk_out) unk_out[i] = unknown;
+}
+
+}  // namespace fitslam
+
+extern "C" fitslam_status fitslam_roadmap_connectable(fitslam_ctx *c, const double *segments, uint32_t n,
+                                                      double radius_to_decide_edges, uint8_t *connectable,
+                                                      int32_t *num_unknown) {
+  using namespace fitslam;
+  if (!c || (!segments && n) || (!connectable && n)) return fail(c, FITSLAM_E_INVALID, "roadmap_connectable: null argument");
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  if (!(radius_to_decide_edges >= 0.0)) return fail(c, FITSLAM_E_INVALID, "roadmap_connectable: bad radius");
+  if (n == 0) return FITSLAM_OK;
+  cudaSetDevice(c->device);
+  cudaPointerAttributes at;
+  const bool seg_dev = cudaPointerGetAttributes(&at, segments) == cudaSuccess && at.type == cudaMemoryTypeDevice;
+  cudaGetLastError();
+  const double *d_seg = segments;
+  if (!seg_dev) {
+    FS_CUDA(c, c->edge_seg.reserve(4 * (size_t)n));
+    FS_CUDA(c, cudaMemcpyAsync(c->edge_seg.p, segments, 4 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    d_seg = c->edge_seg.p;
+  }
+  // [n int32 unknown counts][n bytes flags]
+  FS_CUDA(c, c->edge_out.reserve((size_t)n + ((size_t)n + 3) / 4));
+  int32_t *d_unk = c->edge_out.p;
+  uint8_t *d_ok = reinterpret_cast<uint8_t *>(c->edge_out.p + n);
+  // max_connection_length_ = RADIUS_TO_DECIDE_EDGES * 1.5 (FrontierRoadmap.cpp:32); unsigned int max_length = that / resolution (:675)
+  const unsigned int max_length = (unsigned int)((radius_to_decide_edges * 1.5) / c->res);
+  const double unknown_limit = radius_to_decide_edges / c->res * 0.3;  // :685
+  connectable_kernel<<<(n + 127) / 128, 128, 0, c->stream>>>(map_view(c), d_seg, n, (double)max_length, unknown_limit, d_ok, d_unk);
+  ++c->launches;
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaMemcpyAsync(connectable, d_ok, n, cudaMemcpyDefault, c->stream));
+  if (num_unknown) FS_CUDA(c, cudaMemcpyAsync(num_unknown, d_unk, (size_t)n * sizeof(int32_t), cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}

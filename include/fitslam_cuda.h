@@ -186,6 +186,18 @@ FITSLAM_API fitslam_status fitslam_search_frontiers(fitslam_ctx *ctx, double rob
                                                     uint32_t *every_cells, uint32_t *n_cells);
 FITSLAM_API fitslam_status fitslam_set_search_distance(fitslam_ctx *ctx, double max_frontier_distance);
 
+/* ------------------------------------------------------------------ roadmap edges */
+/* FrontierRoadMap::isConnectable for a batch of node pairs (RE/src/planners/FrontierRoadmap.cpp:671-694): one ray
+ * from (x0, y0) to (x1, y1) per pair through getTracedCells (RE/src/Helpers.cpp:30-91; at most
+ * (unsigned)(1.5 * radius_to_decide_edges / resolution) steps), obstacle band 253..254, unknown = 255.
+ * connectable[i] = 1 iff both ends are on the map, no cell of the ray is in the obstacle band, and the ray crosses at
+ * most radius_to_decide_edges / resolution * 0.3 unknown cells.  segments: n x 4 doubles {x0, y0, x1, y1} (world
+ * frame, host or device); num_unknown (optional, n int32) exposes getNumUnknown() for stage-wise parity (-1 = an end
+ * is off the map). */
+FITSLAM_API fitslam_status fitslam_roadmap_connectable(fitslam_ctx *ctx, const double *segments, uint32_t n,
+                                                       double radius_to_decide_edges, uint8_t *connectable,
+                                                       int32_t *num_unknown);
+
 /* ------------------------------------------------------------------ arrival information */
 /* FrontierCostCalculator::setMaxArrivalInformation (DEP/src/CostCalculator.cpp:123-191). */
 FITSLAM_API fitslam_status fitslam_arrival_limits(fitslam_ctx *ctx, double *max_arrival_info_gt,

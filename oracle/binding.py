@@ -95,6 +95,17 @@ class Oracle:
                                    C.c_void_p(rays.ctypes.data), C.c_void_p(wins.ctypes.data))
         return out, rays, wins
 
+    def roadmap_connectable(self, a, meta, segments, radius):
+        """FrontierRoadMap::isConnectable for n node pairs (n x 4 doubles): (flags uint8, unknown counts int32)."""
+        a, m = self._map(a, meta)
+        seg = np.ascontiguousarray(segments, np.float64).reshape(-1, 4)
+        n = len(seg)
+        ok = np.zeros(n, np.uint8)
+        unk = np.zeros(n, np.int32)
+        self.lib.orc_roadmap_connectable(*m, C.c_void_p(seg.ctypes.data), C.c_uint32(n), C.c_double(radius),
+                                         C.c_void_p(ok.ctypes.data), C.c_void_p(unk.ctypes.data))
+        return ok, unk
+
     def plan_euclidean(self, rx, ry, ryaw, frontiers, achievable):
         fr = np.ascontiguousarray(frontiers)
         n = len(fr)

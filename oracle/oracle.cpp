@@ -434,6 +434,7 @@ class RayTracedCells {
   }
   std::vector<MapLocation> getCells() { return cells_; }
   bool hasHitObstacle() { return hit_obstacle; }
+  size_t getNumUnknown() { return unknown_cells_; }  // RE/include/roadmap_explorer/Helpers.hpp:77-80
 
  private:
   const Costmap2D *costmap_;
@@ -1119,6 +1120,35 @@ int orc_ray_shape(const fitslam_params *p, double res, uint32_t *n_rays, uint32_
   *n_windows = n - kk + 1;
   unsigned int ml = p->max_camera_depth / res;
   *max_length = ml;
+  return FITSLAM_OK;
+}
+
+// FrontierRoadMap::isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-694) for a batch of node pairs; getTracedCells
+// and bresenham2D are the same text in RE/src/Helpers.cpp:7-91 as in DEP (restated above).  max_connection_length_ =
+// RADIUS_TO_DECIDE_EDGES * 1.5 (FrontierRoadmap.cpp:32).
+int orc_roadmap_connectable(const uint8_t *map, uint32_t W, uint32_t H, double res, double ox, double oy,
+                            const double *segments, uint32_t n, double radius_to_decide_edges, uint8_t *connectable,
+                            int32_t *num_unknown) {
+  Costmap2D cm = makeMap(map, W, H, res, ox, oy);
+  const Costmap2D *costmap_ = &cm;
+  const double RADIUS_TO_DECIDE_EDGES = radius_to_decide_edges;
+  const double max_connection_length_ = RADIUS_TO_DECIDE_EDGES * 1.5;
+  for (uint32_t i = 0; i < n; ++i) {
+    const double f1x = segments[4 * i], f1y = segments[4 * i + 1], f2x = segments[4 * i + 2], f2y = segments[4 * i + 3];
+    std::vector<MapLocation> traced_cells;
+    RayTracedCells cell_gatherer(costmap_, traced_cells, 253, 254, 0, 255);
+    unsigned int max_length = max_connection_length_ / costmap_->getResolution();
+    bool ok = true;
+    if (!getTracedCells(f1x, f1y, f2x, f2y, cell_gatherer, max_length, costmap_)) {
+      connectable[i] = 0;
+      if (num_unknown) num_unknown[i] = -1;
+      continue;
+    }
+    if (cell_gatherer.hasHitObstacle()) ok = false;
+    if (cell_gatherer.getNumUnknown() > RADIUS_TO_DECIDE_EDGES / costmap_->getResolution() * 0.3) ok = false;
+    connectable[i] = ok ? 1 : 0;
+    if (num_unknown) num_unknown[i] = (int32_t)cell_gatherer.getNumUnknown();
+  }
   return FITSLAM_OK;
 }
 

@@ -83,6 +83,15 @@ int main(int argc, char **argv) {
     std::printf("F %a %a %d %zu %a %a %d %a %d\n", f->getGoalPoint().x, f->getGoalPoint().y, f->getSize(), f->getUID(),
                 f->getArrivalInformation(), f->getGoalOrientation().z, f->isAchievable() ? 1 : 0, (double)information, safe ? 1 : 0);
   }
+  // roadmap edges: the first frontier against all the others (one launch), and one pair through the single-pair form
+  if (frontiers.size() > 1) {
+    roadmap_explorer::FrontierRoadMap roadmap(ctx, 2.6);
+    std::vector<FrontierPtr> others(frontiers.begin() + 1, frontiers.end());
+    const std::vector<uint8_t> ok = roadmap.areConnectable(frontiers[0], others);
+    std::printf("edges");
+    for (uint8_t v : ok) std::printf(" %d", (int)v);
+    std::printf("\nedge1 %d\n", roadmap.isConnectable(frontiers[0], frontiers[1]) ? 1 : 0);
+  }
   double sx = 0, sy = 0;
   for (auto &c : every) { sx += c[0]; sy += c[1]; }
   std::printf("cellsum %a %a\n", sx, sy);

@@ -80,3 +80,9 @@ def test_shim_matches_oracle(harness, capi, oracle, synth, tmp_path):
     cs = [ln.split() for ln in lines if ln.startswith("cellsum")][0]
     assert float.fromhex(cs[1]) == sx and float.fromhex(cs[2]) == sy
     assert lines[-1].split() == ["offmap", "0"]
+    # roadmap edges of the first frontier (FrontierRoadMap::isConnectable, radius 2.6 m)
+    seg = np.stack([np.full(len(fr) - 1, fr["goal_x"][0]), np.full(len(fr) - 1, fr["goal_y"][0]), fr["goal_x"][1:], fr["goal_y"][1:]], axis=1)
+    wok, _ = oracle.roadmap_connectable(a, meta, seg, 2.6)
+    edges = [ln.split() for ln in lines if ln.startswith("edges")][0]
+    assert [int(v) for v in edges[1:]] == list(wok)
+    assert [ln.split() for ln in lines if ln.startswith("edge1")][0][1] == str(int(wok[0]))
