@@ -12,6 +12,12 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfitslam_cuda.so")
 
 
+class OccupancyParams(C.Structure):
+    """fitslam_occupancy_params (include/fitslam_cuda.h)."""
+    _fields_ = [("lethal_obstacle_threshold", C.c_int32), ("lethal_cost_threshold", C.c_int32), ("unknown_cost_value", C.c_int32),
+                ("trinary_costmap", C.c_int32), ("track_unknown_space", C.c_int32)]
+
+
 class Params(C.Structure):
     _fields_ = [
         ("min_frontier_cluster_size", C.c_int32), ("max_frontier_cluster_size", C.c_int32),
@@ -71,6 +77,9 @@ PROTOTYPES = {
     "fitslam_stream": (_vp, [_vp]),
     "fitslam_launch_count": (C.c_uint64, [_vp]),
     "fitslam_set_costmap": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, _vp]),
+    "fitslam_get_costmap": (C.c_int, [_vp, _vp, C.c_uint64]),
+    "fitslam_set_occupancy_grid": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
+    "fitslam_default_occupancy_params": (None, [_vp]),
     "fitslam_set_map_points": (C.c_int, [_vp, _vp, C.c_uint64]),
     "fitslam_search_frontiers": (C.c_int, [_vp, C.c_double, C.c_double, _vp, _u32p, _vp, _u32p]),
     "fitslam_set_search_distance": (C.c_int, [_vp, C.c_double]),
@@ -103,6 +112,12 @@ def load_library(path=LIB_PATH):
         fn.restype = res
         fn.argtypes = args
     return lib
+
+
+def default_occupancy_params():
+    p = OccupancyParams()
+    load_library().fitslam_default_occupancy_params(C.byref(p))
+    return p
 
 
 def default_params(lib=None):
@@ -173,6 +188,25 @@ class Context:
         d = None if dirty is None else np.asarray(dirty, dtype=np.uint32)
         self._check(self.lib.fitslam_set_costmap(self.h, _ptr(data), W, H, res, ox, oy, _ptr(d)))
         self.W, self.H = W, H
+
+    def set_occupancy_grid(self, data, res, ox, oy, params=None, dirty=None, shape=None):
+        """data: int8 numpy array [H, W] (nav_msgs/OccupancyGrid cells, host) or a raw device address with shape=(H, W)."""
+        if isinstance(data, np.ndarray):
+            assert data.dtype == np.int8 and data.ndim == 2
+            data = np.ascontiguousarray(data)
+            H, W = data.shape
+        else:
+            H, W = shape
+        d = None if dirty is None else np.asarray(dirty, dtype=np.uint32)
+        self._check(self.lib.fitslam_set_occupancy_grid(self.h, _ptr(data), W, H, res, ox, oy,
+                                                        C.byref(params) if params is not None else None, _ptr(d)))
+        self.W, self.H = W, H
+
+    def costmap_copy(self):
+        """The resident costmap as a [H, W] uint8 array (Costmap2D::getCharMap)."""
+        out = np.zeros((self.H, self.W), np.uint8)
+        self._check(self.lib.fitslam_get_costmap(self.h, _ptr(out), out.size))
+        return out
 
     def set_map_points(self, xyz, n=None):
         if isinstance(xyz, np.ndarray):

@@ -178,7 +178,7 @@ void fitslam_destroy(fitslam_ctx *c) {
   c->records.release();
   c->scratch.release();
   if (c->pinned) cudaFreeHost(c->pinned);
-  c->edge_seg.release(); c->edge_out.release();
+  c->edge_seg.release(); c->edge_out.release(); c->occ_stage.release();
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -204,6 +204,163 @@ static bool is_device_ptr(const void *p) {
     return false;
   }
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// ---- costmap ingest
+}  // extern "C"
+
+namespace fitslam {
+
+// threshold_occupancy.cpp:33-45, then StaticLayer::interpretValue (see include/fitslam_cuda.h)
+__host__ __device__ __forceinline__ uint8_t occupancy_to_cost(int8_t raw, const fitslam_occupancy_params P) {
+  int8_t v = raw;
+  if (P.lethal_obstacle_threshold >= 0) v = raw >= P.lethal_obstacle_threshold ? (int8_t)100 : (raw == -1 ? (int8_t)-1 : (int8_t)0);
+  const unsigned char value = (unsigned char)v;  // the static layer reads the grid as unsigned char
+  const unsigned char unknown = (unsigned char)P.unknown_cost_value;
+  if (value == unknown) return P.track_unknown_space ? 255 : 0;
+  if (value >= (unsigned char)P.lethal_cost_threshold) return 254;
+  if (P.trinary_costmap) return 0;
+  const double scale = (double)value / (unsigned char)P.lethal_cost_threshold;
+  return (uint8_t)(scale * 254);
+}
+
+struct OccSimd {  // the trinary cases as per-byte selects (mode 0: none, use occupancy_to_cost per cell)
+  int mode;       // 1: threshold node present (signed >= on the raw cell), 2: static layer only (unsigned >= lethal)
+  uint32_t unknown4, thr4, if_unknown4, if_lethal4, if_free4;
+};
+
+// full map, rows of the device costmap are `pitch` bytes (a multiple of 16): one thread per 16 cells of a row
+__global__ void __launch_bounds__(256) occupancy_rows_kernel(const int8_t *__restrict__ in, uint32_t W, uint32_t H, uint32_t in_pitch,
+                                                              uint8_t *__restrict__ out, uint32_t out_pitch, uint32_t x_off, uint32_t y_off,
+                                                              const fitslam_occupancy_params P, int vec, const OccSimd simd) {
+  const uint32_t chunks = (W + 15u) / 16u;
+  // grid.x covers the chunks of a row, grid.y strides over the rows: no division per chunk
+  for (uint32_t y = blockIdx.y; y < H; y += gridDim.y)
+  for (uint32_t cx = blockIdx.x * blockDim.x + threadIdx.x; cx < chunks; cx += gridDim.x * blockDim.x) {
+    const uint32_t x = cx * 16u;
+    const int8_t *src = in + (size_t)y * in_pitch + x;
+    uint8_t *dst = out + (size_t)(y + y_off) * out_pitch + x + x_off;
+    if (vec && x + 16u <= W) {  // both rows 16-byte aligned: one 16-byte load, one 16-byte store
+      const uint4 q = __ldcs(reinterpret_cast<const uint4 *>(src));  // read once: streaming
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t r = 0;
+        if (simd.mode) {
+          // trinary translation, four cells per instruction: the function takes three values, selected by two per-byte
+          // compares (with the threshold node: == -1, >= threshold signed; without: == unknown, >= lethal unsigned)
+          const uint32_t u = __vcmpeq4(w[k], simd.unknown4);
+          const uint32_t t = (simd.mode == 1 ? __vcmpges4(w[k], simd.thr4) : __vcmpgeu4(w[k], simd.thr4)) & ~u;
+          r = (u & simd.if_unknown4) | (t & simd.if_lethal4) | (~(u | t) & simd.if_free4);
+        } else {
+#pragma unroll
+          for (int b = 0; b < 4; ++b) r |= (uint32_t)occupancy_to_cost((int8_t)((w[k] >> (8 * b)) & 0xFFu), P) << (8 * b);
+        }
+        o[k] = r;
+      }
+      *reinterpret_cast<uint4 *>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+    } else {
+      for (uint32_t k = 0; k < 16u && x + k < W; ++k) dst[k] = occupancy_to_cost(src[k], P);
+    }
+  }
+}
+
+}  // namespace fitslam
+
+extern "C" {
+
+void fitslam_default_occupancy_params(fitslam_occupancy_params *p) {
+  if (!p) return;
+  p->lethal_obstacle_threshold = 85;  // threshold_occupancy.cpp:17
+  p->lethal_cost_threshold = 100;     // nav2 StaticLayer defaults; the reference's yaml leaves them alone
+  p->unknown_cost_value = -1;
+  p->trinary_costmap = 1;
+  p->track_unknown_space = 1;         // DEP/params/exploration_params.yaml:25
+}
+
+fitslam_status fitslam_set_occupancy_grid(fitslam_ctx *c, const int8_t *data, uint32_t size_x, uint32_t size_y, double resolution,
+                                          double origin_x, double origin_y, const fitslam_occupancy_params *p, const uint32_t *dirty) {
+  if (!c || !data || size_x == 0 || size_y == 0 || !(resolution > 0.0))
+    return fail(c, FITSLAM_E_INVALID, "set_occupancy_grid: bad argument");
+  if ((uint64_t)size_x * size_y >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "set_occupancy_grid: more than 2^31 cells");
+  fitslam_occupancy_params P;
+  if (p) P = *p; else fitslam_default_occupancy_params(&P);
+  if (P.lethal_cost_threshold < 0 || P.lethal_cost_threshold > 100) return fail(c, FITSLAM_E_INVALID, "set_occupancy_grid: lethal_cost_threshold outside 0..100");
+  cudaSetDevice(c->device);
+  const bool same_geom = c->have_map && c->W == size_x && c->H == size_y && c->res == resolution &&
+                         c->ox == origin_x && c->oy == origin_y;
+  const bool dev = is_device_ptr(data);
+  uint32_t x0 = 0, y0 = 0, w = size_x, h = size_y;
+  if (dirty) {
+    if (!same_geom) return fail(c, FITSLAM_E_INVALID, "set_occupancy_grid: dirty rectangle needs a resident map of the same geometry");
+    x0 = dirty[0]; y0 = dirty[1]; w = dirty[2]; h = dirty[3];
+    if (w == 0 || h == 0) return FITSLAM_OK;
+    if ((uint64_t)x0 + w > size_x || (uint64_t)y0 + h > size_y) return fail(c, FITSLAM_E_INVALID, "set_occupancy_grid: dirty rectangle outside the map");
+  } else {
+    const uint32_t pitch = (size_x + 15u) & ~15u;  // TMA needs 16-byte row strides
+    FS_CUDA(c, c->map.reserve((size_t)pitch * size_y + 256));
+    if (pitch != size_x) FS_CUDA(c, cudaMemsetAsync(c->map.p, 0, (size_t)pitch * size_y, c->stream));
+    c->pitch = pitch;
+  }
+  // the int8 cells of the rectangle: read in place from a device grid, staged (rows of 16-byte-aligned pitch) from the host
+  const int8_t *src = data + (size_t)y0 * size_x + x0;
+  uint32_t src_pitch = size_x;
+  if (!dev) {
+    const uint32_t sp = (w + 15u) & ~15u;
+    FS_CUDA(c, c->occ_stage.reserve((size_t)sp * h + 16));
+    FS_CUDA(c, cudaMemcpy2DAsync(c->occ_stage.p, sp, src, size_x, w, h, cudaMemcpyHostToDevice, c->stream));
+    src = c->occ_stage.p;
+    src_pitch = sp;
+  }
+  const int vec = ((uintptr_t)src % 16 == 0) && (src_pitch % 16 == 0) && (x0 % 16 == 0) ? 1 : 0;
+  const uint32_t row_chunks = (w + 15u) / 16u;
+  const dim3 grid(std::min<uint32_t>((row_chunks + 255u) / 256u, 64u), std::min<uint32_t>(h, 148u * 32u));
+  OccSimd simd{};
+  auto rep4 = [](uint8_t b) { return (uint32_t)b * 0x01010101u; };
+  if (P.trinary_costmap && P.lethal_obstacle_threshold >= 0 && P.lethal_obstacle_threshold <= 127) {
+    // after the threshold node a cell is -1, 100 or 0: three values of the static layer's function
+    simd.mode = 1;
+    simd.unknown4 = rep4(0xFF);
+    simd.thr4 = rep4((uint8_t)P.lethal_obstacle_threshold);
+    simd.if_unknown4 = rep4(occupancy_to_cost((int8_t)-1, P));
+    simd.if_lethal4 = rep4(occupancy_to_cost((int8_t)P.lethal_obstacle_threshold, P));
+    simd.if_free4 = rep4(occupancy_to_cost((int8_t)(P.lethal_obstacle_threshold > 0 ? 0 : -2), P));
+    if (P.lethal_obstacle_threshold == 0) simd.mode = 0;  // (every non-negative cell is lethal and 0 is not free: keep the scalar form)
+  } else if (P.trinary_costmap && P.lethal_obstacle_threshold < 0 && (uint8_t)P.unknown_cost_value >= (uint8_t)P.lethal_cost_threshold) {
+    simd.mode = 2;  // unknown is tested first and lies above the lethal threshold, as with the defaults (255 vs 100)
+    simd.unknown4 = rep4((uint8_t)P.unknown_cost_value);
+    simd.thr4 = rep4((uint8_t)P.lethal_cost_threshold);
+    simd.if_unknown4 = rep4(P.track_unknown_space ? 255 : 0);
+    simd.if_lethal4 = rep4(254);
+    simd.if_free4 = 0;
+  }
+  occupancy_rows_kernel<<<grid, 256, 0, c->stream>>>(src, w, h, src_pitch, c->map.p, c->pitch, x0, y0, P, vec, simd);
+  ++c->launches;
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));  // the caller may reuse `data` on return
+  if (dirty) return FITSLAM_OK;
+  c->W = size_x;
+  c->H = size_y;
+  c->res = resolution;
+  c->ox = origin_x;
+  c->oy = origin_y;
+  c->have_map = true;
+  if (!same_geom) {
+    c->shape_res = -1.0;
+    c->limits_set = false;
+  }
+  return update_ray_shape(c);
+}
+
+fitslam_status fitslam_get_costmap(fitslam_ctx *c, uint8_t *out, uint64_t capacity) {
+  if (!c || !out) return fail(c, FITSLAM_E_INVALID, "get_costmap: null argument");
+  if (!c->have_map) return fail(c, FITSLAM_E_NO_COSTMAP, "no costmap set");
+  if (capacity < (uint64_t)c->W * c->H) return fail(c, FITSLAM_E_CAPACITY, "get_costmap: buffer too small");
+  cudaSetDevice(c->device);
+  FS_CUDA(c, cudaMemcpy2DAsync(out, c->W, c->map.p, c->pitch, c->W, c->H, cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
 }
 
 fitslam_status fitslam_set_costmap(fitslam_ctx *c, const uint8_t *data, uint32_t size_x, uint32_t size_y,

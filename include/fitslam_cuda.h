@@ -186,6 +186,34 @@ FITSLAM_API fitslam_status fitslam_search_frontiers(fitslam_ctx *ctx, double rob
                                                     uint32_t *every_cells, uint32_t *n_cells);
 FITSLAM_API fitslam_status fitslam_set_search_distance(fitslam_ctx *ctx, double max_frontier_distance);
 
+/* ------------------------------------------------------------------ costmap ingest */
+/* nav_msgs/OccupancyGrid (int8: -1 unknown, 0..100) -> the uint8 costmap the search reads, on the device:
+ * (1) TraversabilityThresholdNode::callback (ORB-SLAM3-ROS2-Docker/traversability_mapping/traversability_ros_interface/
+ *     traversability_mapping_ros/src/threshold_occupancy.cpp:25-49): value >= lethal_obstacle_threshold -> 100,
+ *     -1 -> -1, else 0 (skipped when lethal_obstacle_threshold < 0);
+ * (2) nav2_costmap_2d::StaticLayer::interpretValue (ROS 2 Humble binary package, not under the reference tree; the
+ *     reference configures it with track_unknown_space: true and the defaults lethal_cost_threshold 100,
+ *     unknown_cost_value -1, trinary_costmap true: DEP/params/exploration_params.yaml:25-38): unknown -> 255 (or 0
+ *     without track_unknown_space), >= lethal_cost_threshold -> 254, trinary -> 0, else
+ *     (unsigned char)((double)value / lethal_cost_threshold * 254).
+ * Same geometry / dirty-rectangle rules as fitslam_set_costmap.  `data`: host or device, size_x * size_y int8. */
+typedef struct fitslam_occupancy_params {
+  int32_t lethal_obstacle_threshold; /* threshold node: 85 (threshold_occupancy.cpp:17); < 0 = no threshold node */
+  int32_t lethal_cost_threshold;     /* static layer: 100 */
+  int32_t unknown_cost_value;        /* static layer: -1 */
+  int32_t trinary_costmap;           /* static layer: 1 */
+  int32_t track_unknown_space;       /* costmap: 1 (exploration_params.yaml:25) */
+} fitslam_occupancy_params;
+FITSLAM_API void fitslam_default_occupancy_params(fitslam_occupancy_params *p);
+FITSLAM_API fitslam_status fitslam_set_occupancy_grid(fitslam_ctx *ctx, const int8_t *data, uint32_t size_x,
+                                                      uint32_t size_y, double resolution, double origin_x,
+                                                      double origin_y, const fitslam_occupancy_params *p,
+                                                      const uint32_t *dirty_xywh);
+
+/* Copy-out of the resident costmap (Costmap2D::getCharMap: size_x * size_y bytes, row-major, no padding); `out`: host or
+ * device, `capacity` bytes. */
+FITSLAM_API fitslam_status fitslam_get_costmap(fitslam_ctx *ctx, uint8_t *out, uint64_t capacity);
+
 /* ------------------------------------------------------------------ roadmap edges */
 /* FrontierRoadMap::isConnectable for a batch of node pairs (RE/src/planners/FrontierRoadmap.cpp:671-694): one ray
  * from (x0, y0) to (x1, y1) per pair through getTracedCells (RE/src/Helpers.cpp:30-91; at most

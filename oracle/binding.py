@@ -95,6 +95,13 @@ class Oracle:
                                    C.c_void_p(rays.ctypes.data), C.c_void_p(wins.ctypes.data))
         return out, rays, wins
 
+    def occupancy_to_cost(self, grid, occ_params):
+        """threshold node + StaticLayer::interpretValue on an int8 occupancy grid -> uint8 costs."""
+        g = np.ascontiguousarray(grid, np.int8)
+        out = np.zeros(g.shape, np.uint8)
+        self.lib.orc_occupancy_to_cost(C.c_void_p(g.ctypes.data), C.c_uint64(g.size), C.byref(occ_params), C.c_void_p(out.ctypes.data))
+        return out
+
     def roadmap_connectable(self, a, meta, segments, radius):
         """FrontierRoadMap::isConnectable for n node pairs (n x 4 doubles): (flags uint8, unknown counts int32)."""
         a, m = self._map(a, meta)

@@ -1123,6 +1123,44 @@ int orc_ray_shape(const fitslam_params *p, double res, uint32_t *n_rays, uint32_
   return FITSLAM_OK;
 }
 
+// Costmap ingest.  (1) TraversabilityThresholdNode::callback, ORB-SLAM3-ROS2-Docker/traversability_mapping/
+// traversability_ros_interface/traversability_mapping_ros/src/threshold_occupancy.cpp:25-49.  (2) StaticLayer::interpretValue
+// of nav2_costmap_2d (ROS 2 Humble binary package, absent from the reference tree; restated from the published source:
+// static_layer.cpp, `unsigned char StaticLayer::interpretValue(unsigned char value)`), applied to every cell of the grid as
+// StaticLayer::processMap does.
+static unsigned char interpretValue(unsigned char value, const fitslam_occupancy_params &P) {
+  const bool track_unknown_space_ = P.track_unknown_space != 0, trinary_costmap_ = P.trinary_costmap != 0;
+  const unsigned char unknown_cost_value_ = (unsigned char)P.unknown_cost_value, lethal_threshold_ = (unsigned char)P.lethal_cost_threshold;
+  if (track_unknown_space_ && value == unknown_cost_value_) {
+    return 255;  // NO_INFORMATION
+  } else if (!track_unknown_space_ && value == unknown_cost_value_) {
+    return 0;  // FREE_SPACE
+  } else if (value >= lethal_threshold_) {
+    return 254;  // LETHAL_OBSTACLE
+  } else if (trinary_costmap_) {
+    return 0;
+  }
+  double scale = static_cast<double>(value) / lethal_threshold_;
+  return scale * 254;
+}
+int orc_occupancy_to_cost(const int8_t *data, uint64_t n, const fitslam_occupancy_params *p, uint8_t *out) {
+  std::vector<int8_t> thresholded;
+  const int8_t *grid = data;
+  if (p->lethal_obstacle_threshold >= 0) {
+    const int lethal_threshold_ = p->lethal_obstacle_threshold;
+    thresholded.reserve(n);
+    for (uint64_t i = 0; i < n; ++i) {
+      const int8_t value = data[i];
+      if (value >= lethal_threshold_) thresholded.push_back(100);
+      else if (value == -1) thresholded.push_back(-1);
+      else thresholded.push_back(0);
+    }
+    grid = thresholded.data();
+  }
+  for (uint64_t i = 0; i < n; ++i) out[i] = interpretValue((unsigned char)grid[i], *p);
+  return FITSLAM_OK;
+}
+
 // FrontierRoadMap::isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-694) for a batch of node pairs; getTracedCells
 // and bresenham2D are the same text in RE/src/Helpers.cpp:7-91 as in DEP (restated above).  max_connection_length_ =
 // RADIUS_TO_DECIDE_EDGES * 1.5 (FrontierRoadmap.cpp:32).
