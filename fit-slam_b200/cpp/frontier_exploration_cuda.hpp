@@ -90,6 +90,12 @@ public:
     check(fitslam_set_costmap(ctx_, cm.getCharMap(), cm.getSizeInCellsX(), cm.getSizeInCellsY(), cm.getResolution(),
                               cm.getOriginX(), cm.getOriginY(), nullptr), "fitslam_set_costmap");
   }
+  // the same from a nav_msgs/OccupancyGrid (data: int8 cells, row-major): threshold node + static layer on the device
+  // (threshold_occupancy.cpp:25-49, nav2 StaticLayer::interpretValue); xywh = a dirty rectangle of a resident map, or null
+  void updateOccupancyGrid(const int8_t *data, uint32_t size_x, uint32_t size_y, double resolution, double origin_x, double origin_y,
+                           const fitslam_occupancy_params *params = nullptr, const uint32_t *xywh = nullptr) {
+    check(fitslam_set_occupancy_grid(ctx_, data, size_x, size_y, resolution, origin_x, origin_y, params, xywh), "fitslam_set_occupancy_grid");
+  }
   void check(fitslam_status st, const char *what) const {
     if (st != FITSLAM_OK) throw std::runtime_error(std::string(what) + ": " + fitslam_status_string(st) + " (" + fitslam_last_error(ctx_) + ")");
   }
