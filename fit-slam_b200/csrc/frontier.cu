@@ -59,6 +59,13 @@ static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells 
 static constexpr uint32_t IW_BITS_SMALL = 1024, IW_BITS_LARGE = 8192;  // words of the component's mask window held in shared memory
 static constexpr uint32_t iw_smem(uint32_t cells, uint32_t bit_words) { return (2 * 2 * cells + cells + bit_words) * 4; }
 static constexpr uint32_t HKEY_EMPTY = 0xFFFFFFFFu;
+// per-phase cycle counts of the outer wavefront (FITSLAM_PROF prints them): compiled in only with -DFITSLAM_OW_PROF, the
+// four clock reads per pass are not free in a kernel whose passes are a few thousand cycles long
+#ifdef FITSLAM_OW_PROF
+#define OW_CLOCK() clock64()
+#else
+#define OW_CLOCK() 0ll
+#endif
 
 struct Counters {
   uint32_t n_mask;         // cells in the frontier mask
@@ -72,8 +79,8 @@ struct Counters {
   uint32_t expanded;       // reachable cells dequeued by the outer wavefront
   uint32_t visited;        // queue entries + far cells (cleanup bound)
   uint32_t dirty_queue;    // entries of queue[] whose claim words (and their 4 neighbours') the cleanup must reset
-  uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: rank_bfs_kernel resumes there
-  uint32_t resume_base, resume_n, resume_levels;
+  uint32_t ow_fallback;    // the shared-memory outer wavefront met a level it cannot hold: 2 = repeat with the spill instantiation, 1 = with rank_bfs_kernel
+  uint32_t pad0[3];
   uint32_t widest_level;   // cells in the widest level of the shared-memory outer wavefront
   uint32_t part_flag[OW_PARTS];        // part k of the outer wavefront is complete (published by the kernel, polled by wait_part_kernel)
   uint32_t part_end[OW_PARTS];         // cells dequeued when part k ended: touch keys below 4 * part_end[k] are final after it
@@ -489,12 +496,11 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   __shared__ uint32_t s_start;
   if (cnt->overflow) return;
   if (S.use_smem && cnt->ow_fallback != 1u) return;  // a shared-memory wavefront finished the search
-  const bool resume = false;  // (kept for a queue hand-over; the shared-memory wavefront restarts the search instead)
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
   if (threadIdx.x == 0) s_start = S.robot_cell;  // falls back to pos when no cell qualifies (FrontierSearch.cpp:47-54)
   __syncthreads();
-  if (!resume && S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+  if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
     nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh, cnt, &s_start);
     __syncthreads();
   }
@@ -503,12 +509,7 @@ rank_bfs_kernel(const SearchParams S, const uint32_t *__restrict__ bits, const u
   constexpr uint32_t SQ = 2048;
   __shared__ uint32_t sq[2][SQ];
   uint32_t base = 0, n = 1, levels = 0, cur = 0;
-  if (resume) {  // take over from rank_bfs_smem_kernel: queue[] and claim[] are complete up to the level that did not fit
-    base = cnt->resume_base;
-    n = cnt->resume_n;
-    levels = cnt->resume_levels;
-    for (uint32_t i = threadIdx.x; i < min(n, SQ); i += BFS_THREADS) sq[0][i] = ld_cg(queue + base + i);
-  } else {
+  {
     const uint32_t start = s_start;
     if (threadIdx.x == 0) {
       cnt->start_cell = start;
@@ -641,8 +642,8 @@ __host__ __device__ __forceinline__ uint32_t rk_index(uint32_t x, uint32_t y, ui
 //   * two threads share a queue position (one per axis), so the dependent instruction chain of a level, which is what
 //     bounds it (clock64 breakdown in profiles/README.md), is half as long, thread order is still bid order, and the
 //     winner counts are 0..2 per thread: the block scan is two ballots per warp.
-// Two barriers per pass.  A level wider than ow_qcap sets ow_fallback and rank_bfs_kernel resumes the search from the
-// global queue at that level.
+// Two barriers per pass.  A level wider than ow_qcap sets ow_fallback, and the host repeats the search with the
+// instantiation that spills such levels to a global-memory queue (or, on maps too large for it, with rank_bfs_kernel).
 struct OwQueues {
   // g0 / g1: the same queues in global memory, entries (mask << 28 | y << 14 | x), used while a level is wider than the
   // shared-memory queue (maps up to 16384 cells a side): read when n > ow_qcap, written when the next level could be
@@ -684,7 +685,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
                                            uint32_t rx, uint32_t ry, uint32_t *ws, unsigned long long *prof) {
   const uint32_t W = S.map.W, H = S.map.H;
   const uint32_t next_base = base + n;
-  const long long c0 = clock64();
+  const long long c0 = OW_CLOCK();
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
   const uint32_t pos = tile + (threadIdx.x >> 1), h = threadIdx.x & 1u;
   int ax = 0, ay = 0, bx = 0, by = 0;
@@ -731,7 +732,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
       if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) b_tr = false;
     }
   }
-  c1 = clock64();
+  c1 = OW_CLOCK();
   // ranks of each candidate's three other neighbours (front, and the two sides), all loads independent.
   // directions: 0 = -x, 1 = +x, 2 = -y, 3 = +y; seen from the candidate, this cell lies in direction (slot ^ 1)
   const int fx = h ? 0 : 1, fy = h ? 1 : 0;  // unit step of this thread's axis
@@ -780,7 +781,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   if (a_in && !((wa.x >> (ax & 31)) & 1u) && a_mk) atomicMin(claim + (size_t)ay * W + ax, TOUCH_BIT | (rank * 4u + 2u * h));
   if (b_in && !((wb.x >> (bx & 31)) & 1u) && b_mk) atomicMin(claim + (size_t)by * W + bx, TOUCH_BIT | (rank * 4u + 2u * h + 1u));
   }
-  const long long c2 = clock64();
+  const long long c2 = OW_CLOCK();
   // block-wide exclusive scan of the winner counts (0..2 per thread): two ballots per warp, one barrier
   const uint32_t n_win = (a_win ? 1u : 0u) + (b_win ? 1u : 0u);
   const uint32_t b0 = __ballot_sync(0xffffffffu, n_win & 1u), b1 = __ballot_sync(0xffffffffu, n_win >> 1);
@@ -794,7 +795,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   const uint32_t total = __reduce_add_sync(0xffffffffu, wv);
   const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
   uint32_t dst = n_next + wbase + excl;
-  const long long c3 = clock64();
+  const long long c3 = OW_CLOCK();
   // append the winners in (position, slot) order
   if (a_win) {
     ow_append<WIDE>(S, tm, rk, Q, (uint32_t)ax, (uint32_t)ay, a_dm, dst, next_base);
@@ -802,7 +803,7 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *
   }
   if (b_win) ow_append<WIDE>(S, tm, rk, Q, (uint32_t)bx, (uint32_t)by, b_dm, dst, next_base);
   if (threadIdx.x == 0) {
-    const long long c4 = clock64();
+    const long long c4 = OW_CLOCK();
     prof[0] += c1 - c0; prof[1] += c2 - c1; prof[2] += c3 - c2; prof[3] += c4 - c3; prof[4] += 1;
   }
   return total;
@@ -1770,7 +1771,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
     if (s->prefer_wide && !hc->overflow && hc->widest_level <= hc_qcap(s)) s->prefer_wide = false;  // narrow levels again
     s->last = *hc;
     if (getenv("FITSLAM_PROF"))
-      fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
+      fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles (0 unless built with -DFITSLAM_OW_PROF) stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
               hc->expanded, hc->prof[4], hc->prof[0], hc->prof[1], hc->prof[2], hc->prof[3], hc->prof[5]);
     if (getenv("FITSLAM_PROF")) {
       float t[6] = {0, 0, 0, 0, 0, 0};
