@@ -18,6 +18,17 @@ class OccupancyParams(C.Structure):
                 ("trinary_costmap", C.c_int32), ("track_unknown_space", C.c_int32)]
 
 
+class LethalArea(C.Structure):
+    """fitslam_lethal_area (include/fitslam_cuda.h): kind 0 = addNewMarkedArea circle, 1 = addNewMarkedAreaFOV triangle."""
+    _fields_ = [("wx", C.c_double), ("wy", C.c_double), ("extent", C.c_double), ("yaw", C.c_double), ("kind", C.c_int32), ("reserved", C.c_int32)]
+
+
+class SensorParams(C.Structure):
+    """fitslam_sensor_params (include/fitslam_cuda.h)."""
+    _fields_ = [("sensor_min_angle", C.c_double), ("sensor_max_angle", C.c_double), ("angular_resolution", C.c_double),
+                ("sensor_max_range", C.c_double)]
+
+
 class Params(C.Structure):
     _fields_ = [
         ("min_frontier_cluster_size", C.c_int32), ("max_frontier_cluster_size", C.c_int32),
@@ -80,6 +91,10 @@ PROTOTYPES = {
     "fitslam_get_costmap": (C.c_int, [_vp, _vp, C.c_uint64]),
     "fitslam_set_occupancy_grid": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
     "fitslam_default_occupancy_params": (None, [_vp]),
+    "fitslam_mark_lethal": (C.c_int, [_vp, _vp, C.c_uint32, _u32p]),
+    "fitslam_default_sensor_params": (None, [_vp]),
+    "fitslam_sensor_mark_rays": (C.c_int, [_vp, _vp, _vp, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
+                                           C.c_double, _vp, _u32p]),
     "fitslam_set_map_points": (C.c_int, [_vp, _vp, C.c_uint64]),
     "fitslam_search_frontiers": (C.c_int, [_vp, C.c_double, C.c_double, _vp, _u32p, _vp, _u32p]),
     "fitslam_set_search_distance": (C.c_int, [_vp, C.c_double]),
@@ -118,6 +133,20 @@ def default_occupancy_params():
     p = OccupancyParams()
     load_library().fitslam_default_occupancy_params(C.byref(p))
     return p
+
+
+def default_sensor_params():
+    p = SensorParams()
+    load_library().fitslam_default_sensor_params(C.byref(p))
+    return p
+
+
+def lethal_areas(areas):
+    """[(wx, wy, extent, yaw, kind), ...] -> a fitslam_lethal_area array."""
+    arr = (LethalArea * max(len(areas), 1))()
+    for i, (wx, wy, extent, yaw, kind) in enumerate(areas):
+        arr[i] = LethalArea(wx, wy, extent, yaw, kind, 0)
+    return arr
 
 
 def default_params(lib=None):
@@ -207,6 +236,27 @@ class Context:
         out = np.zeros((self.H, self.W), np.uint8)
         self._check(self.lib.fitslam_get_costmap(self.h, _ptr(out), out.size))
         return out
+
+    def mark_lethal(self, areas):
+        """LethalMarker: stamp 253 over the ray fans of [(wx, wy, extent, yaw, kind), ...] in the resident costmap;
+        returns the number of areas whose centre was on the map."""
+        arr, n = lethal_areas(areas), C.c_uint32(0)
+        self._check(self.lib.fitslam_mark_lethal(self.h, C.cast(arr, _vp), len(areas), C.byref(n)))
+        return n.value
+
+    def sensor_mark_rays(self, latest, explored, res, ox, oy, px, py, yaw, params=None, shape=None):
+        """SensorSimulator ray marking.  latest / explored: int8 numpy arrays [H, W] (explored is updated in place) or two
+        raw device addresses with shape=(H, W).  Returns the number of rays cast."""
+        if isinstance(latest, np.ndarray):
+            assert latest.dtype == np.int8 and explored.dtype == np.int8 and latest.shape == explored.shape
+            assert latest.flags.c_contiguous and explored.flags.c_contiguous
+            H, W = latest.shape
+        else:
+            H, W = shape
+        n = C.c_uint32(0)
+        self._check(self.lib.fitslam_sensor_mark_rays(self.h, _ptr(latest), _ptr(explored), W, H, res, ox, oy, px, py, yaw,
+                                                      C.byref(params) if params is not None else None, C.byref(n)))
+        return n.value
 
     def set_map_points(self, xyz, n=None):
         if isinstance(xyz, np.ndarray):

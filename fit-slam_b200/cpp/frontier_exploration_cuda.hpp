@@ -370,6 +370,58 @@ private:
   double RADIUS_TO_DECIDE_EDGES;
 };
 
+// ---- LethalMarker (include/frontier_exploration/nav2_plugins/lethal_marker.hpp:33-104; FS2 keepout_layer.hpp) ------------
+// The costmap layer keeps every marked area and writes 253 over all of them on each updateCosts (lethal_marker.cpp:303-327).
+// Here the areas are kept as their specifications (as FS2's zone_specs_, keepout_layer.cpp:201-203) and one launch stamps
+// them into the context's resident costmap; call updateCosts() after every updateCostmap / updateOccupancyGrid, which is
+// where the layered costmap would run this layer.
+class LethalMarker {
+public:
+  explicit LethalMarker(CudaContextPtr ctx) : ctx_(ctx) {}
+  void addNewMarkedArea(double center_wx, double center_wy, double radius) {  // lethal_marker.cpp:219-228
+    areas_.push_back(fitslam_lethal_area{center_wx, center_wy, radius, 0.0, 0, 0});
+  }
+  void addNewMarkedAreaFOV(double center_wx, double center_wy, double angleYaw, double height) {  // :230-239
+    areas_.push_back(fitslam_lethal_area{center_wx, center_wy, height, angleYaw, 1, 0});
+  }
+  void setEnabled(bool enabled) { enabled_ = enabled; }  // the `enabled` parameter (:250-275)
+  void clear() { areas_.clear(); }
+  size_t numAdditions() const { return areas_.size(); }
+  // returns the number of areas whose centre lies on the map (the others are skipped, :222-223)
+  uint32_t updateCosts() {
+    if (!enabled_ || areas_.empty()) return 0;  // "Costs returned because not enabled." (:307-311)
+    uint32_t marked = 0;
+    ctx_->check(fitslam_mark_lethal(ctx_->get(), areas_.data(), (uint32_t)areas_.size(), &marked), "fitslam_mark_lethal");
+    return marked;
+  }
+private:
+  CudaContextPtr ctx_;
+  std::vector<fitslam_lethal_area> areas_;
+  bool enabled_ = true;
+};
+
+// ---- SensorSimulator, the marking step (RE/include/roadmap_explorer/SensorSimulator.hpp; SensorSimulator.cpp:193-246) ----
+// timerCallback's ray loop over the int8 cells of latest_map_ / explored_map_ (nav_msgs/OccupancyGrid::data); subscriptions,
+// publishing, map saving and the geometry-change reprojection stay with the caller.
+class SensorSimulator {
+public:
+  explicit SensorSimulator(CudaContextPtr ctx) : ctx_(ctx) { fitslam_default_sensor_params(&params_); }
+  fitslam_sensor_params &parameters() { return params_; }  // sensorSimulator.* of RE/src/Parameters.cpp:227-240
+  // explored (size_x * size_y cells) is updated in place; returns the number of rays cast
+  uint32_t markRays(const std::vector<int8_t> &latest, std::vector<int8_t> &explored, uint32_t size_x, uint32_t size_y, double resolution,
+                    double origin_x, double origin_y, const geometry_msgs::msg::Pose &base_pose, double base_yaw) {
+    if (latest.size() != (size_t)size_x * size_y || explored.size() != latest.size())
+      throw std::runtime_error("SensorSimulator::markRays: grids do not match the geometry");
+    uint32_t n = 0;
+    ctx_->check(fitslam_sensor_mark_rays(ctx_->get(), latest.data(), explored.data(), size_x, size_y, resolution, origin_x, origin_y,
+                                         base_pose.position.x, base_pose.position.y, base_yaw, &params_, &n), "fitslam_sensor_mark_rays");
+    return n;
+  }
+private:
+  CudaContextPtr ctx_;
+  fitslam_sensor_params params_;
+};
+
 }  // namespace frontier_exploration
 
 namespace roadmap_explorer {  // the maintained package uses the same classes under this namespace (RE/include/roadmap_explorer/)
@@ -381,4 +433,6 @@ using frontier_exploration::FrontierCostCalculator;
 using frontier_exploration::FrontierPtr;
 using frontier_exploration::FrontierRoadMap;
 using frontier_exploration::FrontierSearch;
+using frontier_exploration::LethalMarker;
+using frontier_exploration::SensorSimulator;
 }  // namespace roadmap_explorer

@@ -178,7 +178,7 @@ void fitslam_destroy(fitslam_ctx *c) {
   c->records.release();
   c->scratch.release();
   if (c->pinned) cudaFreeHost(c->pinned);
-  c->edge_seg.release(); c->edge_out.release(); c->occ_stage.release();
+  c->edge_seg.release(); c->edge_out.release(); c->occ_stage.release(); c->stamp_tab.release();
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }

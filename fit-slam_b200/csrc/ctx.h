@@ -98,6 +98,7 @@ struct fitslam_ctx {
   uint64_t records_rows = 0;  // rows of `records` the last scoring call laid out (fitslam_score_records)
 
   fitslam::DevBuf<int8_t> occ_stage;  // fitslam_set_occupancy_grid: the int8 grid (or its dirty rectangle) before translation
+  fitslam::DevBuf<double> stamp_tab;  // fitslam_mark_lethal / fitslam_sensor_mark_rays: host-built ray tables
   // ---- roadmap edge batches (fitslam_roadmap_connectable)
   fitslam::DevBuf<double> edge_seg;
   fitslam::DevBuf<int32_t> edge_out;

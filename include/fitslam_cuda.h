@@ -214,6 +214,48 @@ FITSLAM_API fitslam_status fitslam_set_occupancy_grid(fitslam_ctx *ctx, const in
  * device, `capacity` bytes. */
 FITSLAM_API fitslam_status fitslam_get_costmap(fitslam_ctx *ctx, uint8_t *out, uint64_t capacity);
 
+/* ------------------------------------------------------------------ lethal marker (stamping half) */
+/* LethalMarker (DEP/src/nav2_plugins/lethal_marker.cpp; the same layer in FS2/fit_slam2_nav2_plugins/plugins/
+ * keepout_layer.cpp): each marked area is a fan of Bresenham rays (rayTraceGeneric, lethal_marker.cpp:12-41) from the
+ * centre / apex cell; LethalMarker::updateCosts -> markCells writes 253 into every traced cell of the master grid
+ * (:242-248, :303-327).
+ *   kind 0 = addNewMarkedArea (:219-228): 360 rays to the circle of (unsigned)(extent / resolution) cells
+ *            (getPointsInSemiCircle with robot_yaw 0, :52-73);
+ *   kind 1 = addNewMarkedAreaFOV (:230-239): 20 rays from the apex to samples along the base of an isosceles
+ *            triangle of height (unsigned)(extent / resolution) cells, apex angle 45 degrees, pointing along `yaw`
+ *            (getPointsInIsoscelesTriangle, :75-127).
+ * Ray end points are clamped to the map (cellEnforceBoundaries, :5-11).  An area whose centre is off the map is
+ * skipped, as in the reference.  The stamps go into the resident costmap (see fitslam_get_costmap); n_marked
+ * (optional) = areas that were on the map. */
+typedef struct fitslam_lethal_area {
+  double wx, wy;  /* centre (kind 0) / apex (kind 1), world frame */
+  double extent;  /* radius (kind 0) / triangle height (kind 1), metres */
+  double yaw;     /* kind 1: direction from the apex toward the base centre, radians */
+  int32_t kind;
+  int32_t reserved;
+} fitslam_lethal_area;
+FITSLAM_API fitslam_status fitslam_mark_lethal(fitslam_ctx *ctx, const fitslam_lethal_area *areas, uint32_t n,
+                                               uint32_t *n_marked);
+
+/* ------------------------------------------------------------------ sensor simulator */
+/* SensorSimulator::timerCallback ray loop + markRay (RE/src/SensorSimulator.cpp:193-202, 211-246): for
+ * a = min_angle; a <= max_angle; a += angular_resolution, a ray from the robot position along base_yaw + a in steps
+ * of `resolution` up to max_range copies latest[idx] into explored[idx] cell by cell and stops behind the first cell
+ * whose value is > 80 or at the map border.  latest / explored: size_x * size_y int8 (nav_msgs/OccupancyGrid data),
+ * both host or both device; explored is updated in place.  n_rays (optional) = rays cast. */
+typedef struct fitslam_sensor_params {
+  double sensor_min_angle;   /* -pi/4 (RE/src/Parameters.cpp:233-234) */
+  double sensor_max_angle;   /*  pi/4 (:236-237) */
+  double angular_resolution; /* 0.013 (:227-228) */
+  double sensor_max_range;   /* 3.0   (:239-240) */
+} fitslam_sensor_params;
+FITSLAM_API void fitslam_default_sensor_params(fitslam_sensor_params *p);
+FITSLAM_API fitslam_status fitslam_sensor_mark_rays(fitslam_ctx *ctx, const int8_t *latest, int8_t *explored,
+                                                    uint32_t size_x, uint32_t size_y, double resolution,
+                                                    double origin_x, double origin_y, double robot_x, double robot_y,
+                                                    double base_yaw, const fitslam_sensor_params *p,
+                                                    uint32_t *n_rays);
+
 /* ------------------------------------------------------------------ roadmap edges */
 /* FrontierRoadMap::isConnectable for a batch of node pairs (RE/src/planners/FrontierRoadmap.cpp:671-694): one ray
  * from (x0, y0) to (x1, y1) per pair through getTracedCells (RE/src/Helpers.cpp:30-91; at most

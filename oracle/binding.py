@@ -102,6 +102,24 @@ class Oracle:
         self.lib.orc_occupancy_to_cost(C.c_void_p(g.ctypes.data), C.c_uint64(g.size), C.byref(occ_params), C.c_void_p(out.ctypes.data))
         return out
 
+    def mark_lethal(self, a, meta, areas):
+        """LethalMarker on a copy of the costmap: (stamped map, areas that were on the map)."""
+        a, m = self._map(np.array(a, np.uint8, copy=True), meta)
+        arr, n = self.capi.lethal_areas(areas), C.c_uint32(0)
+        self.lib.orc_mark_lethal(*m, C.cast(arr, C.c_void_p), C.c_uint32(len(areas)), C.byref(n))
+        return a, n.value
+
+    def sensor_mark_rays(self, latest, explored, res, ox, oy, px, py, yaw, params):
+        """SensorSimulator ray marking: (updated copy of explored, rays cast)."""
+        lat = np.ascontiguousarray(latest, np.int8)
+        exp = np.array(explored, np.int8, copy=True, order="C")
+        H, W = lat.shape
+        n = C.c_uint32(0)
+        self.lib.orc_sensor_mark_rays(C.c_void_p(lat.ctypes.data), C.c_void_p(exp.ctypes.data), C.c_uint32(W), C.c_uint32(H),
+                                      C.c_double(res), C.c_double(ox), C.c_double(oy), C.c_double(px), C.c_double(py),
+                                      C.c_double(yaw), C.byref(params), C.byref(n))
+        return exp, n.value
+
     def roadmap_connectable(self, a, meta, segments, radius):
         """FrontierRoadMap::isConnectable for n node pairs (n x 4 doubles): (flags uint8, unknown counts int32)."""
         a, m = self._map(a, meta)

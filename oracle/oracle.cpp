@@ -37,6 +37,7 @@
 #include <string>
 #include <unordered_map>
 #include <utility>
+#include <map>
 #include <vector>
 
 #include "../include/fitslam_cuda.h"
@@ -1158,6 +1159,121 @@ int orc_occupancy_to_cost(const int8_t *data, uint64_t n, const fitslam_occupanc
     grid = thresholded.data();
   }
   for (uint64_t i = 0; i < n; ++i) out[i] = interpretValue((unsigned char)grid[i], *p);
+  return FITSLAM_OK;
+}
+
+// LethalMarker (DEP/src/nav2_plugins/lethal_marker.cpp; same layer: FS2/fit_slam2_nav2_plugins/plugins/keepout_layer.cpp).
+// An area is cached as the list of cell indices its rays visit (addNewMarkedArea :219-228, addNewMarkedAreaFOV :230-239);
+// updateCosts (:303-327) then writes 253 over every cached list (markCells :242-248).
+namespace lethal_marker {
+// clamp of a ray end point to the grid (cellEnforceBoundaries, :5-11)
+void clampToGrid(int64_t &x, int64_t &y, const Costmap2D &costmap) {
+  const int64_t last_x = (int64_t)costmap.getSizeInCellsX() - 1, last_y = (int64_t)costmap.getSizeInCellsY() - 1;
+  if (x < 0) x = 0;
+  if (x > last_x) x = last_x;
+  if (y < 0) y = 0;
+  if (y > last_y) y = last_y;
+}
+// the error-term line walk of rayTraceGeneric (:12-41): visits (x0, y0) first and (x1, y1) last; cells whose flat
+// index falls outside [0, W * H) are not recorded
+void traceLine(const Costmap2D &costmap, int64_t x0, int64_t y0, int64_t x1, int64_t y1, std::vector<unsigned int> &cells) {
+  const int64_t map_width = costmap.getSizeInCellsX(), n_cells = (int64_t)(costmap.getSizeInCellsY() * costmap.getSizeInCellsX());
+  const int64_t dx = std::abs(x1 - x0), dy = std::abs(y1 - y0);
+  const int64_t sx = x0 < x1 ? 1 : -1, sy = y0 < y1 ? 1 : -1;
+  int64_t err = dx - dy;
+  for (;;) {
+    const int64_t index = y0 * map_width + x0;
+    if (index >= 0 && index < n_cells) cells.push_back(static_cast<unsigned int>(index));
+    if (x0 == x1 && y0 == y1) return;
+    const int64_t e2 = 2 * err;
+    if (e2 > -dy) { err -= dy; x0 += sx; }
+    if (e2 < dx) { err += dx; y0 += sy; }
+  }
+}
+// getPointsInSemiCircle (:52-73)
+std::vector<unsigned int> circleCells(unsigned int center_x, unsigned int center_y, unsigned int radius_in_cells,
+                                      unsigned int numPoints, double robot_yaw, const Costmap2D &costmap) {
+  std::vector<unsigned int> all_cells;
+  for (unsigned int i = 0; i < numPoints; ++i) {
+    double angle = 2.0 * M_PI * i / numPoints;
+    int64_t x = static_cast<int64_t>(center_x + radius_in_cells * std::cos(robot_yaw - M_PI_2 + angle));
+    int64_t y = static_cast<int64_t>(center_y + radius_in_cells * std::sin(robot_yaw - M_PI_2 + angle));
+    clampToGrid(x, y, costmap);
+    traceLine(costmap, center_x, center_y, static_cast<unsigned int>(x), static_cast<unsigned int>(y), all_cells);
+  }
+  return all_cells;
+}
+// getPointsInIsoscelesTriangle (:75-127)
+std::vector<unsigned int> triangleCells(unsigned int apex_x, unsigned int apex_y, unsigned int triangle_height,
+                                        unsigned int numPoints, double direction, double apex_angle, const Costmap2D &costmap) {
+  std::vector<unsigned int> all_cells;
+  double base_center_x = apex_x + triangle_height * std::cos(direction);
+  double base_center_y = apex_y + triangle_height * std::sin(direction);
+  double half_base = triangle_height * std::tan(apex_angle / 2.0);
+  double left_endpoint_x = base_center_x + half_base * std::cos(direction + M_PI_2);
+  double left_endpoint_y = base_center_y + half_base * std::sin(direction + M_PI_2);
+  double right_endpoint_x = base_center_x + half_base * std::cos(direction - M_PI_2);
+  double right_endpoint_y = base_center_y + half_base * std::sin(direction - M_PI_2);
+  for (unsigned int i = 0; i < numPoints; ++i) {
+    double t = (numPoints > 1) ? static_cast<double>(i) / (numPoints - 1) : 0.0;
+    double sample_x = left_endpoint_x + t * (right_endpoint_x - left_endpoint_x);
+    double sample_y = left_endpoint_y + t * (right_endpoint_y - left_endpoint_y);
+    int64_t cell_x = static_cast<int64_t>(sample_x);
+    int64_t cell_y = static_cast<int64_t>(sample_y);
+    clampToGrid(cell_x, cell_y, costmap);
+    traceLine(costmap, apex_x, apex_y, static_cast<unsigned int>(cell_x), static_cast<unsigned int>(cell_y), all_cells);
+  }
+  return all_cells;
+}
+}  // namespace lethal_marker
+int orc_mark_lethal(uint8_t *map, uint32_t W, uint32_t H, double res, double ox, double oy, const fitslam_lethal_area *areas,
+                    uint32_t n, uint32_t *n_marked) {
+  Costmap2D cm = makeMap(map, W, H, res, ox, oy);
+  std::map<int, std::vector<unsigned int>> latest_cells_to_mark_index_;
+  int numAdditions_ = 0;
+  for (uint32_t a = 0; a < n; ++a) {
+    unsigned int robot_xm, robot_ym;
+    if (!cm.worldToMap(areas[a].wx, areas[a].wy, robot_xm, robot_ym)) continue;
+    auto extent_in_cells = areas[a].extent / cm.getResolution();  // a double, narrowed to unsigned int by the callee
+    if (areas[a].kind == 0)
+      latest_cells_to_mark_index_[numAdditions_] = lethal_marker::circleCells(robot_xm, robot_ym, extent_in_cells, 360, 0, cm);
+    else
+      latest_cells_to_mark_index_[numAdditions_] =
+          lethal_marker::triangleCells(robot_xm, robot_ym, extent_in_cells, 20, areas[a].yaw, 45 * M_PI / 180, cm);
+    numAdditions_++;
+  }
+  for (int add = 0; add < numAdditions_; add++)
+    for (auto index : latest_cells_to_mark_index_.at(add)) map[index] = 253;
+  if (n_marked) *n_marked = (uint32_t)numAdditions_;
+  return FITSLAM_OK;
+}
+
+// SensorSimulator (RE/src/SensorSimulator.cpp): the ray loop of timerCallback (:193-202) and markRay (:211-246) on the
+// int8 cells of two nav_msgs/OccupancyGrid messages of the same geometry.
+int orc_sensor_mark_rays(const int8_t *latest, int8_t *explored, uint32_t size_x, uint32_t size_y, double resolution, double origin_x,
+                         double origin_y, double robot_x, double robot_y, double base_yaw, const fitslam_sensor_params *p,
+                         uint32_t *n_rays) {
+  const double res = resolution;
+  const int w = static_cast<int>(size_x);
+  const int h = static_cast<int>(size_y);
+  uint32_t cast = 0;
+  for (double a = p->sensor_min_angle; a <= p->sensor_max_angle; a += p->angular_resolution) {
+    const double ray_angle = base_yaw + a;
+    const double dx = std::cos(ray_angle);
+    const double dy = std::sin(ray_angle);
+    ++cast;
+    for (double r = 0.0; r <= p->sensor_max_range; r += res) {
+      const double wx = robot_x + r * dx;
+      const double wy = robot_y + r * dy;
+      const int mx = static_cast<int>((wx - origin_x) / res);
+      const int my = static_cast<int>((wy - origin_y) / res);
+      if (mx < 0 || my < 0 || mx >= w || my >= h) break;
+      const std::size_t idx = static_cast<std::size_t>(my) * w + mx;
+      explored[idx] = latest[idx];
+      if (latest[idx] > 80) break;
+    }
+  }
+  if (n_rays) *n_rays = cast;
   return FITSLAM_OK;
 }
 

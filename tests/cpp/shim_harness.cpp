@@ -95,6 +95,39 @@ int main(int argc, char **argv) {
   double sx = 0, sy = 0;
   for (auto &c : every) { sx += c[0]; sy += c[1]; }
   std::printf("cellsum %a %a\n", sx, sy);
+  // sensor simulator: a fan around the robot on an occupancy grid derived from the costmap (254 -> 100, 255 -> -1, else 0)
+  {
+    std::vector<int8_t> latest((size_t)W * H), explored((size_t)W * H, -1);
+    for (size_t i = 0; i < latest.size(); ++i) {
+      const unsigned char v = costmap.getCharMap()[i];
+      latest[i] = v == 254 ? 100 : (v == 255 ? -1 : 0);
+    }
+    roadmap_explorer::SensorSimulator sim(ctx);
+    geometry_msgs::msg::Pose base;
+    base.position.x = g[3];
+    base.position.y = g[4];
+    const uint32_t n_rays = sim.markRays(latest, explored, W, H, g[0], g[1], g[2], base, 0.4);
+    uint64_t seen = 0, wsum = 0;
+    for (size_t i = 0; i < explored.size(); ++i)
+      if (explored[i] != -1) { ++seen; wsum += (uint64_t)i * (uint64_t)(explored[i] + 2); }
+    std::printf("sensor %u %llu %llu\n", n_rays, (unsigned long long)seen, (unsigned long long)wsum);
+  }
+  // lethal marker: the two calls of ExplorationBT.cpp:621-622 stamped into the resident costmap
+  {
+    frontier_exploration::LethalMarker marker(ctx);
+    marker.addNewMarkedAreaFOV(g[3] + 1.0, g[4], 0.7, 3.5);
+    marker.addNewMarkedArea(g[3] - 2.0, g[4] + 1.0, 1.7);
+    marker.addNewMarkedArea(g[1] - 5.0, g[2], 1.7);  // off the map: skipped
+    const uint32_t marked = marker.updateCosts();
+    std::vector<uint8_t> stamped((size_t)W * H);
+    ctx->check(fitslam_get_costmap(ctx->get(), stamped.data(), stamped.size()), "fitslam_get_costmap");
+    uint64_t n253 = 0, isum = 0, changed = 0;
+    for (size_t i = 0; i < stamped.size(); ++i) {
+      if (stamped[i] == 253) { ++n253; isum += i; }
+      if (stamped[i] != costmap.getCharMap()[i]) ++changed;
+    }
+    std::printf("lethal %u %llu %llu %llu\n", marked, (unsigned long long)n253, (unsigned long long)isum, (unsigned long long)changed);
+  }
   // robot off the map: empty list, no exception (FrontierSearch.cpp:28-32)
   robot.x = g[1] - 1.0;
   std::printf("offmap %zu\n", search.searchFrom(robot).size());

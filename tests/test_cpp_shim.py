@@ -86,3 +86,16 @@ def test_shim_matches_oracle(harness, capi, oracle, synth, tmp_path):
     edges = [ln.split() for ln in lines if ln.startswith("edges")][0]
     assert [int(v) for v in edges[1:]] == list(wok)
     assert [ln.split() for ln in lines if ln.startswith("edge1")][0][1] == str(int(wok[0]))
+    # SensorSimulator::markRays and LethalMarker::updateCosts through the shim classes
+    latest = np.where(a == 254, 100, np.where(a == 255, -1, 0)).astype(np.int8)
+    want, n_rays = oracle.sensor_mark_rays(latest, np.full_like(latest, -1), meta["res"], meta["ox"], meta["oy"], meta["robot_x"], meta["robot_y"],
+                                           0.4, capi.default_sensor_params())
+    idx = np.flatnonzero(want.ravel() != -1)
+    wsum = int((idx.astype(np.uint64) * (want.ravel()[idx].astype(np.int64) + 2).astype(np.uint64)).sum())
+    assert [ln.split() for ln in lines if ln.startswith("sensor")][0][1:] == [str(n_rays), str(len(idx)), str(wsum)]
+    areas = [(meta["robot_x"] + 1.0, meta["robot_y"], 3.5, 0.7, 1), (meta["robot_x"] - 2.0, meta["robot_y"] + 1.0, 1.7, 0.0, 0),
+             (meta["ox"] - 5.0, meta["oy"], 1.7, 0.0, 0)]
+    stamped, marked = oracle.mark_lethal(a, meta, areas)
+    i253 = np.flatnonzero(stamped.ravel() == 253)
+    assert marked == 2 and len(i253) > 50
+    assert [ln.split() for ln in lines if ln.startswith("lethal")][0][1:] == [str(marked), str(len(i253)), str(int(i253.sum())), str(int((stamped != a).sum()))]
