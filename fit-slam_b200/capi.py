@@ -107,6 +107,7 @@ PROTOTYPES = {
     "fitslam_fisher_lookup_dims": (C.c_int, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "fitslam_fisher_lookup_copy": (C.c_int, [_vp, _vp, C.c_uint64]),
     "fitslam_score_fisher": (C.c_int, [_vp, _vp, C.c_uint32, _vp, _vp, _vp]),
+    "fitslam_landmarks_in_view": (C.c_int, [_vp, _vp, _vp, C.c_uint32, _u32p]),
     "fitslam_normalise_select": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp, _vp,
                                            C.POINTER(Selection)]),
     "fitslam_cycle": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, C.POINTER(CycleResult)]),
@@ -332,6 +333,15 @@ class Context:
         nvis = np.zeros(n, dtype=np.uint32)
         self._check(self.lib.fitslam_score_fisher(self.h, _ptr(poses), n, _ptr(info), _ptr(safe), _ptr(nvis)))
         return info, safe, nvis
+
+    def landmarks_in_view(self, pose, capacity=None):
+        """GetLandmarksInView (exhaustive) for one pose (a POSE_DTYPE record): (xyz [count, 3] float32 in the pose frame, count)."""
+        pose = np.ascontiguousarray(pose, dtype=POSE_DTYPE).reshape(1)
+        cap = int(capacity if capacity is not None else 1 << 22)
+        out = np.zeros((cap, 3), np.float32)
+        n = C.c_uint32(0)
+        st = self._check(self.lib.fitslam_landmarks_in_view(self.h, _ptr(pose), _ptr(out), cap, C.byref(n)), allow=(E_CAPACITY,))
+        return st, out[:min(n.value, cap)], n.value
 
     def normalise_select(self, path_length_m, path_heading, blacklisted=None):
         n = len(path_length_m)

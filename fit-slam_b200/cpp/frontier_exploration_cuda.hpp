@@ -331,6 +331,21 @@ public:
     if (!poses.empty())
       ctx_->check(fitslam_score_fisher(ctx_->get(), p.data(), (uint32_t)p.size(), information.data(), safe.data(), nullptr), "fitslam_score_fisher");
   }
+  // the landmark service itself (slam_msgs/srv/GetLandmarksInView, exhaustive search): positions of the visible map
+  // points in the frame of `pose`, in map-point order, widened to double as geometry_msgs/Point carries them
+  // (ORBW/src/rgbd/rgbd-slam-node.cpp:406-429 over orb_slam3_interface.cpp:188-317)
+  std::vector<geometry_msgs::msg::Point> getLandmarksInView(const geometry_msgs::msg::Pose &pose) {
+    const fitslam_pose p{pose.position.x, pose.position.y, pose.position.z, pose.orientation.x, pose.orientation.y, pose.orientation.z,
+                         pose.orientation.w};
+    uint32_t n = 0;
+    fitslam_status st = fitslam_landmarks_in_view(ctx_->get(), &p, nullptr, 0, &n);
+    if (st != FITSLAM_OK && st != FITSLAM_E_CAPACITY) ctx_->check(st, "fitslam_landmarks_in_view");
+    std::vector<float> xyz(3 * (size_t)n);
+    if (n) ctx_->check(fitslam_landmarks_in_view(ctx_->get(), &p, xyz.data(), n, &n), "fitslam_landmarks_in_view");
+    std::vector<geometry_msgs::msg::Point> out(n);
+    for (uint32_t i = 0; i < n; ++i) { out[i].x = xyz[3 * i]; out[i].y = xyz[3 * i + 1]; out[i].z = xyz[3 * i + 2]; }
+    return out;
+  }
 private:
   CudaContextPtr ctx_;
   std::string lookup_path_;

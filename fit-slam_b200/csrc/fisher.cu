@@ -997,3 +997,178 @@ extern "C" fitslam_status fitslam_score_fisher(fitslam_ctx *c, const fitslam_pos
   FS_CUDA(c, cudaStreamSynchronize(c->stream));
   return FITSLAM_OK;
 }
+
+// ================================================================================================ GetLandmarksInView
+// The service the Fisher plugin calls (exhaustive mode): ORBSLAM3Interface::mapPointsVisibleFromPose
+// (ORBW/src/orb_slam3_interface.cpp:188-317) over every map point, each visible one converted as the node does before it
+// fills the response (ORBW/src/rgbd/rgbd-slam-node.cpp:406-429), in map-point order.  Ordered compaction in three launches
+// over the caller's (unsorted) points: per-tile counts, a scan of the tile counts, and the writes.
+namespace fitslam {
+
+static constexpr int LIV_THREADS = 256, LIV_PER_THREAD = 4, LIV_TILE = LIV_THREADS * LIV_PER_THREAD;
+
+__device__ __forceinline__ uint32_t liv_visible_mask(const float *__restrict__ xyz, uint64_t n, uint64_t p0, const PoseFrame &F,
+                                                     const FisherParams &P, float4 q[LIV_PER_THREAD]) {
+  uint32_t m = 0;
+  if (p0 + LIV_PER_THREAD <= n) {  // 12 consecutive floats, 48-byte aligned
+    const float4 a = __ldg(reinterpret_cast<const float4 *>(xyz + 3 * p0));
+    const float4 b = __ldg(reinterpret_cast<const float4 *>(xyz + 3 * p0) + 1);
+    const float4 c = __ldg(reinterpret_cast<const float4 *>(xyz + 3 * p0) + 2);
+    q[0] = make_float4(a.x, a.y, a.z, 0.f);
+    q[1] = make_float4(a.w, b.x, b.y, 0.f);
+    q[2] = make_float4(b.z, b.w, c.x, 0.f);
+    q[3] = make_float4(c.y, c.z, c.w, 0.f);
+#pragma unroll
+    for (int k = 0; k < LIV_PER_THREAD; ++k) m |= point_visible(q[k], F, P) ? (1u << k) : 0u;
+  } else {
+    for (int k = 0; k < LIV_PER_THREAD; ++k) {
+      q[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p0 + k < n) {
+        q[k] = make_float4(xyz[3 * (p0 + k)], xyz[3 * (p0 + k) + 1], xyz[3 * (p0 + k) + 2], 0.f);
+        m |= point_visible(q[k], F, P) ? (1u << k) : 0u;
+      }
+    }
+  }
+  return m;
+}
+
+// exclusive offset of this thread's count within the CTA, and the CTA total
+__device__ __forceinline__ uint32_t liv_block_scan(uint32_t cnt, uint32_t *warp_sums, uint32_t *total) {
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (uint32_t)d) incl += v;
+  }
+  if (lane == 31) warp_sums[wid] = incl;
+  __syncthreads();
+  uint32_t base = 0, tot = 0;
+  for (uint32_t w = 0; w < LIV_THREADS / 32; ++w) {
+    const uint32_t s = warp_sums[w];
+    if (w < wid) base += s;
+    tot += s;
+  }
+  *total = tot;
+  return base + incl - cnt;
+}
+
+// pass 0: tile_count[b]; pass 1: writes at tile_offset[b]
+template <int PASS>
+__global__ void __launch_bounds__(LIV_THREADS) landmarks_in_view_kernel(const FisherParams P, const fitslam_pose *__restrict__ pose,
+                                                                         const float *__restrict__ xyz, uint64_t n, uint32_t *tile_count,
+                                                                         const uint32_t *__restrict__ tile_offset, float *__restrict__ out,
+                                                                         uint32_t capacity) {
+  __shared__ PoseFrame F;
+  __shared__ uint32_t warp_sums[LIV_THREADS / 32];
+  if (threadIdx.x == 0) build_pose_frame(*pose, P, F);
+  __syncthreads();
+  const uint64_t p0 = ((uint64_t)blockIdx.x * LIV_THREADS + threadIdx.x) * LIV_PER_THREAD;
+  float4 q[LIV_PER_THREAD];
+  const uint32_t m = liv_visible_mask(xyz, n, p0, F, P, q);
+  uint32_t total;
+  const uint32_t excl = liv_block_scan((uint32_t)__popc(m), warp_sums, &total);
+  if (PASS == 0) {
+    if (threadIdx.x == 0) tile_count[blockIdx.x] = total;
+    return;
+  }
+  uint32_t dst = tile_offset[blockIdx.x] + excl;
+#pragma unroll
+  for (int k = 0; k < LIV_PER_THREAD; ++k) {
+    if (!((m >> k) & 1u)) continue;
+    if (dst < capacity) {
+      // vector3fORBToROS of the ORB-frame point is the ROS triple again (signed permutation; see voxel_of_visible_point),
+      // then affinePosToMap * position (rgbd-slam-node.cpp:419-425)
+      V3f pos; pos.v[0] = q[k].x; pos.v[1] = q[k].y; pos.v[2] = q[k].z;
+      const V3f lp = mulv(F.Rinv, pos);
+      out[3 * (size_t)dst] = lp.v[0] + F.tinv.v[0];
+      out[3 * (size_t)dst + 1] = lp.v[1] + F.tinv.v[1];
+      out[3 * (size_t)dst + 2] = lp.v[2] + F.tinv.v[2];
+    }
+    ++dst;
+  }
+}
+
+// exclusive scan of the tile counts in place (one CTA, chunks of 1024 with a running carry); the total goes to *total
+__global__ void __launch_bounds__(1024) liv_scan_kernel(uint32_t *tile, uint32_t n_tiles, uint32_t *total) {
+  __shared__ uint32_t ws[32];
+  __shared__ uint32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < n_tiles; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < n_tiles ? tile[i] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= (uint32_t)d) incl += u;
+    }
+    if (lane == 31) ws[wid] = incl;
+    __syncthreads();
+    uint32_t wb = 0, tot = 0;
+    for (uint32_t w = 0; w < 32; ++w) {
+      const uint32_t s = ws[w];
+      if (w < wid) wb += s;
+      tot += s;
+    }
+    const uint32_t c0 = carry;
+    if (i < n_tiles) tile[i] = c0 + wb + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry = c0 + tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+}  // namespace fitslam
+
+extern "C" fitslam_status fitslam_landmarks_in_view(fitslam_ctx *c, const fitslam_pose *pose, float *out_xyz, uint32_t capacity,
+                                                    uint32_t *count) {
+  if (!c || !pose || !count || (!out_xyz && capacity)) return fail(c, FITSLAM_E_INVALID, "landmarks_in_view: null argument");
+  cudaSetDevice(c->device);
+  FisherState *f = fstate(c);
+  if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no map points set");
+  *count = 0;
+  const uint64_t n = f->n_points;
+  if (n == 0) return FITSLAM_OK;
+  FisherParams P;
+  memset(&P, 0, sizeof(P));
+  P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
+  P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
+  const uint32_t n_tiles = (uint32_t)((n + LIV_TILE - 1) / LIV_TILE);
+  FS_CUDA(c, f->poses.reserve(1));
+  FS_CUDA(c, f->nvis.reserve((size_t)n_tiles + 1));
+  FS_CUDA(c, cudaMemcpyAsync(f->poses.p, pose, sizeof(fitslam_pose), cudaMemcpyDefault, c->stream));
+  uint32_t *tiles = f->nvis.p, *total = f->nvis.p + n_tiles;
+  landmarks_in_view_kernel<0><<<n_tiles, LIV_THREADS, 0, c->stream>>>(P, f->poses.p, f->raw.p, n, tiles, nullptr, nullptr, 0);
+  liv_scan_kernel<<<1, 1024, 0, c->stream>>>(tiles, n_tiles, total);
+  c->launches += 2;
+  const bool out_dev = [&] {
+    cudaPointerAttributes a;
+    const bool d = out_xyz && cudaPointerGetAttributes(&a, out_xyz) == cudaSuccess && (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    return d;
+  }();
+  float *d_out = out_xyz;
+  if (!out_dev && capacity) {
+    FS_CUDA(c, f->info.reserve(3 * (size_t)std::min<uint64_t>(capacity, n)));
+    d_out = f->info.p;
+  }
+  const uint32_t cap = (uint32_t)std::min<uint64_t>(capacity, n);
+  if (cap) {
+    landmarks_in_view_kernel<1><<<n_tiles, LIV_THREADS, 0, c->stream>>>(P, f->poses.p, f->raw.p, n, nullptr, tiles, d_out, cap);
+    ++c->launches;
+  }
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaMemcpyAsync(count, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (!out_dev && cap) {
+    const uint32_t m = std::min(*count, cap);
+    if (m) FS_CUDA(c, cudaMemcpyAsync(out_xyz, d_out, 3 * (size_t)m * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  if (*count > capacity) return fail(c, FITSLAM_E_CAPACITY, "landmarks_in_view: more visible landmarks than capacity (count holds the number)");
+  return FITSLAM_OK;
+}

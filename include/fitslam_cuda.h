@@ -300,6 +300,16 @@ FITSLAM_API fitslam_status fitslam_fisher_lookup_copy(fitslam_ctx *ctx, float *o
 FITSLAM_API fitslam_status fitslam_score_fisher(fitslam_ctx *ctx, const fitslam_pose *poses, uint32_t n_poses,
                                                 float *information, uint8_t *safe, uint32_t *n_visible);
 
+/* The landmark service behind isPoseSafe (exhaustive mode): the `map_points` of a
+ * slam_msgs/srv/GetLandmarksInView response for one pose, i.e. ORBSLAM3Interface::mapPointsVisibleFromPose
+ * (ORBW/src/orb_slam3_interface.cpp:188-317, exhaustive_search = true) over the resident map points, each visible
+ * one transformed into the pose frame as ORBW/src/rgbd/rgbd-slam-node.cpp:406-429 does, in map-point order.
+ * out_xyz: capacity x 3 floats (host or device; the wire widens them to float64); *count = visible landmarks, also
+ * when it exceeds capacity (FITSLAM_E_CAPACITY, the first `capacity` are written).  The keyframe-structured
+ * non-exhaustive mode (:228-272) is not built. */
+FITSLAM_API fitslam_status fitslam_landmarks_in_view(fitslam_ctx *ctx, const fitslam_pose *pose, float *out_xyz,
+                                                     uint32_t capacity, uint32_t *count);
+
 /* ------------------------------------------------------------------ normalisation + selection */
 /* FrontierCostsManager::assignCosts U1 block (DEP/src/FrontierCostsManager.cpp:121-205) followed by
  * FullPathOptimizer::getFilteredFrontiersN (DEP/src/FullPathOptimizer.cpp:157-227).

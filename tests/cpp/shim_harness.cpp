@@ -95,6 +95,17 @@ int main(int argc, char **argv) {
   double sx = 0, sy = 0;
   for (auto &c : every) { sx += c[0]; sy += c[1]; }
   std::printf("cellsum %a %a\n", sx, sy);
+  // the landmark service for the first frontier's pose (GetLandmarksInView, exhaustive)
+  if (!frontiers.empty()) {
+    geometry_msgs::msg::Pose pose;
+    pose.position = frontiers[0]->getGoalPoint();
+    pose.position.z = 0.3;
+    pose.orientation = frontiers[0]->getGoalOrientation();
+    const auto lm = fisher.getLandmarksInView(pose);
+    double sx = 0, sy = 0, sz = 0;
+    for (const auto &p : lm) { sx += p.x; sy += p.y; sz += p.z; }
+    std::printf("landmarks %zu %a %a %a\n", lm.size(), sx, sy, sz);
+  }
   // sensor simulator: a fan around the robot on an occupancy grid derived from the costmap (254 -> 100, 255 -> -1, else 0)
   {
     std::vector<int8_t> latest((size_t)W * H), explored((size_t)W * H, -1);

@@ -99,3 +99,12 @@ def test_shim_matches_oracle(harness, capi, oracle, synth, tmp_path):
     i253 = np.flatnonzero(stamped.ravel() == 253)
     assert marked == 2 and len(i253) > 50
     assert [ln.split() for ln in lines if ln.startswith("lethal")][0][1:] == [str(marked), str(len(i253)), str(int(i253.sum())), str(int((stamped != a).sum()))]
+    # FisherInformationManager::getLandmarksInView for the first frontier's pose
+    want = oracle.landmarks_in_view(pts, poses[:1]).astype(np.float64)
+    lm = [ln.split() for ln in lines if ln.startswith("landmarks")][0]
+    assert int(lm[1]) == len(want)
+    sums = [0.0, 0.0, 0.0]
+    for row in want.tolist():
+        for k in range(3):
+            sums[k] += row[k]
+    assert [float.fromhex(v) for v in lm[2:5]] == sums

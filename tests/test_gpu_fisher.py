@@ -141,3 +141,55 @@ def test_fisher_errors(capi):
     info, safe, nvis = c.score_fisher(poses)
     assert info[0] == 0 and safe[0] == 0 and nvis[0] == 0
     c.close()
+
+
+@pytest.mark.parametrize("n_points,full_rotation", [(1, False), (1023, False), (1024, True), (60_001, True), (200_000, False)])
+def test_landmarks_in_view_equals_the_service(capi, oracle, n_points, full_rotation):
+    """fitslam_landmarks_in_view = the map_points of a GetLandmarksInView response (exhaustive search): the same landmarks, in
+    map-point order, the same floats (== on every coordinate; a -0.0 / +0.0 difference is the only thing it lets through)."""
+    rng = np.random.default_rng(n_points)
+    pts = rng.uniform(-20, 20, size=(n_points, 3)).astype(np.float32)
+    poses = _poses(capi, rng, 6, (-15, -15, 15, 15), z=1.0, full_rotation=full_rotation)
+    if n_points > 10:
+        pts[0] = (poses[0]["x"], poses[0]["y"], poses[0]["z"])  # a landmark at the camera centre
+        pts[1] = (np.nan, 0, 0)
+        pts[2] = (np.inf, 1, 1)
+    ctx = capi.Context()
+    try:
+        ctx.set_map_points(pts)
+        total = 0
+        for i in range(len(poses)):
+            want = oracle.landmarks_in_view(pts, poses[i:i + 1])
+            st, got, n = ctx.landmarks_in_view(poses[i])
+            assert st == 0 and n == len(want) == len(got)
+            assert np.array_equal(got, want, equal_nan=True)
+            total += n
+            if n > 3:  # a short buffer: the count is still reported, the first entries are written
+                st, part, n2 = ctx.landmarks_in_view(poses[i], capacity=3)
+                assert st == capi.E_CAPACITY and n2 == n and np.array_equal(part, want[:3], equal_nan=True)
+        assert n_points < 1000 or total > 0
+        # device output buffer
+        import torch
+        out = torch.zeros((max(n_points, 1), 3), dtype=torch.float32, device="cuda")
+        cnt = __import__("ctypes").c_uint32(0)
+        pose = np.ascontiguousarray(poses[:1])
+        assert ctx.lib.fitslam_landmarks_in_view(ctx.h, pose.ctypes.data, out.data_ptr(), n_points, __import__("ctypes").byref(cnt)) == 0
+        want = oracle.landmarks_in_view(pts, poses[:1])
+        assert cnt.value == len(want) and np.array_equal(out[:cnt.value].cpu().numpy(), want, equal_nan=True)
+    finally:
+        ctx.close()
+
+
+def test_landmarks_in_view_feeds_the_same_information(lut_ctx, oracle, capi):
+    """isPoseSafe over the adaptor's response (the reference's client side, FisherInfoManager.cpp:39-115, run by the oracle on
+    the points the GPU returned) equals isPoseSafe over the oracle's own landmark query."""
+    rng = np.random.default_rng(77)
+    pts = rng.uniform(-12, 12, size=(30_000, 3)).astype(np.float32)
+    pts[:, 2] = rng.uniform(0, 3, len(pts))
+    oracle.fisher_generate()
+    lut_ctx.set_map_points(pts)
+    poses = _poses(capi, rng, 4, (-8, -8, 8, 8))
+    for i in range(len(poses)):
+        st, got, n = lut_ctx.landmarks_in_view(poses[i])
+        want = oracle.landmarks_in_view(pts, poses[i:i + 1])
+        assert n == len(want) > 0 and np.array_equal(got, want, equal_nan=True)
