@@ -1077,9 +1077,14 @@ __global__ void __launch_bounds__(LIV_THREADS) landmarks_in_view_kernel(const Fi
   for (int k = 0; k < LIV_PER_THREAD; ++k) {
     if (!((m >> k) & 1u)) continue;
     if (dst < capacity) {
-      // vector3fORBToROS of the ORB-frame point is the ROS triple again (signed permutation; see voxel_of_visible_point),
-      // then affinePosToMap * position (rgbd-slam-node.cpp:419-425)
-      V3f pos; pos.v[0] = q[k].x; pos.v[1] = q[k].y; pos.v[2] = q[k].z;
+      // vector3fORBToROS of the ORB-frame point, then affinePosToMap * position (rgbd-slam-node.cpp:419-425).  The signed
+      // permutation is multiplied out as the reference does: for a finite point it returns the ROS triple, for a
+      // non-finite one (which passes the cull: every comparison with NaN is false) 0 * inf turns coordinates into NaN
+      M3f orb2ros;
+      const float b[9] = {0, 0, 1, -1, 0, 0, 0, -1, 0};
+      for (int i = 0; i < 9; ++i) orb2ros.m[i / 3][i % 3] = b[i];
+      V3f Pw; Pw.v[0] = -q[k].y; Pw.v[1] = -q[k].z; Pw.v[2] = q[k].x;
+      const V3f pos = mulv(orb2ros, Pw);
       const V3f lp = mulv(F.Rinv, pos);
       out[3 * (size_t)dst] = lp.v[0] + F.tinv.v[0];
       out[3 * (size_t)dst + 1] = lp.v[1] + F.tinv.v[1];
