@@ -124,7 +124,7 @@ def test_gpu_mark_lethal_matches_oracle(capi, oracle, shape, res):
             np.testing.assert_array_equal(ctx.costmap_copy(), want)
         assert (want == 253).sum() > 100
         # the reference callers: addNewMarkedAreaFOV(x, y, yaw, 3.5) (ExplorationBT.cpp:622), addNewMarkedArea(x, y, 1.7) (:621)
-        areas = [(meta["ox"] + W * res / 2, meta["oy"] + H * res / 2, 3.5, 0.7, 1), (meta["ox"] + 1.0, meta["oy"] + 1.0, 1.7, 0.0, 0)]
+        areas = [(meta["ox"] + W * res / 2, meta["oy"] + H * res / 2, 3.5, 0.7, 1), (meta["ox"] + W * res / 4, meta["oy"] + H * res / 4, 1.7, 0.0, 0)]
         want, n_want = oracle.mark_lethal(want, meta, areas)
         assert ctx.mark_lethal(areas) == n_want == 2
         np.testing.assert_array_equal(ctx.costmap_copy(), want)
