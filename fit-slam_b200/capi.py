@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfitslam_cuda.so")
+LIB_PATH = os.environ.get("FITSLAM_LIB") or os.path.join(_HERE, "libfitslam_cuda.so")
 
 
 class OccupancyParams(C.Structure):

@@ -19,6 +19,8 @@
 // other neighbours; no atomics, no sort) and an order-preserving block scan appends the winners to the queue.
 #include "ctx.h"
 
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -40,13 +42,13 @@ static constexpr uint32_t INNER_BIT = 0x40000000u;
 static constexpr uint32_t TOUCH_BIT = 0x80000000u;
 static constexpr uint32_t MAX_RANK = (1u << 29) - 2;
 static constexpr int BFS_THREADS = 1024;
-static constexpr int OW_THREADS = 1024;      // shared-memory outer wavefront: two threads per queue position, 512 positions per pass
+static constexpr int OW_THREADS = 1024;      // shared-memory outer wavefront: one thread per queue position
 static constexpr int REPLAY_THREADS = 128;
 static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
 // shared-memory wavefronts (the default path; the global-memory kernels below them are the fallback for levels or
 // components that do not fit)
-static constexpr uint32_t OW_QCAP = 8192;    // outer wavefront: widest level the shared-memory queue holds (80 KB; the rest of the SM's 256 KB stays L1)
-static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 4 + 2 * OW_QCAP;
+static constexpr uint32_t OW_QCAP = 8192;    // outer wavefront: widest level the shared-memory queue holds (128 KB; the rest of the SM's 256 KB stays L1)
+static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 8;
 // The outer wavefront publishes its progress every ow_part_levels levels (OW_PARTS - 1 times at most; the last part runs
 // to the end).  After part k the components it touched have their final seed (later touches carry larger keys), so
 // their inner wavefronts replay on side streams, behind a one-thread kernel that polls the flag, while the wavefront
@@ -59,13 +61,6 @@ static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells 
 static constexpr uint32_t IW_BITS_SMALL = 1024, IW_BITS_LARGE = 8192;  // words of the component's mask window held in shared memory
 static constexpr uint32_t iw_smem(uint32_t cells, uint32_t bit_words) { return (2 * 2 * cells + cells + bit_words) * 4; }
 static constexpr uint32_t HKEY_EMPTY = 0xFFFFFFFFu;
-// per-phase cycle counts of the outer wavefront (FITSLAM_PROF prints them): compiled in only with -DFITSLAM_OW_PROF, the
-// four clock reads per pass are not free in a kernel whose passes are a few thousand cycles long
-#ifdef FITSLAM_OW_PROF
-#define OW_CLOCK() clock64()
-#else
-#define OW_CLOCK() 0ll
-#endif
 
 struct Counters {
   uint32_t n_mask;         // cells in the frontier mask
@@ -89,7 +84,7 @@ struct Counters {
   uint32_t coll_fr[OW_PARTS][2];       // frontiers [first, end) of collection k
   uint32_t cell_carry, front_carry;    // running totals of comp_scan_kernel across collections
   uint32_t pad[1];
-  unsigned long long prof[8];  // FITSLAM_PROF: cycles of warp 0 per phase of the outer wavefront
+  unsigned long long prof[8];  // FITSLAM_PROF: [4] passes, [5] cycles of the outer wavefront kernel
 };
 
 struct SearchParams {
@@ -99,12 +94,11 @@ struct SearchParams {
   uint32_t robot_cell;     // getIndex(mx, my) of the robot
   double robot_x, robot_y;
   double dist_limit;       // max_frontier_distance + max_frontier_cluster_size * resolution * 1.414
-  uint32_t near_cells_sq32;  // the same clamped to 32 bits (shared-memory path)
   int64_t near_cells_sq;   // (|dx| + 1)^2 + (|dy| + 1)^2 < near_cells_sq (in cells, from the robot cell) => surely inside dist_limit
+  int64_t far_cells_sq;    // max(|dx| - 1, 0)^2 + max(|dy| - 1, 0)^2 > far_cells_sq => surely outside
   int32_t min_size, max_size;
   uint32_t mask_cap, queue_cap, comp_cap, cell_cap, front_cap;
   uint32_t use_smem;       // 1: shared-memory wavefronts first, global-memory kernels only for what does not fit
-  uint32_t rk_tiles_x;     // 8 x 8 tiles per row of the rank array
   uint32_t ow_wide;        // 1: levels wider than ow_qcap spill to the global queue (maps up to 16384 cells a side)
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
   uint32_t ow_part_levels; // levels per launch of the shared-memory outer wavefront
@@ -117,7 +111,13 @@ struct FrontierState {
   DevBuf<uint32_t> bits;      // frontier mask, wpr words per row
   DevBuf<uint32_t> trav;      // traversable mask (cost < 254), same layout
   DevBuf<uint2> tm;           // {trav word, frontier-mask word} interleaved: one 8-byte load classifies a neighbour
-  DevBuf<uint32_t> rk;        // outer wavefront ranks, rk_index layout; the search disc's tiles are reset before every search
+  DevBuf<uint32_t> ebits;     // expandable cells (traversable and inside the search radius), same layout
+  DevBuf<uint8_t> cls;        // cluster outer wavefront: class byte per cell (same layout), rewritten likewise
+  int ow_cluster = -1;        // CTAs per cluster of ow_cluster_kernel (0: not available, use the single-CTA kernel); -1: not probed yet
+  uint32_t ow_cluster_min = 1500;  // ... used when the last search's widest level had at least this many cells (FITSLAM_OW_CLUSTER_MIN)
+  DevBuf<uint16_t> rk;        // outer wavefront: class of a cell, then its position inside its level (ow_rk_* layout); the search disc's
+                              // tiles are rewritten before every search
+  uint64_t ow_cells = 0;      // padded cells for which rk is initialised
   DevBuf<uint32_t> mcell;     // mask-cell list (unordered)
   DevBuf<uint32_t> parent;    // union-find over list indices
   DevBuf<uint32_t> rkey;      // per root: min touch key of the component
@@ -159,7 +159,7 @@ static FrontierState *fr_state(fitslam_ctx *c) {
 void destroy_frontier_state(fitslam_ctx *c) {
   if (!c->fs) return;
   FrontierState *s = c->fs;
-  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->rk.release(); s->mcell.release();
+  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->rk.release(); s->cls.release(); s->ebits.release(); s->mcell.release();
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
   s->rbox.release(); s->cbox.release(); s->obox.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
@@ -201,11 +201,31 @@ __device__ __forceinline__ bool nbr_of(uint32_t mx, uint32_t my, uint32_t W, uin
 }
 
 // ------------------------------------------------------------------------------------------------ K1: mask
+// Which of the 32 cells (mx0 .. mx0 + 31, my) would be enqueued by the outer wavefront (FrontierSearch.cpp:72-76):
+// distance from the robot to the cell centre < max_frontier_distance + max_frontier_cluster_size * resolution * 1.414.
+// The exact double expression runs only for words that straddle the rim.
+__device__ __forceinline__ uint32_t in_radius_word(const SearchParams &S, uint32_t mx0, uint32_t my) {
+  const int64_t rx = S.robot_cell % S.map.W, ry = S.robot_cell / S.map.W;
+  const int64_t dy = llabs((int64_t)my - ry);
+  const int64_t da = llabs((int64_t)mx0 - rx), db = llabs((int64_t)mx0 + 31 - rx);
+  const int64_t dfar = max(da, db), dnear = ((int64_t)mx0 <= rx && rx <= (int64_t)mx0 + 31) ? 0 : min(da, db);
+  if ((dfar + 1) * (dfar + 1) + (dy + 1) * (dy + 1) < S.near_cells_sq) return 0xFFFFFFFFu;
+  const int64_t nx = max(dnear - 1, (int64_t)0), ny = max(dy - 1, (int64_t)0);
+  if (nx * nx + ny * ny > S.far_cells_sq) return 0u;
+  uint32_t w = 0u;
+  const double ddy = S.robot_y - (S.map.oy + (my + 0.5) * S.map.res);
+  for (int i = 0; i < 32; ++i) {
+    const double ddx = S.robot_x - (S.map.ox + ((mx0 + i) + 0.5) * S.map.res);
+    if (sqrt(ddx * ddx + ddy * ddy) < S.dist_limit) w |= 1u << i;
+  }
+  return w;
+}
+
 // isNewFrontierCell on the static map (DEP/src/FrontierSearch.cpp:218-249, predicates FrontierSearch.hpp:129-142):
 // cost == 255, no 4-neighbour with lethal_threshold <= cost < 255, at least one 4-neighbour with cost < lethal_threshold.
 // One thread per 32-cell mask word; rows are read as 16-byte vectors (pitch is a multiple of 16).
 __global__ void __launch_bounds__(256) mask_kernel(const SearchParams S, uint32_t *__restrict__ bits,
-                                                   uint32_t *__restrict__ trav, uint2 *__restrict__ tm,
+                                                   uint32_t *__restrict__ trav, uint32_t *__restrict__ ebits, uint2 *__restrict__ tm,
                                                    uint32_t *__restrict__ slot, uint32_t *__restrict__ mcell,
                                                    Counters *__restrict__ cnt) {
   const uint32_t W = S.map.W, H = S.map.H, pitch = S.map.pitch;
@@ -262,6 +282,7 @@ __global__ void __launch_bounds__(256) mask_kernel(const SearchParams S, uint32_
     }
     bits[gid] = word;
     trav[gid] = tword;
+    ebits[gid] = tword ? (tword & in_radius_word(S, mx0, my)) : 0u;
     tm[((size_t)(my >> 3) * S.wpr + (mx0 >> 5)) * 8u + (my & 7u)] = make_uint2(tword, word);  // tm_index layout
   }
   // append the set cells to the list: one atomicAdd per warp
@@ -620,217 +641,199 @@ __device__ __forceinline__ uint32_t hslot(uint32_t cell, uint32_t bits) { return
 __host__ __device__ __forceinline__ size_t tm_index(uint32_t wx, uint32_t y, uint32_t wpr) {
   return ((size_t)(y >> 3) * wpr + wx) * 8u + (y & 7u);
 }
-// dequeue ranks of the outer wavefront, one word per cell in 8 x 8 tiles (two 128-byte lines per tile): the ranks a
-// level reads lie within 3 cells of the cells it dequeues, so they share a handful of lines that sit in L1
-__host__ __device__ __forceinline__ uint32_t rk_index(uint32_t x, uint32_t y, uint32_t tiles_x) {
-  return ((y >> 3) * tiles_x + (x >> 3)) * 64u + ((y & 7u) << 3) + (x & 7u);  // < 2^29 + rounding: the map has < 2^29 cells
+// ---- the outer wavefront, default path ---------------------------------------------------------------------------
+// Same decision rule as rank_bfs_kernel above (a dequeued cell p visits a traversable, unvisited neighbour c iff no
+// other neighbour of c was dequeued before p in this level), with everything that does not depend on the order moved
+// out of the loop, and the loop cut down to what the profile says bounds it: instructions per level (one SM issues
+// about two warp instructions per cycle on this integer code) and distinct L1 lines per load (profiles/README.md).
+//   * the state is 2 bytes per cell: ow_prep_kernel (all SMs, once per search) writes the cell's class, the wavefront
+//     replaces it with the cell's position inside its level when the cell is enqueued.
+//       OW_OPEN    expandable, not visited: inside the map, cost < 254, inside the search radius (FrontierSearch.cpp:67,74)
+//       OW_MASK    frontier-mask cell (isNewFrontierCell, the `else if` branch)
+//       OW_BLOCKED anything else
+//       < OW_MAX_LEVEL: position in its level
+//     The loop needs no map bytes, no bounds tests, no radius arithmetic and no visited flags: a dequeued cell reads its
+//     four neighbours; OPEN ones are its candidates, MASK ones get its touch key.
+//   * a cell c that is still OPEN while level d is expanded has no neighbour on a level below d (it would have visited
+//     c), and the 4-connected grid is bipartite, so any neighbour of c with a position IS a level-d cell: no level
+//     stamps.  A thread reads the positions of the 8 cells at distance 2 (those next to a candidate; each diagonal serves
+//     two candidates) and its cell visits c iff none of c's three other neighbours has a smaller position.
+//   * the array is tiled (8 x 8 cells = one 128-byte line) and padded by OW_PAD cells of BLOCKED; a level's cells lie on
+//     diagonals, so a warp's load touches ~5 lines instead of 32.  The index separates into f(x) + g(y): a queue entry
+//     carries the cell's index, and a step to a neighbour is an add plus a select for the tile edge.
+// One CTA: every position it reads was stored by the same CTA before an earlier barrier, so plain L1-cached loads are
+// coherent.  Two barriers per level (one more per 1024 positions beyond the first).
+static constexpr uint32_t OW_PAD = 8;
+static constexpr uint32_t OW_OPEN = 0xFFFFu, OW_MASK = 0xFFFEu, OW_BLOCKED = 0xFFFDu;
+static constexpr uint32_t OW_MAX_LEVEL = 0xFF00u;  // widest level whose positions stay below the class values
+
+struct OwLayout {
+  uint32_t txr;            // tiles (8 x 8 cells) per tile row
+  uint32_t rk_yt;          // txr * 64 - 64: see ow_rk_fy
+  uint32_t Wp, Hp;         // padded size in cells
+};
+// idx = fx(X) + fy(Y) with X = x + OW_PAD, Y = y + OW_PAD
+__host__ __device__ __forceinline__ uint32_t ow_rk_fx(uint32_t X) { return X + (X >> 3) * 56u; }                   // (X >> 3) * 64 + (X & 7)
+__host__ __device__ __forceinline__ uint32_t ow_rk_fy(uint32_t Y, uint32_t yt) { return Y * 8u + (Y >> 3) * yt; }    // (Y >> 3) * txr * 64 + (Y & 7) * 8
+static OwLayout ow_layout(uint32_t W, uint32_t H) {
+  OwLayout L;
+  L.Wp = (W + 2u * OW_PAD + 15u) / 16u * 16u;
+  L.Hp = (H + 2u * OW_PAD + 7u) / 8u * 8u;
+  L.txr = L.Wp / 8u;
+  L.rk_yt = L.txr * 64u - 64u;
+  return L;
 }
 
-// The outer wavefront, default path.  Same decision rule as rank_bfs_kernel above (a dequeued cell p visits a
-// traversable, unvisited neighbour c iff no other neighbour of c was dequeued before p in this level), with the work
-// per level cut to what that rule needs:
-//   * the level's cells (packed y << 16 | x) live in a shared-memory queue, with the directions of their visited
-//     neighbours next to them.  The 4-connected grid is bipartite, so a neighbour of a level-d cell is on level d-1 or d+1;
-//     the level-(d-1) neighbours of a cell are exactly the cells that competed for it, which its winner saw while
-//     deciding.  So "visited_flag[nbr]" is a 4-bit mask carried with the queue entry: no visited array, no load.
-//   * the read-only class bits come through L1, three 8-byte loads per cell (rows above / at / below, tm_index layout).
-//   * only the ranks of a candidate's three other neighbours are read from global memory (claim[], L2): about four 4-byte
-//     loads per dequeued cell, all independent, against 28 for the kernel above.  A shared-memory bid table with atomicMin
-//     was tried first and lost: shared-memory atomics retire at about 2 cycles per LANE on this part, so three atomics
-//     per bid cost more than the L2 round trip they avoided (profiles/README.md, v4/v5).
-//   * a cell beyond the search radius needs no state at all (testing it again gives the same answer).
-//   * two threads share a queue position (one per axis), so the dependent instruction chain of a level, which is what
-//     bounds it (clock64 breakdown in profiles/README.md), is half as long, thread order is still bid order, and the
-//     winner counts are 0..2 per thread: the block scan is two ballots per warp.
-// Two barriers per pass.  A level wider than ow_qcap sets ow_fallback, and the host repeats the search with the
-// instantiation that spills such levels to a global-memory queue (or, on maps too large for it, with rank_bfs_kernel).
+// 32 bits of row y of a 1-bit-per-cell array, columns xs .. xs + 31 (xs >= -32); cells outside the map read 0
+__device__ __forceinline__ uint32_t row_bits(const uint32_t *__restrict__ a, uint32_t wpr, uint32_t H, int y, int xs) {
+  if (y < 0 || y >= (int)H) return 0u;
+  const int w0 = xs >> 5;
+  const uint32_t *row = a + (size_t)y * wpr;
+  const uint32_t lo = (w0 >= 0 && w0 < (int)wpr) ? __ldg(row + w0) : 0u;
+  const uint32_t hi = (w0 + 1 >= 0 && w0 + 1 < (int)wpr) ? __ldg(row + w0 + 1) : 0u;
+  return __funnelshift_r(lo, hi, (uint32_t)xs & 31u);
+}
+
+// Classes for the tiles of the search disc's bounding box (pairs of 8 x 8-cell tiles [2 * tx0, 2 * (tx0 + ntx)) x
+// [ty0, ty0 + nty), padded coordinates).  One thread per 16 cells of a row: two 16-byte stores.  The wavefront never
+// leaves the box: cells are enqueued only inside the disc.
+__global__ void __launch_bounds__(256)
+ow_prep_kernel(const SearchParams S, const OwLayout L, const uint32_t *__restrict__ ebits, const uint32_t *__restrict__ mbits,
+               uint16_t *__restrict__ rk, uint32_t tx0, uint32_t ty0, uint32_t ntx, uint32_t nty) {
+  const uint64_t n = (uint64_t)ntx * nty * 8u;
+  const uint32_t H = S.map.H;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = (uint32_t)(i / ntx), bx = tx0 + (uint32_t)(i - (uint64_t)r * ntx);
+    const uint32_t Y = ty0 * 8u + r, X0 = bx * 16u;
+    const int y = (int)Y - (int)OW_PAD, xs = (int)X0 - (int)OW_PAD;  // bit j of the row words below = column xs + j
+    const uint32_t em = row_bits(ebits, S.wpr, H, y, xs), mm = row_bits(mbits, S.wpr, H, y, xs);  // (0 outside the map)
+    uint32_t out[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t a = ((em >> (2 * k)) & 1u) ? OW_OPEN : (((mm >> (2 * k)) & 1u) ? OW_MASK : OW_BLOCKED);
+      const uint32_t b = ((em >> (2 * k + 1)) & 1u) ? OW_OPEN : (((mm >> (2 * k + 1)) & 1u) ? OW_MASK : OW_BLOCKED);
+      out[k] = a | (b << 16);
+    }
+    uint16_t *t = rk + ((size_t)(Y >> 3) * L.txr + 2u * bx) * 64u + (Y & 7u) * 8u;  // first of the two tiles' rows
+    *reinterpret_cast<uint4 *>(t) = make_uint4(out[0], out[1], out[2], out[3]);
+    *reinterpret_cast<uint4 *>(t + 64) = make_uint4(out[4], out[5], out[6], out[7]);
+  }
+}
+
 struct OwQueues {
-  // g0 / g1: the same queues in global memory, entries (mask << 28 | y << 14 | x), used while a level is wider than the
-  // shared-memory queue (maps up to 16384 cells a side): read when n > ow_qcap, written when the next level could be
-  uint32_t *g0, *g1;
+  // entries: .x = the cell's index in the state array, .y = x | y << 14
+  uint2 *q;        // shared memory: two queues of OW_QCAP entries, this level's (`cur`) and the next one's
+  uint2 *g;        // the same in global memory (two of `gcap` entries), used while a level is wider than the shared-memory queue
+  uint32_t gcap;
   bool from_global, to_global;
-  uint32_t *q0, *q1;
-  uint8_t *qm0, *qm1;
 };
 
-// rank of a cell.  Plain (L1-cached) loads: this kernel is one CTA, every rank it reads was stored by the same CTA
-// before an earlier barrier, so the SM's own write-through L1 is coherent for it.
-template <bool INTERIOR>
-__device__ __forceinline__ uint32_t ow_rank(const uint32_t *rk, uint32_t tiles_x, uint32_t W, uint32_t H, int x, int y, bool want) {
-  if (!want) return KEY_INF;
-  if (!INTERIOR && (x < 0 || y < 0 || x >= (int)W || y >= (int)H)) return KEY_INF;
-  return rk[rk_index((uint32_t)x, (uint32_t)y, tiles_x)];
-}
-__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void ow_bar() { asm volatile("bar.sync 0;" ::: "memory"); }
+#ifdef FITSLAM_OW_PROF
+// cycle stamps of thread 0 (warp 0 works in every pass); `dep` orders the stamp behind the value it times
+__device__ __forceinline__ uint32_t ow_clock(uint32_t dep) { uint32_t t; asm volatile("mov.u32 %0, %%clock;" : "=r"(t) : "r"(dep) : "memory"); return t; }
+#define OW_STAMP(k, dep) do { if (threadIdx.x == 0) { const uint32_t _t = ow_clock(dep); pf.acc[k] += _t - pf.last; pf.last = _t; } } while (0)
+#else
+#define OW_STAMP(k, dep) do { } while (0)
+#endif
+struct OwProf { uint32_t last; uint32_t acc[8]; };
 
-// a winner joins the next level: rank and queue entry.  (Prefetching what the next level will read around it was tried
-// twice, eight lines per winner and one line per winner that crosses into a new line: both made the kernel slower.)
+// one pass over up to OW_THREADS queue positions starting at `tile`; returns the number of cells it appended (valid in
+// the warps that had positions to work on: warp 0 always has).  Warps whose positions all lie beyond the level only
+// take part in the barrier: with ~400 cells per level two thirds of the warps are idle, and the instructions they would
+// spend on an empty scan come out of the issue slots of the busy ones.
+// WIDE: the level or its successor may not fit the shared-memory queue (a separate instantiation keeps the common
+// narrow pass free of those branches).
 template <bool WIDE>
-__device__ __forceinline__ void ow_append(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *rk, const OwQueues &Q,
-                                          uint32_t x, uint32_t y, uint32_t dm, uint32_t dst, uint32_t next_base) {
-  rk[rk_index(x, y, S.rk_tiles_x)] = next_base + dst;
-  if (dst < S.ow_qcap) {
-    Q.q1[dst] = (y << 16) | x;
-    Q.qm1[dst] = (uint8_t)dm;
-  }
-  if (WIDE && Q.to_global) Q.g1[dst] = (dm << 28) | (y << 14) | x;
-}
-
-// one pass over up to OW_THREADS / 2 queue positions starting at `tile`: thread 2i + h takes cell i's neighbours
-// {left, right} (h = 0) or {up, down} (h = 1), so thread order is bid order.  WIDE: the level or its successor may not fit
-// the shared-memory queue (a separate instantiation keeps the common narrow pass free of those branches)
-template <bool WIDE>
-__device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *rk,
-                                           const OwQueues &Q, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
-                                           uint32_t rx, uint32_t ry, uint32_t *ws, unsigned long long *prof) {
-  const uint32_t W = S.map.W, H = S.map.H;
-  const uint32_t next_base = base + n;
-  const long long c0 = OW_CLOCK();
+__device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const OwLayout &L, uint16_t *rk, uint32_t *claim, const OwQueues &Q,
+                                           uint32_t cur, uint32_t safe, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
+                                           uint32_t *ws, OwProf &pf) {
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-  const uint32_t pos = tile + (threadIdx.x >> 1), h = threadIdx.x & 1u;
-  int ax = 0, ay = 0, bx = 0, by = 0;
-  bool a_win = false, b_win = false;
-  uint32_t a_dm = 0, b_dm = 0;
-  long long c1 = c0;
-  // a warp whose 16 positions all lie beyond the level skips straight to the scan (narrow levels leave most warps idle,
-  // and idle warps would otherwise spend issue slots the busy ones need: the pass is issue-bound)
-  if (tile + (wid << 4) < n) {
-  const bool on = pos < n;
-  uint32_t cell = 0u, seen = 15u;
-  if (on) {
-    if (WIDE && Q.from_global) {
-      const uint32_t e = ld_cg(Q.g0 + pos);
-      cell = ((e >> 14) & 0x3FFFu) << 16 | (e & 0x3FFFu);
-      seen = e >> 28;
-    } else {
-      cell = Q.q0[pos];
-      seen = Q.qm0[pos];
-    }
+  if (tile + (wid << 5) >= n) {  // warp-uniform
+    ow_bar();
+    return 0u;
   }
-  const int mx = (int)(cell & 0xFFFFu), my = (int)(cell >> 16);
-  const uint32_t rank = base + pos;
-  // the two neighbours of this thread: a = slot 2h, b = slot 2h + 1
-  ax = h ? mx : mx - 1; ay = h ? my - 1 : my; bx = h ? mx : mx + 1; by = h ? my + 1 : my;
-  const bool a_in = on && ax >= 0 && ay >= 0, b_in = on && bx < (int)W && by < (int)H;
-  const uint2 z = make_uint2(0, 0);
-  const uint2 wa = a_in ? __ldg(tm + tm_index((uint32_t)ax >> 5, (uint32_t)ay, S.wpr)) : z;
-  const uint2 wb = b_in ? __ldg(tm + tm_index((uint32_t)bx >> 5, (uint32_t)by, S.wpr)) : z;
-  bool a_tr = ((wa.x >> (ax & 31)) & 1u) && !((seen >> (2 * h)) & 1u);      // traversable and not on level d-1
-  bool b_tr = ((wb.x >> (bx & 31)) & 1u) && !((seen >> (2 * h + 1)) & 1u);
-  const bool a_mk = (wa.y >> (ax & 31)) & 1u, b_mk = (wb.y >> (bx & 31)) & 1u;
-  // enqueued only inside the search radius (FrontierSearch.cpp:72-76); the exact test runs only near the rim
-  {
-    // (|dx| + 1)^2 + (|dy| + 1)^2 fits 32 bits: the shared-memory path requires W, H <= 32768
-    const uint32_t dxa = (uint32_t)abs(ax - (int)rx) + 1u, dya = (uint32_t)abs(ay - (int)ry) + 1u;
-    const uint32_t dxb = (uint32_t)abs(bx - (int)rx) + 1u, dyb = (uint32_t)abs(by - (int)ry) + 1u;
-    if (a_tr && dxa * dxa + dya * dya >= S.near_cells_sq32) {
-      const double ddx = S.robot_x - (S.map.ox + (ax + 0.5) * S.map.res), ddy = S.robot_y - (S.map.oy + (ay + 0.5) * S.map.res);
-      if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) a_tr = false;
-    }
-    if (b_tr && dxb * dxb + dyb * dyb >= S.near_cells_sq32) {
-      const double ddx = S.robot_x - (S.map.ox + (bx + 0.5) * S.map.res), ddy = S.robot_y - (S.map.oy + (by + 0.5) * S.map.res);
-      if (!(sqrt(ddx * ddx + ddy * ddy) < S.dist_limit)) b_tr = false;
-    }
+  const uint32_t pos = tile + threadIdx.x;
+  uint2 e = make_uint2(safe, 0u);  // lanes beyond the level look at a padding cell: BLOCKED neighbours, nothing to do
+  if (pos < n) e = (WIDE && Q.from_global) ? __ldcg(Q.g + cur * Q.gcap + pos) : Q.q[cur * OW_QCAP + pos];
+  const uint32_t i = e.x;
+  OW_STAMP(0, i);
+  // index steps to the cells at distance 1 and 2: the index separates into f(x) + g(y), so a step along x costs a fixed
+  // amount plus 56 when it crosses a tile edge, a step along y 8 plus (tile row - 64) when it does
+  const uint32_t tx = i & 7u, ty = i & 56u;
+  const uint32_t xb = tx < 1u ? 57u : 1u, xd = tx > 6u ? 57u : 1u;
+  const uint32_t yb = (ty < 8u ? L.rk_yt : 0u) + 8u, yd = (ty > 48u ? L.rk_yt : 0u) + 8u;
+  const uint32_t i0 = i - xb, i1 = i + xd, i2 = i - yb, i3 = i + yd;  // the four neighbours: -x, +x, -y, +y
+  const uint32_t v0 = rk[i0], v1 = rk[i1], v2 = rk[i2], v3 = rk[i3];
+  const uint32_t xa = tx < 2u ? 58u : 2u, xe = tx > 5u ? 58u : 2u;
+  const uint32_t ya = (ty < 16u ? L.rk_yt : 0u) + 16u, ye = (ty > 40u ? L.rk_yt : 0u) + 16u;
+  const bool c0 = v0 == OW_OPEN, c1 = v1 == OW_OPEN, c2 = v2 == OW_OPEN, c3 = v3 == OW_OPEN;
+  OW_STAMP(1, (uint32_t)c0 + c1 + c2 + c3);
+  // positions of the cells at distance 2 that are next to a candidate (all loads independent); a cell without a position
+  // reads as a class, which is above every position
+  const uint32_t l2 = c0 ? (uint32_t)rk[i - xa] : OW_OPEN, r2 = c1 ? (uint32_t)rk[i + xe] : OW_OPEN;
+  const uint32_t u2 = c2 ? (uint32_t)rk[i - ya] : OW_OPEN, d2 = c3 ? (uint32_t)rk[i + ye] : OW_OPEN;
+  const uint32_t ul = (c0 || c2) ? (uint32_t)rk[i0 - yb] : OW_OPEN, ur = (c1 || c2) ? (uint32_t)rk[i1 - yb] : OW_OPEN;
+  const uint32_t dl = (c0 || c3) ? (uint32_t)rk[i0 + yd] : OW_OPEN, dr = (c1 || c3) ? (uint32_t)rk[i1 + yd] : OW_OPEN;
+  // frontier-mask neighbours record the first touch (isNewFrontierCell branch, FrontierSearch.cpp:78-81)
+  if (v0 == OW_MASK || v1 == OW_MASK || v2 == OW_MASK || v3 == OW_MASK) {
+    const uint32_t key = TOUCH_BIT | ((base + pos) << 2);
+    uint32_t *at = claim + (size_t)(e.y >> 14) * S.map.W + (e.y & 0x3FFFu);
+    if (v0 == OW_MASK) atomicMin(at - 1, key);
+    if (v1 == OW_MASK) atomicMin(at + 1, key | 1u);
+    if (v2 == OW_MASK) atomicMin(at - S.map.W, key | 2u);
+    if (v3 == OW_MASK) atomicMin(at + S.map.W, key | 3u);
   }
-  c1 = OW_CLOCK();
-  // ranks of each candidate's three other neighbours (front, and the two sides), all loads independent.
-  // directions: 0 = -x, 1 = +x, 2 = -y, 3 = +y; seen from the candidate, this cell lies in direction (slot ^ 1)
-  const int fx = h ? 0 : 1, fy = h ? 1 : 0;  // unit step of this thread's axis
-  const int px = h ? 1 : 0, py = h ? 0 : 1;  // the perpendicular axis
-  uint32_t ra[3], rb[3];
-  const bool interior = mx >= 2 && my >= 2 && mx + 2 < (int)W && my + 2 < (int)H;
-  if (interior) {
-    ra[0] = ow_rank<true>(rk, S.rk_tiles_x, W, H, ax - fx, ay - fy, a_tr);
-    ra[1] = ow_rank<true>(rk, S.rk_tiles_x, W, H, ax - px, ay - py, a_tr);
-    ra[2] = ow_rank<true>(rk, S.rk_tiles_x, W, H, ax + px, ay + py, a_tr);
-    rb[0] = ow_rank<true>(rk, S.rk_tiles_x, W, H, bx + fx, by + fy, b_tr);
-    rb[1] = ow_rank<true>(rk, S.rk_tiles_x, W, H, bx - px, by - py, b_tr);
-    rb[2] = ow_rank<true>(rk, S.rk_tiles_x, W, H, bx + px, by + py, b_tr);
-  } else {
-    ra[0] = ow_rank<false>(rk, S.rk_tiles_x, W, H, ax - fx, ay - fy, a_tr);
-    ra[1] = ow_rank<false>(rk, S.rk_tiles_x, W, H, ax - px, ay - py, a_tr);
-    ra[2] = ow_rank<false>(rk, S.rk_tiles_x, W, H, ax + px, ay + py, a_tr);
-    rb[0] = ow_rank<false>(rk, S.rk_tiles_x, W, H, bx + fx, by + fy, b_tr);
-    rb[1] = ow_rank<false>(rk, S.rk_tiles_x, W, H, bx - px, by - py, b_tr);
-    rb[2] = ow_rank<false>(rk, S.rk_tiles_x, W, H, bx + px, by + py, b_tr);
-  }
-  // direction bits, seen from the candidate: front of a = slot 2h (further along -axis), of b = slot 2h + 1;
-  // the sides are the two slots of the other axis (minus first)
-  const uint32_t side_lo = 1u << (2 * (h ^ 1u)), side_hi = 2u << (2 * (h ^ 1u));
-  a_win = a_tr; b_win = b_tr;
-  a_dm = 1u << (2 * h + 1); b_dm = 1u << (2 * h);  // this cell, seen from a / from b
-  {
-    const uint32_t dbit[3] = {1u << (2 * h), side_lo, side_hi};
-#pragma unroll
-    for (int j = 0; j < 3; ++j)
-      if (ra[j] >= base && ra[j] < next_base) {  // a level-d neighbour of the candidate: it competes for it
-        a_dm |= dbit[j];
-        if (ra[j] < rank) a_win = false;          // dequeued before this cell: it visited the candidate first
-      }
-  }
-  {
-    const uint32_t dbit[3] = {1u << (2 * h + 1), side_lo, side_hi};
-#pragma unroll
-    for (int j = 0; j < 3; ++j)
-      if (rb[j] >= base && rb[j] < next_base) {
-        b_dm |= dbit[j];
-        if (rb[j] < rank) b_win = false;
-      }
-  }
-  // frontier-mask neighbours record the first touch (isNewFrontierCell branch)
-  if (a_in && !((wa.x >> (ax & 31)) & 1u) && a_mk) atomicMin(claim + (size_t)ay * W + ax, TOUCH_BIT | (rank * 4u + 2u * h));
-  if (b_in && !((wb.x >> (bx & 31)) & 1u) && b_mk) atomicMin(claim + (size_t)by * W + bx, TOUCH_BIT | (rank * 4u + 2u * h + 1u));
-  }
-  const long long c2 = OW_CLOCK();
-  // block-wide exclusive scan of the winner counts (0..2 per thread): two ballots per warp, one barrier
-  const uint32_t n_win = (a_win ? 1u : 0u) + (b_win ? 1u : 0u);
-  const uint32_t b0 = __ballot_sync(0xffffffffu, n_win & 1u), b1 = __ballot_sync(0xffffffffu, n_win >> 1);
+  // a level-d neighbour of the candidate that was dequeued before this cell visited it first
+  const bool w0 = c0 && min(l2, min(ul, dl)) > pos, w1 = c1 && min(r2, min(ur, dr)) > pos;
+  const bool w2 = c2 && min(u2, min(ul, ur)) > pos, w3 = c3 && min(d2, min(dl, dr)) > pos;
+  OW_STAMP(2, (uint32_t)w0 + w1 + w2 + w3);
+  // block-wide exclusive scan of the winner counts (0..4 per thread): three ballots per warp, one barrier
+  const uint32_t nw = (uint32_t)w0 + (uint32_t)w1 + (uint32_t)w2 + (uint32_t)w3;
+  const uint32_t b0 = __ballot_sync(0xffffffffu, nw & 1u), b1 = __ballot_sync(0xffffffffu, nw & 2u), b2 = __ballot_sync(0xffffffffu, nw & 4u);
   const uint32_t lt = (1u << lane) - 1u;
-  const uint32_t excl = __popc(b0 & lt) + 2u * __popc(b1 & lt);
-  if (lane == 0) ws[wid] = __popc(b0) + 2u * __popc(b1);
-  __syncthreads();
-  // every warp needs the block total and the sum of the warps before it: two warp reductions (REDUX) over the 32 warp
-  // totals instead of a shuffle scan
-  const uint32_t wv = lane < OW_THREADS / 32 ? ws[lane] : 0u;
+  const uint32_t excl = __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt);
+  if (lane == 0) ws[wid] = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
+  OW_STAMP(3, excl);
+  ow_bar();
+  OW_STAMP(4, excl);
+  const uint32_t aw = min((n - tile + 31u) >> 5, (uint32_t)(OW_THREADS / 32));  // warps with positions in this pass
+  const uint32_t wv = lane < aw ? ws[lane] : 0u;
   const uint32_t total = __reduce_add_sync(0xffffffffu, wv);
   const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
   uint32_t dst = n_next + wbase + excl;
-  const long long c3 = OW_CLOCK();
   // append the winners in (position, slot) order
-  if (a_win) {
-    ow_append<WIDE>(S, tm, rk, Q, (uint32_t)ax, (uint32_t)ay, a_dm, dst, next_base);
+  auto append = [&](uint32_t ci, uint32_t xy) {
+    rk[ci] = (uint16_t)dst;
+    const uint2 entry = make_uint2(ci, xy);
+    if (dst < S.ow_qcap) Q.q[(cur ^ 1u) * OW_QCAP + dst] = entry;
+    if (WIDE && Q.to_global) Q.g[(cur ^ 1u) * Q.gcap + dst] = entry;
     ++dst;
-  }
-  if (b_win) ow_append<WIDE>(S, tm, rk, Q, (uint32_t)bx, (uint32_t)by, b_dm, dst, next_base);
-  if (threadIdx.x == 0) {
-    const long long c4 = OW_CLOCK();
-    prof[0] += c1 - c0; prof[1] += c2 - c1; prof[2] += c3 - c2; prof[3] += c4 - c3; prof[4] += 1;
-  }
+  };
+  if (w0) append(i0, e.y - 1u);
+  if (w1) append(i1, e.y + 1u);
+  if (w2) append(i2, e.y - (1u << 14));
+  if (w3) append(i3, e.y + (1u << 14));
+  OW_STAMP(5, dst);
   return total;
 }
 
 // WIDE = false: every level fits the shared-memory queue; a level that does not ends the kernel with ow_fallback = 2 (the
 // host repeats the search with the WIDE = true instantiation, which spills such levels to a global-memory queue, and
-// starts with that one from then on while the map keeps producing them) or 1 (maps above 16384 cells a side:
-// rank_bfs_kernel).  Two kernels rather than one: carrying both pass bodies made the common narrow pass 7 % slower.
+// starts with that one from then on while the map keeps producing them) or 1 (maps above 16384 cells a side or levels
+// above OW_MAX_LEVEL cells: rank_bfs_kernel).
 template <bool WIDE>
 __global__ void __launch_bounds__(OW_THREADS, 1)
-rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_t *claim, uint32_t *queue, uint32_t *rk,
-                     Counters *cnt, uint32_t n_parts) {
-  extern __shared__ uint32_t ow_sh[];
+ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim, uint32_t *queue, Counters *cnt, uint32_t n_parts) {
+  extern __shared__ uint2 ow_sh[];
   __shared__ uint32_t sh48[48];
-  __shared__ uint32_t s_start;
+  __shared__ uint32_t s_start, s_n;
   __shared__ uint32_t s_wsum[64];
-  __shared__ unsigned long long s_prof[8];
-  if (threadIdx.x < 8) s_prof[threadIdx.x] = 0;
   const long long k0 = clock64();
   OwQueues Q;
-  Q.q0 = ow_sh;
-  Q.q1 = ow_sh + OW_QCAP;
-  Q.qm0 = reinterpret_cast<uint8_t *>(ow_sh + 2 * OW_QCAP);
-  Q.qm1 = Q.qm0 + OW_QCAP;
-  Q.g0 = queue;
-  Q.g1 = queue + S.queue_cap / 2;
+  Q.q = ow_sh;
+  Q.g = reinterpret_cast<uint2 *>(queue);
+  Q.gcap = S.queue_cap / 4;
   Q.from_global = false;
   Q.to_global = false;
   // parts [from, n_parts - 1) are complete with `end` cells dequeued: every touch key below 4 * end is in memory (the
@@ -844,7 +847,7 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
   if (cnt->overflow) { publish(0, 0); return; }
   const uint32_t W = S.map.W;
   const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
-  uint32_t base = 0, n = 1, levels = 0, scans = 0, part = 0, widest = 1;
+  uint32_t base = 0, n = 1, levels = 0, scans = 0, part = 0, widest = 1, cur = 0;
   if (threadIdx.x == 0) s_start = S.robot_cell;
   __syncthreads();
   if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
@@ -852,44 +855,53 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     __syncthreads();
   }
   const uint32_t start = s_start;
+  const uint32_t safe = ow_rk_fx(4u) + ow_rk_fy(4u, L.rk_yt);  // a padding cell with padding all around it
   if (threadIdx.x == 0) {
     cnt->start_cell = start;
     const uint32_t sy = start / W, sx = start - sy * W;
-    Q.q0[0] = (sy << 16) | sx;
-    Q.qm0[0] = 0;
-    rk[rk_index(sx, sy, S.rk_tiles_x)] = 0;
+    const uint32_t si = ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD, L.rk_yt);
+    Q.q[0] = make_uint2(si, sx | (sy << 14));
+    rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56), whatever its class
   }
   __syncthreads();
+  uint32_t next_part_level = S.ow_part_levels;
+  OwProf pf;
+#ifdef FITSLAM_OW_PROF
+  for (int k = 0; k < 8; ++k) pf.acc[k] = 0;
+  pf.last = ow_clock(0);
+#endif
   while (n > 0) {
+    OW_STAMP(7, n);
     uint32_t n_next = 0;
-    for (uint32_t tile = 0; tile < n;) {
-      uint32_t *ws = s_wsum + (scans & 1u) * 32u;
+    for (uint32_t tile = 0; tile < n; tile += OW_THREADS) {
+      n_next += ow_pass<WIDE>(S, L, rk, claim, Q, cur, safe, tile, n, base, n_next, s_wsum + (scans & 1u) * 32u, pf);
       ++scans;
-      n_next += ow_pass<WIDE>(S, tm, claim, rk, Q, tile, n, base, n_next, rx, ry, ws, s_prof);
-      tile += OW_THREADS / 2;
     }
-    __syncthreads();
+    if (threadIdx.x == 0) s_n = n_next;  // warp 0 works in every pass: its total is the level's
+    ow_bar();
+    OW_STAMP(6, n_next);
     base += n;
-    n = n_next;
+    n = s_n;
     ++levels;
+    cur ^= 1u;
     widest = max(widest, n);
-    if (n > S.ow_qcap && !WIDE) {  // uniform (a block-wide total): the next kernel reruns the search (claim[] holds touch
-      if (threadIdx.x == 0) cnt->ow_fallback = S.ow_wide ? 2u : 1u;  // keys only, and it would write the same ones)
+    if ((n > S.ow_qcap && !WIDE) || n > OW_MAX_LEVEL) {  // uniform: the next kernel reruns the search (claim[] holds touch
+      if (threadIdx.x == 0) cnt->ow_fallback = (S.ow_wide && n <= OW_MAX_LEVEL) ? 2u : 1u;  // keys only, and it would write the same ones)
       publish(part, base);  // every level below `base` ranks is complete: those touches stand
       return;
     }
-    uint32_t *tq = Q.q0; Q.q0 = Q.q1; Q.q1 = tq;
-    uint8_t *tb = Q.qm0; Q.qm0 = Q.qm1; Q.qm1 = tb;
-    tq = Q.g0; Q.g0 = Q.g1; Q.g1 = tq;
-    Q.from_global = n > S.ow_qcap;                     // this level did not fit the shared queue: read it from global memory
-    Q.to_global = S.ow_wide && 3u * n + 4u > S.ow_qcap;  // a level has at most 3 children per cell: the next one may not fit
-    if (part + 1 < n_parts && levels >= (part + 1) * S.ow_part_levels) {
+    if (WIDE) {
+      Q.from_global = n > S.ow_qcap;               // this level did not fit the shared queue: read it from global memory
+      Q.to_global = 3u * n + 4u > S.ow_qcap;       // a level has at most 3 children per cell: the next one may not fit
+    }
+    if (levels >= next_part_level && part + 1 < n_parts) {
       if (threadIdx.x == 0) {
         cnt->part_end[part] = base;
         __threadfence();
         atomicExch(&cnt->part_flag[part], 1u);
       }
       ++part;
+      next_part_level += S.ow_part_levels;
     }
   }
   publish(part, base);
@@ -898,8 +910,244 @@ rank_bfs_smem_kernel(const SearchParams S, const uint2 *__restrict__ tm, uint32_
     cnt->expanded = base;
     cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
     cnt->widest_level = widest;
-    for (int i = 0; i < 5; ++i) cnt->prof[i] = s_prof[i];
+    cnt->prof[4] = scans;
     cnt->prof[5] = clock64() - k0;
+#ifdef FITSLAM_OW_PROF
+    for (int k = 0; k < 8; ++k) printf("ow_prof[%d] = %u (%.1f per level)\n", k, pf.acc[k], (double)pf.acc[k] / levels);
+#endif
+  }
+}
+
+// ---- the outer wavefront on a thread-block cluster ----------------------------------------------------------------
+// The same search with a level spread over the CTAs of one cluster (16 SMs; 8 where the non-portable size is refused).
+// The single-CTA kernel above is bound by what one SM's L1 pipeline can look up per level (~7 cycles per dequeued cell:
+// 80 ms for C4's 22.8 M cells); here every CTA takes a contiguous slice of the level's positions.
+//   * the level queue lives in distributed shared memory: positions [r * per, (r + 1) * per) of a level are CTA r's
+//     slice (per = a power of two >= n / CTAs), and whoever appends a cell stores its entry straight into the slice of
+//     the CTA that will dequeue it (st.shared::cluster through cluster.map_shared_rank).
+//   * positions (2 bytes per cell, the tiled array of the single-CTA kernel, OW_OPEN = none) go through L2 (ld.global.cg /
+//     plain stores): written in one level, read in the next, with a cluster barrier (release / acquire) in between.
+//   * the static class bytes (bit k: neighbour k is expandable, bit 4 + k: neighbour k is a frontier-mask cell; same tile
+//     geometry) are read-only for the kernel; the appender loads the new cell's byte next to its position loads and puts
+//     the candidate directions (expandable and not visited: the visited ones are the cells that competed for it, which
+//     its winner saw while deciding) into the entry, so a level has one dependent L2 round trip.
+//   * order: a CTA's winners go, in (position, slot) order, into a local list; the CTAs' counts are exchanged through
+//     distributed shared memory; after a cluster barrier every CTA knows its base and the level's size, stores the
+//     positions and the entries of its winners, and a second cluster barrier ends the level.
+static constexpr int OWC_THREADS = 512;
+static constexpr uint32_t OWC_SLICE = 4096;             // queue entries per CTA and level (16 CTAs: levels up to OW_MAX_LEVEL)
+static constexpr uint32_t OWC_LOCAL = 3 * OWC_SLICE;    // winners of one CTA in one level: at most 3 per dequeued cell
+static constexpr uint32_t OWC_SMEM = (2 * OWC_SLICE + OWC_LOCAL) * 8;
+static constexpr uint32_t OWC_NONE = 0xFFFFu;
+
+// class bytes + "no position" for the tiles of the search disc's bounding box (see ow_prep_kernel)
+__global__ void __launch_bounds__(256)
+owc_prep_kernel(const SearchParams S, const OwLayout L, const uint32_t *__restrict__ ebits, const uint32_t *__restrict__ mbits,
+                uint8_t *__restrict__ cls, uint16_t *__restrict__ rk, uint32_t tx0, uint32_t ty0, uint32_t ntx, uint32_t nty) {
+  const uint64_t n = (uint64_t)ntx * nty * 8u;
+  const uint32_t W = S.map.W, H = S.map.H;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = (uint32_t)(i / ntx), bx = tx0 + (uint32_t)(i - (uint64_t)r * ntx);
+    const uint32_t Y = ty0 * 8u + r, X0 = bx * 16u;
+    const int y = (int)Y - (int)OW_PAD, xs = (int)X0 - (int)OW_PAD - 1;  // bit j of the row words below = column xs + j
+    uint32_t out[4] = {0u, 0u, 0u, 0u};
+    if (y >= 0 && y < (int)H) {
+      const uint32_t em = row_bits(ebits, S.wpr, H, y, xs), eu = row_bits(ebits, S.wpr, H, y - 1, xs), ed = row_bits(ebits, S.wpr, H, y + 1, xs);
+      const uint32_t mm = row_bits(mbits, S.wpr, H, y, xs), mu = row_bits(mbits, S.wpr, H, y - 1, xs), md = row_bits(mbits, S.wpr, H, y + 1, xs);
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int x = xs + 1 + k;
+        if (x < 0 || x >= (int)W) continue;
+        const uint32_t b = ((em >> k) & 1u) | (((em >> (k + 2)) & 1u) << 1) | (((eu >> (k + 1)) & 1u) << 2) | (((ed >> (k + 1)) & 1u) << 3) |
+                           (((mm >> k) & 1u) << 4) | (((mm >> (k + 2)) & 1u) << 5) | (((mu >> (k + 1)) & 1u) << 6) | (((md >> (k + 1)) & 1u) << 7);
+        out[k >> 2] |= b << (8 * (k & 3));
+      }
+    }
+    const size_t at = ((size_t)(Y >> 3) * L.txr + 2u * bx) * 64u + (Y & 7u) * 8u;  // first of the two tiles' rows
+    *reinterpret_cast<uint2 *>(cls + at) = make_uint2(out[0], out[1]);
+    *reinterpret_cast<uint2 *>(cls + at + 64) = make_uint2(out[2], out[3]);
+    const uint4 none = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+    *reinterpret_cast<uint4 *>(rk + at) = none;
+    *reinterpret_cast<uint4 *>(rk + at + 64) = none;
+  }
+}
+
+// queue entry: .x = x | y << 14 | candidate directions << 28, .y = directions of the frontier-mask neighbours
+__global__ void __launch_bounds__(OWC_THREADS, 1)
+ow_cluster_kernel(const SearchParams S, const OwLayout L, const uint8_t *__restrict__ cls, uint16_t *rk, uint32_t *claim, uint32_t *queue,
+                  Counters *cnt, uint32_t n_parts) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const uint32_t CS = cluster.num_blocks(), rank = cluster.block_rank();
+  extern __shared__ uint2 owc_sh[];
+  uint2 *qs = owc_sh;                       // two slices of OWC_SLICE entries
+  uint2 *lout = owc_sh + 2 * OWC_SLICE;     // this CTA's winners of the level, in order
+  __shared__ uint32_t s_cnt[2][16];         // winners per CTA (written by the CTAs themselves), by level parity
+  __shared__ uint32_t s_ws[2][OWC_THREADS / 32];
+  __shared__ uint32_t sh48[48];
+  __shared__ uint32_t s_start;
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  const uint32_t W = S.map.W;
+  const long long k0 = clock64();
+  auto publish = [&](uint32_t from, uint32_t end) {  // (CTA 0, after a cluster barrier: every CTA's touches precede it)
+    if (rank != 0 || threadIdx.x != 0) return;
+    for (uint32_t k = from; k + 1 < n_parts; ++k) cnt->part_end[k] = end;
+    __threadfence();
+    for (uint32_t k = from; k + 1 < n_parts; ++k) atomicExch(&cnt->part_flag[k], 1u);
+  };
+  if (cnt->overflow) { publish(0, 0); return; }  // (uniform: written before this kernel)
+  if (rank == 0) {
+    const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
+    if (threadIdx.x == 0) s_start = S.robot_cell;
+    __syncthreads();
+    if (S.map.data[(size_t)ry * S.map.pitch + rx] >= S.lethal) {
+      nearest_free_cell(S, claim, queue, queue + S.queue_cap / 2, S.robot_cell, sh48, cnt, &s_start);
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      const uint32_t start = s_start;
+      cnt->start_cell = start;
+      const uint32_t sy = start / W, sx = start - sy * W;
+      const uint32_t si = ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD, L.rk_yt);
+      qs[0] = make_uint2(sx | (sy << 14) | ((uint32_t)cls[si] << 28), (uint32_t)cls[si] >> 4);
+      rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56)
+    }
+  }
+  cluster.sync();
+  uint32_t base = 0, n = 1, levels = 0, part = 0, widest = 1, cur = 0, scans = 0;
+  uint32_t per = 32;  // slice length of the current level
+  uint32_t next_part_level = S.ow_part_levels;
+  bool bad = false;
+  OwProf pf;
+#ifdef FITSLAM_OW_PROF
+  for (int k = 0; k < 8; ++k) pf.acc[k] = 0;
+  pf.last = ow_clock(0);
+#endif
+  while (n > 0) {
+    const uint32_t lo = rank * per, m = lo < n ? min(per, n - lo) : 0u;  // this CTA's positions: [lo, lo + m)
+    OW_STAMP(0, m);
+    const uint2 *q = qs + cur * OWC_SLICE;
+    uint32_t n_local = 0;
+    for (uint32_t tile = 0; tile < m; tile += OWC_THREADS) {
+      uint32_t *ws = s_ws[scans & 1u];
+      ++scans;
+      const uint32_t pl = tile + threadIdx.x;
+      uint32_t wmask = 0u, xy = 0u, o0 = 0u, o1 = 0u, o2 = 0u, o3 = 0u, m0 = 0u, m1 = 0u, m2 = 0u, m3 = 0u;
+      if (tile + (wid << 5) < m) {  // warp-uniform
+        uint2 e = make_uint2(0u, 0u);
+        if (pl < m) e = q[pl];
+        const uint32_t pos = lo + pl, cand = e.x >> 28, mk = e.y;
+        xy = e.x & 0x0FFFFFFFu;
+        const uint32_t x = xy & 0x3FFFu, y = xy >> 14;
+        const uint32_t i = ow_rk_fx(x + OW_PAD) + ow_rk_fy(y + OW_PAD, L.rk_yt);
+        const uint32_t tx = i & 7u, ty = i & 56u;
+        const uint32_t xa = tx < 2u ? 58u : 2u, xb = tx < 1u ? 57u : 1u, xd = tx > 6u ? 57u : 1u, xe = tx > 5u ? 58u : 2u;
+        const uint32_t ya = (ty < 16u ? L.rk_yt : 0u) + 16u, yb = (ty < 8u ? L.rk_yt : 0u) + 8u, yd = (ty > 48u ? L.rk_yt : 0u) + 8u,
+                       ye = (ty > 40u ? L.rk_yt : 0u) + 16u;
+        const uint32_t i0 = i - xb, i1 = i + xd, i2 = i - yb, i3 = i + yd;
+        const uint32_t l2 = (cand & 1u) ? (uint32_t)__ldcg(rk + i - xa) : OWC_NONE, r2 = (cand & 2u) ? (uint32_t)__ldcg(rk + i + xe) : OWC_NONE;
+        const uint32_t u2 = (cand & 4u) ? (uint32_t)__ldcg(rk + i - ya) : OWC_NONE, d2 = (cand & 8u) ? (uint32_t)__ldcg(rk + i + ye) : OWC_NONE;
+        const uint32_t ul = (cand & 5u) ? (uint32_t)__ldcg(rk + i0 - yb) : OWC_NONE, ur = (cand & 6u) ? (uint32_t)__ldcg(rk + i1 - yb) : OWC_NONE;
+        const uint32_t dl = (cand & 9u) ? (uint32_t)__ldcg(rk + i0 + yd) : OWC_NONE, dr = (cand & 10u) ? (uint32_t)__ldcg(rk + i1 + yd) : OWC_NONE;
+        const uint32_t k0c = (cand & 1u) ? (uint32_t)__ldg(cls + i0) : 0u, k1c = (cand & 2u) ? (uint32_t)__ldg(cls + i1) : 0u;
+        const uint32_t k2c = (cand & 4u) ? (uint32_t)__ldg(cls + i2) : 0u, k3c = (cand & 8u) ? (uint32_t)__ldg(cls + i3) : 0u;
+        if (mk) {  // frontier-mask neighbours record the first touch (isNewFrontierCell branch, FrontierSearch.cpp:78-81)
+          const uint32_t key = TOUCH_BIT | ((base + pos) << 2);
+          uint32_t *at = claim + (size_t)y * W + x;
+          if (mk & 1u) atomicMin(at - 1, key);
+          if (mk & 2u) atomicMin(at + 1, key | 1u);
+          if (mk & 4u) atomicMin(at - W, key | 2u);
+          if (mk & 8u) atomicMin(at + W, key | 3u);
+        }
+        if ((cand & 1u) && min(l2, min(ul, dl)) > pos) wmask |= 1u;
+        if ((cand & 2u) && min(r2, min(ur, dr)) > pos) wmask |= 2u;
+        if ((cand & 4u) && min(u2, min(ul, ur)) > pos) wmask |= 4u;
+        if ((cand & 8u) && min(d2, min(dl, dr)) > pos) wmask |= 8u;
+        // candidate directions of the cells this one visits: expandable neighbours minus its level-d neighbours (this
+        // cell and whichever cells at distance 2 have a position)
+        const uint32_t hl2 = l2 < OW_MAX_LEVEL, hr2 = r2 < OW_MAX_LEVEL, hu2 = u2 < OW_MAX_LEVEL, hd2 = d2 < OW_MAX_LEVEL;
+        const uint32_t hul = ul < OW_MAX_LEVEL, hur = ur < OW_MAX_LEVEL, hdl = dl < OW_MAX_LEVEL, hdr = dr < OW_MAX_LEVEL;
+        o0 = (xy - 1u) | ((k0c & ~(2u | hl2 | (hul << 2) | (hdl << 3))) << 28); m0 = k0c >> 4;
+        o1 = (xy + 1u) | ((k1c & ~(1u | (hr2 << 1) | (hur << 2) | (hdr << 3))) << 28); m1 = k1c >> 4;
+        o2 = (xy - (1u << 14)) | ((k2c & ~(8u | hul | (hur << 1) | (hu2 << 2))) << 28); m2 = k2c >> 4;
+        o3 = (xy + (1u << 14)) | ((k3c & ~(4u | hdl | (hdr << 1) | (hd2 << 3))) << 28); m3 = k3c >> 4;
+      }
+      // CTA-wide exclusive scan of the winner counts (0..4 per thread): three ballots per warp, one barrier
+      const uint32_t nw = __popc(wmask);
+      const uint32_t b0 = __ballot_sync(0xffffffffu, nw & 1u), b1 = __ballot_sync(0xffffffffu, nw & 2u), b2 = __ballot_sync(0xffffffffu, nw & 4u);
+      const uint32_t lt = (1u << lane) - 1u;
+      const uint32_t excl = __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt);
+      if (lane == 0) ws[wid] = __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2);
+      __syncthreads();
+      const uint32_t wv = lane < OWC_THREADS / 32 ? ws[lane] : 0u;
+      const uint32_t total = __reduce_add_sync(0xffffffffu, wv);
+      const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
+      uint32_t dst = n_local + wbase + excl;
+      if (n_local + total > OWC_LOCAL) bad = true;  // (uniform; cannot happen: at most 3 winners per dequeued cell, 4 at the start)
+      else {
+        if (wmask & 1u) lout[dst++] = make_uint2(o0, m0);
+        if (wmask & 2u) lout[dst++] = make_uint2(o1, m1);
+        if (wmask & 4u) lout[dst++] = make_uint2(o2, m2);
+        if (wmask & 8u) lout[dst++] = make_uint2(o3, m3);
+      }
+      n_local += total;
+    }
+    OW_STAMP(1, n_local);
+    // every CTA tells every CTA how many cells it appends
+    if (threadIdx.x < CS) cluster.map_shared_rank(&s_cnt[levels & 1u][0], threadIdx.x)[rank] = bad ? 0xFFFFFFFFu : n_local;
+    OW_STAMP(2, n_local);
+    cluster.sync();
+    OW_STAMP(3, n_local);
+    const uint32_t cv = lane < CS ? s_cnt[levels & 1u][lane] : 0u;  // (every warp: one load and three warp reductions)
+    const bool any_bad = __reduce_max_sync(0xffffffffu, cv) == 0xFFFFFFFFu;
+    const uint32_t n_next = __reduce_add_sync(0xffffffffu, cv), gbase = __reduce_add_sync(0xffffffffu, lane < rank ? cv : 0u);
+    base += n;
+    ++levels;
+    widest = max(widest, n_next);
+    if (any_bad || n_next > OW_MAX_LEVEL || n_next > CS * OWC_SLICE) {  // uniform across the cluster: the global-memory wavefront
+      if (rank == 0 && threadIdx.x == 0) cnt->ow_fallback = 1u;      // reruns the search (claim[] holds touch keys only, and it
+      publish(part, base);                                           // would write the same ones)
+      return;
+    }
+    // slice length of the next level: a power of two, so that position -> (CTA, offset) is a shift and a mask
+    const uint32_t need = (n_next + CS - 1u) / CS;  // CS is 8 or 16
+    const uint32_t sh = need <= 32u ? 5u : 32u - __clz(need - 1u), per_next = 1u << sh;
+    uint2 *qn = qs + (cur ^ 1u) * OWC_SLICE;
+    OW_STAMP(4, n_next);
+    for (uint32_t k = threadIdx.x; k < n_local; k += OWC_THREADS) {
+      const uint2 e = lout[k];
+      const uint32_t j = gbase + k;  // the cell's position in the next level
+      const uint32_t x = e.x & 0x3FFFu, y = (e.x >> 14) & 0x3FFFu;
+      rk[ow_rk_fx(x + OW_PAD) + ow_rk_fy(y + OW_PAD, L.rk_yt)] = (uint16_t)j;
+      cluster.map_shared_rank(qn, j >> sh)[j & (per_next - 1u)] = e;
+    }
+    OW_STAMP(5, n_next);
+    cluster.sync();  // release / acquire: the positions (global memory) and the entries (distributed shared memory) of the next level
+    OW_STAMP(6, n_next);
+    n = n_next;
+    per = per_next;
+    cur ^= 1u;
+    if (levels >= next_part_level && part + 1 < n_parts) {
+      if (rank == 0 && threadIdx.x == 0) {
+        cnt->part_end[part] = base;
+        __threadfence();
+        atomicExch(&cnt->part_flag[part], 1u);
+      }
+      ++part;
+      next_part_level += S.ow_part_levels;
+    }
+  }
+  publish(part, base);
+  if (rank == 0 && threadIdx.x == 0) {
+    cnt->bfs_levels = levels;
+    cnt->expanded = base;
+    cnt->dirty_queue = 0;  // claim[] was written at frontier-mask cells only
+    cnt->widest_level = widest;
+    cnt->prof[4] = scans;
+    cnt->prof[5] = clock64() - k0;
+#ifdef FITSLAM_OW_PROF
+    for (int k = 0; k < 8; ++k) printf("owc_prof[%d] = %u (%.1f per level)\n", k, pf.acc[k], (double)pf.acc[k] / levels);
+#endif
   }
 }
 
@@ -915,18 +1163,6 @@ __global__ void wait_part_kernel(Counters *cnt, uint32_t part) {
     }
   }
   __threadfence();
-}
-
-// Resets the rank tiles of the search disc's bounding box to "not dequeued" before the outer wavefront (16-byte stores,
-// all SMs; it also leaves those lines in L2).  The wavefront never leaves the box: cells are enqueued only inside the disc.
-__global__ void rk_reset_kernel(uint32_t *rk, uint32_t tiles_x, uint32_t tx0, uint32_t ty0, uint32_t ntx, uint32_t nty) {
-  const uint64_t n = (uint64_t)ntx * nty * 16u;  // uint4 stores per tile: 64 words
-  const uint4 e = make_uint4(KEY_INF, KEY_INF, KEY_INF, KEY_INF);
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-    const uint64_t t = i >> 4;
-    const uint32_t r = (uint32_t)(t / ntx), cx = (uint32_t)(t - (uint64_t)r * ntx);
-    reinterpret_cast<uint4 *>(rk + ((size_t)(ty0 + r) * tiles_x + tx0 + cx) * 64u)[i & 15u] = e;
-  }
 }
 
 // ------------------------------------------------------------------------------------------------ K4: found components
@@ -1486,7 +1722,18 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   FS_CUDA(c, s->bits.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->trav.reserve((size_t)wpr * c->H));
   FS_CUDA(c, s->tm.reserve((size_t)wpr * ((c->H + 7u) / 8u) * 8u));
-  FS_CUDA(c, s->rk.reserve((size_t)((c->W + 7u) / 8u) * ((c->H + 7u) / 8u) * 64u));
+  FS_CUDA(c, s->ebits.reserve((size_t)wpr * c->H));
+  {
+    const OwLayout L = ow_layout(c->W, c->H);
+    const uint64_t pc = (uint64_t)L.Wp * L.Hp;
+    if (s->rk.cap < pc || s->ow_cells != pc) {  // padding: OW_BLOCKED (0xFDFD is above OW_MAX_LEVEL and none of the other classes)
+      FS_CUDA(c, s->rk.reserve(pc));
+      FS_CUDA(c, s->cls.reserve(pc));
+      FS_CUDA(c, cudaMemsetAsync(s->rk.p, 0xFD, s->rk.cap * sizeof(uint16_t), c->stream));
+      FS_CUDA(c, cudaMemsetAsync(s->cls.p, 0, s->cls.cap, c->stream));
+      s->ow_cells = pc;
+    }
+  }
   FS_CUDA(c, s->slot.reserve(N));
   FS_CUDA(c, s->queue.reserve(N + 8));
   FS_CUDA(c, s->counters.reserve(1));
@@ -1537,8 +1784,8 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   S.dist_limit = mfd + (c->prm.max_frontier_cluster_size * c->res * 1.414);  // FrontierSearch.cpp:74
   {
     const double L = S.dist_limit / c->res;
-    S.near_cells_sq = L > 4.0 ? (int64_t)(L * L * (1.0 - 1e-6)) - 2 : 0;
-    S.near_cells_sq32 = (uint32_t)std::min<int64_t>(S.near_cells_sq, 0x7FFFFFFF);
+    S.near_cells_sq = L > 4.0 ? (int64_t)std::min(L * L * (1.0 - 1e-6), 4e18) - 2 : 0;
+    S.far_cells_sq = (int64_t)std::min(L * L * (1.0 + 1e-6), 4e18) + 2;
   }
   if (s->force_global < 0) {
     const char *e = getenv("FITSLAM_WAVEFRONT");
@@ -1549,16 +1796,37 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     const long v = e ? atol(e) : (long)OW_QCAP;
     S.ow_qcap = (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
   }
-  S.rk_tiles_x = (c->W + 7u) / 8u;
   // a batch is about 1/12 of the frontiers; the launches are sized for a quarter of the last search's count
   S.early_cap = std::min<uint32_t>(std::max<uint32_t>(EARLY_SLICE_CAP, s->last.n_frontiers / 4u), 8192u);
   S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
-  S.ow_wide = (c->W <= 16384u && c->H <= 16384u && !getenv("FITSLAM_OW_NOWIDE")) ? 1u : 0u;
-  S.use_smem = (s->force_global || c->W > 32768u || c->H > 32768u) ? 0u : 1u;  // queue entries pack y << 16 | x; 32-bit radius prefilter
+  S.ow_wide = getenv("FITSLAM_OW_NOWIDE") ? 0u : 1u;
+  S.use_smem = (s->force_global || c->W > 16384u || c->H > 16384u) ? 0u : 1u;  // queue entries pack x | y << 14 | mask << 28
   if (!s->attr_set) {
-    FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
-    FS_CUDA(c, cudaFuncSetAttribute(rank_bfs_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
+    FS_CUDA(c, cudaFuncSetAttribute(ow_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
+    FS_CUDA(c, cudaFuncSetAttribute(ow_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
     FS_CUDA(c, cudaFuncSetAttribute(replay_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)iw_smem(IW_CELLS, IW_BITS_LARGE)));
+    // the cluster wavefront: 16 CTAs (non-portable size) where the device takes it, else 8, else the single-CTA kernel
+    s->ow_cluster = 0;
+    if (const char *e = getenv("FITSLAM_OW_CLUSTER_MIN")) s->ow_cluster_min = (uint32_t)atol(e);
+    const char *ev = getenv("FITSLAM_OW_CLUSTER");  // 0: single-CTA kernel; 8 / 16: that cluster size
+    const int want = ev ? atoi(ev) : 16;
+    if (want > 1 && cudaFuncSetAttribute(ow_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OWC_SMEM) == cudaSuccess) {
+      for (int cs = want >= 16 ? 16 : 8; cs >= 8 && !s->ow_cluster; cs -= 8) {
+        if (cs > 8 && cudaFuncSetAttribute(ow_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) continue;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(cs);
+        cfg.blockDim = dim3(OWC_THREADS);
+        cfg.dynamicSmemBytes = OWC_SMEM;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, ow_cluster_kernel, &cfg) == cudaSuccess && nc > 0) s->ow_cluster = cs;
+      }
+      cudaGetLastError();
+    }
     s->attr_set = true;
   }
   S.min_size = c->prm.min_frontier_cluster_size;
@@ -1579,7 +1847,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   if (phase == 0) {
     FS_CUDA(c, cudaMemsetAsync(cnt, 0, sizeof(Counters), c->stream));
     FS_CUDA(c, cudaMemsetAsync(s->ftag.p, 0, s->front_cap, c->stream));
-    mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
+    mask_kernel<<<(unsigned)((n_words + 255) / 256), 256, 0, c->stream>>>(S, s->bits.p, s->trav.p, s->ebits.p, s->tm.p, s->slot.p, s->mcell.p, cnt);
     c->launches += 1;
   }
   if (!s->have_ev) {
@@ -1664,19 +1932,45 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     return cudaSuccess;
   };
   if (S.use_smem && phase == 0) {
-    // bounding box of the search disc (+ a halo), in 8 x 8 tiles, clipped to the map
+    // bounding box of the search disc (+ a halo) clipped to the map, in 16 x 8-cell tiles of the padded arrays
+    const OwLayout L = ow_layout(c->W, c->H);
     const uint32_t rcx = robot_cell % c->W, rcy = robot_cell / c->W;
     const uint32_t rad = (uint32_t)std::min<double>(S.dist_limit / c->res + 8.0, 1e9);
-    const uint32_t tx0 = (rcx > rad ? rcx - rad : 0u) >> 3, tx1 = (uint32_t)std::min<uint64_t>((uint64_t)rcx + rad, c->W - 1) >> 3;
-    const uint32_t ty0 = (rcy > rad ? rcy - rad : 0u) >> 3, ty1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1) >> 3;
-    rk_reset_kernel<<<wide, 256, 0, c->stream>>>(s->rk.p, S.rk_tiles_x, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
+    const uint32_t bx0 = rcx > rad ? rcx - rad : 0u, bx1 = (uint32_t)std::min<uint64_t>((uint64_t)rcx + rad, c->W - 1);
+    const uint32_t by0 = rcy > rad ? rcy - rad : 0u, by1 = (uint32_t)std::min<uint64_t>((uint64_t)rcy + rad, c->H - 1);
+    // (a halo of OW_PAD cells around the box, so the padded coordinates of its corners are bx0 .. bx1 + 2 * OW_PAD)
+    const uint32_t tx0 = bx0 >> 4, tx1 = std::min((bx1 + 2u * OW_PAD) >> 4, L.Wp / 16u - 1u);
+    const uint32_t ty0 = by0 >> 3, ty1 = std::min((by1 + 2u * OW_PAD) >> 3, L.Hp / 8u - 1u);
+    const uint32_t n_parts = s->ow_parts;
+    // narrow levels (a few hundred cells) are bound by the latency of a level, which one CTA keeps lowest; wide ones by the
+    // lookups per level, which the cluster spreads over its SMs.  Decided by the widest level of the last search (first
+    // search on a map: by the size of the search disc)
+    const uint32_t guess = s->last.bfs_levels ? s->last.widest_level : (uint32_t)std::min<double>(S.dist_limit / c->res, 1e9);
+    const bool cluster = s->ow_cluster && guess >= s->ow_cluster_min;
+    if (cluster) {
+      owc_prep_kernel<<<wide, 256, 0, c->stream>>>(S, L, s->ebits.p, s->bits.p, s->cls.p, s->rk.p, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(s->ow_cluster);
+      cfg.blockDim = dim3(OWC_THREADS);
+      cfg.dynamicSmemBytes = OWC_SMEM;
+      cfg.stream = c->stream;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = s->ow_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      FS_CUDA(c, cudaLaunchKernelEx(&cfg, ow_cluster_kernel, S, L, (const uint8_t *)s->cls.p, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts));
+      ++c->launches;
+    } else {
+      ow_prep_kernel<<<wide, 256, 0, c->stream>>>(S, L, s->ebits.p, s->bits.p, s->rk.p, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
+    }
     ++c->launches;
     // the search on the context stream; behind each published part but the last, a collection on the second stream
-    const uint32_t n_parts = s->ow_parts;
-    if (s->prefer_wide && S.ow_wide)
-      rank_bfs_smem_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
+    if (cluster) {
+    } else if (s->prefer_wide && S.ow_wide)
+      ow_kernel<true><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, L, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts);
     else
-      rank_bfs_smem_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, s->tm.p, s->claim.p, s->queue.p, s->rk.p, cnt, n_parts);
+      ow_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, L, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts);
     ++c->launches;
     FS_CUDA(c, cudaGetLastError());  // (the kernels below poll flags only this one sets)
     for (uint32_t part = 0; part + 1 < n_parts; ++part) {
@@ -1771,8 +2065,8 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
     if (s->prefer_wide && !hc->overflow && hc->widest_level <= hc_qcap(s)) s->prefer_wide = false;  // narrow levels again
     s->last = *hc;
     if (getenv("FITSLAM_PROF"))
-      fprintf(stderr, "outer wavefront: levels %u expanded %u passes %llu | cycles (0 unless built with -DFITSLAM_OW_PROF) stage1 %llu stage2+3 %llu scan %llu append %llu total %llu\n", hc->bfs_levels,
-              hc->expanded, hc->prof[4], hc->prof[0], hc->prof[1], hc->prof[2], hc->prof[3], hc->prof[5]);
+      fprintf(stderr, "outer wavefront: levels %u expanded %u widest %u passes %llu cycles %llu\n", hc->bfs_levels, hc->expanded,
+              hc->widest_level, hc->prof[4], hc->prof[5]);
     if (getenv("FITSLAM_PROF")) {
       float t[6] = {0, 0, 0, 0, 0, 0};
       const int seq[7] = {0, 1, 3, 4, 2, 5, 6};
