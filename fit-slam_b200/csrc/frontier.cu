@@ -112,7 +112,6 @@ struct FrontierState {
   DevBuf<uint32_t> trav;      // traversable mask (cost < 254), same layout
   DevBuf<uint2> tm;           // {trav word, frontier-mask word} interleaved: one 8-byte load classifies a neighbour
   DevBuf<uint32_t> ebits;     // expandable cells (traversable and inside the search radius), same layout
-  DevBuf<uint8_t> cls;        // cluster outer wavefront: class byte per cell (same layout), rewritten likewise
   int ow_cluster = -1;        // CTAs per cluster of ow_cluster_kernel (0: not available, use the single-CTA kernel); -1: not probed yet
   uint32_t ow_cluster_min = 1500;  // ... used when the last search's widest level had at least this many cells (FITSLAM_OW_CLUSTER_MIN)
   DevBuf<uint16_t> rk;        // outer wavefront: class of a cell, then its position inside its level (ow_rk_* layout); the search disc's
@@ -159,7 +158,7 @@ static FrontierState *fr_state(fitslam_ctx *c) {
 void destroy_frontier_state(fitslam_ctx *c) {
   if (!c->fs) return;
   FrontierState *s = c->fs;
-  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->rk.release(); s->cls.release(); s->ebits.release(); s->mcell.release();
+  s->claim.release(); s->slot.release(); s->bits.release(); s->trav.release(); s->tm.release(); s->rk.release(); s->ebits.release(); s->mcell.release();
   s->parent.release(); s->rkey.release(); s->rsize.release(); s->queue.release();
   s->rbox.release(); s->cbox.release(); s->obox.release();
   s->ckey.release(); s->cseed.release(); s->csize.release();
@@ -721,7 +720,9 @@ ow_prep_kernel(const SearchParams S, const OwLayout L, const uint32_t *__restric
 }
 
 struct OwQueues {
-  // entries: .x = the cell's index in the state array, .y = x | y << 14
+  // entries: .x = x | y << 14 | candidate directions << 28 (the OPEN neighbours), .y = directions of the MASK neighbours.
+  // Whoever appends a cell has read the cell's other three neighbours to decide (they are cells at distance 2 from the
+  // appender), so the classes of all four travel with the entry and a dequeued cell never reads its own neighbours.
   uint2 *q;        // shared memory: two queues of OW_QCAP entries, this level's (`cur`) and the next one's
   uint2 *g;        // the same in global memory (two of `gcap` entries), used while a level is wider than the shared-memory queue
   uint32_t gcap;
@@ -738,6 +739,71 @@ __device__ __forceinline__ uint32_t ow_clock(uint32_t dep) { uint32_t t; asm vol
 #endif
 struct OwProf { uint32_t last; uint32_t acc[8]; };
 
+// The decision of one dequeued cell (both wavefront kernels).  In: its queue entry, its position `pos` in the level, the
+// state array through `ld` (plain loads in the single-CTA kernel, ld.global.cg in the cluster kernel).  Out: which
+// neighbours it visits (`win`), and for each of them the state index (`ci`) and the queue entry (`ent`).
+struct OwCell {
+  uint32_t win;
+  uint32_t ci[4];
+  uint2 ent[4];
+};
+template <typename Load>
+__device__ __forceinline__ void ow_decide(const OwLayout &L, const uint2 e, uint32_t pos, Load ld, OwCell &out) {
+  const uint32_t cand = e.x >> 28, xy = e.x & 0x0FFFFFFFu;
+  const uint32_t i = ow_rk_fx((xy & 0x3FFFu) + OW_PAD) + ow_rk_fy((xy >> 14) + OW_PAD, L.rk_yt);
+  // index steps to the cells at distance 1 and 2: the index separates into f(x) + g(y), so a step along x costs a fixed
+  // amount plus 56 when it crosses a tile edge, a step along y 8 plus (tile row - 64) when it does
+  const uint32_t tx = i & 7u, ty = i & 56u;
+  const uint32_t xa = tx < 2u ? 58u : 2u, xb = tx < 1u ? 57u : 1u, xd = tx > 6u ? 57u : 1u, xe = tx > 5u ? 58u : 2u;
+  const uint32_t ya = (ty < 16u ? L.rk_yt : 0u) + 16u, yb = (ty < 8u ? L.rk_yt : 0u) + 8u, yd = (ty > 48u ? L.rk_yt : 0u) + 8u,
+                 ye = (ty > 40u ? L.rk_yt : 0u) + 16u;
+  const uint32_t i0 = i - xb, i1 = i + xd, i2 = i - yb, i3 = i + yd;  // the four neighbours: -x, +x, -y, +y
+  // state of the cells at distance 2 that are next to a candidate (all loads independent): a position if the cell is on
+  // this level, else its class, which is above every position
+  const uint32_t l2 = (cand & 1u) ? ld(i - xa) : OW_BLOCKED, r2 = (cand & 2u) ? ld(i + xe) : OW_BLOCKED;
+  const uint32_t u2 = (cand & 4u) ? ld(i - ya) : OW_BLOCKED, d2 = (cand & 8u) ? ld(i + ye) : OW_BLOCKED;
+  const uint32_t ul = (cand & 5u) ? ld(i0 - yb) : OW_BLOCKED, ur = (cand & 6u) ? ld(i1 - yb) : OW_BLOCKED;
+  const uint32_t dl = (cand & 9u) ? ld(i0 + yd) : OW_BLOCKED, dr = (cand & 10u) ? ld(i1 + yd) : OW_BLOCKED;
+  // a level-d neighbour of the candidate that was dequeued before this cell visited it first
+  uint32_t win = 0u;
+  if ((cand & 1u) && min(l2, min(ul, dl)) > pos) win |= 1u;
+  if ((cand & 2u) && min(r2, min(ur, dr)) > pos) win |= 2u;
+  if ((cand & 4u) && min(u2, min(ul, ur)) > pos) win |= 4u;
+  if ((cand & 8u) && min(d2, min(dl, dr)) > pos) win |= 8u;
+  out.win = win;
+  out.ci[0] = i0; out.ci[1] = i1; out.ci[2] = i2; out.ci[3] = i3;
+  // entries of the visited cells: their OPEN neighbours are their candidates, their MASK neighbours get their touch key
+  // (the fourth neighbour is this cell)
+  const uint32_t ol2 = l2 == OW_OPEN, or2 = r2 == OW_OPEN, ou2 = u2 == OW_OPEN, od2 = d2 == OW_OPEN;
+  const uint32_t oul = ul == OW_OPEN, our = ur == OW_OPEN, odl = dl == OW_OPEN, odr = dr == OW_OPEN;
+  const uint32_t ml2 = l2 == OW_MASK, mr2 = r2 == OW_MASK, mu2 = u2 == OW_MASK, md2 = d2 == OW_MASK;
+  const uint32_t mul = ul == OW_MASK, mur = ur == OW_MASK, mdl = dl == OW_MASK, mdr = dr == OW_MASK;
+  out.ent[0] = make_uint2((xy - 1u) | ((ol2 | (oul << 2) | (odl << 3)) << 28), ml2 | (mul << 2) | (mdl << 3));
+  out.ent[1] = make_uint2((xy + 1u) | (((or2 << 1) | (our << 2) | (odr << 3)) << 28), (mr2 << 1) | (mur << 2) | (mdr << 3));
+  out.ent[2] = make_uint2((xy - (1u << 14)) | ((oul | (our << 1) | (ou2 << 2)) << 28), mul | (mur << 1) | (mu2 << 2));
+  out.ent[3] = make_uint2((xy + (1u << 14)) | ((odl | (odr << 1) | (od2 << 3)) << 28), mdl | (mdr << 1) | (md2 << 3));
+}
+// frontier-mask neighbours record the first touch (isNewFrontierCell branch, FrontierSearch.cpp:78-81)
+__device__ __forceinline__ void ow_touch(uint32_t *claim, uint32_t W, const uint2 e, uint32_t rank) {
+  if (!e.y) return;
+  const uint32_t key = TOUCH_BIT | (rank << 2);
+  uint32_t *at = claim + (size_t)((e.x >> 14) & 0x3FFFu) * W + (e.x & 0x3FFFu);
+  if (e.y & 1u) atomicMin(at - 1, key);
+  if (e.y & 2u) atomicMin(at + 1, key | 1u);
+  if (e.y & 4u) atomicMin(at - W, key | 2u);
+  if (e.y & 8u) atomicMin(at + W, key | 3u);
+}
+// entry of the start cell: the classes of its four neighbours
+__device__ __forceinline__ uint2 ow_start_entry(const OwLayout &L, const uint16_t *rk, uint32_t sx, uint32_t sy, uint32_t *si) {
+  const uint32_t i = ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD, L.rk_yt);
+  const uint32_t v[4] = {rk[ow_rk_fx(sx + OW_PAD - 1u) + ow_rk_fy(sy + OW_PAD, L.rk_yt)], rk[ow_rk_fx(sx + OW_PAD + 1u) + ow_rk_fy(sy + OW_PAD, L.rk_yt)],
+                         rk[ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD - 1u, L.rk_yt)], rk[ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD + 1u, L.rk_yt)]};
+  uint32_t cand = 0u, mk = 0u;
+  for (int k = 0; k < 4; ++k) { cand |= (v[k] == OW_OPEN ? 1u : 0u) << k; mk |= (v[k] == OW_MASK ? 1u : 0u) << k; }
+  *si = i;
+  return make_uint2(sx | (sy << 14) | (cand << 28), mk);
+}
+
 // one pass over up to OW_THREADS queue positions starting at `tile`; returns the number of cells it appended (valid in
 // the warps that had positions to work on: warp 0 always has).  Warps whose positions all lie beyond the level only
 // take part in the barrier: with ~400 cells per level two thirds of the warps are idle, and the instructions they would
@@ -746,7 +812,7 @@ struct OwProf { uint32_t last; uint32_t acc[8]; };
 // narrow pass free of those branches).
 template <bool WIDE>
 __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const OwLayout &L, uint16_t *rk, uint32_t *claim, const OwQueues &Q,
-                                           uint32_t cur, uint32_t safe, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
+                                           uint32_t cur, uint32_t tile, uint32_t n, uint32_t base, uint32_t n_next,
                                            uint32_t *ws, OwProf &pf) {
   const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
   if (tile + (wid << 5) >= n) {  // warp-uniform
@@ -754,42 +820,15 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const OwLayou
     return 0u;
   }
   const uint32_t pos = tile + threadIdx.x;
-  uint2 e = make_uint2(safe, 0u);  // lanes beyond the level look at a padding cell: BLOCKED neighbours, nothing to do
+  uint2 e = make_uint2(0u, 0u);  // lanes beyond the level: no candidates, no mask neighbours
   if (pos < n) e = (WIDE && Q.from_global) ? __ldcg(Q.g + cur * Q.gcap + pos) : Q.q[cur * OW_QCAP + pos];
-  const uint32_t i = e.x;
-  OW_STAMP(0, i);
-  // index steps to the cells at distance 1 and 2: the index separates into f(x) + g(y), so a step along x costs a fixed
-  // amount plus 56 when it crosses a tile edge, a step along y 8 plus (tile row - 64) when it does
-  const uint32_t tx = i & 7u, ty = i & 56u;
-  const uint32_t xb = tx < 1u ? 57u : 1u, xd = tx > 6u ? 57u : 1u;
-  const uint32_t yb = (ty < 8u ? L.rk_yt : 0u) + 8u, yd = (ty > 48u ? L.rk_yt : 0u) + 8u;
-  const uint32_t i0 = i - xb, i1 = i + xd, i2 = i - yb, i3 = i + yd;  // the four neighbours: -x, +x, -y, +y
-  const uint32_t v0 = rk[i0], v1 = rk[i1], v2 = rk[i2], v3 = rk[i3];
-  const uint32_t xa = tx < 2u ? 58u : 2u, xe = tx > 5u ? 58u : 2u;
-  const uint32_t ya = (ty < 16u ? L.rk_yt : 0u) + 16u, ye = (ty > 40u ? L.rk_yt : 0u) + 16u;
-  const bool c0 = v0 == OW_OPEN, c1 = v1 == OW_OPEN, c2 = v2 == OW_OPEN, c3 = v3 == OW_OPEN;
-  OW_STAMP(1, (uint32_t)c0 + c1 + c2 + c3);
-  // positions of the cells at distance 2 that are next to a candidate (all loads independent); a cell without a position
-  // reads as a class, which is above every position
-  const uint32_t l2 = c0 ? (uint32_t)rk[i - xa] : OW_OPEN, r2 = c1 ? (uint32_t)rk[i + xe] : OW_OPEN;
-  const uint32_t u2 = c2 ? (uint32_t)rk[i - ya] : OW_OPEN, d2 = c3 ? (uint32_t)rk[i + ye] : OW_OPEN;
-  const uint32_t ul = (c0 || c2) ? (uint32_t)rk[i0 - yb] : OW_OPEN, ur = (c1 || c2) ? (uint32_t)rk[i1 - yb] : OW_OPEN;
-  const uint32_t dl = (c0 || c3) ? (uint32_t)rk[i0 + yd] : OW_OPEN, dr = (c1 || c3) ? (uint32_t)rk[i1 + yd] : OW_OPEN;
-  // frontier-mask neighbours record the first touch (isNewFrontierCell branch, FrontierSearch.cpp:78-81)
-  if (v0 == OW_MASK || v1 == OW_MASK || v2 == OW_MASK || v3 == OW_MASK) {
-    const uint32_t key = TOUCH_BIT | ((base + pos) << 2);
-    uint32_t *at = claim + (size_t)(e.y >> 14) * S.map.W + (e.y & 0x3FFFu);
-    if (v0 == OW_MASK) atomicMin(at - 1, key);
-    if (v1 == OW_MASK) atomicMin(at + 1, key | 1u);
-    if (v2 == OW_MASK) atomicMin(at - S.map.W, key | 2u);
-    if (v3 == OW_MASK) atomicMin(at + S.map.W, key | 3u);
-  }
-  // a level-d neighbour of the candidate that was dequeued before this cell visited it first
-  const bool w0 = c0 && min(l2, min(ul, dl)) > pos, w1 = c1 && min(r2, min(ur, dr)) > pos;
-  const bool w2 = c2 && min(u2, min(ul, ur)) > pos, w3 = c3 && min(d2, min(dl, dr)) > pos;
-  OW_STAMP(2, (uint32_t)w0 + w1 + w2 + w3);
+  OW_STAMP(0, e.x);
+  OwCell d;
+  ow_decide(L, e, pos, [&](uint32_t at) { return (uint32_t)rk[at]; }, d);
+  ow_touch(claim, S.map.W, e, base + pos);
+  OW_STAMP(2, d.win);
   // block-wide exclusive scan of the winner counts (0..4 per thread): three ballots per warp, one barrier
-  const uint32_t nw = (uint32_t)w0 + (uint32_t)w1 + (uint32_t)w2 + (uint32_t)w3;
+  const uint32_t nw = __popc(d.win);
   const uint32_t b0 = __ballot_sync(0xffffffffu, nw & 1u), b1 = __ballot_sync(0xffffffffu, nw & 2u), b2 = __ballot_sync(0xffffffffu, nw & 4u);
   const uint32_t lt = (1u << lane) - 1u;
   const uint32_t excl = __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt);
@@ -803,17 +842,14 @@ __device__ __forceinline__ uint32_t ow_pass(const SearchParams &S, const OwLayou
   const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
   uint32_t dst = n_next + wbase + excl;
   // append the winners in (position, slot) order
-  auto append = [&](uint32_t ci, uint32_t xy) {
-    rk[ci] = (uint16_t)dst;
-    const uint2 entry = make_uint2(ci, xy);
-    if (dst < S.ow_qcap) Q.q[(cur ^ 1u) * OW_QCAP + dst] = entry;
-    if (WIDE && Q.to_global) Q.g[(cur ^ 1u) * Q.gcap + dst] = entry;
-    ++dst;
-  };
-  if (w0) append(i0, e.y - 1u);
-  if (w1) append(i1, e.y + 1u);
-  if (w2) append(i2, e.y - (1u << 14));
-  if (w3) append(i3, e.y + (1u << 14));
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (d.win & (1u << k)) {
+      rk[d.ci[k]] = (uint16_t)dst;
+      if (dst < S.ow_qcap) Q.q[(cur ^ 1u) * OW_QCAP + dst] = d.ent[k];
+      if (WIDE && Q.to_global) Q.g[(cur ^ 1u) * Q.gcap + dst] = d.ent[k];
+      ++dst;
+    }
   OW_STAMP(5, dst);
   return total;
 }
@@ -855,12 +891,11 @@ ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim,
     __syncthreads();
   }
   const uint32_t start = s_start;
-  const uint32_t safe = ow_rk_fx(4u) + ow_rk_fy(4u, L.rk_yt);  // a padding cell with padding all around it
   if (threadIdx.x == 0) {
     cnt->start_cell = start;
     const uint32_t sy = start / W, sx = start - sy * W;
-    const uint32_t si = ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD, L.rk_yt);
-    Q.q[0] = make_uint2(si, sx | (sy << 14));
+    uint32_t si;
+    Q.q[0] = ow_start_entry(L, rk, sx, sy, &si);
     rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56), whatever its class
   }
   __syncthreads();
@@ -874,7 +909,7 @@ ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim,
     OW_STAMP(7, n);
     uint32_t n_next = 0;
     for (uint32_t tile = 0; tile < n; tile += OW_THREADS) {
-      n_next += ow_pass<WIDE>(S, L, rk, claim, Q, cur, safe, tile, n, base, n_next, s_wsum + (scans & 1u) * 32u, pf);
+      n_next += ow_pass<WIDE>(S, L, rk, claim, Q, cur, tile, n, base, n_next, s_wsum + (scans & 1u) * 32u, pf);
       ++scans;
     }
     if (threadIdx.x == 0) s_n = n_next;  // warp 0 works in every pass: its total is the level's
@@ -925,12 +960,9 @@ ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim,
 //   * the level queue lives in distributed shared memory: positions [r * per, (r + 1) * per) of a level are CTA r's
 //     slice (per = a power of two >= n / CTAs), and whoever appends a cell stores its entry straight into the slice of
 //     the CTA that will dequeue it (st.shared::cluster through cluster.map_shared_rank).
-//   * positions (2 bytes per cell, the tiled array of the single-CTA kernel, OW_OPEN = none) go through L2 (ld.global.cg /
-//     plain stores): written in one level, read in the next, with a cluster barrier (release / acquire) in between.
-//   * the static class bytes (bit k: neighbour k is expandable, bit 4 + k: neighbour k is a frontier-mask cell; same tile
-//     geometry) are read-only for the kernel; the appender loads the new cell's byte next to its position loads and puts
-//     the candidate directions (expandable and not visited: the visited ones are the cells that competed for it, which
-//     its winner saw while deciding) into the entry, so a level has one dependent L2 round trip.
+//   * the state array (class or position, 2 bytes per cell, as in the single-CTA kernel) goes through L2 (ld.global.cg /
+//     plain stores): positions are written in one level and read in the next, with a cluster barrier (release / acquire)
+//     in between; one dependent L2 round trip per level.
 //   * order: a CTA's winners go, in (position, slot) order, into a local list; the CTAs' counts are exchanged through
 //     distributed shared memory; after a cluster barrier every CTA knows its base and the level's size, stores the
 //     positions and the entries of its winners, and a second cluster barrier ends the level.
@@ -938,44 +970,9 @@ static constexpr int OWC_THREADS = 512;
 static constexpr uint32_t OWC_SLICE = 4096;             // queue entries per CTA and level (16 CTAs: levels up to OW_MAX_LEVEL)
 static constexpr uint32_t OWC_LOCAL = 3 * OWC_SLICE;    // winners of one CTA in one level: at most 3 per dequeued cell
 static constexpr uint32_t OWC_SMEM = (2 * OWC_SLICE + OWC_LOCAL) * 8;
-static constexpr uint32_t OWC_NONE = 0xFFFFu;
 
-// class bytes + "no position" for the tiles of the search disc's bounding box (see ow_prep_kernel)
-__global__ void __launch_bounds__(256)
-owc_prep_kernel(const SearchParams S, const OwLayout L, const uint32_t *__restrict__ ebits, const uint32_t *__restrict__ mbits,
-                uint8_t *__restrict__ cls, uint16_t *__restrict__ rk, uint32_t tx0, uint32_t ty0, uint32_t ntx, uint32_t nty) {
-  const uint64_t n = (uint64_t)ntx * nty * 8u;
-  const uint32_t W = S.map.W, H = S.map.H;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-    const uint32_t r = (uint32_t)(i / ntx), bx = tx0 + (uint32_t)(i - (uint64_t)r * ntx);
-    const uint32_t Y = ty0 * 8u + r, X0 = bx * 16u;
-    const int y = (int)Y - (int)OW_PAD, xs = (int)X0 - (int)OW_PAD - 1;  // bit j of the row words below = column xs + j
-    uint32_t out[4] = {0u, 0u, 0u, 0u};
-    if (y >= 0 && y < (int)H) {
-      const uint32_t em = row_bits(ebits, S.wpr, H, y, xs), eu = row_bits(ebits, S.wpr, H, y - 1, xs), ed = row_bits(ebits, S.wpr, H, y + 1, xs);
-      const uint32_t mm = row_bits(mbits, S.wpr, H, y, xs), mu = row_bits(mbits, S.wpr, H, y - 1, xs), md = row_bits(mbits, S.wpr, H, y + 1, xs);
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const int x = xs + 1 + k;
-        if (x < 0 || x >= (int)W) continue;
-        const uint32_t b = ((em >> k) & 1u) | (((em >> (k + 2)) & 1u) << 1) | (((eu >> (k + 1)) & 1u) << 2) | (((ed >> (k + 1)) & 1u) << 3) |
-                           (((mm >> k) & 1u) << 4) | (((mm >> (k + 2)) & 1u) << 5) | (((mu >> (k + 1)) & 1u) << 6) | (((md >> (k + 1)) & 1u) << 7);
-        out[k >> 2] |= b << (8 * (k & 3));
-      }
-    }
-    const size_t at = ((size_t)(Y >> 3) * L.txr + 2u * bx) * 64u + (Y & 7u) * 8u;  // first of the two tiles' rows
-    *reinterpret_cast<uint2 *>(cls + at) = make_uint2(out[0], out[1]);
-    *reinterpret_cast<uint2 *>(cls + at + 64) = make_uint2(out[2], out[3]);
-    const uint4 none = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-    *reinterpret_cast<uint4 *>(rk + at) = none;
-    *reinterpret_cast<uint4 *>(rk + at + 64) = none;
-  }
-}
-
-// queue entry: .x = x | y << 14 | candidate directions << 28, .y = directions of the frontier-mask neighbours
 __global__ void __launch_bounds__(OWC_THREADS, 1)
-ow_cluster_kernel(const SearchParams S, const OwLayout L, const uint8_t *__restrict__ cls, uint16_t *rk, uint32_t *claim, uint32_t *queue,
-                  Counters *cnt, uint32_t n_parts) {
+ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim, uint32_t *queue, Counters *cnt, uint32_t n_parts) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const uint32_t CS = cluster.num_blocks(), rank = cluster.block_rank();
@@ -1008,8 +1005,8 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, const uint8_t *__restr
       const uint32_t start = s_start;
       cnt->start_cell = start;
       const uint32_t sy = start / W, sx = start - sy * W;
-      const uint32_t si = ow_rk_fx(sx + OW_PAD) + ow_rk_fy(sy + OW_PAD, L.rk_yt);
-      qs[0] = make_uint2(sx | (sy << 14) | ((uint32_t)cls[si] << 28), (uint32_t)cls[si] >> 4);
+      uint32_t si;
+      qs[0] = ow_start_entry(L, rk, sx, sy, &si);
       rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56)
     }
   }
@@ -1032,46 +1029,15 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, const uint8_t *__restr
       uint32_t *ws = s_ws[scans & 1u];
       ++scans;
       const uint32_t pl = tile + threadIdx.x;
-      uint32_t wmask = 0u, xy = 0u, o0 = 0u, o1 = 0u, o2 = 0u, o3 = 0u, m0 = 0u, m1 = 0u, m2 = 0u, m3 = 0u;
+      OwCell d;
+      d.win = 0u;
       if (tile + (wid << 5) < m) {  // warp-uniform
         uint2 e = make_uint2(0u, 0u);
         if (pl < m) e = q[pl];
-        const uint32_t pos = lo + pl, cand = e.x >> 28, mk = e.y;
-        xy = e.x & 0x0FFFFFFFu;
-        const uint32_t x = xy & 0x3FFFu, y = xy >> 14;
-        const uint32_t i = ow_rk_fx(x + OW_PAD) + ow_rk_fy(y + OW_PAD, L.rk_yt);
-        const uint32_t tx = i & 7u, ty = i & 56u;
-        const uint32_t xa = tx < 2u ? 58u : 2u, xb = tx < 1u ? 57u : 1u, xd = tx > 6u ? 57u : 1u, xe = tx > 5u ? 58u : 2u;
-        const uint32_t ya = (ty < 16u ? L.rk_yt : 0u) + 16u, yb = (ty < 8u ? L.rk_yt : 0u) + 8u, yd = (ty > 48u ? L.rk_yt : 0u) + 8u,
-                       ye = (ty > 40u ? L.rk_yt : 0u) + 16u;
-        const uint32_t i0 = i - xb, i1 = i + xd, i2 = i - yb, i3 = i + yd;
-        const uint32_t l2 = (cand & 1u) ? (uint32_t)__ldcg(rk + i - xa) : OWC_NONE, r2 = (cand & 2u) ? (uint32_t)__ldcg(rk + i + xe) : OWC_NONE;
-        const uint32_t u2 = (cand & 4u) ? (uint32_t)__ldcg(rk + i - ya) : OWC_NONE, d2 = (cand & 8u) ? (uint32_t)__ldcg(rk + i + ye) : OWC_NONE;
-        const uint32_t ul = (cand & 5u) ? (uint32_t)__ldcg(rk + i0 - yb) : OWC_NONE, ur = (cand & 6u) ? (uint32_t)__ldcg(rk + i1 - yb) : OWC_NONE;
-        const uint32_t dl = (cand & 9u) ? (uint32_t)__ldcg(rk + i0 + yd) : OWC_NONE, dr = (cand & 10u) ? (uint32_t)__ldcg(rk + i1 + yd) : OWC_NONE;
-        const uint32_t k0c = (cand & 1u) ? (uint32_t)__ldg(cls + i0) : 0u, k1c = (cand & 2u) ? (uint32_t)__ldg(cls + i1) : 0u;
-        const uint32_t k2c = (cand & 4u) ? (uint32_t)__ldg(cls + i2) : 0u, k3c = (cand & 8u) ? (uint32_t)__ldg(cls + i3) : 0u;
-        if (mk) {  // frontier-mask neighbours record the first touch (isNewFrontierCell branch, FrontierSearch.cpp:78-81)
-          const uint32_t key = TOUCH_BIT | ((base + pos) << 2);
-          uint32_t *at = claim + (size_t)y * W + x;
-          if (mk & 1u) atomicMin(at - 1, key);
-          if (mk & 2u) atomicMin(at + 1, key | 1u);
-          if (mk & 4u) atomicMin(at - W, key | 2u);
-          if (mk & 8u) atomicMin(at + W, key | 3u);
-        }
-        if ((cand & 1u) && min(l2, min(ul, dl)) > pos) wmask |= 1u;
-        if ((cand & 2u) && min(r2, min(ur, dr)) > pos) wmask |= 2u;
-        if ((cand & 4u) && min(u2, min(ul, ur)) > pos) wmask |= 4u;
-        if ((cand & 8u) && min(d2, min(dl, dr)) > pos) wmask |= 8u;
-        // candidate directions of the cells this one visits: expandable neighbours minus its level-d neighbours (this
-        // cell and whichever cells at distance 2 have a position)
-        const uint32_t hl2 = l2 < OW_MAX_LEVEL, hr2 = r2 < OW_MAX_LEVEL, hu2 = u2 < OW_MAX_LEVEL, hd2 = d2 < OW_MAX_LEVEL;
-        const uint32_t hul = ul < OW_MAX_LEVEL, hur = ur < OW_MAX_LEVEL, hdl = dl < OW_MAX_LEVEL, hdr = dr < OW_MAX_LEVEL;
-        o0 = (xy - 1u) | ((k0c & ~(2u | hl2 | (hul << 2) | (hdl << 3))) << 28); m0 = k0c >> 4;
-        o1 = (xy + 1u) | ((k1c & ~(1u | (hr2 << 1) | (hur << 2) | (hdr << 3))) << 28); m1 = k1c >> 4;
-        o2 = (xy - (1u << 14)) | ((k2c & ~(8u | hul | (hur << 1) | (hu2 << 2))) << 28); m2 = k2c >> 4;
-        o3 = (xy + (1u << 14)) | ((k3c & ~(4u | hdl | (hdr << 1) | (hd2 << 3))) << 28); m3 = k3c >> 4;
+        ow_decide(L, e, lo + pl, [&](uint32_t at) { return (uint32_t)__ldcg(rk + at); }, d);
+        ow_touch(claim, W, e, base + lo + pl);
       }
+      const uint32_t wmask = d.win;
       // CTA-wide exclusive scan of the winner counts (0..4 per thread): three ballots per warp, one barrier
       const uint32_t nw = __popc(wmask);
       const uint32_t b0 = __ballot_sync(0xffffffffu, nw & 1u), b1 = __ballot_sync(0xffffffffu, nw & 2u), b2 = __ballot_sync(0xffffffffu, nw & 4u);
@@ -1085,10 +1051,9 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, const uint8_t *__restr
       uint32_t dst = n_local + wbase + excl;
       if (n_local + total > OWC_LOCAL) bad = true;  // (uniform; cannot happen: at most 3 winners per dequeued cell, 4 at the start)
       else {
-        if (wmask & 1u) lout[dst++] = make_uint2(o0, m0);
-        if (wmask & 2u) lout[dst++] = make_uint2(o1, m1);
-        if (wmask & 4u) lout[dst++] = make_uint2(o2, m2);
-        if (wmask & 8u) lout[dst++] = make_uint2(o3, m3);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (wmask & (1u << k)) lout[dst++] = d.ent[k];
       }
       n_local += total;
     }
@@ -1728,9 +1693,7 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
     const uint64_t pc = (uint64_t)L.Wp * L.Hp;
     if (s->rk.cap < pc || s->ow_cells != pc) {  // padding: OW_BLOCKED (0xFDFD is above OW_MAX_LEVEL and none of the other classes)
       FS_CUDA(c, s->rk.reserve(pc));
-      FS_CUDA(c, s->cls.reserve(pc));
       FS_CUDA(c, cudaMemsetAsync(s->rk.p, 0xFD, s->rk.cap * sizeof(uint16_t), c->stream));
-      FS_CUDA(c, cudaMemsetAsync(s->cls.p, 0, s->cls.cap, c->stream));
       s->ow_cells = pc;
     }
   }
@@ -1947,8 +1910,9 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     // search on a map: by the size of the search disc)
     const uint32_t guess = s->last.bfs_levels ? s->last.widest_level : (uint32_t)std::min<double>(S.dist_limit / c->res, 1e9);
     const bool cluster = s->ow_cluster && guess >= s->ow_cluster_min;
+    ow_prep_kernel<<<wide, 256, 0, c->stream>>>(S, L, s->ebits.p, s->bits.p, s->rk.p, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
+    ++c->launches;
     if (cluster) {
-      owc_prep_kernel<<<wide, 256, 0, c->stream>>>(S, L, s->ebits.p, s->bits.p, s->cls.p, s->rk.p, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(s->ow_cluster);
       cfg.blockDim = dim3(OWC_THREADS);
@@ -1959,12 +1923,9 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
       at[0].val.clusterDim.x = s->ow_cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at;
       cfg.numAttrs = 1;
-      FS_CUDA(c, cudaLaunchKernelEx(&cfg, ow_cluster_kernel, S, L, (const uint8_t *)s->cls.p, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts));
+      FS_CUDA(c, cudaLaunchKernelEx(&cfg, ow_cluster_kernel, S, L, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts));
       ++c->launches;
-    } else {
-      ow_prep_kernel<<<wide, 256, 0, c->stream>>>(S, L, s->ebits.p, s->bits.p, s->rk.p, tx0, ty0, tx1 - tx0 + 1, ty1 - ty0 + 1);
     }
-    ++c->launches;
     // the search on the context stream; behind each published part but the last, a collection on the second stream
     if (cluster) {
     } else if (s->prefer_wide && S.ow_wide)
