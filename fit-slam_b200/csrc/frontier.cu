@@ -1255,7 +1255,6 @@ replay_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t 
   const uint32_t n_comp = min(cnt->n_comp, S.comp_cap);
   if (cnt->overflow) return;
   for (uint32_t comp = blockIdx.x; comp < n_comp; comp += gridDim.x) {
-    if (S.use_smem && osize[comp] <= IW_CELLS) continue;  // replay_warp_kernel took it
     uint32_t *out = cells + ocell0[comp];
     const uint32_t seed = oseed[comp];
     if (threadIdx.x == 0) {
@@ -1423,6 +1422,65 @@ replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, cons
       n = n_next;
     }
     __syncwarp();
+  }
+}
+
+// The inner wavefront of a component above IW_SMALL cells: one warp, ONE dequeued cell per step, lane s < 8 takes its
+// neighbour s in the reference's order.  Components of this class are long and thin (arcs of sensor discs: 1-2 cells per
+// level for thousands of levels), so what bounds them is the latency of a step; a step here is a shared-memory read of
+// the queue head (the queue's tail is mirrored in a ring), a mask-bit load, a load of the neighbour's visited flag (the
+// top bit of its slot[] word: slot[] is rewritten by every search, and a cell belongs to one component only) and a
+// ballot that appends the accepted neighbours in slot order.  Exactly buildNewFrontier's loop (FrontierSearch.cpp:123-189).
+static constexpr uint32_t IL_RING = 2048;
+static constexpr uint32_t IL_VISITED = 0x80000000u;
+__global__ void __launch_bounds__(32)
+replay_line_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint32_t *slot, const uint32_t *__restrict__ oseed,
+                   const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0, uint32_t *cells, const Counters *cnt,
+                   uint32_t min_cells, uint32_t max_cells, int coll) {
+  __shared__ uint32_t ring[IL_RING];
+  const uint32_t W = S.map.W, H = S.map.H;
+  if (cnt->overflow) return;
+  const uint32_t c_lo = coll < 0 ? 0u : cnt->coll_c0[coll], c_hi = min(coll < 0 ? cnt->n_comp : cnt->coll_c1[coll], S.comp_cap);
+  const uint32_t lane = threadIdx.x, sl = lane & 7u;
+  const bool act = lane < 8u;
+  // neighbour sl in the reference's order: -1, +1, -W, +W, -1-W, -1+W, +1-W, +1+W (DEP/src/Helpers.cpp:185-255)
+  const int ddx = (int)((0xA058u >> (2 * sl)) & 3u) - 1, ddy = (int)((0x8885u >> (2 * sl)) & 3u) - 1;
+  const uint32_t mW = 0xFFFFFFFFu / W;  // floor(2^32 / W), or one less: the quotient estimate below is at most 2 short
+  const uint32_t lt = (1u << lane) - 1u;
+  for (uint32_t comp = c_lo + blockIdx.x; comp < c_hi; comp += gridDim.x) {
+    const uint32_t size = osize[comp];
+    if (size < min_cells || size > max_cells) continue;
+    uint32_t *out = cells + ocell0[comp];
+    if (lane == 0) {
+      const uint32_t seed = oseed[comp];
+      out[0] = seed;
+      ring[0] = seed;
+      slot[seed] |= IL_VISITED;
+    }
+    __syncwarp();
+    uint32_t head = 0, tail = 1;
+    while (head < tail) {
+      // (the ring holds positions [tail - IL_RING, tail): a level wider than that reads the list itself, through L2)
+      const uint32_t p = (tail - head <= IL_RING) ? ring[head & (IL_RING - 1u)] : ld_cg(out + head);
+      ++head;
+      uint32_t y = __umulhi(p, mW), x = p - y * W;
+      while (x >= W) { x -= W; ++y; }
+      const int nx = (int)x + ddx, ny = (int)y + ddy;
+      const bool in = act && nx >= 0 && ny >= 0 && nx < (int)W && ny < (int)H;
+      const uint32_t nb = (uint32_t)ny * W + (uint32_t)nx;
+      const bool bit = in && ((__ldg(bits + (size_t)ny * S.wpr + ((uint32_t)nx >> 5)) >> ((uint32_t)nx & 31u)) & 1u);
+      const uint32_t sv = bit ? slot[nb] : IL_VISITED;  // isNewFrontierCell: a mask cell whose frontier_flag is not set yet
+      const bool acc = !(sv & IL_VISITED);
+      const uint32_t bal = __ballot_sync(0xffffffffu, acc);
+      if (acc) {
+        const uint32_t at = tail + __popc(bal & lt);
+        slot[nb] = sv | IL_VISITED;
+        out[at] = nb;
+        ring[at & (IL_RING - 1u)] = nb;
+      }
+      tail += __popc(bal);
+      __syncwarp();
+    }
   }
 }
 
@@ -1863,8 +1921,8 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
         if (e == cudaSuccess) e = cudaStreamWaitEvent(st_large, s->ev_coll[coll], 0);
         if (e != cudaSuccess) return e;
       }
-      replay_warp_kernel<<<148 * 2, 32, iw_smem(IW_CELLS, IW_BITS_LARGE), st_large>>>(
-          S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, IW_SMALL + 1, IW_CELLS, IW_BITS_LARGE, coll);
+      replay_line_kernel<<<148 * 4, 32, 0, st_large>>>(S, s->bits.p, s->slot.p, s->oseed.p, s->osize.p, s->ocell0.p, s->cells.p, cnt,
+                                                       IW_SMALL + 1, 0xFFFFFFFFu, coll);
       replay_warp_kernel<<<148 * 16, 32, iw_smem(IW_SMALL, IW_BITS_SMALL), st>>>(
           S, s->bits.p, s->tm.p, s->oseed.p, s->osize.p, s->ocell0.p, s->obox.p, s->cells.p, cnt, 0, IW_SMALL, IW_BITS_SMALL, coll);
       c->launches += 2;
@@ -1873,7 +1931,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
         // on the stream that replayed it (frontier.cu knows nothing about scoring: cycle.cu's hook launches it)
         const uint32_t *range = &cnt->coll_fr[coll][0];
         cudaStream_t sts[2] = {st, st_large};
-        const uint32_t lo[2] = {0u, IW_SMALL + 1u}, hi[2] = {IW_SMALL, IW_CELLS};
+        const uint32_t lo[2] = {0u, IW_SMALL + 1u}, hi[2] = {IW_SMALL, 0xFFFFFFFFu};
         for (int cls = 0; cls < 2; ++cls) {
           const uint32_t tag = 1u + 2u * (uint32_t)coll + (uint32_t)cls;
           chunk_kernel<<<148 * 2, 64, 0, sts[cls]>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
@@ -1954,8 +2012,8 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[4], c->stream));
   FS_CUDA(c, collect(c->stream, c->stream, -1));
-  replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p,
-                                                            s->cells.p, cnt);  // components above IW_CELLS cells
+  if (!S.use_smem)  // (the global-memory path replays every component here)
+    replay_kernel<<<148 * 8, REPLAY_THREADS, 0, c->stream>>>(S, s->bits.p, s->claim.p, s->oseed.p, s->osize.p, s->ocell0.p, s->cells.p, cnt);
   if (side)  // the large inner wavefronts still running on their streams: the frontiers not built yet may be theirs
     for (int i = 0; i < OW_LARGE_STREAMS; ++i) {
       FS_CUDA(c, cudaEventRecord(s->ev_join_large[i], s->stream_large[i]));
@@ -1965,7 +2023,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
                                                s->centroids.p, s->ftag.p, cnt, -1, 0, 0xFFFFFFFFu, TAG_FINAL);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
-  c->launches += 3;  // legacy replay, chunk, cleanup
+  c->launches += S.use_smem ? 2 : 3;  // (legacy replay,) chunk, cleanup
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[5], c->stream));
   if (side && hook)
     for (int i = 0; i < 1 + OW_LARGE_STREAMS; ++i) {  // scores of the early batches: complete when the search is
