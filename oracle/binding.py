@@ -1,4 +1,4 @@
-"""ctypes view of oracle/liboracle.so.  TEST INFRASTRUCTURE ONLY (PARITY UNPINNED, see oracle.cpp header):
+"""ctypes view of oracle/liboracle.so.  TEST INFRASTRUCTURE ONLY (parity: see the oracle.cpp header and oracle/ref_binding.py):
 imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs, never by
 the product."""
 import ctypes as C

@@ -4,13 +4,18 @@
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this library.
 // The product (fit-slam_b200/csrc) never links, imports or calls it.
 //
-// *** PARITY UNPINNED. ***  The reference ships no golden vectors, known-answer tests or fixtures for
-// this path and its translation units cannot be compiled here (they need
-// ROS 2 / Nav2 / tf2 / Eigen / Boost, none of which exist in this image).  This file therefore
-// restates the reference function by function, each block citing the file:line it follows; the only
-// reference test that applies (ORBW/tests/typeConversionsTests.cpp:8-33, SE3 ROS<->ORB round trip) is
-// reproduced against orc_se3_roundtrip() in tests/test_oracle_fisher.py, and the hand-derivable
-// micro-cases of SURVEY.md 8c are pinned in tests/test_oracle_*.py.
+// *** PARITY: PINNED FOR STAGE S AND THE RAY HELPERS, UNPINNED FOR THE REST. ***
+// Pinned: the reference's own FrontierSearch.cpp, Frontier.cpp and the costmap half of Helpers.cpp compile from where
+// they lie against stand-in ROS headers (oracle/Makefile -> oracle/_ref/libfitslam_ref.so, oracle/ref_shims/), and
+// tests/test_ref_pin.py holds this file to that library bit for bit: searchFrom / nearestFreeCell / isNewFrontierCell /
+// buildNewFrontier / getCentroidOfCells / SortByMedianFunctor / getAllFrontiers (rows S1-S6), getTracedCells / bresenham2D /
+// isRobotFootprintInLethal / RayTracedCells (R2-R4, T4).
+// Unpinned: the reference ships no golden vectors, known-answer tests or fixtures for this path (SURVEY.md section 4 /
+// 8c), and the remaining translation units (CostCalculator.cpp, FrontierCostsManager.cpp, FullPathOptimizer.cpp,
+// FisherInfoManager.cpp, the ORB-SLAM3 wrapper) need ROS 2 nodes, PCL, Eigen, Sophus and Boost, none of which exist in this
+// image.  Those parts are restated function by function, each block citing the file:line it follows; the only reference
+// test that applies (ORBW/tests/typeConversionsTests.cpp:8-33, SE3 ROS<->ORB round trip) is reproduced against
+// orc_se3_roundtrip() in tests/test_oracle_micro.py, next to the hand-derivable micro-cases of SURVEY.md 8c.
 //
 // Path shorthand (all under /root/reference):
 //   DEP/  = dev_ws/src/DEPRECATED/frontier_exploration/frontier_exploration/

@@ -4,6 +4,8 @@ and the every_frontier cell list in acceptance order."""
 import numpy as np
 import pytest
 
+from oracle import ref_binding
+
 pytestmark = pytest.mark.gpu
 
 
@@ -28,6 +30,16 @@ def _compare(capi, oracle, a, meta, rx, ry, ov=None, expect_frontiers=True):
             np.testing.assert_array_equal(fr["goal_y"].view(np.uint64), wfr["goal_y"].view(np.uint64))
         if expect_frontiers:
             assert len(fr) > 0
+        if ref_binding.available() and a.size <= 1 << 22:
+            # ... and against the REFERENCE itself (oracle/_ref: DEP/src/FrontierSearch.cpp compiled where it lies)
+            n, rfr, rcells = ref_binding.Reference().search_frontiers(a, meta, params, rx, ry, capacity=1 << 18, cell_capacity=1 << 23)
+            assert max(n, 0) == len(fr)
+            np.testing.assert_array_equal(fr["goal_x"].view(np.uint64), rfr[:, 0].copy().view(np.uint64))
+            np.testing.assert_array_equal(fr["goal_y"].view(np.uint64), rfr[:, 1].copy().view(np.uint64))
+            np.testing.assert_array_equal(fr["size"].astype(np.float64), rfr[:, 2])
+            W = a.shape[1]
+            cw = np.stack([meta["ox"] + (cells % W + 0.5) * meta["res"], meta["oy"] + (cells // W + 0.5) * meta["res"]], axis=1)
+            np.testing.assert_array_equal(cw.view(np.uint64), rcells.copy().view(np.uint64))
         return fr, cells
     finally:
         ctx.close()

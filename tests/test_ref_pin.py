@@ -1,0 +1,172 @@
+"""Pins the oracle to the REFERENCE ITSELF: oracle/_ref/libfitslam_ref.so is DEP/src/FrontierSearch.cpp, Frontier.cpp and
+the costmap half of Helpers.cpp compiled from /root/reference where it lies (oracle/Makefile) against stand-in ROS
+headers.  Every comparison is exact: goal points and every_frontier coordinates bit for bit, sizes, orders, ray counts.
+Rows pinned: S1-S6 (searchFrom, nearestFreeCell, isNewFrontierCell, buildNewFrontier, centroid + median sort
+with glibc atan2, getAllFrontiers), R2-R4 (getTracedCells, bresenham2D, isRobotFootprintInLethal), T4 (RayTracedCells)."""
+import math
+
+import numpy as np
+import pytest
+
+from oracle import ref_binding
+
+pytestmark = pytest.mark.skipif(not ref_binding.available(), reason="oracle/_ref is built where /root/reference exists")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    return ref_binding.Reference()
+
+
+def _cells_world(cells, a, meta):
+    W = a.shape[1]
+    my, mx = cells // W, cells % W
+    return np.stack([meta["ox"] + (mx + 0.5) * meta["res"], meta["oy"] + (my + 0.5) * meta["res"]], axis=1)
+
+
+def _same_search(oracle, ref, a, meta, rx, ry, ov=None):
+    for k, v in (ov or {}).items():
+        setattr(oracle.params, k, v)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, rx, ry, capacity=1 << 17, cell_capacity=1 << 22)
+    n, rfr, rcells = ref.search_frontiers(a, meta, oracle.params, rx, ry, capacity=1 << 17, cell_capacity=1 << 22)
+    if n < 0:
+        assert st != 0 and len(fr) == 0
+        return 0
+    assert st == 0 and n == len(fr), (n, len(fr))
+    np.testing.assert_array_equal(fr["goal_x"].view(np.uint64), rfr[:, 0].copy().view(np.uint64))
+    np.testing.assert_array_equal(fr["goal_y"].view(np.uint64), rfr[:, 1].copy().view(np.uint64))
+    np.testing.assert_array_equal(fr["size"].astype(np.float64), rfr[:, 2])
+    assert len(cells) == len(rcells)
+    np.testing.assert_array_equal(_cells_world(cells.astype(np.int64), a, meta).view(np.uint64), rcells.copy().view(np.uint64))
+    return n
+
+
+@pytest.mark.parametrize("name", ["C1", "C3"])
+def test_reference_search_on_configs(oracle, ref, synth, name):
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    n = _same_search(oracle, ref, a, meta, meta["robot_x"], meta["robot_y"], dict(max_frontier_distance=ov["max_frontier_distance"]))
+    assert n > 100
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_reference_search_inflated_small_radius(oracle, ref, synth, seed):
+    a, meta = synth.make_costmap(701, 577, seed=seed, n_disc=12, r_lo=25, r_hi=70, n_holes=30, inflation=5 if seed % 2 else 0)
+    assert _same_search(oracle, ref, a, meta, meta["robot_x"], meta["robot_y"], dict(max_frontier_distance=6.0 + 3 * seed)) > 0
+
+
+def test_reference_search_cluster_size_parameters(oracle, ref, synth):
+    a, meta = synth.make_costmap(600, 600, seed=5, n_disc=10, r_lo=30, r_hi=80, n_holes=20)
+    for mn, mx in ((1, 20), (3, 7), (0, 40), (5, 62)):
+        assert _same_search(oracle, ref, a, meta, meta["robot_x"], meta["robot_y"],
+                            dict(min_frontier_cluster_size=mn, max_frontier_cluster_size=mx)) > 0
+
+
+def test_reference_search_random_noise(oracle, ref):
+    rng = np.random.default_rng(7)
+    for W, H in ((64, 48), (97, 131), (200, 200)):
+        for k in range(6):
+            a = rng.choice(np.array([0, 0, 0, 100, 200, 253, 254, 255, 255], np.uint8), size=(H, W))
+            meta = dict(res=0.05 if k % 2 else 0.1, ox=-1.3 * k, oy=0.7 * k)
+            rx = meta["ox"] + (W // 2 + 0.3) * meta["res"]
+            ry = meta["oy"] + (H // 2 + 0.6) * meta["res"]
+            _same_search(oracle, ref, a, meta, rx, ry, dict(max_frontier_distance=2.0 + k))
+
+
+@pytest.mark.parametrize("res", [0.05, 0.1, 1.0 / 16])
+def test_reference_straight_frontiers_median_sort(oracle, ref, res):
+    # straight axis-aligned frontiers found from their middle: two-branch chunks of collinear cells, whose median sort
+    # compares atan2 values that differ in the last place at 0.05 m (the case VERDICT r1 "What's weak" #2 names)
+    for W, H, horizontal in ((400, 40, True), (40, 400, False), (3000, 12, True)):
+        a = np.full((H, W), 255, np.uint8)
+        if horizontal:
+            a[H // 2:, :] = 0
+            a[H // 2 + 4:, :] = 254
+        else:
+            a[:, W // 2:] = 0
+            a[:, W // 2 + 4:] = 254
+        meta = dict(res=res, ox=-W * res / 2, oy=-H * res / 2)
+        cy, cx = (H // 2 + 1, W // 2) if horizontal else (H // 2, W // 2 + 1)
+        rx, ry = meta["ox"] + (cx + 0.5) * res, meta["oy"] + (cy + 0.5) * res
+        assert _same_search(oracle, ref, a, meta, rx, ry, dict(max_frontier_distance=500.0)) >= W * H // (40 * 21) - 2
+
+
+def test_reference_robot_on_lethal_unknown_and_off_map(oracle, ref, synth):
+    a, meta = synth.make_costmap(300, 300, seed=9, n_disc=6, r_lo=20, r_hi=50, n_holes=5)
+    H, W = a.shape
+    b = a.copy()
+    b[H // 2 - 3:H // 2 + 4, W // 2 - 3:W // 2 + 4] = 254       # nearestFreeCell has to walk out of a lethal block
+    _same_search(oracle, ref, b, meta, meta["robot_x"], meta["robot_y"])
+    b = a.copy()
+    b[H // 2 - 2:H // 2 + 3, W // 2 - 2:W // 2 + 3] = 255       # ... of an unknown block
+    _same_search(oracle, ref, b, meta, meta["robot_x"], meta["robot_y"])
+    _same_search(oracle, ref, a, meta, meta["ox"] - 1.0, meta["robot_y"])    # off the map: empty list
+    _same_search(oracle, ref, a, meta, meta["ox"] + W * meta["res"] + 0.01, meta["robot_y"])
+
+
+def test_reference_nearest_free_cell_and_neighbourhoods(oracle, ref):
+    rng = np.random.default_rng(3)
+    for _ in range(20):
+        W, H = int(rng.integers(3, 40)), int(rng.integers(3, 40))
+        a = rng.choice(np.array([0, 159, 160, 254, 255], np.uint8), size=(H, W), p=[0.1, 0.1, 0.3, 0.3, 0.2])
+        start = int(rng.integers(0, W * H))
+        assert oracle.nearest_free_cell(a, start, 160) == ref.nearest_free_cell(a, start, 160)
+    # corner, edge and interior cells: the order of nhood4 / nhood8 (DEP/src/Helpers.cpp:185-262)
+    W, H = 7, 5
+    for idx in (0, 3, 6, 7, 17, 28, 31, 34):
+        x, y = idx % W, idx // W
+        want4 = [i for ok, i in ((x > 0, idx - 1), (x < W - 1, idx + 1), (y > 0, idx - W), (y < H - 1, idx + W)) if ok]
+        assert ref.nhood(W, H, idx, False) == want4
+        assert ref.nhood(W, H, idx, True)[:len(want4)] == want4
+
+
+def _ray_ends(params, meta, a, gx, gy, poly):
+    """End points of the ray fan of setArrivalInformationForFrontier (DEP/src/CostCalculator.cpp:36-48)."""
+    H, W = a.shape
+    size_x, size_y = (W - 1 + 0.5) * meta["res"], (H - 1 + 0.5) * meta["res"]
+    ends = []
+    theta = 0.0
+    while theta <= 2 * math.pi:
+        wx = gx + params.max_camera_depth * math.cos(theta)
+        wy = gy + params.max_camera_depth * math.sin(theta)
+        wx = max(poly[0], max(meta["ox"], min(poly[2], min(meta["ox"] + size_x, wx))))
+        wy = max(poly[1], max(meta["oy"], min(poly[3], min(meta["oy"] + size_y, wy))))
+        ends.append((wx, wy))
+        theta += params.delta_theta
+    return ends
+
+
+def test_reference_traced_cells_and_footprint(oracle, ref, synth):
+    """Per-ray unknown-cell counts of the oracle's arrival stage == the reference's getTracedCells + RayTracedCells on the
+    same rays; its footprint flag == isRobotFootprintInLethal."""
+    a, meta = synth.make_costmap(400, 400, seed=11, n_disc=8, r_lo=20, r_hi=60, n_holes=15, inflation=3)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"])
+    assert st == 0 and len(fr) > 20
+    poly = [meta["ox"], meta["oy"], meta["ox"] + a.shape[1] * meta["res"], meta["oy"] + a.shape[0] * meta["res"]]
+    arr, rays, wins = oracle.score_arrival(a, meta, fr, poly)
+    max_length = float(int(oracle.params.max_camera_depth / meta["res"]))
+    radius_cells = math.ceil(oracle.params.robot_radius / meta["res"])
+    for f in range(0, len(fr), max(1, len(fr) // 40)):
+        gx, gy = float(fr["goal_x"][f]), float(fr["goal_y"][f])
+        ends = _ray_ends(oracle.params, meta, a, gx, gy, poly)
+        assert len(ends) == rays.shape[1]
+        for i, (wx, wy) in enumerate(ends):
+            ok, pushed, hit, unknown, allc = ref.traced_cells(a, meta, gx, gy, wx, wy, max_length)
+            assert ok and pushed == int(rays[f, i]), (f, i, pushed, int(rays[f, i]))
+        assert ref.footprint_in_lethal(a, meta, int(fr["goal_mx"][f]), int(fr["goal_my"][f]), radius_cells) == bool(arr["footprint_in_lethal"][f])
+
+
+def test_reference_roadmap_rays(oracle, ref, synth):
+    """FrontierRoadMap::isConnectable's ray (obstacle band 253..254, every cell traced) against the oracle's restatement."""
+    a, meta = synth.make_costmap(300, 300, seed=13, n_disc=6, r_lo=20, r_hi=50, n_holes=10, inflation=2)
+    rng = np.random.default_rng(5)
+    H, W = a.shape
+    seg = np.stack([meta["ox"] + rng.uniform(1, W - 1, 300) * meta["res"], meta["oy"] + rng.uniform(1, H - 1, 300) * meta["res"],
+                    meta["ox"] + rng.uniform(1, W - 1, 300) * meta["res"], meta["oy"] + rng.uniform(1, H - 1, 300) * meta["res"]], axis=1)
+    radius = 2.6
+    ok_o, unk_o = oracle.roadmap_connectable(a, meta, seg, radius)
+    for k, (sx, sy, ex, ey) in enumerate(seg):
+        ok, pushed, hit, unknown, allc = ref.traced_cells(a, meta, sx, sy, ex, ey, float(int(1.5 * radius / meta["res"])) if False else 1.5 * radius / meta["res"],
+                                                          obstacle=(253, 254), trace=(0, 255))
+        assert ok
+        want = (not hit) and unknown <= radius / meta["res"] * 0.3
+        assert bool(ok_o[k]) == want, (k, hit, unknown)
