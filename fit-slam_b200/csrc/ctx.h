@@ -210,6 +210,7 @@ __device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slo
 }
 #endif
 static constexpr uint32_t TAG_FINAL = 255;     // frontier produced after the search ended: scored by the host-sized launches
+static constexpr uint32_t TAG_HOST = 254;      // frontier whose median sort the host redoes after the search (then TAG_FINAL)
 static constexpr uint32_t EARLY_SLICE_CAP = 512;  // frontiers one early launch covers; what exceeds it is left to the final pass
 // called by the frontier search once per finished batch of frontiers, on a side stream (cycle.cu scores them there)
 struct EarlyHook {
@@ -227,7 +228,7 @@ fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, 
                                    const fitslam_arrival *d_arrival, uint32_t poses_per_frontier);
 bool fisher_ready(const fitslam_ctx *c);
 fitslam_status plan_euclidean_device(fitslam_ctx *c, uint32_t n, const fitslam_frontier *d_fr, const fitslam_arrival *d_arr,
-                                     double rx, double ry, double ryaw);
+                                     const double *d_goal_yaw, double rx, double ry, double ryaw);
 fitslam_status select_device(fitslam_ctx *c, uint32_t n, const fitslam_arrival *d_arr, const uint8_t *d_ach,
                              const uint8_t *d_bl, const double *d_len, const double *d_head);
 fitslam_status raycast_limits(fitslam_ctx *c);

@@ -25,6 +25,12 @@ struct CycleState {
   DevBuf<uint8_t> fisher_safe;
   DevBuf<uint32_t> fisher_nvis;
   DevBuf<double> yaw_q;        // per yaw window: qz, qw of orientationAroundZAxis(window * delta_theta + fov / 2)
+  // atan2(goal - robot) per frontier for the path heading, evaluated by the host's libm while the scoring kernels run
+  DevBuf<double> goal_yaw;
+  fitslam_frontier *h_fr = nullptr;  // pinned
+  double *h_yaw = nullptr;           // pinned
+  size_t h_cap = 0;
+  cudaEvent_t ev_fr = nullptr;
   uint32_t yaw_windows = 0;
   double yaw_dt = 0, yaw_fov = 0;
   cudaEvent_t ev[8] = {};
@@ -46,8 +52,13 @@ void destroy_cycle_state(fitslam_ctx *c) {
   if (!c->cy) return;
   CycleState *s = c->cy;
   s->poses.release(); s->fisher.release(); s->fisher_best.release(); s->fisher_safe.release(); s->fisher_nvis.release(); s->yaw_q.release();
-  if (s->have_events)
+  s->goal_yaw.release();
+  if (s->h_fr) cudaFreeHost(s->h_fr);
+  if (s->h_yaw) cudaFreeHost(s->h_yaw);
+  if (s->have_events) {
     for (auto &e : s->ev) cudaEventDestroy(e);
+    cudaEventDestroy(s->ev_fr);
+  }
   delete s;
   c->cy = nullptr;
 }
@@ -166,6 +177,7 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->open = false;
   if (!s->have_events) {
     for (auto &e : s->ev) FS_CUDA(c, cudaEventCreate(&e));
+    FS_CUDA(c, cudaEventCreateWithFlags(&s->ev_fr, cudaEventDisableTiming));
     s->have_events = true;
   }
   if (fisher_mode != FITSLAM_FISHER_OFF && !fisher_ready(c))
@@ -220,6 +232,19 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->res.ambiguous_sorts = ambiguous;
   if (n_frontiers) *n_frontiers = F;
   if (F == 0) return fail(c, FITSLAM_E_NO_FRONTIERS, "No frontiers found from frontier search.");
+  // the goal points come to the host now (70 KB at C2), ahead of the scoring launches below
+  if (s->h_cap < F) {
+    if (s->h_fr) cudaFreeHost(s->h_fr);
+    if (s->h_yaw) cudaFreeHost(s->h_yaw);
+    s->h_fr = nullptr; s->h_yaw = nullptr; s->h_cap = 0;
+    const size_t want = (size_t)F + F / 4 + 64;
+    FS_CUDA(c, cudaMallocHost((void **)&s->h_fr, want * sizeof(fitslam_frontier)));
+    FS_CUDA(c, cudaMallocHost((void **)&s->h_yaw, want * sizeof(double)));
+    s->h_cap = want;
+  }
+  FS_CUDA(c, s->goal_yaw.reserve(F));
+  FS_CUDA(c, cudaMemcpyAsync(s->h_fr, c->frontiers.p, (size_t)F * sizeof(fitslam_frontier), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaEventRecord(s->ev_fr, c->stream));
   // ---- arrival and Fisher information for this rank's share of the frontiers: the ones not scored during the search
   const uint64_t n_poses = (uint64_t)F * ppf;
   if (n_poses >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "cycle: too many candidate poses");
@@ -269,6 +294,10 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   }
   FS_CUDA(c, cudaEventRecord(s->ev[3], c->stream));
   FS_CUDA(c, cudaGetLastError());
+  // ... and while those kernels run: goal_yaw = atan2(goal - robot) with the reference's own libm (CostCalculator.cpp:469)
+  FS_CUDA(c, cudaEventSynchronize(s->ev_fr));
+  for (uint32_t i = 0; i < F; ++i) s->h_yaw[i] = atan2(s->h_fr[i].goal_y - ry, s->h_fr[i].goal_x - rx);
+  FS_CUDA(c, cudaMemcpyAsync(s->goal_yaw.p, s->h_yaw, (size_t)F * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   s->rx = rx; s->ry = ry; s->ryaw = ryaw;
   s->fisher_mode = fisher_mode;
   s->open = true;
@@ -288,7 +317,7 @@ fitslam_status fitslam_cycle_end(fitslam_ctx *c, fitslam_cycle_result *result) {
                                                                   c->prm.camera_fov / 2);
     ++c->launches;
   }
-  fitslam_status st = plan_euclidean_device(c, F, c->frontiers.p, c->arrival.p, s->rx, s->ry, s->ryaw);
+  fitslam_status st = plan_euclidean_device(c, F, c->frontiers.p, c->arrival.p, s->goal_yaw.p, s->rx, s->ry, s->ryaw);
   if (st != FITSLAM_OK) return st;
   FS_CUDA(c, cudaEventRecord(s->ev[5], c->stream));
   SelectState *ss = sstate(c);

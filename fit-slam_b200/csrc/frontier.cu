@@ -18,6 +18,7 @@
 // decides locally whether it is the first in queue order to reach a neighbour (it reads the ranks of the neighbour's
 // other neighbours; no atomics, no sort) and an order-preserving block scan appends the winners to the queue.
 #include "ctx.h"
+#include "atan2_cr.h"
 
 #include <cooperative_groups.h>
 
@@ -70,7 +71,7 @@ struct Counters {
   uint32_t bfs_levels;
   uint32_t start_cell;
   uint32_t overflow;       // bit0 mask list, bit1 bfs queue, bit2 component table
-  uint32_t ambiguous;      // chunk sorts with two angles within 4 ulp, or a comparator walk off the array
+  uint32_t ambiguous;      // chunk sorts handed to the host (see chunk_kernel): entries of the fix list
   uint32_t expanded;       // reachable cells dequeued by the outer wavefront
   uint32_t visited;        // queue entries + far cells (cleanup bound)
   uint32_t dirty_queue;    // entries of queue[] whose claim words (and their 4 neighbours') the cleanup must reset
@@ -103,6 +104,7 @@ struct SearchParams {
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
   uint32_t ow_part_levels; // levels per launch of the shared-memory outer wavefront
   uint32_t early_cap;      // frontiers one early scoring launch covers (what exceeds it waits for the launches after the search)
+  uint32_t fix_all;        // FITSLAM_FIX_ALL=1: every chunk's median sort goes to the host (test of that path)
 };
 
 struct FrontierState {
@@ -128,7 +130,10 @@ struct FrontierState {
   DevBuf<uint32_t> oseed, osize, ocell0, ofront0;    // component table in discovery order + offsets
   DevBuf<uint32_t> cells;     // every_frontier list, discovery order
   DevBuf<double> centroids;   // per frontier: centroid after the offset rule (stage dump)
-  DevBuf<uint8_t> ftag;       // per frontier: 0 = not built yet, else the launch that scores it (ctx.h: TAG_FINAL, early tags)
+  DevBuf<uint8_t> ftag;       // per frontier: 0 = not built yet, else the launch that scores it (ctx.h: TAG_FINAL, TAG_HOST, early tags)
+  DevBuf<uint32_t> fix_list;  // frontiers whose median sort the host redoes with its own libm (chunk_kernel), in append order
+  DevBuf<uint32_t> fix_stage; // per fix-list entry: frontier, cell count, cells / the host's answers on the way back
+  std::vector<uint32_t> fix_host;
   DevBuf<Counters> counters;
   double search_distance = -1.0;  // < 0: use params.max_frontier_distance
   uint64_t claim_cells = 0;   // cells for which claim is known to be all KEY_INF
@@ -176,7 +181,7 @@ void destroy_frontier_state(fitslam_ctx *c) {
     for (auto &st : s->score_stream) cudaStreamDestroy(st);
   }
   s->oseed.release(); s->osize.release(); s->ocell0.release(); s->ofront0.release();
-  s->cells.release(); s->centroids.release(); s->ftag.release(); s->counters.release();
+  s->cells.release(); s->centroids.release(); s->ftag.release(); s->counters.release(); s->fix_list.release(); s->fix_stage.release();
   delete s;
   c->fs = nullptr;
 }
@@ -1630,7 +1635,8 @@ __device__ void s_std_sort(SortCtx &sc) {
 __global__ void __launch_bounds__(64)
 chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uint32_t *__restrict__ ocell0,
              const uint32_t *__restrict__ ofront0, const uint32_t *__restrict__ cells, fitslam_frontier *out,
-             double *centroids, uint8_t *ftag, Counters *cnt, int coll, uint32_t min_cells, uint32_t max_cells, uint32_t tag) {
+             double *centroids, uint8_t *ftag, uint32_t *fix_list, Counters *cnt, int coll, uint32_t min_cells, uint32_t max_cells,
+             uint32_t tag) {
   // coll >= 0: the frontiers of collection `coll` whose component is in the size class [min_cells, max_cells] (its inner
   // wavefronts have just been replayed on this stream), at most EARLY_SLICE_CAP of them; they get `tag`, and the launch
   // that scores them follows on the same stream.  coll < 0, after the search: every frontier not built yet, TAG_FINAL.
@@ -1677,22 +1683,39 @@ chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uin
     const double distance_to_offset = S.map.res * 1.414 * 2;
     if (varX > varY && offset_centroid) centerY -= distance_to_offset;
     if (varX < varY && offset_centroid) centerX -= distance_to_offset;
+    // Angles: correctly rounded (atan2_cr.h).  glibc's atan2, which the reference sorts by, returns the same value unless the
+    // exact one lies within 0.03 ulp of a rounding boundary (`risky`), and then at most its neighbour.  A risky angle can
+    // only change the outcome where a comparison hangs on its last bit: another angle within 2 ulp, or one of the
+    // comparator's thresholds.  Such a chunk (in practice: collinear cells of a straight axis-aligned frontier, whose
+    // angles all sit within a few ulp of pi / 2) is sorted again by the host with its own libm (fix_flagged_frontiers).
+    unsigned long long risky = 0ull;
     for (int k = 0; k < n; ++k) {
       const uint32_t c = cl[k];
       const uint32_t my = c / W, mx = c - my * W;
-      double a = atan2((S.map.oy + (my + 0.5) * S.map.res) - centerY, (S.map.ox + (mx + 0.5) * S.map.res) - centerX);
+      bool rk;
+      double a = atan2cr::atan2_cr((S.map.oy + (my + 0.5) * S.map.res) - centerY, (S.map.ox + (mx + 0.5) * S.map.res) - centerX, &rk);
       if (a < 0) a = a + (2 * M_PI);
       ang[k] = a;
       idx[k] = (uint8_t)k;
+      if (rk) risky |= 1ull << k;
     }
     SortCtx sc{ang, idx, n, false};
     s_std_sort(sc);
-    bool ambiguous = sc.bad;
-    for (int k = 0; k + 1 < n; ++k) {
-      const long long a = __double_as_longlong(ang[idx[k]]), b = __double_as_longlong(ang[idx[k + 1]]);
-      if (a != b && llabs(a - b) <= 4) ambiguous = true;  // device atan2 is within 2 ulp of libm's
+    bool to_host = sc.bad || S.fix_all;
+    if (risky && !to_host) {
+      const long long t0 = __double_as_longlong(M_PI / 2), t1 = __double_as_longlong(3 * M_PI / 2), t2 = __double_as_longlong(2 * M_PI);
+      for (int k = 0; k < n && !to_host; ++k) {
+        if (!((risky >> k) & 1ull)) continue;
+        const long long a = __double_as_longlong(ang[k]);  // (angles are in [0, 2 pi]: bit distance = distance in ulp)
+        if (llabs(a - t0) <= 2 || llabs(a - t1) <= 2 || llabs(a - t2) <= 2) to_host = true;
+        for (int j = 0; j < n; ++j)
+          if (j != k && llabs(a - __double_as_longlong(ang[j])) <= 2) to_host = true;
+      }
     }
-    if (ambiguous) atomicAdd(&cnt->ambiguous, 1u);
+    if (to_host) {
+      atomicAdd(&cnt->ambiguous, 1u);
+      fix_list[atomicAdd(&cnt->pad0[0], 1u)] = f;  // (one entry per frontier at most: the list holds front_cap)
+    }
     const uint32_t g = cl[idx[n / 2]];
     fitslam_frontier r;
     r.goal_my = g / W;
@@ -1704,12 +1727,35 @@ chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uin
     r.chunk = j;
     r.first_cell = first_cell;
     out[f] = r;
-    ftag[f] = (uint8_t)tag;
+    ftag[f] = (uint8_t)(to_host ? TAG_HOST : tag);
     if (centroids) {
       centroids[2 * f] = centerX;
       centroids[2 * f + 1] = centerY;
     }
   }
+}
+
+// ---- the chunks whose median sort goes to the host (chunk_kernel)
+static constexpr uint32_t FIX_WORDS = 2 + MAX_CHUNK;  // per entry: frontier, cell count, cells
+__global__ void fix_gather_kernel(const uint32_t *__restrict__ fix_list, uint32_t n, const fitslam_frontier *__restrict__ fr,
+                                  const uint32_t *__restrict__ cells, uint32_t *stage) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n * FIX_WORDS; i += gridDim.x * blockDim.x) {
+    const uint32_t e = i / FIX_WORDS, k = i - e * FIX_WORDS;
+    const uint32_t f = fix_list[e];
+    const uint32_t sz = (uint32_t)fr[f].size;
+    stage[i] = k == 0 ? f : (k == 1 ? sz : (k - 2 < sz ? cells[fr[f].first_cell + k - 2] : 0u));
+  }
+}
+// stage on the way back: per entry {frontier, goal cell}
+__global__ void fix_apply_kernel(const uint32_t *__restrict__ stage, uint32_t n, MapView map, fitslam_frontier *fr, uint8_t *ftag) {
+  const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const uint32_t f = stage[2 * e], g = stage[2 * e + 1];
+  fr[f].goal_my = g / map.W;
+  fr[f].goal_mx = g - fr[f].goal_my * map.W;
+  fr[f].goal_x = map.ox + (fr[f].goal_mx + 0.5) * map.res;
+  fr[f].goal_y = map.oy + (fr[f].goal_my + 0.5) * map.res;
+  ftag[f] = (uint8_t)TAG_FINAL;  // scored by the launches that follow the search
 }
 
 // ------------------------------------------------------------------------------------------------ K7: clean claim[]
@@ -1786,6 +1832,7 @@ static fitslam_status ensure_frontier_buffers(fitslam_ctx *c, FrontierState *s) 
   FS_CUDA(c, s->cells.reserve(s->cell_cap));
   FS_CUDA(c, s->centroids.reserve(2 * (size_t)s->front_cap));
   FS_CUDA(c, s->ftag.reserve(s->front_cap));
+  FS_CUDA(c, s->fix_list.reserve(s->front_cap));
   FS_CUDA(c, c->frontiers.reserve(s->front_cap));
   return FITSLAM_OK;
 }
@@ -1821,6 +1868,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   S.early_cap = std::min<uint32_t>(std::max<uint32_t>(EARLY_SLICE_CAP, s->last.n_frontiers / 4u), 8192u);
   S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
   S.ow_wide = getenv("FITSLAM_OW_NOWIDE") ? 0u : 1u;
+  S.fix_all = getenv("FITSLAM_FIX_ALL") ? 1u : 0u;
   S.use_smem = (s->force_global || c->W > 16384u || c->H > 16384u) ? 0u : 1u;  // queue entries pack x | y << 14 | mask << 28
   if (!s->attr_set) {
     FS_CUDA(c, cudaFuncSetAttribute(ow_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OW_SMEM));
@@ -1935,7 +1983,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
         for (int cls = 0; cls < 2; ++cls) {
           const uint32_t tag = 1u + 2u * (uint32_t)coll + (uint32_t)cls;
           chunk_kernel<<<148 * 2, 64, 0, sts[cls]>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
-                                                     s->centroids.p, s->ftag.p, cnt, coll, lo[cls], hi[cls], tag);
+                                                     s->centroids.p, s->ftag.p, s->fix_list.p, cnt, coll, lo[cls], hi[cls], tag);
           ++c->launches;
           ScoreSlice sl;
           sl.range = range;
@@ -2021,7 +2069,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     }
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[2], c->stream));
   chunk_kernel<<<148 * 4, 64, 0, c->stream>>>(S, s->osize.p, s->ocell0.p, s->ofront0.p, s->cells.p, c->frontiers.p,
-                                               s->centroids.p, s->ftag.p, cnt, -1, 0, 0xFFFFFFFFu, TAG_FINAL);
+                                               s->centroids.p, s->ftag.p, s->fix_list.p, cnt, -1, 0, 0xFFFFFFFFu, TAG_FINAL);
   cleanup_kernel<<<wide, 256, 0, c->stream>>>(S, s->queue.p, s->mcell.p, s->claim.p, cnt);
   c->launches += S.use_smem ? 2 : 3;  // (legacy replay,) chunk, cleanup
   FS_CUDA(c, cudaEventRecord(s->ev_bfs[5], c->stream));
@@ -2041,6 +2089,66 @@ static uint32_t hc_qcap(const FrontierState *) {
   const char *e = getenv("FITSLAM_OW_QCAP");
   const long v = e ? atol(e) : (long)OW_QCAP;
   return (uint32_t)std::min<long>(std::max<long>(v, 1), (long)OW_QCAP);
+}
+
+// The median sort of the chunks the device would not decide (chunk_kernel), on the host and with the host's libm, exactly as
+// the reference does it: getCentroidOfCells + SortByMedianFunctor + std::sort + the middle element
+// (DEP/include/frontier_exploration/FrontierSearch.hpp:85-126, 156-184; DEP/src/FrontierSearch.cpp:161-165, 194-199).
+static uint32_t host_median_cell(const fitslam_ctx *c, const uint32_t *cells, uint32_t n) {
+  struct P { double first, second; uint32_t cell; };
+  std::vector<P> v(n);
+  const double res = c->res;
+  double sumX = 0, sumY = 0;
+  for (uint32_t k = 0; k < n; ++k) {
+    const uint32_t my = cells[k] / c->W, mx = cells[k] - my * c->W;
+    v[k] = P{c->ox + (mx + 0.5) * res, c->oy + (my + 0.5) * res, cells[k]};  // Costmap2D::mapToWorld
+    sumX += v[k].first;
+    sumY += v[k].second;
+  }
+  double centerX = static_cast<double>(sumX) / v.size(), centerY = static_cast<double>(sumY) / v.size();
+  bool offset_centroid = false;
+  double varX = 0, varY = 0;
+  for (const P &p : v) {
+    if (sqrt(pow(p.first - centerX, 2) + pow(p.second - centerY, 2)) < res * 3) offset_centroid = true;
+    varX += std::abs(p.first - centerX);
+    varY += std::abs(p.second - centerY);
+  }
+  const double distance_to_offset = res * 1.414 * 2;
+  if (varX > varY && offset_centroid) centerY -= distance_to_offset;
+  if (varX < varY && offset_centroid) centerX -= distance_to_offset;
+  std::sort(v.begin(), v.end(), [centerX, centerY](const P &a, const P &b) {
+    auto angle_a = atan2(a.second - centerY, a.first - centerX);
+    if (angle_a < 0) angle_a = angle_a + (2 * M_PI);
+    auto angle_b = atan2(b.second - centerY, b.first - centerX);
+    if (angle_b < 0) angle_b = angle_b + (2 * M_PI);
+    if (0 <= angle_a && angle_a <= M_PI / 2 && 3 * M_PI / 2 <= angle_b && angle_b <= 2 * M_PI) return false;
+    if (0 <= angle_b && angle_b <= M_PI / 2 && 3 * M_PI / 2 <= angle_a && angle_a <= 2 * M_PI) return true;
+    return angle_a < angle_b;
+  });
+  return v[static_cast<int>(v.size() / 2)].cell;
+}
+
+// after the search has drained: the flagged chunks come to the host, get their goal cell, and go back tagged TAG_FINAL
+static fitslam_status fix_flagged_frontiers(fitslam_ctx *c, FrontierState *s, uint32_t n_flagged) {
+  const uint32_t n = std::min(n_flagged, s->front_cap);
+  if (n == 0) return FITSLAM_OK;
+  FS_CUDA(c, s->fix_stage.reserve((size_t)n * FIX_WORDS));
+  s->fix_host.resize((size_t)n * FIX_WORDS);
+  fix_gather_kernel<<<std::min<uint32_t>((n * FIX_WORDS + 255) / 256, 148 * 8), 256, 0, c->stream>>>(s->fix_list.p, n, c->frontiers.p, s->cells.p,
+                                                                                                  s->fix_stage.p);
+  FS_CUDA(c, cudaMemcpyAsync(s->fix_host.data(), s->fix_stage.p, (size_t)n * FIX_WORDS * 4, cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  std::vector<uint32_t> back(2 * (size_t)n);
+  for (uint32_t e = 0; e < n; ++e) {
+    const uint32_t *rec = s->fix_host.data() + (size_t)e * FIX_WORDS;
+    back[2 * e] = rec[0];
+    back[2 * e + 1] = host_median_cell(c, rec + 2, std::min<uint32_t>(rec[1], MAX_CHUNK));
+  }
+  FS_CUDA(c, cudaMemcpyAsync(s->fix_stage.p, back.data(), back.size() * 4, cudaMemcpyHostToDevice, c->stream));
+  fix_apply_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(s->fix_stage.p, n, map_view(c), c->frontiers.p, s->ftag.p);
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));  // (`back` is pageable and goes out of scope)
+  c->launches += 2;
+  return FITSLAM_OK;
 }
 
 // FrontierSearch::searchFrom on the device; the frontier list stays resident in c->frontiers (c->n_frontiers entries).
@@ -2105,7 +2213,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
     }
     if (!hc->overflow) {
       c->n_frontiers = hc->n_frontiers;
-      return FITSLAM_OK;
+      return fix_flagged_frontiers(c, s, s->last.pad0[0]);
     }
     // a list was too small: grow to what this run counted (plus slack) and search again
     grown = true;

@@ -50,9 +50,11 @@ __global__ void init_achievable_kernel(const fitslam_arrival *__restrict__ arr, 
   if (i < n) ach[i] = arr[i].achievable;
 }
 
-// setPlanForFrontierEuclidean for every frontier (DEP/src/CostCalculator.cpp:445-485); robot_yaw is an input.
-__global__ void plan_euclidean_kernel(const fitslam_frontier *__restrict__ fr, uint8_t *ach, double *len, double *head,
-                                      uint32_t n, double rx, double ry, double robot_yaw_in) {
+// setPlanForFrontierEuclidean for every frontier (DEP/src/CostCalculator.cpp:445-485); robot_yaw is an input, and so is
+// atan2(goal - robot) per frontier: the host evaluates it with its own libm (glibc's atan2 is not correctly rounded, so no
+// device implementation can promise the reference's last bit; cycle.cu overlaps the F calls with the scoring kernels).
+__global__ void plan_euclidean_kernel(const fitslam_frontier *__restrict__ fr, const double *__restrict__ goal_yaw_in, uint8_t *ach,
+                                      double *len, double *head, uint32_t n, double rx, double ry, double robot_yaw_in) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   if (!ach[i]) {
@@ -70,7 +72,7 @@ __global__ void plan_euclidean_kernel(const fitslam_frontier *__restrict__ fr, u
   }
   double robot_yaw = robot_yaw_in;
   if (robot_yaw < 0) robot_yaw = robot_yaw + (M_PI * 2);
-  double goal_yaw = atan2(fr[i].goal_y - ry, fr[i].goal_x - rx);
+  double goal_yaw = goal_yaw_in[i];
   if (goal_yaw < 0) goal_yaw = goal_yaw + (M_PI * 2);
   double h = fabs(robot_yaw - goal_yaw);
   if (h > M_PI) h = (2 * M_PI) - h;
@@ -212,13 +214,13 @@ fitslam_status select_device(fitslam_ctx *c, uint32_t n, const fitslam_arrival *
 }
 
 fitslam_status plan_euclidean_device(fitslam_ctx *c, uint32_t n, const fitslam_frontier *d_fr, const fitslam_arrival *d_arr,
-                                     double rx, double ry, double ryaw) {
+                                     const double *d_goal_yaw, double rx, double ry, double ryaw) {
   SelectState *s = sstate(c);
   FS_CUDA(c, s->ach.reserve(n));
   FS_CUDA(c, s->len.reserve(n));
   FS_CUDA(c, s->head.reserve(n));
   init_achievable_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d_arr, s->ach.p, n);
-  plan_euclidean_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d_fr, s->ach.p, s->len.p, s->head.p, n, rx, ry, ryaw);
+  plan_euclidean_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d_fr, d_goal_yaw, s->ach.p, s->len.p, s->head.p, n, rx, ry, ryaw);
   c->launches += 2;
   FS_CUDA(c, cudaGetLastError());
   return FITSLAM_OK;

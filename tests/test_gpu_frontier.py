@@ -134,10 +134,45 @@ def test_search_wide_levels_fall_back(capi, oracle, monkeypatch, wide):
     monkeypatch.setenv("FITSLAM_OW_QCAP", "3000")
     if not wide:
         monkeypatch.setenv("FITSLAM_OW_NOWIDE", "1")
-    # (resolution 1/16 m keeps every cell centre an exact double: the two-branch chunks of a straight frontier then give
-    # exact angle ties instead of ulp-level atan2 noise, which is a libm property and not what this test is about)
+    # (resolution 1/16 m keeps every cell centre an exact double; test_search_straight_frontiers_at_5cm is the same square
+    # at the reference's 0.05 m, where the median sort hangs on the last bit of atan2)
     W = H = 3000
     a = np.full((H, W), 255, np.uint8)
     a[200:2800, 200:2800] = 0
     meta = dict(res=0.0625, ox=-93.75, oy=-93.75)
     _compare(capi, oracle, a, meta, 0.0, 0.0, dict(max_frontier_distance=250.0))
+
+
+@pytest.mark.parametrize("shape", ["h", "v", "square"])
+def test_search_straight_frontiers_at_5cm(capi, oracle, shape):
+    # straight axis-aligned frontiers found from their middle at the reference's resolution (0.05 m): the chunks are two
+    # collinear branches, the centroid is off the line by rounding noise (~1e-15), and the order of the angles is decided in
+    # their last bit.  The device decides what a correctly rounded atan2 decides for certain and hands the rest to the host's
+    # libm; goal cells equal the oracle's (and, where oracle/_ref is built, the reference's own) everywhere.
+    if shape == "square":
+        W = H = 1200
+        a = np.full((H, W), 255, np.uint8)
+        a[100:H - 100, 100:W - 100] = 0
+        cx, cy = W // 2, H // 2
+    else:
+        W, H = (900, 30) if shape == "h" else (30, 900)
+        a = np.full((H, W), 255, np.uint8)
+        if shape == "h":
+            a[H // 2:, :] = 0
+            a[H // 2 + 5:, :] = 254
+            cx, cy = W // 2, H // 2 + 1
+        else:
+            a[:, W // 2:] = 0
+            a[:, W // 2 + 5:] = 254
+            cx, cy = W // 2 + 1, H // 2
+    meta = dict(res=0.05, ox=-W * 0.05 / 2, oy=-H * 0.05 / 2)
+    fr, cells = _compare(capi, oracle, a, meta, meta["ox"] + (cx + 0.5) * 0.05, meta["oy"] + (cy + 0.5) * 0.05, dict(max_frontier_distance=100.0))
+    assert len(fr) >= 40
+
+
+def test_search_host_sorted_chunks_equal_device_sorted(capi, oracle, synth, monkeypatch):
+    # FITSLAM_FIX_ALL=1 sends every chunk's median sort to the host path (gather, libm + std::sort on the host, scatter):
+    # the same lists as the oracle, and as the default path
+    a, meta, pts, ov = synth.make_config("C1", reference_rays=True)
+    monkeypatch.setenv("FITSLAM_FIX_ALL", "1")
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], ov)
