@@ -114,6 +114,7 @@ PROTOTYPES = {
     "fitslam_cycle_begin": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, _u32p]),
     "fitslam_cycle_end": (C.c_int, [_vp, C.POINTER(CycleResult)]),
     "fitslam_cycle_fetch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint32]),
+    "fitslam_cycle_fetch_candidates": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp]),
     "fitslam_score_records": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
 }
 
@@ -385,6 +386,15 @@ class Context:
         self._check(self.lib.fitslam_cycle_fetch(self.h, _ptr(fr), _ptr(ar), _ptr(pl), _ptr(ph), _ptr(wc), _ptr(fi),
                                                  _ptr(srt), n))
         return dict(frontiers=fr, arrival=ar, path_length_m=pl, path_heading=ph, weighted_cost=wc, fisher=fi, sorted=srt)
+
+    def cycle_fetch_candidates(self, n_poses):
+        """Per-candidate Fisher results of the last cycle: (information, safe, n_visible), pose = frontier * ppf + window."""
+        info = np.zeros(n_poses, dtype=np.float32)
+        safe = np.zeros(n_poses, dtype=np.uint8)
+        nvis = np.zeros(n_poses, dtype=np.uint32)
+        n = C.c_uint32()
+        self._check(self.lib.fitslam_cycle_fetch_candidates(self.h, _ptr(info), _ptr(safe), _ptr(nvis), n_poses, C.byref(n)))
+        return info[:n.value], safe[:n.value], nvis[:n.value]
 
     def records_tensor(self):
         """Zero-copy torch view (int32, [nranks * B, 4]) of the device score records, for the NCCL all-gather."""

@@ -385,4 +385,21 @@ fitslam_status fitslam_cycle_fetch(fitslam_ctx *c, fitslam_frontier *frontiers, 
   return FITSLAM_OK;
 }
 
+fitslam_status fitslam_cycle_fetch_candidates(fitslam_ctx *c, float *information, uint8_t *safe, uint32_t *n_visible, uint32_t capacity,
+                                              uint32_t *n_poses) {
+  if (!c || !c->cy) return fail(c, FITSLAM_E_INVALID, "cycle_fetch_candidates before fitslam_cycle");
+  cudaSetDevice(c->device);
+  CycleState *s = c->cy;
+  const uint32_t n = s->n_poses;
+  if (n_poses) *n_poses = n;
+  if (s->fisher_mode == FITSLAM_FISHER_OFF) return fail(c, FITSLAM_E_INVALID, "cycle_fetch_candidates: the last cycle ran without the Fisher stage");
+  if (capacity < n) return fail(c, FITSLAM_E_CAPACITY, "cycle_fetch_candidates: buffers too small");
+  if (n == 0) return FITSLAM_OK;
+  if (information) FS_CUDA(c, cudaMemcpyAsync(information, s->fisher.p, (size_t)n * 4, cudaMemcpyDefault, c->stream));
+  if (safe) FS_CUDA(c, cudaMemcpyAsync(safe, s->fisher_safe.p, n, cudaMemcpyDefault, c->stream));
+  if (n_visible) FS_CUDA(c, cudaMemcpyAsync(n_visible, s->fisher_nvis.p, (size_t)n * 4, cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return FITSLAM_OK;
+}
+
 }  // extern "C"

@@ -343,6 +343,14 @@ FITSLAM_API fitslam_status fitslam_cycle_fetch(fitslam_ctx *ctx, fitslam_frontie
                                                fitslam_arrival *arrival, double *path_length_m,
                                                double *path_heading, double *weighted_cost, float *fisher_info,
                                                uint32_t *sorted, uint32_t capacity);
+/* Copy-out of the per-CANDIDATE Fisher results of the last cycle: one entry per candidate pose, pose index =
+ * frontier * poses_per_frontier + window (FITSLAM_FISHER_ALL_YAWS: every yaw window, poses_per_frontier = n_windows;
+ * FITSLAM_FISHER_BEST_YAW: one pose per frontier).  Each entry is what FisherInformationManager::isPoseSafe returns for
+ * that pose (DEP/src/fisher_information/FisherInfoManager.cpp:39-115): `information`, the bool, and the number of
+ * landmarks that contributed.  Any pointer may be NULL; capacity in poses; *n_poses receives the count.  With several
+ * ranks the entries of frontiers another rank scored are zero (the merged records only carry the best yaw). */
+FITSLAM_API fitslam_status fitslam_cycle_fetch_candidates(fitslam_ctx *ctx, float *information, uint8_t *safe,
+                                                          uint32_t *n_visible, uint32_t capacity, uint32_t *n_poses);
 
 /* ------------------------------------------------------------------ multi-GPU plumbing (8e) */
 /* Device address + byte size of the packed per-frontier score records of the last scoring call, laid out

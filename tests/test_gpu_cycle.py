@@ -88,6 +88,47 @@ def test_cycle_all_yaws_record_is_best_yaw(capi, oracle, synth):
     ctx.close()
 
 
+@pytest.mark.parametrize("name,n_check", [("C1", 0), ("C2", 256)])
+def test_cycle_all_yaws_candidates_match_oracle(capi, oracle, synth, name, n_check):
+    """The benchmarked mode (FISHER_ALL_YAWS on the BASELINE ray shape): EVERY candidate's Fisher information, read through
+    fitslam_cycle_fetch_candidates, against the oracle's isPoseSafe for the pose (frontier goal, yaw of the window):
+    1e-4 relative, no allowance for the number of landmarks.  C2: the first 256 frontiers (4 096 poses x 200 k points)."""
+    a, meta, pts, ov = synth.make_config(name)  # 64 rays; 8 (C1) / 16 (C2) yaw windows
+    synth.apply_overrides(oracle.params, ov)
+    ctx = capi.Context(oracle.params)
+    ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+    ctx.fisher_generate_lookup()
+    ctx.set_map_points(pts)
+    st, res = ctx.cycle(meta["robot_x"], meta["robot_y"], 0.0, meta["poly"], capi.FISHER_ALL_YAWS)
+    assert st == 0
+    Y = ctx.ray_shape()[2]
+    assert res.n_fisher_poses == res.n_frontiers * Y and Y == (8 if name == "C1" else 16)
+    got = ctx.cycle_fetch(res.n_frontiers)
+    info, safe, nvis = ctx.cycle_fetch_candidates(res.n_fisher_poses)
+    assert len(info) == res.n_fisher_poses
+    F = n_check or res.n_frontiers
+    fr = got["frontiers"][:F]
+    oracle.fisher_generate()
+    th0 = np.arange(Y) * oracle.params.delta_theta + oracle.params.camera_fov / 2   # setGoalOrientation of window w
+    th = np.tile(th0, F)
+    poses = synth.frontier_poses(np.repeat(fr, Y), th, oracle.params.candidate_pose_z)
+    q = np.array([oracle.orientation_around_z(t) for t in th])
+    poses["qx"], poses["qy"], poses["qz"], poses["qw"] = q.T
+    st, winfo, wsafe, wvis, wused = oracle.fisher_poses(pts, poses)
+    ok = np.repeat(got["arrival"]["ray_failed"][:F] == 0, Y)
+    g = info[:F * Y]
+    assert np.all(np.abs(g - winfo)[ok] <= 1e-4 * np.abs(winfo[ok]) + 1e-6), np.max(np.abs(g - winfo)[ok] / np.maximum(np.abs(winfo[ok]), 1))
+    np.testing.assert_array_equal(nvis[:F * Y][ok], wused[ok])
+    thr = oracle.params.fisher_information_threshold
+    clear = np.abs(winfo - thr) > 1e-3 * thr
+    np.testing.assert_array_equal(safe[:F * Y][ok & clear], wsafe[ok & clear])
+    # the record of a frontier carries the information of its best yaw
+    best = info.reshape(-1, Y)[np.arange(res.n_frontiers), got["arrival"]["max_index"]]
+    okf = got["arrival"]["ray_failed"] == 0
+    np.testing.assert_array_equal(best[okf], got["fisher"][okf])
+    ctx.close()
+
+
 @pytest.mark.parametrize("nranks", [2, 3])
 def test_sharded_cycle_equals_single(capi, oracle, synth, nranks):
     """N ranks emulated in one process on one GPU: each context scores its share (frontier f on rank f % N), the records

@@ -70,17 +70,18 @@ def _poses(capi, rng, n, box, z=0.3, full_rotation=False):
     return p
 
 
-def _check(ctx, oracle, pts, poses):
+def _check(ctx, oracle, pts, poses, float_sum_allowance=False):
     info, safe, nvis = ctx.score_fisher(poses)
     st, winfo, wsafe, wvis, wused = oracle.fisher_poses(pts, poses)
     assert st == 0
     np.testing.assert_array_equal(nvis, wused)
     # arithmetic parity: the same per-landmark terms, accumulated in double on both sides
     np.testing.assert_allclose(info, oracle.last_information_f64, rtol=1e-6, atol=1e-6)
-    # against the reference's float accumulation (FisherInfoManager.cpp:85-97): 1e-4 relative, widened only by the
-    # reference's own order-dependent rounding when tens of thousands of landmarks are summed into one float
-    rtol = np.maximum(RTOL, wused.astype(np.float64) * 2.0 ** -24)
-    assert np.all(np.abs(info - winfo) <= rtol * np.abs(winfo) + 1e-6), np.abs(info - winfo) / np.maximum(winfo, 1)
+    # against the reference's float accumulation in arrival order (FisherInfoManager.cpp:85-97): 1e-4 relative, flat.
+    # float_sum_allowance (the dense-clump test only: 50 000+ landmarks in one pose): the reference's own `float +=` loses
+    # up to n * 2^-24 of the total there, which is its rounding, not a difference in what is summed (the line above)
+    rtol = np.maximum(RTOL, wused.astype(np.float64) * 2.0 ** -24) if float_sum_allowance else RTOL
+    assert np.all(np.abs(info - winfo) <= rtol * np.abs(winfo) + 1e-6), np.max(np.abs(info - winfo) / np.maximum(winfo, 1))
     clear = np.abs(winfo - 550.0) > 1.0
     np.testing.assert_array_equal(safe[clear], wsafe[clear])
     return info
@@ -109,7 +110,7 @@ def test_fisher_dense_cloud_crowding_and_overflow(lut_ctx, oracle, capi):
     lut_ctx.set_map_points(pts)
     poses = _poses(capi, rng, 24, (-10, -10, 10, 10))
     poses[0]["x"], poses[0]["y"], poses[0]["qz"], poses[0]["qw"] = 0.0, 0.5, 0.0, 1.0  # looks straight at the clump
-    info = _check(lut_ctx, oracle, pts, poses)
+    info = _check(lut_ctx, oracle, pts, poses, float_sum_allowance=True)
     assert info.max() > 550.0
 
 
