@@ -3,7 +3,8 @@ oracle would take minutes:
   * C4 (16384^2 map, 1M map points, ~20k frontiers x 32 yaw windows): a second cycle on the same context gives the same
     bits (scratch state is clean between cycles), the union of 4 candidate shards equals the unsharded records, every goal
     cell is an unknown cell next to known space, sizes obey the cluster bounds, the every_frontier list has no duplicates;
-    a sample of the frontiers is scored by the oracle (arrival information, bit-exact);
+    the whole frontier list and every_frontier list equal the oracle's bit for bit; samples of the frontiers / candidate poses
+    are scored by the oracle (arrival information bit-exact, Fisher information 1e-4);
   * C5 (rapid mode): a random walk reveals discs on a C1-size map; each step uploads only the dirty rectangle, and the
     cycle must equal a cycle on a fresh context with the full map, and the oracle every 8th step."""
 import numpy as np
@@ -32,6 +33,7 @@ def test_c4_full_size_properties(capi, oracle, synth):
         ctx.set_map_points(pts)
         res1, out1 = _fetch(ctx, capi, meta, capi.FISHER_ALL_YAWS)
         res2, out2 = _fetch(ctx, capi, meta, capi.FISHER_ALL_YAWS)
+        info, safe, nvis = ctx.cycle_fetch_candidates(res2.n_fisher_poses)
         F = res1.n_frontiers
         n_rays, k, n_win, max_len = ctx.ray_shape()
         assert F > 5000 and n_win == 32 and res1.n_candidates == F * n_win == res1.n_fisher_poses
@@ -72,11 +74,33 @@ def test_c4_full_size_properties(capi, oracle, synth):
         np.testing.assert_array_equal(merged_arr["information"], out1["arrival"]["information"])
         np.testing.assert_array_equal(merged_arr["max_index"], out1["arrival"]["max_index"])
         np.testing.assert_array_equal(merged_f.view(np.uint32), out1["fisher"].view(np.uint32))
+        # the whole extraction against the oracle (18 M expanded cells: the cluster wavefront and the 30 k-cell rim component
+        # at their real sizes): frontier list and every_frontier list bit for bit
+        sto, wfr, wcells, wseeds, wcent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"], capacity=1 << 17, cell_capacity=1 << 23)
+        assert sto == 0 and len(wfr) == F and len(wseeds) == res1.n_components
+        np.testing.assert_array_equal(cells, wcells)
+        for key in ("goal_mx", "goal_my", "size", "component", "chunk", "first_cell"):
+            np.testing.assert_array_equal(fr[key], wfr[key], err_msg=key)
+        np.testing.assert_array_equal(fr["goal_x"].view(np.uint64), wfr["goal_x"].view(np.uint64))
+        np.testing.assert_array_equal(fr["goal_y"].view(np.uint64), wfr["goal_y"].view(np.uint64))
         # a sample of the frontiers through the oracle: arrival information bit-exact
         pick = np.linspace(0, F - 1, 400).astype(np.int64)
         arr, _, _ = oracle.score_arrival(a, meta, fr[pick], meta["poly"])
         for key in REC_FIELDS:
             np.testing.assert_array_equal(out1["arrival"][key][pick], arr[key], err_msg=key)
+        # ... and Fisher information of 96 sampled candidates (3 yaw windows of 32 frontiers) over the 1 M map points: 1e-4
+        oracle.fisher_generate()
+        pf = np.repeat(np.linspace(0, F - 1, 32).astype(np.int64), 3)
+        pw = np.tile(np.array([0, 11, 31]), 32)
+        th = pw * params.delta_theta + params.camera_fov / 2
+        poses = synth.frontier_poses(fr[pf], th, params.candidate_pose_z)
+        q = np.array([oracle.orientation_around_z(t) for t in th])
+        poses["qx"], poses["qy"], poses["qz"], poses["qw"] = q.T
+        stf, winfo, wsafe, wvis, wused = oracle.fisher_poses(pts, poses)
+        g = info[pf * n_win + pw]
+        okp = out1["arrival"]["ray_failed"][pf] == 0
+        assert np.all(np.abs(g - winfo)[okp] <= 1e-4 * np.abs(winfo[okp]) + 1e-6), np.max(np.abs(g - winfo)[okp] / np.abs(winfo[okp]))
+        np.testing.assert_array_equal(nvis[pf * n_win + pw][okp], wused[okp])
     finally:
         ctx.close()
 
