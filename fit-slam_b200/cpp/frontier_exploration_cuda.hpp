@@ -11,10 +11,17 @@
 //   Frontier / FrontierPtr      include/frontier_exploration/Frontier.hpp:39-136,        src/Frontier.cpp:5-246
 //   FrontierCostCalculator      include/frontier_exploration/CostCalculator.hpp:56-116,  src/CostCalculator.cpp:23-191,512-520
 //   FisherInformationManager    include/.../fisher_information/FisherInfoManager.hpp:69-127, src/.../FisherInfoManager.cpp:39-324
+//   FrontierCostsManager        include/frontier_exploration/FrontierCostsManager.hpp:40-95, src/FrontierCostsManager.cpp:47-222
+//   CostAssigner (+ request / response)  include/frontier_exploration/CostAssigner.hpp:43-100, src/CostAssigner.cpp:29-168
+//   FullPathOptimizer (selection part)   include/frontier_exploration/FullPathOptimizer.hpp:24-130, src/FullPathOptimizer.cpp:157-227,342-352,548-639
+//   Fisher helper free functions         include/frontier_exploration/Helpers.hpp:144-165, src/Helpers.cpp:333-449
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <functional>
+#include <mutex>
+#include <unordered_map>
 #include <limits>
 #include <map>
 #include <memory>
@@ -34,6 +41,10 @@ namespace geometry_msgs { namespace msg {
 struct Point { double x = 0, y = 0, z = 0; };
 struct Quaternion { double x = 0, y = 0, z = 0, w = 1; };
 struct Pose { Point position; Quaternion orientation; };
+struct PoseStamped { struct { std::string frame_id; } header; Pose pose; };
+struct Point32 { float x = 0, y = 0, z = 0; };
+struct Polygon { std::vector<Point32> points; };
+struct PolygonStamped { struct { std::string frame_id; } header; Polygon polygon; };
 }}  // namespace geometry_msgs::msg
 namespace nav2_costmap_2d {
 static constexpr unsigned char NO_INFORMATION = 255, LETHAL_OBSTACLE = 254, INSCRIBED_INFLATED_OBSTACLE = 253, FREE_SPACE = 0;
@@ -49,6 +60,8 @@ public:
   double getResolution() const { return resolution_; }
   double getOriginX() const { return origin_x_; }
   double getOriginY() const { return origin_y_; }
+  double getSizeInMetersX() const { return (size_x_ - 1 + 0.5) * resolution_; }
+  double getSizeInMetersY() const { return (size_y_ - 1 + 0.5) * resolution_; }
   unsigned int getIndex(unsigned int mx, unsigned int my) const { return my * size_x_ + mx; }
   void mapToWorld(unsigned int mx, unsigned int my, double &wx, double &wy) const {
     wx = origin_x_ + (mx + 0.5) * resolution_;
@@ -149,6 +162,7 @@ public:
   bool isAchievable() const { return get(is_achievable_, "Achievability frontier property is null"); }
   bool isBlacklisted() const { return get(is_blacklisted_, "Blacklist frontier property is null"); }
   bool isFrontierNull() const { return !unique_id_ && !size_ && !goal_point_; }
+  bool hasPathLength() const { return (bool)path_length_ || !isAchievable(); }  // not in the reference: a planner has filled it in
   // not in the reference: the cell the goal point is the centre of, kept so that a batch call needs no worldToMap
   uint32_t goal_mx = 0, goal_my = 0;
 private:
@@ -352,6 +366,424 @@ private:
   float step_max = 0.3f;
 };
 
+// ---- Fisher helper free functions (Helpers.hpp:144-165, Helpers.cpp:333-449) -------------------------------------------
+// With FITSLAM_HAVE_EIGEN the reference's own definitions can be compiled against real Eigen; otherwise these tiny
+// fixed-size stand-ins carry the same signatures.  The arithmetic follows Eigen 3.4's evaluation order for fixed-size float
+// expressions (3-term dot products as x0*y0 + (x1*y1 + x2*y2), Matrix3f::inverse through cofactors), which is what makes
+// computeInformationOfPointLocal(voxel centre, I) equal the lookup table the device generates, bit for bit
+// (tests/cpp/shim_harness.cpp checks that against fitslam_fisher_lookup_copy).
+#ifndef FITSLAM_HAVE_EIGEN
+}  // namespace frontier_exploration
+namespace Eigen {
+template <typename T, int R, int C>
+struct Matrix {
+  T m[R][C];
+  Matrix() { for (int i = 0; i < R; ++i) for (int j = 0; j < C; ++j) m[i][j] = T(0); }
+  Matrix(T x, T y, T z) { static_assert(R == 3 && C == 1, "3-vector"); m[0][0] = x; m[1][0] = y; m[2][0] = z; }
+  T &operator()(int i, int j) { return m[i][j]; }
+  const T &operator()(int i, int j) const { return m[i][j]; }
+  T &operator()(int i) { return m[i][0]; }
+  const T &operator()(int i) const { return m[i][0]; }
+  static Matrix Identity() { Matrix r; for (int i = 0; i < (R < C ? R : C); ++i) r.m[i][i] = T(1); return r; }
+  T trace() const {  // Eigen's unrolled redux: halves, then x0 + (x1 + x2) inside a half of three
+    static_assert(R == C, "square");
+    if (R == 6) return (m[0][0] + (m[1][1] + m[2][2])) + (m[3][3] + (m[4][4] + m[5][5]));
+    T t = m[0][0];
+    for (int i = 1; i < R; ++i) t += m[i][i];
+    return t;
+  }
+};
+using Matrix3f = Matrix<float, 3, 3>;
+using Vector3f = Matrix<float, 3, 1>;
+}  // namespace Eigen
+namespace frontier_exploration {
+#endif
+namespace detail {
+inline float dot3(float a0, float b0, float a1, float b1, float a2, float b2) { return a0 * b0 + (a1 * b1 + a2 * b2); }
+inline Eigen::Matrix3f inverse3(const Eigen::Matrix3f &a) {  // Eigen compute_inverse<Matrix3f>: cofactors, determinant from column 0
+  auto cof = [&a](int i, int j) {
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    return a(i1, j1) * a(i2, j2) - a(i1, j2) * a(i2, j1);
+  };
+  const float c0 = cof(0, 0), c1 = cof(1, 0), c2 = cof(2, 0);
+  const float invdet = 1.0f / dot3(c0, a(0, 0), c1, a(1, 0), c2, a(2, 0));
+  Eigen::Matrix3f r;
+  r(0, 0) = c0 * invdet; r(0, 1) = c1 * invdet; r(0, 2) = c2 * invdet;
+  for (int i = 1; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) r(i, j) = cof(j, i) * invdet;
+  return r;
+}
+}  // namespace detail
+inline Eigen::Matrix3f getSkewMatrix(const Eigen::Vector3f &v) {  // Helpers.cpp:333-340
+  Eigen::Matrix3f s;
+  s(0, 0) = 0; s(0, 1) = -v(2); s(0, 2) = v(1);
+  s(1, 0) = v(2); s(1, 1) = 0; s(1, 2) = -v(0);
+  s(2, 0) = -v(1); s(2, 1) = v(0); s(2, 2) = 0;
+  return s;
+}
+inline Eigen::Matrix<float, 3, 6> computeJacobianForPointLocal(Eigen::Vector3f &p) {  // Helpers.cpp:397-417
+  const float n = std::sqrt(detail::dot3(p(0), p(0), p(1), p(1), p(2), p(2)));
+  const float a = 1 / n, s = 1 / (n * n * n);
+  Eigen::Matrix3f df;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) df(i, j) = a * (i == j ? 1.0f : 0.0f) - (s * p(i)) * p(j);
+  Eigen::Matrix<float, 3, 6> right;
+  const Eigen::Matrix3f skew = getSkewMatrix(p);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      right(i, j) = (float)((-1.0) * (i == j ? 1.0f : 0.0f));
+      right(i, 3 + j) = skew(i, j);
+    }
+  Eigen::Matrix<float, 3, 6> J;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 6; ++j) J(i, j) = detail::dot3(df(i, 0), right(0, j), df(i, 1), right(1, j), df(i, 2), right(2, j));
+  return J;
+}
+inline Eigen::Matrix<float, 6, 6> computeFIM(Eigen::Matrix<float, 3, 6> &J, Eigen::Matrix3f &Q) {  // Helpers.cpp:419-422
+  const Eigen::Matrix3f Qi = detail::inverse3(Q);
+  Eigen::Matrix<float, 6, 6> F;
+  for (int i = 0; i < 6; ++i) {
+    float q[3];
+    for (int k = 0; k < 3; ++k) q[k] = detail::dot3(J(0, i), Qi(0, k), J(1, i), Qi(1, k), J(2, i), Qi(2, k));
+    for (int j = 0; j < 6; ++j) F(i, j) = detail::dot3(q[0], J(0, j), q[1], J(1, j), q[2], J(2, j));
+  }
+  return F;
+}
+inline float computeInformationOfPointLocal(Eigen::Vector3f &p, Eigen::Matrix3f Q) {  // Helpers.cpp:440-449
+  auto jac = computeJacobianForPointLocal(p);
+  auto fim = computeFIM(jac, Q);
+  return fim.trace();
+}
+
+// ---- FrontierCostsManager (FrontierCostsManager.hpp:40-95) ------------------------------------------------------------
+struct FrontierHash {  // Frontier.hpp:163-180
+  size_t operator()(const FrontierPtr &key) const { return generateUID(key->getGoalPoint().x, key->getGoalPoint().y); }
+};
+struct FrontierGoalPointEquality {  // Frontier.hpp:139-143
+  bool operator()(const FrontierPtr &a, const FrontierPtr &b) const { return a->getGoalPoint().x == b->getGoalPoint().x && a->getGoalPoint().y == b->getGoalPoint().y && a->getGoalPoint().z == b->getGoalPoint().z; }
+};
+class FrontierCostsManager {
+public:
+  FrontierCostsManager(nav2_costmap_2d::Costmap2D *costmap, CudaContextPtr ctx)
+      : costmap_(costmap), ctx_(ctx), costCalculator_(std::make_shared<FrontierCostCalculator>(costmap, ctx)) {}
+  // assignCosts (FrontierCostsManager.cpp:47-213).  costTypes per frontier: "ArrivalInformation" and a distance method.
+  // "EuclideanDistance" is setPlanForFrontierEuclidean (CostCalculator.cpp:445-485) on the host (the reference's own libm).
+  // "RoadmapPlannerDistance" / "A*PlannerDistance" are the reference's planners (out of scope here): a frontier that asks
+  // for one must already carry the planner's result (setPathLength / setPathLengthInM / setPathHeading, or
+  // setAchievability(false)); one that carries nothing gets the Euclidean values.  The arrival information of the whole
+  // list is one raycast launch, the U1 block one launch (bit-exact weighted costs).  map_data is unused, as in the reference.
+  bool assignCosts(std::vector<FrontierPtr> &frontier_list, std::vector<double> polygon_xy_min_max, geometry_msgs::msg::Pose start_pose_w,
+                   std::shared_ptr<void> map_data, std::vector<std::vector<std::string>> &costTypes) {
+    (void)map_data;
+    costCalculator_->reset();
+    costCalculator_->setMaxArrivalInformation();
+    if (frontier_list.size() == 0) return false;       // "No frontiers found from frontier search."
+    if (polygon_xy_min_max.size() <= 0) return false;  // "Frontier cannot be selected, no polygon."
+    for (size_t i = 0; i < frontier_list.size(); ++i)  // findDuplicates (:25-45): the same pointer twice
+      for (size_t j = i + 1; j < frontier_list.size(); ++j)
+        if (frontier_list[i] == frontier_list[j]) throw std::runtime_error("Duplicate frontiers found.");
+    const size_t n = frontier_list.size();
+    std::vector<uint8_t> blacklisted(n, 0);
+    {
+      std::lock_guard<std::mutex> lock(blacklist_mutex_);
+      for (size_t i = 0; i < n; ++i) blacklisted[i] = frontier_blacklist_.count(frontier_list[i]) > 0;
+    }
+    auto has = [&costTypes](size_t i, const char *what) {
+      return i < costTypes.size() && std::find(costTypes[i].begin(), costTypes[i].end(), std::string(what)) != costTypes[i].end();
+    };
+    // arrival information: one launch over the list (IMPORTANT in the reference too: before the planning); the results go to
+    // the frontiers that ask for it, and the scored list stays resident for the U1 launch below
+    std::vector<fitslam_frontier> in(n);
+    for (size_t i = 0; i < n; ++i) {
+      in[i] = fitslam_frontier{};
+      in[i].goal_x = frontier_list[i]->getGoalPoint().x;
+      in[i].goal_y = frontier_list[i]->getGoalPoint().y;
+      in[i].size = frontier_list[i]->getSize();
+      unsigned int mx = 0, my = 0;
+      costmap_->worldToMap(in[i].goal_x, in[i].goal_y, mx, my);
+      in[i].goal_mx = mx;
+      in[i].goal_my = my;
+    }
+    std::vector<fitslam_arrival> arr(n);
+    ctx_->check(fitslam_score_arrival(ctx_->get(), in.data(), (uint32_t)n, polygon_xy_min_max.data(), arr.data(), nullptr, nullptr), "fitslam_score_arrival");
+    for (size_t i = 0; i < n; ++i) {
+      if (blacklisted[i] || !has(i, "ArrivalInformation")) continue;
+      frontier_list[i]->setArrivalInformation((double)arr[i].information);
+      frontier_list[i]->setGoalOrientation(arr[i].theta_s_star);
+      if (!arr[i].achievable) frontier_list[i]->setAchievability(false);  // CostCalculator.cpp:77-82, 112-117
+    }
+    std::vector<double> len(n, std::numeric_limits<double>::max()), head(n, std::numeric_limits<double>::max());
+    for (size_t i = 0; i < n; ++i) {
+      FrontierPtr &f = frontier_list[i];
+      if (blacklisted[i]) {  // :77-86
+        f->setArrivalInformation(0.0);
+        f->setGoalOrientation(0.0);
+        f->setFisherInformation(0.0);
+        f->setPathLength(std::numeric_limits<double>::max());
+        f->setPathLengthInM(std::numeric_limits<double>::max());
+        f->setWeightedCost(std::numeric_limits<double>::max());
+        continue;
+      }
+      const bool planner = has(i, "A*PlannerDistance") || has(i, "RoadmapPlannerDistance");
+      if (!(planner && f->hasPathLength())) setPlanForFrontierEuclidean(start_pose_w, f);
+      if (f->isAchievable()) { len[i] = f->getPathLength(); head[i] = f->getPathHeading(); }
+      costCalculator_->recomputeNormalizationFactors(f);
+    }
+    // U1 (:121-205) on the device (a frontier without a plan, length DBL_MAX, counts as not achievable); its two throws come
+    // back as statuses
+    std::vector<double> wc(n), ua(n), ud(n);
+    const fitslam_status st = fitslam_normalise_select(ctx_->get(), len.data(), head.data(), blacklisted.data(), (uint32_t)n, wc.data(), ua.data(),
+                                                       ud.data(), nullptr, nullptr, nullptr);
+    if (st == FITSLAM_E_ARRIVAL_UTILITY || st == FITSLAM_E_COST_OUT_OF_BOUNDS) {
+      const std::string msg = fitslam_last_error(ctx_->get());  // "... (frontier K)"
+      const size_t at = msg.rfind("(frontier ");
+      const size_t k = at == std::string::npos ? 0 : (size_t)std::strtoul(msg.c_str() + at + 10, nullptr, 10);
+      if (st == FITSLAM_E_COST_OUT_OF_BOUNDS) throw std::runtime_error("Cost out of bounds");
+      throw std::runtime_error("ARRIVAL UTILITY ERROR! MORE THAN 1. It is: " + std::to_string(frontier_list[std::min(k, n - 1)]->getArrivalInformation()));
+    }
+    ctx_->check(st, "fitslam_normalise_select");
+    for (size_t i = 0; i < n; ++i) {
+      if (blacklisted[i]) continue;
+      frontier_list[i]->setWeightedCost(wc[i]);
+      frontier_list[i]->setCost("arrival_gain_utility", ua[i]);
+      frontier_list[i]->setCost("distance_utility", ud[i]);
+    }
+    return true;
+  }
+  void setFrontierBlacklist(std::vector<FrontierPtr> &blacklist) {  // :215-222
+    std::lock_guard<std::mutex> lock(blacklist_mutex_);
+    for (auto frontier : blacklist) frontier_blacklist_[frontier] = true;
+  }
+  std::shared_ptr<FrontierCostCalculator> getCostCalcPtr() { return costCalculator_; }
+  // setPlanForFrontierEuclidean (CostCalculator.cpp:445-485); robot yaw = tf2 getRPY of the pose's quaternion (GeometryUtils.hpp:22-32)
+  static void setPlanForFrontierEuclidean(geometry_msgs::msg::Pose start_pose_w, FrontierPtr &goal_point_w) {
+    const auto unachievable = [&goal_point_w]() {
+      goal_point_w->setAchievability(false);
+      goal_point_w->setPathLength(std::numeric_limits<double>::max());
+      goal_point_w->setPathLengthInM(std::numeric_limits<double>::max());
+      goal_point_w->setPathHeading(std::numeric_limits<double>::max());
+      goal_point_w->setFisherInformation(0);
+    };
+    if (goal_point_w->isAchievable() == false) return unachievable();
+    const auto start_point_w = start_pose_w.position;
+    const double length_to_frontier = sqrt(pow(start_point_w.x - goal_point_w->getGoalPoint().x, 2) + pow(start_point_w.y - goal_point_w->getGoalPoint().y, 2));
+    if (length_to_frontier < 0.5) return unachievable();
+    goal_point_w->setAchievability(true);
+    double robot_yaw = yawOf(start_pose_w.orientation);
+    if (robot_yaw < 0) robot_yaw = robot_yaw + (M_PI * 2);
+    double goal_yaw = atan2(goal_point_w->getGoalPoint().y - start_pose_w.position.y, goal_point_w->getGoalPoint().x - start_pose_w.position.x);
+    if (goal_yaw < 0) goal_yaw = goal_yaw + (M_PI * 2);
+    double path_heading = std::abs(robot_yaw - goal_yaw);
+    if (path_heading > M_PI) path_heading = (2 * M_PI) - path_heading;
+    goal_point_w->setPathLength(length_to_frontier);
+    goal_point_w->setPathLengthInM(length_to_frontier);
+    goal_point_w->setPathHeading(path_heading);
+    goal_point_w->setFisherInformation(0.0);
+  }
+  static double yawOf(const geometry_msgs::msg::Quaternion &q) {  // tf2::Matrix3x3(q).getRPY yaw (the first Euler solution)
+    const double d = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w, s = 2.0 / d;
+    const double ys = q.y * s, zs = q.z * s, wy = q.w * ys, wz = q.w * zs, xy = q.x * ys, xz = q.x * zs, yy = q.y * ys, zz = q.z * zs;
+    const double m00 = 1.0 - (yy + zz), m10 = xy + wz, m20 = xz - wy;
+    if (std::fabs(m20) >= 1) return 0.0;
+    const double pitch = -std::asin(m20);
+    return std::atan2(m10 / std::cos(pitch), m00 / std::cos(pitch));
+  }
+private:
+  nav2_costmap_2d::Costmap2D *costmap_;
+  CudaContextPtr ctx_;
+  std::shared_ptr<FrontierCostCalculator> costCalculator_;
+  std::unordered_map<FrontierPtr, bool, FrontierHash, FrontierGoalPointEquality> frontier_blacklist_;
+  std::mutex blacklist_mutex_;
+};
+
+// ---- CostAssigner (CostAssigner.hpp:43-100) ------------------------------------------------------------------------------
+struct GetFrontierCostsRequest {
+  geometry_msgs::msg::PoseStamped start_pose;
+  std::vector<FrontierPtr> frontier_list;
+  std::vector<std::vector<double>> every_frontier;
+  std::vector<FrontierPtr> prohibited_frontiers;
+};
+struct GetFrontierCostsResponse {
+  bool success = false;
+  std::vector<FrontierPtr> frontier_list;
+  std::vector<double> frontier_costs;
+  std::vector<double> frontier_distances;
+  std::vector<double> frontier_arrival_information;
+  std::vector<double> frontier_path_information;
+};
+class CostAssigner {
+public:
+  // (the reference takes the Costmap2DROS and reads its layered costmap: CostAssigner.cpp:8-27)
+  CostAssigner(nav2_costmap_2d::Costmap2D *costmap, CudaContextPtr ctx, std::vector<std::string> methods = {"EuclideanDistance", "ArrivalInformation"})
+      : costmap_(costmap), frontierCostsManager_(std::make_shared<FrontierCostsManager>(costmap, ctx)), chosenMethods_(std::move(methods)) {}
+  // updateBoundaryPolygon (CostAssigner.cpp:121-167): an empty boundary means the whole map, with the reference's own corner
+  // values (origin and size in metres, as it mixes them)
+  bool updateBoundaryPolygon(geometry_msgs::msg::PolygonStamped &explore_boundary) {
+    for (const auto &point32 : explore_boundary.polygon.points) polygon_.points.push_back(point32);
+    if (polygon_.points.empty()) {
+      geometry_msgs::msg::Point32 temp;
+      temp.x = (float)costmap_->getOriginX();
+      temp.y = (float)costmap_->getOriginY();
+      polygon_.points.push_back(temp);
+      temp.y = (float)costmap_->getSizeInMetersY();
+      polygon_.points.push_back(temp);
+      temp.x = (float)costmap_->getSizeInMetersX();
+      polygon_.points.push_back(temp);
+      temp.y = (float)costmap_->getOriginY();
+      polygon_.points.push_back(temp);
+    }
+    double min_x = std::numeric_limits<double>::infinity(), min_y = std::numeric_limits<double>::infinity();
+    double max_x = -std::numeric_limits<double>::infinity(), max_y = -std::numeric_limits<double>::infinity();
+    for (const auto &point : polygon_.points) {
+      min_x = std::min(min_x, (double)point.x);
+      min_y = std::min(min_y, (double)point.y);
+      max_x = std::max(max_x, (double)point.x);
+      max_y = std::max(max_y, (double)point.y);
+    }
+    polygon_xy_min_max_.push_back(min_x);
+    polygon_xy_min_max_.push_back(min_y);
+    polygon_xy_min_max_.push_back(max_x);
+    polygon_xy_min_max_.push_back(max_y);
+    return true;
+  }
+  // getFrontierCosts (CostAssigner.cpp:73-119): the response carries the SAME pointers in the SAME order
+  bool getFrontierCosts(std::shared_ptr<GetFrontierCostsRequest> requestData, std::shared_ptr<GetFrontierCostsResponse> resultData) {
+    frontierCostsManager_->setFrontierBlacklist(requestData->prohibited_frontiers);
+    std::vector<std::vector<std::string>> costTypes(requestData->frontier_list.size(), chosenMethods_);
+    const bool costsResult = frontierCostsManager_->assignCosts(requestData->frontier_list, polygon_xy_min_max_, requestData->start_pose.pose,
+                                                                nullptr, costTypes);
+    if (costsResult == false) {
+      resultData->success = false;
+      return resultData->success;
+    }
+    resultData->success = true;
+    std::vector<FrontierPtr> frontiers_list;
+    std::vector<double> frontier_costs, frontier_distances, frontier_arrival_information;
+    for (auto &frontier : requestData->frontier_list) {
+      frontiers_list.push_back(frontier);
+      frontier_costs.push_back(frontier->getWeightedCost());
+      frontier_distances.push_back(frontier->getPathLengthInM());
+      frontier_arrival_information.push_back(frontier->getArrivalInformation());
+    }
+    resultData->frontier_list = frontiers_list;
+    resultData->frontier_costs = frontier_costs;
+    resultData->frontier_distances = frontier_distances;
+    resultData->frontier_arrival_information = frontier_arrival_information;
+    if (resultData->frontier_list != requestData->frontier_list) throw std::runtime_error("Lists are not SAME!");
+    return resultData->success;
+  }
+  std::shared_ptr<FrontierCostsManager> getCostManagerPtr() { return frontierCostsManager_; }
+  const std::vector<double> &polygonXYMinMax() const { return polygon_xy_min_max_; }
+private:
+  nav2_costmap_2d::Costmap2D *costmap_;
+  std::shared_ptr<FrontierCostsManager> frontierCostsManager_;
+  std::vector<std::string> chosenMethods_;
+  geometry_msgs::msg::Polygon polygon_;
+  std::vector<double> polygon_xy_min_max_;
+};
+
+// ---- FullPathOptimizer, the selection part (FullPathOptimizer.hpp:24-130) -----------------------------------------------
+enum PathSafetyStatus { SAFE, UNSAFE, UNDETERMINED };  // FullPathOptimizer.hpp:24-28
+struct SortedFrontiers {                              // :70-75
+  std::vector<FrontierPtr> local_frontiers;
+  std::vector<FrontierPtr> global_frontiers;
+  FrontierPtr closest_global_frontier;
+};
+class FullPathOptimizer {
+public:
+  static constexpr double NUM_FRONTIERS_IN_LOCAL_AREA = 5.0, LOCAL_FRONTIER_SEARCH_RADIUS = 12.0, BLACKLISTING_CIRCLE_RADIUS = 1.7;  // :13-19
+  explicit FullPathOptimizer(std::shared_ptr<FisherInformationManager> fisher = nullptr, bool exhaustiveLandmarkSearch = true)
+      : fisher_information_manager_(std::move(fisher)), exhaustiveLandmarkSearch_(exhaustiveLandmarkSearch) {}
+  bool isInBlacklistedRegion(const FrontierPtr &frontier) {  // :118-130
+    for (auto &zone : circularBlacklistCenters_) {
+      const double dx = frontier->getGoalPoint().x - zone->getGoalPoint().x, dy = frontier->getGoalPoint().y - zone->getGoalPoint().y;
+      if (sqrt(pow(dx, 2) + pow(dy, 2)) < BLACKLISTING_CIRCLE_RADIUS) return true;
+    }
+    return false;
+  }
+  void blacklistFrontier(FrontierPtr &frontier) { circularBlacklistCenters_.push_back(frontier); }
+  // getFilteredFrontiersN (FullPathOptimizer.cpp:157-227): host logic over the F pointers, with the library's own std::sort
+  // (unstable on equal path lengths, as the reference's)
+  void getFilteredFrontiersN(std::vector<FrontierPtr> &frontier_list, size_t n, SortedFrontiers &sortedFrontiers, geometry_msgs::msg::PoseStamped &robotP) {
+    (void)robotP;
+    std::vector<FrontierPtr> all_frontiers;
+    for (const auto &frontier : frontier_list)
+      if (frontier->isAchievable() && !frontier->isBlacklisted() && !isInBlacklistedRegion(frontier)) all_frontiers.push_back(frontier);
+    std::sort(all_frontiers.begin(), all_frontiers.end(), [](const FrontierPtr &a, const FrontierPtr &b) { return a->getPathLengthInM() < b->getPathLengthInM(); });
+    bool global_assigned = false;
+    if (all_frontiers.size() == 0) return;  // "No achievable frontiers exist during sorting."
+    size_t counter = 1;
+    bool need_to_pop = false;
+    for (const auto &frontier : all_frontiers) {
+      if (frontier->getPathLengthInM() <= LOCAL_FRONTIER_SEARCH_RADIUS && counter <= n) {
+        sortedFrontiers.local_frontiers.push_back(frontier);
+        sortedFrontiers.closest_global_frontier = frontier;
+        need_to_pop = true;
+      } else if (frontier->getPathLengthInM() <= LOCAL_FRONTIER_SEARCH_RADIUS && counter > n) {
+        sortedFrontiers.closest_global_frontier = frontier;
+        need_to_pop = false;
+      } else if (frontier->getPathLengthInM() > LOCAL_FRONTIER_SEARCH_RADIUS) {
+        if (!global_assigned) {
+          sortedFrontiers.closest_global_frontier = frontier;
+          global_assigned = true;
+        }
+        need_to_pop = false;
+        sortedFrontiers.global_frontiers.push_back(frontier);
+      }
+      counter++;
+    }
+    if (need_to_pop) sortedFrontiers.local_frontiers.pop_back();
+    if (sortedFrontiers.global_frontiers.size() == 0 && sortedFrontiers.local_frontiers.size() == 0)
+      sortedFrontiers.global_frontiers.push_back(sortedFrontiers.closest_global_frontier);
+  }
+  PathSafetyStatus isRobotPoseSafe(geometry_msgs::msg::Pose &robotPose) {  // :342-352
+    float information;
+    const bool safety_value = fisher_information_manager_->isPoseSafe(robotPose, exhaustiveLandmarkSearch_, information);
+    return safety_value ? SAFE : UNSAFE;
+  }
+  // The order in which the local frontiers are visited is the reference's travelling-salesman step (getBestFullPath, out of
+  // scope: SURVEY.md 2.2); a caller that has it plugs it in here.  bestPath[0] is the robot, bestPath[1] the next goal.
+  // Default: the local frontiers in order of path length.
+  std::function<bool(SortedFrontiers &, std::vector<FrontierPtr> &, geometry_msgs::msg::PoseStamped &)> getBestFullPath;
+  // getNextGoal (FullPathOptimizer.cpp:548-639)
+  PathSafetyStatus getNextGoal(std::vector<FrontierPtr> &frontier_list, FrontierPtr &nextFrontier, size_t n, geometry_msgs::msg::PoseStamped &robotP,
+                               geometry_msgs::msg::PoseStamped &robotPFI, bool use_fi) {
+    (void)n;  // the reference ignores it too and uses NUM_FRONTIERS_IN_LOCAL_AREA (:552)
+    SortedFrontiers sortedFrontiers;
+    getFilteredFrontiersN(frontier_list, (size_t)NUM_FRONTIERS_IN_LOCAL_AREA, sortedFrontiers, robotP);
+    FrontierPtr zeroFrontier = std::make_shared<Frontier>();
+    std::vector<FrontierPtr> bestFrontierWaypoint;
+    if (sortedFrontiers.local_frontiers.size() == 0) {
+      if (sortedFrontiers.global_frontiers.size() >= 1) {
+        nextFrontier = sortedFrontiers.closest_global_frontier;
+        if (use_fi && isRobotPoseSafe(robotPFI.pose) == UNSAFE) return PathSafetyStatus::UNSAFE;  // "Dead reckoning!!"
+        return PathSafetyStatus::SAFE;
+      }
+      nextFrontier = zeroFrontier;
+      return PathSafetyStatus::UNDETERMINED;
+    }
+    bool have_path;
+    if (getBestFullPath) {
+      have_path = getBestFullPath(sortedFrontiers, bestFrontierWaypoint, robotP);
+    } else {
+      bestFrontierWaypoint.push_back(zeroFrontier);  // the robot's place in the path
+      for (auto &f : sortedFrontiers.local_frontiers) bestFrontierWaypoint.push_back(f);
+      have_path = true;
+    }
+    if (!have_path || bestFrontierWaypoint.size() < 2) {
+      nextFrontier = zeroFrontier;
+      return PathSafetyStatus::UNDETERMINED;
+    }
+    nextFrontier = bestFrontierWaypoint[1];
+    if (use_fi && isRobotPoseSafe(robotPFI.pose) == UNSAFE) return PathSafetyStatus::UNSAFE;
+    return PathSafetyStatus::SAFE;
+  }
+private:
+  std::shared_ptr<FisherInformationManager> fisher_information_manager_;
+  bool exhaustiveLandmarkSearch_;
+  std::vector<FrontierPtr> circularBlacklistCenters_;
+};
+
 // ---- FrontierRoadMap, the edge test only (RE/include/roadmap_explorer/planners/FrontierRoadmap.hpp:173-188) -------------
 // isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-694) decides the roadmap's edges: one traced ray per node pair.
 // The node store, A* and publishing stay with the caller; the batch form scores every candidate pair of a node in one launch.
@@ -444,8 +876,15 @@ using frontier_exploration::CudaContext;
 using frontier_exploration::CudaContextPtr;
 using frontier_exploration::FisherInformationManager;
 using frontier_exploration::Frontier;
+using frontier_exploration::CostAssigner;
 using frontier_exploration::FrontierCostCalculator;
+using frontier_exploration::FrontierCostsManager;
 using frontier_exploration::FrontierPtr;
+using frontier_exploration::FullPathOptimizer;
+using frontier_exploration::GetFrontierCostsRequest;
+using frontier_exploration::GetFrontierCostsResponse;
+using frontier_exploration::PathSafetyStatus;
+using frontier_exploration::SortedFrontiers;
 using frontier_exploration::FrontierRoadMap;
 using frontier_exploration::FrontierSearch;
 using frontier_exploration::LethalMarker;

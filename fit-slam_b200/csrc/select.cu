@@ -49,6 +49,11 @@ __global__ void init_achievable_kernel(const fitslam_arrival *__restrict__ arr, 
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) ach[i] = arr[i].achievable;
 }
+// the caller's path lengths decide too: a frontier the planner could not reach carries DBL_MAX (CostCalculator.cpp:449-466)
+__global__ void init_achievable_len_kernel(const fitslam_arrival *__restrict__ arr, const double *__restrict__ len, uint8_t *ach, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) ach[i] = arr[i].achievable && len[i] != DBL_MAX;
+}
 
 // setPlanForFrontierEuclidean for every frontier (DEP/src/CostCalculator.cpp:445-485); robot_yaw is an input, and so is
 // atan2(goal - robot) per frontier: the host evaluates it with its own libm (glibc's atan2 is not correctly rounded, so no
@@ -247,7 +252,7 @@ extern "C" fitslam_status fitslam_normalise_select(fitslam_ctx *c, const double 
   FS_CUDA(c, cudaMemcpyAsync(s->len.p, path_length_m, (size_t)n * 8, cudaMemcpyDefault, c->stream));
   FS_CUDA(c, cudaMemcpyAsync(s->head.p, path_heading, (size_t)n * 8, cudaMemcpyDefault, c->stream));
   if (blacklisted) FS_CUDA(c, cudaMemcpyAsync(s->bl.p, blacklisted, n, cudaMemcpyDefault, c->stream));
-  init_achievable_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(c->arrival.p, s->ach.p, n);
+  init_achievable_len_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(c->arrival.p, s->len.p, s->ach.p, n);
   ++c->launches;
   fitslam_status st = select_device(c, n, c->arrival.p, s->ach.p, blacklisted ? s->bl.p : nullptr, s->len.p, s->head.p);
   if (st != FITSLAM_OK) return st;

@@ -314,7 +314,8 @@ FITSLAM_API fitslam_status fitslam_landmarks_in_view(fitslam_ctx *ctx, const fit
 /* FrontierCostsManager::assignCosts U1 block (DEP/src/FrontierCostsManager.cpp:121-205) followed by
  * FullPathOptimizer::getFilteredFrontiersN (DEP/src/FullPathOptimizer.cpp:157-227).
  * arrival/achievable come from the last fitslam_score_arrival.  path_length_m / path_heading: one per
- * frontier (inputs produced by the planner in the reference); blacklisted may be NULL. */
+ * frontier (inputs produced by the planner in the reference; DBL_MAX = the planner found the frontier not achievable,
+ * DEP/src/CostCalculator.cpp:449-466); blacklisted may be NULL. */
 FITSLAM_API fitslam_status fitslam_normalise_select(fitslam_ctx *ctx, const double *path_length_m,
                                                     const double *path_heading, const uint8_t *blacklisted,
                                                     uint32_t n_frontiers, double *weighted_cost,

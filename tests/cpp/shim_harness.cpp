@@ -37,6 +37,69 @@ static int host_only() {
   fitslam_default_params(&p);
   if (p.max_frontier_cluster_size != 20 || fitslam_abi_version() != FITSLAM_ABI_VERSION) ++bad;
   if (std::strlen(fitslam_status_string(FITSLAM_E_NO_LOOKUP_TABLE)) == 0) ++bad;
+  // Fisher helpers (Helpers.cpp:397-449): trace(FIM)(p) = 2 + 2 / |p|^2, skew matrix layout
+  {
+    Eigen::Vector3f p(1.0f, 0.0f, 0.0f);
+    if (computeInformationOfPointLocal(p, Eigen::Matrix3f::Identity()) != 4.0f) ++bad;
+    Eigen::Vector3f q(3.0f, 0.0f, 0.0f);
+    if (std::fabs(computeInformationOfPointLocal(q, Eigen::Matrix3f::Identity()) - (2.0f + 2.0f / 9.0f)) > 1e-6f) ++bad;
+    const Eigen::Matrix3f sk = getSkewMatrix(Eigen::Vector3f(1.0f, 2.0f, 3.0f));
+    if (sk(0, 1) != -3.0f || sk(0, 2) != 2.0f || sk(1, 0) != 3.0f || sk(1, 2) != -1.0f || sk(2, 0) != -2.0f || sk(2, 1) != 1.0f || sk(0, 0) != 0.0f) ++bad;
+    Eigen::Matrix<float, 3, 6> J = computeJacobianForPointLocal(q);
+    Eigen::Matrix3f I = Eigen::Matrix3f::Identity();
+    if (computeFIM(J, I).trace() != computeInformationOfPointLocal(q, I)) ++bad;
+  }
+  // getFilteredFrontiersN known answers (FullPathOptimizer.cpp:157-227)
+  {
+    auto make = [](int k) {
+      std::vector<FrontierPtr> v;
+      for (int i = 0; i < k; ++i) {
+        auto f = std::make_shared<Frontier>();
+        f->setGoalPoint(10.0 + i, 0.0);
+        f->setUID(generateUID(10.0 + i, 0.0));
+        f->setSize(5);
+        f->setPathLengthInM(1.0 + ((i * 3) % k));  // lengths 1..k in a scrambled order
+        v.push_back(f);
+      }
+      return v;
+    };
+    geometry_msgs::msg::PoseStamped robotP;
+    FullPathOptimizer opt;
+    SortedFrontiers s7;
+    auto v7 = make(7);
+    opt.getFilteredFrontiersN(v7, 5, s7, robotP);
+    if (s7.local_frontiers.size() != 5 || !s7.global_frontiers.empty() || s7.closest_global_frontier->getPathLengthInM() != 7.0) ++bad;
+    for (size_t i = 0; i < s7.local_frontiers.size(); ++i)
+      if (s7.local_frontiers[i]->getPathLengthInM() != 1.0 + i) ++bad;
+    SortedFrontiers s5;
+    auto v5 = make(5);
+    opt.getFilteredFrontiersN(v5, 5, s5, robotP);
+    if (s5.local_frontiers.size() != 4 || s5.closest_global_frontier->getPathLengthInM() != 5.0) ++bad;  // the last one is popped (:221-222)
+    // a blacklisted region (1.7 m around a frontier) and an unachievable frontier are filtered out
+    auto v3 = make(3);
+    v3[0]->setAchievability(false);
+    opt.blacklistFrontier(v3[1]);
+    SortedFrontiers s3;
+    opt.getFilteredFrontiersN(v3, 5, s3, robotP);  // v3[2] is 1 m from the blacklisted centre: inside the circle too
+    if (!s3.local_frontiers.empty() || !s3.global_frontiers.empty()) ++bad;
+    // getNextGoal without local or global frontiers: a zero frontier and UNDETERMINED (:583-588)
+    FrontierPtr next;
+    if (opt.getNextGoal(v3, next, 5, robotP, robotP, false) != UNDETERMINED || !next->isFrontierNull()) ++bad;
+  }
+  // setPlanForFrontierEuclidean (CostCalculator.cpp:445-485)
+  {
+    geometry_msgs::msg::Pose start;
+    start.orientation.z = std::sin(0.35);  // yaw 0.7
+    start.orientation.w = std::cos(0.35);
+    auto f = std::make_shared<Frontier>();
+    f->setGoalPoint(3.0, 4.0);
+    FrontierCostsManager::setPlanForFrontierEuclidean(start, f);
+    if (f->getPathLength() != 5.0 || std::fabs(f->getPathHeading() - (std::atan2(4.0, 3.0) - 0.7)) > 1e-12 || !f->isAchievable()) ++bad;
+    auto near = std::make_shared<Frontier>();
+    near->setGoalPoint(0.3, 0.0);
+    FrontierCostsManager::setPlanForFrontierEuclidean(start, near);
+    if (near->isAchievable() || near->getPathLength() != std::numeric_limits<double>::max()) ++bad;
+  }
   std::printf("host-only checks: %d failed\n", bad);
   return bad;
 }
@@ -138,6 +201,74 @@ int main(int argc, char **argv) {
       if (stamped[i] != costmap.getCharMap()[i]) ++changed;
     }
     std::printf("lethal %u %llu %llu %llu\n", marked, (unsigned long long)n253, (unsigned long long)isum, (unsigned long long)changed);
+  }
+  // ---- cost assignment and goal selection in the behaviour tree's order (ExplorationBT.cpp:371-423, 517-637):
+  // CostAssigner::updateBoundaryPolygon / getFrontierCosts, then FullPathOptimizer::getNextGoal
+  {
+    ctx->updateCostmap(costmap);  // (the lethal marker above stamped the resident copy)
+    std::vector<FrontierPtr> list = search.searchFrom(robot);
+    CostAssigner assigner(&costmap, ctx);
+    geometry_msgs::msg::PolygonStamped boundary;  // the map's corners, as float32 (geometry_msgs/Point32)
+    const float bx[4] = {(float)g[1], (float)g[1], (float)(g[1] + W * g[0]), (float)(g[1] + W * g[0])};
+    const float by[4] = {(float)g[2], (float)(g[2] + H * g[0]), (float)(g[2] + H * g[0]), (float)g[2]};
+    for (int k = 0; k < 4; ++k) {
+      geometry_msgs::msg::Point32 p32;
+      p32.x = bx[k];
+      p32.y = by[k];
+      boundary.polygon.points.push_back(p32);
+    }
+    assigner.updateBoundaryPolygon(boundary);
+    auto req = std::make_shared<GetFrontierCostsRequest>();
+    auto res = std::make_shared<GetFrontierCostsResponse>();
+    req->start_pose.pose.position = robot;
+    req->frontier_list = list;
+    req->every_frontier = search.getAllFrontiers();
+    if (list.size() > 4) req->prohibited_frontiers.push_back(list[3]);  // one blacklisted frontier (:77-86)
+    const bool ok = assigner.getFrontierCosts(req, res);
+    std::printf("costs %d %zu\n", ok ? 1 : 0, res->frontier_list.size());
+    for (size_t i = 0; i < res->frontier_list.size(); ++i) {
+      const FrontierPtr &f = res->frontier_list[i];
+      if (f != list[i]) std::printf("NOT THE SAME POINTER %zu\n", i);
+      std::printf("C %a %a %a %d\n", res->frontier_costs[i], res->frontier_distances[i], res->frontier_arrival_information[i], f->isAchievable() ? 1 : 0);
+    }
+    auto fisher_mgr = std::make_shared<FisherInformationManager>(ctx);
+    FullPathOptimizer optimizer(fisher_mgr);
+    geometry_msgs::msg::PoseStamped robotP;
+    robotP.pose.position = robot;
+    robotP.pose.position.z = 0.3;
+    FrontierPtr next;
+    const PathSafetyStatus status = optimizer.getNextGoal(list, next, 5, robotP, robotP, true);
+    float robot_info = 0;
+    const bool robot_safe = fisher_mgr->isPoseSafe(robotP.pose, true, robot_info);
+    std::printf("next %d %a %a %d %a\n", (int)status, next->isFrontierNull() ? 0.0 : next->getGoalPoint().x, next->isFrontierNull() ? 0.0 : next->getGoalPoint().y,
+                robot_safe ? 1 : 0, (double)robot_info);
+    // the reference's exceptions: the same frontier twice, and a response list that is not the request's
+    try {
+      std::vector<FrontierPtr> twice{list[0], list[0]};
+      std::vector<std::vector<std::string>> types(2, {"EuclideanDistance", "ArrivalInformation"});
+      assigner.getCostManagerPtr()->assignCosts(twice, assigner.polygonXYMinMax(), robotP.pose, nullptr, types);
+      std::printf("duplicates NOT DETECTED\n");
+    } catch (const std::runtime_error &e) {
+      std::printf("duplicates %s\n", e.what());
+    }
+    // the Fisher helper free functions against the device's lookup table: every entry along two lines of voxels
+    int32_t dims[3], org[3];
+    ctx->check(fitslam_fisher_lookup_dims(ctx->get(), dims, org), "fitslam_fisher_lookup_dims");
+    std::vector<float> lut((size_t)dims[0] * dims[1] * dims[2]);
+    ctx->check(fitslam_fisher_lookup_copy(ctx->get(), lut.data(), lut.size()), "fitslam_fisher_lookup_copy");
+    int lut_bad = 0, lut_n = 0;
+    for (int ix = 1; ix < dims[0]; ++ix)
+      for (int iy = 0; iy < dims[1]; iy += 7) {
+        const int iz = (ix * 5 + iy) % dims[2];
+        float vx = 0, vy = 0, vz = 0;
+        fisher_mgr->getVoxelCoordinate(vx, vy, vz, (float)((ix + org[0]) * 0.3), (float)((iy + org[1]) * 0.3), (float)((iz + org[2]) * 0.3));
+        Eigen::Vector3f p(vx, vy, vz);
+        const float want = lut[((size_t)ix * dims[1] + iy) * dims[2] + iz];
+        const float got = computeInformationOfPointLocal(p, Eigen::Matrix3f::Identity());
+        ++lut_n;
+        if (std::memcmp(&want, &got, 4) != 0) ++lut_bad;
+      }
+    std::printf("lut %d %d\n", lut_n, lut_bad);
   }
   // robot off the map: empty list, no exception (FrontierSearch.cpp:28-32)
   robot.x = g[1] - 1.0;

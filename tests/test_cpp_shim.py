@@ -108,3 +108,48 @@ def test_shim_matches_oracle(harness, capi, oracle, synth, tmp_path):
         for k in range(3):
             sums[k] += row[k]
     assert [float.fromhex(v) for v in lm[2:5]] == sums
+
+    # ---- cost assignment and goal selection (CostAssigner::getFrontierCosts, FullPathOptimizer::getNextGoal), BT order
+    f32 = lambda v: float(np.float32(v))
+    poly32 = [f32(meta["ox"]), f32(meta["oy"]), f32(meta["ox"] + W * meta["res"]), f32(meta["oy"] + H * meta["res"])]
+    arr2, _, _ = oracle.score_arrival(a, meta, fr, poly32)
+    bl = np.zeros(len(fr), np.uint8)
+    if len(fr) > 4:
+        bl[3] = 1
+    ach_in = arr2["achievable"].copy()
+    ach, pl, ph = oracle.plan_euclidean(meta["robot_x"], meta["robot_y"], 0.0, fr, ach_in)
+    stn, wc, ua, ud, err = oracle.normalise(arr2, ach, pl, ph, bl, oracle.arrival_limits(a, meta)[0])
+    assert stn == 0
+    head = [ln.split() for ln in lines if ln.startswith("costs")][0]
+    assert head[1:] == ["1", str(len(fr))] and not any("NOT THE SAME POINTER" in ln for ln in lines)
+    crow = [ln.split() for ln in lines if ln.startswith("C ")]
+    assert len(crow) == len(fr)
+    DBL_MAX = np.finfo(np.float64).max
+    for i, row in enumerate(crow):
+        cost, dist, info = (float.fromhex(v) for v in row[1:4])
+        if bl[i]:
+            assert cost == DBL_MAX and dist == DBL_MAX and info == 0.0
+            continue
+        assert cost == wc[i], (i, cost, wc[i])                     # weighted cost: bit-exact
+        assert dist == (pl[i] if ach[i] else DBL_MAX)
+        assert info == float(arr2["information"][i])
+        assert int(row[4]) == int(ach[i])
+    # getNextGoal: the shortest-path local frontier (no travelling-salesman step in this build), or the closest global one
+    elig = np.flatnonzero(ach.astype(bool) & (bl == 0))
+    order = elig[np.argsort(pl[elig], kind="stable")]
+    nxt = [ln.split() for ln in lines if ln.startswith("next")][0]
+    local = [i for i in order[:5] if pl[i] <= 12.0]
+    if len(order) <= 5 and len(local) == len(order) and local:
+        local = local[:-1]  # need_to_pop
+    want_next = local[0] if local else (order[0] if len(order) else None)
+    if want_next is not None:
+        assert float.fromhex(nxt[2]) == fr["goal_x"][want_next] and float.fromhex(nxt[3]) == fr["goal_y"][want_next]
+    rp = synth.frontier_poses(fr[:1], 0.0, 0.3)
+    rp["x"], rp["y"] = meta["robot_x"], meta["robot_y"]
+    rp["qx"], rp["qy"], rp["qz"], rp["qw"] = 0.0, 0.0, 0.0, 1.0
+    str_, rinfo, rsafe, *_ = oracle.fisher_poses(pts, rp)
+    assert abs(float.fromhex(nxt[5]) - rinfo[0]) <= 1e-4 * abs(rinfo[0]) + 1e-6
+    assert int(nxt[1]) == (0 if rsafe[0] else 1) and int(nxt[4]) == int(rsafe[0])   # SAFE / UNSAFE = isRobotPoseSafe
+    assert [ln for ln in lines if ln.startswith("duplicates")][0] == "duplicates Duplicate frontiers found."
+    lut = [ln.split() for ln in lines if ln.startswith("lut")][0]
+    assert int(lut[1]) > 500 and int(lut[2]) == 0   # the helper free functions reproduce the device's table bit for bit
