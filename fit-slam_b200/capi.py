@@ -66,7 +66,7 @@ class CycleResult(C.Structure):
     _fields_ = [("n_frontiers", C.c_uint32), ("n_frontier_cells", C.c_uint32), ("n_components", C.c_uint32),
                 ("n_candidates", C.c_uint32), ("n_fisher_poses", C.c_uint32), ("bfs_levels", C.c_uint32),
                 ("ambiguous_sorts", C.c_uint32), ("_pad", C.c_uint32), ("selection", Selection),
-                ("stage_ms", C.c_float * 8)]
+                ("stage_ms", C.c_float * 8), ("widest_level", C.c_uint32), ("wavefront_ctas", C.c_uint32)]
 
 
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NO_COSTMAP, E_ROBOT_OUT_OF_BOUNDS, E_NO_FRONTIERS, E_NO_POLYGON, \
@@ -115,6 +115,10 @@ PROTOTYPES = {
     "fitslam_cycle_end": (C.c_int, [_vp, C.POINTER(CycleResult)]),
     "fitslam_cycle_fetch": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint32]),
     "fitslam_cycle_fetch_candidates": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp]),
+    "fitslam_comm_unique_id": (C.c_int, [_vp, C.c_uint64]),
+    "fitslam_comm_init": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "fitslam_comm_destroy": (C.c_int, [_vp]),
+    "fitslam_cycle_merge": (C.c_int, [_vp]),
     "fitslam_score_records": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
 }
 
@@ -208,8 +212,29 @@ class Context:
     def set_shard(self, rank, nranks):
         self._check(self.lib.fitslam_set_shard(self.h, rank, nranks))
 
+    # ---- one NCCL communicator per context (csrc/comm.cu)
+    @staticmethod
+    def comm_unique_id():
+        """128 bytes (an ncclUniqueId): made on rank 0, carried to the other ranks by the host."""
+        buf = C.create_string_buffer(128)
+        st = load_library().fitslam_comm_unique_id(buf, 128)
+        if st != OK:
+            raise FitslamError(st, "fitslam_comm_unique_id: libnccl.so.2 not loadable")
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, nranks):
+        assert len(unique_id) == 128
+        self._check(self.lib.fitslam_comm_init(self.h, C.c_char_p(bytes(unique_id)), rank, nranks))
+
+    def comm_destroy(self):
+        self._check(self.lib.fitslam_comm_destroy(self.h))
+
+    def cycle_merge(self):
+        self._check(self.lib.fitslam_cycle_merge(self.h))
+
     def set_costmap(self, data, res, ox, oy, dirty=None, shape=None):
-        """data: uint8 numpy array [H, W] (host) or a raw device address with shape=(H, W)."""
+        """data: uint8 numpy array [H, W] (host) or a raw device address with shape=(H, W); None with shape=(H, W) on the
+        receiving ranks of a communicator (comm_init)."""
         if isinstance(data, np.ndarray):
             assert data.dtype == np.uint8 and data.ndim == 2
             data = np.ascontiguousarray(data)

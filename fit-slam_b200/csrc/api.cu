@@ -13,7 +13,7 @@ using namespace fitslam;
 
 static_assert(sizeof(fitslam_params) == 192, "ABI layout");
 static_assert(sizeof(fitslam_frontier) == 40 && sizeof(fitslam_arrival) == 24 && sizeof(fitslam_pose) == 56, "ABI layout");
-static_assert(sizeof(fitslam_selection) == 24 && sizeof(fitslam_cycle_result) == 88 && sizeof(ScoreRecord) == 16, "ABI layout");
+static_assert(sizeof(fitslam_selection) == 24 && sizeof(fitslam_cycle_result) == 96 && sizeof(ScoreRecord) == 16, "ABI layout");
 
 namespace fitslam {
 
@@ -169,6 +169,7 @@ void fitslam_destroy(fitslam_ctx *c) {
   destroy_fisher_state(c);
   destroy_select_state(c);
   destroy_cycle_state(c);
+  destroy_comm_state(c);
   c->map.release();
   c->ray_dxdy.release();
   c->frontiers.release();
@@ -365,27 +366,35 @@ fitslam_status fitslam_get_costmap(fitslam_ctx *c, uint8_t *out, uint64_t capaci
 
 fitslam_status fitslam_set_costmap(fitslam_ctx *c, const uint8_t *data, uint32_t size_x, uint32_t size_y,
                                    double resolution, double origin_x, double origin_y, const uint32_t *dirty) {
-  if (!c || !data || size_x == 0 || size_y == 0 || !(resolution > 0.0))
+  // with a communicator (fitslam_comm_init) the call is collective: rank 0 uploads, the others pass data = NULL and receive
+  const bool receive = c && comm_active(c) && c->rank != 0;
+  if (!c || (!data && !receive) || size_x == 0 || size_y == 0 || !(resolution > 0.0))
     return fail(c, FITSLAM_E_INVALID, "set_costmap: bad argument");
   if ((uint64_t)size_x * size_y >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "set_costmap: more than 2^31 cells");
   cudaSetDevice(c->device);
   const bool same_geom = c->have_map && c->W == size_x && c->H == size_y && c->res == resolution &&
                          c->ox == origin_x && c->oy == origin_y;
-  const cudaMemcpyKind kind = is_device_ptr(data) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  const cudaMemcpyKind kind = (data && is_device_ptr(data)) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   if (dirty) {
     if (!same_geom) return fail(c, FITSLAM_E_INVALID, "set_costmap: dirty rectangle needs a resident map of the same geometry");
     const uint32_t x0 = dirty[0], y0 = dirty[1], w = dirty[2], h = dirty[3];
     if (w == 0 || h == 0) return FITSLAM_OK;
     if ((uint64_t)x0 + w > size_x || (uint64_t)y0 + h > size_y) return fail(c, FITSLAM_E_INVALID, "set_costmap: dirty rectangle outside the map");
-    FS_CUDA(c, cudaMemcpy2DAsync(c->map.p + (size_t)y0 * c->pitch + x0, c->pitch, data + (size_t)y0 * size_x + x0, size_x,
-                                 w, h, kind, c->stream));
+    if (!receive)
+      FS_CUDA(c, cudaMemcpy2DAsync(c->map.p + (size_t)y0 * c->pitch + x0, c->pitch, data + (size_t)y0 * size_x + x0, size_x,
+                                   w, h, kind, c->stream));
+    // (the rows of the rectangle, whole: the ranks' maps agree outside it)
+    fitslam_status bst = comm_broadcast(c, c->map.p + (size_t)y0 * c->pitch, (size_t)h * c->pitch);
+    if (bst != FITSLAM_OK) return bst;
     FS_CUDA(c, cudaStreamSynchronize(c->stream));  // the caller may reuse `data` on return
     return FITSLAM_OK;
   }
   const uint32_t pitch = (size_x + 15u) & ~15u;  // TMA needs 16-byte row strides
   FS_CUDA(c, c->map.reserve((size_t)pitch * size_y + 256));
   if (pitch != size_x) FS_CUDA(c, cudaMemsetAsync(c->map.p, 0, (size_t)pitch * size_y, c->stream));
-  FS_CUDA(c, cudaMemcpy2DAsync(c->map.p, pitch, data, size_x, size_x, size_y, kind, c->stream));
+  if (!receive) FS_CUDA(c, cudaMemcpy2DAsync(c->map.p, pitch, data, size_x, size_x, size_y, kind, c->stream));
+  fitslam_status bst = comm_broadcast(c, c->map.p, (size_t)pitch * size_y);
+  if (bst != FITSLAM_OK) return bst;
   FS_CUDA(c, cudaStreamSynchronize(c->stream));
   c->W = size_x;
   c->H = size_y;

@@ -53,6 +53,7 @@ struct FrontierState;
 struct FisherState;
 struct SelectState;
 struct CycleState;
+struct CommState;
 
 struct ScoreRecord {  // 16 bytes, the all-gather unit
   int32_t information;
@@ -113,6 +114,7 @@ struct fitslam_ctx {
   fitslam::FisherState *fi = nullptr;
   fitslam::SelectState *sel = nullptr;
   fitslam::CycleState *cy = nullptr;
+  fitslam::CommState *comm = nullptr;  // NCCL communicator (comm.cu); null on a single GPU
 };
 
 namespace fitslam {
@@ -162,6 +164,9 @@ void destroy_frontier_state(fitslam_ctx *c);
 void destroy_fisher_state(fitslam_ctx *c);
 void destroy_select_state(fitslam_ctx *c);
 void destroy_cycle_state(fitslam_ctx *c);
+void destroy_comm_state(fitslam_ctx *c);
+bool comm_active(const fitslam_ctx *c);
+fitslam_status comm_broadcast(fitslam_ctx *c, void *dev, size_t bytes);  // rank 0 -> all, on the context stream
 
 // ---- stage N state (select.cu), shared with cycle.cu
 struct SelectMeta {
@@ -223,6 +228,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
 uint32_t frontier_capacity(fitslam_ctx *c);          // frontiers the resident list can hold (0 on failure)
 const uint8_t *frontier_tags_device(fitslam_ctx *c);  // per frontier of the last search: TAG_FINAL or the early launch that scored it
 const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_t *n_comp, uint32_t *levels, uint32_t *ambiguous);
+void frontier_wavefront_device(fitslam_ctx *c, uint32_t *widest_level, uint32_t *ctas);  // of the last search's outer wavefront
 fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, uint32_t n, uint32_t first, uint32_t count,
                                    float *d_info, uint8_t *d_safe, uint32_t *d_nvis, ScoreRecord *d_rec,
                                    const fitslam_arrival *d_arrival, uint32_t poses_per_frontier);

@@ -230,6 +230,7 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->res.n_components = n_comp;
   s->res.bfs_levels = levels;
   s->res.ambiguous_sorts = ambiguous;
+  frontier_wavefront_device(c, &s->res.widest_level, &s->res.wavefront_ctas);
   if (n_frontiers) *n_frontiers = F;
   if (F == 0) return fail(c, FITSLAM_E_NO_FRONTIERS, "No frontiers found from frontier search.");
   // the goal points come to the host now (70 KB at C2), ahead of the scoring launches below
@@ -355,6 +356,8 @@ fitslam_status fitslam_cycle(fitslam_ctx *c, double rx, double ry, double ryaw, 
     if (result && c && c->cy) *result = c->cy->res;
     return st;
   }
+  st = fitslam_cycle_merge(c);  // (nothing on one GPU or without a communicator)
+  if (st != FITSLAM_OK) return st;
   return fitslam_cycle_end(c, result);
 }
 

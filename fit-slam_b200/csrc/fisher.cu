@@ -502,7 +502,9 @@ static double lut_reach(const fitslam_ctx *c) {
 }  // namespace fitslam
 
 extern "C" fitslam_status fitslam_set_map_points(fitslam_ctx *c, const float *xyz, uint64_t n) {
-  if (!c || (!xyz && n)) return fail(c, FITSLAM_E_INVALID, "set_map_points: null argument");
+  // with a communicator the call is collective: rank 0 uploads, the others pass xyz = NULL and receive
+  const bool receive = c && comm_active(c) && c->rank != 0;
+  if (!c || (!xyz && n && !receive)) return fail(c, FITSLAM_E_INVALID, "set_map_points: null argument");
   if (n >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "set_map_points: more than 2^31 points");
   cudaSetDevice(c->device);
   FisherState *f = fstate(c);
@@ -511,7 +513,11 @@ extern "C" fitslam_status fitslam_set_map_points(fitslam_ctx *c, const float *xy
   FS_CUDA(c, f->raw.reserve(3 * n + 3));
   FS_CUDA(c, f->pts.reserve(n + 1));
   FS_CUDA(c, f->bbox.reserve(8));
-  if (n) FS_CUDA(c, cudaMemcpyAsync(f->raw.p, xyz, 3 * n * sizeof(float), cudaMemcpyDefault, c->stream));
+  if (n && !receive) FS_CUDA(c, cudaMemcpyAsync(f->raw.p, xyz, 3 * n * sizeof(float), cudaMemcpyDefault, c->stream));
+  {
+    const fitslam_status bst = comm_broadcast(c, f->raw.p, 3 * n * sizeof(float));
+    if (bst != FITSLAM_OK) return bst;
+  }
   const uint32_t init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0, 0, 0};
   FS_CUDA(c, cudaMemcpyAsync(f->bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, c->stream));
   const unsigned grid = (unsigned)std::min<uint64_t>(148 * 8, (n + 255) / 256 + 1);

@@ -115,6 +115,7 @@ struct FrontierState {
   DevBuf<uint2> tm;           // {trav word, frontier-mask word} interleaved: one 8-byte load classifies a neighbour
   DevBuf<uint32_t> ebits;     // expandable cells (traversable and inside the search radius), same layout
   int ow_cluster = -1;        // CTAs per cluster of ow_cluster_kernel (0: not available, use the single-CTA kernel); -1: not probed yet
+  uint32_t last_ow_ctas = 0;  // CTAs the last search's outer wavefront ran on (1, or the cluster size)
   uint32_t ow_cluster_min = 1500;  // ... used when the last search's widest level had at least this many cells (FITSLAM_OW_CLUSTER_MIN)
   DevBuf<uint16_t> rk;        // outer wavefront: class of a cell, then its position inside its level (ow_rk_* layout); the search disc's
                               // tiles are rewritten before every search
@@ -2030,8 +2031,8 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
       cfg.attrs = at;
       cfg.numAttrs = 1;
       FS_CUDA(c, cudaLaunchKernelEx(&cfg, ow_cluster_kernel, S, L, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts));
-      ++c->launches;
     }
+    s->last_ow_ctas = cluster ? (uint32_t)s->ow_cluster : 1u;
     // the search on the context stream; behind each published part but the last, a collection on the second stream
     if (cluster) {
     } else if (s->prefer_wide && S.ow_wide)
@@ -2236,6 +2237,12 @@ const uint32_t *frontier_cells_device(fitslam_ctx *c, uint32_t *n_cells, uint32_
   if (ambiguous) *ambiguous = s->last.ambiguous;
   c->last_bfs_ms = s->bfs_ms;
   return s->cells.p;
+}
+
+void frontier_wavefront_device(fitslam_ctx *c, uint32_t *widest_level, uint32_t *ctas) {
+  FrontierState *s = fr_state(c);
+  *widest_level = s->last.widest_level;
+  *ctas = s->last_ow_ctas;
 }
 
 }  // namespace fitslam

@@ -34,7 +34,7 @@ extern "C" {
 #define FITSLAM_API __attribute__((visibility("default")))
 #endif
 
-#define FITSLAM_ABI_VERSION 1
+#define FITSLAM_ABI_VERSION 2
 
 typedef struct fitslam_ctx fitslam_ctx;
 
@@ -142,10 +142,13 @@ typedef struct fitslam_cycle_result {
   uint32_t n_candidates;   /* frontier x yaw-window candidates scored */
   uint32_t n_fisher_poses; /* poses scored by the Fisher stage */
   uint32_t bfs_levels;
-  uint32_t ambiguous_sorts;/* chunks whose median sort had two angles within 4 ulp */
+  uint32_t ambiguous_sorts;/* chunks whose median sort was redone on the host with libm's atan2 (an angle within 0.03 ulp of a
+                              rounding boundary and 2 ulp of another angle or of a comparator threshold) */
   uint32_t _pad;
   fitslam_selection selection;
   float stage_ms[8];       /* extract, arrival, distance, fisher, normalise+select, cycle_begin total, cycle_end total, outer-wavefront kernel alone */
+  uint32_t widest_level;   /* cells in the widest level of the outer wavefront */
+  uint32_t wavefront_ctas; /* CTAs the outer wavefront ran on: 1, or the size of the thread-block cluster */
 } fitslam_cycle_result;
 
 enum { FITSLAM_DIST_GIVEN = 0, FITSLAM_DIST_EUCLIDEAN = 1 };
@@ -158,8 +161,10 @@ FITSLAM_API fitslam_status fitslam_create(const fitslam_params *p, int device, f
 FITSLAM_API void fitslam_destroy(fitslam_ctx *ctx);
 FITSLAM_API const char *fitslam_last_error(const fitslam_ctx *ctx);
 FITSLAM_API const char *fitslam_status_string(fitslam_status s);
-/* Restrict the scoring stages to this rank's contiguous block of frontiers, [rank * B, min(F, (rank + 1) * B)) with
- * B = ceil(F / nranks) (8e: candidate sharding).  Records of the other frontiers are left zero in the output buffers. */
+/* Candidate sharding (8e).  In a cycle this rank scores the frontiers f with f % nranks == rank (known the moment a
+ * frontier exists, so the scoring overlaps the search); the stand-alone scoring calls on a caller's list take the
+ * contiguous block [rank * B, min(F, (rank + 1) * B)), B = ceil(F / nranks).  Records of the other frontiers are left
+ * zero in the output buffers.  fitslam_comm_init sets the shard itself. */
 FITSLAM_API fitslam_status fitslam_set_shard(fitslam_ctx *ctx, int rank, int nranks);
 /* The CUDA stream all work of this context is enqueued on (a cudaStream_t). */
 FITSLAM_API void *fitslam_stream(fitslam_ctx *ctx);
@@ -360,6 +365,19 @@ FITSLAM_API fitslam_status fitslam_cycle_fetch_candidates(fitslam_ctx *ctx, floa
  * {int32 information, int32 max_index, float fisher, uint32 flags (bit0 achievable, bit1 footprint in lethal,
  * bit2 ray failed, bit3 fisher valid, bit4 fisher safe)}. */
 FITSLAM_API fitslam_status fitslam_score_records(fitslam_ctx *ctx, void **device_ptr, uint64_t *bytes);
+/* One NCCL communicator per context, one process per GPU (the reference is one CPU thread and has no
+ * analogue).  fitslam_comm_unique_id: 128 bytes (an ncclUniqueId) made on rank 0 and carried to the other ranks by the
+ * host's own means.  fitslam_comm_init joins the communicator and sets the shard (rank, nranks).  From then on
+ *   - fitslam_set_costmap / fitslam_set_map_points are collective: rank 0 passes the data, the other ranks pass NULL (with
+ *     the same geometry / count) and receive it by ncclBroadcast over NVLink (a dirty rectangle broadcasts its rows only);
+ *   - fitslam_cycle merges the ranks' score records with an ncclAllReduce (int32 sum: one owner per row, zeros elsewhere)
+ *     on the context stream between its two halves; a caller that drives cycle_begin / cycle_end itself calls
+ *     fitslam_cycle_merge in between.
+ * libnccl.so.2 is loaded at run time by fitslam_comm_unique_id / fitslam_comm_init; a single-GPU host never needs it. */
+FITSLAM_API fitslam_status fitslam_comm_unique_id(void *id, uint64_t bytes);
+FITSLAM_API fitslam_status fitslam_comm_init(fitslam_ctx *ctx, const void *nccl_unique_id, int rank, int nranks);
+FITSLAM_API fitslam_status fitslam_comm_destroy(fitslam_ctx *ctx);
+FITSLAM_API fitslam_status fitslam_cycle_merge(fitslam_ctx *ctx);
 
 #ifdef __cplusplus
 }

@@ -26,7 +26,7 @@ def test_library_exports_every_symbol(capi):
 
 def test_abi_version_and_defaults(capi):
     lib = capi.load_library()
-    assert lib.fitslam_abi_version() == 1
+    assert lib.fitslam_abi_version() == 2
     p = capi.default_params(lib)
     assert (p.min_frontier_cluster_size, p.max_frontier_cluster_size, p.lethal_threshold) == (1, 20, 160)
     assert (p.max_camera_depth, p.delta_theta, p.camera_fov, p.robot_radius) == (2.0, 0.10, 1.04, 0.60)
@@ -38,7 +38,7 @@ def test_struct_layouts_match_header(capi):
     # sizes the C side static_asserts (csrc/api.cu); keeps ctypes/numpy views honest
     assert C.sizeof(capi.Params) == 192
     assert capi.FRONTIER_DTYPE.itemsize == 40 and capi.ARRIVAL_DTYPE.itemsize == 24
-    assert C.sizeof(capi.Selection) == 24 and C.sizeof(capi.CycleResult) == 32 + 24 + 32
+    assert C.sizeof(capi.Selection) == 24 and C.sizeof(capi.CycleResult) == 32 + 24 + 32 + 8
 
 
 def test_params_shared_with_oracle(capi, oracle):
