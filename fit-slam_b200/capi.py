@@ -168,6 +168,23 @@ class FitslamError(RuntimeError):
         self.status = status
 
 
+def _prefer_bundled_nccl():
+    """A Python process that also imports torch must not end up with two NCCL versions under one soname: point the library at
+    the NCCL PyTorch bundles (nvidia-nccl wheel) unless the caller named one or torch has loaded it already."""
+    if os.environ.get("FITSLAM_NCCL_LIB"):
+        return
+    import importlib.util
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except (ImportError, ValueError):
+        spec = None
+    for d in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+        cand = os.path.join(d, "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            os.environ["FITSLAM_NCCL_LIB"] = cand
+            return
+
+
 def _ptr(a):
     if a is None:
         return None
@@ -216,6 +233,7 @@ class Context:
     @staticmethod
     def comm_unique_id():
         """128 bytes (an ncclUniqueId): made on rank 0, carried to the other ranks by the host."""
+        _prefer_bundled_nccl()
         buf = C.create_string_buffer(128)
         st = load_library().fitslam_comm_unique_id(buf, 128)
         if st != OK:
@@ -224,6 +242,7 @@ class Context:
 
     def comm_init(self, unique_id, rank, nranks):
         assert len(unique_id) == 128
+        _prefer_bundled_nccl()
         self._check(self.lib.fitslam_comm_init(self.h, C.c_char_p(bytes(unique_id)), rank, nranks))
 
     def comm_destroy(self):

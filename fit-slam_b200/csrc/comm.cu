@@ -5,7 +5,7 @@
 // (fitslam_cycle_merge; fitslam_cycle does it between its two halves).  The reference has no analogue (one CPU thread).
 //
 // NCCL is loaded at run time (dlopen of libnccl.so.2 in fitslam_comm_init): a single-GPU host needs no NCCL at all, and a
-// process that already carries one (PyTorch's) shares it.
+// process that already carries one (PyTorch's) shares it.  FITSLAM_NCCL_LIB names a particular file.
 #include "ctx.h"
 
 #include <dlfcn.h>
@@ -26,10 +26,13 @@ struct CommState {
 
 static bool load_nccl(CommState *s, std::string *why) {
   if (s->lib) return true;
-  for (const char *name : {"libnccl.so.2", "libnccl.so"}) {
-    s->lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
-    if (s->lib) break;
-  }
+  // an NCCL the process already carries (a host linked against it, PyTorch's bundled one) is shared; else FITSLAM_NCCL_LIB
+  // names the file, else the loader's search path decides.  RTLD_LOCAL: the library's symbols stay out of the global scope
+  const char *named = getenv("FITSLAM_NCCL_LIB");
+  s->lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL | RTLD_NOLOAD);
+  if (!s->lib && named && *named) s->lib = dlopen(named, RTLD_NOW | RTLD_LOCAL);
+  for (const char *name : {"libnccl.so.2", "libnccl.so"})
+    if (!s->lib) s->lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
   if (!s->lib) { *why = std::string("cannot load libnccl: ") + dlerror(); return false; }
   s->GetUniqueId = reinterpret_cast<decltype(s->GetUniqueId)>(dlsym(s->lib, "ncclGetUniqueId"));
   s->CommInitRank = reinterpret_cast<decltype(s->CommInitRank)>(dlsym(s->lib, "ncclCommInitRank"));
