@@ -30,9 +30,17 @@
 namespace fitslam {
 
 static constexpr int CROWD_MAX = 512;       // exp(1 - j^0.8) underflows to 0 in float long before j = 512
-static constexpr int HASH_SLOTS = 16384;    // per-CTA voxel hash table: one packed word per slot (64 KB of dynamic shared memory)
-static constexpr int CNT_BITS = 10;         // low bits of a slot: landmarks in the voxel, saturating (>= CROWD_MAX is enough)
+// Per-CTA voxel bookkeeping, both in dynamic shared memory.  A bitmap over the part of the lookup domain a visible point can
+// fall in (per x-slab of voxels, the z-rows the image height admits: `XRow`) says whether a voxel has its first landmark; the
+// second and later landmarks of a voxel (about 1 in 8 at C2) and the points outside the bitmap's rows are counted in a
+// small hash table of packed words, (voxel + 1 | outside << 21) << CNT_BITS | count.
+static constexpr int BM_WORDS = 10240;      // 327 680 bits, 40 KB
+static constexpr int SEC_SLOTS = 8192;      // 32 KB
+static constexpr int CNT_BITS = 10;         // low bits of a slot: landmarks counted in it, saturating (>= CROWD_MAX is enough)
 static constexpr uint32_t CNT_MASK = (1u << CNT_BITS) - 1u;
+static constexpr uint32_t OUTSIDE_BIT = 1u << 21;  // key space of the voxels the bitmap has no bit for
+static constexpr int MAX_XROWS = 256;       // x-slabs of the lookup domain the per-slab table holds (more: no bitmap at all)
+static constexpr int FISHER_DYN_SMEM = (BM_WORDS + SEC_SLOTS) * 4;
 static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding square of the lookup domain)
 // 768 threads x 2 CTAs per SM = 48 warps (40 registers; the only spills are in thread 0's build_pose_frame).  The point
 // loop is latency-bound (one L2 load and one shared-memory CAS chain per iteration), so warps in flight are what pays:
@@ -136,10 +144,12 @@ struct FisherState {
   DevBuf<float> lut;
   int32_t dims[3] = {0, 0, 0}, org[3] = {0, 0, 0};
   bool have_lut = false;
+  bool attr_set = false;
   bool lut_dense = false;       // no NaN inside dims (true for a generated table)
   std::vector<int> axis[3];     // voxel indices per axis in generation order (file order of the .dat records)
   DevBuf<int32_t> d_axis;
   DevBuf<double> crowd;         // S[k] = sum_{j<=k} (float)exp(1 - pow(j, s)), k = 0..CROWD_MAX
+  DevBuf<uint2> xrow;           // per x-slab of the table: {first bit of the slab in the CTA bitmap, z_lo | rows << 16} (build_xrows)
   // map points, bucketed
   DevBuf<float4> pts;           // sorted by bin
   DevBuf<float> raw;            // staging copy of the caller's xyz
@@ -237,6 +247,8 @@ static fitslam_status upload_crowd_table(fitslam_ctx *c) {
   return FITSLAM_OK;
 }
 
+static fitslam_status build_xrows(fitslam_ctx *c);
+
 static fitslam_status alloc_lut(fitslam_ctx *c, const int lo[3], const int hi[3]) {
   FisherState *f = fstate(c);
   long n = 1;
@@ -245,10 +257,45 @@ static fitslam_status alloc_lut(fitslam_ctx *c, const int lo[3], const int hi[3]
     f->dims[a] = std::max(hi[a], 0) - f->org[a] + 1;
     n *= f->dims[a];
   }
-  if (n <= 0 || n >= (1l << (32 - CNT_BITS)) - 1) return fail(c, FITSLAM_E_INVALID, "lookup table too large (voxel index must fit 22 bits)");
+  if (n <= 0 || n >= (long)OUTSIDE_BIT - 1) return fail(c, FITSLAM_E_INVALID, "lookup table too large (voxel index must fit 21 bits)");
   FS_CUDA(c, f->lut.reserve((size_t)n));
   fill_nan_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(f->lut.p, n);
   ++c->launches;
+  return build_xrows(c);
+}
+
+// Rows of the CTA bitmap (fisher_kernel).  A visible point has |z| <= t * x in the pose frame, t = the larger half-height of
+// the image over fy, so the voxels of x-slab ix it can fall in have |iz| <= t * (ix + 0.5) + 1.5: per slab, dims[1] rows of
+// that many bits.  If that does not fit BM_WORDS (a wide image, a long table) the rows are narrowed until it does; landmarks
+// outside the rows are counted in the hash table instead, so the rows only decide speed, never the result.
+static fitslam_status build_xrows(fitslam_ctx *c) {
+  FisherState *f = fstate(c);
+  const int nx = f->dims[0], ny = f->dims[1], nz = f->dims[2];
+  if (nx > MAX_XROWS || nz > 0xffff) { f->xrow.release(); return FITSLAM_OK; }
+  const double t = std::max((double)c->prm.cy, (double)c->prm.img_max_v - (double)c->prm.cy) / (double)c->prm.fy;
+  std::vector<uint2> rows((size_t)nx);
+  for (double scale = 1.0; scale > 1e-3; scale *= 0.95) {
+    uint64_t bits = 0;
+    for (int i = 0; i < nx; ++i) {
+      const int ix = f->org[0] + i;  // voxel index along the viewing axis
+      int z_lo = 0, z_hi = -1;
+      if (ix >= 0) {
+        const int hz = (int)std::ceil(scale * (t * (ix + 0.5) + 1.5));
+        z_lo = std::max(0, -f->org[2] - hz);
+        z_hi = std::min(nz - 1, -f->org[2] + hz);
+      }
+      const int n = std::max(0, z_hi - z_lo + 1);
+      rows[(size_t)i] = make_uint2((uint32_t)bits, (uint32_t)z_lo | ((uint32_t)n << 16));
+      bits += (uint64_t)ny * n;
+    }
+    if (bits <= (uint64_t)BM_WORDS * 32) {
+      FS_CUDA(c, f->xrow.reserve((size_t)nx));
+      FS_CUDA(c, cudaMemcpyAsync(f->xrow.p, rows.data(), (size_t)nx * sizeof(uint2), cudaMemcpyHostToDevice, c->stream));
+      FS_CUDA(c, cudaStreamSynchronize(c->stream));
+      return FITSLAM_OK;
+    }
+  }
+  f->xrow.release();
   return FITSLAM_OK;
 }
 
@@ -579,6 +626,7 @@ struct FisherParams {
   uint32_t first;       // this launch scores poses [first, first + gridDim.x)
   uint32_t poses_per_frontier;  // record f = pose / poses_per_frontier (cycle mode)
   int lut_dense;        // every voxel inside dims has an entry: the visibility test needs no table read
+  const uint2 *xrow;    // dims[0] entries (build_xrows); null: no bitmap, every landmark is counted in the hash table
   int use_slice;        // poses are frontier * poses_per_frontier + window for the frontiers of `slice` (cycle.cu)
   ScoreSlice slice;
 };
@@ -696,12 +744,69 @@ __device__ __forceinline__ int voxel_of_visible_point(const float4 q, const Pose
   return (val == val) ? lin : -1;
 }
 
-// count one landmark in its voxel: packed slot (voxel + 1) << CNT_BITS | count; plain loads walk the probe sequence and
-// only the claiming / counting step is an atomic (shared-memory atomics cost 2-4 cycles per LANE on this part).
-// Returns the landmark's rank in its voxel (1 = it claimed the slot), or 0 if the table is full.
-__device__ __forceinline__ uint32_t table_count(uint32_t *tab, uint32_t h, int vox) {
-  uint32_t slot = h & (HASH_SLOTS - 1);
-  const uint32_t key = ((uint32_t)vox + 1u) << CNT_BITS;
+// The same decision as point_visible with one approximate reciprocal instead of two IEEE divisions: u and v are within 5e-4
+// of the exact ones (|u|, |v| < 1000 px), so a point at least 0.01 px inside all four image borders is visible and one a pixel
+// outside any of them is not; the others (3 in 1000) take the reference's arithmetic.
+__device__ __forceinline__ bool point_visible_fast(const float4 q, const PoseFrame &F, const FisherParams &P) {
+  V3f Pw; Pw.v[0] = -q.y; Pw.v[1] = -q.z; Pw.v[2] = q.x;
+  const V3f RP = mulv(F.Rcw, Pw);
+  const float Xc = RP.v[0] + F.tcw.v[0], Yc = RP.v[1] + F.tcw.v[1], Zc = RP.v[2] + F.tcw.v[2];
+  if (Zc < 0.0f) return false;
+  const float tx = P.fx * Xc, ty = P.fy * Yc;
+  if (Zc >= 1e-30f) {
+    const float rz = __frcp_rn(Zc);
+    const float ua = tx * rz + P.cx, va = ty * rz + P.cy;
+    if (ua >= 0.01f && ua <= P.max_u - 0.01f && va >= 0.01f && va <= P.max_v - 0.01f) return true;
+    if (ua < -1.0f || ua > P.max_u + 1.0f || va < -1.0f || va > P.max_v + 1.0f) return false;
+  }
+  const float u = tx / Zc + P.cx;
+  const float v = ty / Zc + P.cy;
+  return !(u < 0.0f || u > P.max_u) && !(v < 0.0f || v > P.max_v);
+}
+
+// voxel of a visible map point in the pose frame: the index into the lookup table (-1 if outside the table or a NaN entry)
+// and its bit in the CTA bitmap (-1 if the bitmap has no row for it)
+__device__ __forceinline__ int voxel_and_bit(const float4 q, const PoseFrame &F, const FisherParams &P, const uint2 *xrow, int *bit) {
+  V3f pos; pos.v[0] = q.x; pos.v[1] = q.y; pos.v[2] = q.z;
+  const V3f lp = mulv(F.Rinv, pos);
+  int idx[3];
+  bool ok = true;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {  // as voxel_of_visible_point
+    const float c = lp.v[a] + F.tinv.v[a];
+    const float rf = c * P.inv_step_f;
+    const float ri = rintf(rf);
+    int r;
+    if (fabsf(rf - ri) < 0.4999f && fabsf(rf) < 512.0f) {
+      r = (int)ri;
+    } else {
+      const double rd = round((double)c * P.inv_step);
+      r = (rd >= -2147483000.0 && rd <= 2147483000.0) ? (int)rd : INT_MIN;
+    }
+    ok = ok && r >= P.org[a] && r < P.org[a] + P.dims[a];
+    idx[a] = r - P.org[a];
+  }
+  *bit = -1;
+  if (!ok) return -1;
+  const int lin = (idx[0] * P.dims[1] + idx[1]) * P.dims[2] + idx[2];
+  if (!P.lut_dense) {
+    const float val = __ldg(P.lut + lin);
+    if (!(val == val)) return -1;
+  }
+  if (xrow) {
+    const uint2 xr = xrow[idx[0]];
+    const int rows = (int)(xr.y >> 16), zr = idx[2] - (int)(xr.y & 0xffffu);
+    if ((unsigned)zr < (unsigned)rows) *bit = (int)xr.x + idx[1] * rows + zr;
+  }
+  return lin;
+}
+
+// count one landmark in the hash table: packed slot key << CNT_BITS | count; plain loads walk the probe sequence and only
+// the claiming / counting step is an atomic (shared-memory atomics cost 2-4 cycles per LANE on this part).
+// Returns the count including this landmark (1 = it claimed the slot), or 0 if the table is full.
+__device__ __forceinline__ uint32_t table_count(uint32_t *tab, uint32_t h, uint32_t key22) {
+  uint32_t slot = h & (SEC_SLOTS - 1);
+  const uint32_t key = key22 << CNT_BITS;
   for (int probe = 0; probe < 256; ++probe) {
     uint32_t prev = ((volatile uint32_t *)tab)[slot];
     if (prev == 0u) prev = atomicCAS(&tab[slot], 0u, key | 1u);
@@ -711,7 +816,7 @@ __device__ __forceinline__ uint32_t table_count(uint32_t *tab, uint32_t h, int v
       if ((prev & CNT_MASK) >= CNT_MASK - 256u) return CROWD_MAX + 1u;
       return min((atomicAdd(&tab[slot], 1u) & CNT_MASK) + 1u, (uint32_t)CROWD_MAX + 1u);
     }
-    slot = (slot + 1) & (HASH_SLOTS - 1);
+    slot = (slot + 1) & (SEC_SLOTS - 1);
   }
   return 0u;
 }
@@ -721,11 +826,16 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
               uint8_t *__restrict__ safe_out, uint32_t *__restrict__ nvis_out, ScoreRecord *__restrict__ rec_out,
               const fitslam_arrival *__restrict__ arrival) {
   __shared__ PoseFrame F;
-  extern __shared__ uint32_t tab[];  // HASH_SLOTS packed slots: (voxel + 1) << CNT_BITS | count, 0 = empty
-  __shared__ uint32_t s_used, s_overflow, s_nchunk, s_next, s_chunk_ovf;
+  extern __shared__ uint32_t dyn[];
+  uint32_t *bm = dyn;               // BM_WORDS: bit = the voxel has its first landmark
+  uint32_t *tab = dyn + BM_WORDS;   // SEC_SLOTS packed slots, 0 = empty
+  __shared__ uint32_t s_used, s_coll, s_overflow, s_nchunk, s_next, s_chunk_ovf;
   __shared__ uint2 s_chunk[MAX_CHUNKS];  // [first, last) point ranges of the bins that survive the cull
   __shared__ float s_wq[FISHER_THREADS / 32][3][64];  // per warp: coordinates of visible points waiting for the voxel step
                                                        // (kept here instead of their indices: no second load per point)
+  __shared__ uint2 s_cq[FISHER_THREADS / 32][64];      // per warp: {table index | outside << 31, information} of landmarks
+                                                       // waiting for the hash-table step
+  __shared__ uint2 s_xrow[MAX_XROWS];
   __shared__ double s_red[FISHER_THREADS / 32];
   uint32_t pi;
   if (P.use_slice) {
@@ -738,6 +848,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
     if (pi >= P.n_poses) return;
   }
   if (threadIdx.x == 0) build_pose_frame(poses[pi], P, F);
+  else if (P.xrow && threadIdx.x >= 32 && threadIdx.x - 32 < (uint32_t)P.dims[0]) s_xrow[threadIdx.x - 32] = __ldg(P.xrow + threadIdx.x - 32);
+  const uint2 *xrow = P.xrow ? s_xrow : nullptr;
   __syncthreads();
   if (threadIdx.x < 11) build_pose_plane(P, F, (int)threadIdx.x);
   __syncthreads();
@@ -803,33 +915,36 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
 
   double total = 0.0;
   uint32_t used = 0;
-  // Attempt 1 inserts every contributing landmark into one table.  If the table fills up (more occupied voxels than
-  // slots), the rest of the attempt only counts; the count then sizes a multi-pass run in which pass p owns the voxels
+  // Attempt 1 takes every contributing landmark in one pass.  If the hash table fills up (more voxels with a second landmark
+  // than slots), the rest of the attempt only counts; the count then sizes a multi-pass run in which pass p owns the voxels
   // whose hash falls in partition p, so that every pass fits with a load factor <= 1/2.
   volatile uint32_t *v_overflow = &s_overflow;
+  float (*wq)[64] = s_wq[wid];
+  uint2 *cq = s_cq[wid];
   for (uint32_t npass = 1; npass <= 65536;) {
     total = 0.0;
-    if (threadIdx.x == 0) { s_used = 0; s_overflow = 0; }
+    if (threadIdx.x == 0) { s_used = 0; s_coll = 0; s_overflow = 0; }
     for (uint32_t pass = 0; pass < npass; ++pass) {
-      for (int i = threadIdx.x; i < HASH_SLOTS; i += FISHER_THREADS) tab[i] = 0;
+      for (int i = threadIdx.x; i < BM_WORDS + SEC_SLOTS; i += FISHER_THREADS) dyn[i] = 0;
       if (threadIdx.x == 0) s_next = 0;
       __syncthreads();
-      uint32_t my_used = 0;
-      // Two steps per point, with a compaction in between: the visibility test runs on every point of the chunk, the
-      // indices of the visible ones (about 4 in 10) queue up per warp, and the voxel + table step runs on full warps.
-      float (*wq)[64] = s_wq[wid];
-      uint32_t n_q = 0;
+      uint32_t my_used = 0, my_coll = 0;
+      // Three steps per point, with a compaction before the second and the third: the visibility test runs on every point
+      // of the chunk; the visible ones (about 6 in 10) queue up per warp and the voxel + bitmap step runs on full warps;
+      // the landmarks whose voxel already had one (1 in 8) queue up again and the hash-table step runs on full warps.
+      // Both queues are stacks: a step takes the top 32 entries, the rest stays where it is.
+      uint32_t n_q = 0, n_c = 0;
       while (true) {
         uint32_t ci = 0;
         if (lane == 0) ci = atomicAdd(&s_next, 1u);
         ci = __shfl_sync(0xffffffffu, ci, 0);
         const bool last = ci >= n_chunk;
         const uint2 ch = last ? make_uint2(0, 0) : s_chunk[ci];
-        for (uint32_t i0 = ch.x; i0 < ch.y || (last && n_q > 0); i0 += 32) {
+        for (uint32_t i0 = ch.x; i0 < ch.y || (last && (n_q > 0 || n_c > 0)); i0 += 32) {
           const uint32_t i = i0 + lane;
           float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
           if (i < ch.y) q = __ldg(P.pts + i);
-          const bool vis = i < ch.y && point_visible(q, F, P);
+          const bool vis = i < ch.y && point_visible_fast(q, F, P);
           const uint32_t bal = __ballot_sync(0xffffffffu, vis);
           if (vis) {
             const uint32_t at = n_q + __popc(bal & ((1u << lane) - 1u));
@@ -837,48 +952,71 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
           }
           n_q += __popc(bal);
           __syncwarp();
+          bool collide = false;
+          uint32_t c_key = 0;
+          float inf_v = 0.f;
           if (n_q >= 32 || (last && n_q > 0)) {
-            const uint32_t take = min(n_q, 32u);
-            int vox = -1;
-            if (lane < take) vox = voxel_of_visible_point(make_float4(wq[0][lane], wq[1][lane], wq[2][lane], 0.f), F, P);
-            const uint32_t rest = n_q - take;
-            float m0 = 0.f, m1 = 0.f, m2 = 0.f;
-            if (lane < rest) { m0 = wq[0][32 + lane]; m1 = wq[1][32 + lane]; m2 = wq[2][32 + lane]; }
+            const uint32_t take = min(n_q, 32u), at0 = n_q - take;
+            int vox = -1, bit = -1;
+            if (lane < take) vox = voxel_and_bit(make_float4(wq[0][at0 + lane], wq[1][at0 + lane], wq[2][at0 + lane], 0.f), F, P, xrow, &bit);
+            n_q = at0;
             __syncwarp();
-            if (lane < rest) { wq[0][lane] = m0; wq[1][lane] = m1; wq[2][lane] = m2; }
-            n_q = rest;
-            __syncwarp();
-            if (vox >= 0) {
-              const uint32_t h = mix32((uint32_t)vox);
-              if (npass == 1 || ((h >> 12) & (npass - 1)) == pass) {
-                ++my_used;
-                if (!*v_overflow) {  // a lost attempt keeps counting only
-                  // information(voxel) * exp(1 - k^0.8) for the k-th landmark of the voxel, added by whoever counted it:
-                  // the table load is in flight during the probe, and no pass over the table is needed afterwards
-                  const float inf_v = __ldg(P.lut + vox);
-                  const uint32_t k = table_count(tab, h, vox);
-                  if (k == 0u) *v_overflow = 1;
-                  else if (k == 1u) total += (double)inf_v;
-                  else if (k <= (uint32_t)CROWD_MAX) total += (double)inf_v * (__ldg(P.crowd + k) - __ldg(P.crowd + k - 1u));
+            if (vox >= 0 && (npass == 1 || ((mix32((uint32_t)vox) >> 12) & (npass - 1)) == pass)) {
+              ++my_used;
+              if (!*v_overflow) {  // a lost attempt keeps counting only
+                inf_v = __ldg(P.lut + vox);
+                if (bit >= 0) {
+                  const uint32_t w = (uint32_t)bit >> 5, m = 1u << (bit & 31);
+                  uint32_t old = ((volatile uint32_t *)bm)[w];
+                  if (!(old & m)) old = atomicOr(&bm[w], m);
+                  if (!(old & m)) total += (double)inf_v;  // first landmark of its voxel: factor exp(1 - 1^s) = 1
+                  else { collide = true; c_key = (uint32_t)vox; }
+                } else {
+                  collide = true;
+                  c_key = (uint32_t)vox | 0x80000000u;
                 }
               }
             }
+          }
+          const uint32_t cbal = __ballot_sync(0xffffffffu, collide);
+          if (cbal) {
+            if (collide) cq[n_c + __popc(cbal & ((1u << lane) - 1u))] = make_uint2(c_key, __float_as_uint(inf_v));
+            n_c += __popc(cbal);
+            my_coll += collide ? 1u : 0u;
+            __syncwarp();
+          }
+          if (n_c >= 32 || (last && n_q == 0 && n_c > 0)) {
+            const uint32_t take = min(n_c, 32u), at0 = n_c - take;
+            if (lane < take && !*v_overflow) {
+              const uint2 e = cq[at0 + lane];
+              const uint32_t outside = e.x >> 31, vox = e.x & 0x7fffffffu;
+              // the landmark that raises a voxel's count to k adds information(voxel) * exp(1 - k^s), as a difference of
+              // the host-tabulated prefix sums; inside the bitmap the table counts from the second landmark on
+              const uint32_t cnt = table_count(tab, mix32(vox), (vox + 1u) | (outside ? OUTSIDE_BIT : 0u));
+              const uint32_t k = cnt + 1u - outside;
+              if (cnt == 0u) *v_overflow = 1;
+              else if (k <= (uint32_t)CROWD_MAX) total += (double)__uint_as_float(e.y) * (__ldg(P.crowd + k) - __ldg(P.crowd + k - 1u));
+            }
+            n_c = at0;
+            __syncwarp();
           }
         }
         if (last) break;
       }
       if (my_used) atomicAdd(&s_used, my_used);
+      if (my_coll) atomicAdd(&s_coll, my_coll);
       __syncthreads();
-      if (s_overflow && npass > 1) break;  // npass == 1: finish the (only) pass so that s_used is the full count
+      if (s_overflow && npass > 1) break;  // npass == 1: finish the (only) pass so that the counts are complete
       __syncthreads();
     }
     used = s_used;
+    const uint32_t coll = s_coll;
     const bool ovf = s_overflow != 0;
     __syncthreads();
     if (!ovf) break;
-    if (npass == 1) {  // size the partitioning from the exact count: <= HASH_SLOTS / 2 landmarks per pass on average
+    if (npass == 1) {  // size the partitioning from the count of table entries at most needed: <= SEC_SLOTS / 2 per pass on average
       uint32_t want = 2;
-      while ((uint64_t)want * (HASH_SLOTS / 2) < used) want <<= 1;
+      while ((uint64_t)want * (SEC_SLOTS / 2) < coll) want <<= 1;
       npass = want;
     } else {
       npass <<= 1;  // skewed partitions: halve them again
@@ -928,10 +1066,10 @@ static fitslam_status fisher_params(fitslam_ctx *c, FisherParams &P) {
   P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
   P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
   P.lut_dense = f->lut_dense ? 1 : 0;
-  static bool attr_set = false;
-  if (!attr_set) {
-    FS_CUDA(c, cudaFuncSetAttribute(fisher_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HASH_SLOTS * 4));
-    attr_set = true;
+  P.xrow = f->xrow.p;
+  if (!f->attr_set) {  // (per device)
+    FS_CUDA(c, cudaFuncSetAttribute(fisher_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FISHER_DYN_SMEM));
+    f->attr_set = true;
   }
   return FITSLAM_OK;
 }
@@ -947,7 +1085,7 @@ fitslam_status fisher_score_device(fitslam_ctx *c, const fitslam_pose *d_poses, 
   P.n_poses = n;
   P.first = first;
   P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
-  fisher_kernel<<<count, FISHER_THREADS, HASH_SLOTS * 4, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, d_arrival);
+  fisher_kernel<<<count, FISHER_THREADS, FISHER_DYN_SMEM, c->stream>>>(P, d_poses, d_info, d_safe, d_nvis, d_rec, d_arrival);
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
   return FITSLAM_OK;
@@ -966,7 +1104,7 @@ fitslam_status fisher_score_slice(fitslam_ctx *c, cudaStream_t stream, const fit
   P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
   P.use_slice = 1;
   P.slice = slice;
-  fisher_kernel<<<(unsigned)(slots * P.poses_per_frontier), FISHER_THREADS, HASH_SLOTS * 4, stream>>>(P, d_poses, d_info, d_safe, d_nvis,
+  fisher_kernel<<<(unsigned)(slots * P.poses_per_frontier), FISHER_THREADS, FISHER_DYN_SMEM, stream>>>(P, d_poses, d_info, d_safe, d_nvis,
                                                                                                      d_rec, d_arrival);
   ++c->launches;
   FS_CUDA(c, cudaGetLastError());
