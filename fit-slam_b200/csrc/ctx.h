@@ -191,6 +191,7 @@ SelectState *sstate(fitslam_ctx *c);
 struct ScoreSlice {
   const uint32_t *range = nullptr;
   uint32_t first = 0, count = 0, cap = 0xFFFFFFFFu;
+  uint32_t limit = 0xFFFFFFFFu;   // with `range`: frontiers at or above this index belong to a later launch
   const uint8_t *tags = nullptr;  // per frontier: which launch scores it (nullptr: no filter)
   uint32_t tag = 0;
   uint32_t mod = 1, rem = 0;      // only frontiers f with f % mod == rem (the cycle's sharding: rank `rem` of `mod`)
@@ -198,14 +199,14 @@ struct ScoreSlice {
 #ifdef __CUDACC__
 __device__ __forceinline__ uint32_t slice_slots(const ScoreSlice &s) {  // slots of the slice (owned or not, any tag)
   if (!s.range) return s.count;
-  const uint32_t first = s.range[0], end = s.range[1];
+  const uint32_t first = s.range[0], end = min(s.range[1], s.limit);
   return end > first ? min(end - first, s.cap) : 0u;
 }
 __device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slot, uint32_t &f) {
   uint32_t first = s.first, count = s.count;
   if (s.range) {
     first = s.range[0];
-    const uint32_t end = s.range[1];
+    const uint32_t end = min(s.range[1], s.limit);
     count = end > first ? min(end - first, s.cap) : 0u;
   }
   if (slot >= count) return false;
@@ -221,6 +222,7 @@ static constexpr uint32_t EARLY_SLICE_CAP = 512;  // frontiers one early launch 
 struct EarlyHook {
   fitslam_status (*fn)(fitslam_ctx *c, cudaStream_t stream, const ScoreSlice &slice, void *user);
   void *user;
+  uint32_t limit;  // the scorer's buffers hold this many frontiers: the ones at or above it are left to the launches after the search
 };
 
 // stage entry points (each .cu file)

@@ -12,6 +12,7 @@
 // fitslam_cycle_end unpacks the merged records and runs the global steps (plan, normalise, select).
 #include "ctx.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <vector>
@@ -198,12 +199,16 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   // The frontiers are scored as the search produces them: buffers for as many frontiers as the search can return are laid
   // out first, and the search calls score_slice on its side streams.  With several ranks each scores the frontiers f with
   // f % nranks == rank into zeroed buffers (the caller's all-reduce merges the records).
-  EarlyHook hook{score_slice, &cfg};
+  EarlyHook hook{score_slice, &cfg, 0};
   const bool early = !getenv("FITSLAM_NO_EARLY_SCORING");
   uint32_t cap = 0;
   if (early) {
+    // (not for as many as the list can hold, N / 64 frontiers: 4 x what the last search found, at least 64 k; frontiers
+    // beyond that are left to the launches after the search)
     cap = frontier_capacity(c);
     if (cap == 0) return fail(c, FITSLAM_E_CUDA, "cycle: frontier buffers");
+    cap = std::min<uint32_t>(cap, std::max<uint32_t>(65536u, 4u * c->n_frontiers));
+    hook.limit = cap;
     FS_CUDA(c, c->arrival.reserve(cap));
     FS_CUDA(c, c->records.reserve(cap));
     if (ppf) {
@@ -271,7 +276,8 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   rest.count = F;
   rest.mod = (uint32_t)c->nranks;
   rest.rem = (uint32_t)c->rank;
-  rest.tags = frontier_tags_device(c);
+  // (more frontiers than the early buffers hold: they were grown above, so every frontier is scored now, whatever its tag says)
+  rest.tags = scored_early ? frontier_tags_device(c) : nullptr;
   rest.tag = TAG_FINAL;
   // two launches so that the stage times keep their meaning: arrival, then poses + Fisher
   ScoreCfg arrival_only = cfg;

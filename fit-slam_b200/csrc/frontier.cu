@@ -104,6 +104,7 @@ struct SearchParams {
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
   uint32_t ow_part_levels; // levels per launch of the shared-memory outer wavefront
   uint32_t early_cap;      // frontiers one early scoring launch covers (what exceeds it waits for the launches after the search)
+  uint32_t early_limit;    // frontier indices at or above this are not scored early (EarlyHook::limit)
   uint32_t fix_all;        // FITSLAM_FIX_ALL=1: every chunk's median sort goes to the host (test of that path)
 };
 
@@ -1644,7 +1645,7 @@ chunk_kernel(const SearchParams S, const uint32_t *__restrict__ osize, const uin
   if (cnt->overflow) return;
   const uint32_t c_lo = coll < 0 ? 0u : cnt->coll_c0[coll], c_hi = coll < 0 ? min(cnt->n_comp, S.comp_cap) : min(cnt->coll_c1[coll], S.comp_cap);
   const uint32_t f_lo = coll < 0 ? 0u : cnt->coll_fr[coll][0];
-  const uint32_t f_hi = coll < 0 ? cnt->n_frontiers : min(cnt->coll_fr[coll][1], f_lo + S.early_cap);
+  const uint32_t f_hi = coll < 0 ? cnt->n_frontiers : min(min(cnt->coll_fr[coll][1], S.early_limit), f_lo + S.early_cap);
   if (f_hi > S.front_cap) return;
   const uint32_t run = (uint32_t)S.max_size + 1u;
   const uint32_t W = S.map.W;
@@ -1867,6 +1868,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   }
   // a batch is about 1/12 of the frontiers; the launches are sized for a quarter of the last search's count
   S.early_cap = std::min<uint32_t>(std::max<uint32_t>(EARLY_SLICE_CAP, s->last.n_frontiers / 4u), 8192u);
+  S.early_limit = hook ? hook->limit : 0xFFFFFFFFu;
   S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
   S.ow_wide = getenv("FITSLAM_OW_NOWIDE") ? 0u : 1u;
   S.fix_all = getenv("FITSLAM_FIX_ALL") ? 1u : 0u;
@@ -1989,6 +1991,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
           ScoreSlice sl;
           sl.range = range;
           sl.cap = S.early_cap;
+          sl.limit = S.early_limit;
           sl.tags = s->ftag.p;
           sl.tag = tag;
           cudaError_t e = cudaEventRecord(s->ev_chunk[coll][cls], sts[cls]);
