@@ -72,6 +72,7 @@ class CycleResult(C.Structure):
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NO_COSTMAP, E_ROBOT_OUT_OF_BOUNDS, E_NO_FRONTIERS, E_NO_POLYGON, \
     E_ARRIVAL_UTILITY, E_COST_OUT_OF_BOUNDS, E_NO_LOOKUP_TABLE, E_NO_MAP_POINTS, E_IO = range(13)
 DIST_GIVEN, DIST_EUCLIDEAN = 0, 1
+LIV_STATIC_MAX_POINTS = 4194304  # FITSLAM_LIV_STATIC_MAX_POINTS
 FISHER_OFF, FISHER_BEST_YAW, FISHER_ALL_YAWS = 0, 1, 2
 
 _vp, _u32p, _dp = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_double)
@@ -108,6 +109,7 @@ PROTOTYPES = {
     "fitslam_fisher_lookup_copy": (C.c_int, [_vp, _vp, C.c_uint64]),
     "fitslam_score_fisher": (C.c_int, [_vp, _vp, C.c_uint32, _vp, _vp, _vp]),
     "fitslam_landmarks_in_view": (C.c_int, [_vp, _vp, _vp, C.c_uint32, _u32p]),
+    "fitslam_landmarks_in_view_static": (C.c_int, [_vp, _vp, C.c_uint64, _vp, _vp, C.c_uint32, _vp]),
     "fitslam_normalise_select": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp, _vp,
                                            C.POINTER(Selection)]),
     "fitslam_cycle": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, C.POINTER(CycleResult)]),
@@ -387,6 +389,12 @@ class Context:
         n = C.c_uint32(0)
         st = self._check(self.lib.fitslam_landmarks_in_view(self.h, _ptr(pose), _ptr(out), cap, C.byref(n)), allow=(E_CAPACITY,))
         return st, out[:min(n.value, cap)], n.value
+
+    def landmarks_in_view_static(self, d_xyz, n_points, d_pose, d_out, capacity, d_count):
+        """fitslam_landmarks_in_view_static: raw DEVICE addresses in and out, nothing allocated, nothing synchronised (the
+        kernels run on self.stream).  Returns the status; LIV_STATIC_MAX_POINTS is the largest n_points."""
+        return self.lib.fitslam_landmarks_in_view_static(self.h, _ptr(d_xyz), n_points, _ptr(d_pose), _ptr(d_out), capacity,
+                                                         _ptr(d_count))
 
     def normalise_select(self, path_length_m, path_heading, blacklisted=None):
         n = len(path_length_m)

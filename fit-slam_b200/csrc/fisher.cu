@@ -25,6 +25,8 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <mutex>
+#include <string>
 #include <vector>
 
 namespace fitslam {
@@ -1319,5 +1321,75 @@ extern "C" fitslam_status fitslam_landmarks_in_view(fitslam_ctx *c, const fitsla
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
   }
   if (*count > capacity) return fail(c, FITSLAM_E_CAPACITY, "landmarks_in_view: more visible landmarks than capacity (count holds the number)");
+  return FITSLAM_OK;
+}
+
+// ================================================================================================ no-allocation variant
+// fitslam_landmarks_in_view_static: the same three launches as fitslam_landmarks_in_view for callers that cannot call
+// cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The scratch the kernels need (one count per tile of LIV_TILE points + the total) lives in
+// a file-scope device array of fixed size instead of a context buffer; the caller passes every input and output as a device
+// pointer, nothing is staged, nothing is synchronised.
+namespace fitslam {
+
+static constexpr uint64_t LIV_STATIC_MAX_POINTS = FITSLAM_LIV_STATIC_MAX_POINTS;
+static constexpr uint32_t LIV_STATIC_MAX_TILES = (uint32_t)((LIV_STATIC_MAX_POINTS + LIV_TILE - 1) / LIV_TILE);
+// 16 KB + one word per GPU that loads the library, held until the process exits
+static __device__ __align__(256) uint32_t liv_static_scratch[LIV_STATIC_MAX_TILES + 1];
+
+// In host code `liv_static_scratch` is a host-side stand-in, not a device address: the kernels get the address
+// cudaGetSymbolAddress returns, looked up once per device with that device current.
+static constexpr int LIV_STATIC_MAX_DEVICES = 64;
+static uint32_t *liv_static_ptr[LIV_STATIC_MAX_DEVICES] = {};
+static std::mutex liv_static_mutex;
+
+static cudaError_t liv_static_address(int device, uint32_t **out) {
+  if (device < 0 || device >= LIV_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(liv_static_mutex);
+  if (!liv_static_ptr[device]) {
+    uint32_t *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&p, liv_static_scratch);  // (the caller has made `device` current)
+    if (e != cudaSuccess) return e;
+    liv_static_ptr[device] = p;
+  }
+  *out = liv_static_ptr[device];
+  return cudaSuccess;
+}
+
+}  // namespace fitslam
+
+extern "C" fitslam_status fitslam_landmarks_in_view_static(fitslam_ctx *c, const float *d_xyz, uint64_t n_points,
+                                                           const fitslam_pose *d_pose, float *d_out_xyz, uint32_t capacity,
+                                                           uint32_t *d_count) {
+  if (!c || !d_pose || !d_count || (!d_xyz && n_points) || (!d_out_xyz && capacity))
+    return fail(c, FITSLAM_E_INVALID, "landmarks_in_view_static: null argument");
+  if (n_points > LIV_STATIC_MAX_POINTS)
+    return fail(c, FITSLAM_E_CAPACITY, "landmarks_in_view_static: n_points = " + std::to_string(n_points) + " exceeds the static scratch (" +
+                                           std::to_string(LIV_STATIC_MAX_POINTS) + " points, FITSLAM_LIV_STATIC_MAX_POINTS); use fitslam_landmarks_in_view");
+  FS_CUDA(c, cudaSetDevice(c->device));
+  if (n_points == 0) {
+    FS_CUDA(c, cudaMemsetAsync(d_count, 0, sizeof(uint32_t), c->stream));
+    return FITSLAM_OK;
+  }
+  uint32_t *scratch = nullptr;
+  FS_CUDA(c, liv_static_address(c->device, &scratch));
+  FisherParams P;
+  memset(&P, 0, sizeof(P));
+  P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
+  P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
+  const uint32_t n_tiles = (uint32_t)((n_points + LIV_TILE - 1) / LIV_TILE);
+  // every scratch word this call reads is written by it first (pass 0 writes all n_tiles counts, the scan writes the total):
+  // nothing has to start at zero, whatever the last call left behind
+  uint32_t *tiles = scratch, *total = scratch + LIV_STATIC_MAX_TILES;
+  landmarks_in_view_kernel<0><<<n_tiles, LIV_THREADS, 0, c->stream>>>(P, d_pose, d_xyz, n_points, tiles, nullptr, nullptr, 0);
+  liv_scan_kernel<<<1, 1024, 0, c->stream>>>(tiles, n_tiles, total);
+  c->launches += 2;
+  const uint32_t cap = (uint32_t)std::min<uint64_t>(capacity, n_points);
+  if (cap) {
+    landmarks_in_view_kernel<1><<<n_tiles, LIV_THREADS, 0, c->stream>>>(P, d_pose, d_xyz, n_points, nullptr, tiles, d_out_xyz, cap);
+    ++c->launches;
+  }
+  FS_CUDA(c, cudaGetLastError());
+  FS_CUDA(c, cudaMemcpyAsync(d_count, total, sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
   return FITSLAM_OK;
 }

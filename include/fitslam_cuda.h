@@ -315,6 +315,24 @@ FITSLAM_API fitslam_status fitslam_score_fisher(fitslam_ctx *ctx, const fitslam_
 FITSLAM_API fitslam_status fitslam_landmarks_in_view(fitslam_ctx *ctx, const fitslam_pose *pose, float *out_xyz,
                                                      uint32_t capacity, uint32_t *count);
 
+/* The same query without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It calls no cudaMalloc / cudaFree / allocating routine, stages nothing and does not synchronise: three kernels and one
+ * 4-byte device-to-device copy are enqueued on the context stream (fitslam_stream) and the call returns.
+ *   d_xyz     n_points x 3 floats, DEVICE memory, the caller's map points (the resident points of fitslam_set_map_points are
+ *             not used; n_points <= FITSLAM_LIV_STATIC_MAX_POINTS, else FITSLAM_E_CAPACITY and nothing is enqueued)
+ *   d_pose    one fitslam_pose in DEVICE memory
+ *   d_out_xyz capacity x 3 floats, DEVICE memory: the first min(count, capacity) visible landmarks, as fitslam_landmarks_in_view
+ *   d_count   one uint32 in DEVICE memory: the number of visible landmarks (may exceed capacity; the caller compares)
+ * The kernels' scratch (one count per 1024 points + the total, 16 KB) is a fixed device array inside the library, one per GPU
+ * that loads it, held until the process exits.  Every call on a GPU shares it and finds the last call's contents there; a
+ * call overwrites every word before it reads it, so nothing needs clearing, but two calls that overlap on the GPU (different
+ * contexts / streams of one device) race: keep them ordered. */
+#define FITSLAM_LIV_STATIC_MAX_POINTS 4194304ull
+FITSLAM_API fitslam_status fitslam_landmarks_in_view_static(fitslam_ctx *ctx, const float *d_xyz, uint64_t n_points,
+                                                            const fitslam_pose *d_pose, float *d_out_xyz, uint32_t capacity,
+                                                            uint32_t *d_count);
+
 /* ------------------------------------------------------------------ normalisation + selection */
 /* FrontierCostsManager::assignCosts U1 block (DEP/src/FrontierCostsManager.cpp:121-205) followed by
  * FullPathOptimizer::getFilteredFrontiersN (DEP/src/FullPathOptimizer.cpp:157-227).
