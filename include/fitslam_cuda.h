@@ -311,7 +311,12 @@ FITSLAM_API fitslam_status fitslam_score_fisher(fitslam_ctx *ctx, const fitslam_
  * one transformed into the pose frame as ORBW/src/rgbd/rgbd-slam-node.cpp:406-429 does, in map-point order.
  * out_xyz: capacity x 3 floats (host or device; the wire widens them to float64); *count = visible landmarks, also
  * when it exceeds capacity (FITSLAM_E_CAPACITY, the first `capacity` are written).  The keyframe-structured
- * non-exhaustive mode (:228-272) is not built. */
+ * non-exhaustive mode (:228-272) is not built.
+ * NOT the service's response on a multi-keyframe atlas: the service stops adding keyframes once more than maxLandmarks = 1000
+ * landmarks are collected (:270-271, also in exhaustive mode; rgbd-slam-node.cpp:413).  That cutoff needs the atlas's
+ * keyframe-to-point lists, which this interface does not receive: the resident cloud is treated as ONE keyframe, for which the
+ * reference's loop returns every visible point too.  The same holds for fitslam_score_fisher and the cycle's Fisher stage:
+ * their totals are upper bounds of what isPoseSafe would sum behind the real service. */
 FITSLAM_API fitslam_status fitslam_landmarks_in_view(fitslam_ctx *ctx, const fitslam_pose *pose, float *out_xyz,
                                                      uint32_t capacity, uint32_t *count);
 
