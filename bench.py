@@ -183,6 +183,7 @@ def run_gpu(args):
         raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     uids = [None, None]
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version banner must not share stdout with the JSON line
     if world > 1:
         # torch.distributed is the launcher's plumbing only (barriers, the max over ranks of the timings, carrying the two
         # 128-byte NCCL ids); the data path's collectives are the library's own (csrc/comm.cu)
