@@ -1475,8 +1475,12 @@ replay_line_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint
       const int nx = (int)x + ddx, ny = (int)y + ddy;
       const bool in = act && nx >= 0 && ny >= 0 && nx < (int)W && ny < (int)H;
       const uint32_t nb = (uint32_t)ny * W + (uint32_t)nx;
-      const bool bit = in && ((__ldg(bits + (size_t)ny * S.wpr + ((uint32_t)nx >> 5)) >> ((uint32_t)nx & 31u)) & 1u);
-      const uint32_t sv = bit ? slot[nb] : IL_VISITED;  // isNewFrontierCell: a mask cell whose frontier_flag is not set yet
+      // both loads at once (the slot word of a cell that turns out not to be a mask cell is read and dropped): a step is one
+      // memory round trip, not two
+      const uint32_t mw = in ? __ldg(bits + (size_t)ny * S.wpr + ((uint32_t)nx >> 5)) : 0u;
+      const uint32_t sw = in ? slot[nb] : IL_VISITED;
+      const bool bit = (mw >> ((uint32_t)nx & 31u)) & 1u;
+      const uint32_t sv = bit ? sw : IL_VISITED;  // isNewFrontierCell: a mask cell whose frontier_flag is not set yet
       const bool acc = !(sv & IL_VISITED);
       const uint32_t bal = __ballot_sync(0xffffffffu, acc);
       if (acc) {
