@@ -54,7 +54,8 @@ ARRIVAL_DTYPE = np.dtype([("information", "<i4"), ("max_index", "<i4"), ("theta_
 POSE_DTYPE = np.dtype([("x", "<f8"), ("y", "<f8"), ("z", "<f8"), ("qx", "<f8"), ("qy", "<f8"), ("qz", "<f8"),
                        ("qw", "<f8")])
 RECORD_DTYPE = np.dtype([("information", "<i4"), ("max_index", "<i4"), ("fisher", "<f4"), ("flags", "<u4")])
-assert FRONTIER_DTYPE.itemsize == 40 and ARRIVAL_DTYPE.itemsize == 24 and POSE_DTYPE.itemsize == 56
+KEYFRAME_DTYPE = np.dtype([("Rwc", "<f4", (9,)), ("twc", "<f4", (3,)), ("first", "<u4"), ("count", "<u4")])  # fitslam_keyframe
+assert FRONTIER_DTYPE.itemsize == 40 and ARRIVAL_DTYPE.itemsize == 24 and POSE_DTYPE.itemsize == 56 and KEYFRAME_DTYPE.itemsize == 56
 
 
 class Selection(C.Structure):
@@ -110,6 +111,9 @@ PROTOTYPES = {
     "fitslam_score_fisher": (C.c_int, [_vp, _vp, C.c_uint32, _vp, _vp, _vp]),
     "fitslam_landmarks_in_view": (C.c_int, [_vp, _vp, _vp, C.c_uint32, _u32p]),
     "fitslam_landmarks_in_view_static": (C.c_int, [_vp, _vp, C.c_uint64, _vp, _vp, C.c_uint32, _vp]),
+    "fitslam_set_keyframes": (C.c_int, [_vp, _vp, C.c_uint32, _vp, C.c_uint64]),
+    "fitslam_landmarks_in_view_keyframes": (C.c_int, [_vp, _vp, C.c_int32, C.c_float, C.c_float, C.c_int, _vp, C.c_uint32, _u32p, _u32p]),
+    "fitslam_score_fisher_keyframes": (C.c_int, [_vp, _vp, C.c_int32, C.c_float, C.c_int, _vp, _vp, _u32p, _u32p]),
     "fitslam_normalise_select": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp, _vp,
                                            C.POINTER(Selection)]),
     "fitslam_cycle": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double, _vp, C.c_int, C.POINTER(CycleResult)]),
@@ -389,6 +393,32 @@ class Context:
         n = C.c_uint32(0)
         st = self._check(self.lib.fitslam_landmarks_in_view(self.h, _ptr(pose), _ptr(out), cap, C.byref(n)), allow=(E_CAPACITY,))
         return st, out[:min(n.value, cap)], n.value
+
+    def set_keyframes(self, keyframes, point_index):
+        """The atlas of the keyframe-structured landmark query: KEYFRAME_DTYPE records in service order + the concatenated
+        map-point lists (indices into the points of set_map_points)."""
+        keyframes = np.ascontiguousarray(keyframes, dtype=KEYFRAME_DTYPE)
+        point_index = np.ascontiguousarray(point_index, dtype=np.uint32)
+        self._check(self.lib.fitslam_set_keyframes(self.h, _ptr(keyframes), len(keyframes), _ptr(point_index), len(point_index)))
+
+    def landmarks_in_view_keyframes(self, pose, max_landmarks=1000, max_distance=5.0, exhaustive=False, capacity=None):
+        """mapPointsVisibleFromPose over the keyframe atlas: (status, xyz [count, 3] in the pose frame, count, keyframes checked)."""
+        pose = np.ascontiguousarray(pose, dtype=POSE_DTYPE).reshape(1)
+        cap = int(capacity if capacity is not None else 1 << 22)
+        out = np.zeros((cap, 3), np.float32)
+        n, chk = C.c_uint32(0), C.c_uint32(0)
+        st = self._check(self.lib.fitslam_landmarks_in_view_keyframes(self.h, _ptr(pose), max_landmarks, max_distance, 0.0, int(exhaustive),
+                                                                       _ptr(out), cap, C.byref(n), C.byref(chk)), allow=(E_CAPACITY,))
+        return st, out[:min(n.value, cap)], n.value, chk.value
+
+    def score_fisher_keyframes(self, pose, max_landmarks=1000, max_distance=5.0, exhaustive=False):
+        """isPoseSafe behind the keyframe-structured service: (information, safe, landmarks returned, landmarks used)."""
+        pose = np.ascontiguousarray(pose, dtype=POSE_DTYPE).reshape(1)
+        info, safe = np.zeros(1, np.float32), np.zeros(1, np.uint8)
+        n, used = C.c_uint32(0), C.c_uint32(0)
+        self._check(self.lib.fitslam_score_fisher_keyframes(self.h, _ptr(pose), max_landmarks, max_distance, int(exhaustive), _ptr(info),
+                                                            _ptr(safe), C.byref(n), C.byref(used)))
+        return float(info[0]), int(safe[0]), n.value, used.value
 
     def landmarks_in_view_static(self, d_xyz, n_points, d_pose, d_out, capacity, d_count):
         """fitslam_landmarks_in_view_static: raw DEVICE addresses in and out, nothing allocated, nothing synchronised (the

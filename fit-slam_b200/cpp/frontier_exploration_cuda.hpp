@@ -360,6 +360,42 @@ public:
     for (uint32_t i = 0; i < n; ++i) { out[i].x = xyz[3 * i]; out[i].y = xyz[3 * i + 1]; out[i].z = xyz[3 * i + 2]; }
     return out;
   }
+  // ---- the service as it really runs on a multi-keyframe atlas (orb_slam3_interface.cpp:188-317): keyframes in service order
+  // with GetPoseInverse() and their map-point lists, the per-keyframe prefilter unless exhaustive, and the cutoff after more
+  // than maxLandmarks landmarks (1000 in rgbd-slam-node.cpp:413)
+  void setKeyframes(const std::vector<fitslam_keyframe> &keyframes, const std::vector<uint32_t> &point_index) {
+    ctx_->check(fitslam_set_keyframes(ctx_->get(), keyframes.data(), (uint32_t)keyframes.size(), point_index.data(), point_index.size()),
+                "fitslam_set_keyframes");
+  }
+  std::vector<geometry_msgs::msg::Point> getLandmarksInView(const geometry_msgs::msg::Pose &pose, float max_dist_pose_observation,
+                                                            float max_angle_pose_observation, bool exhaustive_search,
+                                                            int maxLandmarks = 1000) {
+    const fitslam_pose p{pose.position.x, pose.position.y, pose.position.z, pose.orientation.x, pose.orientation.y, pose.orientation.z,
+                         pose.orientation.w};
+    uint32_t n = 0, checked = 0;
+    fitslam_status st = fitslam_landmarks_in_view_keyframes(ctx_->get(), &p, maxLandmarks, max_dist_pose_observation,
+                                                            max_angle_pose_observation, exhaustive_search ? 1 : 0, nullptr, 0, &n, &checked);
+    if (st != FITSLAM_OK && st != FITSLAM_E_CAPACITY) ctx_->check(st, "fitslam_landmarks_in_view_keyframes");
+    std::vector<float> xyz(3 * (size_t)n);
+    if (n)
+      ctx_->check(fitslam_landmarks_in_view_keyframes(ctx_->get(), &p, maxLandmarks, max_dist_pose_observation, max_angle_pose_observation,
+                                                      exhaustive_search ? 1 : 0, xyz.data(), n, &n, &checked),
+                  "fitslam_landmarks_in_view_keyframes");
+    std::vector<geometry_msgs::msg::Point> out(n);
+    for (uint32_t i = 0; i < n; ++i) { out[i].x = xyz[3 * i]; out[i].y = xyz[3 * i + 1]; out[i].z = xyz[3 * i + 2]; }
+    return out;
+  }
+  // isPoseSafe with the request fields the reference fills (FisherInfoManager.cpp:48-57) behind that service
+  bool isPoseSafe(geometry_msgs::msg::Pose &given_pose, bool exhaustiveSearch, float max_dist_pose_observation, float &information,
+                  int maxLandmarks = 1000) {
+    const fitslam_pose p{given_pose.position.x, given_pose.position.y, given_pose.position.z, given_pose.orientation.x,
+                         given_pose.orientation.y, given_pose.orientation.z, given_pose.orientation.w};
+    uint8_t safe = 0;
+    ctx_->check(fitslam_score_fisher_keyframes(ctx_->get(), &p, maxLandmarks, max_dist_pose_observation, exhaustiveSearch ? 1 : 0,
+                                               &information, &safe, nullptr, nullptr),
+                "fitslam_score_fisher_keyframes");
+    return safe != 0;
+  }
 private:
   CudaContextPtr ctx_;
   std::string lookup_path_;

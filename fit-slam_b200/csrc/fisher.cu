@@ -167,6 +167,20 @@ struct FisherState {
   DevBuf<float> info;
   DevBuf<uint8_t> safe;
   DevBuf<uint32_t> nvis;
+  // keyframe-structured atlas (fitslam_set_keyframes) and the scratch of its query
+  DevBuf<fitslam_keyframe> kf;
+  DevBuf<uint32_t> kf_entry_pt, kf_entry_kf;  // per entry: map point, keyframe
+  uint32_t n_kf = 0;
+  uint64_t n_entries = 0;
+  bool have_kf = false;
+  DevBuf<uint32_t> kf_first;   // per map point: its first entry among the keyframes that pass the prefilter
+  DevBuf<uint32_t> kf_state;   // 4 words per keyframe: passes the prefilter, visible landmarks, landmarks before it, processed
+  DevBuf<uint8_t> kf_vis;      // per entry: a visible landmark taken for the first time
+  DevBuf<uint32_t> kf_tiles;   // ordered compaction: per-tile counts + total + keyframes checked
+  DevBuf<float> kf_out;        // the response, pose frame
+  DevBuf<uint32_t> kf_vox;     // Fisher over the response: landmarks per voxel, per landmark {voxel, rank}
+  DevBuf<int32_t> kf_lm;
+  DevBuf<double> kf_part;
 };
 
 static FisherState *fstate(fitslam_ctx *c) {
@@ -179,7 +193,9 @@ void destroy_fisher_state(fitslam_ctx *c) {
   FisherState *f = c->fi;
   f->lut.release(); f->d_axis.release(); f->crowd.release(); f->pts.release(); f->raw.release();
   f->bin_start.release(); f->bin_cursor.release(); f->bbox.release(); f->poses.release(); f->info.release();
-  f->safe.release(); f->nvis.release();
+  f->safe.release(); f->nvis.release(); f->xrow.release();
+  f->kf.release(); f->kf_entry_pt.release(); f->kf_entry_kf.release(); f->kf_first.release(); f->kf_state.release();
+  f->kf_vis.release(); f->kf_tiles.release(); f->kf_out.release(); f->kf_vox.release(); f->kf_lm.release(); f->kf_part.release();
   delete f;
   c->fi = nullptr;
 }
@@ -558,6 +574,7 @@ extern "C" fitslam_status fitslam_set_map_points(fitslam_ctx *c, const float *xy
   cudaSetDevice(c->device);
   FisherState *f = fstate(c);
   f->have_points = false;
+  f->have_kf = false;  // the keyframes' point indices meant the previous points
   f->n_points = n;
   FS_CUDA(c, f->raw.reserve(3 * n + 3));
   FS_CUDA(c, f->pts.reserve(n + 1));
@@ -1321,6 +1338,400 @@ extern "C" fitslam_status fitslam_landmarks_in_view(fitslam_ctx *c, const fitsla
     FS_CUDA(c, cudaStreamSynchronize(c->stream));
   }
   if (*count > capacity) return fail(c, FITSLAM_E_CAPACITY, "landmarks_in_view: more visible landmarks than capacity (count holds the number)");
+  return FITSLAM_OK;
+}
+
+// ================================================================================================ keyframe-structured query
+// ORBSLAM3Interface::mapPointsVisibleFromPose as the service runs it (ORBW/src/orb_slam3_interface.cpp:188-317): keyframes in
+// the caller's order, a per-keyframe prefilter unless exhaustive_search (:240-267), every map point once (:263-265), and the
+// cutoff "more than maxLandmarks collected: stop" checked at the start of a keyframe (:270-271).  The loop is sequential in the
+// reference; what it computes is order-free up to a prefix sum:
+//   pass[k]      the prefilter of keyframe k (independent per keyframe)
+//   first[p]     the first entry of map point p among the passing keyframes (atomicMin of entry indices): the entry that
+//                processes p.  The cutoff removes a suffix of keyframes, and the first entry of p inside the kept prefix is
+//                first[p] or nothing, so it can be taken before the cutoff is known
+//   cnt[k]       visible fresh landmarks of keyframe k;  before[k] = sum of cnt over j < k
+//   processed[k] = pass[k] and before[k] <= maxLandmarks (monotone, so this is the reference's `break`)
+// and the response is the ordered compaction of the visible fresh entries of processed keyframes.
+namespace fitslam {
+
+static constexpr uint32_t KF_PASS = 0, KF_CNT = 1, KF_BEFORE = 2, KF_PROC = 3;
+
+// Eigen 3.4 eulerAngles(2, 0, 1) (odd = 0, i = 2, j = 0, k = 1) + rotationORBToEulerROS (ORBW/src/type_conversion.cpp:143-153),
+// component 2
+__device__ float kf_relative_yaw(const M3f &R) {
+  float res0 = atan2f(R.m[0][1], R.m[1][1]);
+  if (res0 > 0.0f) res0 -= (float)M_PI;
+  const float s1 = sinf(res0), c1 = cosf(res0);
+  float res2 = atan2f(s1 * R.m[1][2] - c1 * R.m[0][2], c1 * R.m[0][0] - s1 * R.m[1][0]);
+  res2 = -res2;
+  float e2 = -res2;
+  e2 = e2 < 0 ? (float)((2 * M_PI) + (double)e2) : e2;
+  return e2;
+}
+
+__global__ void kf_prefilter_kernel(const FisherParams P, const fitslam_pose *__restrict__ pose, const fitslam_keyframe *__restrict__ kfs,
+                                    uint32_t n_kf, float max_distance, int exhaustive, uint32_t *state) {
+  __shared__ PoseFrame F;
+  if (threadIdx.x == 0) build_pose_frame(*pose, P, F);
+  __syncthreads();
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_kf) return;
+  bool pass = true;
+  if (!exhaustive) {
+    M3f Rwc;
+    V3f twc;
+    for (int a = 0; a < 3; ++a) {
+      for (int b = 0; b < 3; ++b) Rwc.m[a][b] = kfs[k].Rwc[3 * a + b];
+      twc.v[a] = kfs[k].twc[a];
+    }
+    const M3f relR = mulm(F.Rcw, Rwc);  // rel_T_CamToKF = Tcw * pKF->GetPoseInverse()
+    const V3f rt = mulv(F.Rcw, twc);
+    const float tx = rt.v[0] + F.tcw.v[0], ty = rt.v[1] + F.tcw.v[1], tz = rt.v[2] + F.tcw.v[2];
+    const float yaw = kf_relative_yaw(relR);
+    const float dist = sqrtf(dot3(tx, tx, ty, ty, tz, tz));
+    if ((double)dist >= (double)max_distance * 2.0) {
+      pass = false;
+    } else {
+      if (dist > max_distance) {
+        if (tz < 0.0f) pass = false;
+        else if (tz > 0.0f && (((double)yaw >= 0 && (double)yaw < M_PI / 2.0) || ((double)yaw > 3.0 * M_PI / 2.0 && (double)yaw < 2 * M_PI)))
+          pass = false;
+      }
+      if (pass && dist <= max_distance && tz < 0.0f && ((double)yaw >= 2.0944 && (double)yaw < 4.18879)) pass = false;
+    }
+  }
+  state[4 * k + KF_PASS] = pass ? 1u : 0u;
+  state[4 * k + KF_CNT] = 0u;
+}
+
+__global__ void kf_first_kernel(const uint32_t *__restrict__ entry_pt, const uint32_t *__restrict__ entry_kf, uint64_t n_entries,
+                                const uint32_t *__restrict__ state, uint32_t *first) {
+  const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_entries) return;
+  if (state[4 * entry_kf[e] + KF_PASS]) atomicMin(&first[entry_pt[e]], (uint32_t)e);
+}
+
+__global__ void kf_visible_kernel(const FisherParams P, const fitslam_pose *__restrict__ pose, const float *__restrict__ xyz,
+                                  const uint32_t *__restrict__ entry_pt, const uint32_t *__restrict__ entry_kf, uint64_t n_entries,
+                                  const uint32_t *__restrict__ first, uint32_t *state, uint8_t *vis) {
+  __shared__ PoseFrame F;
+  if (threadIdx.x == 0) build_pose_frame(*pose, P, F);
+  __syncthreads();
+  const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n_entries) return;
+  const uint32_t pt = entry_pt[e], k = entry_kf[e];
+  bool v = false;
+  if (state[4 * k + KF_PASS] && first[pt] == (uint32_t)e) {
+    const float4 q = make_float4(xyz[3 * (size_t)pt], xyz[3 * (size_t)pt + 1], xyz[3 * (size_t)pt + 2], 0.f);
+    v = point_visible(q, F, P);
+  }
+  vis[e] = v ? 1 : 0;
+  if (v) atomicAdd(&state[4 * k + KF_CNT], 1u);
+}
+
+// one CTA: before[k] = landmarks collected when the loop reaches keyframe k; processed[k]; *checked = numKFsChecked
+__global__ void __launch_bounds__(1024) kf_cutoff_kernel(uint32_t *state, uint32_t n_kf, long long max_landmarks, uint32_t *checked) {
+  __shared__ uint32_t ws[32];
+  __shared__ uint32_t carry, s_checked, s_break;
+  if (threadIdx.x == 0) { carry = 0; s_checked = 0; s_break = 0; }
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < n_kf; base += 1024) {
+    const uint32_t k = base + threadIdx.x;
+    const bool pass = k < n_kf && state[4 * k + KF_PASS];
+    const uint32_t v = pass ? state[4 * k + KF_CNT] : 0u;
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t u = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= (uint32_t)d) incl += u;
+    }
+    if (lane == 31) ws[wid] = incl;
+    __syncthreads();
+    uint32_t wb = 0, tot = 0;
+    for (uint32_t w = 0; w < 32; ++w) {
+      const uint32_t x = ws[w];
+      if (w < wid) wb += x;
+      tot += x;
+    }
+    const uint32_t c0 = carry;
+    if (k < n_kf) {
+      const uint32_t before = c0 + wb + incl - v;
+      const bool proc = pass && (long long)before <= max_landmarks;
+      state[4 * k + KF_BEFORE] = before;
+      state[4 * k + KF_PROC] = proc ? 1u : 0u;
+      if (proc) atomicAdd(&s_checked, 1u);
+      // numKFsChecked++ comes before the cutoff test (:269-271): the keyframe that breaks the loop is counted too.  It is the
+      // first passing keyframe that is not processed (before[] is monotone: the passing keyframes after it are never reached)
+      if (pass && !proc) s_break = 1u;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry = c0 + tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *checked = s_checked + s_break;
+}
+
+// ordered compaction of the response; pass 0: tile counts, pass 1: writes (same transform as landmarks_in_view_kernel)
+template <int PASS>
+__global__ void __launch_bounds__(LIV_THREADS) kf_compact_kernel(const FisherParams P, const fitslam_pose *__restrict__ pose,
+                                                                  const float *__restrict__ xyz, const uint32_t *__restrict__ entry_pt,
+                                                                  const uint32_t *__restrict__ entry_kf, uint64_t n_entries,
+                                                                  const uint32_t *__restrict__ state, const uint8_t *__restrict__ vis,
+                                                                  uint32_t *tile_count, const uint32_t *__restrict__ tile_offset,
+                                                                  float *__restrict__ out, uint32_t capacity) {
+  __shared__ PoseFrame F;
+  __shared__ uint32_t warp_sums[LIV_THREADS / 32];
+  if (PASS == 1) {
+    if (threadIdx.x == 0) build_pose_frame(*pose, P, F);
+    __syncthreads();
+  }
+  const uint64_t e0 = ((uint64_t)blockIdx.x * LIV_THREADS + threadIdx.x) * LIV_PER_THREAD;
+  uint32_t m = 0;
+  for (int k = 0; k < LIV_PER_THREAD; ++k) {
+    const uint64_t e = e0 + k;
+    if (e < n_entries && vis[e] && state[4 * entry_kf[e] + KF_PROC]) m |= 1u << k;
+  }
+  uint32_t total;
+  const uint32_t excl = liv_block_scan((uint32_t)__popc(m), warp_sums, &total);
+  if (PASS == 0) {
+    if (threadIdx.x == 0) tile_count[blockIdx.x] = total;
+    return;
+  }
+  uint32_t dst = tile_offset[blockIdx.x] + excl;
+  for (int k = 0; k < LIV_PER_THREAD; ++k) {
+    if (!((m >> k) & 1u)) continue;
+    if (dst < capacity) {
+      const uint32_t pt = entry_pt[e0 + k];
+      const float qx = xyz[3 * (size_t)pt], qy = xyz[3 * (size_t)pt + 1], qz = xyz[3 * (size_t)pt + 2];
+      // vector3fORBToROS of the ORB-frame point, then affinePosToMap * position (rgbd-slam-node.cpp:419-425)
+      M3f orb2ros;
+      const float b[9] = {0, 0, 1, -1, 0, 0, 0, -1, 0};
+      for (int i = 0; i < 9; ++i) orb2ros.m[i / 3][i % 3] = b[i];
+      V3f Pw; Pw.v[0] = -qy; Pw.v[1] = -qz; Pw.v[2] = qx;
+      const V3f pos = mulv(orb2ros, Pw);
+      const V3f lp = mulv(F.Rinv, pos);
+      out[3 * (size_t)dst] = lp.v[0] + F.tinv.v[0];
+      out[3 * (size_t)dst + 1] = lp.v[1] + F.tinv.v[1];
+      out[3 * (size_t)dst + 2] = lp.v[2] + F.tinv.v[2];
+    }
+    ++dst;
+  }
+}
+
+// getVoxelCoordinate + table entry for a landmark given in the pose frame (the client side of the service response)
+__device__ __forceinline__ int voxel_of_local_point(float cx, float cy, float cz, const FisherParams &P) {
+  const float c3[3] = {cx, cy, cz};
+  int idx[3];
+  bool ok = true;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    const double rd = round((double)c3[a] * P.inv_step);  // FisherInfoManager.hpp:108-123
+    const int r = (rd >= -2147483000.0 && rd <= 2147483000.0) ? (int)rd : INT_MIN;  // also rejects NaN
+    ok = ok && r >= P.org[a] && r < P.org[a] + P.dims[a];
+    idx[a] = r - P.org[a];
+  }
+  if (!ok) return -1;
+  const int lin = (idx[0] * P.dims[1] + idx[1]) * P.dims[2] + idx[2];
+  const float val = __ldg(P.lut + lin);
+  return (val == val) ? lin : -1;
+}
+
+__global__ void kf_fisher_count_kernel(const FisherParams P, const float *__restrict__ lm, uint32_t n, uint32_t *vox_cnt, int32_t *lm_vox) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int lin = voxel_of_local_point(lm[3 * (size_t)i], lm[3 * (size_t)i + 1], lm[3 * (size_t)i + 2], P);
+  int rank = -1;
+  if (lin >= 0) rank = (int)atomicAdd(&vox_cnt[lin], 1u);
+  lm_vox[2 * (size_t)i] = lin;
+  lm_vox[2 * (size_t)i + 1] = rank;
+}
+
+// the first landmark of a voxel adds the whole voxel: information(v) * sum_{k <= n} exp(1 - k^s); per-block sums in a fixed order
+__global__ void __launch_bounds__(256) kf_fisher_sum_kernel(const FisherParams P, uint32_t n, const uint32_t *__restrict__ vox_cnt,
+                                                            const int32_t *__restrict__ lm_vox, double *part, uint32_t *used) {
+  __shared__ double sd[256];
+  __shared__ uint32_t su[256];
+  const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+  double t = 0.0;
+  uint32_t u = 0;
+  if (i < n) {
+    const int lin = lm_vox[2 * (size_t)i], rank = lm_vox[2 * (size_t)i + 1];
+    if (lin >= 0) {
+      u = 1;
+      if (rank == 0) t = (double)__ldg(P.lut + lin) * __ldg(P.crowd + min(vox_cnt[lin], (uint32_t)CROWD_MAX));
+    }
+  }
+  sd[threadIdx.x] = t;
+  su[threadIdx.x] = u;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) { sd[threadIdx.x] += sd[threadIdx.x + o]; su[threadIdx.x] += su[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { part[blockIdx.x] = sd[0]; atomicAdd(used, su[0]); }
+}
+
+__global__ void kf_fisher_final_kernel(const double *__restrict__ part, uint32_t n_blocks, double threshold, float *info, uint8_t *safe) {
+  double t = 0.0;
+  for (uint32_t b = 0; b < n_blocks; ++b) t += part[b];
+  const float information = (float)t;
+  *info = information;
+  *safe = (double)information > threshold ? 1 : 0;  // FisherInfoManager.cpp:112-114
+}
+
+// the query on the context stream; leaves the response in f->kf_out, *count / *checked on the host (one sync)
+static fitslam_status kf_query(fitslam_ctx *c, const fitslam_pose *pose, long long max_landmarks, float max_distance, int exhaustive,
+                               uint32_t *count, uint32_t *checked) {
+  FisherState *f = fstate(c);
+  *count = 0;
+  *checked = 0;
+  if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no map points set");
+  if (!f->have_kf) return fail(c, FITSLAM_E_NO_MAP_POINTS, "no keyframes set (fitslam_set_keyframes, after fitslam_set_map_points)");
+  if (f->n_kf == 0) return FITSLAM_OK;
+  FisherParams P;
+  memset(&P, 0, sizeof(P));
+  P.fx = c->prm.fx; P.fy = c->prm.fy; P.cx = c->prm.cx; P.cy = c->prm.cy;
+  P.max_u = c->prm.img_max_u; P.max_v = c->prm.img_max_v;
+  const uint64_t ne = f->n_entries;
+  const uint32_t n_tiles = (uint32_t)((ne + LIV_TILE - 1) / LIV_TILE);
+  const uint32_t out_cap = (uint32_t)std::min<uint64_t>(ne, f->n_points);  // every map point at most once
+  FS_CUDA(c, f->poses.reserve(1));
+  FS_CUDA(c, f->kf_first.reserve(f->n_points + 1));
+  FS_CUDA(c, f->kf_state.reserve(4 * (size_t)f->n_kf));
+  FS_CUDA(c, f->kf_vis.reserve(ne + 1));
+  FS_CUDA(c, f->kf_tiles.reserve((size_t)n_tiles + 4));
+  FS_CUDA(c, f->kf_out.reserve(3 * (size_t)out_cap + 3));
+  FS_CUDA(c, cudaMemcpyAsync(f->poses.p, pose, sizeof(fitslam_pose), cudaMemcpyDefault, c->stream));
+  FS_CUDA(c, cudaMemsetAsync(f->kf_first.p, 0xFF, (f->n_points + 1) * sizeof(uint32_t), c->stream));
+  uint32_t *tiles = f->kf_tiles.p, *total = tiles + n_tiles, *d_checked = tiles + n_tiles + 1;
+  kf_prefilter_kernel<<<(f->n_kf + 255) / 256, 256, 0, c->stream>>>(P, f->poses.p, f->kf.p, f->n_kf, max_distance, exhaustive, f->kf_state.p);
+  ++c->launches;
+  if (ne) {
+    const unsigned eg = (unsigned)((ne + 255) / 256);
+    kf_first_kernel<<<eg, 256, 0, c->stream>>>(f->kf_entry_pt.p, f->kf_entry_kf.p, ne, f->kf_state.p, f->kf_first.p);
+    kf_visible_kernel<<<eg, 256, 0, c->stream>>>(P, f->poses.p, f->raw.p, f->kf_entry_pt.p, f->kf_entry_kf.p, ne, f->kf_first.p,
+                                                 f->kf_state.p, f->kf_vis.p);
+    c->launches += 2;
+  }
+  kf_cutoff_kernel<<<1, 1024, 0, c->stream>>>(f->kf_state.p, f->n_kf, max_landmarks, d_checked);
+  ++c->launches;
+  if (ne) {
+    kf_compact_kernel<0><<<n_tiles, LIV_THREADS, 0, c->stream>>>(P, f->poses.p, f->raw.p, f->kf_entry_pt.p, f->kf_entry_kf.p, ne,
+                                                                 f->kf_state.p, f->kf_vis.p, tiles, nullptr, nullptr, 0);
+    liv_scan_kernel<<<1, 1024, 0, c->stream>>>(tiles, n_tiles, total);
+    kf_compact_kernel<1><<<n_tiles, LIV_THREADS, 0, c->stream>>>(P, f->poses.p, f->raw.p, f->kf_entry_pt.p, f->kf_entry_kf.p, ne,
+                                                                 f->kf_state.p, f->kf_vis.p, nullptr, tiles, f->kf_out.p, out_cap);
+    c->launches += 3;
+  } else {
+    FS_CUDA(c, cudaMemsetAsync(total, 0, sizeof(uint32_t), c->stream));
+  }
+  FS_CUDA(c, cudaGetLastError());
+  uint32_t h[2] = {0, 0};
+  FS_CUDA(c, cudaMemcpyAsync(h, total, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  *count = h[0];
+  *checked = h[1];
+  return FITSLAM_OK;
+}
+
+}  // namespace fitslam
+
+extern "C" fitslam_status fitslam_set_keyframes(fitslam_ctx *c, const fitslam_keyframe *kfs, uint32_t n_kf, const uint32_t *point_index,
+                                                uint64_t n_entries) {
+  if (!c || (!kfs && n_kf) || (!point_index && n_entries)) return fail(c, FITSLAM_E_INVALID, "set_keyframes: null argument");
+  if (n_entries >= (1ull << 32) - 1) return fail(c, FITSLAM_E_INVALID, "set_keyframes: more than 2^32 - 2 entries");
+  cudaSetDevice(c->device);
+  FisherState *f = fstate(c);
+  if (!f->have_points) return fail(c, FITSLAM_E_NO_MAP_POINTS, "set_keyframes: set the map points first (the lists index them)");
+  f->have_kf = false;
+  // the lists must tile [0, n_entries) in keyframe order (the service order is keyframe by keyframe), indices inside the points
+  std::vector<uint32_t> entry_kf((size_t)n_entries);
+  uint64_t at = 0;
+  for (uint32_t k = 0; k < n_kf; ++k) {
+    if (kfs[k].first != at || (uint64_t)kfs[k].first + kfs[k].count > n_entries)
+      return fail(c, FITSLAM_E_INVALID, "set_keyframes: keyframe " + std::to_string(k) + ": the lists must follow each other in point_index");
+    for (uint32_t i = 0; i < kfs[k].count; ++i) entry_kf[(size_t)at + i] = k;
+    at += kfs[k].count;
+  }
+  if (at != n_entries) return fail(c, FITSLAM_E_INVALID, "set_keyframes: the lists cover fewer entries than n_entries");
+  for (uint64_t e = 0; e < n_entries; ++e)
+    if (point_index[e] >= f->n_points) return fail(c, FITSLAM_E_INVALID, "set_keyframes: point index beyond the resident map points");
+  FS_CUDA(c, f->kf.reserve((size_t)n_kf + 1));
+  FS_CUDA(c, f->kf_entry_pt.reserve((size_t)n_entries + 1));
+  FS_CUDA(c, f->kf_entry_kf.reserve((size_t)n_entries + 1));
+  if (n_kf) FS_CUDA(c, cudaMemcpyAsync(f->kf.p, kfs, (size_t)n_kf * sizeof(fitslam_keyframe), cudaMemcpyHostToDevice, c->stream));
+  if (n_entries) {
+    FS_CUDA(c, cudaMemcpyAsync(f->kf_entry_pt.p, point_index, (size_t)n_entries * 4, cudaMemcpyHostToDevice, c->stream));
+    FS_CUDA(c, cudaMemcpyAsync(f->kf_entry_kf.p, entry_kf.data(), (size_t)n_entries * 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  f->n_kf = n_kf;
+  f->n_entries = n_entries;
+  f->have_kf = true;
+  return FITSLAM_OK;
+}
+
+extern "C" fitslam_status fitslam_landmarks_in_view_keyframes(fitslam_ctx *c, const fitslam_pose *pose, int32_t max_landmarks,
+                                                              float max_distance, float max_angle, int exhaustive_search,
+                                                              float *out_xyz, uint32_t capacity, uint32_t *count,
+                                                              uint32_t *n_keyframes_checked) {
+  (void)max_angle;  // accepted and unused, as in the reference
+  if (!c || !pose || !count || (!out_xyz && capacity)) return fail(c, FITSLAM_E_INVALID, "landmarks_in_view_keyframes: null argument");
+  cudaSetDevice(c->device);
+  uint32_t checked = 0;
+  const fitslam_status st = kf_query(c, pose, max_landmarks, max_distance, exhaustive_search, count, &checked);
+  if (st != FITSLAM_OK) return st;
+  if (n_keyframes_checked) *n_keyframes_checked = checked;
+  const uint32_t m = std::min(*count, capacity);
+  if (m) {
+    FS_CUDA(c, cudaMemcpyAsync(out_xyz, c->fi->kf_out.p, 3 * (size_t)m * sizeof(float), cudaMemcpyDefault, c->stream));
+    FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  if (*count > capacity) return fail(c, FITSLAM_E_CAPACITY, "landmarks_in_view_keyframes: more landmarks than capacity (count holds the number)");
+  return FITSLAM_OK;
+}
+
+extern "C" fitslam_status fitslam_score_fisher_keyframes(fitslam_ctx *c, const fitslam_pose *pose, int32_t max_landmarks, float max_distance,
+                                                         int exhaustive_search, float *information, uint8_t *safe, uint32_t *n_landmarks,
+                                                         uint32_t *n_used) {
+  if (!c || !pose || !information) return fail(c, FITSLAM_E_INVALID, "score_fisher_keyframes: null argument");
+  cudaSetDevice(c->device);
+  FisherParams P;
+  fitslam_status st = fisher_params(c, P);  // (lookup table and map points present)
+  if (st != FITSLAM_OK) return st;
+  FisherState *f = c->fi;
+  uint32_t count = 0, checked = 0;
+  st = kf_query(c, pose, max_landmarks, max_distance, exhaustive_search, &count, &checked);
+  if (st != FITSLAM_OK) return st;
+  if (n_landmarks) *n_landmarks = count;
+  const size_t lut_n = (size_t)lut_size(f);
+  const uint32_t nb = (count + 255) / 256;
+  FS_CUDA(c, f->kf_vox.reserve(lut_n + 1));
+  FS_CUDA(c, f->kf_lm.reserve(2 * (size_t)count + 2));
+  FS_CUDA(c, f->kf_part.reserve((size_t)nb + 1));
+  FS_CUDA(c, f->info.reserve(4));
+  FS_CUDA(c, f->safe.reserve(4));
+  FS_CUDA(c, f->nvis.reserve(4));
+  FS_CUDA(c, cudaMemsetAsync(f->kf_vox.p, 0, lut_n * sizeof(uint32_t), c->stream));
+  FS_CUDA(c, cudaMemsetAsync(f->nvis.p, 0, sizeof(uint32_t), c->stream));
+  if (count) {
+    kf_fisher_count_kernel<<<nb, 256, 0, c->stream>>>(P, f->kf_out.p, count, f->kf_vox.p, f->kf_lm.p);
+    kf_fisher_sum_kernel<<<nb, 256, 0, c->stream>>>(P, count, f->kf_vox.p, f->kf_lm.p, f->kf_part.p, f->nvis.p);
+    c->launches += 2;
+  }
+  kf_fisher_final_kernel<<<1, 1, 0, c->stream>>>(f->kf_part.p, nb, P.threshold, f->info.p, f->safe.p);
+  ++c->launches;
+  FS_CUDA(c, cudaGetLastError());
+  uint8_t h_safe = 0;
+  uint32_t h_used = 0;
+  FS_CUDA(c, cudaMemcpyAsync(information, f->info.p, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaMemcpyAsync(&h_safe, f->safe.p, 1, cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaMemcpyAsync(&h_used, f->nvis.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (safe) *safe = h_safe;
+  if (n_used) *n_used = h_used;
   return FITSLAM_OK;
 }
 

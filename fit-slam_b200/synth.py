@@ -220,3 +220,40 @@ def frontier_poses(frontiers, theta, z, orientation_fn=None):
     p["qz"] = np.sin(th * 0.5)
     p["qw"] = np.cos(th * 0.5)
     return p
+
+
+def make_keyframes(pts, n_kf, seed, max_range=8.0, fov=1.2, per_kf=None):
+    """A synthetic ORB-SLAM3 atlas over the map points `pts` (ROS map frame): n_kf keyframes along a random walk through the
+    cloud's bounding box, each listing the points in front of it within `max_range` and a horizontal field of view `fov`
+    (so neighbouring keyframes share many points, as covisible keyframes do).  Returns (KEYFRAME_DTYPE records with
+    GetPoseInverse() in the ORB world frame, concatenated point indices)."""
+    from .capi import KEYFRAME_DTYPE
+    rng = np.random.default_rng(seed)
+    lo, hi = pts[:, :2].min(axis=0), pts[:, :2].max(axis=0)
+    pos = rng.uniform(lo, hi)
+    yaw = rng.uniform(-np.pi, np.pi)
+    perm = np.array([[0, -1, 0], [0, 0, -1], [1, 0, 0]], dtype=np.float64)  # ROS map axes -> ORB world axes
+    kfs = np.zeros(n_kf, dtype=KEYFRAME_DTYPE)
+    lists = []
+    at = 0
+    for k in range(n_kf):
+        yaw += rng.normal(0, 0.5)
+        pos = np.clip(pos + 0.8 * np.array([np.cos(yaw), np.sin(yaw)]) + rng.normal(0, 0.1, 2), lo, hi)
+        z = 0.3
+        c, s_ = np.cos(yaw), np.sin(yaw)
+        R_ros = np.array([[c, -s_, 0], [s_, c, 0], [0, 0, 1]])
+        kfs[k]["Rwc"] = (perm @ R_ros @ perm.T).astype(np.float32).ravel()
+        kfs[k]["twc"] = (perm @ np.array([pos[0], pos[1], z])).astype(np.float32)
+        d = pts[:, :2] - pos
+        r = np.hypot(d[:, 0], d[:, 1])
+        ang = np.abs((np.arctan2(d[:, 1], d[:, 0]) - yaw + np.pi) % (2 * np.pi) - np.pi)
+        idx = np.nonzero((r < max_range) & (ang < fov / 2))[0]
+        if per_kf is not None and len(idx) > per_kf:
+            idx = rng.choice(idx, per_kf, replace=False)
+        idx = rng.permutation(idx).astype(np.uint32)
+        if len(idx) > 4:  # a map point listed twice by one keyframe must be taken once as well
+            idx = np.concatenate([idx, idx[:2]])
+        kfs[k]["first"], kfs[k]["count"] = at, len(idx)
+        at += len(idx)
+        lists.append(idx)
+    return kfs, (np.concatenate(lists) if lists else np.zeros(0, np.uint32)).astype(np.uint32)

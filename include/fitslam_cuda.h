@@ -314,11 +314,47 @@ FITSLAM_API fitslam_status fitslam_score_fisher(fitslam_ctx *ctx, const fitslam_
  * non-exhaustive mode (:228-272) is not built.
  * NOT the service's response on a multi-keyframe atlas: the service stops adding keyframes once more than maxLandmarks = 1000
  * landmarks are collected (:270-271, also in exhaustive mode; rgbd-slam-node.cpp:413).  That cutoff needs the atlas's
- * keyframe-to-point lists, which this interface does not receive: the resident cloud is treated as ONE keyframe, for which the
- * reference's loop returns every visible point too.  The same holds for fitslam_score_fisher and the cycle's Fisher stage:
- * their totals are upper bounds of what isPoseSafe would sum behind the real service. */
+ * keyframe-to-point lists: this call treats the resident cloud as ONE keyframe, for which the reference's loop returns every
+ * visible point too.  The same holds for fitslam_score_fisher and the cycle's Fisher stage: their totals are upper bounds of
+ * what isPoseSafe would sum behind the real service.  fitslam_landmarks_in_view_keyframes / fitslam_score_fisher_keyframes
+ * below take the keyframe lists and reproduce the cutoff. */
 FITSLAM_API fitslam_status fitslam_landmarks_in_view(fitslam_ctx *ctx, const fitslam_pose *pose, float *out_xyz,
                                                      uint32_t capacity, uint32_t *count);
+
+/* The keyframe-structured query: ORBSLAM3Interface::mapPointsVisibleFromPose as the service really runs it
+ * (ORBW/src/orb_slam3_interface.cpp:188-317), over an atlas given as keyframes with their map-point lists.
+ *   fitslam_set_keyframes   the atlas: n_kf keyframes in the order the service iterates them (the reference walks a
+ *                           std::vector made from a std::set<KeyFrame*>, i.e. pointer order, which no caller can know: the order
+ *                           given here IS the iteration order), each with GetPoseInverse() (Twc, ORB world frame) and the range
+ *                           [first, first + count) of `point_index` that lists its map points (indices into the points of
+ *                           fitslam_set_map_points; a point may appear in several keyframes and is taken once, :263-265).
+ *   max_landmarks           the service passes 1000 (ORBW/src/rgbd/rgbd-slam-node.cpp:413).  A keyframe is skipped with everything
+ *                           after it once MORE than max_landmarks landmarks are collected (:270-271; the check sits outside the
+ *                           exhaustive_search test, so it applies in both modes).
+ *   exhaustive_search = 0   the per-keyframe prefilter of :240-267 (distance to the keyframe against max_distance, behind /
+ *                           in front, relative yaw) runs first.  max_angle is accepted and unused, as in the reference.
+ * out_xyz / count as fitslam_landmarks_in_view (pose frame, service order: keyframe by keyframe, list order inside a keyframe);
+ * n_keyframes_checked = numKFsChecked.  The prefilter multiplies 3x3 float matrices where Sophus multiplies unit quaternions:
+ * a keyframe within a few ulp of one of its thresholds may fall on the other side. */
+typedef struct fitslam_keyframe {
+  float Rwc[9];   /* KeyFrame::GetPoseInverse() rotation, row-major */
+  float twc[3];   /* ... translation */
+  uint32_t first; /* its map points: point_index[first .. first + count) */
+  uint32_t count;
+} fitslam_keyframe;
+FITSLAM_API fitslam_status fitslam_set_keyframes(fitslam_ctx *ctx, const fitslam_keyframe *keyframes, uint32_t n_keyframes,
+                                                 const uint32_t *point_index, uint64_t n_entries);
+FITSLAM_API fitslam_status fitslam_landmarks_in_view_keyframes(fitslam_ctx *ctx, const fitslam_pose *pose, int32_t max_landmarks,
+                                                               float max_distance, float max_angle, int exhaustive_search,
+                                                               float *out_xyz, uint32_t capacity, uint32_t *count,
+                                                               uint32_t *n_keyframes_checked);
+/* FisherInformationManager::isPoseSafe (DEP/src/fisher_information/FisherInfoManager.cpp:39-115) behind that service: the
+ * landmarks of fitslam_landmarks_in_view_keyframes (max_landmarks = 1000 and the request's max_dist_pose_observation /
+ * exhaustive_search in the reference) summed through the lookup table with the per-voxel crowding factor.
+ * n_landmarks = landmarks the service returned, n_used = those that hit a lookup-table entry. */
+FITSLAM_API fitslam_status fitslam_score_fisher_keyframes(fitslam_ctx *ctx, const fitslam_pose *pose, int32_t max_landmarks,
+                                                          float max_distance, int exhaustive_search, float *information,
+                                                          uint8_t *safe, uint32_t *n_landmarks, uint32_t *n_used);
 
 /* The same query without any allocation.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -231,6 +231,34 @@ class Oracle:
                                        C.byref(cnt))
         return out[:cnt.value]
 
+    def landmarks_in_view_keyframes(self, xyz, keyframes, point_index, pose, max_landmarks=1000, max_distance=5.0,
+                                    exhaustive=False, cap=1 << 20):
+        """mapPointsVisibleFromPose over a keyframe atlas (ORBW/src/orb_slam3_interface.cpp:188-317): (xyz in the pose frame,
+        keyframes checked)."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        keyframes, point_index, pose = np.ascontiguousarray(keyframes), np.ascontiguousarray(point_index, dtype=np.uint32), np.ascontiguousarray(pose)
+        out = np.zeros((cap, 3), dtype=np.float32)
+        cnt, chk = C.c_uint32(), C.c_uint32()
+        self.lib.orc_landmarks_in_view_keyframes(self.fisher, C.c_void_p(xyz.ctypes.data), C.c_uint64(len(xyz)),
+                                                 C.c_void_p(keyframes.ctypes.data), C.c_uint32(len(keyframes)),
+                                                 C.c_void_p(point_index.ctypes.data), C.c_void_p(pose.ctypes.data),
+                                                 C.c_int32(max_landmarks), C.c_float(max_distance), C.c_int(int(exhaustive)),
+                                                 C.c_void_p(out.ctypes.data), C.c_uint32(cap), C.byref(cnt), C.byref(chk))
+        return out[:cnt.value], chk.value
+
+    def fisher_pose_keyframes(self, xyz, keyframes, point_index, pose, max_landmarks=1000, max_distance=5.0, exhaustive=False):
+        """isPoseSafe behind that service: (status, information, information accumulated in double, safe, landmarks, used)."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        keyframes, point_index, pose = np.ascontiguousarray(keyframes), np.ascontiguousarray(point_index, dtype=np.uint32), np.ascontiguousarray(pose)
+        info, info64, safe = C.c_float(), C.c_double(), C.c_uint8()
+        n, used = C.c_uint32(), C.c_uint32()
+        st = self.lib.orc_fisher_pose_keyframes(self.fisher, C.c_void_p(xyz.ctypes.data), C.c_uint64(len(xyz)),
+                                                C.c_void_p(keyframes.ctypes.data), C.c_uint32(len(keyframes)),
+                                                C.c_void_p(point_index.ctypes.data), C.c_void_p(pose.ctypes.data),
+                                                C.c_int32(max_landmarks), C.c_float(max_distance), C.c_int(int(exhaustive)),
+                                                C.byref(info), C.byref(info64), C.byref(safe), C.byref(n), C.byref(used))
+        return st, info.value, info64.value, safe.value, n.value, used.value
+
     def se3_roundtrip(self, R, t):
         R = np.ascontiguousarray(R, dtype=np.float32)
         t = np.ascontiguousarray(t, dtype=np.float32)

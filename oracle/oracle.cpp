@@ -1013,6 +1013,123 @@ class FisherInformationManager {
     }
   }
 
+  // Eigen 3.4 MatrixBase::eulerAngles(2, 0, 1) (Eigen/src/Geometry/EulerAngles.h: a0 = 2, a1 = 0 => odd = 0, i = 2, j = 0, k = 1)
+  // followed by WrapperTypeConversions::rotationORBToEulerROS (ORBW/src/type_conversion.cpp:143-153); only component 2 is used
+  static float yawOfRotationORBToEulerROS(const M3 &R) {
+    const int i = 2, j = 0, k = 1;
+    float res0 = atan2f(R.m[j][k], R.m[k][k]);
+    const float c2 = sqrtf(R.m[i][i] * R.m[i][i] + R.m[i][j] * R.m[i][j]);
+    float res1;
+    if (res0 > 0.0f) {  // (!odd) && res[0] > 0
+      if (res0 > 0.0f) res0 -= (float)M_PI;
+      else res0 += (float)M_PI;
+      res1 = atan2f(-R.m[i][k], -c2);
+    } else {
+      res1 = atan2f(-R.m[i][k], c2);
+    }
+    (void)res1;
+    const float s1 = sinf(res0), c1 = cosf(res0);
+    float res2 = atan2f(s1 * R.m[k][i] - c1 * R.m[j][i], c1 * R.m[j][j] - s1 * R.m[k][j]);
+    res2 = -res2;          // if (!odd) res = -res
+    float e2 = -res2;      // type_conversion.cpp:147
+    // :151 (the float is promoted to double for the sum and narrowed back into the Vector3f)
+    e2 = e2 < 0 ? (float)((2 * M_PI) + (double)e2) : e2;
+    return e2;
+  }
+
+  // ORBSLAM3Interface::mapPointsVisibleFromPose over a keyframe-structured atlas (ORBW/src/orb_slam3_interface.cpp:188-317):
+  // keyframes in the caller's order, each with GetPoseInverse() and its map-point list; per-keyframe prefilter unless
+  // exhaustive_search (:240-267); the maxLandmarks cutoff (:270-271); each map point once (:263-265); then the node's transform
+  // into the query-pose frame (ORBW/src/rgbd/rgbd-slam-node.cpp:406-429).  rel_T_CamToKF = Tcw * Twc is formed with 3x3
+  // products here (Sophus multiplies unit quaternions: the same transform up to float rounding).
+  void landmarksInViewKeyframes(const fitslam_pose &cameraPose, const float *xyz, uint64_t P, const fitslam_keyframe *kfs,
+                                uint32_t n_kf, const uint32_t *point_index, int maxLandmarks, float maxDistance,
+                                bool exhaustive_search, std::vector<V3> &map_points, uint32_t &numKFsChecked_out) {
+    Affine Tcw = se3ROSToORB(poseToAffine(cameraPose));
+    const M3 &mRcw = Tcw.R;
+    const V3 &mtcw = Tcw.t;
+    const float fx = prm.fx, fy = prm.fy, cx = prm.cx, cy = prm.cy;
+    float mnMinX = 0.0f, mnMaxX = prm.img_max_u, mnMinY = 0.0f, mnMaxY = prm.img_max_v;
+    Affine affinePosToMap = inverseAffine(poseToAffine(cameraPose));
+    int numVisibleMapPoints = 0;
+    int numKFsChecked = 0;
+    std::vector<uint8_t> processedMapPoints(P, 0);
+    map_points.clear();
+    for (uint32_t kf = 0; kf < n_kf; ++kf) {
+      M3 Rwc;
+      V3 twc;
+      for (int a = 0; a < 3; ++a) {
+        for (int b = 0; b < 3; ++b) Rwc.m[a][b] = kfs[kf].Rwc[3 * a + b];
+        twc.v[a] = kfs[kf].twc[a];
+      }
+      const M3 relR = mul(mRcw, Rwc);
+      const V3 rt = mul(mRcw, twc);
+      const V3 relt = {{rt.v[0] + mtcw.v[0], rt.v[1] + mtcw.v[1], rt.v[2] + mtcw.v[2]}};
+      const float yaw = yawOfRotationORBToEulerROS(relR);
+      // Eigen stableNorm-free norm(): sqrt of the redux x0*x0 + (x1*x1 + x2*x2)
+      const float distBwKfs = sqrtf(dot3(relt.v[0], relt.v[0], relt.v[1], relt.v[1], relt.v[2], relt.v[2]));
+      if (!exhaustive_search) {
+        if (distBwKfs >= maxDistance * 2.0) continue;
+        if (distBwKfs > maxDistance) {
+          if (relt.v[2] < 0.0) continue;
+          else if (relt.v[2] > 0.0) {
+            if ((yaw >= 0 && yaw < M_PI / 2.0) || (yaw > 3.0 * M_PI / 2.0 && yaw < 2 * M_PI)) continue;
+          }
+        }
+        if (distBwKfs <= maxDistance) {
+          if (relt.v[2] < 0.0) {
+            if ((yaw >= 2.0944 && yaw < 4.18879)) continue;
+          }
+        }
+      }
+      numKFsChecked++;
+      if (numVisibleMapPoints > maxLandmarks) break;
+      for (uint32_t e = kfs[kf].first; e < kfs[kf].first + kfs[kf].count; ++e) {
+        const uint32_t pi = point_index[e];
+        if (processedMapPoints[pi]) continue;
+        processedMapPoints[pi] = 1;
+        const float rx = xyz[3 * (uint64_t)pi], ry = xyz[3 * (uint64_t)pi + 1], rz = xyz[3 * (uint64_t)pi + 2];
+        V3 Pw = {{-ry, -rz, rx}};
+        V3 RP = mul(mRcw, Pw);
+        V3 Pc = {{RP.v[0] + mtcw.v[0], RP.v[1] + mtcw.v[1], RP.v[2] + mtcw.v[2]}};
+        if (Pc.v[2] < 0.0f) continue;
+        float u = fx * Pc.v[0] / Pc.v[2] + cx;
+        float v = fy * Pc.v[1] / Pc.v[2] + cy;
+        if (u < mnMinX || u > mnMaxX) continue;
+        if (v < mnMinY || v > mnMaxY) continue;
+        V3 position = mul(tfORBToROS, Pw);
+        map_points.push_back(apply(affinePosToMap, position));
+        numVisibleMapPoints++;
+      }
+    }
+    numKFsChecked_out = (uint32_t)numKFsChecked;
+  }
+
+  // isPoseSafe (cpp:39-115) over the response of the keyframe-structured service
+  bool isPoseSafeKeyframes(const fitslam_pose &given_pose, const float *xyz, uint64_t P, const fitslam_keyframe *kfs, uint32_t n_kf,
+                           const uint32_t *point_index, int maxLandmarks, float maxDistance, bool exhaustive_search,
+                           float &information, uint32_t &n_landmarks) {
+    ++latest_version_;
+    std::vector<V3> map_points;
+    uint32_t checked = 0;
+    landmarksInViewKeyframes(given_pose, xyz, P, kfs, n_kf, point_index, maxLandmarks, maxDistance, exhaustive_search, map_points,
+                             checked);
+    n_landmarks = (uint32_t)map_points.size();
+    float total_information = 0.0;
+    occupied_voxel_count_ = 0;
+    n_used_ = 0;
+    total_information_f64_ = 0.0;
+    for (const auto &mp : map_points) {
+      float info = getInformationFromLookup(mp.v[0], mp.v[1], mp.v[2], latest_version_);
+      if (std::isnan(info)) continue;
+      ++n_used_;
+      total_information_f64_ += (double)info;
+      total_information += info;
+    }
+    information = total_information;
+    return total_information > prm.fisher_information_threshold;
+  }
+
   // cpp:39-115
   double total_information_f64_ = 0.0;  // stage dump: the same per-landmark float terms accumulated in double
   uint32_t n_used_ = 0;  // stage dump: landmarks of the last query that hit a lookup-table entry
@@ -1584,6 +1701,37 @@ int orc_landmarks_in_view(void *h, const float *xyz, uint64_t P, const fitslam_p
     out_xyz[3 * i + 2] = pts[i].v[2];
   }
   return pts.size() > cap ? FITSLAM_E_CAPACITY : FITSLAM_OK;
+}
+
+// the keyframe-structured service response (pose frame) and isPoseSafe behind it
+int orc_landmarks_in_view_keyframes(void *h, const float *xyz, uint64_t P, const fitslam_keyframe *kfs, uint32_t n_kf,
+                                    const uint32_t *point_index, const fitslam_pose *pose, int32_t max_landmarks, float max_distance,
+                                    int exhaustive, float *out_xyz, uint32_t cap, uint32_t *count, uint32_t *n_checked) {
+  auto *m = static_cast<FisherInformationManager *>(h);
+  std::vector<V3> pts;
+  m->landmarksInViewKeyframes(*pose, xyz, P, kfs, n_kf, point_index, max_landmarks, max_distance, exhaustive != 0, pts, *n_checked);
+  *count = (uint32_t)pts.size();
+  for (size_t i = 0; i < pts.size() && i < cap; ++i) {
+    out_xyz[3 * i] = pts[i].v[0];
+    out_xyz[3 * i + 1] = pts[i].v[1];
+    out_xyz[3 * i + 2] = pts[i].v[2];
+  }
+  return pts.size() > cap ? FITSLAM_E_CAPACITY : FITSLAM_OK;
+}
+int orc_fisher_pose_keyframes(void *h, const float *xyz, uint64_t P, const fitslam_keyframe *kfs, uint32_t n_kf,
+                              const uint32_t *point_index, const fitslam_pose *pose, int32_t max_landmarks, float max_distance,
+                              int exhaustive, float *information, double *information_f64, uint8_t *safe, uint32_t *n_landmarks,
+                              uint32_t *n_used) {
+  auto *m = static_cast<FisherInformationManager *>(h);
+  if (m->lookup_table_fi_.empty()) return FITSLAM_E_NO_LOOKUP_TABLE;
+  float info = 0;
+  const bool ok = m->isPoseSafeKeyframes(*pose, xyz, P, kfs, n_kf, point_index, max_landmarks, max_distance, exhaustive != 0, info,
+                                         *n_landmarks);
+  *information = info;
+  *information_f64 = m->total_information_f64_;
+  *safe = ok ? 1 : 0;
+  *n_used = m->n_used_;
+  return FITSLAM_OK;
 }
 
 // ORBW/tests/typeConversionsTests.cpp:8-33 : se3ORBToROS(se3ROSToORB(A)) for an affine given as R (row-major 9) + t

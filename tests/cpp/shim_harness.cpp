@@ -168,6 +168,27 @@ int main(int argc, char **argv) {
     double sx = 0, sy = 0, sz = 0;
     for (const auto &p : lm) { sx += p.x; sy += p.y; sz += p.z; }
     std::printf("landmarks %zu %a %a %a\n", lm.size(), sx, sy, sz);
+    // the same service over a keyframe atlas: two keyframes at the identity pose, even points then odd points then the first
+    // 10 again; a cutoff of 20 landmarks stops after the first keyframe (orb_slam3_interface.cpp:270-271)
+    std::vector<fitslam_keyframe> kfs(3);
+    std::vector<uint32_t> index;
+    for (int k = 0; k < 3; ++k) {
+      for (int i = 0; i < 9; ++i) kfs[k].Rwc[i] = (i % 4 == 0) ? 1.0f : 0.0f;
+      kfs[k].twc[0] = kfs[k].twc[1] = kfs[k].twc[2] = 0.0f;
+      kfs[k].first = (uint32_t)index.size();
+      if (k < 2) { for (uint32_t i = (uint32_t)k; i < P; i += 2) index.push_back(i); }
+      else { for (uint32_t i = 0; i < 10 && i < P; ++i) index.push_back(i); }
+      kfs[k].count = (uint32_t)index.size() - kfs[k].first;
+    }
+    fisher.setKeyframes(kfs, index);
+    const auto all = fisher.getLandmarksInView(pose, 5.0f, 0.0f, true, 1 << 30);
+    const auto cut = fisher.getLandmarksInView(pose, 5.0f, 0.0f, true, 20);
+    double ax = 0, cx = 0;
+    for (const auto &p : all) ax += p.x;
+    for (const auto &p : cut) cx += p.x;
+    float info_kf = 0;
+    const bool safe_kf = fisher.isPoseSafe(pose, true, 5.0f, info_kf, 20);
+    std::printf("landmarks_kf %zu %a %zu %a %a %d\n", all.size(), ax, cut.size(), cx, (double)info_kf, safe_kf ? 1 : 0);
   }
   // sensor simulator: a fan around the robot on an occupancy grid derived from the costmap (254 -> 100, 255 -> -1, else 0)
   {

@@ -108,6 +108,23 @@ def test_shim_matches_oracle(harness, capi, oracle, synth, tmp_path):
         for k in range(3):
             sums[k] += row[k]
     assert [float.fromhex(v) for v in lm[2:5]] == sums
+    # ... and over a keyframe atlas (setKeyframes + the four-argument getLandmarksInView / isPoseSafe): every point once, and
+    # the maxLandmarks cutoff
+    P = len(pts)
+    lists = [np.arange(0, P, 2), np.arange(1, P, 2), np.arange(min(10, P))]
+    kfs = np.zeros(3, dtype=capi.KEYFRAME_DTYPE)
+    kfs["Rwc"] = np.eye(3, dtype=np.float32).ravel()
+    kfs["count"] = [len(l) for l in lists]
+    kfs["first"] = np.concatenate([[0], np.cumsum(kfs["count"])[:-1]])
+    idx = np.concatenate(lists).astype(np.uint32)
+    w_all, _ = oracle.landmarks_in_view_keyframes(pts, kfs, idx, poses[:1], 1 << 30, 5.0, True)
+    w_cut, _ = oracle.landmarks_in_view_keyframes(pts, kfs, idx, poses[:1], 20, 5.0, True)
+    sto, winfo, winfo64, wsafe, wn, wused = oracle.fisher_pose_keyframes(pts, kfs, idx, poses[:1], 20, 5.0, True)
+    lk = [ln.split() for ln in lines if ln.startswith("landmarks_kf")][0]
+    fsum = lambda rows: float(sum(float(v) for v in rows[:, 0].astype(np.float64).tolist())) if len(rows) else 0.0
+    assert int(lk[1]) == len(w_all) == len(want) and float.fromhex(lk[2]) == fsum(w_all)
+    assert int(lk[3]) == len(w_cut) <= len(w_all) and float.fromhex(lk[4]) == fsum(w_cut)
+    assert abs(float.fromhex(lk[5]) - winfo) <= 1e-4 * abs(winfo) + 1e-6 and (abs(winfo - 550.0) < 1.0 or int(lk[6]) == wsafe)
 
     # ---- cost assignment and goal selection (CostAssigner::getFrontierCosts, FullPathOptimizer::getNextGoal), BT order
     f32 = lambda v: float(np.float32(v))
