@@ -474,6 +474,66 @@ def run_reference(args):
     print(json.dumps(out))
 
 
+def run_c5(args):
+    """BASELINE.json configs[4] (rapid mode): `--steps` successive incremental costmap updates on the C2 map (a random walk of
+    0.2 m steps revealing a 2 m disc each: SURVEY 8d), every one followed by a full re-extraction and rescoring cycle.  An update
+    uploads only the dirty rectangle from pinned host memory.  Timed per update + cycle on the host clock (the call returns
+    after its own sync), L2 not flushed (a rapid-mode loop would not either); the reference ticks at 5 Hz
+    (fit_slam2/xml/rapid_exploration.xml:4)."""
+    import torch
+    pkg, capi, synth = load()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
+    wl = Workload("C2", capi, synth)
+    a, meta = wl.a, wl.meta
+    H, W = a.shape
+    ctx = capi.Context(wl.params(capi.default_params()))
+    a_pin = torch.from_numpy(a.copy()).pin_memory().numpy()
+    ctx.set_costmap(a_pin, meta["res"], meta["ox"], meta["oy"])
+    ctx.fisher_generate_lookup()
+    ctx.set_map_points(wl.pts)
+    rng = np.random.default_rng(55)
+    cx = int((meta["robot_x"] - meta["ox"]) / meta["res"])
+    cy = int((meta["robot_y"] - meta["oy"]) / meta["res"])
+    n_win = ctx.ray_shape()[2]
+    ms, cand, dirty, fr = [], [], [], []
+    l0 = None
+    with ClockSampler(0) as clk:
+        for step in range(args.warmup + args.steps):
+            cx = int(np.clip(cx + rng.integers(-4, 5), 100, W - 100))
+            cy = int(np.clip(cy + rng.integers(-4, 5), 100, H - 100))
+            rect = synth.reveal_step(a_pin, meta, cx, cy, rng)  # (host work of the producer, outside the timed region)
+            rx, ry = meta["ox"] + (cx + 0.5) * meta["res"], meta["oy"] + (cy + 0.5) * meta["res"]
+            if step == args.warmup:
+                l0 = ctx.launch_count
+            t0 = time.perf_counter()
+            ctx.set_costmap(a_pin, meta["res"], meta["ox"], meta["oy"], dirty=rect)
+            st, res = ctx.cycle(rx, ry, wl.ryaw, meta["poly"], wl.fisher_mode)
+            t1 = time.perf_counter()
+            assert st == 0, st
+            if step >= args.warmup:
+                ms.append((t1 - t0) * 1e3)
+                cand.append(res.n_frontiers * n_win)
+                dirty.append(rect[2] * rect[3])
+                fr.append(res.n_frontiers)
+    ms = np.array(ms)
+    out = {"metric": METRIC, "value": float(np.sum(cand) / (ms.sum() * 1e-3)), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": float(ms.mean()), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "u8/int32 (extraction, arrival), f32 (Fisher), f64 (geometry, costs)", "data": "synthetic",
+           "config": {"workload": f"C5: {args.steps} successive incremental costmap updates on the C2 map ({W}x{H} @ {meta['res']} m, {len(wl.pts)} map "
+                                  f"points), re-extraction + rescoring of all (frontier, yaw) candidates per update; dirty rectangle uploaded from pinned host memory",
+                      "l2": "not flushed (successive cycles of one loop)"},
+           "c5": {"updates": int(args.steps), "ms_median": float(np.median(ms)), "ms_p99": float(np.percentile(ms, 99)), "ms_max": float(ms.max()),
+                  "ms_min": float(ms.min()), "dirty_bytes_mean": float(np.mean(dirty)), "frontiers_mean": float(np.mean(fr)),
+                  "candidates_mean": float(np.mean(cand)), "tick_budget_ms": 200.0,
+                  "note": "per update: dirty-rectangle H2D + whole cycle through the C ABI, host clock around both calls"},
+           "e2e": {"value": float(np.sum(cand) / (ms.sum() * 1e-3)), "unit": UNIT, "ms_per_step": float(ms.mean()),
+                   "h2d_bytes_per_step": int(np.mean(dirty)), "d2h_bytes_per_step": 0},
+           "gpu_launches": int(ctx.launch_count - l0), "clocks": clk.summary()}
+    ctx.close()
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -486,6 +546,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == "C5":
+        run_c5(args)
     else:
         run_gpu(args)
 

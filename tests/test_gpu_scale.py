@@ -147,3 +147,53 @@ def test_c5_rapid_mode_dirty_rectangles(capi, oracle, synth):
                     np.testing.assert_array_equal(got["arrival"][key], arr[key], err_msg=key)
     finally:
         ctx.close()
+
+
+def test_c5_thousand_updates_on_c2(capi, oracle, synth):
+    """configs[4] at its real size: 1 000 successive dirty-rectangle updates on the 4096^2 map, a full cycle after each; the
+    oracle checks the extraction and the arrival information every 50th step, a fresh context the whole cycle every 250th."""
+    a, meta, pts, ov = synth.make_config("C2")
+    a = a.copy()
+    params = synth.apply_overrides(capi.default_params(), ov)
+    synth.apply_overrides(oracle.params, ov)
+    rng = np.random.default_rng(55)
+    H, W = a.shape
+    ctx = capi.Context(params)
+    try:
+        ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        ctx.fisher_generate_lookup()
+        ctx.set_map_points(pts)
+        cx = int((meta["robot_x"] - meta["ox"]) / meta["res"])
+        cy = int((meta["robot_y"] - meta["oy"]) / meta["res"])
+        for step in range(1000):
+            cx = int(np.clip(cx + rng.integers(-4, 5), 100, W - 100))
+            cy = int(np.clip(cy + rng.integers(-4, 5), 100, H - 100))
+            rect = synth.reveal_step(a, meta, cx, cy, rng)
+            rx, ry = meta["ox"] + (cx + 0.5) * meta["res"], meta["oy"] + (cy + 0.5) * meta["res"]
+            ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"], dirty=rect)
+            st, res = ctx.cycle(rx, ry, 0.3, meta["poly"], capi.FISHER_BEST_YAW)
+            assert st == 0
+            if step % 50 == 49:
+                got = ctx.cycle_fetch(res.n_frontiers)
+                sto, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, rx, ry, capacity=1 << 17, cell_capacity=1 << 22)
+                assert len(fr) == res.n_frontiers, step
+                for key in ("goal_mx", "goal_my", "size", "component", "chunk", "first_cell"):
+                    np.testing.assert_array_equal(got["frontiers"][key], fr[key], err_msg=f"{step} {key}")
+                pick = np.linspace(0, len(fr) - 1, 200).astype(np.int64)
+                arr, _, _ = oracle.score_arrival(a, meta, fr[pick], meta["poly"])
+                for key in REC_FIELDS:
+                    np.testing.assert_array_equal(got["arrival"][key][pick], arr[key], err_msg=f"{step} {key}")
+            if step % 250 == 249:
+                got = ctx.cycle_fetch(res.n_frontiers)
+                ref = capi.Context(params)
+                ref.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+                ref.fisher_generate_lookup()
+                ref.set_map_points(pts)
+                st2, res2 = ref.cycle(rx, ry, 0.3, meta["poly"], capi.FISHER_BEST_YAW)
+                want = ref.cycle_fetch(res2.n_frontiers)
+                ref.close()
+                assert st2 == 0 and res2.n_frontiers == res.n_frontiers
+                for key in got:
+                    assert got[key].tobytes() == want[key].tobytes(), (step, key)
+    finally:
+        ctx.close()
