@@ -654,7 +654,10 @@ struct PoseFrame {      // per-CTA, built by thread 0
   M3f Rcw;  V3f tcw;    // se3ROSToORB(poseToAffine(pose))
   M3f Rinv; V3f tinv;   // inverse(poseToAffine(pose)): map -> pose frame
   double plane[11][4];  // n.p + d >= -margin inside (map frame, unit normals): 5 frustum + 6 lookup-domain planes
-  float px, py;
+  float px, py, pz;
+  float guard;          // metres: bound on |one-transform local coordinates - either of the reference's float evaluations|
+  float gu, gv, gvox;   // the guard in the units of the image tests (times Zc) and of the voxel rounding
+  int exact_only;       // Rinv is not the transpose of R to rounding (a quaternion far from unit length): no shortcut
 };
 
 __device__ void build_pose_frame(const fitslam_pose &pose, const FisherParams &P, PoseFrame &F) {
@@ -679,7 +682,22 @@ __device__ void build_pose_frame(const fitslam_pose &pose, const FisherParams &P
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) neg.m[i][j] = -F.Rinv.m[i][j];
   F.tinv = mulv(neg, t);
-  F.px = t.v[0]; F.py = t.v[1];
+  F.px = t.v[0]; F.py = t.v[1]; F.pz = t.v[2];
+  // The point loop evaluates l = Rinv * (p - t) once and reads both the camera coordinates (-l.y, -l.z, l.x) and the pose-frame
+  // coordinates off it; the reference evaluates them separately as Rcw * Pw + tcw and Rinv * p + tinv.  All three round the
+  // same real vector (when Rinv = R^T, which holds to rounding for a unit quaternion).  Error of a reference evaluation:
+  // three products and two sums per dot product, each 2^-24 relative to at most |p|_1 = |t|_1 + |d|_1, the same for the
+  // translation term, one more rounding for the final sum: under 2^-22 * (2 |t|_1 + |d|_1).  Of the one-transform form:
+  // 2^-22 * |d|_1.  |d|_1 <= 3 * reach < 80 m.  The guard doubles that sum; a decision closer than the guard to its boundary
+  // is taken again with the reference's own arithmetic.
+  float asym = 0.f;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) asym = fmaxf(asym, fabsf(F.Rinv.m[i][j] - R.m[j][i]));
+  F.exact_only = !(asym <= 1e-5f) ? 1 : 0;  // (also NaN)
+  F.guard = 1e-6f * (fabsf(t.v[0]) + fabsf(t.v[1]) + fabsf(t.v[2]) + 96.f) + 3.f * asym * 96.f;
+  F.gu = (P.fx + fmaxf(P.cx, P.max_u - P.cx)) * F.guard;
+  F.gv = (P.fy + fmaxf(P.cy, P.max_v - P.cy)) * F.guard;
+  F.gvox = F.guard * P.inv_step_f + 2e-4f;  // + the rounding of the float product
 }
 
 // ---- conservative culling planes (double; only used to skip whole bins): plane k of 11, one thread each
@@ -850,10 +868,9 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   uint32_t *tab = dyn + BM_WORDS;   // SEC_SLOTS packed slots, 0 = empty
   __shared__ uint32_t s_used, s_coll, s_overflow, s_nchunk, s_next, s_chunk_ovf;
   __shared__ uint2 s_chunk[MAX_CHUNKS];  // [first, last) point ranges of the bins that survive the cull
-  __shared__ float s_wq[FISHER_THREADS / 32][3][64];  // per warp: coordinates of visible points waiting for the voxel step
-                                                       // (kept here instead of their indices: no second load per point)
   __shared__ uint2 s_cq[FISHER_THREADS / 32][64];      // per warp: {table index | outside << 31, information} of landmarks
                                                        // waiting for the hash-table step
+  __shared__ uint32_t s_uq[FISHER_THREADS / 32][64];   // per warp: points waiting for the reference's own arithmetic
   __shared__ uint2 s_xrow[MAX_XROWS];
   __shared__ double s_red[FISHER_THREADS / 32];
   uint32_t pi;
@@ -868,7 +885,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   }
   if (threadIdx.x == 0) build_pose_frame(poses[pi], P, F);
   else if (P.xrow && threadIdx.x >= 32 && threadIdx.x - 32 < (uint32_t)P.dims[0]) s_xrow[threadIdx.x - 32] = __ldg(P.xrow + threadIdx.x - 32);
-  const uint2 *xrow = P.xrow ? s_xrow : nullptr;
+  const uint2 *xrow = P.xrow ? s_xrow : nullptr;  // (the exact path's argument)
+  const bool have_rows = P.xrow != nullptr;
   __syncthreads();
   if (threadIdx.x < 11) build_pose_plane(P, F, (int)threadIdx.x);
   __syncthreads();
@@ -938,8 +956,8 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   // than slots), the rest of the attempt only counts; the count then sizes a multi-pass run in which pass p owns the voxels
   // whose hash falls in partition p, so that every pass fits with a load factor <= 1/2.
   volatile uint32_t *v_overflow = &s_overflow;
-  float (*wq)[64] = s_wq[wid];
   uint2 *cq = s_cq[wid];
+  uint32_t *uq = s_uq[wid];
   for (uint32_t npass = 1; npass <= 65536;) {
     total = 0.0;
     if (threadIdx.x == 0) { s_used = 0; s_coll = 0; s_overflow = 0; }
@@ -948,79 +966,139 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
       if (threadIdx.x == 0) s_next = 0;
       __syncthreads();
       uint32_t my_used = 0, my_coll = 0;
-      // Three steps per point, with a compaction before the second and the third: the visibility test runs on every point
-      // of the chunk; the visible ones (about 6 in 10) queue up per warp and the voxel + bitmap step runs on full warps;
-      // the landmarks whose voxel already had one (1 in 8) queue up again and the hash-table step runs on full warps.
-      // Both queues are stacks: a step takes the top 32 entries, the rest stays where it is.
-      uint32_t n_q = 0, n_c = 0;
+      // Two steps per point.  The first runs on every point of the chunk: one transform into the pose frame, the visibility
+      // test and the voxel read off it, the voxel's bit in the CTA bitmap.  A point closer than the guard to one of those
+      // decisions' boundaries (1 or 2 in 100) waits in a per-warp stack for the reference's own arithmetic; a landmark whose
+      // voxel already had one (1 in 8) waits in another for the hash-table step.  Both stacks are taken 32 entries at a time.
+      uint32_t n_c = 0, n_u = 0;
+      // hash-table step on the top `take` entries of the collision stack
+      auto drain_collisions = [&]() {
+        const uint32_t take = min(n_c, 32u), at0 = n_c - take;
+        if (lane < take && !*v_overflow) {
+          const uint2 e = cq[at0 + lane];
+          const uint32_t outside = e.x >> 31, vox = e.x & 0x7fffffffu;
+          // the landmark that raises a voxel's count to k adds information(voxel) * exp(1 - k^s), as a difference of
+          // the host-tabulated prefix sums; inside the bitmap the table counts from the second landmark on
+          const uint32_t cnt = table_count(tab, mix32(vox), (vox + 1u) | (outside ? OUTSIDE_BIT : 0u));
+          const uint32_t k = cnt + 1u - outside;
+          if (cnt == 0u) *v_overflow = 1;
+          else if (k <= (uint32_t)CROWD_MAX) total += (double)__uint_as_float(e.y) * (__ldg(P.crowd + k) - __ldg(P.crowd + k - 1u));
+        }
+        n_c = at0;
+        __syncwarp();
+      };
+      // one landmark per lane (vox < 0: none): bitmap, or onto the collision stack
+      auto commit = [&](int vox, int bit) {
+        bool collide = false;
+        uint32_t c_key = 0;
+        float inf_v = 0.f;
+        if (vox >= 0 && (npass == 1 || ((mix32((uint32_t)vox) >> 12) & (npass - 1)) == pass)) {
+          ++my_used;
+          if (!*v_overflow) {  // a lost attempt keeps counting only
+            inf_v = __ldg(P.lut + vox);
+            if (bit >= 0) {
+              const uint32_t w = (uint32_t)bit >> 5, m = 1u << (bit & 31);
+              uint32_t old = ((volatile uint32_t *)bm)[w];
+              if (!(old & m)) old = atomicOr(&bm[w], m);
+              if (!(old & m)) total += (double)inf_v;  // first landmark of its voxel: factor exp(1 - 1^s) = 1
+              else { collide = true; c_key = (uint32_t)vox; }
+            } else {
+              collide = true;
+              c_key = (uint32_t)vox | 0x80000000u;
+            }
+          }
+        }
+        const uint32_t cbal = __ballot_sync(0xffffffffu, collide);
+        if (cbal) {
+          if (collide) cq[n_c + __popc(cbal & ((1u << lane) - 1u))] = make_uint2(c_key, __float_as_uint(inf_v));
+          n_c += __popc(cbal);
+          my_coll += collide ? 1u : 0u;
+          __syncwarp();
+          if (n_c >= 32) drain_collisions();  // (the stack holds 64)
+        }
+      };
+      // the reference's own arithmetic on the top entries of the stack of uncertain points
+      auto drain_unsure = [&]() {
+        const uint32_t take = min(n_u, 32u), at0 = n_u - take;
+        int vox = -1, bit = -1;
+        if (lane < take) {
+          const float4 q = __ldg(P.pts + uq[at0 + lane]);
+          if (point_visible(q, F, P)) vox = voxel_and_bit(q, F, P, xrow, &bit);
+        }
+        n_u = at0;
+        __syncwarp();
+        commit(vox, bit);
+      };
       while (true) {
         uint32_t ci = 0;
         if (lane == 0) ci = atomicAdd(&s_next, 1u);
         ci = __shfl_sync(0xffffffffu, ci, 0);
         const bool last = ci >= n_chunk;
         const uint2 ch = last ? make_uint2(0, 0) : s_chunk[ci];
-        for (uint32_t i0 = ch.x; i0 < ch.y || (last && (n_q > 0 || n_c > 0)); i0 += 32) {
+        for (uint32_t i0 = ch.x; i0 < ch.y; i0 += 32) {
           const uint32_t i = i0 + lane;
-          float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (i < ch.y) q = __ldg(P.pts + i);
-          const bool vis = i < ch.y && point_visible_fast(q, F, P);
-          const uint32_t bal = __ballot_sync(0xffffffffu, vis);
-          if (vis) {
-            const uint32_t at = n_q + __popc(bal & ((1u << lane) - 1u));
-            wq[0][at] = q.x; wq[1][at] = q.y; wq[2][at] = q.z;
-          }
-          n_q += __popc(bal);
-          __syncwarp();
-          bool collide = false;
-          uint32_t c_key = 0;
-          float inf_v = 0.f;
-          if (n_q >= 32 || (last && n_q > 0)) {
-            const uint32_t take = min(n_q, 32u), at0 = n_q - take;
-            int vox = -1, bit = -1;
-            if (lane < take) vox = voxel_and_bit(make_float4(wq[0][at0 + lane], wq[1][at0 + lane], wq[2][at0 + lane], 0.f), F, P, xrow, &bit);
-            n_q = at0;
-            __syncwarp();
-            if (vox >= 0 && (npass == 1 || ((mix32((uint32_t)vox) >> 12) & (npass - 1)) == pass)) {
-              ++my_used;
-              if (!*v_overflow) {  // a lost attempt keeps counting only
-                inf_v = __ldg(P.lut + vox);
-                if (bit >= 0) {
-                  const uint32_t w = (uint32_t)bit >> 5, m = 1u << (bit & 31);
-                  uint32_t old = ((volatile uint32_t *)bm)[w];
-                  if (!(old & m)) old = atomicOr(&bm[w], m);
-                  if (!(old & m)) total += (double)inf_v;  // first landmark of its voxel: factor exp(1 - 1^s) = 1
-                  else { collide = true; c_key = (uint32_t)vox; }
-                } else {
-                  collide = true;
-                  c_key = (uint32_t)vox | 0x80000000u;
+          int vox = -1, bit = -1;
+          bool unsure = false;
+          if (i < ch.y) {
+            const float4 q = __ldg(P.pts + i);
+            const float dx = q.x - F.px, dy = q.y - F.py, dz = q.z - F.pz;
+            const float lx = __fmaf_rn(F.Rinv.m[0][0], dx, __fmaf_rn(F.Rinv.m[0][1], dy, F.Rinv.m[0][2] * dz));
+            const float ly = __fmaf_rn(F.Rinv.m[1][0], dx, __fmaf_rn(F.Rinv.m[1][1], dy, F.Rinv.m[1][2] * dz));
+            const float lz = __fmaf_rn(F.Rinv.m[2][0], dx, __fmaf_rn(F.Rinv.m[2][1], dy, F.Rinv.m[2][2] * dz));
+            // camera coordinates (Xc, Yc, Zc) = (-ly, -lz, lx); u = fx Xc / Zc + cx in [0, max_u] <=> -cx Zc <= fx Xc <= (max_u - cx) Zc
+            // (fminf / fmaxf drop NaNs: non-finite points must not reach them)
+            const bool finite = fabsf(dx) + fabsf(dy) + fabsf(dz) < 1e6f;
+            bool sure = !F.exact_only && finite && lx >= 0.05f, vis = false;
+            if (sure) {
+              const float au = -P.fx * ly, av = -P.fy * lz;
+              const float eu = F.gu + 4e-4f * lx, ev = F.gv + 4e-4f * lx;  // + the roundings of u, v themselves (3 ulp of 10^3 px) times Zc
+              const float u0 = au + P.cx * lx, u1 = (P.max_u - P.cx) * lx - au, v0 = av + P.cy * lx, v1 = (P.max_v - P.cy) * lx - av;
+              const float inner = fminf(fminf(u0 - eu, u1 - eu), fminf(v0 - ev, v1 - ev));
+              const float outer = fminf(fminf(u0 + eu, u1 + eu), fminf(v0 + ev, v1 + ev));
+              vis = inner >= 0.f;
+              sure = vis || outer < 0.f;
+            } else if (!F.exact_only && finite && lx < -F.guard) {
+              sure = true;  // behind the camera whichever evaluation is asked
+            }
+            if (sure && vis) {
+              // voxel = round(l / step) per axis, outside the guard band of a half-integer
+              const float rx = lx * P.inv_step_f, ry = ly * P.inv_step_f, rz = lz * P.inv_step_f;
+              const float fx_ = rintf(rx), fy_ = rintf(ry), fz_ = rintf(rz);
+              const float edge = fmaxf(fmaxf(fabsf(rx - fx_), fabsf(ry - fy_)), fabsf(rz - fz_));
+              if (edge < 0.5f - F.gvox && fmaxf(fmaxf(fabsf(rx), fabsf(ry)), fabsf(rz)) < 512.0f) {
+                const int i0_ = (int)fx_ - P.org[0], i1_ = (int)fy_ - P.org[1], i2_ = (int)fz_ - P.org[2];
+                if ((unsigned)i0_ < (unsigned)P.dims[0] && (unsigned)i1_ < (unsigned)P.dims[1] && (unsigned)i2_ < (unsigned)P.dims[2]) {
+                  vox = (i0_ * P.dims[1] + i1_) * P.dims[2] + i2_;
+                  if (!P.lut_dense) {
+                    const float val = __ldg(P.lut + vox);
+                    if (!(val == val)) vox = -1;
+                  }
+                  if (vox >= 0 && have_rows) {
+                    const uint2 xr = s_xrow[i0_];
+                    const int rows = (int)(xr.y >> 16), zr = i2_ - (int)(xr.y & 0xffffu);
+                    if ((unsigned)zr < (unsigned)rows) bit = (int)xr.x + i1_ * rows + zr;
+                  }
                 }
+              } else {
+                sure = false;
               }
             }
+            unsure = !sure;
           }
-          const uint32_t cbal = __ballot_sync(0xffffffffu, collide);
-          if (cbal) {
-            if (collide) cq[n_c + __popc(cbal & ((1u << lane) - 1u))] = make_uint2(c_key, __float_as_uint(inf_v));
-            n_c += __popc(cbal);
-            my_coll += collide ? 1u : 0u;
+          const uint32_t ubal = __ballot_sync(0xffffffffu, unsure);
+          if (ubal) {
+            if (unsure) uq[n_u + __popc(ubal & ((1u << lane) - 1u))] = i;
+            n_u += __popc(ubal);
             __syncwarp();
+            if (n_u >= 32) drain_unsure();  // (the stack holds 64)
           }
-          if (n_c >= 32 || (last && n_q == 0 && n_c > 0)) {
-            const uint32_t take = min(n_c, 32u), at0 = n_c - take;
-            if (lane < take && !*v_overflow) {
-              const uint2 e = cq[at0 + lane];
-              const uint32_t outside = e.x >> 31, vox = e.x & 0x7fffffffu;
-              // the landmark that raises a voxel's count to k adds information(voxel) * exp(1 - k^s), as a difference of
-              // the host-tabulated prefix sums; inside the bitmap the table counts from the second landmark on
-              const uint32_t cnt = table_count(tab, mix32(vox), (vox + 1u) | (outside ? OUTSIDE_BIT : 0u));
-              const uint32_t k = cnt + 1u - outside;
-              if (cnt == 0u) *v_overflow = 1;
-              else if (k <= (uint32_t)CROWD_MAX) total += (double)__uint_as_float(e.y) * (__ldg(P.crowd + k) - __ldg(P.crowd + k - 1u));
-            }
-            n_c = at0;
-            __syncwarp();
-          }
+          commit(vox, bit);
         }
-        if (last) break;
+        if (last) {
+          while (n_u > 0) drain_unsure();
+          while (n_c > 0) drain_collisions();
+          break;
+        }
       }
       if (my_used) atomicAdd(&s_used, my_used);
       if (my_coll) atomicAdd(&s_coll, my_coll);
