@@ -183,7 +183,12 @@ def run_gpu(args):
         raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
     torch.cuda.set_device(local)
     uids = [None, None]
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version banner must not share stdout with the JSON line
+    saved_stdout = None
+    if world > 1:
+        # NCCL prints its version banner on stdout when the first communicator is made: stdout carries the JSON line only
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
     if world > 1:
         # torch.distributed is the launcher's plumbing only (barriers, the max over ranks of the timings, carrying the two
         # 128-byte NCCL ids); the data path's collectives are the library's own (csrc/comm.cu)
@@ -191,6 +196,11 @@ def run_gpu(args):
         if rank == 0:
             uids = [capi.Context.comm_unique_id(), capi.Context.comm_unique_id()]
         dist.broadcast_object_list(uids, src=0)
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def barrier():
