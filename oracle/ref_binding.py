@@ -65,3 +65,59 @@ class Reference:
         out = (C.c_uint32 * 8)()
         n = self.lib.ref_nhood(C.c_uint32(W), C.c_uint32(H), C.c_uint32(idx), C.c_int(1 if eight else 0), out)
         return [out[i] for i in range(n)]
+
+    def score_arrival(self, a, meta, params, goals, sizes, poly):
+        """FrontierCostCalculator::setMaxArrivalInformation + setArrivalInformationForFrontier per frontier
+        (DEP/src/CostCalculator.cpp:23-191, compiled from the reference).  Returns (rows [n, 6] = arrival information, achievable,
+        goal orientation x y z w; limits = (return value, max_arrival_info_gt, min_arrival_info_gt))."""
+        a, m = self._map(a, meta)
+        g = np.ascontiguousarray(np.column_stack([np.asarray(goals, np.float64), np.asarray(sizes, np.float64)]))
+        n = len(g)
+        poly = np.ascontiguousarray(poly, dtype=np.float64)
+        out = np.zeros((n, 6), dtype=np.float64)
+        lim = np.zeros(3, dtype=np.float64)
+        self.lib.ref_score_arrival(*m, C.c_double(params.max_camera_depth), C.c_double(params.delta_theta), C.c_double(params.camera_fov),
+                                   C.c_double(params.robot_radius), C.c_void_p(g.ctypes.data), C.c_uint32(n), C.c_void_p(poly.ctypes.data),
+                                   C.c_void_p(out.ctypes.data), C.c_void_p(lim.ctypes.data))
+        return out, tuple(lim)
+
+    def plan_euclidean(self, rx, ry, quat_xyzw, goals, achievable, arrival):
+        """setPlanForFrontierEuclidean + recomputeNormalizationFactors (DEP/src/CostCalculator.cpp:445-485, 512-520).  Returns
+        (rows [n, 3] = achievable, path length, path heading; (min, max plan distance, min arrival information); robot yaw as
+        quatToEuler computes it)."""
+        robot = np.array([rx, ry, *quat_xyzw], dtype=np.float64)
+        g = np.ascontiguousarray(goals, dtype=np.float64)
+        ach = np.ascontiguousarray(achievable, dtype=np.uint8)
+        arr = np.ascontiguousarray(arrival, dtype=np.float64)
+        n = len(g)
+        out = np.zeros((n, 3), dtype=np.float64)
+        norm = np.zeros(3, dtype=np.float64)
+        yaw = C.c_double()
+        self.lib.ref_plan_euclidean(C.c_void_p(robot.ctypes.data), C.c_void_p(g.ctypes.data), C.c_void_p(ach.ctypes.data),
+                                    C.c_void_p(arr.ctypes.data), C.c_uint32(n), C.c_void_p(out.ctypes.data), C.c_void_p(norm.ctypes.data),
+                                    C.byref(yaw))
+        return out, tuple(norm), yaw.value
+
+    def assign_costs(self, a, meta, params, goals, sizes, poly, rx, ry, quat_xyzw, blacklisted=None):
+        """FrontierCostsManager::assignCosts({"ArrivalInformation", "EuclideanDistance"}) then
+        FullPathOptimizer::getFilteredFrontiersN(n = num_frontiers_in_local_area), both compiled from the reference
+        (DEP/src/FrontierCostsManager.cpp:47-213, DEP/src/FullPathOptimizer.cpp:157-227).  Returns (status, rows [n, 7] = weighted
+        cost, arrival utility, distance utility, achievable, arrival information, path length, path heading; local indices, global
+        indices, closest global index)."""
+        a, m = self._map(a, meta)
+        g = np.ascontiguousarray(np.column_stack([np.asarray(goals, np.float64), np.asarray(sizes, np.float64)]))
+        n = len(g)
+        poly = np.ascontiguousarray(poly, dtype=np.float64)
+        robot = np.array([rx, ry, *quat_xyzw], dtype=np.float64)
+        bl = None if blacklisted is None else np.ascontiguousarray(blacklisted, dtype=np.uint8)
+        out = np.zeros((n, 7), dtype=np.float64)
+        sel = np.zeros(3, dtype=np.int32)
+        loc, glo = np.full(n + 1, -1, np.int32), np.full(n + 1, -1, np.int32)
+        st = self.lib.ref_assign_costs(*m, C.c_double(params.max_camera_depth), C.c_double(params.delta_theta), C.c_double(params.camera_fov),
+                                       C.c_double(params.robot_radius), C.c_double(params.alpha), C.c_double(params.beta),
+                                       C.c_double(params.vx_max), C.c_double(params.wz_max), C.c_void_p(g.ctypes.data), C.c_uint32(n),
+                                       C.c_void_p(poly.ctypes.data), C.c_void_p(robot.ctypes.data),
+                                       C.c_void_p(bl.ctypes.data) if bl is not None else None, C.c_uint32(params.num_frontiers_in_local_area),
+                                       C.c_void_p(out.ctypes.data), C.c_void_p(sel.ctypes.data), C.c_void_p(loc.ctypes.data),
+                                       C.c_void_p(glo.ctypes.data))
+        return st, out, loc[:sel[0]], glo[:sel[1]], int(sel[2])

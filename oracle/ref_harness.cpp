@@ -1,12 +1,17 @@
 // ref_harness.cpp -- C entry points over the REFERENCE's own frontier search and ray helpers, compiled from
 // /root/reference where it lies (oracle/Makefile, target _ref/libfitslam_ref.so): DEP/src/Frontier.cpp,
-// DEP/src/FrontierSearch.cpp and the costmap half of DEP/src/Helpers.cpp (lines 1-330: bresenham2D, getTracedCells,
-// isRobotFootprintInLethal, nhood4 / nhood8, nearestFreeCell), against the stand-in headers of oracle/ref_shims/.
+// DEP/src/FrontierSearch.cpp, the costmap half of DEP/src/Helpers.cpp (lines 1-330: bresenham2D, getTracedCells,
+// isRobotFootprintInLethal, nhood4 / nhood8, nearestFreeCell) and four member functions of DEP/src/CostCalculator.cpp
+// (setArrivalInformationForFrontier, setMaxArrivalInformation, setPlanForFrontierEuclidean, recomputeNormalizationFactors),
+// against the stand-in headers of oracle/ref_shims/.
 // Test infrastructure: it pins the restatement in oracle.cpp (tests/test_ref_pin.py) and nothing else links it.
 #include <cstdint>
 #include <cstring>
 #include <vector>
 
+#include <frontier_exploration/CostCalculator.hpp>
+#include <frontier_exploration/FrontierCostsManager.hpp>
+#include <frontier_exploration/FullPathOptimizer.hpp>
 #include <frontier_exploration/FrontierSearch.hpp>
 #include <frontier_exploration/Helpers.hpp>
 
@@ -94,6 +99,125 @@ int ref_nhood(uint32_t W, uint32_t H, uint32_t idx, int eight, uint32_t *out) {
   const std::vector<unsigned int> v = eight ? frontier_exploration::nhood8(idx, map) : frontier_exploration::nhood4(idx, map);
   for (size_t i = 0; i < v.size() && i < 8; ++i) out[i] = v[i];
   return (int)v.size();
+}
+
+// FrontierCostCalculator::setMaxArrivalInformation then setArrivalInformationForFrontier for n frontiers (DEP/src/CostCalculator.cpp:
+// 23-191), as FrontierCostsManager::assignCosts calls them.  goals: n x 3 doubles (goal x, goal y, size); poly: {xmin, ymin, xmax,
+// ymax}.  out: n x 6 doubles (arrival information, achievable, goal orientation x y z w); limits: {return value of
+// setMaxArrivalInformation, max_arrival_info_gt, min_arrival_info_gt}.
+void ref_score_arrival(const uint8_t *cells, uint32_t W, uint32_t H, double res, double ox, double oy, double max_camera_depth,
+                       double delta_theta, double camera_fov, double robot_radius, const double *goals, uint32_t n, const double *poly,
+                       double *out, double *limits) {
+  Costmap2D map = make_map(cells, W, H, res, ox, oy);
+  frontier_exploration::FrontierCostCalculator calc(&map, max_camera_depth, delta_theta, camera_fov, robot_radius);
+  limits[0] = calc.setMaxArrivalInformation();
+  limits[1] = calc.getMaxArrivalInformation();
+  limits[2] = calc.getMinArrivalInformationGT();
+  std::vector<double> polygon(poly, poly + 4);
+  for (uint32_t i = 0; i < n; ++i) {
+    FrontierPtr f = std::make_shared<Frontier>();
+    f->setGoalPoint(goals[3 * i], goals[3 * i + 1]);
+    f->setSize((int)goals[3 * i + 2]);
+    f->setAchievability(true);
+    calc.setArrivalInformationForFrontier(f, polygon);
+    out[6 * i] = f->getArrivalInformation();
+    out[6 * i + 1] = f->isAchievable() ? 1.0 : 0.0;
+    const auto q = f->getGoalOrientation();
+    out[6 * i + 2] = q.x; out[6 * i + 3] = q.y; out[6 * i + 4] = q.z; out[6 * i + 5] = q.w;
+  }
+}
+
+// setPlanForFrontierEuclidean (DEP/src/CostCalculator.cpp:445-485) + recomputeNormalizationFactors (:512-520) over n frontiers.
+// robot: {x, y, qx, qy, qz, qw}; goals: n x 2; achievable_in: n flags; arrival: n doubles (for the normalisation factors).
+// out: n x 3 doubles (achievable, path length, path heading); norm: {min, max plan distance, min arrival information};
+// *robot_yaw = quatToEuler(orientation)[2] as the function computes it (before its own +2 pi).
+void ref_plan_euclidean(const double *robot, const double *goals, const uint8_t *achievable_in, const double *arrival, uint32_t n,
+                        double *out, double *norm, double *robot_yaw) {
+  Costmap2D map(4, 4, 1.0, 0.0, 0.0);
+  frontier_exploration::FrontierCostCalculator calc(&map, 2.0, 0.1, 1.04, 0.6);
+  calc.reset();
+  geometry_msgs::msg::Pose start;
+  start.position.x = robot[0]; start.position.y = robot[1];
+  start.orientation.x = robot[2]; start.orientation.y = robot[3]; start.orientation.z = robot[4]; start.orientation.w = robot[5];
+  *robot_yaw = frontier_exploration::quatToEuler(start.orientation)[2];
+  for (uint32_t i = 0; i < n; ++i) {
+    FrontierPtr f = std::make_shared<Frontier>();
+    f->setGoalPoint(goals[2 * i], goals[2 * i + 1]);
+    f->setAchievability(achievable_in[i] != 0);
+    f->setArrivalInformation(arrival[i]);
+    calc.setPlanForFrontierEuclidean(start, f, nullptr, false, false);
+    calc.recomputeNormalizationFactors(f);
+    out[3 * i] = f->isAchievable() ? 1.0 : 0.0;
+    out[3 * i + 1] = f->getPathLength();
+    out[3 * i + 2] = f->getPathHeading();
+  }
+  norm[0] = calc.getMinPlanDistance();
+  norm[1] = calc.getMaxPlanDistance();
+  norm[2] = calc.getMinArrivalInformation();
+}
+
+// FrontierCostsManager::assignCosts with cost types {"ArrivalInformation", "EuclideanDistance"} (DEP/src/FrontierCostsManager.cpp:
+// 47-213: arrival information, Euclidean plan, normalisation factors, the U1 block) followed by
+// FullPathOptimizer::getFilteredFrontiersN (DEP/src/FullPathOptimizer.cpp:157-227) with n = n_local.
+// goals: n x 3 (goal x, goal y, size); robot: {x, y, qx, qy, qz, qw}; blacklisted: n flags (setFrontierBlacklist).
+// out: n x 7 doubles (weighted cost, arrival_gain_utility, distance_utility, achievable, arrival information, path length, path
+// heading); sel: {n_local, n_global, index of closest_global_frontier or -1}; local_idx / global_idx: frontier indices in order.
+// Returns 0, 1 if assignCosts returned false, 2 / 3 if it threw "ARRIVAL UTILITY ERROR..." / "Cost out of bounds", 4 for another throw.
+int ref_assign_costs(const uint8_t *cells, uint32_t W, uint32_t H, double res, double ox, double oy, double max_camera_depth,
+                     double delta_theta, double camera_fov, double robot_radius, double alpha, double beta, double vx_max, double wz_max,
+                     const double *goals, uint32_t n, const double *poly, const double *robot, const uint8_t *blacklisted, uint32_t n_local,
+                     double *out, int32_t *sel, int32_t *local_idx, int32_t *global_idx) {
+  Costmap2D map = make_map(cells, W, H, res, ox, oy);
+  frontier_exploration::FrontierCostsManager mgr(&map, max_camera_depth, delta_theta, camera_fov, robot_radius, alpha, beta, vx_max, wz_max);
+  std::vector<FrontierPtr> list, black;
+  for (uint32_t i = 0; i < n; ++i) {
+    FrontierPtr f = std::make_shared<Frontier>();
+    f->setGoalPoint(goals[3 * i], goals[3 * i + 1]);
+    f->setSize((int)goals[3 * i + 2]);
+    f->setUID(generateUID(f));
+    f->setAchievability(true);
+    f->setBlacklisted(false);
+    list.push_back(f);
+    if (blacklisted && blacklisted[i]) black.push_back(f);
+  }
+  if (!black.empty()) mgr.setFrontierBlacklist(black);
+  geometry_msgs::msg::Pose start;
+  start.position.x = robot[0]; start.position.y = robot[1];
+  start.orientation.x = robot[2]; start.orientation.y = robot[3]; start.orientation.z = robot[4]; start.orientation.w = robot[5];
+  std::vector<std::vector<std::string>> types(n, {"ArrivalInformation", "EuclideanDistance"});
+  std::vector<double> polygon(poly, poly + 4);
+  int status = 0;
+  try {
+    if (!mgr.assignCosts(list, polygon, start, nullptr, types)) status = 1;
+  } catch (const std::runtime_error &e) {
+    const std::string w = e.what();
+    status = w.rfind("ARRIVAL UTILITY ERROR", 0) == 0 ? 2 : (w == "Cost out of bounds" ? 3 : 4);
+  }
+  if (status != 0) return status;
+  for (uint32_t i = 0; i < n; ++i) {
+    const FrontierPtr &f = list[i];
+    out[7 * i] = f->getWeightedCost();
+    const bool blk = blacklisted && blacklisted[i];
+    out[7 * i + 1] = blk ? 0.0 : f->getCost("arrival_gain_utility");
+    out[7 * i + 2] = blk ? 0.0 : f->getCost("distance_utility");
+    out[7 * i + 3] = f->isAchievable() ? 1.0 : 0.0;
+    out[7 * i + 4] = f->getArrivalInformation();
+    out[7 * i + 5] = f->getPathLength();
+    out[7 * i + 6] = blk ? 0.0 : f->getPathHeading();
+    if (blk) f->setBlacklisted(true);  // what the behaviour tree does with a blacklisted frontier before the selection
+  }
+  frontier_exploration::FullPathOptimizer opt;
+  frontier_exploration::SortedFrontiers sorted;
+  geometry_msgs::msg::PoseStamped robotP;
+  robotP.pose = start;
+  opt.getFilteredFrontiersN(list, n_local, sorted, robotP);
+  auto index_of = [&](const FrontierPtr &f) { for (uint32_t i = 0; i < n; ++i) if (list[i] == f) return (int32_t)i; return (int32_t)-1; };
+  sel[0] = (int32_t)sorted.local_frontiers.size();
+  sel[1] = (int32_t)sorted.global_frontiers.size();
+  sel[2] = sorted.closest_global_frontier ? index_of(sorted.closest_global_frontier) : -1;
+  for (size_t i = 0; i < sorted.local_frontiers.size(); ++i) local_idx[i] = index_of(sorted.local_frontiers[i]);
+  for (size_t i = 0; i < sorted.global_frontiers.size(); ++i) global_idx[i] = index_of(sorted.global_frontiers[i]);
+  return 0;
 }
 
 }  // extern "C"

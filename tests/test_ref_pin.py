@@ -1,8 +1,12 @@
-"""Pins the oracle to the REFERENCE ITSELF: oracle/_ref/libfitslam_ref.so is DEP/src/FrontierSearch.cpp, Frontier.cpp and
-the costmap half of Helpers.cpp compiled from /root/reference where it lies (oracle/Makefile) against stand-in ROS
-headers.  Every comparison is exact: goal points and every_frontier coordinates bit for bit, sizes, orders, ray counts.
+"""Pins the oracle to the REFERENCE ITSELF: oracle/_ref/libfitslam_ref.so is DEP/src/FrontierSearch.cpp, Frontier.cpp, the
+costmap half of Helpers.cpp and the member functions of CostCalculator.cpp, FrontierCostsManager.cpp and FullPathOptimizer.cpp
+that make up stages R and N, compiled from /root/reference where it lies (oracle/Makefile) against stand-in ROS headers.
+Every comparison is exact: goal points, every_frontier coordinates, path lengths, headings and weighted costs bit for bit,
+sizes, orders, ray counts, selections.
 Rows pinned: S1-S6 (searchFrom, nearestFreeCell, isNewFrontierCell, buildNewFrontier, centroid + median sort
-with glibc atan2, getAllFrontiers), R2-R4 (getTracedCells, bresenham2D, isRobotFootprintInLethal), T4 (RayTracedCells)."""
+with glibc atan2, getAllFrontiers), R1-R6 (setArrivalInformationForFrontier, getTracedCells, bresenham2D,
+isRobotFootprintInLethal, setMaxArrivalInformation, recomputeNormalizationFactors), T4 (RayTracedCells), N1-N3 (assignCosts with
+the U1 block, setPlanForFrontierEuclidean, getFilteredFrontiersN)."""
 import math
 
 import numpy as np
@@ -170,3 +174,146 @@ def test_reference_roadmap_rays(oracle, ref, synth):
         assert ok
         want = (not hit) and unknown <= radius / meta["res"] * 0.3
         assert bool(ok_o[k]) == want, (k, hit, unknown)
+
+
+# ---- stage R and the Euclidean plan against the reference's own CostCalculator.cpp member functions -----------------------------
+def _arrival_vs_reference(oracle, ref, a, meta, fr, poly):
+    arr, rays, wins = oracle.score_arrival(a, meta, fr, poly)
+    rows, (ret, max_gt, min_gt) = ref.score_arrival(a, meta, oracle.params, np.stack([fr["goal_x"], fr["goal_y"]], axis=1), fr["size"], poly)
+    omax, omin, oval = oracle.arrival_limits(a, meta)
+    assert (ret, max_gt, min_gt) == (float(oval), omax, omin)  # setMaxArrivalInformation: return value, * 1.2, * 0.70 (bit for bit)
+    np.testing.assert_array_equal(rows[:, 0], arr["information"].astype(np.float64))
+    np.testing.assert_array_equal(rows[:, 1].astype(np.uint8), arr["achievable"])
+    # setGoalOrientation((maxIndex * DELTA_THETA) + (CAMERA_FOV / 2)), or 0.0 after a failed ray
+    theta = np.where(arr["ray_failed"] != 0, 0.0, arr["max_index"] * oracle.params.delta_theta + oracle.params.camera_fov / 2)
+    want_q = np.array([oracle.orientation_around_z(t) for t in theta])
+    np.testing.assert_array_equal(rows[:, 2:6].copy().view(np.uint64), want_q.view(np.uint64))
+    return arr
+
+
+@pytest.mark.parametrize("name,reference_rays", [("C1", True), ("C1", False), ("C3", True)])
+def test_reference_arrival_information_on_configs(oracle, ref, synth, capi, name, reference_rays):
+    a, meta, pts, ov = synth.make_config(name, reference_rays=reference_rays)
+    synth.apply_overrides(oracle.params, ov)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"])
+    assert st == 0 and len(fr) > 50
+    arr = _arrival_vs_reference(oracle, ref, a, meta, fr, meta["poly"])
+    assert arr["information"].max() > 0 and (arr["achievable"] == 0).any() and (arr["achievable"] == 1).any()
+    # a boundary polygon that cuts the rays short, and one that lies off the frontiers
+    box = synth.explored_bbox(a, meta)
+    cx, cy = 0.5 * (box[0] + box[2]), 0.5 * (box[1] + box[3])
+    _arrival_vs_reference(oracle, ref, a, meta, fr, [cx - 6.0, cy - 4.0, cx + 5.0, cy + 7.0])
+    _arrival_vs_reference(oracle, ref, a, meta, fr[:64], [box[2] + 1.0, box[3] + 1.0, box[2] + 3.0, box[3] + 3.0])
+
+
+def test_reference_arrival_information_near_lethal_and_borders(oracle, ref, synth, capi):
+    # goals next to lethal cells (footprint penalty: small frontiers become unachievable), goals whose rays leave the map
+    a, meta = synth.make_costmap(700, 600, seed=77, n_disc=14, r_lo=30, r_hi=90, n_holes=80)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"])
+    assert st == 0 and len(fr) > 20
+    H, W = a.shape
+    # keep the footprint disc inside the array (the reference does not bounds-check it: DESIGN.md section 1)
+    r = int(math.ceil(oracle.params.robot_radius / meta["res"])) + 1
+    ok = (fr["goal_mx"] >= r) & (fr["goal_mx"] < W - r) & (fr["goal_my"] >= r) & (fr["goal_my"] < H - r)
+    arr = _arrival_vs_reference(oracle, ref, a, meta, fr[ok], meta["poly"])
+    assert arr["footprint_in_lethal"].any()
+
+
+def test_reference_plan_euclidean_and_normalisation_factors(oracle, ref, synth, capi):
+    a, meta, pts, ov = synth.make_config("C1")
+    synth.apply_overrides(oracle.params, ov)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"])
+    arr, _, _ = oracle.score_arrival(a, meta, fr, meta["poly"])
+    rng = np.random.default_rng(8)
+    goals = np.stack([fr["goal_x"], fr["goal_y"]], axis=1)
+    for yaw_in in [0.0, 0.4, -2.9, 3.1, 1.5707963267948966, -1e-9] + list(rng.uniform(-np.pi, np.pi, 6)):
+        q = oracle.orientation_around_z(yaw_in)
+        # the robot at the map's robot pose, and right on top of a frontier (length < 0.5 m: not achievable)
+        for rx, ry in ((meta["robot_x"], meta["robot_y"]), (float(fr["goal_x"][3]) + 0.1, float(fr["goal_y"][3]))):
+            rows, norm, ref_yaw = ref.plan_euclidean(rx, ry, q, goals, arr["achievable"], arr["information"].astype(np.float64))
+            # the oracle takes the yaw the reference extracts from the quaternion (tf2 getRPY)
+            ach, pl, ph = oracle.plan_euclidean(rx, ry, ref_yaw, fr, arr["achievable"])
+            np.testing.assert_array_equal(rows[:, 0].astype(np.uint8), ach)
+            np.testing.assert_array_equal(rows[:, 1].view(np.uint64), pl.view(np.uint64))
+            np.testing.assert_array_equal(rows[:, 2].view(np.uint64), ph.view(np.uint64))
+            # recomputeNormalizationFactors over the list: min / max path length and min arrival information of the achievable ones
+            m = ach != 0
+            assert norm == (pl[m].min(), pl[m].max(), float(arr["information"][m].min()))
+            assert abs(ref_yaw - math.atan2(math.sin(yaw_in), math.cos(yaw_in))) < 1e-12
+
+
+# ---- stage N against the reference's own FrontierCostsManager::assignCosts and FullPathOptimizer::getFilteredFrontiersN -----------
+def _oracle_chain(oracle, a, meta, fr, poly, rx, ry, yaw, blacklisted):
+    arr, _, _ = oracle.score_arrival(a, meta, fr, poly)
+    ach, pl, ph = oracle.plan_euclidean(rx, ry, yaw, fr, arr["achievable"])
+    max_gt = oracle.arrival_limits(a, meta)[0]
+    st, wc, ua, ud, err = oracle.normalise(arr, ach, pl, ph, blacklisted, max_gt)
+    eligible = ach.astype(bool) if blacklisted is None else (ach.astype(bool) & ~np.asarray(blacklisted, bool))
+    srt, sel = oracle.select(eligible, pl)
+    return arr, ach, pl, ph, st, wc, ua, ud, srt, sel
+
+
+@pytest.mark.parametrize("name,with_blacklist", [("C1", False), ("C1", True), ("C3", False)])
+def test_reference_assign_costs_and_selection(oracle, ref, synth, capi, name, with_blacklist):
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    synth.apply_overrides(oracle.params, ov)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"])
+    assert st == 0 and len(fr) > 50
+    rng = np.random.default_rng(3)
+    bl = (rng.random(len(fr)) < 0.15).astype(np.uint8) if with_blacklist else None
+    for yaw_in in (0.4, -2.2):
+        q = oracle.orientation_around_z(yaw_in)
+        rx, ry = meta["robot_x"], meta["robot_y"]
+        _, _, ref_yaw = ref.plan_euclidean(rx, ry, q, np.zeros((0, 2)), np.zeros(0, np.uint8), np.zeros(0))
+        arr, ach, pl, ph, sto, wc, ua, ud, srt, sel = _oracle_chain(oracle, a, meta, fr, meta["poly"], rx, ry, ref_yaw, bl)
+        st, rows, loc, glo, closest = ref.assign_costs(a, meta, oracle.params, np.stack([fr["goal_x"], fr["goal_y"]], axis=1), fr["size"],
+                                                       meta["poly"], rx, ry, q, bl)
+        if with_blacklist:
+            # The reference itself cannot finish this call: a blacklisted frontier skips the plan step (FrontierCostsManager.cpp:
+            # 75-85), stays "achievable", and the U1 loop then reads its path heading, which was never set:
+            # Frontier::getPathHeading throws "Path heading frontier property is null" (Frontier.cpp:194-199).  The oracle and the
+            # device give such frontiers weighted_cost = DBL_MAX and carry on (DESIGN.md section 1 lists the deviation).
+            assert st == 4 and sto == 0
+            assert np.all(wc[bl.astype(bool)] == np.finfo(np.float64).max)
+            continue
+        assert st == 0 and sto == 0
+        blm = np.zeros(len(fr), bool) if bl is None else bl.astype(bool)
+        # weighted cost of every frontier, bit for bit (DBL_MAX for unachievable and blacklisted ones)
+        np.testing.assert_array_equal(rows[:, 0].copy().view(np.uint64), wc.view(np.uint64))
+        m = ~blm
+        np.testing.assert_array_equal(rows[m, 1].copy().view(np.uint64), ua[m].view(np.uint64))
+        np.testing.assert_array_equal(rows[m, 2].copy().view(np.uint64), ud[m].view(np.uint64))
+        np.testing.assert_array_equal(rows[m, 3].astype(np.uint8), ach[m])
+        np.testing.assert_array_equal(rows[m, 4], arr["information"][m].astype(np.float64))
+        np.testing.assert_array_equal(rows[m, 5].copy().view(np.uint64), pl[m].view(np.uint64))
+        np.testing.assert_array_equal(rows[m, 6].copy().view(np.uint64), ph[m].view(np.uint64))
+        # getFilteredFrontiersN: local list, global list, closest global frontier
+        np.testing.assert_array_equal(loc, srt[:sel.n_local].astype(np.int32))
+        np.testing.assert_array_equal(glo, srt[sel.global_begin:sel.global_begin + sel.n_global].astype(np.int32))
+        assert closest == sel.closest_global
+        assert len(loc) + len(glo) > 0
+
+
+def test_reference_assign_costs_few_frontiers_and_errors(oracle, ref, synth, capi):
+    a, meta, pts, ov = synth.make_config("C1", reference_rays=True)
+    synth.apply_overrides(oracle.params, ov)
+    st, fr, cells, seeds, cent = oracle.search_frontiers(a, meta, meta["robot_x"], meta["robot_y"])
+    q = oracle.orientation_around_z(0.0)
+    rx, ry = meta["robot_x"], meta["robot_y"]
+    _, _, ref_yaw = ref.plan_euclidean(rx, ry, q, np.zeros((0, 2)), np.zeros(0, np.uint8), np.zeros(0))
+    # the five cases of getFilteredFrontiersN's comment: fewer / more local candidates than n, none global, none local
+    d = np.hypot(fr["goal_x"] - rx, fr["goal_y"] - ry)
+    near, far = np.argsort(d)[:12], np.argsort(d)[-6:]
+    for pick in (near[:3], near[:5], near[:6], near, far, np.concatenate([near[:2], far]), np.concatenate([near, far])):
+        sub = fr[np.sort(pick)]
+        arr, ach, pl, ph, sto, wc, ua, ud, srt, sel = _oracle_chain(oracle, a, meta, sub, meta["poly"], rx, ry, ref_yaw, None)
+        st, rows, loc, glo, closest = ref.assign_costs(a, meta, oracle.params, np.stack([sub["goal_x"], sub["goal_y"]], axis=1), sub["size"],
+                                                       meta["poly"], rx, ry, q, None)
+        assert st == 0 and sto == 0
+        np.testing.assert_array_equal(rows[:, 0].copy().view(np.uint64), wc.view(np.uint64))
+        np.testing.assert_array_equal(loc, srt[:sel.n_local].astype(np.int32))
+        np.testing.assert_array_equal(glo, srt[sel.global_begin:sel.global_begin + sel.n_global].astype(np.int32))
+        assert closest == sel.closest_global
+    # no frontiers: assignCosts returns false (FrontierCostsManager.cpp:55-59)
+    st, rows, loc, glo, closest = ref.assign_costs(a, meta, oracle.params, np.zeros((0, 2)), np.zeros(0), meta["poly"], rx, ry, q, None)
+    assert st == 1
