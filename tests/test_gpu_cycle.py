@@ -188,3 +188,48 @@ def test_cycle_with_host_sorted_chunks(capi, oracle, synth, monkeypatch):
     assert st == 0 and res.ambiguous_sorts == res.n_frontiers
     _check_against(capi, ctx.cycle_fetch(res.n_frontiers), res, want, 1)
     ctx.close()
+
+
+@pytest.mark.parametrize("name", ["C1", "C3"])
+def test_cycle_matches_the_compiled_reference(capi, oracle, synth, name):
+    """The device cycle against the REFERENCE'S OWN code, no oracle in between: FrontierSearch::searchFrom, then
+    FrontierCostsManager::assignCosts({"ArrivalInformation", "EuclideanDistance"}) and FullPathOptimizer::getFilteredFrontiersN,
+    all compiled from the reference sources into oracle/_ref (oracle/Makefile).  Goal points, arrival information, achievability,
+    path lengths, headings, weighted costs and the selection, bit for bit."""
+    from oracle import ref_binding
+    if not ref_binding.available():
+        pytest.skip("oracle/_ref is built where /root/reference exists")
+    ref = ref_binding.Reference()
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    params = synth.apply_overrides(capi.default_params(), ov)
+    ryaw = 0.7
+    rx, ry = meta["robot_x"], meta["robot_y"]
+    q = oracle.orientation_around_z(ryaw)
+    _, _, ref_yaw = ref.plan_euclidean(rx, ry, q, np.zeros((0, 2)), np.zeros(0, np.uint8), np.zeros(0))
+    n, rfr, rcells = ref.search_frontiers(a, meta, params, rx, ry, capacity=1 << 17, cell_capacity=1 << 22)
+    assert n > 50
+    st, rows, loc, glo, closest = ref.assign_costs(a, meta, params, rfr[:, :2], rfr[:, 2], meta["poly"], rx, ry, q, None)
+    assert st == 0
+    ctx = capi.Context(params)
+    try:
+        ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        st, res = ctx.cycle(rx, ry, ref_yaw, meta["poly"], capi.FISHER_OFF)  # the yaw the reference extracts from the quaternion
+        assert st == 0 and res.n_frontiers == n
+        got = ctx.cycle_fetch(n)
+        fr = got["frontiers"]
+        np.testing.assert_array_equal(fr["goal_x"].view(np.uint64), rfr[:, 0].copy().view(np.uint64))
+        np.testing.assert_array_equal(fr["goal_y"].view(np.uint64), rfr[:, 1].copy().view(np.uint64))
+        np.testing.assert_array_equal(fr["size"].astype(np.float64), rfr[:, 2])
+        np.testing.assert_array_equal(got["weighted_cost"].view(np.uint64), rows[:, 0].copy().view(np.uint64))
+        np.testing.assert_array_equal(got["arrival"]["information"].astype(np.float64), rows[:, 4])
+        ach = rows[:, 3].astype(bool)
+        # (the reference's achievable flag after the plan step; the record keeps arrival and plan achievability apart)
+        np.testing.assert_array_equal(np.isfinite(got["path_length_m"]) & (got["path_length_m"] < 1e300), ach)
+        np.testing.assert_array_equal(got["path_length_m"].view(np.uint64), rows[:, 5].copy().view(np.uint64))
+        np.testing.assert_array_equal(got["path_heading"].view(np.uint64), rows[:, 6].copy().view(np.uint64))
+        sel = res.selection
+        np.testing.assert_array_equal(got["sorted"][:sel.n_local].astype(np.int32), loc)
+        np.testing.assert_array_equal(got["sorted"][sel.global_begin:sel.global_begin + sel.n_global].astype(np.int32), glo)
+        assert sel.closest_global == closest
+    finally:
+        ctx.close()
