@@ -4,18 +4,20 @@
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this library.
 // The product (fit-slam_b200/csrc) never links, imports or calls it.
 //
-// *** PARITY: PINNED FOR STAGES S, R AND N, UNPINNED FOR STAGE F. ***
-// Pinned: the reference's own FrontierSearch.cpp, Frontier.cpp, the costmap half of Helpers.cpp and the member functions of
+// *** PARITY: PINNED FOR STAGES S, R, N AND THE CLIENT HALF OF STAGE F; UNPINNED FOR THE ORB-SLAM3 WRAPPER'S HALF (F1, F2). ***
+// Pinned: the reference's own FrontierSearch.cpp, Frontier.cpp, the costmap half of Helpers.cpp, the member functions of
 // CostCalculator.cpp (setArrivalInformationForFrontier, setMaxArrivalInformation, setPlanForFrontierEuclidean,
-// recomputeNormalizationFactors), FrontierCostsManager.cpp (assignCosts, setFrontierBlacklist) and FullPathOptimizer.cpp
-// (getFilteredFrontiersN) compile from where they lie against stand-in ROS headers (oracle/Makefile ->
-// oracle/_ref/libfitslam_ref.so, oracle/ref_shims/), and tests/test_ref_pin.py holds this file to that library bit for bit:
-// rows S1-S6, R1-R6, T4, N1-N3 of SURVEY.md 8a.
+// recomputeNormalizationFactors), FrontierCostsManager.cpp (assignCosts, setFrontierBlacklist), FullPathOptimizer.cpp
+// (getFilteredFrontiersN), FisherInfoManager.cpp (whole) and the Fisher helpers of Helpers.cpp it calls compile from where they lie
+// against stand-in ROS / pcl / Eigen headers (oracle/Makefile -> oracle/_ref/libfitslam_ref.so, oracle/ref_shims/), and
+// tests/test_ref_pin.py holds this file to that library bit for bit: rows S1-S6, R1-R6, T4, N1-N3, F3-F7 of SURVEY.md 8a.  (Eigen
+// is not in the image: the fixed-size float algebra under the Fisher helpers is ref_shims/Eigen/Core's restatement of Eigen 3.4's
+// evaluation order, the same reading as this file's.)
 // Unpinned: the reference ships no golden vectors, known-answer tests or fixtures for this path, and
-// the Fisher translation units (FisherInfoManager.cpp, the second half of Helpers.cpp, the ORB-SLAM3 wrapper) need Eigen, Sophus,
-// PCL and ROS 2 nodes, none of which exist in this image.  Stage F is restated function by function, each block citing the
-// file:line it follows; the only reference test that applies (ORBW/tests/typeConversionsTests.cpp:8-33, SE3 ROS<->ORB round trip)
-// is reproduced against orc_se3_roundtrip() in tests/test_oracle_micro.py, next to the hand-derivable micro-cases of SURVEY.md 8c.
+// the ORB-SLAM3 wrapper (mapPointsVisibleFromPose, the service handler, se3ROSToORB) needs Sophus, ORB_SLAM3's classes and ROS 2
+// nodes, none of which exist in this image.  Those functions are restated, each block citing the file:line it follows; the only
+// reference test that applies (ORBW/tests/typeConversionsTests.cpp:8-33, SE3 ROS<->ORB round trip) is reproduced against
+// orc_se3_roundtrip() in tests/test_oracle_micro.py, next to the hand-derivable micro-cases of SURVEY.md 8c.
 //
 // Path shorthand (all under /root/reference):
 //   DEP/  = dev_ws/src/DEPRECATED/frontier_exploration/frontier_exploration/

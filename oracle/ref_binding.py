@@ -121,3 +121,39 @@ class Reference:
                                        C.c_void_p(out.ctypes.data), C.c_void_p(sel.ctypes.data), C.c_void_p(loc.ctypes.data),
                                        C.c_void_p(glo.ctypes.data))
         return st, out, loc[:sel[0]], glo[:sel[1]], int(sel[2])
+
+    # ---- stage F: the reference's FisherInformationManager, compiled whole
+    def fisher_generate(self, path, params):
+        """generateLookupTable(minX .. maxZ) into `path` (DEP/src/fisher_information/FisherInfoManager.cpp:117-229)."""
+        self.lib.ref_fisher_generate(C.c_char_p(path.encode()), C.c_float(params.lut_min_x), C.c_float(params.lut_max_x),
+                                     C.c_float(params.lut_min_y), C.c_float(params.lut_max_y), C.c_float(params.lut_min_z),
+                                     C.c_float(params.lut_max_z))
+
+    def fisher_manager(self, path):
+        """A FisherInformationManager whose constructor loaded the table at `path` (None if the file is missing)."""
+        self.lib.ref_fisher_create.restype = C.c_void_p
+        h = self.lib.ref_fisher_create(C.c_char_p(path.encode()))
+        return C.c_void_p(h) if h else None
+
+    def fisher_destroy(self, h):
+        self.lib.ref_fisher_destroy(h)
+
+    def fisher_pose(self, h, landmarks, threshold):
+        """isPoseSafe with the landmark service answering `landmarks` ([n, 3], pose frame): (safe, information)."""
+        lm = np.ascontiguousarray(landmarks, dtype=np.float64)
+        info = C.c_float()
+        safe = self.lib.ref_fisher_pose(h, C.c_void_p(lm.ctypes.data), C.c_uint32(len(lm)), C.c_double(threshold), C.byref(info))
+        return bool(safe), info.value
+
+    def fisher_voxel(self, x, y, z):
+        out = (C.c_float * 3)()
+        ok = self.lib.ref_fisher_voxel(C.c_float(x), C.c_float(y), C.c_float(z), out)
+        return bool(ok), (out[0], out[1], out[2])
+
+    def crowd_factor(self, num, s):
+        self.lib.ref_crowd_factor.restype = C.c_float
+        return self.lib.ref_crowd_factor(C.c_int(num), C.c_float(s))
+
+    def information_of_point(self, x, y, z):
+        self.lib.ref_information_of_point.restype = C.c_float
+        return self.lib.ref_information_of_point(C.c_float(x), C.c_float(y), C.c_float(z))

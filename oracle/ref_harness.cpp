@@ -12,6 +12,7 @@
 #include <frontier_exploration/CostCalculator.hpp>
 #include <frontier_exploration/FrontierCostsManager.hpp>
 #include <frontier_exploration/FullPathOptimizer.hpp>
+#include <frontier_exploration/fisher_information/FisherInfoManager.hpp>
 #include <frontier_exploration/FrontierSearch.hpp>
 #include <frontier_exploration/Helpers.hpp>
 
@@ -25,6 +26,10 @@ Costmap2D make_map(const uint8_t *cells, uint32_t W, uint32_t H, double res, dou
   return m;
 }
 }  // namespace
+
+// where FisherInfoManager.cpp reads / writes its lookup table (ref_shims/frontier_exploration/util/rosVisualizer.hpp)
+static std::string g_lookup_path;
+std::string fitslam_ref_lookup_path() { return g_lookup_path; }
 
 extern "C" {
 
@@ -218,6 +223,57 @@ int ref_assign_costs(const uint8_t *cells, uint32_t W, uint32_t H, double res, d
   for (size_t i = 0; i < sorted.local_frontiers.size(); ++i) local_idx[i] = index_of(sorted.local_frontiers[i]);
   for (size_t i = 0; i < sorted.global_frontiers.size(); ++i) global_idx[i] = index_of(sorted.global_frontiers[i]);
   return 0;
+}
+
+// ---- stage F: the reference's FisherInformationManager (DEP/src/fisher_information/FisherInfoManager.cpp, whole) --------------
+// generateLookupTable into the file `path` (FisherInfoManager.cpp:117-229 + the Fisher helpers of DEP/src/Helpers.cpp)
+void ref_fisher_generate(const char *path, float min_x, float max_x, float min_y, float max_y, float min_z, float max_z) {
+  g_lookup_path = path;
+  frontier_exploration::FisherInformationManager m;
+  m.generateLookupTable(min_x, max_x, min_y, max_y, min_z, max_z);
+}
+// a manager that loads the table at `path` (the constructor's loadLookupTable, :231-262); 0 if the file cannot be read
+void *ref_fisher_create(const char *path) {
+  g_lookup_path = path;
+  try {
+    return new frontier_exploration::FisherInformationManager(rclcpp::Node::make_shared("ref"));
+  } catch (const std::runtime_error &) {
+    return nullptr;
+  }
+}
+void ref_fisher_destroy(void *h) { delete static_cast<frontier_exploration::FisherInformationManager *>(h); }
+// isPoseSafe (:39-115) with the service answering `n` landmarks (pose frame, float64 as on the wire).  Returns safe.
+int ref_fisher_pose(void *h, const double *landmarks, uint32_t n, double threshold, float *information) {
+  using Srv = slam_msgs::srv::GetLandmarksInView;
+  parameterInstance.set("fisherInformation/fisher_information_threshold", threshold);
+  rclcpp::Client<Srv>::handler() = [landmarks, n](const Srv::Request &, Srv::Response &resp) {
+    resp.map_points.resize(n);
+    for (uint32_t i = 0; i < n; ++i) {
+      resp.map_points[i].position.x = landmarks[3 * i];
+      resp.map_points[i].position.y = landmarks[3 * i + 1];
+      resp.map_points[i].position.z = landmarks[3 * i + 2];
+    }
+  };
+  geometry_msgs::msg::Pose pose;
+  pose.orientation.w = 1.0;
+  float info = 0.0f;
+  const bool safe = static_cast<frontier_exploration::FisherInformationManager *>(h)->isPoseSafe(pose, true, info);
+  *information = info;
+  return safe ? 1 : 0;
+}
+// getVoxelCoordinate and getFactorFromNum (FisherInfoManager.hpp:102-123)
+int ref_fisher_voxel(float x, float y, float z, float *out3) {
+  frontier_exploration::FisherInformationManager m;
+  return m.getVoxelCoordinate(out3[0], out3[1], out3[2], x, y, z) ? 1 : 0;
+}
+float ref_crowd_factor(int num, float s) {
+  frontier_exploration::FisherInformationManager m;
+  return m.getFactorFromNum(num, s);
+}
+// computeInformationOfPointLocal(p, I) (DEP/src/Helpers.cpp:440-449)
+float ref_information_of_point(float x, float y, float z) {
+  Eigen::Vector3f p(x, y, z);
+  return frontier_exploration::computeInformationOfPointLocal(p, Eigen::Matrix3f::Identity());
 }
 
 }  // extern "C"

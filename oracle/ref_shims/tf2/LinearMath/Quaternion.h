@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <cmath>
+#include "tf2/LinearMath/Vector3.h"
 namespace tf2 {
 class Quaternion {
 public:

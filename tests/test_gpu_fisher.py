@@ -43,6 +43,11 @@ def test_lookup_file_roundtrip(capi, oracle, tmp_path):
     c.fisher_generate_lookup(p_gpu)
     assert oracle.fisher_generate(p_orc) == 0
     assert open(p_gpu, "rb").read() == open(p_orc, "rb").read()  # same 16-byte records in the same order
+    from oracle import ref_binding
+    if ref_binding.available():  # ... and the file the reference's own generateLookupTable writes (oracle/_ref)
+        p_ref = str(tmp_path / "ref.dat")
+        ref_binding.Reference().fisher_generate(p_ref, oracle.params)
+        assert open(p_gpu, "rb").read() == open(p_ref, "rb").read()
     c2 = capi.Context()
     c2.fisher_load_lookup(p_orc)
     a, oa = c.fisher_lookup()

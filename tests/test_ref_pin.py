@@ -6,7 +6,8 @@ sizes, orders, ray counts, selections.
 Rows pinned: S1-S6 (searchFrom, nearestFreeCell, isNewFrontierCell, buildNewFrontier, centroid + median sort
 with glibc atan2, getAllFrontiers), R1-R6 (setArrivalInformationForFrontier, getTracedCells, bresenham2D,
 isRobotFootprintInLethal, setMaxArrivalInformation, recomputeNormalizationFactors), T4 (RayTracedCells), N1-N3 (assignCosts with
-the U1 block, setPlanForFrontierEuclidean, getFilteredFrontiersN)."""
+the U1 block, setPlanForFrontierEuclidean, getFilteredFrontiersN), F3-F7 (the Fisher helpers, generateLookupTable / loadLookupTable,
+getVoxelCoordinate, getInformationFromLookup with the crowding factor, isPoseSafe: FisherInfoManager.cpp compiled whole)."""
 import math
 
 import numpy as np
@@ -317,3 +318,72 @@ def test_reference_assign_costs_few_frontiers_and_errors(oracle, ref, synth, cap
     # no frontiers: assignCosts returns false (FrontierCostsManager.cpp:55-59)
     st, rows, loc, glo, closest = ref.assign_costs(a, meta, oracle.params, np.zeros((0, 2)), np.zeros(0), meta["poly"], rx, ry, q, None)
     assert st == 1
+
+
+# ---- stage F against the reference's own FisherInformationManager (compiled whole) and its Fisher helpers ---------------------------
+# (the fixed-size float algebra underneath is oracle/ref_shims/Eigen/Core's restatement of Eigen 3.4's evaluation order: Eigen
+# itself is not in the image.  Everything above it -- the table's loops, keys, de-duplication and file format, getVoxelCoordinate,
+# the crowding factor, the order and type of the accumulation in isPoseSafe -- is the reference's code.)
+def test_reference_fisher_lookup_table_file_is_byte_identical(oracle, ref, tmp_path):
+    p_ref, p_orc = str(tmp_path / "ref.dat"), str(tmp_path / "orc.dat")
+    ref.fisher_generate(p_ref, oracle.params)
+    assert oracle.fisher_generate(p_orc) == 0
+    b_ref, b_orc = open(p_ref, "rb").read(), open(p_orc, "rb").read()
+    assert len(b_ref) == len(b_orc) > 16 * 500_000  # 16-byte records: 3 float keys + the value
+    assert b_ref == b_orc
+    # loadLookupTable: both read the same number of distinct keys (the trailing (0, 0, 0) record overwrites the one generated)
+    h = ref.fisher_manager(p_orc)
+    assert h is not None
+    ref.fisher_destroy(h)
+    assert ref.fisher_manager(str(tmp_path / "missing.dat")) is None  # "Cannot load lookup table. Does it exist in the path?"
+
+
+def test_reference_fisher_helpers_known_answers(oracle, ref):
+    rng = np.random.default_rng(4)
+    for x, y, z in [(0.3, 0.0, 0.0), (0.0, 0.3, 0.0), (2.1, -0.9, 0.6), (20.7, 14.4, -14.7)] + [tuple(v) for v in rng.uniform(-15, 21, (200, 3))]:
+        a, b = ref.information_of_point(x, y, z), oracle.information_of_point_local(x, y, z)
+        assert np.float32(a).view(np.uint32) == np.float32(b).view(np.uint32), (x, y, z, a, b)
+    assert abs(ref.information_of_point(0.3, 0.0, 0.0) - (2 + 2 / 0.09)) < 1e-3  # trace = 2 + 2 / |p|^2
+    for x, y, z in [tuple(v) for v in rng.uniform(-16, 22, (500, 3))] + [(0.15, -0.15, 0.45), (0.149999, 0.150001, -0.45)]:
+        ok, v = ref.fisher_voxel(x, y, z)
+        w = oracle.voxel_coordinate(x, y, z)
+        assert ok and np.array_equal(np.array(v, np.float32).view(np.uint32), np.asarray(w, np.float32).view(np.uint32)), (x, y, z)
+    for num in list(range(1, 40)) + [100, 511, 512]:
+        assert np.float32(ref.crowd_factor(num, 0.8)).view(np.uint32) == np.float32(oracle.crowd_factor(num)).view(np.uint32)
+
+
+def test_reference_is_pose_safe_equals_oracle(oracle, ref, synth, capi, tmp_path):
+    path = str(tmp_path / "lut.dat")
+    assert oracle.fisher_generate(path) == 0
+    h = ref.fisher_manager(path)
+    assert h is not None
+    try:
+        rng = np.random.default_rng(12)
+        a, meta, pts, ov = synth.make_config("C1")
+        box = synth.explored_bbox(a, meta)
+        n_safe = 0
+        for t in range(24):
+            pose = np.zeros(1, dtype=capi.POSE_DTYPE)
+            pose["x"], pose["y"], pose["z"] = rng.uniform(box[0], box[2]), rng.uniform(box[1], box[3]), 0.3
+            yaw = rng.uniform(-np.pi, np.pi)
+            pose["qz"], pose["qw"] = np.sin(yaw / 2), np.cos(yaw / 2)
+            st, winfo, wsafe, wvis, wused = oracle.fisher_poses(pts, pose)
+            lm = oracle.landmarks_in_view(pts, pose)  # the service's response for this pose (float32 widened on the wire)
+            assert st == 0 and len(lm) == wvis[0]
+            safe, info = ref.fisher_pose(h, lm.astype(np.float64), oracle.params.fisher_information_threshold)
+            # the same float accumulation in the same order: bit for bit
+            assert np.float32(info).view(np.uint32) == winfo[:1].view(np.uint32)[0], (t, info, winfo[0])
+            assert safe == bool(wsafe[0])
+            n_safe += safe
+        # a dense clump: hundreds of landmarks per voxel (crowding factors), and the empty response
+        clump = (rng.normal(0, 0.05, (3000, 3)) + np.array([3.0, 0.2, 0.1])).astype(np.float32)
+        pose = np.zeros(1, dtype=capi.POSE_DTYPE)
+        pose["qw"] = 1.0
+        st, winfo, wsafe, wvis, wused = oracle.fisher_poses(clump, pose)
+        lm = oracle.landmarks_in_view(clump, pose)
+        safe, info = ref.fisher_pose(h, lm.astype(np.float64), oracle.params.fisher_information_threshold)
+        assert len(lm) > 2000 and np.float32(info).view(np.uint32) == winfo[:1].view(np.uint32)[0] and safe == bool(wsafe[0])
+        safe, info = ref.fisher_pose(h, np.zeros((0, 3)), oracle.params.fisher_information_threshold)
+        assert not safe and info == 0.0
+    finally:
+        ref.fisher_destroy(h)
