@@ -187,8 +187,12 @@ void fitslam_default_sensor_params(fitslam_sensor_params *p) {
 }
 
 fitslam_status fitslam_sensor_mark_rays(fitslam_ctx *c, const int8_t *latest, int8_t *explored, uint32_t size_x, uint32_t size_y,
-                                        double resolution, double origin_x, double origin_y, double robot_x, double robot_y,
+                                        double resolution_in, double origin_x, double origin_y, double robot_x, double robot_y,
                                         double base_yaw, const fitslam_sensor_params *p, uint32_t *n_rays) {
+  // `const double res = latest_map_->info.resolution;` (SensorSimulator.cpp:217): nav_msgs/MapMetaData.resolution is a float32,
+  // so the reference steps with 0.05f widened, not with 0.05 (a cell's difference here and there; found against the reference's
+  // own markRay, tests/test_ref_pin.py)
+  const double resolution = static_cast<double>(static_cast<float>(resolution_in));
   if (!c || !latest || !explored || size_x == 0 || size_y == 0 || !(resolution > 0.0))
     return fail(c, FITSLAM_E_INVALID, "sensor_mark_rays: bad argument");
   if ((uint64_t)size_x * size_y >= (1ull << 31)) return fail(c, FITSLAM_E_INVALID, "sensor_mark_rays: more than 2^31 cells");

@@ -247,7 +247,8 @@ FITSLAM_API fitslam_status fitslam_mark_lethal(fitslam_ctx *ctx, const fitslam_l
  * a = min_angle; a <= max_angle; a += angular_resolution, a ray from the robot position along base_yaw + a in steps
  * of `resolution` up to max_range copies latest[idx] into explored[idx] cell by cell and stops behind the first cell
  * whose value is > 80 or at the map border.  latest / explored: size_x * size_y int8 (nav_msgs/OccupancyGrid data),
- * both host or both device; explored is updated in place.  n_rays (optional) = rays cast. */
+ * both host or both device; explored is updated in place.  n_rays (optional) = rays cast.  `resolution` is narrowed to float32
+ * first: that is what the message carries (nav_msgs/MapMetaData.resolution) and what the reference widens again (:217). */
 typedef struct fitslam_sensor_params {
   double sensor_min_angle;   /* -pi/4 (RE/src/Parameters.cpp:233-234) */
   double sensor_max_angle;   /*  pi/4 (:236-237) */

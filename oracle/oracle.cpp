@@ -10,7 +10,9 @@
 // recomputeNormalizationFactors), FrontierCostsManager.cpp (assignCosts, setFrontierBlacklist), FullPathOptimizer.cpp
 // (getFilteredFrontiersN), FisherInfoManager.cpp (whole) and the Fisher helpers of Helpers.cpp it calls compile from where they lie
 // against stand-in ROS / pcl / Eigen headers (oracle/Makefile -> oracle/_ref/libfitslam_ref.so, oracle/ref_shims/), and
-// tests/test_ref_pin.py holds this file to that library bit for bit: rows S1-S6, R1-R6, T4, N1-N3, F3-F7 of SURVEY.md 8a.  (Eigen
+// tests/test_ref_pin.py holds this file to that library bit for bit: rows S1-S6, R1-R6, T4, N1-N3, F3-F7 of SURVEY.md 8a; a second
+// library (oracle/ref_harness_re.cpp) does the same for FrontierRoadMap::isConnectable and SensorSimulator::markRay of the
+// roadmap-explorer package (rows 8f-2, 8f-4).  (Eigen
 // is not in the image: the fixed-size float algebra under the Fisher helpers is ref_shims/Eigen/Core's restatement of Eigen 3.4's
 // evaluation order, the same reading as this file's.)
 // Unpinned: the reference ships no golden vectors, known-answer tests or fixtures for this path, and
@@ -1377,7 +1379,8 @@ int orc_mark_lethal(uint8_t *map, uint32_t W, uint32_t H, double res, double ox,
 int orc_sensor_mark_rays(const int8_t *latest, int8_t *explored, uint32_t size_x, uint32_t size_y, double resolution, double origin_x,
                          double origin_y, double robot_x, double robot_y, double base_yaw, const fitslam_sensor_params *p,
                          uint32_t *n_rays) {
-  const double res = resolution;
+  // `const double res = latest_map_->info.resolution;` (:217): nav_msgs/MapMetaData.resolution is a float32
+  const double res = static_cast<double>(static_cast<float>(resolution));
   const int w = static_cast<int>(size_x);
   const int h = static_cast<int>(size_y);
   uint32_t cast = 0;

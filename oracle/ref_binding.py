@@ -9,10 +9,44 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_ref", "libfitslam_ref.so")
+LIB_PATH_RE = os.path.join(_HERE, "_ref", "libfitslam_ref_re.so")  # the roadmap-explorer package's own copies (rows 8f-2, 8f-4)
 
 
 def available():
     return os.path.exists(LIB_PATH)
+
+
+def available_re():
+    return os.path.exists(LIB_PATH_RE)
+
+
+class ReferenceRE:
+    """oracle/_ref/libfitslam_ref_re.so: FrontierRoadMap::isConnectable and SensorSimulator::markRay of the roadmap-explorer
+    package, compiled from the reference (oracle/ref_harness_re.cpp)."""
+
+    def __init__(self):
+        self.lib = C.CDLL(LIB_PATH_RE)
+
+    def connectable(self, a, meta, segments, radius):
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        H, W = a.shape
+        seg = np.ascontiguousarray(segments, np.float64).reshape(-1, 4)
+        out = np.zeros(len(seg), np.uint8)
+        self.lib.ref_re_connectable(C.c_void_p(a.ctypes.data), C.c_uint32(W), C.c_uint32(H), C.c_double(meta["res"]), C.c_double(meta["ox"]),
+                                    C.c_double(meta["oy"]), C.c_double(radius), C.c_void_p(seg.ctypes.data), C.c_uint32(len(seg)),
+                                    C.c_void_p(out.ctypes.data))
+        return out
+
+    def mark_rays(self, latest, explored, res, ox, oy, px, py, yaw, params):
+        lat = np.ascontiguousarray(latest, np.int8)
+        exp = np.array(explored, np.int8, copy=True, order="C")
+        H, W = lat.shape
+        self.lib.ref_re_mark_rays.restype = C.c_uint32
+        n = self.lib.ref_re_mark_rays(C.c_void_p(lat.ctypes.data), C.c_void_p(exp.ctypes.data), C.c_uint32(W), C.c_uint32(H), C.c_double(res),
+                                      C.c_double(ox), C.c_double(oy), C.c_double(px), C.c_double(py), C.c_double(yaw),
+                                      C.c_double(params.sensor_min_angle), C.c_double(params.sensor_max_angle),
+                                      C.c_double(params.angular_resolution), C.c_double(params.sensor_max_range))
+        return exp, n
 
 
 class Reference:

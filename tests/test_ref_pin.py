@@ -7,7 +7,9 @@ Rows pinned: S1-S6 (searchFrom, nearestFreeCell, isNewFrontierCel
 with glibc atan2, getAllFrontiers), R1-R6 (setArrivalInformationForFrontier, getTracedCells, bresenham2D,
 isRobotFootprintInLethal, setMaxArrivalInformation, recomputeNormalizationFactors), T4 (RayTracedCells), N1-N3 (assignCosts with
 the U1 block, setPlanForFrontierEuclidean, getFilteredFrontiersN), F3-F7 (the Fisher helpers, generateLookupTable / loadLookupTable,
-getVoxelCoordinate, getInformationFromLookup with the crowding factor, isPoseSafe: FisherInfoManager.cpp compiled whole)."""
+getVoxelCoordinate, getInformationFromLookup with the crowding factor, isPoseSafe: FisherInfoManager.cpp compiled whole); next rows
+8f-2 (FrontierRoadMap::isConnectable) and 8f-4 (SensorSimulator::markRay) against the roadmap-explorer package's own code in
+oracle/_ref/libfitslam_ref_re.so."""
 import math
 
 import numpy as np
@@ -387,3 +389,48 @@ def test_reference_is_pose_safe_equals_oracle(oracle, ref, synth, capi, tmp_path
         assert not safe and info == 0.0
     finally:
         ref.fisher_destroy(h)
+
+
+# ---- next rows 8f-2 and 8f-4 against the roadmap-explorer package's own code (oracle/_ref/libfitslam_ref_re.so) ---------------------
+@pytest.mark.skipif(not ref_binding.available_re(), reason="oracle/_ref is built where /root/reference exists")
+def test_reference_roadmap_is_connectable(oracle, synth):
+    """FrontierRoadMap::isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-692 over RE/src/Helpers.cpp getTracedCells),
+    compiled from the reference, against the oracle: 3 000 node pairs x 3 radii."""
+    re = ref_binding.ReferenceRE()
+    a, meta = synth.make_costmap(300, 300, seed=13, n_disc=6, r_lo=20, r_hi=50, n_holes=10, inflation=2)
+    rng = np.random.default_rng(5)
+    H, W = a.shape
+    n = 3000
+    x1, y1 = meta["ox"] + rng.uniform(1, W - 1, n) * meta["res"], meta["oy"] + rng.uniform(1, H - 1, n) * meta["res"]
+    d, th = rng.uniform(0.0, 5.0, n), rng.uniform(-np.pi, np.pi, n)
+    x2 = np.clip(x1 + d * np.cos(th), meta["ox"] + meta["res"], meta["ox"] + (W - 1) * meta["res"])
+    y2 = np.clip(y1 + d * np.sin(th), meta["oy"] + meta["res"], meta["oy"] + (H - 1) * meta["res"])
+    seg = np.stack([x1, y1, x2, y2], axis=1)
+    seg[:5, 2:] = seg[:5, :2]  # a node paired with itself
+    for radius in (2.6, 1.0, 4.0):
+        want = re.connectable(a, meta, seg, radius)
+        got, _ = oracle.roadmap_connectable(a, meta, seg, radius)
+        np.testing.assert_array_equal(got, want)
+        assert 0 < want.sum() < n
+
+
+@pytest.mark.skipif(not ref_binding.available_re(), reason="oracle/_ref is built where /root/reference exists")
+def test_reference_sensor_simulator_rays(oracle, capi):
+    """SensorSimulator::markRay (RE/src/SensorSimulator.cpp:212-246, compiled from the reference) under the fan loop of
+    timerCallback, against the oracle: explored grids equal cell for cell, same number of rays."""
+    re = ref_binding.ReferenceRE()
+    rng = np.random.default_rng(17)
+    p = capi.default_sensor_params()
+    for H, W, res in ((200, 260, 0.05), (97, 131, 0.1), (64, 64, 1.0 / 16)):
+        latest = rng.choice(np.array([0, 100, -1, 81, 80], np.int8), size=(H, W), p=[0.8, 0.05, 0.1, 0.02, 0.03])
+        ox, oy = -W * res / 2 + 0.0071, -H * res / 2 - 0.0033
+        explored_o = np.full((H, W), -1, np.int8)
+        explored_r = explored_o.copy()
+        for t in range(12):
+            px, py = rng.uniform(ox - 0.5, ox + W * res + 0.5), rng.uniform(oy - 0.5, oy + H * res + 0.5)  # sometimes off the map
+            yaw = rng.uniform(-7, 7)
+            explored_o, n_o = oracle.sensor_mark_rays(latest, explored_o, res, ox, oy, px, py, yaw, p)
+            explored_r, n_r = re.mark_rays(latest, explored_r, res, ox, oy, px, py, yaw, p)
+            assert n_o == n_r == 121
+            np.testing.assert_array_equal(explored_o, explored_r)
+        assert (explored_o != -1).sum() > 100
