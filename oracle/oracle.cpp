@@ -12,7 +12,8 @@
 // against stand-in ROS / pcl / Eigen headers (oracle/Makefile -> oracle/_ref/libfitslam_ref.so, oracle/ref_shims/), and
 // tests/test_ref_pin.py holds this file to that library bit for bit: rows S1-S6, R1-R6, T4, N1-N3, F3-F7 of SURVEY.md 8a; a second
 // library (oracle/ref_harness_re.cpp) does the same for FrontierRoadMap::isConnectable and SensorSimulator::markRay of the
-// roadmap-explorer package (rows 8f-2, 8f-4).  (Eigen
+// roadmap-explorer package (rows 8f-2, 8f-4); lethal_marker.cpp (rays, circle, triangle, addNewMarkedArea / FOV, updateCosts) and the
+// threshold node's callback (row 8f-3) are in the first library.  (Eigen
 // is not in the image: the fixed-size float algebra under the Fisher helpers is ref_shims/Eigen/Core's restatement of Eigen 3.4's
 // evaluation order, the same reading as this file's.)
 // Unpinned: the reference ships no golden vectors, known-answer tests or fixtures for this path, and

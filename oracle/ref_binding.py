@@ -191,3 +191,17 @@ class Reference:
     def information_of_point(self, x, y, z):
         self.lib.ref_information_of_point.restype = C.c_float
         return self.lib.ref_information_of_point(C.c_float(x), C.c_float(y), C.c_float(z))
+
+    def mark_lethal(self, a, meta, areas):
+        """LethalMarker (the reference's own lethal_marker.cpp) on a copy of the costmap; areas: (wx, wy, extent, yaw, kind)."""
+        a, m = self._map(np.array(a, np.uint8, copy=True), meta)
+        ar = np.ascontiguousarray(np.asarray(areas, np.float64).reshape(-1, 5))
+        n = self.lib.ref_mark_lethal(*m, C.c_void_p(ar.ctypes.data), C.c_uint32(len(ar)))
+        return a, n
+
+    def threshold_occupancy(self, grid, lethal_threshold):
+        """TraversabilityThresholdNode::callback (the reference's own text) on an int8 grid: the published data."""
+        g = np.ascontiguousarray(grid, np.int8)
+        out = np.zeros(g.shape, np.int8)
+        self.lib.ref_threshold_occupancy(C.c_void_p(g.ctypes.data), C.c_uint64(g.size), C.c_int(lethal_threshold), C.c_void_p(out.ctypes.data))
+        return out

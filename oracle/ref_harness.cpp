@@ -15,6 +15,8 @@
 #include <frontier_exploration/fisher_information/FisherInfoManager.hpp>
 #include <frontier_exploration/FrontierSearch.hpp>
 #include <frontier_exploration/Helpers.hpp>
+#include <frontier_exploration/nav2_plugins/lethal_marker.hpp>
+#include <nav_msgs/msg/occupancy_grid.hpp>
 
 using frontier_exploration::FrontierSearch;
 using nav2_costmap_2d::Costmap2D;
@@ -30,6 +32,22 @@ Costmap2D make_map(const uint8_t *cells, uint32_t W, uint32_t H, double res, dou
 // where FisherInfoManager.cpp reads / writes its lookup table (ref_shims/frontier_exploration/util/rosVisualizer.hpp)
 static std::string g_lookup_path;
 std::string fitslam_ref_lookup_path() { return g_lookup_path; }
+
+// TraversabilityThresholdNode::callback (ORB-SLAM3-ROS2-Docker/traversability_mapping/.../threshold_occupancy.cpp:24-49): the
+// member function's own text, cut by oracle/Makefile into _ref/threshold_occupancy_callback.inc, inside a class that has the two
+// members it names: the threshold and a publisher that keeps the message.
+namespace threshold_node {
+struct CapturePublisher {
+  nav_msgs::msg::OccupancyGrid last;
+  void publish(const nav_msgs::msg::OccupancyGrid &m) { last = m; }
+};
+class TraversabilityThresholdNode {
+public:
+#include "_ref/threshold_occupancy_callback.inc"
+  CapturePublisher capture_, *publisher_ = &capture_;
+  int lethal_threshold_ = 85;
+};
+}  // namespace threshold_node
 
 extern "C" {
 
@@ -274,6 +292,35 @@ float ref_crowd_factor(int num, float s) {
 float ref_information_of_point(float x, float y, float z) {
   Eigen::Vector3f p(x, y, z);
   return frontier_exploration::computeInformationOfPointLocal(p, Eigen::Matrix3f::Identity());
+}
+
+// LethalMarker::addNewMarkedArea / addNewMarkedAreaFOV per area, then one updateCosts over the whole map (DEP/src/nav2_plugins/
+// lethal_marker.cpp:218-236, 305-327).  areas: n * 5 doubles (wx, wy, extent, yaw, kind); cells is stamped in place.
+// Returns the number of areas that were on the map (numAdditions_).
+int ref_mark_lethal(uint8_t *cells, uint32_t W, uint32_t H, double res, double ox, double oy, const double *areas, uint32_t n) {
+  Costmap2D map = make_map(cells, W, H, res, ox, oy);
+  nav2_costmap_2d::LayeredCostmap layered(&map);
+  frontier_exploration::LethalMarker layer(&layered);
+  for (uint32_t a = 0; a < n; ++a) {
+    const double *r = areas + 5 * a;
+    if (r[4] == 0.0)
+      layer.addNewMarkedArea(r[0], r[1], r[2]);
+    else
+      layer.addNewMarkedAreaFOV(r[0], r[1], r[3], r[2]);
+  }
+  layer.updateCosts(map, 0, 0, (int)W, (int)H);
+  std::memcpy(cells, map.getCharMap(), (size_t)W * H);
+  return layer.additions();
+}
+
+// The threshold node on n int8 cells: out = the published message's data.
+void ref_threshold_occupancy(const int8_t *data, uint64_t n, int lethal_threshold, int8_t *out) {
+  threshold_node::TraversabilityThresholdNode node;
+  node.lethal_threshold_ = lethal_threshold;
+  auto msg = std::make_shared<nav_msgs::msg::OccupancyGrid>();
+  msg->data.assign(data, data + n);
+  node.callback(msg);
+  std::memcpy(out, node.capture_.last.data.data(), node.capture_.last.data.size());
 }
 
 }  // extern "C"

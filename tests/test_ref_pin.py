@@ -7,7 +7,9 @@ Rows pinned: S1-S6 (searchFrom, nearestFreeCell, isNewFrontierCel
 with glibc atan2, getAllFrontiers), R1-R6 (setArrivalInformationForFrontier, getTracedCells, bresenham2D,
 isRobotFootprintInLethal, setMaxArrivalInformation, recomputeNormalizationFactors), T4 (RayTracedCells), N1-N3 (assignCosts with
 the U1 block, setPlanForFrontierEuclidean, getFilteredFrontiersN), F3-F7 (the Fisher helpers, generateLookupTable / loadLookupTable,
-getVoxelCoordinate, getInformationFromLookup with the crowding factor, isPoseSafe: FisherInfoManager.cpp compiled whole); next rows
+getVoxelCoordinate, getInformationFromLookup with the crowding factor, isPoseSafe: FisherInfoManager.cpp compiled whole); next row
+8f-3 (LethalMarker: the ray / circle / triangle functions, addNewMarkedArea, addNewMarkedAreaFOV, updateCosts; the threshold node's
+callback) and next rows
 8f-2 (FrontierRoadMap::isConnectable) and 8f-4 (SensorSimulator::markRay) against the roadmap-explorer package's own code in
 oracle/_ref/libfitslam_ref_re.so."""
 import math
@@ -392,6 +394,49 @@ def test_reference_is_pose_safe_equals_oracle(oracle, ref, synth, capi, tmp_path
 
 
 # ---- next rows 8f-2 and 8f-4 against the roadmap-explorer package's own code (oracle/_ref/libfitslam_ref_re.so) ---------------------
+@pytest.mark.parametrize("shape,res,ox,oy", [((120, 160), 0.05, -3.0, -2.0), ((37, 300), 0.1, 0.0, 0.0), ((513, 257), 0.03, -7.7, 1.3)])
+def test_reference_lethal_marker(oracle, ref, shape, res, ox, oy):
+    """nav2_plugins/lethal_marker.cpp compiled from where it lies: the stamped map and the number of cached areas."""
+    rng = np.random.default_rng(shape[0])
+    H, W = shape
+    meta = dict(res=res, ox=ox, oy=oy)
+    a = rng.integers(0, 253, size=shape, dtype=np.uint8)
+    areas = []
+    for _ in range(40):
+        wx = rng.uniform(ox - 0.5, ox + W * res + 0.5)  # some centres off the map: skipped, not counted
+        wy = rng.uniform(oy - 0.5, oy + H * res + 0.5)
+        kind = int(rng.integers(0, 2))
+        extent = float(rng.choice([0.0, res * 0.4, 0.33, 1.0, 2.75, 40.0]))  # 40 m: every ray end clamped to the border
+        areas.append((wx, wy, extent, float(rng.uniform(-7, 7)), kind))
+    areas += [(ox, oy, 1.0, 0.3, 0), (ox + W * res - 1e-9, oy + H * res - 1e-9, 1.0, -2.0, 1), (ox + W * res, oy, 1.0, 0.0, 0)]
+    for sub in (areas, areas[:1], areas[5:9], []):
+        want, n_want = ref.mark_lethal(a, meta, sub)
+        got, n_got = oracle.mark_lethal(a, meta, sub)
+        assert n_got == n_want
+        assert np.array_equal(got, want)
+    assert n_want == 0 and np.array_equal(want, a)
+    want, n_want = ref.mark_lethal(a, meta, areas)
+    assert 0 < n_want < len(areas) and (want != a).sum() > 100
+
+
+def test_reference_threshold_node(oracle, ref, capi):
+    """The threshold half of the ingest (threshold_occupancy.cpp:24-49, the reference's own text): every int8 value at the node's
+    default threshold and at others.  The oracle composes it with the static layer's translation; with the trinary static layer
+    {-1, 0, 100} -> {255, 0, 254} is one to one, so equal costs mean equal thresholded grids.  (The static layer itself is a Nav2
+    binary package absent from the reference tree: that half stays a restatement.)"""
+    g = np.concatenate([np.arange(-128, 128, dtype=np.int16).astype(np.int8), np.random.default_rng(3).integers(-128, 128, 5000).astype(np.int8)])
+    for thr in (85, 0, 1, 50, 100, 101, 127):
+        p = capi.default_occupancy_params()
+        p.lethal_obstacle_threshold = thr
+        q = capi.default_occupancy_params()
+        q.lethal_obstacle_threshold = -1  # no threshold node: the static layer alone
+        t = ref.threshold_occupancy(g, thr)
+        assert set(np.unique(t).tolist()) <= {-1, 0, 100}
+        assert np.array_equal(oracle.occupancy_to_cost(g, p), oracle.occupancy_to_cost(t, q))
+    t = ref.threshold_occupancy(np.array([-1, 0, 84, 85, 100, -2, -128, 127], np.int8), 85)
+    assert t.tolist() == [-1, 0, 0, 100, 100, 0, 0, 100]
+
+
 @pytest.mark.skipif(not ref_binding.available_re(), reason="oracle/_ref is built where /root/reference exists")
 def test_reference_roadmap_is_connectable(oracle, synth):
     """FrontierRoadMap::isConnectable (RE/src/planners/FrontierRoadmap.cpp:671-692 over RE/src/Helpers.cpp getTracedCells),
