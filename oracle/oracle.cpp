@@ -4,7 +4,8 @@
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this library.
 // The product (fit-slam_b200/csrc) never links, imports or calls it.
 //
-// *** PARITY: PINNED FOR STAGES S, R, N AND THE CLIENT HALF OF STAGE F; UNPINNED FOR THE ORB-SLAM3 WRAPPER'S HALF (F1, F2). ***
+// *** PARITY: PINNED FOR STAGES S, R, N AND THE CLIENT HALF OF STAGE F; FOR THE ORB-SLAM3 WRAPPER'S HALF (F1, F2, KEYFRAME MODE) THE
+// CONTROL FLOW IS PINNED, THE ARITHMETIC INSIDE SOPHUS / EIGEN'S AFFINE TRANSFORMS IS NOT. ***
 // Pinned: the reference's own FrontierSearch.cpp, Frontier.cpp, the costmap half of Helpers.cpp, the member functions of
 // CostCalculator.cpp (setArrivalInformationForFrontier, setMaxArrivalInformation, setPlanForFrontierEuclidean,
 // recomputeNormalizationFactors), FrontierCostsManager.cpp (assignCosts, setFrontierBlacklist), FullPathOptimizer.cpp
@@ -16,10 +17,13 @@
 // threshold node's callback (row 8f-3) are in the first library.  (Eigen
 // is not in the image: the fixed-size float algebra under the Fisher helpers is ref_shims/Eigen/Core's restatement of Eigen 3.4's
 // evaluation order, the same reading as this file's.)
-// Unpinned: the reference ships no golden vectors, known-answer tests or fixtures for this path, and
-// the ORB-SLAM3 wrapper (mapPointsVisibleFromPose, the service handler, se3ROSToORB) needs Sophus, ORB_SLAM3's classes and ROS 2
-// nodes, none of which exist in this image.  Those functions are restated, each block citing the file:line it follows; the only
-// reference test that applies (ORBW/tests/typeConversionsTests.cpp:8-33, SE3 ROS<->ORB round trip) is reproduced against
+// The wrapper's half: the reference ships no golden vectors, known-answer tests or fixtures for this path (SURVEY.md section 4 /
+// 8c), and the ORB-SLAM3 wrapper (mapPointsVisibleFromPose, the service handler, se3ROSToORB) needs Sophus, ORB_SLAM3's classes
+// and ROS 2 nodes, none of which exist in this image.  A third library (oracle/ref_harness_orbw.cpp ->
+// oracle/_ref/libfitslam_ref_orbw.so) compiles those function bodies against stand-in declarations (oracle/ref_shims_orbw/: an
+// atlas the harness fills, Sophus::SE3f as (R, t)) and tests/test_ref_pin.py holds landmarksInView / landmarksInViewKeyframes to
+// it coordinate for coordinate: the control flow and the order of operations are the reference's, Sophus's quaternion storage
+// and Eigen's Affine rotation() are not modelled.  The only reference test that applies (ORBW/tests/typeConversionsTests.cpp:8-33, SE3 ROS<->ORB round trip) is reproduced against
 // orc_se3_roundtrip() in tests/test_oracle_micro.py, next to the hand-derivable micro-cases of SURVEY.md 8c.
 //
 // Path shorthand (all under /root/reference):

@@ -10,6 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_ref", "libfitslam_ref.so")
 LIB_PATH_RE = os.path.join(_HERE, "_ref", "libfitslam_ref_re.so")  # the roadmap-explorer package's own copies (rows 8f-2, 8f-4)
+LIB_PATH_ORBW = os.path.join(_HERE, "_ref", "libfitslam_ref_orbw.so")  # the ORB-SLAM3 wrapper's landmark query (rows F1, F2, 8f-1)
 
 
 def available():
@@ -18,6 +19,45 @@ def available():
 
 def available_re():
     return os.path.exists(LIB_PATH_RE)
+
+
+def available_orbw():
+    return os.path.exists(LIB_PATH_ORBW)
+
+
+class ReferenceORBW:
+    """oracle/_ref/libfitslam_ref_orbw.so: ORBSLAM3Interface::mapPointsVisibleFromPose, the landmark service handler and the
+    type conversions under them, compiled from the reference against stand-in ORB_SLAM3 / Sophus / Eigen declarations
+    (oracle/ref_harness_orbw.cpp)."""
+
+    def __init__(self):
+        self.lib = C.CDLL(LIB_PATH_ORBW)
+
+    def landmarks_in_view(self, xyz, keyframes, point_index, pose, params, max_landmarks=1000, max_distance=5.0, exhaustive=False):
+        """(landmarks in the query-pose frame as the response's float64 positions, keyframes checked)."""
+        xyz = np.ascontiguousarray(xyz, np.float32)
+        kf_pose = np.ascontiguousarray(np.concatenate([keyframes["Rwc"].reshape(-1, 9), keyframes["twc"].reshape(-1, 3)], axis=1), np.float32)
+        first = np.ascontiguousarray(keyframes["first"], np.uint32)
+        count = np.ascontiguousarray(keyframes["count"], np.uint32)
+        idx = np.ascontiguousarray(point_index, np.uint32)
+        p = np.asarray(pose).reshape(-1)[0]
+        pose7 = np.array([p["x"], p["y"], p["z"], p["qx"], p["qy"], p["qz"], p["qw"]], np.float64)
+        cam = np.array([params.fx, params.fy, params.cx, params.cy], np.float32)
+        cap = len(xyz) + 1
+        out = np.zeros((cap, 3), np.float64)
+        chk = C.c_int(-1)
+        n = self.lib.ref_orbw_landmarks_in_view(C.c_void_p(pose7.ctypes.data), C.c_void_p(xyz.ctypes.data), C.c_uint64(len(xyz)),
+                                                C.c_void_p(kf_pose.ctypes.data), C.c_void_p(first.ctypes.data), C.c_void_p(count.ctypes.data),
+                                                C.c_uint32(len(first)), C.c_void_p(idx.ctypes.data), C.c_int(max_landmarks),
+                                                C.c_float(max_distance), C.c_int(int(exhaustive)), C.c_void_p(cam.ctypes.data),
+                                                C.c_void_p(out.ctypes.data), C.c_uint32(cap), C.byref(chk))
+        return out[:n], chk.value
+
+    def euler_ros(self, R):
+        R = np.ascontiguousarray(R, np.float32)
+        out = np.zeros(3, np.float32)
+        self.lib.ref_orbw_euler_ros(C.c_void_p(R.ctypes.data), C.c_void_p(out.ctypes.data))
+        return out
 
 
 class ReferenceRE:

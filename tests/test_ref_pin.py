@@ -11,7 +11,8 @@ getVoxelCoordinate, getInformationFromLookup with the crowding factor, isPoseSaf
 8f-3 (LethalMarker: the ray / circle / triangle functions, addNewMarkedArea, addNewMarkedAreaFOV, updateCosts; the threshold node's
 callback) and next rows
 8f-2 (FrontierRoadMap::isConnectable) and 8f-4 (SensorSimulator::markRay) against the roadmap-explorer package's own code in
-oracle/_ref/libfitslam_ref_re.so."""
+oracle/_ref/libfitslam_ref_re.so; rows F1, F2 and the keyframe mode of 8f-1 in control flow (the ORB-SLAM3 wrapper's functions against
+stand-in ORB_SLAM3 / Sophus types, oracle/_ref/libfitslam_ref_orbw.so; see the section at the end)."""
 import math
 
 import numpy as np
@@ -479,3 +480,95 @@ def test_reference_sensor_simulator_rays(oracle, capi):
             assert n_o == n_r == 121
             np.testing.assert_array_equal(explored_o, explored_r)
         assert (explored_o != -1).sum() > 100
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# Rows F1, F2 and the keyframe mode of 8f-1: the ORB-SLAM3 wrapper's own mapPointsVisibleFromPose (both overloads), landmark
+# service handler and type conversions (oracle/_ref/libfitslam_ref_orbw.so), against stand-in ORB_SLAM3 / Sophus / Eigen
+# declarations.  Pinned: the control flow and the sequence of operations.  Not pinned: Sophus's quaternion storage and Eigen's
+# Affine rotation() (the stand-ins keep (R, t), as oracle.cpp does).
+# ---------------------------------------------------------------------------------------------------------------------------
+orbw = pytest.mark.skipif(not ref_binding.available_orbw(), reason="oracle/_ref is built where /root/reference exists")
+
+
+def _pose_q(capi, x, y, z, q):
+    p = np.zeros(1, dtype=capi.POSE_DTYPE)
+    p["x"], p["y"], p["z"] = x, y, z
+    p["qx"], p["qy"], p["qz"], p["qw"] = q
+    return p
+
+
+def _yaw_q(yaw):
+    return (0.0, 0.0, math.sin(yaw / 2), math.cos(yaw / 2))
+
+
+@orbw
+@pytest.mark.parametrize("exhaustive", [True, False])
+def test_reference_landmark_query_keyframes(oracle, synth, capi, exhaustive):
+    """A synthetic atlas of 200 keyframes over 60 k points: the landmarks of the response coordinate for coordinate and in order,
+    the number of keyframes checked, with the handler's own 1000-landmark cutoff, smaller ones and none."""
+    orb = ref_binding.ReferenceORBW()
+    rng = np.random.default_rng(21)
+    pts = rng.uniform(-25, 25, size=(60_000, 3)).astype(np.float32)
+    pts[:, 2] = rng.uniform(0, 3, len(pts))
+    kfs, idx = synth.make_keyframes(pts, 200, seed=9)
+    perm = np.array([[0, -1, 0], [0, 0, -1], [1, 0, 0]], dtype=np.float64)
+    seen_cut = seen_skip = 0
+    for t in range(30):
+        k = int(rng.integers(len(kfs)))
+        t_ros = perm.T @ kfs[k]["twc"].astype(np.float64)
+        if t % 3 == 2:  # a tilted camera (roll and pitch too), a quaternion not quite of unit length
+            q = rng.normal(size=4)
+            q = q / np.linalg.norm(q) * (1 + 1e-4 * rng.normal())
+        else:
+            q = _yaw_q(rng.uniform(-np.pi, np.pi))
+        pose = _pose_q(capi, t_ros[0] + rng.normal(0, 1.5), t_ros[1] + rng.normal(0, 1.5), 0.3, q)
+        for max_landmarks in (1000, 120, 0, 1 << 30):
+            for max_distance in (5.0, 2.5):
+                want, chk_w = orb.landmarks_in_view(pts, kfs, idx, pose, oracle.params, max_landmarks, max_distance, exhaustive)
+                got, chk = oracle.landmarks_in_view_keyframes(pts, kfs, idx, pose, max_landmarks, max_distance, exhaustive)
+                assert chk == chk_w and len(got) == len(want), (t, max_landmarks, max_distance, chk, chk_w, len(got), len(want))
+                # the response carries float64 positions holding the handler's floats
+                assert np.array_equal(got.astype(np.float64), want, equal_nan=True)
+                seen_cut += int(max_landmarks == 1000 and len(want) > 1000)
+                seen_skip += int(not exhaustive and chk_w < len(kfs))
+    assert seen_cut > 0 or not exhaustive
+    assert exhaustive or seen_skip > 0
+
+
+@orbw
+def test_reference_landmark_query_one_keyframe_is_the_exhaustive_query(oracle, capi):
+    """Rows F1 / F2 as the other entry points answer them: one keyframe holding every map point, exhaustive search, no cutoff in
+    reach; points behind the camera, on the image border, at the camera centre, non-finite."""
+    orb = ref_binding.ReferenceORBW()
+    rng = np.random.default_rng(4)
+    pts = rng.uniform(-12, 12, size=(20_000, 3)).astype(np.float32)
+    for t in range(12):
+        q = rng.normal(size=4)
+        q /= np.linalg.norm(q)
+        if t % 2:
+            q = np.array(_yaw_q(rng.uniform(-np.pi, np.pi)))
+        pose = _pose_q(capi, rng.uniform(-5, 5), rng.uniform(-5, 5), rng.uniform(0, 2), q)
+        pts[0] = (pose["x"][0], pose["y"][0], pose["z"][0])  # Zc = 0: 0 / 0 in the projection
+        pts[1] = (np.nan, 0, 0)
+        pts[2] = (np.inf, 1, 1)
+        one = np.zeros(1, dtype=capi.KEYFRAME_DTYPE)
+        one["Rwc"] = np.eye(3, dtype=np.float32).ravel()
+        one["count"] = len(pts)
+        idx = np.arange(len(pts), dtype=np.uint32)
+        want, chk = orb.landmarks_in_view(pts, one, idx, pose, oracle.params, 1 << 30, 5.0, True)
+        got = oracle.landmarks_in_view(pts, pose)
+        assert chk == 1 and len(got) == len(want) > 0
+        assert np.array_equal(got.astype(np.float64), want, equal_nan=True)
+
+
+@orbw
+def test_reference_rotation_to_euler_ros(oracle):
+    """rotationORBToEulerROS: the relative yaw the prefilter reads, for rotations about the ORB y axis (a ROS yaw)."""
+    orb = ref_binding.ReferenceORBW()
+    perm = np.array([[0, -1, 0], [0, 0, -1], [1, 0, 0]], dtype=np.float64)
+    for yaw in (0.0, 0.3, 1.5, 2.0, 3.0, -0.3, -1.5, -2.0, -3.0):
+        c, s = math.cos(yaw), math.sin(yaw)
+        R = perm @ np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]]) @ perm.T
+        e = orb.euler_ros(R.astype(np.float32))
+        assert abs(e[2] - (yaw % (2 * math.pi))) < 1e-5, (yaw, e)
