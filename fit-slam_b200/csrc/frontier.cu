@@ -193,6 +193,7 @@ __device__ __forceinline__ bool get_bit(const uint32_t *__restrict__ bits, uint3
   return (__ldg(bits + (size_t)my * wpr + (mx >> 5)) >> (mx & 31u)) & 1u;
 }
 __device__ __forceinline__ uint32_t ld_cg(const uint32_t *p) { return __ldcg(p); }
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 // neighbour `s` of cell (mx, my) in the reference's order: -1, +1, -W, +W, -1-W, -1+W, +1-W, +1+W
 // (DEP/src/Helpers.cpp:185-255).  Returns false where the reference's bounds tests drop the neighbour.
@@ -1461,37 +1462,117 @@ replay_line_kernel(const SearchParams S, const uint32_t *__restrict__ bits, uint
     if (lane == 0) {
       const uint32_t seed = oseed[comp];
       out[0] = seed;
-      ring[0] = seed;
+      ring[0] = (seed % W) | ((seed / W) << 16);  // the ring holds x | y << 16 (W, H < 65536 as in replay_warp_kernel)
       slot[seed] |= IL_VISITED;
     }
     __syncwarp();
     uint32_t head = 0, tail = 1;
+    // queue positions where the level before the dequeued cell's, that cell's level and the next one begin: a visited neighbour
+    // of a level-L cell lies in levels L - 1 .. L + 1 (the 8-neighbourhood is symmetric), that is in [lv_prev, tail)
+    uint32_t lv_prev = 0, lv_cur = 0, lv_end = 1;
+#ifdef FITSLAM_IL_PROF
+    long long pc[5] = {0, 0, 0, 0, 0}, t0 = clock64(), t1;
+    uint32_t n_win = 0, n_fall = 0;
+#define IL_T(k) { t1 = clock64(); pc[k] += t1 - t0; t0 = t1; }
+#else
+#define IL_T(k)
+#endif
     while (head < tail) {
-      // (the ring holds positions [tail - IL_RING, tail): a level wider than that reads the list itself, through L2)
-      const uint32_t p = (tail - head <= IL_RING) ? ring[head & (IL_RING - 1u)] : ld_cg(out + head);
-      ++head;
-      uint32_t y = __umulhi(p, mW), x = p - y * W;
-      while (x >= W) { x -= W; ++y; }
-      const int nx = (int)x + ddx, ny = (int)y + ddy;
-      const bool in = act && nx >= 0 && ny >= 0 && nx < (int)W && ny < (int)H;
-      const uint32_t nb = (uint32_t)ny * W + (uint32_t)nx;
-      // both loads at once (the slot word of a cell that turns out not to be a mask cell is read and dropped): a step is one
-      // memory round trip, not two
-      const uint32_t mw = in ? __ldg(bits + (size_t)ny * S.wpr + ((uint32_t)nx >> 5)) : 0u;
-      const uint32_t sw = in ? slot[nb] : IL_VISITED;
-      const bool bit = (mw >> ((uint32_t)nx & 31u)) & 1u;
-      const uint32_t sv = bit ? sw : IL_VISITED;  // isNewFrontierCell: a mask cell whose frontier_flag is not set yet
-      const bool acc = !(sv & IL_VISITED);
-      const uint32_t bal = __ballot_sync(0xffffffffu, acc);
-      if (acc) {
-        const uint32_t at = tail + __popc(bal & lt);
-        slot[nb] = sv | IL_VISITED;
-        out[at] = nb;
-        ring[at & (IL_RING - 1u)] = nb;
+      if (head == lv_end) { lv_prev = lv_cur; lv_cur = lv_end; lv_end = tail; }
+      const uint32_t wlen = tail - lv_prev;
+      if (wlen <= 64u) {
+        // Thin levels (the arcs this kernel is for).  The visited test is a search of the last three levels in the ring, 64
+        // entries over the 32 lanes, instead of a load of slot[] (whose line the store below evicts from L1 every step: an L2
+        // round trip per dequeued cell): each lane marks which cells of the 3 x 3 block around a dequeued cell its two entries
+        // are, one warp-wide OR gives the block's visited cells.  And the step takes TWO cells, A = queue[head] on lanes 0-7 and
+        // B = queue[head + 1] on lanes 8-15, when B is of A's level: a neighbour of B inside A's block that passes B's tests
+        // passes A's too (same mask bit, same visited set), so A accepts it first and B's lane drops it; lane order is then
+        // the reference's append order.  slot[]'s flag is still set, for the steps that take the other branch.
+        const bool pair = head + 1u < lv_end;
+        const uint32_t pa = ring[head & (IL_RING - 1u)], pb = ring[(head + 1u) & (IL_RING - 1u)];
+        const uint32_t xa = pa & 0xFFFFu, ya = pa >> 16, xb = pb & 0xFFFFu, yb = pb >> 16;
+        const bool second = (lane & 8u) != 0u;
+        const bool act2 = lane < 8u || (lane < 16u && pair);
+        const int nx = (int)(second ? xb : xa) + ddx, ny = (int)(second ? yb : ya) + ddy;
+        const bool in = act2 && nx >= 0 && ny >= 0 && nx < (int)W && ny < (int)H;
+        const uint32_t nb = (uint32_t)ny * W + (uint32_t)nx;
+        IL_T(0)
+        const uint32_t mw = in ? __ldg(bits + (size_t)ny * S.wpr + ((uint32_t)nx >> 5)) : 0u;
+#ifdef FITSLAM_IL_PROF
+        ++n_win;
+#endif
+        uint32_t m = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 2u; ++k) {
+          if (lane + 32u * k < wlen) {
+            const uint32_t e = ring[(lv_prev + 32u * k + lane) & (IL_RING - 1u)];
+            const uint32_t ex = e & 0xFFFFu, ey = e >> 16;
+            const uint32_t dxa = ex - xa + 1u, dya = ey - ya + 1u, dxb = ex - xb + 1u, dyb = ey - yb + 1u;
+            if (dxa < 3u && dya < 3u) m |= 1u << (dya * 3u + dxa);
+            if (dxb < 3u && dyb < 3u) m |= 512u << (dyb * 3u + dxb);
+          }
+        }
+        const uint32_t seen = __reduce_or_sync(0xffffffffu, m);
+        IL_T(1)
+        const bool bit = (mw >> ((uint32_t)nx & 31u)) & 1u;
+#ifdef FITSLAM_IL_PROF
+        if (__ballot_sync(0xffffffffu, bit)) {}
+        IL_T(2)
+#endif
+        const bool in_a = (uint32_t)(nx - (int)xa + 1) < 3u && (uint32_t)(ny - (int)ya + 1) < 3u;
+        const bool acc = in && bit && !((seen >> ((second ? 9u : 0u) + (uint32_t)((ddy + 1) * 3 + (ddx + 1)))) & 1u) && !(second && in_a);
+        const uint32_t bal = __ballot_sync(0xffffffffu, acc);
+        if (acc) {
+          const uint32_t at = tail + __popc(bal & lt);
+          atomicOr(&slot[nb], IL_VISITED);
+          out[at] = nb;
+          ring[at & (IL_RING - 1u)] = (uint32_t)nx | ((uint32_t)ny << 16);
+        }
+        tail += __popc(bal);
+        head += pair ? 2u : 1u;
+        IL_T(3)
+      } else {
+        // (the ring holds positions [tail - IL_RING, tail): a level wider than that reads the list itself, through L2)
+        uint32_t x, y;
+        if (tail - head <= IL_RING) {
+          const uint32_t pxy = ring[head & (IL_RING - 1u)];
+          x = pxy & 0xFFFFu;
+          y = pxy >> 16;
+        } else {
+          const uint32_t p = ld_cg(out + head);
+          y = __umulhi(p, mW);
+          x = p - y * W;
+          while (x >= W) { x -= W; ++y; }
+        }
+        ++head;
+        const int nx = (int)x + ddx, ny = (int)y + ddy;
+        const bool in = act && nx >= 0 && ny >= 0 && nx < (int)W && ny < (int)H;
+        const uint32_t nb = (uint32_t)ny * W + (uint32_t)nx;
+        // both loads at once (the slot word of a cell that turns out not to be a mask cell is read and dropped): a step is one
+        // memory round trip, not two
+        const uint32_t mw = in ? __ldg(bits + (size_t)ny * S.wpr + ((uint32_t)nx >> 5)) : 0u;
+        const uint32_t sw = in ? ld_cg(slot + nb) : IL_VISITED;
+#ifdef FITSLAM_IL_PROF
+        ++n_fall;
+#endif
+        const bool bit = (mw >> ((uint32_t)nx & 31u)) & 1u;
+        const uint32_t sv = bit ? sw : IL_VISITED;  // isNewFrontierCell: a mask cell whose frontier_flag is not set yet
+        const bool acc = !(sv & IL_VISITED);
+        const uint32_t bal = __ballot_sync(0xffffffffu, acc);
+        if (acc) {
+          const uint32_t at = tail + __popc(bal & lt);
+          slot[nb] = sv | IL_VISITED;
+          out[at] = nb;
+          ring[at & (IL_RING - 1u)] = (uint32_t)nx | ((uint32_t)ny << 16);
+        }
+        tail += __popc(bal);
       }
-      tail += __popc(bal);
       __syncwarp();
+      IL_T(4)
     }
+#ifdef FITSLAM_IL_PROF
+    if (lane == 0 && tail > 5000) printf("line comp %u cells %u window steps %u fallback %u cycles: head %lld window %lld maskwait %lld append %lld sync/fallback %lld\n", comp, tail, n_win, n_fall, pc[0], pc[1], pc[2], pc[3], pc[4]);
+#endif
   }
 }
 
