@@ -1050,9 +1050,11 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
             const bool finite = fabsf(dx) + fabsf(dy) + fabsf(dz) < 1e6f;
             bool sure = !F.exact_only && finite && lx >= 0.05f, vis = false;
             if (sure) {
+              // (fused by hand: the library is built with -fmad=false, and these feed a guarded decision only)
               const float au = -P.fx * ly, av = -P.fy * lz;
-              const float eu = F.gu + 4e-4f * lx, ev = F.gv + 4e-4f * lx;  // + the roundings of u, v themselves (3 ulp of 10^3 px) times Zc
-              const float u0 = au + P.cx * lx, u1 = (P.max_u - P.cx) * lx - au, v0 = av + P.cy * lx, v1 = (P.max_v - P.cy) * lx - av;
+              const float eu = __fmaf_rn(4e-4f, lx, F.gu), ev = __fmaf_rn(4e-4f, lx, F.gv);  // + the roundings of u, v themselves (3 ulp of 10^3 px) times Zc
+              const float u0 = __fmaf_rn(P.cx, lx, au), u1 = __fmaf_rn(P.max_u - P.cx, lx, -au);
+              const float v0 = __fmaf_rn(P.cy, lx, av), v1 = __fmaf_rn(P.max_v - P.cy, lx, -av);
               const float inner = fminf(fminf(u0 - eu, u1 - eu), fminf(v0 - ev, v1 - ev));
               const float outer = fminf(fminf(u0 + eu, u1 + eu), fminf(v0 + ev, v1 + ev));
               vis = inner >= 0.f;
