@@ -195,6 +195,13 @@ struct ScoreSlice {
   const uint8_t *tags = nullptr;  // per frontier: which launch scores it (nullptr: no filter)
   uint32_t tag = 0;
   uint32_t mod = 1, rem = 0;      // only frontiers f with f % mod == rem (the cycle's sharding: rank `rem` of `mod`)
+  // Compact work list of a Fisher launch (optional): make_poses_kernel appends every frontier of the slice that passes the
+  // filters above, so that the Fisher grid holds work only (CTAs of slots outside the range, of another tag or of another
+  // rank used to start and exit: up to 12 of them per scored pose).  *work_count = frontiers appended; the launch covers the
+  // first work_cap entries of work_list; the ones beyond it are retagged TAG_FINAL (scored by the launches after the search).
+  uint32_t *work_count = nullptr, *work_list = nullptr;
+  uint32_t work_cap = 0;
+  uint8_t *retag = nullptr;
 };
 #ifdef __CUDACC__
 __device__ __forceinline__ uint32_t slice_slots(const ScoreSlice &s) {  // slots of the slice (owned or not, any tag)
@@ -213,6 +220,14 @@ __device__ __forceinline__ bool slice_frontier(const ScoreSlice &s, uint32_t slo
   f = first + slot;
   if (s.mod > 1u && f % s.mod != s.rem) return false;
   return !s.tags || s.tags[f] == s.tag;
+}
+#endif
+#ifdef __CUDACC__
+// slot k of a launch that reads its frontiers from the work list
+__device__ __forceinline__ bool slice_work_frontier(const ScoreSlice &s, uint32_t slot, uint32_t &f) {
+  if (slot >= min(*s.work_count, s.work_cap)) return false;
+  f = s.work_list[slot];
+  return true;
 }
 #endif
 static constexpr uint32_t TAG_FINAL = 255;     // frontier produced after the search ended: scored by the host-sized launches

@@ -32,6 +32,15 @@ struct CycleState {
   double *h_yaw = nullptr;           // pinned
   size_t h_cap = 0;
   cudaEvent_t ev_fr = nullptr;
+  // Work lists of the Fisher launches (ScoreSlice::work_*): WORK_LAUNCHES counters, then one list of WORK_LIST frontier indices
+  // per early launch (index = the launch's tag); work_final: counter + list of the launch after the search.  hist[] = how many
+  // frontiers each early launch had in the last cycle: the next cycle sizes its grids from it (the host cannot know the
+  // counts of a search that is still running; what a grid does not cover is scored after the search).
+  static constexpr uint32_t WORK_LAUNCHES = 64, WORK_LIST = 8192;
+  DevBuf<uint32_t> work, work_final;
+  uint32_t *h_work = nullptr;  // pinned: WORK_LAUNCHES + 1
+  uint32_t hist[WORK_LAUNCHES] = {};
+  bool have_hist = false, hist_pending = false;
   uint32_t yaw_windows = 0;
   double yaw_dt = 0, yaw_fov = 0;
   cudaEvent_t ev[8] = {};
@@ -54,6 +63,8 @@ void destroy_cycle_state(fitslam_ctx *c) {
   CycleState *s = c->cy;
   s->poses.release(); s->fisher.release(); s->fisher_best.release(); s->fisher_safe.release(); s->fisher_nvis.release(); s->yaw_q.release();
   s->goal_yaw.release();
+  s->work.release(); s->work_final.release();
+  if (s->h_work) cudaFreeHost(s->h_work);
   if (s->h_fr) cudaFreeHost(s->h_fr);
   if (s->h_yaw) cudaFreeHost(s->h_yaw);
   if (s->have_events) {
@@ -74,6 +85,11 @@ __global__ void make_poses_kernel(const fitslam_frontier *__restrict__ fr, const
   const uint32_t slot = i / ppf, w = i - slot * ppf;
   uint32_t f = 0;
   if (!slice_frontier(slice, slot, f)) return;
+  if (slice.work_count && w == 0) {
+    const uint32_t k = atomicAdd(slice.work_count, 1u);
+    if (k < slice.work_cap) slice.work_list[k] = f;
+    else if (slice.retag) slice.retag[f] = (uint8_t)TAG_FINAL;  // more frontiers than the launch was sized for: scored after the search
+  }
   const uint32_t win = ppf == 1 ? (uint32_t)arr[f].max_index : w;
   fitslam_pose p;
   p.x = fr[f].goal_x;
@@ -109,6 +125,14 @@ static fitslam_status score_slice(fitslam_ctx *c, cudaStream_t stream, const Sco
   if (st != FITSLAM_OK || cfg->ppf == 0) return st;
   const uint64_t slots = sl.range ? sl.cap : sl.count;
   if (slots == 0) return FITSLAM_OK;
+  if (sl.range && sl.tags && sl.tag < CycleState::WORK_LAUNCHES && s->work.p) {
+    // an early launch: its Fisher grid is sized from what this launch found in the last cycle (+ 25 %), not from the cap
+    sl.work_count = s->work.p + sl.tag;
+    sl.work_list = s->work.p + CycleState::WORK_LAUNCHES + (size_t)sl.tag * CycleState::WORK_LIST;
+    sl.work_cap = std::min<uint32_t>(sl.cap, CycleState::WORK_LIST);
+    if (s->have_hist) sl.work_cap = std::min<uint32_t>(sl.work_cap, s->hist[sl.tag] + s->hist[sl.tag] / 4u + 8u);
+    sl.retag = const_cast<uint8_t *>(sl.tags);
+  }
   const uint64_t np = slots * cfg->ppf;
   make_poses_kernel<<<(unsigned)((np + 255) / 256), 256, 0, stream>>>(c->frontiers.p, c->arrival.p, s->yaw_q.p, sl, cfg->ppf,
                                                                        c->prm.candidate_pose_z, s->poses.p);
@@ -223,9 +247,19 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
       if (ppf) FS_CUDA(c, cudaMemsetAsync(s->fisher.p, 0, (size_t)cap * ppf * sizeof(float), c->stream));
     }
   }
+  if (early && ppf) {
+    FS_CUDA(c, s->work.reserve(CycleState::WORK_LAUNCHES * (size_t)(1 + CycleState::WORK_LIST)));
+    FS_CUDA(c, cudaMemsetAsync(s->work.p, 0, CycleState::WORK_LAUNCHES * sizeof(uint32_t), c->stream));
+    if (!s->h_work) FS_CUDA(c, cudaMallocHost((void **)&s->h_work, (CycleState::WORK_LAUNCHES + 1) * sizeof(uint32_t)));
+  }
+  s->hist_pending = false;
   FS_CUDA(c, cudaEventRecord(s->ev[0], c->stream));
   st = frontier_search_device(c, rx, ry, early ? &hook : nullptr);  // one host sync inside: the list sizes decide the next launches
   if (st != FITSLAM_OK) return st;
+  if (early && ppf) {  // (the search has waited for its scoring streams: the counts are final; read at the end of the cycle)
+    FS_CUDA(c, cudaMemcpyAsync(s->h_work, s->work.p, CycleState::WORK_LAUNCHES * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    s->hist_pending = true;
+  }
   FS_CUDA(c, cudaEventRecord(s->ev[1], c->stream));
   const uint32_t F = c->n_frontiers;
   uint32_t n_cells = 0, n_comp = 0, levels = 0, ambiguous = 0;
@@ -288,9 +322,26 @@ fitslam_status fitslam_cycle_begin(fitslam_ctx *c, double rx, double ry, double 
   s->res.n_candidates = F * c->shape.n_windows;
   s->n_poses = 0;
   if (ppf && rest.count) {
+    // the frontiers left for this launch (this rank's, not scored during the search) go into a list, and the host reads
+    // their number: a grid over all F frontiers would start up to F * ppf CTAs that find nothing to do
+    FS_CUDA(c, s->work_final.reserve((size_t)F + 1));
+    if (!s->h_work) FS_CUDA(c, cudaMallocHost((void **)&s->h_work, (CycleState::WORK_LAUNCHES + 1) * sizeof(uint32_t)));
+    FS_CUDA(c, cudaMemsetAsync(s->work_final.p, 0, sizeof(uint32_t), c->stream));
+    rest.work_count = s->work_final.p;
+    rest.work_list = s->work_final.p + 1;
+    rest.work_cap = F;
     make_poses_kernel<<<(unsigned)(((uint64_t)rest.count * ppf + 255) / 256), 256, 0, c->stream>>>(
         c->frontiers.p, c->arrival.p, s->yaw_q.p, rest, ppf, c->prm.candidate_pose_z, s->poses.p);
     ++c->launches;
+    uint32_t *h_n = s->h_work + CycleState::WORK_LAUNCHES;
+    FS_CUDA(c, cudaMemcpyAsync(h_n, s->work_final.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    FS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (s->hist_pending) {  // (the same synchronisation brought the early launches' counts)
+      memcpy(s->hist, s->h_work, sizeof(s->hist));
+      s->have_hist = true;
+      s->hist_pending = false;
+    }
+    rest.work_cap = std::min<uint32_t>(*h_n, F);
     st = fisher_score_slice(c, c->stream, s->poses.p, ppf, rest, s->fisher.p, s->fisher_safe.p, s->fisher_nvis.p, c->records.p,
                             c->arrival.p);
     if (st != FITSLAM_OK) return st;

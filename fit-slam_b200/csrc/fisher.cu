@@ -53,6 +53,9 @@ static constexpr int MAX_BINS = 1024;       // bins one pose can touch (bounding
 #ifndef FS_FISHER_MINB
 #define FS_FISHER_MINB 2
 #endif
+#ifndef FS_FISHER_BOUND   // the register budget is that of this many threads x FS_FISHER_MINB CTAs, whatever the CTA launched
+#define FS_FISHER_BOUND (FS_FISHER_THREADS > 768 ? FS_FISHER_THREADS : 768)
+#endif
 static constexpr int FISHER_THREADS = FS_FISHER_THREADS;
 #ifndef FS_CHUNK_PTS
 #define FS_CHUNK_PTS 64
@@ -858,7 +861,7 @@ __device__ __forceinline__ uint32_t table_count(uint32_t *tab, uint32_t h, uint3
   return 0u;
 }
 
-__global__ void __launch_bounds__(FISHER_THREADS, FS_FISHER_MINB)
+__global__ void __launch_bounds__(FS_FISHER_BOUND, FS_FISHER_MINB)
 fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, float *__restrict__ info_out,
               uint8_t *__restrict__ safe_out, uint32_t *__restrict__ nvis_out, ScoreRecord *__restrict__ rec_out,
               const fitslam_arrival *__restrict__ arrival) {
@@ -877,7 +880,7 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
   if (P.use_slice) {
     const uint32_t slot = blockIdx.x / P.poses_per_frontier;
     uint32_t f = 0;
-    if (!slice_frontier(P.slice, slot, f)) return;
+    if (P.slice.work_count ? !slice_work_frontier(P.slice, slot, f) : !slice_frontier(P.slice, slot, f)) return;
     pi = f * P.poses_per_frontier + (blockIdx.x - slot * P.poses_per_frontier);
   } else {
     pi = P.first + blockIdx.x;
@@ -1198,7 +1201,7 @@ fitslam_status fisher_score_slice(fitslam_ctx *c, cudaStream_t stream, const fit
   FisherParams P;
   const fitslam_status st = fisher_params(c, P);
   if (st != FITSLAM_OK) return st;
-  const uint64_t slots = slice.range ? slice.cap : slice.count;
+  const uint64_t slots = slice.work_count ? slice.work_cap : (slice.range ? slice.cap : slice.count);
   if (slots == 0) return FITSLAM_OK;
   P.poses_per_frontier = poses_per_frontier ? poses_per_frontier : 1;
   P.use_slice = 1;

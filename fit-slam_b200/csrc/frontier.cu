@@ -1953,6 +1953,7 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   }
   // a batch is about 1/12 of the frontiers; the launches are sized for a quarter of the last search's count
   S.early_cap = std::min<uint32_t>(std::max<uint32_t>(EARLY_SLICE_CAP, s->last.n_frontiers / 4u), 8192u);
+  if (const char *e = getenv("FITSLAM_EARLY_CAP")) S.early_cap = (uint32_t)std::min<long>(std::max<long>(atol(e), 1), 8192);
   S.early_limit = hook ? hook->limit : 0xFFFFFFFFu;
   S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
   S.ow_wide = getenv("FITSLAM_OW_NOWIDE") ? 0u : 1u;

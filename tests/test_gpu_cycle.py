@@ -233,3 +233,47 @@ def test_cycle_matches_the_compiled_reference(capi, oracle, synth, name):
         assert sel.closest_global == closest
     finally:
         ctx.close()
+
+
+def test_cycle_after_a_much_smaller_one(capi, oracle, synth):
+    """The Fisher launches that run during the search are sized from what the same launch found in the previous cycle.  A cycle
+    that finds far more frontiers than the one before leaves the excess to the launches after the search: every candidate is
+    still scored once, and the results equal a fresh context's bit for bit."""
+    a, meta, pts, ov = synth.make_config("C1")
+    synth.apply_overrides(oracle.params, ov)
+    H, W = a.shape
+    walled = a.copy()  # a lethal box close around the robot: the search stays inside it and finds few frontiers
+    ry, rx = int((meta["robot_y"] - meta["oy"]) / meta["res"]), int((meta["robot_x"] - meta["ox"]) / meta["res"])
+    r = min(H, W) // 16
+    walled[max(ry - r, 0):ry + r, max(rx - r, 0)] = 254
+    walled[max(ry - r, 0):ry + r, min(rx + r, W - 1)] = 254
+    walled[max(ry - r, 0), max(rx - r, 0):rx + r] = 254
+    walled[min(ry + r, H - 1), max(rx - r, 0):rx + r + 1] = 254
+
+    def run(ctx, grid):
+        ctx.set_costmap(grid, meta["res"], meta["ox"], meta["oy"])
+        st, res = ctx.cycle(meta["robot_x"], meta["robot_y"], 0.4, meta["poly"], capi.FISHER_ALL_YAWS)
+        assert st in (0, capi.E_NO_FRONTIERS)
+        if st != 0:
+            return res, None, None
+        return res, ctx.cycle_fetch(res.n_frontiers), ctx.cycle_fetch_candidates(res.n_fisher_poses)
+
+    fresh = capi.Context(oracle.params)
+    fresh.fisher_generate_lookup()
+    fresh.set_map_points(pts)
+    want_res, want, want_c = run(fresh, a)
+    fresh.close()
+    ctx = capi.Context(oracle.params)
+    ctx.fisher_generate_lookup()
+    ctx.set_map_points(pts)
+    for _ in range(2):
+        small_res, _, _ = run(ctx, walled)
+    assert 0 < small_res.n_frontiers * 4 < want_res.n_frontiers
+    for _ in range(2):  # the first one runs on the small cycle's sizes, the second on its own
+        res, got, got_c = run(ctx, a)
+        assert res.n_frontiers == want_res.n_frontiers
+        for k in ("frontiers", "arrival", "fisher", "weighted_cost", "sorted"):
+            np.testing.assert_array_equal(got[k], want[k], err_msg=k)
+        for g, w in zip(got_c, want_c):
+            np.testing.assert_array_equal(g, w)
+    ctx.close()
