@@ -964,30 +964,35 @@ ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim,
 // ---- the outer wavefront on a thread-block cluster ----------------------------------------------------------------
 // The same search with a level spread over the CTAs of one cluster (16 SMs; 8 where the non-portable size is refused).
 // The single-CTA kernel above is bound by what one SM's L1 pipeline can look up per level (~7 cycles per dequeued cell:
-// 80 ms for C4's 22.8 M cells); here every CTA takes a contiguous slice of the level's positions.
-//   * the level queue lives in distributed shared memory: positions [r * per, (r + 1) * per) of a level are CTA r's
-//     slice (per = a power of two >= n / CTAs), and whoever appends a cell stores its entry straight into the slice of
-//     the CTA that will dequeue it (st.shared::cluster through cluster.map_shared_rank).
-//   * the state array (class or position, 2 bytes per cell, as in the single-CTA kernel) goes through L2 (ld.global.cg /
-//     plain stores): positions are written in one level and read in the next, with a cluster barrier (release / acquire)
-//     in between; one dependent L2 round trip per level.
-//   * order: a CTA's winners go, in (position, slot) order, into a local list; the CTAs' counts are exchanged through
-//     distributed shared memory; after a cluster barrier every CTA knows its base and the level's size, stores the
-//     positions and the entries of its winners, and a second cluster barrier ends the level.
+// 80 ms for C4's 22.8 M cells); here every CTA takes a contiguous slice of the level's positions.  ONE cluster barrier
+// per level:
+//   * CTA r keeps the cells it appends (its winners, in (position, slot) order) in its own shared memory, and the state
+//     array gets r * OWC_SLICE + k for its k-th winner at once.  The CTAs' slices of a level are consecutive position
+//     ranges, so these codes grow with the position in the next level: they order the cells exactly as positions do,
+//     which is all the decision rule asks of them (ow_decide compares, never indexes), and nobody has to know the other
+//     CTAs' counts to write them.  The store is safe while other CTAs are still deciding: a level-d decision reads cells
+//     at distance 2 from level-d cells through an unvisited candidate, i.e. cells of level d or d + 2 (the grid is
+//     bipartite), and the cells written during level d are the level-(d + 1) ones.
+//   * every CTA tells every CTA its count through distributed shared memory, then barrier.cluster (release / acquire: the
+//     codes in global memory, the winners' entries and the counts in shared memory).
+//   * the next level is cut into equal position ranges again; a CTA PULLS the entries of its range out of the winner lists
+//     of the CTAs that produced them (ld.shared::cluster), position p belonging to the producer whose prefix of counts
+//     covers it.  Balance is restored every level without a second barrier.
+//   * the state array goes through L2 (ld.global.cg / plain stores): L1 is not coherent across CTAs.
+// Touch keys need the exact dequeue rank: base + p, known to the puller.
 static constexpr int OWC_THREADS = 512;
-static constexpr uint32_t OWC_SLICE = 4096;             // queue entries per CTA and level (16 CTAs: levels up to OW_MAX_LEVEL)
-static constexpr uint32_t OWC_LOCAL = 3 * OWC_SLICE;    // winners of one CTA in one level: at most 3 per dequeued cell
-static constexpr uint32_t OWC_SMEM = (2 * OWC_SLICE + OWC_LOCAL) * 8;
+static constexpr uint32_t OWC_SLICE = 4080;             // winners one CTA can append per level; 16 * 4080 = OW_MAX_LEVEL codes
+static constexpr uint32_t OWC_SMEM = 2 * OWC_SLICE * 8;
+static_assert(16u * OWC_SLICE <= OW_MAX_LEVEL, "codes stay below the class values");
 
 __global__ void __launch_bounds__(OWC_THREADS, 1)
 ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim, uint32_t *queue, Counters *cnt, uint32_t n_parts) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   const uint32_t CS = cluster.num_blocks(), rank = cluster.block_rank();
-  extern __shared__ uint2 owc_sh[];
-  uint2 *qs = owc_sh;                       // two slices of OWC_SLICE entries
-  uint2 *lout = owc_sh + 2 * OWC_SLICE;     // this CTA's winners of the level, in order
+  extern __shared__ uint2 owc_sh[];         // two winner lists of OWC_SLICE entries: this level's (read by every CTA) and the next one's
   __shared__ uint32_t s_cnt[2][16];         // winners per CTA (written by the CTAs themselves), by level parity
+  __shared__ uint32_t s_pref[16];           // inclusive prefix of this level's counts
   __shared__ uint32_t s_ws[2][OWC_THREADS / 32];
   __shared__ uint32_t sh48[48];
   __shared__ uint32_t s_start;
@@ -1001,6 +1006,7 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
     for (uint32_t k = from; k + 1 < n_parts; ++k) atomicExch(&cnt->part_flag[k], 1u);
   };
   if (cnt->overflow) { publish(0, 0); return; }  // (uniform: written before this kernel)
+  if (threadIdx.x < 16) s_cnt[0][threadIdx.x] = threadIdx.x == 0 ? 1u : 0u;  // level 0: the start cell, CTA 0's first winner
   if (rank == 0) {
     const uint32_t ry = S.robot_cell / W, rx = S.robot_cell - ry * W;
     if (threadIdx.x == 0) s_start = S.robot_cell;
@@ -1014,13 +1020,12 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
       cnt->start_cell = start;
       const uint32_t sy = start / W, sx = start - sy * W;
       uint32_t si;
-      qs[0] = ow_start_entry(L, rk, sx, sy, &si);
-      rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56)
+      owc_sh[0] = ow_start_entry(L, rk, sx, sy, &si);
+      rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56): code 0 = CTA 0's winner 0
     }
   }
   cluster.sync();
-  uint32_t base = 0, n = 1, levels = 0, part = 0, widest = 1, cur = 0, scans = 0;
-  uint32_t per = 32;  // slice length of the current level
+  uint32_t base = 0, levels = 0, part = 0, widest = 1, cur = 0, scans = 0;
   uint32_t next_part_level = S.ow_part_levels;
   bool bad = false;
   OwProf pf;
@@ -1028,10 +1033,30 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
   for (int k = 0; k < 8; ++k) pf.acc[k] = 0;
   pf.last = ow_clock(0);
 #endif
-  while (n > 0) {
+  for (;;) {
+    // this level: counts per producer (every warp: one load, a shuffle scan and two reductions)
+    const uint32_t cv = lane < CS ? s_cnt[levels & 1u][lane] : 0u;
+    const bool any_bad = __reduce_max_sync(0xffffffffu, cv) == 0xFFFFFFFFu;
+    uint32_t incl = cv;
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    const uint32_t n = any_bad ? 0u : __shfl_sync(0xffffffffu, incl, 15);
+    if (any_bad) {  // uniform across the cluster: a CTA appended more than its list holds; the global-memory wavefront reruns the
+      if (rank == 0 && threadIdx.x == 0) cnt->ow_fallback = 1u;  // search (claim[] holds touch keys only, and it would write the same ones)
+      publish(part, base);
+      return;
+    }
+    if (n == 0) break;
+    widest = max(widest, n);
+    if (lane < 16) s_pref[lane] = incl;  // (every warp stores the same values)
+    __syncwarp();
+    OW_STAMP(0, n);
+    const uint32_t per = (n + CS - 1u) / CS;
     const uint32_t lo = rank * per, m = lo < n ? min(per, n - lo) : 0u;  // this CTA's positions: [lo, lo + m)
-    OW_STAMP(0, m);
-    const uint2 *q = qs + cur * OWC_SLICE;
+    uint2 *lnext = owc_sh + (cur ^ 1u) * OWC_SLICE;
     uint32_t n_local = 0;
     for (uint32_t tile = 0; tile < m; tile += OWC_THREADS) {
       uint32_t *ws = s_ws[scans & 1u];
@@ -1041,9 +1066,18 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
       d.win = 0u;
       if (tile + (wid << 5) < m) {  // warp-uniform
         uint2 e = make_uint2(0u, 0u);
-        if (pl < m) e = q[pl];
-        ow_decide(L, e, lo + pl, [&](uint32_t at) { return (uint32_t)__ldcg(rk + at); }, d);
-        ow_touch(claim, W, e, base + lo + pl);
+        uint32_t code = 0u;
+        const uint32_t p = lo + pl;
+        if (pl < m) {
+          uint32_t prod = 0;
+#pragma unroll
+          for (int j = 0; j < 15; ++j) prod += (p >= s_pref[j]) ? 1u : 0u;  // the producer whose prefix of counts covers p
+          const uint32_t k = p - (prod ? s_pref[prod - 1u] : 0u);
+          e = cluster.map_shared_rank(owc_sh + cur * OWC_SLICE, prod)[k];
+          code = prod * OWC_SLICE + k;
+        }
+        ow_decide(L, e, code, [&](uint32_t at) { return (uint32_t)__ldcg(rk + at); }, d);
+        ow_touch(claim, W, e, base + p);
       }
       const uint32_t wmask = d.win;
       // CTA-wide exclusive scan of the winner counts (0..4 per thread): three ballots per warp, one barrier
@@ -1057,48 +1091,26 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
       const uint32_t total = __reduce_add_sync(0xffffffffu, wv);
       const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
       uint32_t dst = n_local + wbase + excl;
-      if (n_local + total > OWC_LOCAL) bad = true;  // (uniform; cannot happen: at most 3 winners per dequeued cell, 4 at the start)
+      if (n_local + total > OWC_SLICE) bad = true;  // (uniform in the CTA)
       else {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          if (wmask & (1u << k)) lout[dst++] = d.ent[k];
+          if (wmask & (1u << k)) {
+            lnext[dst] = d.ent[k];
+            rk[d.ci[k]] = (uint16_t)(rank * OWC_SLICE + dst);
+            ++dst;
+          }
       }
       n_local += total;
     }
     OW_STAMP(1, n_local);
-    // every CTA tells every CTA how many cells it appends
-    if (threadIdx.x < CS) cluster.map_shared_rank(&s_cnt[levels & 1u][0], threadIdx.x)[rank] = bad ? 0xFFFFFFFFu : n_local;
+    // every CTA tells every CTA how many cells it appended
+    if (threadIdx.x < CS) cluster.map_shared_rank(&s_cnt[(levels + 1u) & 1u][0], threadIdx.x)[rank] = bad ? 0xFFFFFFFFu : n_local;
     OW_STAMP(2, n_local);
-    cluster.sync();
+    cluster.sync();  // release / acquire: the codes (global memory), the winners' entries and the counts (shared memory)
     OW_STAMP(3, n_local);
-    const uint32_t cv = lane < CS ? s_cnt[levels & 1u][lane] : 0u;  // (every warp: one load and three warp reductions)
-    const bool any_bad = __reduce_max_sync(0xffffffffu, cv) == 0xFFFFFFFFu;
-    const uint32_t n_next = __reduce_add_sync(0xffffffffu, cv), gbase = __reduce_add_sync(0xffffffffu, lane < rank ? cv : 0u);
     base += n;
     ++levels;
-    widest = max(widest, n_next);
-    if (any_bad || n_next > OW_MAX_LEVEL || n_next > CS * OWC_SLICE) {  // uniform across the cluster: the global-memory wavefront
-      if (rank == 0 && threadIdx.x == 0) cnt->ow_fallback = 1u;      // reruns the search (claim[] holds touch keys only, and it
-      publish(part, base);                                           // would write the same ones)
-      return;
-    }
-    // slice length of the next level: a power of two, so that position -> (CTA, offset) is a shift and a mask
-    const uint32_t need = (n_next + CS - 1u) / CS;  // CS is 8 or 16
-    const uint32_t sh = need <= 32u ? 5u : 32u - __clz(need - 1u), per_next = 1u << sh;
-    uint2 *qn = qs + (cur ^ 1u) * OWC_SLICE;
-    OW_STAMP(4, n_next);
-    for (uint32_t k = threadIdx.x; k < n_local; k += OWC_THREADS) {
-      const uint2 e = lout[k];
-      const uint32_t j = gbase + k;  // the cell's position in the next level
-      const uint32_t x = e.x & 0x3FFFu, y = (e.x >> 14) & 0x3FFFu;
-      rk[ow_rk_fx(x + OW_PAD) + ow_rk_fy(y + OW_PAD, L.rk_yt)] = (uint16_t)j;
-      cluster.map_shared_rank(qn, j >> sh)[j & (per_next - 1u)] = e;
-    }
-    OW_STAMP(5, n_next);
-    cluster.sync();  // release / acquire: the positions (global memory) and the entries (distributed shared memory) of the next level
-    OW_STAMP(6, n_next);
-    n = n_next;
-    per = per_next;
     cur ^= 1u;
     if (levels >= next_part_level && part + 1 < n_parts) {
       if (rank == 0 && threadIdx.x == 0) {
