@@ -180,7 +180,7 @@ struct SelectMeta {
 struct SelectState {
   DevBuf<double> len, head, wc, ua, ud;
   DevBuf<uint8_t> bl, ach;
-  DevBuf<uint32_t> sorted;
+  DevBuf<uint32_t> sorted, rank;
   DevBuf<SelectMeta> meta;
 };
 SelectState *sstate(fitslam_ctx *c);

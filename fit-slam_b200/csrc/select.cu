@@ -26,7 +26,7 @@ void destroy_select_state(fitslam_ctx *c) {
   if (!c->sel) return;
   SelectState *s = c->sel;
   s->len.release(); s->head.release(); s->wc.release(); s->ua.release(); s->ud.release();
-  s->bl.release(); s->ach.release(); s->sorted.release(); s->meta.release();
+  s->bl.release(); s->ach.release(); s->sorted.release(); s->rank.release(); s->meta.release();
   delete s;
   c->sel = nullptr;
 }
@@ -173,6 +173,41 @@ rank_kernel(const uint8_t *__restrict__ ach, const uint8_t *__restrict__ bl, con
   if (mine) sorted[r] = i;
 }
 
+// The same ranks for long lists: the comparisons of one frontier are split over gridDim.y CTAs (each counts the smaller
+// elements of its part of the list, partial ranks added up in `rank`), then a scatter.  One CTA per 256 frontiers alone is
+// 85 CTAs at C4's 21 791 frontiers, each walking the whole list: 0.3 ms on a third of the GPU.
+__global__ void __launch_bounds__(256)
+rank_count_kernel(const uint8_t *__restrict__ ach, const uint8_t *__restrict__ bl, const double *__restrict__ len, uint32_t n,
+                  uint32_t part, uint32_t *rank) {
+  __shared__ double s_len[256];
+  __shared__ uint8_t s_ok[256];
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool mine = i < n && ach[i] && !(bl && bl[i]);
+  const double li = mine ? len[i] : 0.0;
+  uint32_t r = 0;
+  const uint32_t j0 = blockIdx.y * part, j1 = min(n, j0 + part);
+  for (uint32_t base = j0; base < j1; base += 256) {
+    const uint32_t j = base + threadIdx.x;
+    s_ok[threadIdx.x] = j < j1 && ach[j] && !(bl && bl[j]);
+    s_len[threadIdx.x] = j < j1 ? len[j] : 0.0;
+    __syncthreads();
+    if (mine) {
+      const uint32_t m = min(256u, j1 - base);
+      for (uint32_t t = 0; t < m; ++t) {
+        const double lj = s_len[t];
+        r += (s_ok[t] && (lj < li || (lj == li && base + t < i))) ? 1u : 0u;
+      }
+    }
+    __syncthreads();
+  }
+  if (mine && r) atomicAdd(rank + i, r);
+}
+__global__ void rank_scatter_kernel(const uint8_t *__restrict__ ach, const uint8_t *__restrict__ bl, const uint32_t *__restrict__ rank,
+                                    uint32_t n, uint32_t *__restrict__ sorted) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && ach[i] && !(bl && bl[i])) sorted[rank[i]] = i;
+}
+
 // The local/global walk of getFilteredFrontiersN (:186-226) in closed form.
 __global__ void selection_kernel(const SelectParams P, const uint32_t *__restrict__ sorted, SelectMeta *meta) {
   fitslam_selection s;
@@ -211,7 +246,17 @@ fitslam_status select_device(fitslam_ctx *c, uint32_t n, const fitslam_arrival *
   P.n = n;
   P.n_local_area = (uint32_t)std::max(0, c->prm.num_frontiers_in_local_area);
   normalise_kernel<<<1, 1024, 0, c->stream>>>(P, d_arr, d_ach, d_bl, d_len, d_head, s->wc.p, s->ua.p, s->ud.p, s->meta.p);
-  rank_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d_ach, d_bl, d_len, n, s->sorted.p);
+  const uint32_t parts = std::min<uint32_t>(n / 2048u, 16u);
+  if (parts >= 2) {
+    FS_CUDA(c, s->rank.reserve(n));
+    FS_CUDA(c, cudaMemsetAsync(s->rank.p, 0, (size_t)n * sizeof(uint32_t), c->stream));
+    const uint32_t part = ((n + parts - 1u) / parts + 255u) / 256u * 256u;
+    rank_count_kernel<<<dim3((n + 255) / 256, (n + part - 1u) / part), 256, 0, c->stream>>>(d_ach, d_bl, d_len, n, part, s->rank.p);
+    rank_scatter_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d_ach, d_bl, s->rank.p, n, s->sorted.p);
+    ++c->launches;
+  } else {
+    rank_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(d_ach, d_bl, d_len, n, s->sorted.p);
+  }
   selection_kernel<<<1, 1, 0, c->stream>>>(P, s->sorted.p, s->meta.p);
   c->launches += 3;
   FS_CUDA(c, cudaGetLastError());

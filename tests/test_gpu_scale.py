@@ -88,6 +88,15 @@ def test_c4_full_size_properties(capi, oracle, synth):
         arr, _, _ = oracle.score_arrival(a, meta, fr[pick], meta["poly"])
         for key in REC_FIELDS:
             np.testing.assert_array_equal(out1["arrival"][key][pick], arr[key], err_msg=key)
+        # path lengths, the sorted list and the selection of all 21 k frontiers (the ranks of a list this long are counted by
+        # several CTAs per frontier): the oracle's plan + std::sort on the device's arrival records
+        ach, pl, ph = oracle.plan_euclidean(meta["robot_x"], meta["robot_y"], 0.3, fr, out1["arrival"]["achievable"])
+        np.testing.assert_array_equal(out1["path_length_m"].view(np.uint64), pl.view(np.uint64))
+        wsrt, wsel = oracle.select(ach, pl)
+        assert res1.selection.n_sorted == wsel.n_sorted == len(wsrt) > 0 and F > 4096
+        np.testing.assert_array_equal(out1["sorted"][:wsel.n_sorted], wsrt)
+        for f in ("n_local", "global_begin", "n_global", "closest_global"):
+            assert getattr(res1.selection, f) == getattr(wsel, f), f
         # ... and Fisher information of 96 sampled candidates (3 yaw windows of 32 frontiers) over the 1 M map points: 1e-4
         oracle.fisher_generate()
         pf = np.repeat(np.linspace(0, F - 1, 32).astype(np.int64), 3)
