@@ -1445,12 +1445,13 @@ replay_warp_kernel(const SearchParams S, const uint32_t *__restrict__ bits, cons
   }
 }
 
-// The inner wavefront of a component above IW_SMALL cells: one warp, ONE dequeued cell per step, lane s < 8 takes its
-// neighbour s in the reference's order.  Components of this class are long and thin (arcs of sensor discs: 1-2 cells per
-// level for thousands of levels), so what bounds them is the latency of a step; a step here is a shared-memory read of
-// the queue head (the queue's tail is mirrored in a ring), a mask-bit load, a load of the neighbour's visited flag (the
-// top bit of its slot[] word: slot[] is rewritten by every search, and a cell belongs to one component only) and a
-// ballot that appends the accepted neighbours in slot order.  Exactly buildNewFrontier's loop (FrontierSearch.cpp:123-189).
+// The inner wavefront of a component above IW_SMALL cells: one warp walks buildNewFrontier's loop (FrontierSearch.cpp:123-189),
+// one or two dequeued cells per step, lane s of a group of 8 takes neighbour s in the reference's order.  Components of this
+// class are long and thin (arcs of sensor discs: 1-2 cells per level for thousands of levels), so what bounds them is the
+// latency of a step: a shared-memory read of the queue head (the queue's tail is mirrored in a ring), a mask-bit load, the
+// visited test and a ballot that appends the accepted neighbours in slot order.  While the last three levels hold at most 64
+// cells the visited test is a search of the ring (see the loop); wider levels read the visited flag in the top bit of the
+// cell's slot[] word (slot[] is rewritten by every search, and a cell belongs to one component only).
 static constexpr uint32_t IL_RING = 2048;
 static constexpr uint32_t IL_VISITED = 0x80000000u;
 __global__ void __launch_bounds__(32)
