@@ -36,7 +36,7 @@ struct CycleState {
   // per early launch (index = the launch's tag); work_final: counter + list of the launch after the search.  hist[] = how many
   // frontiers each early launch had in the last cycle: the next cycle sizes its grids from it (the host cannot know the
   // counts of a search that is still running; what a grid does not cover is scored after the search).
-  static constexpr uint32_t WORK_LAUNCHES = 64, WORK_LIST = 8192;
+  static constexpr uint32_t WORK_LAUNCHES = 128, WORK_LIST = 8192;
   DevBuf<uint32_t> work, work_final;
   uint32_t *h_work = nullptr;  // pinned: WORK_LAUNCHES + 1
   uint32_t hist[WORK_LAUNCHES] = {};

@@ -56,7 +56,10 @@ static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 8;
 // goes on: the long thin components that bound the replay time are usually touched long before it ends.  (Separate
 // launches per part were tried first: once the side streams fill the other SMs, the next part waits for a whole SM.)
 static constexpr int OW_LARGE_STREAMS = 4;
-static constexpr int OW_PARTS = 16;          // levels per part: search radius in cells / OW_PARTS (SearchParams::ow_part_levels)
+#ifndef FS_OW_PARTS
+#define FS_OW_PARTS 16
+#endif
+static constexpr int OW_PARTS = FS_OW_PARTS;          // levels per part: search radius in cells / OW_PARTS (SearchParams::ow_part_levels)
 static constexpr uint32_t IW_CELLS = 4096;   // inner wavefront: largest component replayed out of shared memory
 static constexpr uint32_t IW_SMALL = 128;    // size classes: <= IW_SMALL cells (many warps per SM), <= IW_CELLS cells (two per SM)
 static constexpr uint32_t IW_BITS_SMALL = 1024, IW_BITS_LARGE = 8192;  // words of the component's mask window held in shared memory
