@@ -23,6 +23,7 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
@@ -153,6 +154,7 @@ struct FrontierState {
                                       // warp walks a thin component for up to milliseconds, and must not hold up the next collection
   cudaStream_t score_stream[1 + OW_LARGE_STREAMS] = {};  // low priority: early scoring (cycle.cu's hook), [0] small class, [1 + i] behind stream_large[i]
   uint32_t ow_parts = OW_PARTS;    // FITSLAM_OW_PARTS=1: one launch, no overlap (ablation)
+  double host_enqueue_ms = 0;      // FITSLAM_PROF: host time spent enqueuing the side work of a search
   bool have_ev = false;
   bool attr_set = false;
   int force_global = -1;      // FITSLAM_WAVEFRONT=global selects the global-memory wavefront kernels (ablation / fallback test)
@@ -2146,11 +2148,13 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
       ow_kernel<false><<<1, OW_THREADS, OW_SMEM, c->stream>>>(S, L, s->rk.p, s->claim.p, s->queue.p, cnt, n_parts);
     ++c->launches;
     FS_CUDA(c, cudaGetLastError());  // (the kernels below poll flags only this one sets)
+    const auto host_t0 = std::chrono::steady_clock::now();
     for (uint32_t part = 0; part + 1 < n_parts; ++part) {
       wait_part_kernel<<<1, 1, 0, s->stream2>>>(cnt, part);
       ++c->launches;
       FS_CUDA(c, collect(s->stream2, s->stream_large[part % OW_LARGE_STREAMS], (int)part));
     }
+    s->host_enqueue_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
     FS_CUDA(c, cudaEventRecord(s->ev_bfs[1], c->stream));
     if (n_parts > 1) {  // the kernels below rewrite or rescan what the collections' table kernels read
       FS_CUDA(c, cudaEventRecord(s->ev_join, s->stream2));
@@ -2307,6 +2311,7 @@ fitslam_status frontier_search_device(fitslam_ctx *c, double rx, double ry, cons
       fprintf(stderr, "context stream, ms: outer wavefront %.3f | wait for the collections %.3f | fallback kernels %.3f | last collection + "
                       "large inner wavefronts %.3f | frontiers of the rest, cleanup %.3f | wait for the early scoring %.3f\n",
               t[0], t[1], t[2], t[3], t[4], t[5]);
+      fprintf(stderr, "host: %.3f ms to enqueue the work behind the parts of the outer wavefront\n", s->host_enqueue_ms);
       fprintf(stderr, "collections (cells dequeued | frontiers):");
       for (int k = 0; k < OW_PARTS; ++k) fprintf(stderr, " %u|%u", hc->part_end[k], hc->coll_fr[k][1] - hc->coll_fr[k][0]);
       fprintf(stderr, "\n");
