@@ -995,7 +995,9 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
         bool collide = false;
         uint32_t c_key = 0;
         float inf_v = 0.f;
-        if (vox >= 0 && (npass == 1 || ((mix32((uint32_t)vox) >> 12) & (npass - 1)) == pass)) {
+        bool mine = vox >= 0;
+        if (npass != 1) mine = mine && ((mix32((uint32_t)vox) >> 12) & (npass - 1)) == pass;  // (uniform branch: one pass is the rule)
+        if (mine) {
           ++my_used;
           if (!*v_overflow) {  // a lost attempt keeps counting only
             inf_v = __ldg(P.lut + vox);
@@ -1003,7 +1005,9 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
               const uint32_t w = (uint32_t)bit >> 5, m = 1u << (bit & 31);
               uint32_t old = ((volatile uint32_t *)bm)[w];
               if (!(old & m)) old = atomicOr(&bm[w], m);
-              if (!(old & m)) total += (double)inf_v;  // first landmark of its voxel: factor exp(1 - 1^s) = 1
+              // first landmark of its voxel: factor exp(1 - 1^s) = 1.  (In double: which thread meets which landmark changes from
+              // run to run, and only a double sum rounds to the same float whatever the order; a float partial sum was tried.)
+              if (!(old & m)) total += (double)inf_v;
               else { collide = true; c_key = (uint32_t)vox; }
             } else {
               collide = true;
@@ -1070,7 +1074,9 @@ fisher_kernel(const FisherParams P, const fitslam_pose *__restrict__ poses, floa
               const float rx = lx * P.inv_step_f, ry = ly * P.inv_step_f, rz = lz * P.inv_step_f;
               const float fx_ = rintf(rx), fy_ = rintf(ry), fz_ = rintf(rz);
               const float edge = fmaxf(fmaxf(fabsf(rx - fx_), fabsf(ry - fy_)), fabsf(rz - fz_));
-              if (edge < 0.5f - F.gvox && fmaxf(fmaxf(fabsf(rx), fabsf(ry)), fabsf(rz)) < 512.0f) {
+              // (an index inside the table implies |r| < 512, which is what the guard's bound on the float product assumes; the
+              // conversion saturates for huge values and `finite` has kept NaNs out)
+              if (edge < 0.5f - F.gvox) {
                 const int i0_ = (int)fx_ - P.org[0], i1_ = (int)fy_ - P.org[1], i2_ = (int)fz_ - P.org[2];
                 if ((unsigned)i0_ < (unsigned)P.dims[0] && (unsigned)i1_ < (unsigned)P.dims[1] && (unsigned)i2_ < (unsigned)P.dims[2]) {
                   vox = (i0_ * P.dims[1] + i1_) * P.dims[2] + i2_;
