@@ -1096,7 +1096,7 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
       const uint32_t total = __reduce_add_sync(0xffffffffu, wv);
       const uint32_t wbase = __reduce_add_sync(0xffffffffu, lane < wid ? wv : 0u);
       uint32_t dst = n_local + wbase + excl;
-      if (n_local + total > OWC_SLICE) bad = true;  // (uniform in the CTA)
+      if (n_local + total > min(OWC_SLICE, S.ow_qcap)) bad = true;  // (uniform in the CTA; FITSLAM_OW_QCAP lowers the limit in tests)
       else {
 #pragma unroll
         for (int k = 0; k < 4; ++k)

@@ -143,6 +143,35 @@ def test_search_wide_levels_fall_back(capi, oracle, monkeypatch, wide):
     _compare(capi, oracle, a, meta, 0.0, 0.0, dict(max_frontier_distance=250.0))
 
 
+@pytest.mark.parametrize("name", ["C1", "C3", "C2"])
+def test_search_on_the_cluster_wavefront(capi, oracle, synth, name, monkeypatch):
+    # FITSLAM_OW_CLUSTER_MIN=1: every search runs on the thread-block cluster kernel, whatever the width of its levels (the
+    # default keeps narrow searches on one CTA)
+    monkeypatch.setenv("FITSLAM_OW_CLUSTER_MIN", "1")
+    a, meta, pts, ov = synth.make_config(name, reference_rays=True)
+    _compare(capi, oracle, a, meta, meta["robot_x"], meta["robot_y"], ov)
+    ctx = capi.Context(synth.apply_overrides(capi.default_params(), ov))
+    try:
+        ctx.set_costmap(a, meta["res"], meta["ox"], meta["oy"])
+        ctas = [ctx.cycle(meta["robot_x"], meta["robot_y"], 0.0, meta["poly"], capi.FISHER_OFF)[1].wavefront_ctas for _ in range(2)]
+        assert all(n in (8, 16) for n in ctas), ctas
+    finally:
+        ctx.close()
+
+
+def test_search_cluster_wavefront_falls_back(capi, oracle, monkeypatch):
+    # the cluster wavefront forced on the same open map with a winner list of 100 entries per CTA: the level in which a CTA
+    # appends more than that ends the kernel, and the global-memory wavefront reruns the search (the touch keys already written
+    # are the ones it writes again)
+    monkeypatch.setenv("FITSLAM_OW_CLUSTER_MIN", "1")
+    monkeypatch.setenv("FITSLAM_OW_QCAP", "100")
+    W = H = 3000
+    a = np.full((H, W), 255, np.uint8)
+    a[200:2800, 200:2800] = 0
+    meta = dict(res=0.0625, ox=-93.75, oy=-93.75)
+    _compare(capi, oracle, a, meta, 0.0, 0.0, dict(max_frontier_distance=250.0))
+
+
 @pytest.mark.parametrize("shape", ["h", "v", "square"])
 def test_search_straight_frontiers_at_5cm(capi, oracle, shape):
     # straight axis-aligned frontiers found from their middle at the reference's resolution (0.05 m): the chunks are two
