@@ -162,11 +162,24 @@ class GpuJob:
         self.last["res"] = res
         return res
 
+    def _result_buffers(self, n_frontiers, n_poses):
+        """Pinned host buffers for the results, kept between steps as a caller of the C ABI would (grown when a cycle finds
+        more frontiers than they hold)."""
+        torch = self.torch
+        b = getattr(self, "_buf", None)
+        if b is None or len(b["frontiers"]) < n_frontiers or len(b["candidate_fisher"]) < n_poses:
+            def pinned(n, dtype):
+                t = torch.empty(max(n, 1) * np.dtype(dtype).itemsize, dtype=torch.uint8).pin_memory()
+                return t.numpy().view(dtype)
+            self._buf = b = self.capi.Context.fetch_buffers(2 * n_frontiers, 2 * max(n_poses, 1), alloc=pinned)
+        return b
+
     def e2e_step(self):
         self.upload()
         res = self.cycle()
-        out = self.ctx.cycle_fetch(res.n_frontiers)
-        info, safe, nvis = self.ctx.cycle_fetch_candidates(res.n_fisher_poses)  # every (frontier, yaw) candidate's Fisher result
+        buf = self._result_buffers(res.n_frontiers, res.n_fisher_poses)
+        out = self.ctx.cycle_fetch(res.n_frontiers, out=buf)
+        info, safe, nvis = self.ctx.cycle_fetch_candidates(res.n_fisher_poses, out=buf)  # every (frontier, yaw) candidate's Fisher result
         out.update(candidate_fisher=info, candidate_safe=safe, candidate_landmarks=nvis)
         self.last["out"] = out
         return res

@@ -459,23 +459,43 @@ class Context:
         self._check(self.lib.fitslam_cycle_end(self.h, C.byref(res)))
         return res
 
-    def cycle_fetch(self, n):
-        fr = np.zeros(n, dtype=FRONTIER_DTYPE)
-        ar = np.zeros(n, dtype=ARRIVAL_DTYPE)
-        pl, ph, wc = (np.zeros(n, dtype=np.float64) for _ in range(3))
-        fi = np.zeros(n, dtype=np.float32)
-        srt = np.zeros(n, dtype=np.uint32)
-        self._check(self.lib.fitslam_cycle_fetch(self.h, _ptr(fr), _ptr(ar), _ptr(pl), _ptr(ph), _ptr(wc), _ptr(fi),
-                                                 _ptr(srt), n))
-        return dict(frontiers=fr, arrival=ar, path_length_m=pl, path_heading=ph, weighted_cost=wc, fisher=fi, sorted=srt)
+    @staticmethod
+    def fetch_buffers(capacity, n_poses=0, alloc=np.zeros):
+        """Host buffers for cycle_fetch / cycle_fetch_candidates that a caller keeps between cycles (`alloc(n, dtype=...)`:
+        np.zeros, or an allocator of pinned memory)."""
+        b = dict(frontiers=alloc(capacity, dtype=FRONTIER_DTYPE), arrival=alloc(capacity, dtype=ARRIVAL_DTYPE),
+                 path_length_m=alloc(capacity, dtype=np.float64), path_heading=alloc(capacity, dtype=np.float64),
+                 weighted_cost=alloc(capacity, dtype=np.float64), fisher=alloc(capacity, dtype=np.float32),
+                 sorted=alloc(capacity, dtype=np.uint32))
+        if n_poses:
+            b.update(candidate_fisher=alloc(n_poses, dtype=np.float32), candidate_safe=alloc(n_poses, dtype=np.uint8),
+                     candidate_landmarks=alloc(n_poses, dtype=np.uint32))
+        return b
 
-    def cycle_fetch_candidates(self, n_poses):
-        """Per-candidate Fisher results of the last cycle: (information, safe, n_visible), pose = frontier * ppf + window."""
-        info = np.zeros(n_poses, dtype=np.float32)
-        safe = np.zeros(n_poses, dtype=np.uint8)
-        nvis = np.zeros(n_poses, dtype=np.uint32)
+    def cycle_fetch(self, n, out=None):
+        """Results of the last cycle for its n frontiers.  `out`: buffers from fetch_buffers() to fill (views of the first n
+        entries are returned); default: fresh arrays."""
+        if out is not None and len(out["frontiers"]) < n:
+            raise FitslamError(E_CAPACITY, "cycle_fetch: the caller's buffers hold fewer than n frontiers")
+        b = out if out is not None else self.fetch_buffers(n)
+        fr, ar, pl, ph, wc, fi, srt = (b[k] for k in ("frontiers", "arrival", "path_length_m", "path_heading", "weighted_cost",
+                                                       "fisher", "sorted"))
+        self._check(self.lib.fitslam_cycle_fetch(self.h, _ptr(fr), _ptr(ar), _ptr(pl), _ptr(ph), _ptr(wc), _ptr(fi),
+                                                 _ptr(srt), len(fr)))
+        return dict(frontiers=fr[:n], arrival=ar[:n], path_length_m=pl[:n], path_heading=ph[:n], weighted_cost=wc[:n], fisher=fi[:n],
+                    sorted=srt[:n])
+
+    def cycle_fetch_candidates(self, n_poses, out=None):
+        """Per-candidate Fisher results of the last cycle: (information, safe, n_visible), pose = frontier * ppf + window.
+        `out`: buffers from fetch_buffers(..., n_poses) to fill."""
+        if out is not None and len(out["candidate_fisher"]) >= n_poses:
+            info, safe, nvis = out["candidate_fisher"], out["candidate_safe"], out["candidate_landmarks"]
+        else:
+            info = np.zeros(n_poses, dtype=np.float32)
+            safe = np.zeros(n_poses, dtype=np.uint8)
+            nvis = np.zeros(n_poses, dtype=np.uint32)
         n = C.c_uint32()
-        self._check(self.lib.fitslam_cycle_fetch_candidates(self.h, _ptr(info), _ptr(safe), _ptr(nvis), n_poses, C.byref(n)))
+        self._check(self.lib.fitslam_cycle_fetch_candidates(self.h, _ptr(info), _ptr(safe), _ptr(nvis), len(info), C.byref(n)))
         return info[:n.value], safe[:n.value], nvis[:n.value]
 
     def records_tensor(self):
