@@ -106,7 +106,8 @@ struct SearchParams {
   uint32_t use_smem;       // 1: shared-memory wavefronts first, global-memory kernels only for what does not fit
   uint32_t ow_wide;        // 1: levels wider than ow_qcap spill to the global queue (maps up to 16384 cells a side)
   uint32_t ow_qcap;        // widest level the shared-memory outer wavefront keeps (<= OW_QCAP; FITSLAM_OW_QCAP lowers it in tests)
-  uint32_t ow_part_levels; // levels per launch of the shared-memory outer wavefront
+  uint32_t ow_part_levels; // levels per part of the outer wavefront where the schedule below is not used (first search on a map)
+  uint32_t ow_part_end[OW_PARTS];  // part k of the outer wavefront ends when this many levels are done (ascending; see enqueue_search)
   uint32_t early_cap;      // frontiers one early scoring launch covers (what exceeds it waits for the launches after the search)
   uint32_t early_limit;    // frontier indices at or above this are not scored early (EarlyHook::limit)
   uint32_t fix_all;        // FITSLAM_FIX_ALL=1: every chunk's median sort goes to the host (test of that path)
@@ -912,7 +913,7 @@ ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim,
     rk[si] = 0;  // visited_flag[bfs.front()] = true (FrontierSearch.cpp:56), whatever its class
   }
   __syncthreads();
-  uint32_t next_part_level = S.ow_part_levels;
+  uint32_t next_part_level = S.ow_part_end[0];
   OwProf pf;
 #ifdef FITSLAM_OW_PROF
   for (int k = 0; k < 8; ++k) pf.acc[k] = 0;
@@ -949,7 +950,7 @@ ow_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t *claim,
         atomicExch(&cnt->part_flag[part], 1u);
       }
       ++part;
-      next_part_level += S.ow_part_levels;
+      next_part_level = S.ow_part_end[min(part, (uint32_t)OW_PARTS - 1u)];
     }
   }
   publish(part, base);
@@ -1031,7 +1032,7 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
   }
   cluster.sync();
   uint32_t base = 0, levels = 0, part = 0, widest = 1, cur = 0, scans = 0;
-  uint32_t next_part_level = S.ow_part_levels;
+  uint32_t next_part_level = S.ow_part_end[0];
   bool bad = false;
   OwProf pf;
 #ifdef FITSLAM_OW_PROF
@@ -1124,7 +1125,7 @@ ow_cluster_kernel(const SearchParams S, const OwLayout L, uint16_t *rk, uint32_t
         atomicExch(&cnt->part_flag[part], 1u);
       }
       ++part;
-      next_part_level += S.ow_part_levels;
+      next_part_level = S.ow_part_end[min(part, (uint32_t)OW_PARTS - 1u)];
     }
   }
   publish(part, base);
@@ -1974,6 +1975,26 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
   if (const char *e = getenv("FITSLAM_EARLY_CAP")) S.early_cap = (uint32_t)std::min<long>(std::max<long>(atol(e), 1), 8192);
   S.early_limit = hook ? hook->limit : 0xFFFFFFFFu;
   S.ow_part_levels = (uint32_t)std::min<double>(std::max<double>(S.dist_limit / c->res / OW_PARTS, 64.0), 1e6);
+  {
+    // When the parts end.  First search on a map: every ow_part_levels levels (the search radius in cells / OW_PARTS).  After
+    // that the number of levels is known from the last search, and the boundaries crowd towards its end: what is found after
+    // the last boundary waits for the search to finish before anything of it can be scored, and on wide maps a fifth of the
+    // frontiers used to be found there.  (A search shorter than the last one just never reaches the late boundaries.)
+    const uint32_t known = s->last.bfs_levels;
+    static const double late[4] = {0.85, 0.92, 0.965, 0.99};
+    uint32_t prev = 0;
+    for (int k = 0; k < OW_PARTS; ++k) {
+      uint32_t e;
+      const int n_uniform = OW_PARTS - 1 - 4;  // boundaries 0 .. n_uniform - 1 share the first 3/4 of the levels
+      if (!known || OW_PARTS < 8) e = (uint32_t)(k + 1) * S.ow_part_levels;
+      else if (k < n_uniform) e = (uint32_t)((k + 1) * 0.75 * known / n_uniform);
+      else if (k < OW_PARTS - 1) e = (uint32_t)(late[k - n_uniform] * known);
+      else e = 0xFFFFFFFFu;
+      e = std::max(e, prev + 16u);
+      S.ow_part_end[k] = e;
+      prev = e;
+    }
+  }
   S.ow_wide = getenv("FITSLAM_OW_NOWIDE") ? 0u : 1u;
   S.fix_all = getenv("FITSLAM_FIX_ALL") ? 1u : 0u;
   S.use_smem = (s->force_global || c->W > 16384u || c->H > 16384u) ? 0u : 1u;  // queue entries pack x | y << 14 | mask << 28
