@@ -1981,7 +1981,8 @@ static fitslam_status enqueue_search(fitslam_ctx *c, FrontierState *s, uint32_t 
     // the last boundary waits for the search to finish before anything of it can be scored, and on wide maps a fifth of the
     // frontiers used to be found there.  (A search shorter than the last one just never reaches the late boundaries.)
     const uint32_t known = s->last.bfs_levels;
-    static const double late[4] = {0.85, 0.92, 0.965, 0.99};
+    double late[4] = {0.85, 0.92, 0.965, 0.99};
+    if (const char *e = getenv("FITSLAM_OW_LATE")) sscanf(e, "%lf,%lf,%lf,%lf", &late[0], &late[1], &late[2], &late[3]);  // (tuning)
     uint32_t prev = 0;
     for (int k = 0; k < OW_PARTS; ++k) {
       uint32_t e;
