@@ -51,8 +51,8 @@ static constexpr int MAX_CHUNK = 64;  // max_frontier_cluster_size + 1 <= 64
 // components that do not fit)
 static constexpr uint32_t OW_QCAP = 8192;    // outer wavefront: widest level the shared-memory queue holds (128 KB; the rest of the SM's 256 KB stays L1)
 static constexpr uint32_t OW_SMEM = 2 * OW_QCAP * 8;
-// The outer wavefront publishes its progress every ow_part_levels levels (OW_PARTS - 1 times at most; the last part runs
-// to the end).  After part k the components it touched have their final seed (later touches carry larger keys), so
+// The outer wavefront publishes its progress OW_PARTS - 1 times at most, at the level counts of SearchParams::ow_part_end (the
+// last part runs to the end).  After part k the components it touched have their final seed (later touches carry larger keys), so
 // their inner wavefronts replay on side streams, behind a one-thread kernel that polls the flag, while the wavefront
 // goes on: the long thin components that bound the replay time are usually touched long before it ends.  (Separate
 // launches per part were tried first: once the side streams fill the other SMs, the next part waits for a whole SM.)
