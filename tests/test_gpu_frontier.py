@@ -143,6 +143,27 @@ def test_search_wide_levels_fall_back(capi, oracle, monkeypatch, wide):
     _compare(capi, oracle, a, meta, 0.0, 0.0, dict(max_frontier_distance=250.0))
 
 
+@pytest.mark.parametrize("thr", [1, 100, 127, 128, 129, 200, 253, 254, 255])
+def test_search_lethal_thresholds(capi, oracle, thr):
+    # the mask kernel compares four cost bytes at a time against the lethal threshold: every kind of threshold the context
+    # admits (1 .. 254: below / at / above 128, the ends of the range) on a map that holds every cost value, odd width
+    if thr > 254:
+        p = capi.default_params()
+        p.lethal_threshold = thr
+        with pytest.raises(capi.FitslamError):
+            capi.Context(p)
+        return
+    rng = np.random.default_rng(thr)
+    H, W = 203, 301
+    a = rng.integers(0, 256, size=(H, W)).astype(np.uint8)
+    a[rng.random((H, W)) < 0.35] = 255
+    a[rng.random((H, W)) < 0.35] = 0
+    a[90:110, 140:160] = 0  # the robot stands in free space
+    meta = dict(res=0.05, ox=-7.5, oy=-5.0)
+    _compare(capi, oracle, a, meta, meta["ox"] + 150.5 * 0.05, meta["oy"] + 100.5 * 0.05,
+             dict(lethal_threshold=thr, max_frontier_distance=30.0), expect_frontiers=False)
+
+
 @pytest.mark.parametrize("name", ["C1", "C3", "C2"])
 def test_search_on_the_cluster_wavefront(capi, oracle, synth, name, monkeypatch):
     # FITSLAM_OW_CLUSTER_MIN=1: every search runs on the thread-block cluster kernel, whatever the width of its levels (the
